@@ -1,0 +1,348 @@
+/*
+ * tfs_gpu.h — C ABI of the B200-native TensorProto / PredictRequest / PredictResponse wire codec.
+ *
+ * This is the drop-in boundary for the ONE hot path of simonrw/rust-tensorflow-serving2: the prost
+ * encode / decode that tonic's ProstCodec runs around `self.prediction_client.predict(request)`
+ * (reference src/lib.rs:265; message built at src/lib.rs:229-263; wire contract in
+ * protos/tensorflow/core/framework/tensor.proto:14-84, tensor_shape.proto:13-46, types.proto:12-68,
+ * protos/tensorflow_serving/apis/predict.proto:12-40, model.proto:9-33).  The reference has no FFI of
+ * its own; these are the symbols a `GpuCodec: tonic::codec::Codec` in src/lib.rs would bind through
+ * `extern "C"` (see INTEGRATION.md for the Rust stub and rust/ for the shim sources).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no C++/torch types; every function returns a tfs_status_t
+ *     and never throws or aborts across the boundary.
+ *   - one tfs_ctx_t per GPU (one process per GPU); a ctx is NOT re-entrant: serialise calls on one
+ *     ctx, use several ctxs for several streams/threads.
+ *   - "device pointer" = memory the GPU can address (cudaMalloc'd / torch CUDA tensor storage).
+ *     "host pointer" = ordinary host memory; the *_host entry points stage it through the ctx's
+ *     pinned slabs (host<->device copies are inside those calls).
+ *   - output bytes are byte-identical to prost 0.6.0's encoding of the same message with map entries
+ *     in the caller's order; decoded values are value-identical.
+ *   - there is no CPU fallback anywhere behind this header: without a usable CUDA device every
+ *     compute entry point fails with TFS_ERR_CUDA.
+ */
+#ifndef TFS_GPU_H_
+#define TFS_GPU_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TFS_ABI_VERSION 1
+#define TFS_MAX_DIMS 8   /* dims carried inline per tensor; larger ranks -> TFS_ERR_UNSUPPORTED */
+#define TFS_N_SLOTS 12   /* payload field slots of a TensorProto, see tfs_slot_of_kind() */
+
+typedef int32_t tfs_status_t;
+typedef struct tfs_ctx tfs_ctx_t;
+typedef struct tfs_decoded tfs_decoded_t;
+
+/* Status codes. The decode codes mirror prost 0.6.0 DecodeError descriptions so the
+ * Rust shim can rebuild the same `Status::internal(..)` text tonic's ProstDecoder would produce. */
+enum {
+  TFS_OK = 0,
+  TFS_ERR_INVALID_VARINT = 1,   /* "invalid varint" */
+  TFS_ERR_BUFFER_UNDERFLOW = 2, /* "buffer underflow" */
+  TFS_ERR_LENGTH_EXCEEDED = 3,  /* "delimited length exceeded" */
+  TFS_ERR_WIRE_TYPE = 4,        /* "invalid wire type: X (expected Y)" */
+  TFS_ERR_WIRE_TYPE_VALUE = 5,  /* "invalid wire type value: N" (6, 7) */
+  TFS_ERR_INVALID_KEY = 6,      /* "invalid key value: N" (key > u32::MAX) */
+  TFS_ERR_INVALID_TAG = 7,      /* "invalid tag value: 0" */
+  TFS_ERR_RECURSION = 8,        /* "recursion limit reached" */
+  TFS_ERR_END_GROUP = 9,        /* "unexpected end group tag" */
+  TFS_ERR_UTF8 = 10,            /* "invalid string value: data is not UTF-8 encoded" */
+  TFS_ERR_GRPC_FLAG = 11,       /* gRPC frame: compressed flag != 0 (tonic: Unimplemented / Internal) */
+  TFS_ERR_UNSUPPORTED = 12,     /* valid wire, but uses something this library leaves to prost
+                                   (variant_val, resource_handle_val, rank > TFS_MAX_DIMS, dim names) */
+  TFS_ERR_INVALID_ARG = 20,
+  TFS_ERR_NOMEM = 21,           /* dst / pool capacity too small, or allocation failed */
+  TFS_ERR_CUDA = 22,            /* CUDA runtime error; tfs_last_error_detail() has the text */
+  TFS_ERR_BATCH = 23            /* at least one message of the batch failed; see per-message status */
+};
+
+/* TensorProto payload fields, numbered by their proto field number (tensor.proto:36-83). */
+enum {
+  TFS_KIND_NONE = 0,
+  TFS_KIND_TENSOR_CONTENT = 4, /* bytes */
+  TFS_KIND_FLOAT_VAL = 5,      /* packed fixed32 */
+  TFS_KIND_DOUBLE_VAL = 6,     /* packed fixed64 */
+  TFS_KIND_INT_VAL = 7,        /* packed varint, int32 sign-extended */
+  TFS_KIND_STRING_VAL = 8,     /* repeated bytes (not packed) */
+  TFS_KIND_SCOMPLEX_VAL = 9,   /* packed fixed32 */
+  TFS_KIND_INT64_VAL = 10,     /* packed varint */
+  TFS_KIND_BOOL_VAL = 11,      /* packed varint 0/1 */
+  TFS_KIND_DCOMPLEX_VAL = 12,  /* packed fixed64 */
+  TFS_KIND_HALF_VAL = 13,      /* packed varint of the 16-bit pattern held in an int32 */
+  TFS_KIND_UINT32_VAL = 16,    /* packed varint */
+  TFS_KIND_UINT64_VAL = 17     /* packed varint */
+};
+
+/* In-memory element types (little-endian, dense). */
+enum {
+  TFS_T_NONE = 0,
+  TFS_T_U8 = 1,
+  TFS_T_I8 = 2,
+  TFS_T_U16 = 3,
+  TFS_T_I16 = 4,
+  TFS_T_I32 = 5,
+  TFS_T_U32 = 6,
+  TFS_T_I64 = 7,
+  TFS_T_U64 = 8,
+  TFS_T_F16 = 9,   /* IEEE binary16 bit pattern */
+  TFS_T_BF16 = 10, /* bfloat16 bit pattern */
+  TFS_T_F32 = 11,
+  TFS_T_F64 = 12,
+  TFS_T_BOOL = 13  /* one byte per element, non-zero = true (Rust `bool`) */
+};
+
+/* Arithmetic fused into the u8 -> f32 widening of float_val (reference src/lib.rs:237-242:
+ * `*p as f32` followed by the user's preprocessing_fn; examples/prediction.rs:43 uses `v / 255.`). */
+enum {
+  TFS_OP_NONE = 0,
+  TFS_OP_DIV = 1, /* y = (float)x / param   (IEEE round-to-nearest division) */
+  TFS_OP_MUL = 2  /* y = (float)x * param */
+};
+
+enum {
+  TFS_MSG_TENSOR_PROTO = 0,     /* bare tensorflow.TensorProto */
+  TFS_MSG_PREDICT_REQUEST = 1,  /* predict.proto:12-31 */
+  TFS_MSG_PREDICT_RESPONSE = 2  /* predict.proto:34-40 */
+};
+
+enum { TFS_VERSION_NONE = 0, TFS_VERSION_NUMBER = 1, TFS_VERSION_LABEL = 2 }; /* model.proto:22-28 */
+
+/* Encode / decode flags. */
+enum {
+  TFS_F_GRPC_PREFIX = 1u << 0,   /* encode: write tonic's 5-byte frame prefix (00 + u32 BE length) in
+                                    front of every message; decode: each message starts with it */
+  TFS_F_ALIGN_PAYLOAD = 1u << 1, /* encode: place each message so that its largest bulk payload starts
+                                    on a 16-byte boundary of dst (messages are then not back-to-back) */
+  TFS_F_HALF_TO_F32 = 1u << 2,   /* decode: half_val of a DT_HALF(19)/DT_BFLOAT16(14) tensor is widened
+                                    to f32 instead of prost's Vec<i32> */
+  TFS_F_CONTENT_HALF_TO_F32 = 1u << 3 /* decode: tensor_content of a DT_HALF/DT_BFLOAT16 tensor is
+                                    widened to f32 */
+};
+
+typedef struct {
+  uint64_t off; /* byte offset into the blob the span refers to */
+  uint32_t len;
+  uint32_t _pad;
+} tfs_span_t;
+
+typedef struct {
+  const char* ptr; /* host pointer, not NUL-terminated */
+  uint32_t len;
+  uint32_t _pad;
+} tfs_str_t;
+
+/* ----------------------------------------------------------------------------------------------
+ * Encode-side descriptors: a plain-data picture of the prost structs the reference builds at
+ * src/lib.rs:249-263 (TensorProto, then the `inputs` map, then PredictRequest).
+ * -------------------------------------------------------------------------------------------- */
+
+/* One payload field of a TensorProto (`float_val: pixels` at src/lib.rs:252). */
+typedef struct {
+  int32_t kind;     /* TFS_KIND_* */
+  int32_t src_type; /* TFS_T_* of the memory at `data` */
+  int32_t dst_type; /* element type that goes on the wire; TFS_T_NONE = the field's natural type.
+                       Allowed conversions: identical; U8->F32 (float_val, with op); F32->F16 / F32->BF16
+                       (half_val or tensor_content, round-to-nearest-even, NaN kept quiet with sign);
+                       F16/BF16/U16 -> half_val pattern; I8/U8/I16/U16 -> I32 (int_val). */
+  int32_t op;       /* TFS_OP_* (only with U8->F32) */
+  float op_param;
+  uint32_t _pad;
+  uint64_t n_elems; /* number of source elements (bytes for raw tensor_content with src_type U8) */
+  const void* data; /* device pointer for tfs_encode, host pointer for tfs_encode_host */
+} tfs_field_desc_t;
+
+/* One TensorProto together with the map key it is stored under (src/lib.rs:256-257). */
+typedef struct {
+  tfs_str_t name;          /* map key; ignored for TFS_MSG_TENSOR_PROTO */
+  int32_t dtype;           /* DataType enum value (types.proto:12-68); 0 is omitted like prost does */
+  int32_t version_number;  /* tensor.proto:29 */
+  int32_t has_shape;       /* Option<TensorShapeProto> is Some (always at src/lib.rs:251) */
+  int32_t unknown_rank;    /* tensor_shape.proto:45 */
+  uint32_t n_dims;         /* <= TFS_MAX_DIMS; Dim.name is always "" (src/lib.rs:233) */
+  uint32_t first_field;    /* index into tfs_batch_t.fields */
+  uint32_t n_fields;       /* payload fields of this tensor, any order, at most one per kind */
+  uint32_t _pad;
+  int64_t dims[TFS_MAX_DIMS];
+} tfs_tensor_desc_t;
+
+/* One message of the batch (src/lib.rs:259-263; ModelSpec from build_model_spec, src/lib.rs:433-447). */
+typedef struct {
+  int32_t kind;            /* TFS_MSG_* */
+  int32_t has_model_spec;  /* Option<ModelSpec> is Some */
+  tfs_str_t model_name;
+  tfs_str_t signature_name;
+  tfs_str_t version_label;
+  int32_t version_choice;  /* TFS_VERSION_* */
+  uint32_t _pad;
+  int64_t version;
+  uint32_t first_tensor;   /* map entries in the order they are to be emitted */
+  uint32_t n_tensors;
+  uint32_t first_filter;   /* PredictRequest.output_filter, index into tfs_batch_t.filters */
+  uint32_t n_filters;
+} tfs_msg_desc_t;
+
+typedef struct {
+  const tfs_msg_desc_t* msgs;
+  const tfs_tensor_desc_t* tensors;
+  const tfs_field_desc_t* fields;
+  const tfs_str_t* filters;
+  uint32_t n_msgs;
+  uint32_t n_tensors;
+  uint32_t n_fields;
+  uint32_t n_filters;
+} tfs_batch_t;
+
+/* ----------------------------------------------------------------------------------------------
+ * Decode-side results: what prost's derived `merge` leaves in PredictResponse / PredictRequest /
+ * TensorProto, as plain data.  Spans point into tfs_decoded_view_t.strings.
+ * -------------------------------------------------------------------------------------------- */
+
+typedef struct {
+  tfs_span_t key;          /* map key ("" when the entry had none) */
+  uint32_t msg_index;
+  int32_t dtype;
+  int32_t version_number;
+  int32_t has_shape;
+  int32_t unknown_rank;
+  uint32_t n_dims;
+  int64_t dims[TFS_MAX_DIMS];
+  uint64_t n_elems[TFS_N_SLOTS]; /* elements per payload slot (bytes for tensor_content) */
+  uint64_t dst_off[TFS_N_SLOTS]; /* byte offset of that slot's values inside the pool */
+  int32_t dst_type[TFS_N_SLOTS]; /* TFS_T_* the values are written as */
+} tfs_tensor_out_t;
+
+typedef struct {
+  tfs_status_t status;     /* TFS_OK or the decode error of this message */
+  int32_t has_model_spec;
+  uint64_t err_offset;     /* byte offset (within the message) where the error was detected */
+  tfs_span_t model_name;
+  tfs_span_t signature_name;
+  tfs_span_t version_label;
+  int32_t version_choice;
+  uint32_t _pad;
+  int64_t version;
+  uint32_t first_tensor;   /* map entries in wire order; a repeated key means "last wins" */
+  uint32_t n_tensors;
+  uint32_t first_filter;
+  uint32_t n_filters;
+} tfs_msg_out_t;
+
+typedef struct {
+  const tfs_msg_out_t* msgs;
+  const tfs_tensor_out_t* tensors;
+  const tfs_span_t* filters;   /* output_filter strings of decoded PredictRequests */
+  const uint8_t* strings;      /* blob the spans index */
+  uint64_t strings_bytes;
+  uint64_t pool_bytes;         /* size the dst pool of tfs_decode must have */
+  uint32_t n_msgs;
+  uint32_t n_tensors;
+  uint32_t n_filters;
+  uint32_t n_failed;           /* messages whose status != TFS_OK */
+} tfs_decoded_view_t;
+
+/* ----------------------------------------------------------------------------------------------
+ * Context, memory and stream plumbing.  Replaces nothing in the reference: the client owns no
+ * device today; a ctx is created where the channels are (src/lib.rs:117-145) and shared by clones
+ * (src/lib.rs:148-156).
+ * -------------------------------------------------------------------------------------------- */
+
+int32_t tfs_abi_version(void);
+const char* tfs_strerror(tfs_status_t status);
+
+/* Create a context on CUDA device `device`.  `pinned_bytes` sizes the pinned staging slabs used by
+ * the *_host entry points (0 = allocate lazily). */
+tfs_status_t tfs_ctx_create(int32_t device, uint64_t pinned_bytes, tfs_ctx_t** out);
+tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx);
+/* Text of the last failure on this ctx (CUDA error string, offending argument, ...). */
+const char* tfs_last_error_detail(const tfs_ctx_t* ctx);
+/* Run the ctx's work on `cuda_stream` (a cudaStream_t; NULL = the ctx's own stream). */
+tfs_status_t tfs_ctx_set_stream(tfs_ctx_t* ctx, void* cuda_stream);
+tfs_status_t tfs_sync(tfs_ctx_t* ctx);
+/* Number of kernels this ctx has launched since creation (bench.py's gpu_launches). */
+uint64_t tfs_launch_count(const tfs_ctx_t* ctx);
+
+/* Pinned host slabs: the bridge between tonic's BytesMut and HBM. */
+tfs_status_t tfs_host_alloc(tfs_ctx_t* ctx, uint64_t bytes, void** out);
+tfs_status_t tfs_host_free(tfs_ctx_t* ctx, void* p);
+tfs_status_t tfs_dev_alloc(tfs_ctx_t* ctx, uint64_t bytes, void** out);
+tfs_status_t tfs_dev_free(tfs_ctx_t* ctx, void* p);
+tfs_status_t tfs_copy_h2d(tfs_ctx_t* ctx, void* dst_dev, const void* src_host, uint64_t bytes);
+tfs_status_t tfs_copy_d2h(tfs_ctx_t* ctx, void* dst_host, const void* src_dev, uint64_t bytes);
+
+/* ----------------------------------------------------------------------------------------------
+ * Encode.  Replaces prost's `Message::encoded_len` + `Message::encode` as called by tonic's
+ * ProstEncoder for the request built at src/lib.rs:259-263 and sent at src/lib.rs:265.
+ * -------------------------------------------------------------------------------------------- */
+
+/* Exact wire length of every message (prost `encoded_len`), without writing anything.
+ * `msg_len_out` is a host array of n_msgs entries (the 5-byte prefix is NOT included). */
+tfs_status_t tfs_encode_size(tfs_ctx_t* ctx, const tfs_batch_t* batch, uint64_t* msg_len_out);
+
+/* Host-side upper bound of the bytes tfs_encode may need in dst for this batch and flags. */
+uint64_t tfs_encode_bound(const tfs_batch_t* batch, uint32_t flags);
+
+/* Encode the whole batch into device memory `dst_dev` (capacity dst_capacity bytes).
+ * Field data pointers are device pointers.  On return (the call synchronises the stream):
+ * msg_off_out[i] = byte offset in dst_dev of message i's first byte (of its gRPC prefix when
+ * TFS_F_GRPC_PREFIX), msg_len_out[i] = its protobuf length (prefix excluded), *total_out = one past
+ * the last byte written. */
+tfs_status_t tfs_encode(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst_dev, uint64_t dst_capacity,
+                        uint32_t flags, uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out);
+
+/* Same, end to end from host memory to host memory: field data are host pointers, dst_host is a host
+ * buffer (pinned by tfs_host_alloc for full speed); host->device and device->host copies happen
+ * inside the call. */
+tfs_status_t tfs_encode_host(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst_host, uint64_t dst_capacity,
+                             uint32_t flags, uint64_t* msg_off_out, uint64_t* msg_len_out,
+                             uint64_t* total_out);
+
+/* ----------------------------------------------------------------------------------------------
+ * Decode.  Replaces prost's `Message::decode` as called by tonic's ProstDecoder on the response
+ * body of src/lib.rs:265-266.
+ * -------------------------------------------------------------------------------------------- */
+
+/* Pass 1: walk the structure of n_msgs messages of kind `msg_kind` stored in device memory
+ * wire_dev[msg_off[i] .. msg_off[i]+msg_len[i]) (msg_off / msg_len are host arrays; with
+ * TFS_F_GRPC_PREFIX each region starts with the 5-byte prefix and msg_len includes it), count the
+ * elements of every payload field and lay out the value pool.  The result handle owns host arrays
+ * described by tfs_decoded_view(). Returns TFS_ERR_BATCH when some messages are malformed (the others
+ * are still usable). */
+tfs_status_t tfs_decode_scan(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off,
+                             const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags,
+                             tfs_decoded_t** out);
+tfs_status_t tfs_decoded_view(const tfs_decoded_t* dec, tfs_decoded_view_t* view);
+/* Pass 2: write every payload value into the device pool (pool_bytes >= view.pool_bytes). */
+tfs_status_t tfs_decode(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_dev, uint64_t pool_bytes);
+tfs_status_t tfs_decoded_free(tfs_ctx_t* ctx, tfs_decoded_t* dec);
+
+/* End to end: wire bytes in host memory, values written to a host pool (both pinned for full speed).
+ * The pool is allocated by the caller after looking at the view: call with pool_host == NULL to get
+ * the handle and the sizes (the wire stays staged on the device), then tfs_decode_host_finish. */
+tfs_status_t tfs_decode_host(tfs_ctx_t* ctx, const void* wire_host, uint64_t wire_bytes, const uint64_t* msg_off,
+                             const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags,
+                             tfs_decoded_t** out);
+tfs_status_t tfs_decode_host_finish(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_host, uint64_t pool_bytes);
+
+/* ----------------------------------------------------------------------------------------------
+ * Sharding helper (host only).  Requests are independent, so a batch is split across GPUs with no
+ * collective: greedy largest-first balancing on bytes.  shard_out[i] in [0, n_shards).
+ * -------------------------------------------------------------------------------------------- */
+tfs_status_t tfs_shard_plan(const uint64_t* msg_bytes, uint32_t n_msgs, uint32_t n_shards, uint32_t* shard_out);
+
+/* Slot index (0..TFS_N_SLOTS-1) of a payload kind, -1 if the kind has no slot. */
+int32_t tfs_slot_of_kind(int32_t kind);
+int32_t tfs_kind_of_slot(int32_t slot);
+/* Size in bytes of a TFS_T_* element, 0 for TFS_T_NONE. */
+uint32_t tfs_type_size(int32_t type);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TFS_GPU_H_ */

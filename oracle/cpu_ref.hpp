@@ -1,0 +1,165 @@
+// cpu_ref.hpp — CPU ORACLE (test infrastructure, NOT product code).
+//
+// A plain C++17 restatement of what prost 0.6.0 + prost-derive 0.6.0 do for the messages the reference
+// sends at src/lib.rs:265: TensorProto (protos/tensorflow/core/framework/tensor.proto:14-84),
+// TensorShapeProto (tensor_shape.proto:13-46), ModelSpec (protos/tensorflow_serving/apis/model.proto:9-33),
+// PredictRequest / PredictResponse (predict.proto:12-40).  prost / tonic / bytes are only PINNED in the
+// reference's Cargo.lock (prost 0.6.0 Cargo.lock:831-832, prost-derive 0.6.0 :857-858, bytes 0.5.3
+// :131-132, tonic 0.1.0 :1264-1265) and are not vendored, so their algorithm is restated here from the
+// protobuf wire format and those crate versions' published behaviour, keeping
+// prost's PASS STRUCTURE (no cached sizes: nested lengths are recomputed by every caller; one put per
+// element; push-with-growth on decode) so that this file is also the timed CPU baseline.
+//
+// PARITY UNPINNED: the reference has no tests, golden vectors or fixtures for this path (SURVEY.md §4,
+// §8c) and cannot be compiled here (no rustc/cargo/protoc).  This oracle is pinned instead against
+// (1) the known-answer vectors of SURVEY.md Appendix B and (2) upb (python protobuf 6.33.6 with
+// tensorboard's compiled TensorProto) as an independent implementation — tests/golden/.
+//
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may use
+// anything in oracle/.  The product (rust-tensorflow-serving2_b200/) never does.
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <optional>
+#include <string>
+#include <utility>
+#include <vector>
+
+namespace cpu_ref {
+
+// ---- prost::DecodeError description classes; numeric values = tfs_gpu.h TFS_ERR_* ----
+enum class Err : int32_t {
+  Ok = 0,
+  InvalidVarint = 1,
+  BufferUnderflow = 2,
+  LengthExceeded = 3,
+  WireType = 4,
+  WireTypeValue = 5,
+  InvalidKey = 6,
+  InvalidTag = 7,
+  Recursion = 8,
+  EndGroup = 9,
+  Utf8 = 10,
+  GrpcFlag = 11,
+  Unsupported = 12,
+};
+
+struct DecodeError {
+  Err code;
+  uint64_t offset;  // bytes consumed from the message when the error was raised
+};
+
+// ---- bytes::Buf over a slice (bytes 0.5.3 `impl Buf for &[u8]`) ----
+struct Buf {
+  const uint8_t* base;
+  const uint8_t* p;
+  const uint8_t* end;
+  Buf(const uint8_t* b, size_t n) : base(b), p(b), end(b + n) {}
+  size_t remaining() const { return static_cast<size_t>(end - p); }
+  bool has_remaining() const { return p != end; }
+  uint64_t consumed() const { return static_cast<uint64_t>(p - base); }
+  void advance(size_t n) { p += n; }
+};
+
+// ---- bytes::BufMut over a growable byte vector (BytesMut) ----
+struct BufMut {
+  std::vector<uint8_t>& v;
+  explicit BufMut(std::vector<uint8_t>& vec) : v(vec) {}
+  void put_u8(uint8_t b) { v.push_back(b); }
+  void put_slice(const void* s, size_t n) {
+    const uint8_t* c = static_cast<const uint8_t*>(s);
+    v.insert(v.end(), c, c + n);
+  }
+};
+
+enum WireType : uint32_t { Varint = 0, SixtyFourBit = 1, LengthDelimited = 2, StartGroup = 3, EndGroup = 4, ThirtyTwoBit = 5 };
+
+// ---- generated structs (prost-build output shape for the .proto files above) ----
+struct Dim {
+  int64_t size = 0;
+  std::string name;
+  bool operator==(const Dim& o) const { return size == o.size && name == o.name; }
+};
+struct TensorShapeProto {
+  std::vector<Dim> dim;
+  bool unknown_rank = false;
+  bool operator==(const TensorShapeProto& o) const { return dim == o.dim && unknown_rank == o.unknown_rank; }
+};
+struct TensorProto {
+  int32_t dtype = 0;                                // tag 1 (enumeration stored as i32)
+  std::optional<TensorShapeProto> tensor_shape;     // tag 2
+  int32_t version_number = 0;                       // tag 3
+  std::vector<uint8_t> tensor_content;              // tag 4
+  std::vector<int32_t> half_val;                    // tag 13
+  std::vector<float> float_val;                     // tag 5
+  std::vector<double> double_val;                   // tag 6
+  std::vector<int32_t> int_val;                     // tag 7
+  std::vector<std::vector<uint8_t>> string_val;     // tag 8
+  std::vector<float> scomplex_val;                  // tag 9
+  std::vector<int64_t> int64_val;                   // tag 10
+  std::vector<uint8_t> bool_val;                    // tag 11 (Vec<bool>)
+  std::vector<double> dcomplex_val;                 // tag 12
+  std::vector<uint32_t> uint32_val;                 // tag 16
+  std::vector<uint64_t> uint64_val;                 // tag 17
+  bool has_unsupported = false;                     // saw resource_handle_val(14) / variant_val(15)
+  bool is_default() const;
+};
+struct ModelSpec {
+  std::string name;  // tag 1
+  // oneof version_choice { Int64Value version = 2 (prost maps the wrapper to i64); string version_label = 4 }
+  int32_t version_choice = 0;  // 0 none, 1 version, 2 label
+  int64_t version = 0;
+  std::string version_label;
+  std::string signature_name;  // tag 3
+};
+using TensorMap = std::vector<std::pair<std::string, TensorProto>>;  // HashMap in caller / wire order
+struct PredictRequest {
+  std::optional<ModelSpec> model_spec;     // tag 1
+  TensorMap inputs;                        // tag 2
+  std::vector<std::string> output_filter;  // tag 3
+};
+struct PredictResponse {
+  TensorMap outputs;                    // tag 1
+  std::optional<ModelSpec> model_spec;  // tag 2
+};
+
+// ---- prost::encoding primitives ----
+size_t encoded_len_varint(uint64_t value);
+void encode_varint(uint64_t value, BufMut& buf);
+bool decode_varint(Buf& buf, uint64_t* out);  // false => "invalid varint"
+
+// ---- prost::Message surface ----
+size_t encoded_len(const TensorProto& m);
+size_t encoded_len(const PredictRequest& m);
+size_t encoded_len(const PredictResponse& m);
+void encode_raw(const TensorProto& m, BufMut& buf);
+void encode_raw(const PredictRequest& m, BufMut& buf);
+void encode_raw(const PredictResponse& m, BufMut& buf);
+
+// tonic ProstEncoder::encode: len = encoded_len(); reserve(len); Message::encode (which sizes again)
+template <class M>
+void prost_encoder_encode(const M& m, std::vector<uint8_t>& dst) {
+  size_t len = encoded_len(m);
+  dst.reserve(dst.size() + len);
+  size_t required = encoded_len(m);  // Message::encode's own capacity check
+  (void)required;
+  BufMut b(dst);
+  encode_raw(m, b);
+}
+
+// Message::decode: default value, then merge until the buffer is empty.
+bool decode(const uint8_t* p, size_t n, TensorProto* out, DecodeError* err);
+bool decode(const uint8_t* p, size_t n, PredictRequest* out, DecodeError* err);
+bool decode(const uint8_t* p, size_t n, PredictResponse* out, DecodeError* err);
+
+// Rust core::str::from_utf8 validity.
+bool is_utf8(const uint8_t* p, size_t n);
+
+// f32 -> f16 / bf16 bit patterns, round-to-nearest-even, NaN stays a quiet NaN with its sign
+// (the cast policy of DESIGN.md; the reference has no half code, tensor.proto:43-45 only fixes the carrier).
+uint16_t f32_to_f16_bits(float f);
+uint16_t f32_to_bf16_bits(float f);
+float f16_bits_to_f32(uint16_t h);
+float bf16_bits_to_f32(uint16_t h);
+
+}  // namespace cpu_ref

@@ -1,0 +1,15 @@
+"""B200-native TensorProto / PredictRequest / PredictResponse wire codec (the one hot path of
+simonrw/rust-tensorflow-serving2, reference src/lib.rs:229-266), behind the C ABI of include/tfs_gpu.h.
+
+Python here is only the harness above the C ABI (the role the Rust shim plays in the reference crate):
+message objects, descriptor building and a ctypes binding.  All compute is in csrc/ (CUDA, sm_100a).
+There is no CPU fallback: using the codec without the built library or without a GPU raises.
+"""
+from . import abi  # noqa: F401
+from .messages import (  # noqa: F401
+    ModelSpec, Payload, PredictRequest, PredictResponse, TensorProto, TensorShapeProto, build_batch,
+    messages_from_view,
+)
+
+__all__ = ["abi", "ModelSpec", "Payload", "PredictRequest", "PredictResponse", "TensorProto",
+           "TensorShapeProto", "build_batch", "messages_from_view"]

@@ -1,0 +1,276 @@
+"""Host-side mirror of the prost structs the reference sends and receives, plus the conversion
+between them and the C ABI's plain-data descriptors.
+
+Field names follow the generated Rust structs (`TensorProto { dtype, tensor_shape, float_val, .. }`,
+`PredictRequest { model_spec, inputs, output_filter }`, reference src/lib.rs:249-263); map fields are
+ordered lists of (key, TensorProto) because the ABI emits entries in the caller's order (prost's
+HashMap order is unspecified).
+
+Payload values are 1-D contiguous numpy arrays (host) or torch tensors (host or CUDA); nothing here
+computes on them — only pointers and sizes go into the descriptors.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Any, List, Optional, Tuple
+
+import numpy as np
+
+from . import abi
+
+try:  # torch is only plumbing (device memory, streams)
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+@dataclass
+class Payload:
+    """A payload array with an explicit in-memory type and (optionally) a fused conversion."""
+    data: Any
+    src_type: int
+    dst_type: int = abi.T_NONE
+    op: int = abi.OP_NONE
+    op_param: float = 0.0
+
+
+@dataclass
+class TensorShapeProto:
+    dim: List[int] = field(default_factory=list)  # Dim.size; Dim.name is always "" (src/lib.rs:233)
+    unknown_rank: bool = False
+
+
+@dataclass
+class TensorProto:
+    dtype: int = 0
+    tensor_shape: Optional[TensorShapeProto] = None
+    version_number: int = 0
+    tensor_content: Any = None
+    half_val: Any = None
+    float_val: Any = None
+    double_val: Any = None
+    int_val: Any = None
+    string_val: Any = None
+    scomplex_val: Any = None
+    int64_val: Any = None
+    bool_val: Any = None
+    dcomplex_val: Any = None
+    uint32_val: Any = None
+    uint64_val: Any = None
+
+    def payloads(self):
+        """(kind, value) for every payload field that is set, ascending field number."""
+        for kind in abi.SLOT_KINDS:
+            v = getattr(self, abi.KIND_FIELD_NAMES[kind])
+            if v is not None:
+                yield kind, v
+
+
+@dataclass
+class ModelSpec:
+    name: str = ""
+    version: Optional[int] = None        # oneof version_choice: Int64Value version = 2
+    version_label: Optional[str] = None  #                        string version_label = 4
+    signature_name: str = ""
+
+
+@dataclass
+class PredictRequest:
+    model_spec: Optional[ModelSpec] = None
+    inputs: List[Tuple[str, TensorProto]] = field(default_factory=list)
+    output_filter: List[str] = field(default_factory=list)
+
+
+@dataclass
+class PredictResponse:
+    outputs: List[Tuple[str, TensorProto]] = field(default_factory=list)
+    model_spec: Optional[ModelSpec] = None
+
+
+_NP_TYPES = {
+    "uint8": abi.T_U8, "int8": abi.T_I8, "uint16": abi.T_U16, "int16": abi.T_I16, "int32": abi.T_I32,
+    "uint32": abi.T_U32, "int64": abi.T_I64, "uint64": abi.T_U64, "float16": abi.T_F16, "float32": abi.T_F32,
+    "float64": abi.T_F64, "bool": abi.T_BOOL,
+}
+
+
+def _array_info(data):
+    """(pointer, n_elems, TFS_T_*, keepalive) of a 1-D contiguous numpy array or torch tensor."""
+    if isinstance(data, np.ndarray):
+        if not data.flags["C_CONTIGUOUS"]:
+            raise ValueError("payload arrays must be C-contiguous")
+        t = _NP_TYPES.get(data.dtype.name)
+        if t is None:
+            raise TypeError(f"unsupported numpy dtype {data.dtype}")
+        return (data.ctypes.data if data.size else 0), int(data.size), t, data
+    if torch is not None and isinstance(data, torch.Tensor):
+        if not data.is_contiguous():
+            raise ValueError("payload tensors must be contiguous")
+        name = str(data.dtype).replace("torch.", "")
+        t = abi.T_BF16 if name == "bfloat16" else _NP_TYPES.get(name)
+        if t is None:
+            raise TypeError(f"unsupported torch dtype {data.dtype}")
+        return (data.data_ptr() if data.numel() else 0), int(data.numel()), t, data
+    raise TypeError(f"payload must be a numpy array or torch tensor, got {type(data)}")
+
+
+class BuiltBatch:
+    """Owns the ctypes arrays of one tfs_batch_t and everything they point at."""
+
+    def __init__(self, msgs, tensors, fields, filters, keep):
+        self.msgs, self.tensors, self.fields, self.filters = msgs, tensors, fields, filters
+        self._keep = keep
+        self.batch = abi.Batch(
+            C.cast(msgs, C.POINTER(abi.MsgDesc)), C.cast(tensors, C.POINTER(abi.TensorDesc)),
+            C.cast(fields, C.POINTER(abi.FieldDesc)), C.cast(filters, C.POINTER(abi.Str)),
+            len(msgs), len(tensors), len(fields), len(filters))
+
+    @property
+    def n_msgs(self):
+        return len(self.msgs)
+
+
+def _mk_str(s, keep):
+    b = s if isinstance(s, (bytes, bytearray)) else s.encode("utf-8")
+    if not b:
+        return abi.Str(None, 0, 0)
+    buf = C.create_string_buffer(bytes(b), len(b))
+    keep.append(buf)
+    return abi.Str(C.cast(buf, C.c_void_p), len(b), 0)
+
+
+def build_batch(messages, kind) -> BuiltBatch:
+    """Turn a list of TensorProto / PredictRequest / PredictResponse into a tfs_batch_t."""
+    keep: list = []
+    msg_l, ten_l, fld_l, flt_l = [], [], [], []
+
+    def add_tensor(name, t: TensorProto):
+        td = abi.TensorDesc()
+        td.name = _mk_str(name, keep)
+        td.dtype = int(t.dtype)
+        td.version_number = int(t.version_number)
+        if t.tensor_shape is not None:
+            td.has_shape = 1
+            td.unknown_rank = 1 if t.tensor_shape.unknown_rank else 0
+            td.n_dims = len(t.tensor_shape.dim)
+            if td.n_dims > abi.TFS_MAX_DIMS:
+                raise ValueError("rank exceeds TFS_MAX_DIMS")
+            for i, d in enumerate(t.tensor_shape.dim):
+                td.dims[i] = int(d)
+        td.first_field = len(fld_l)
+        n = 0
+        for k, v in t.payloads():
+            p = v if isinstance(v, Payload) else Payload(v, abi.T_NONE)
+            ptr, count, ty, ka = _array_info(p.data)
+            keep.append(ka)
+            fd = abi.FieldDesc()
+            fd.kind = k
+            fd.src_type = p.src_type if p.src_type != abi.T_NONE else ty
+            fd.dst_type = p.dst_type
+            fd.op = p.op
+            fd.op_param = float(p.op_param)
+            # a source array viewed as a wider / narrower type than it is stored in
+            fd.n_elems = count * abi.TYPE_SIZE[ty] // abi.TYPE_SIZE[fd.src_type]
+            fd.data = ptr
+            fld_l.append(fd)
+            n += 1
+        td.n_fields = n
+        ten_l.append(td)
+
+    for m in messages:
+        md = abi.MsgDesc()
+        md.kind = kind
+        md.first_tensor = len(ten_l)
+        md.first_filter = len(flt_l)
+        if kind == abi.MSG_TENSOR_PROTO:
+            add_tensor("", m)
+        else:
+            entries = m.inputs if kind == abi.MSG_PREDICT_REQUEST else m.outputs
+            for name, t in entries:
+                add_tensor(name, t)
+            if m.model_spec is not None:
+                ms = m.model_spec
+                md.has_model_spec = 1
+                md.model_name = _mk_str(ms.name, keep)
+                md.signature_name = _mk_str(ms.signature_name, keep)
+                if ms.version is not None:
+                    md.version_choice = abi.VERSION_NUMBER
+                    md.version = int(ms.version)
+                elif ms.version_label is not None:
+                    md.version_choice = abi.VERSION_LABEL
+                    md.version_label = _mk_str(ms.version_label, keep)
+            if kind == abi.MSG_PREDICT_REQUEST:
+                for s in m.output_filter:
+                    flt_l.append(_mk_str(s, keep))
+        md.n_tensors = len(ten_l) - md.first_tensor
+        md.n_filters = len(flt_l) - md.first_filter
+        msg_l.append(md)
+
+    return BuiltBatch((abi.MsgDesc * len(msg_l))(*msg_l), (abi.TensorDesc * len(ten_l))(*ten_l),
+                      (abi.FieldDesc * len(fld_l))(*fld_l), (abi.Str * len(flt_l))(*flt_l), keep)
+
+
+# ------------------------------------------------------------------------------------------------
+# decode results -> message objects
+# ------------------------------------------------------------------------------------------------
+
+@dataclass
+class DecodedMessage:
+    status: int
+    err_offset: int
+    message: Any  # TensorProto / PredictRequest / PredictResponse, or None when status != 0
+
+
+def _span_bytes(strings: bytes, sp) -> bytes:
+    return strings[sp.off: sp.off + sp.len]
+
+
+def _tensor_from_out(to, strings: bytes, pool: np.ndarray) -> Tuple[str, TensorProto]:
+    t = TensorProto(dtype=to.dtype, version_number=to.version_number)
+    if to.has_shape:
+        t.tensor_shape = TensorShapeProto([int(to.dims[i]) for i in range(to.n_dims)], bool(to.unknown_rank))
+    for slot, kind in enumerate(abi.SLOT_KINDS):
+        n = int(to.n_elems[slot])
+        if n == 0:
+            continue
+        ty = int(to.dst_type[slot])
+        off = int(to.dst_off[slot])
+        if kind == abi.KIND_STRING_VAL:
+            offs = pool[off: off + 8 * (n + 1)].view("<u8")
+            base = off + 8 * (n + 1)
+            val = [bytes(pool[base + int(offs[i]): base + int(offs[i + 1])]) for i in range(n)]
+        elif kind == abi.KIND_TENSOR_CONTENT and ty == abi.T_F32:
+            val = pool[off: off + (n // 2) * 4].view("<f4")  # widened 16-bit content
+        else:
+            val = pool[off: off + n * abi.TYPE_SIZE[ty]].view(abi.TYPE_NUMPY[ty])
+        setattr(t, abi.KIND_FIELD_NAMES[kind], val)
+    return _span_bytes(strings, to.key).decode("utf-8"), t
+
+
+def messages_from_view(view: abi.DecodedView, pool: np.ndarray, kind: int) -> List[DecodedMessage]:
+    """Rebuild message objects from a tfs_decoded_view_t and the (host copy of the) value pool."""
+    strings = C.string_at(view.strings, view.strings_bytes) if view.strings_bytes else b""
+    out = []
+    for i in range(view.n_msgs):
+        mo = view.msgs[i]
+        if mo.status != abi.TFS_OK:
+            out.append(DecodedMessage(mo.status, int(mo.err_offset), None))
+            continue
+        entries = [_tensor_from_out(view.tensors[mo.first_tensor + j], strings, pool) for j in range(mo.n_tensors)]
+        ms = None
+        if mo.has_model_spec:
+            ms = ModelSpec(_span_bytes(strings, mo.model_name).decode("utf-8"),
+                           int(mo.version) if mo.version_choice == abi.VERSION_NUMBER else None,
+                           _span_bytes(strings, mo.version_label).decode("utf-8")
+                           if mo.version_choice == abi.VERSION_LABEL else None,
+                           _span_bytes(strings, mo.signature_name).decode("utf-8"))
+        if kind == abi.MSG_TENSOR_PROTO:
+            msg = entries[0][1] if entries else TensorProto()
+        elif kind == abi.MSG_PREDICT_REQUEST:
+            flt = [_span_bytes(strings, view.filters[mo.first_filter + j]).decode("utf-8") for j in range(mo.n_filters)]
+            msg = PredictRequest(ms, entries, flt)
+        else:
+            msg = PredictResponse(entries, ms)
+        out.append(DecodedMessage(0, 0, msg))
+    return out
