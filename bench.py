@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""bench.py — TensorProto / PredictRequest wire encode+decode throughput (BASELINE.json's metric).
+
+A step = one pass of the hot path over one batch of synthetic requests: for each of the two C2 variants
+(ResNet-50 input 64x224x224x3 DT_FLOAT carried as `float_val`, and as `tensor_content`) encode R
+PredictRequests to wire bytes and decode those wire bytes back to values.  `value` counts WIRE bytes
+(encode output + decode input) per second with everything resident in HBM; `e2e` is the same work through
+the host-memory entry points (payloads and wire in pinned host memory, H2D/D2H inside the timed region).
+
+  python bench.py --gpus N --steps K --warmup W            our arm (one process per GPU; torchrun for N > 1)
+  python bench.py --impl reference ...                      the reference's CPU path (oracle port of prost) on host cores
+
+Requests are independent, so N GPUs each take their own shard of the batch: no collective on the data
+path; torch.distributed (nccl) is only used for the barrier and the max-over-ranks time.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "tensorproto_encode_decode_wire_GBps"
+UNIT = "GB/s"
+C2_ELEMS = 64 * 224 * 224 * 3
+C2_WIRE = 38535239  # prost encoded_len of one C2 PredictRequest
+VARIANTS = ("float_val", "tensor_content")
+
+
+def workload_name(r):
+    return (f"C2 ResNet-50 input 64x224x224x3 DT_FLOAT as float_val and as tensor_content; per step and per GPU: "
+            f"{r} PredictRequests per variant encoded, then decoded")
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            with open(path) as f:
+                return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc, self.thread = device, [], None, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except Exception:
+                continue
+            for nm, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# =====================================================================================================
+# our arm
+# =====================================================================================================
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import tfs_b200 as tfs
+    from tfs_b200 import abi, workloads
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the codec has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    codec = tfs.GpuCodec(tfs.GpuContext(local))
+    ctx, enc, dec = codec.ctx, codec.encoder(), codec.decoder()
+    R = args.requests
+    kind = abi.MSG_PREDICT_REQUEST
+    flags = abi.F_ALIGN_PAYLOAD
+
+    # ---- device-resident inputs: R distinct payloads per variant (R * 38.5 MB > L2 for R >= 4)
+    g = torch.Generator(device=dev)
+    g.manual_seed(2001 + rank)
+    src = torch.randn(R, C2_ELEMS, device=dev, generator=g)
+
+    def requests(payload_rows, variant):
+        out = []
+        for i in range(R):
+            shape = tfs.TensorShapeProto([64, 224, 224, 3])
+            t = (tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, float_val=payload_rows[i]) if variant == "float_val"
+                 else tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, tensor_content=payload_rows[i]))
+            out.append(tfs.PredictRequest(tfs.ModelSpec("resnet", signature_name="serving_default"), [("input", t)]))
+        return out
+
+    built = {v: tfs.build_batch(requests(src, v), kind) for v in VARIANTS}  # the "prost structs", built once
+    cap = enc.bound(built["float_val"], flags)
+    wire = {v: torch.empty(cap, dtype=torch.uint8, device=dev) for v in VARIANTS}
+    pool = {v: torch.empty(R * (C2_ELEMS * 4 + 4096), dtype=torch.uint8, device=dev) for v in VARIANTS}
+
+    def step():
+        n = 0
+        for v in VARIANTS:
+            eb = enc.encode(built[v], kind, flags, dst=wire[v])
+            d = dec.decode(eb.wire, eb.offsets, eb.lengths, kind, 0, pool=pool[v])
+            n += 2 * sum(eb.lengths)
+            d.close()
+        return n
+
+    # correctness of what is being timed: decoded values == source, wire length == prost's encoded_len
+    eb = enc.encode(built["float_val"], kind, flags, dst=wire["float_val"])
+    assert eb.lengths == [C2_WIRE] * R, eb.lengths[:2]
+    d = dec.decode(eb.wire, eb.offsets, eb.lengths, kind, 0, pool=pool["float_val"])
+    t0 = d.view.tensors[d.view.msgs[R - 1].first_tensor]
+    got = pool["float_val"][t0.dst_off[1]: t0.dst_off[1] + 4 * C2_ELEMS].view(torch.float32)
+    assert torch.equal(got, src[R - 1]), "decode(encode(x)) != x"
+    d.close()
+
+    for _ in range(args.warmup):
+        step()
+    ctx.prof_enable(True)
+    for k in range(5):
+        ctx.prof_read(k, reset=True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    launches0 = ctx.launch_count()
+    e0.record()
+    wire_bytes = 0
+    for _ in range(args.steps):
+        wire_bytes += step()
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ctx.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    n_copy, ms_copy = ctx.prof_read(abi.PK_COPY)
+    ctx.prof_enable(False)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+
+    # ---- end to end: pinned host payloads -> host wire -> host values, smaller batch (PCIe-bound)
+    Re = min(args.e2e_requests, R)
+    h_src = torch.randn(Re, C2_ELEMS).pin_memory()
+    h_wire = torch.empty(enc.bound(built["float_val"], flags) // R * Re + 4096, dtype=torch.uint8).pin_memory()
+    h_pool = torch.empty(Re * (C2_ELEMS * 4 + 4096), dtype=torch.uint8).pin_memory()
+    rows = [h_src[i].numpy() for i in range(Re)]
+
+    def host_requests(variant):
+        out = []
+        for i in range(Re):
+            shape = tfs.TensorShapeProto([64, 224, 224, 3])
+            t = (tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, float_val=rows[i]) if variant == "float_val"
+                 else tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, tensor_content=rows[i]))
+            out.append(tfs.PredictRequest(tfs.ModelSpec("resnet", signature_name="serving_default"), [("input", t)]))
+        return out
+
+    hbuilt = {v: tfs.build_batch(host_requests(v), kind) for v in VARIANTS}
+    h_wire_np, h_pool_np = h_wire.numpy(), h_pool.numpy()
+
+    def e2e_step():
+        n = h2d = d2h = 0
+        for v in VARIANTS:
+            eb = enc.encode_host(hbuilt[v], kind, flags, dst=h_wire_np)
+            h2d += Re * C2_ELEMS * 4
+            d2h += eb.total
+            d = dec.decode_host(h_wire_np[: eb.total], eb.offsets, eb.lengths, kind, 0, pool=h_pool_np)
+            h2d += eb.total
+            d2h += d.pool_bytes
+            n += 2 * sum(eb.lengths)
+            d.close()
+        return n, h2d, d2h
+
+    e2e_step()
+    e2e_steps = max(1, min(args.steps, 5))
+    barrier()
+    torch.cuda.synchronize()
+    t_start = time.perf_counter()
+    e2e_bytes = h2d = d2h = 0
+    for _ in range(e2e_steps):
+        a, b, c = e2e_step()
+        e2e_bytes += a
+        h2d, d2h = b, c
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t_start
+    if world > 1:
+        t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    last = pool_check = h_pool[: 16].clone()  # touch the result (device -> host read is part of every step)
+    del last, pool_check
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = load_peaks()
+    value = world * wire_bytes / (ms * 1e-3) / 1e9
+    # K5 k_copy: one launch per encode and per decode; algorithmic bytes of one launch = read + write of
+    # R payloads (fixed / content encode or decode = N*w_src + N*w_dst)
+    alg_per_launch = 2.0 * R * C2_ELEMS * 4
+    achieved = alg_per_launch / (ms_copy / max(1, n_copy) * 1e-3) / 1e9 if n_copy else None
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": workload_name(R), "requests_per_variant_per_gpu": R, "wire_bytes_per_request": C2_WIRE,
+                   "l2": f"inputs larger than L2: each pass streams {R * C2_WIRE / 1e6:.0f} MB in and out (L2 is 126 MB)",
+                   "flags": "TFS_F_ALIGN_PAYLOAD", "sharding": f"dp{world}: independent requests per GPU, no collective"},
+        "clocks": clocks,
+        "e2e": {"value": round(world * e2e_bytes / e2e_s / 1e9, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "path": "tfs_encode_host + tfs_decode_host, pinned host buffers"},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "k_copy (K5 bulk copy, encode and decode launches)", "achieved": round(achieved, 1) if achieved else None,
+                     "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4) if achieved else None, "peak_source": peak_src,
+                     "traffic": None, "launches_timed": n_copy, "avg_launch_ms": round(ms_copy / max(1, n_copy), 4),
+                     "algorithmic_bytes_per_launch": alg_per_launch,
+                     "step_frac_of_peak": round(2 * value / world / peak, 4)},
+        "cpu_baseline": cpu_baseline(R, budget_s=args.cpu_budget),
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# =====================================================================================================
+# CPU side: the oracle port of prost's algorithm, timed on the host cores
+# =====================================================================================================
+def cpu_pass(threads, n_msgs, reps_budget_s, min_reps=1):
+    """Encode + decode n_msgs C2 requests per variant with `threads` host threads; returns (GB/s wire, reps, seconds)."""
+    import tfs_b200 as tfs
+    from tfs_b200 import abi
+    import oracle_bind as ob
+
+    x = np.random.default_rng(2001).standard_normal(C2_ELEMS, dtype=np.float32)
+    total_b, total_s, reps = 0, 0.0, 0
+    preps = []
+    for v in VARIANTS:
+        shape = tfs.TensorShapeProto([64, 224, 224, 3])
+        msgs = []
+        for _ in range(n_msgs):
+            t = (tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, float_val=x) if v == "float_val"
+                 else tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, tensor_content=x))
+            msgs.append(tfs.PredictRequest(tfs.ModelSpec("resnet", signature_name="serving_default"), [("input", t)]))
+        preps.append(ob.Prepared(tfs.build_batch(msgs, abi.MSG_PREDICT_REQUEST)))
+    t_begin = time.perf_counter()
+    while reps < min_reps or (time.perf_counter() - t_begin) < reps_budget_s:
+        for p in preps:
+            s_e, wb = p.run_encode(threads)
+            s_d, wb2, _ = p.run_decode(threads)
+            assert wb == wb2 == n_msgs * C2_WIRE
+            total_b += wb + wb2
+            total_s += s_e + s_d
+        reps += 1
+    for p in preps:
+        p.close()
+    return total_b / total_s / 1e9, reps, total_s
+
+
+def cpu_baseline(R, budget_s=12.0):
+    cores = os.cpu_count() or 1
+    threads = max(1, min(cores, 16))
+    n_msgs = threads
+    gbs, reps, secs = cpu_pass(threads, n_msgs, budget_s)
+    return {"value": round(gbs, 3), "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{n_msgs} C2 requests per variant (one per thread), encode+decode, {reps} passes, {secs:.1f} s of CPU work; "
+                      f"oracle/cpu_ref.cpp = C++ port of prost 0.6.0's pass structure (prost itself: unavailable on this box, no rustc/cargo)",
+            "host_cores_available": cores}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    threads = max(1, min(cores, 64))
+    n_msgs = threads
+    # warm-up + K timed steps, each a bounded sample (one request per thread and variant)
+    per_step_budget = 0.0
+    t0 = time.perf_counter()
+    for _ in range(max(0, min(args.warmup, 1))):
+        cpu_pass(threads, n_msgs, 0.0)
+    steps = max(1, min(args.steps, 5))
+    tot_b = tot_s = 0.0
+    for _ in range(steps):
+        gbs, reps, secs = cpu_pass(threads, n_msgs, per_step_budget)
+        tot_b += gbs * secs
+        tot_s += secs
+    value = tot_b / tot_s
+    sample = (f"{n_msgs} C2 requests per variant per step (one per host thread), {steps} steps, oracle/cpu_ref.cpp "
+              f"(C++ port of prost 0.6.0; the Rust reference cannot be built here: no rustc/cargo, crates not vendored)")
+    line = {"impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+            "warmup": min(args.warmup, 1), "ms_per_step": round(tot_s / steps * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": workload_name(n_msgs), "requests_per_variant_per_gpu": n_msgs, "wire_bytes_per_request": C2_WIRE},
+            "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
+                             "host_cores_available": cores},
+            "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "wall_s": round(time.perf_counter() - t0, 1)}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--requests", type=int, default=16, help="C2 requests per variant, per GPU and per step")
+    ap.add_argument("--e2e-requests", type=int, default=4)
+    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU baseline sampling")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

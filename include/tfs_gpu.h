@@ -268,6 +268,19 @@ tfs_status_t tfs_sync(tfs_ctx_t* ctx);
 /* Number of kernels this ctx has launched since creation (bench.py's gpu_launches). */
 uint64_t tfs_launch_count(const tfs_ctx_t* ctx);
 
+/* Per-kernel device timing (instrumentation; nothing in the reference corresponds to it).  While
+ * enabled, every launch of the kernels below is bracketed by CUDA events on the ctx's stream;
+ * tfs_prof_read synchronises the stream and returns the launches and summed milliseconds so far. */
+enum {
+  TFS_PK_COPY = 0,           /* K5 bulk copy / cast */
+  TFS_PK_VARINT_SIZE = 1,    /* K1 */
+  TFS_PK_VARINT_SCATTER = 2, /* K3 */
+  TFS_PK_VARINT_COUNT = 3,   /* K4a */
+  TFS_PK_VARINT_GATHER = 4   /* K4c */
+};
+tfs_status_t tfs_prof_enable(tfs_ctx_t* ctx, int32_t on);
+tfs_status_t tfs_prof_read(tfs_ctx_t* ctx, int32_t kernel_id, uint64_t* launches_out, double* ms_out, int32_t reset);
+
 /* Pinned host slabs: the bridge between tonic's BytesMut and HBM. */
 tfs_status_t tfs_host_alloc(tfs_ctx_t* ctx, uint64_t bytes, void** out);
 tfs_status_t tfs_host_free(tfs_ctx_t* ctx, void* p);

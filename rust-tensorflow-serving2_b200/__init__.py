@@ -5,11 +5,14 @@ Python here is only the harness above the C ABI (the role the Rust shim plays in
 message objects, descriptor building and a ctypes binding.  All compute is in csrc/ (CUDA, sm_100a).
 There is no CPU fallback: using the codec without the built library or without a GPU raises.
 """
-from . import abi  # noqa: F401
+from . import abi, messages, workloads, _lib, codec  # noqa: F401  (all submodules, so aliases of the package see them)
+from ._lib import TfsError  # noqa: F401
+from .codec import GpuCodec, GpuContext, GpuDecoder, GpuEncoder  # noqa: F401
 from .messages import (  # noqa: F401
     ModelSpec, Payload, PredictRequest, PredictResponse, TensorProto, TensorShapeProto, build_batch,
     messages_from_view,
 )
 
-__all__ = ["abi", "ModelSpec", "Payload", "PredictRequest", "PredictResponse", "TensorProto",
-           "TensorShapeProto", "build_batch", "messages_from_view"]
+__all__ = ["abi", "workloads", "codec", "ModelSpec", "Payload", "PredictRequest", "PredictResponse", "TensorProto",
+           "TensorShapeProto", "build_batch", "messages_from_view", "GpuCodec", "GpuContext", "GpuEncoder", "GpuDecoder",
+           "TfsError"]

@@ -1,0 +1,238 @@
+"""GpuCodec — host-side mirror of the seam the reference uses for this path.
+
+In the reference every RPC stub builds `tonic::codec::ProstCodec::default()` and hands it to
+`Grpc::unary(request, path, codec)` (generated code behind `self.prediction_client.predict(request)`,
+reference src/lib.rs:265).  tonic's Codec contract is `encoder() -> Encoder`, `decoder() -> Decoder`,
+with `Encoder::encode(item, &mut BytesMut)` appending exactly the protobuf bytes and
+`Decoder::decode(&mut BytesMut) -> Option<Item>` consuming one complete message.
+
+`GpuCodec` keeps those names; because a GPU wants batches, `encode` / `decode` take a list of messages
+(the Rust shim queues the requests of a short window, rust/codec.rs).  Everything below only drives the
+C ABI (include/tfs_gpu.h) through ctypes — no arithmetic happens in Python.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+from typing import List, Optional, Sequence
+
+import numpy as np
+
+from . import abi
+from ._lib import TfsError, lib
+from .messages import BuiltBatch, DecodedMessage, build_batch, messages_from_view
+
+try:
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+class GpuContext:
+    """One tfs_ctx_t: one GPU, one stream (one process per GPU; the reference creates its channels in
+    TensorflowServingBuilder::build, src/lib.rs:117-145 — this is created alongside)."""
+
+    def __init__(self, device: Optional[int] = None, pinned_bytes: int = 0, use_torch_stream: bool = True):
+        if device is None:
+            device = int(os.environ.get("LOCAL_RANK", "0"))
+        self.device = device
+        self._h = C.c_void_p()
+        st = lib().tfs_ctx_create(device, pinned_bytes, C.byref(self._h))
+        if st != abi.TFS_OK:
+            raise TfsError(st, "tfs_ctx_create failed: no usable CUDA device (this package has no CPU fallback)")
+        if use_torch_stream and torch is not None and torch.cuda.is_available():
+            torch.cuda.set_device(device)
+            self.set_stream(torch.cuda.current_stream(device).cuda_stream)
+
+    @property
+    def handle(self):
+        return self._h
+
+    def check(self, st, ok=(abi.TFS_OK,)):
+        if st not in ok:
+            raise TfsError(st, (lib().tfs_last_error_detail(self._h) or b"").decode("utf-8", "replace"))
+        return st
+
+    def set_stream(self, cuda_stream: int):
+        self.check(lib().tfs_ctx_set_stream(self._h, C.c_void_p(cuda_stream)))
+
+    def sync(self):
+        self.check(lib().tfs_sync(self._h))
+
+    def launch_count(self) -> int:
+        return int(lib().tfs_launch_count(self._h))
+
+    def prof_enable(self, on: bool = True):
+        self.check(lib().tfs_prof_enable(self._h, 1 if on else 0))
+
+    def prof_read(self, kernel_id: int, reset: bool = False):
+        """-> (launches, total milliseconds) of one kernel since profiling was enabled / last reset."""
+        n, ms = C.c_uint64(0), C.c_double(0.0)
+        self.check(lib().tfs_prof_read(self._h, kernel_id, C.byref(n), C.byref(ms), 1 if reset else 0))
+        return int(n.value), float(ms.value)
+
+    def close(self):
+        if self._h:
+            lib().tfs_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+@dataclass
+class EncodedBatch:
+    wire: object            # torch.uint8 CUDA tensor (device path) or numpy uint8 array (host path)
+    offsets: List[int]      # first byte of each message (of its gRPC prefix with F_GRPC_PREFIX)
+    lengths: List[int]      # protobuf length of each message (prefix excluded)
+    total: int
+    flags: int = 0
+
+    def message_bytes(self, i: int) -> bytes:
+        pre = 5 if self.flags & abi.F_GRPC_PREFIX else 0
+        w = self.wire
+        lo, hi = self.offsets[i], self.offsets[i] + self.lengths[i] + pre
+        if isinstance(w, np.ndarray):
+            return bytes(w[lo:hi])
+        return bytes(w[lo:hi].cpu().numpy())
+
+    def all_bytes(self) -> List[bytes]:
+        w = self.wire if isinstance(self.wire, np.ndarray) else self.wire[: self.total].cpu().numpy()
+        pre = 5 if self.flags & abi.F_GRPC_PREFIX else 0
+        return [bytes(w[o: o + l + pre]) for o, l in zip(self.offsets, self.lengths)]
+
+
+class GpuEncoder:
+    """tonic `Encoder` for PredictRequest / PredictResponse / TensorProto batches."""
+
+    def __init__(self, ctx: GpuContext):
+        self.ctx = ctx
+
+    def encoded_len(self, messages: Sequence, kind: int) -> List[int]:
+        """prost `Message::encoded_len` of every message (payload arrays on the device)."""
+        built = messages if isinstance(messages, BuiltBatch) else build_batch(messages, kind)
+        out = (C.c_uint64 * max(1, built.n_msgs))()
+        self.ctx.check(lib().tfs_encode_size(self.ctx.handle, C.byref(built.batch), out))
+        return [int(out[i]) for i in range(built.n_msgs)]
+
+    def bound(self, built: BuiltBatch, flags: int = 0) -> int:
+        return int(lib().tfs_encode_bound(C.byref(built.batch), flags))
+
+    def encode(self, messages: Sequence, kind: int, flags: int = 0, dst=None) -> EncodedBatch:
+        """Device path: payload arrays are CUDA tensors, the wire bytes stay in HBM."""
+        built = messages if isinstance(messages, BuiltBatch) else build_batch(messages, kind)
+        if dst is None:
+            dst = torch.empty(self.bound(built, flags), dtype=torch.uint8, device=f"cuda:{self.ctx.device}")
+        n = built.n_msgs
+        off, ln, total = (C.c_uint64 * max(1, n))(), (C.c_uint64 * max(1, n))(), C.c_uint64(0)
+        self.ctx.check(lib().tfs_encode(self.ctx.handle, C.byref(built.batch), C.c_void_p(dst.data_ptr()), dst.numel(), flags,
+                                        off, ln, C.byref(total)))
+        return EncodedBatch(dst, [int(off[i]) for i in range(n)], [int(ln[i]) for i in range(n)], int(total.value), flags)
+
+    def encode_host(self, messages: Sequence, kind: int, flags: int = 0, dst: Optional[np.ndarray] = None) -> EncodedBatch:
+        """End to end: payload arrays in host memory, wire bytes returned in host memory."""
+        built = messages if isinstance(messages, BuiltBatch) else build_batch(messages, kind)
+        if dst is None:
+            dst = np.empty(self.bound(built, flags), dtype=np.uint8)
+        n = built.n_msgs
+        off, ln, total = (C.c_uint64 * max(1, n))(), (C.c_uint64 * max(1, n))(), C.c_uint64(0)
+        self.ctx.check(lib().tfs_encode_host(self.ctx.handle, C.byref(built.batch), C.c_void_p(dst.ctypes.data), dst.size, flags,
+                                             off, ln, C.byref(total)))
+        return EncodedBatch(dst, [int(off[i]) for i in range(n)], [int(ln[i]) for i in range(n)], int(total.value), flags)
+
+
+class DecodedBatch:
+    """Result of the decode scan: plain-data view + (after `values`) the value pool."""
+
+    def __init__(self, ctx: GpuContext, handle, status: int, kind: int):
+        self.ctx, self._h, self.status, self.kind = ctx, handle, status, kind
+        self.view = abi.DecodedView()
+        ctx.check(lib().tfs_decoded_view(self._h, C.byref(self.view)))
+        self.pool = None
+
+    @property
+    def pool_bytes(self) -> int:
+        return int(self.view.pool_bytes)
+
+    def messages(self) -> List[DecodedMessage]:
+        pool = self.pool
+        if pool is None:
+            raise RuntimeError("values have not been decoded yet")
+        if not isinstance(pool, np.ndarray):
+            pool = pool.cpu().numpy()
+        return messages_from_view(self.view, pool, self.kind)
+
+    def close(self):
+        if self._h:
+            lib().tfs_decoded_free(self.ctx.handle, self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class GpuDecoder:
+    """tonic `Decoder` for PredictResponse / PredictRequest / TensorProto batches."""
+
+    def __init__(self, ctx: GpuContext):
+        self.ctx = ctx
+
+    @staticmethod
+    def _arrays(offsets, lengths):
+        n = len(offsets)
+        return n, (C.c_uint64 * max(1, n))(*[int(x) for x in offsets]), (C.c_uint64 * max(1, n))(*[int(x) for x in lengths])
+
+    def scan(self, wire, offsets, lengths, kind: int, flags: int = 0) -> DecodedBatch:
+        """Pass 1 on device-resident wire bytes (torch.uint8 CUDA tensor)."""
+        n, off, ln = self._arrays(offsets, lengths)
+        h = C.c_void_p()
+        st = lib().tfs_decode_scan(self.ctx.handle, C.c_void_p(wire.data_ptr() if wire.numel() else 0), wire.numel(), off, ln, n, kind,
+                                   flags, C.byref(h))
+        self.ctx.check(st, ok=(abi.TFS_OK, abi.TFS_ERR_BATCH))
+        return DecodedBatch(self.ctx, h, st, kind)
+
+    def values(self, dec: DecodedBatch, pool=None) -> DecodedBatch:
+        """Pass 2: write every value into a device pool."""
+        if pool is None:
+            pool = torch.empty(max(1, dec.pool_bytes), dtype=torch.uint8, device=f"cuda:{self.ctx.device}")
+        self.ctx.check(lib().tfs_decode(self.ctx.handle, dec._h, C.c_void_p(pool.data_ptr()), pool.numel()))
+        dec.pool = pool
+        return dec
+
+    def decode(self, wire, offsets, lengths, kind: int, flags: int = 0, pool=None) -> DecodedBatch:
+        return self.values(self.scan(wire, offsets, lengths, kind, flags), pool)
+
+    def decode_host(self, wire: np.ndarray, offsets, lengths, kind: int, flags: int = 0, pool: Optional[np.ndarray] = None) -> DecodedBatch:
+        """End to end: wire bytes in host memory, values returned in a host pool."""
+        wire = np.ascontiguousarray(wire, dtype=np.uint8)
+        n, off, ln = self._arrays(offsets, lengths)
+        h = C.c_void_p()
+        st = lib().tfs_decode_host(self.ctx.handle, C.c_void_p(wire.ctypes.data if wire.size else 0), wire.size, off, ln, n, kind, flags,
+                                   C.byref(h))
+        self.ctx.check(st, ok=(abi.TFS_OK, abi.TFS_ERR_BATCH))
+        dec = DecodedBatch(self.ctx, h, st, kind)
+        if pool is None:
+            pool = np.empty(max(1, dec.pool_bytes), dtype=np.uint8)
+        self.ctx.check(lib().tfs_decode_host_finish(self.ctx.handle, dec._h, C.c_void_p(pool.ctypes.data), pool.size))
+        dec.pool = pool
+        return dec
+
+
+class GpuCodec:
+    """`impl tonic::codec::Codec for GpuCodec { fn encoder(..); fn decoder(..) }`"""
+
+    def __init__(self, ctx: Optional[GpuContext] = None):
+        self.ctx = ctx or GpuContext()
+
+    def encoder(self) -> GpuEncoder:
+        return GpuEncoder(self.ctx)
+
+    def decoder(self) -> GpuDecoder:
+        return GpuDecoder(self.ctx)

@@ -1,0 +1,1157 @@
+// tfs_decode.cu — batched TensorProto / PredictRequest / PredictResponse DECODE on sm_100a.
+//
+// Replaces, on the reference path (response of src/lib.rs:265, returned at src/lib.rs:266), what tonic's
+// ProstDecoder does: prost `Message::decode` = merge loop + derived merge_field.
+//   structure walk (decode_key / merge_field / hash_map::merge / skip_field)  -> K6d k_walk<COUNT>, k_walk<FILL>
+//                                                                                 (one thread per message)
+//   *::merge_repeated for varint types (decode_varint + push per element)      -> K4a k_varint_count (terminator ballots),
+//                                                                                 K4b k_span_scan, K4c k_varint_gather
+//   float/double::merge_repeated, bytes::merge                                 -> K5 k_copy (tfs_copy.cu)
+// Element counts are known before any value is written (prost grows its Vecs by doubling instead).
+// Integer / byte work bound by HBM bandwidth: no tensor cores.
+#include <cstring>
+#include <new>
+
+#include "tfs_device.cuh"
+
+struct tfs_decoded {
+  uint64_t generation = 0;
+  tfs_ctx* owner = nullptr;
+  tfs::DecTables T{};
+  uint64_t totals[8] = {0};
+  std::vector<tfs_msg_out_t> msgs;
+  std::vector<tfs_tensor_out_t> tensors;
+  std::vector<tfs_span_t> filters;
+  std::vector<uint8_t> strings;
+  uint32_t n_failed = 0;
+  bool host_staged = false;  // wire was staged by tfs_decode_host
+  uint64_t stage_generation = 0;
+};
+
+namespace tfs {
+
+namespace {
+
+enum { WT_VARINT = 0, WT_64 = 1, WT_LEN = 2, WT_SGROUP = 3, WT_EGROUP = 4, WT_32 = 5 };
+enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED };
+
+__device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
+  // 4..13 -> 0..9, 16 -> 10, 17 -> 11
+  return tag <= 13 ? tag - 4u : tag - 6u;
+}
+
+// Rust core::str::from_utf8 validity (no overlongs, no surrogates, <= U+10FFFF)
+__device__ bool utf8_ok(const uint8_t* p, uint32_t n) {
+  uint32_t i = 0;
+  while (i < n) {
+    const uint8_t b = p[i];
+    if (b < 0x80) {
+      i += 1;
+    } else if (b >= 0xC2 && b <= 0xDF) {
+      if (i + 1 >= n || (p[i + 1] & 0xC0) != 0x80) return false;
+      i += 2;
+    } else if (b >= 0xE0 && b <= 0xEF) {
+      if (i + 2 >= n) return false;
+      const uint8_t c1 = p[i + 1], c2 = p[i + 2];
+      const uint8_t lo = b == 0xE0 ? 0xA0 : 0x80, hi = b == 0xED ? 0x9F : 0xBF;
+      if (c1 < lo || c1 > hi || (c2 & 0xC0) != 0x80) return false;
+      i += 3;
+    } else if (b >= 0xF0 && b <= 0xF4) {
+      if (i + 3 >= n) return false;
+      const uint8_t c1 = p[i + 1], c2 = p[i + 2], c3 = p[i + 3];
+      const uint8_t lo = b == 0xF0 ? 0x90 : 0x80, hi = b == 0xF4 ? 0x8F : 0xBF;
+      if (c1 < lo || c1 > hi || (c2 & 0xC0) != 0x80 || (c3 & 0xC0) != 0x80) return false;
+      i += 4;
+    } else {
+      return false;
+    }
+  }
+  return true;
+}
+
+__device__ __forceinline__ uint32_t varint_tiles_of(const uint8_t* wire, uint64_t off, uint64_t len) {
+  if (len == 0) return 0;
+  const uint64_t a = reinterpret_cast<uintptr_t>(wire) + off;
+  const uint64_t a0 = a & ~static_cast<uint64_t>(15);
+  return static_cast<uint32_t>((a + len - a0 + kDecTileBytes - 1) / kDecTileBytes);
+}
+
+// =====================================================================================================
+// K6d: structure walk, one thread per message.  FILL == false counts what the message needs
+// (tensors, filters, spans, string bytes, tiles) and finds structural errors; FILL == true repeats
+// the identical traversal and writes the records at the bases the scan of the counts produced.
+// =====================================================================================================
+template <bool FILL>
+struct Walker {
+  const DecTables& T;
+  const uint8_t* w;  // wire base
+  uint64_t beg, end, pos;
+  uint32_t msg;
+  int32_t err = 0;
+  uint64_t err_pos = 0;
+  bool soft_unsupported = false;
+  // counters (COUNT) / cursors (FILL)
+  uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0;
+  // current tensor
+  uint32_t cur = 0;
+  uint32_t cur_dims = 0;
+  uint32_t content_span = 0xFFFFFFFFu;
+
+  __device__ Walker(const DecTables& t, uint32_t m) : T(t), w(t.wire), msg(m) {}
+
+  __device__ __forceinline__ bool fail(int32_t code) {
+    if (!err) {
+      err = code;
+      err_pos = pos - beg;
+    }
+    return false;
+  }
+  // prost decode_varint: <= 10 bytes, the 10th byte's high bits fall off, running out of buffer or a
+  // 10th continuation byte is "invalid varint"
+  __device__ bool varint(uint64_t* v) {
+    uint64_t r = 0;
+    const uint64_t rem = end - pos;
+    const uint32_t n = rem < 10 ? static_cast<uint32_t>(rem) : 10u;
+    for (uint32_t i = 0; i < n; ++i) {
+      const uint8_t b = w[pos++];
+      r |= static_cast<uint64_t>(b & 0x7F) << (7u * i);
+      if (b < 0x80) {
+        *v = r;
+        return true;
+      }
+    }
+    return fail(TFS_ERR_INVALID_VARINT);
+  }
+  __device__ bool key(uint32_t* tag, uint32_t* wt) {
+    uint64_t k;
+    if (!varint(&k)) return false;
+    if (k > 0xFFFFFFFFull) return fail(TFS_ERR_INVALID_KEY);
+    const uint32_t x = static_cast<uint32_t>(k & 7u);
+    if (x > 5u) return fail(TFS_ERR_WIRE_TYPE_VALUE);
+    const uint32_t t = static_cast<uint32_t>(k) >> 3;
+    if (t < 1u) return fail(TFS_ERR_INVALID_TAG);
+    *tag = t;
+    *wt = x;
+    return true;
+  }
+  __device__ __forceinline__ bool check_wt(uint32_t expected, uint32_t actual) { return expected == actual ? true : fail(TFS_ERR_WIRE_TYPE); }
+  // merge_loop prologue / epilogue
+  __device__ bool loop_begin(uint64_t* region_end) {
+    uint64_t len;
+    if (!varint(&len)) return false;
+    if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+    *region_end = pos + len;
+    return true;
+  }
+  __device__ __forceinline__ bool loop_end(uint64_t region_end) { return pos == region_end ? true : fail(TFS_ERR_LENGTH_EXCEEDED); }
+
+  __device__ bool skip_simple(uint32_t wt) {
+    uint64_t len = 0;
+    switch (wt) {
+      case WT_VARINT: {
+        uint64_t v;
+        if (!varint(&v)) return false;
+        break;
+      }
+      case WT_32: len = 4; break;
+      case WT_64: len = 8; break;
+      case WT_LEN:
+        if (!varint(&len)) return false;
+        break;
+      default: return fail(TFS_ERR_END_GROUP);  // a stray end-group
+    }
+    if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+    pos += len;
+    return true;
+  }
+  // prost skip_field with its recursion budget `ctx`; groups are unwound iteratively
+  __device__ bool skip(uint32_t wt, uint32_t tag, uint32_t ctx) {
+    if (ctx == 0) return fail(TFS_ERR_RECURSION);
+    if (wt != WT_SGROUP) return skip_simple(wt);
+    uint32_t stack[100];
+    uint32_t depth = 1;
+    stack[0] = tag;
+    while (depth > 0) {
+      uint32_t it, iw;
+      if (!key(&it, &iw)) return false;
+      if (iw == WT_EGROUP) {
+        if (it != stack[depth - 1]) return fail(TFS_ERR_END_GROUP);
+        --depth;
+        continue;
+      }
+      if (ctx - depth == 0) return fail(TFS_ERR_RECURSION);
+      if (iw == WT_SGROUP) {
+        stack[depth++] = it;
+        continue;
+      }
+      if (!skip_simple(iw)) return false;
+    }
+    return true;
+  }
+
+  // ---- outputs ----
+  __device__ tfs_span_t add_string(uint64_t off, uint32_t len) {
+    tfs_span_t sp;
+    sp.off = n_str;
+    sp.len = len;
+    sp._pad = 0;
+    if (FILL)
+      for (uint32_t i = 0; i < len; ++i) T.strings[n_str + i] = w[off + i];
+    n_str += len;
+    return sp;
+  }
+  // string::merge: LEN wire type, length check, UTF-8 check
+  __device__ bool string_field(uint32_t wt, tfs_span_t* out) {
+    if (!check_wt(WT_LEN, wt)) return false;
+    uint64_t len;
+    if (!varint(&len)) return false;
+    if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+    const uint64_t off = pos;
+    pos += len;
+    if (!utf8_ok(w + off, static_cast<uint32_t>(len))) return fail(TFS_ERR_UTF8);
+    *out = add_string(off, static_cast<uint32_t>(len));
+    return true;
+  }
+
+  __device__ void begin_tensor() {
+    cur = n_tensors++;
+    cur_dims = 0;
+    content_span = 0xFFFFFFFFu;
+    if (FILL) T.tensors[cur].msg_index = msg;
+  }
+  __device__ void add_span(uint32_t slot, uint32_t cls, uint64_t off, uint64_t len, uint64_t n_elems, uint32_t out_mult) {
+    const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(w, off, len) : 0u;
+    const uint32_t ct = cls == SC_COPY ? static_cast<uint32_t>((len * out_mult + kCopyTileBytes - 1) / kCopyTileBytes) : 0u;
+    if (FILL) {
+      DecSpan s;
+      s.wire_off = off;
+      s.len = len;
+      s.elem_base = 0;
+      s.n_elems = n_elems;
+      s.tensor = cur;
+      s.slot = slot;
+      s.msg = msg;
+      s.cls = cls;
+      s.first_tile = cls == SC_VARINT ? n_vt : n_ct;
+      s.elem_tile0 = n_vt;
+      T.spans[n_spans] = s;
+      // both numberings stay monotone over the span table (a span owns no tiles of the other class)
+      T.span_vtile0[n_spans] = n_vt;
+      T.span_ctile0[n_spans] = n_ct;
+    }
+    n_spans++;
+    n_vt += vt;
+    n_ct += ct;
+  }
+
+  // {int32,int64,uint32,uint64,bool}::merge_repeated
+  __device__ bool repeated_varint(uint32_t slot, uint32_t wt) {
+    if (wt == WT_LEN) {
+      uint64_t rend;
+      if (!loop_begin(&rend)) return false;
+      const uint64_t off = pos, len = rend - pos;
+      if (len) {
+        // does the last varint of the body end exactly at the limit?  prost reads on past it.
+        if (w[rend - 1] & 0x80) {
+          uint32_t k = 0;  // continuation bytes at the end of the body
+          while (k < 10 && k < len && (w[rend - 1 - k] & 0x80)) ++k;
+          pos = rend;
+          if (k >= 10) return fail(TFS_ERR_INVALID_VARINT);
+          for (uint32_t j = k; j < 10; ++j) {
+            if (pos >= end) return fail(TFS_ERR_INVALID_VARINT);
+            if (!(w[pos++] & 0x80)) return fail(TFS_ERR_LENGTH_EXCEEDED);
+          }
+          return fail(TFS_ERR_INVALID_VARINT);
+        }
+        add_span(slot, SC_VARINT, off, len, 0, 1);
+      }
+      pos = rend;
+      return true;
+    }
+    if (!check_wt(WT_VARINT, wt)) return false;
+    const uint64_t off = pos;
+    uint64_t v;
+    if (!varint(&v)) return false;
+    add_span(slot, SC_VARINT, off, pos - off, 0, 1);
+    return true;
+  }
+  // {float,double}::merge_repeated
+  __device__ bool repeated_fixed(uint32_t slot, uint32_t wt, uint32_t width) {
+    if (wt == WT_LEN) {
+      uint64_t rend;
+      if (!loop_begin(&rend)) return false;
+      const uint64_t off = pos, len = rend - pos;
+      const uint64_t rem = len % width;
+      if (rem) {  // the last element straddles the limit, or the buffer ends inside it
+        pos = rend - rem;
+        if (end - pos >= width) {
+          pos += width;
+          return fail(TFS_ERR_LENGTH_EXCEEDED);
+        }
+        return fail(TFS_ERR_BUFFER_UNDERFLOW);
+      }
+      if (len) add_span(slot, SC_COPY, off, len, len / width, 1);
+      pos = rend;
+      return true;
+    }
+    if (!check_wt(width == 4 ? WT_32 : WT_64, wt)) return false;
+    if (end - pos < width) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+    add_span(slot, SC_COPY, pos, width, 1, 1);
+    pos += width;
+    return true;
+  }
+
+  __device__ bool dim_field(uint32_t tag, uint32_t wt, uint32_t ctx, int64_t* size) {
+    if (tag == 1) {
+      if (!check_wt(WT_VARINT, wt)) return false;
+      uint64_t v;
+      if (!varint(&v)) return false;
+      *size = static_cast<int64_t>(v);
+      return true;
+    }
+    if (tag == 2) {
+      tfs_span_t sp;
+      const uint32_t before = n_str;
+      if (!string_field(wt, &sp)) return false;
+      n_str = before;  // Dim.name is not carried; a non-empty one makes the message UNSUPPORTED
+      if (sp.len) soft_unsupported = true;
+      return true;
+    }
+    return skip(wt, tag, ctx);
+  }
+  __device__ bool shape_field(uint32_t tag, uint32_t wt, uint32_t ctx) {
+    if (tag == 2) {  // repeated Dim
+      if (!check_wt(WT_LEN, wt)) return false;
+      uint64_t rend;
+      if (!loop_begin(&rend)) return false;
+      int64_t size = 0;
+      while (pos < rend) {
+        uint32_t t2, w2;
+        if (!key(&t2, &w2)) return false;
+        if (!dim_field(t2, w2, ctx - 1, &size)) return false;
+      }
+      if (!loop_end(rend)) return false;
+      if (cur_dims < TFS_MAX_DIMS) {
+        if (FILL) T.tensors[cur].dims[cur_dims] = size;
+      } else {
+        soft_unsupported = true;
+      }
+      cur_dims++;
+      if (FILL) T.tensors[cur].n_dims = cur_dims;
+      return true;
+    }
+    if (tag == 3) {
+      if (!check_wt(WT_VARINT, wt)) return false;
+      uint64_t v;
+      if (!varint(&v)) return false;
+      if (FILL) T.tensors[cur].unknown_rank = v != 0;
+      return true;
+    }
+    return skip(wt, tag, ctx);
+  }
+  // TensorProto::merge_field; `ctx` is the recursion budget its fields are merged with
+  __device__ bool tensor_field(uint32_t tag, uint32_t wt, uint32_t ctx) {
+    switch (tag) {
+      case 1:
+      case 3: {
+        if (!check_wt(WT_VARINT, wt)) return false;
+        uint64_t v;
+        if (!varint(&v)) return false;
+        if (FILL) {
+          if (tag == 1) T.tensors[cur].dtype = static_cast<int32_t>(v);
+          else T.tensors[cur].version_number = static_cast<int32_t>(v);
+        }
+        return true;
+      }
+      case 2: {
+        if (!check_wt(WT_LEN, wt)) return false;
+        uint64_t rend;
+        if (!loop_begin(&rend)) return false;
+        if (FILL) T.tensors[cur].has_shape = 1;
+        while (pos < rend) {
+          uint32_t t2, w2;
+          if (!key(&t2, &w2)) return false;
+          if (!shape_field(t2, w2, ctx - 1)) return false;
+        }
+        return loop_end(rend);
+      }
+      case 4: {  // bytes::merge: the last occurrence replaces earlier ones
+        if (!check_wt(WT_LEN, wt)) return false;
+        uint64_t len;
+        if (!varint(&len)) return false;
+        if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+        if (FILL && content_span != 0xFFFFFFFFu) {
+          T.spans[content_span].len = 0;
+          T.spans[content_span].n_elems = 0;
+        }
+        content_span = n_spans;
+        add_span(0, SC_COPY, pos, len, len, (T.flags & TFS_F_CONTENT_HALF_TO_F32) ? 2u : 1u);
+        pos += len;
+        return true;
+      }
+      case 5: case 9: return repeated_fixed(slot_of(tag), wt, 4);
+      case 6: case 12: return repeated_fixed(slot_of(tag), wt, 8);
+      case 7: case 10: case 11: case 13: case 16: case 17: return repeated_varint(slot_of(tag), wt);
+      case 8: case 14: case 15: return fail(TFS_ERR_UNSUPPORTED);  // string_val / resource / variant: left to prost
+      default: return skip(wt, tag, ctx);
+    }
+  }
+  __device__ bool tensor_message(uint32_t wt, uint32_t ctx) {  // message::merge of a TensorProto
+    if (!check_wt(WT_LEN, wt)) return false;
+    uint64_t rend;
+    if (!loop_begin(&rend)) return false;
+    while (pos < rend) {
+      uint32_t t2, w2;
+      if (!key(&t2, &w2)) return false;
+      if (!tensor_field(t2, w2, ctx - 1)) return false;
+    }
+    return loop_end(rend);
+  }
+  // hash_map::merge — the map field's own wire type is not looked at
+  __device__ bool map_entry(uint32_t ctx) {
+    uint64_t rend;
+    if (!loop_begin(&rend)) return false;
+    begin_tensor();
+    while (pos < rend) {
+      uint32_t t2, w2;
+      if (!key(&t2, &w2)) return false;
+      if (t2 == 1) {
+        tfs_span_t sp;
+        if (!string_field(w2, &sp)) return false;
+        if (FILL) T.tensors[cur].key = sp;
+      } else if (t2 == 2) {
+        if (!tensor_message(w2, ctx - 1)) return false;
+      } else if (!skip(w2, t2, ctx - 1)) {
+        return false;
+      }
+    }
+    return loop_end(rend);
+  }
+  __device__ bool model_spec(uint32_t wt, uint32_t ctx, tfs_msg_out_t* mo) {
+    if (!check_wt(WT_LEN, wt)) return false;
+    uint64_t rend;
+    if (!loop_begin(&rend)) return false;
+    mo->has_model_spec = 1;
+    while (pos < rend) {
+      uint32_t t2, w2;
+      if (!key(&t2, &w2)) return false;
+      switch (t2) {
+        case 1:
+          if (!string_field(w2, &mo->model_name)) return false;
+          break;
+        case 3:
+          if (!string_field(w2, &mo->signature_name)) return false;
+          break;
+        case 4:
+          if (!string_field(w2, &mo->version_label)) return false;
+          mo->version_choice = TFS_VERSION_LABEL;
+          mo->version = 0;
+          break;
+        case 2: {  // Int64Value: oneof merge keeps the value when the variant is already `version`
+          if (!check_wt(WT_LEN, w2)) return false;
+          uint64_t r2;
+          if (!loop_begin(&r2)) return false;
+          if (mo->version_choice != TFS_VERSION_NUMBER) mo->version = 0;
+          while (pos < r2) {
+            uint32_t t3, w3;
+            if (!key(&t3, &w3)) return false;
+            if (t3 == 1) {
+              if (!check_wt(WT_VARINT, w3)) return false;
+              uint64_t v;
+              if (!varint(&v)) return false;
+              mo->version = static_cast<int64_t>(v);
+            } else if (!skip(w3, t3, ctx - 2)) {
+              return false;
+            }
+          }
+          if (!loop_end(r2)) return false;
+          mo->version_choice = TFS_VERSION_NUMBER;
+          mo->version_label.off = 0;
+          mo->version_label.len = 0;
+          break;
+        }
+        default:
+          if (!skip(w2, t2, ctx - 1)) return false;
+      }
+    }
+    return loop_end(rend);
+  }
+
+  __device__ bool run(tfs_msg_out_t* mo) {
+    if (T.flags & TFS_F_GRPC_PREFIX) {  // tonic Streaming: flag byte 0, u32 big-endian length
+      const uint64_t n = end - beg;
+      if (n < 5) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+      if (w[beg] != 0) return fail(TFS_ERR_GRPC_FLAG);
+      const uint64_t l = (static_cast<uint64_t>(w[beg + 1]) << 24) | (static_cast<uint64_t>(w[beg + 2]) << 16) |
+                         (static_cast<uint64_t>(w[beg + 3]) << 8) | w[beg + 4];
+      pos = beg + 1;
+      if (l != n - 5) return fail(l > n - 5 ? TFS_ERR_BUFFER_UNDERFLOW : TFS_ERR_LENGTH_EXCEEDED);
+      pos = beg + 5;
+    }
+    const uint64_t body = pos;
+    if (T.msg_kind == TFS_MSG_TENSOR_PROTO) begin_tensor();
+    while (pos < end) {
+      uint32_t tag, wt;
+      if (!key(&tag, &wt)) return false;
+      bool ok;
+      if (T.msg_kind == TFS_MSG_TENSOR_PROTO) {
+        ok = tensor_field(tag, wt, 100);
+      } else if (T.msg_kind == TFS_MSG_PREDICT_REQUEST) {
+        if (tag == 1) ok = model_spec(wt, 100, mo);
+        else if (tag == 2) ok = map_entry(100);
+        else if (tag == 3) {
+          tfs_span_t sp;
+          ok = string_field(wt, &sp);
+          if (ok) {
+            if (FILL) T.filters[n_filters] = sp;
+            n_filters++;
+          }
+        } else ok = skip(wt, tag, 100);
+      } else {
+        if (tag == 1) ok = map_entry(100);
+        else if (tag == 2) ok = model_spec(wt, 100, mo);
+        else ok = skip(wt, tag, 100);
+      }
+      if (!ok) return false;
+    }
+    (void)body;
+    if (soft_unsupported) {
+      pos = beg;
+      return fail(TFS_ERR_UNSUPPORTED);
+    }
+    return true;
+  }
+};
+
+template <bool FILL>
+__global__ void __launch_bounds__(128) k_walk(DecTables T) {
+  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (mi >= T.n_msgs) return;
+  Walker<FILL> wk(T, mi);
+  wk.beg = T.msg_off[mi];
+  wk.end = wk.beg + T.msg_len[mi];
+  wk.pos = wk.beg;
+  tfs_msg_out_t mo;
+  memset(&mo, 0, sizeof(mo));
+  if (!FILL) {
+    const bool in_bounds = wk.end <= T.wire_bytes && wk.end >= wk.beg;
+    bool ok = in_bounds ? wk.run(&mo) : wk.fail(TFS_ERR_BUFFER_UNDERFLOW);
+    T.msgs[mi].status = ok ? TFS_OK : wk.err;
+    T.msgs[mi].err_offset = ok ? 0 : wk.err_pos;
+    T.cnt_tensors[mi] = ok ? wk.n_tensors : 0u;
+    T.cnt_filters[mi] = ok ? wk.n_filters : 0u;
+    T.cnt_spans[mi] = ok ? wk.n_spans : 0u;
+    T.cnt_strbytes[mi] = ok ? wk.n_str : 0u;
+    T.cnt_vtiles[mi] = ok ? wk.n_vt : 0u;
+    T.cnt_ctiles[mi] = ok ? wk.n_ct : 0u;
+  } else {
+    const int32_t st = T.msgs[mi].status;
+    const uint64_t eo = T.msgs[mi].err_offset;
+    // cnt_* now hold the exclusive prefixes
+    wk.n_tensors = T.cnt_tensors[mi];
+    wk.n_filters = T.cnt_filters[mi];
+    wk.n_spans = T.cnt_spans[mi];
+    wk.n_str = T.cnt_strbytes[mi];
+    wk.n_vt = T.cnt_vtiles[mi];
+    wk.n_ct = T.cnt_ctiles[mi];
+    mo.first_tensor = wk.n_tensors;
+    mo.first_filter = wk.n_filters;
+    const uint32_t t0 = wk.n_tensors, f0 = wk.n_filters;
+    if (st == TFS_OK) {
+      wk.run(&mo);
+      mo.n_tensors = wk.n_tensors - t0;
+      mo.n_filters = wk.n_filters - f0;
+    } else {
+      mo.status = st;
+      mo.err_offset = eo;
+    }
+    T.msgs[mi] = mo;
+  }
+}
+
+// exclusive scan of `a[0..n)` in place by one 1024-thread CTA; returns the total in every thread
+__device__ uint64_t cta_scan_u32(uint32_t* a, uint32_t n, uint64_t* smem) {
+  uint64_t carry = 0;
+  for (uint32_t base = 0; base < n; base += 1024) {
+    const uint32_t i = base + threadIdx.x;
+    const uint64_t v = i < n ? a[i] : 0u;
+    uint64_t total;
+    const uint64_t ex = block_exclusive_scan<uint64_t, 32>(v, smem, &total);
+    if (i < n) a[i] = static_cast<uint32_t>(carry + ex);
+    carry += total;
+    __syncthreads();
+  }
+  return carry;
+}
+
+__global__ void __launch_bounds__(1024) k_scan_counts(DecTables T) {
+  __shared__ uint64_t smem[33];
+  const uint64_t t0 = cta_scan_u32(T.cnt_tensors, T.n_msgs, smem);
+  const uint64_t t1 = cta_scan_u32(T.cnt_filters, T.n_msgs, smem);
+  const uint64_t t2 = cta_scan_u32(T.cnt_spans, T.n_msgs, smem);
+  const uint64_t t3 = cta_scan_u32(T.cnt_strbytes, T.n_msgs, smem);
+  const uint64_t t4 = cta_scan_u32(T.cnt_vtiles, T.n_msgs, smem);
+  const uint64_t t5 = cta_scan_u32(T.cnt_ctiles, T.n_msgs, smem);
+  if (threadIdx.x == 0) {
+    T.totals[TOT_TENSORS] = t0;
+    T.totals[TOT_FILTERS] = t1;
+    T.totals[TOT_SPANS] = t2;
+    T.totals[TOT_STR] = t3;
+    T.totals[TOT_VTILES] = t4;
+    T.totals[TOT_CTILES] = t5;
+    T.totals[TOT_POOL] = 0;
+    T.totals[TOT_FAILED] = 0;
+  }
+}
+
+// =====================================================================================================
+// K4a: terminators per 4 KiB tile of a packed varint body (a terminator is a byte with its MSB clear),
+// plus detection of >10-byte varints: 10 consecutive continuation bytes inside the body.
+// Tiles are cut on 16-byte boundaries of the absolute address so every thread's 16-byte load is aligned.
+// =====================================================================================================
+struct TileRef {
+  uint64_t span_abs0;  // absolute address of the first byte of the span
+  uint64_t span_end;   // absolute address one past its last byte
+  uint64_t tile_abs;   // absolute (16-byte aligned) address of the tile's first byte
+  uint32_t span;
+  uint32_t msg;
+};
+
+__device__ __forceinline__ TileRef locate_vtile(const DecTables& T, uint32_t n_spans, uint64_t tile) {
+  const uint32_t si = find_segment(T.span_vtile0, n_spans, static_cast<uint32_t>(tile));
+  const DecSpan& s = T.spans[si];
+  TileRef r;
+  r.span = si;
+  r.msg = s.msg;
+  r.span_abs0 = reinterpret_cast<uintptr_t>(T.wire) + s.wire_off;
+  r.span_end = r.span_abs0 + s.len;
+  r.tile_abs = (r.span_abs0 & ~static_cast<uint64_t>(15)) + (tile - T.span_vtile0[si]) * kDecTileBytes;
+  return r;
+}
+
+// 16 bytes of the tile owned by this thread: continuation mask and validity mask (bit j = byte j)
+__device__ __forceinline__ void chunk_masks(uint64_t chunk_abs, uint64_t span_abs0, uint64_t span_end, uint4* data,
+                                            uint32_t* cont, uint32_t* valid) {
+  if (chunk_abs + 16 <= span_abs0 || chunk_abs >= span_end) {
+    *data = make_uint4(0, 0, 0, 0);
+    *cont = 0;
+    *valid = 0;
+    return;
+  }
+  const uint4 d = ld_stream16(reinterpret_cast<const void*>(chunk_abs));
+  *data = d;
+  // MSB of each byte -> one bit per byte
+  auto msb4 = [](uint32_t x) { return ((x >> 7) & 1u) | ((x >> 14) & 2u) | ((x >> 21) & 4u) | ((x >> 28) & 8u); };
+  const uint32_t m = msb4(d.x) | (msb4(d.y) << 4) | (msb4(d.z) << 8) | (msb4(d.w) << 12);
+  uint32_t v = 0xFFFFu;
+  if (chunk_abs < span_abs0) v &= 0xFFFFu << (span_abs0 - chunk_abs);
+  if (chunk_abs + 16 > span_end) v &= 0xFFFFu >> (chunk_abs + 16 - span_end);
+  *valid = v & 0xFFFFu;
+  *cont = m & *valid;
+}
+
+__global__ void __launch_bounds__(kDecThreads) k_varint_count(DecTables T, uint32_t n_spans, uint64_t n_tiles) {
+  __shared__ TileRef s_ref;
+  __shared__ uint32_t warp_cnt[kDecThreads / 32];
+  for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_ref = locate_vtile(T, n_spans, tile);
+    __syncthreads();
+    const TileRef r = s_ref;
+    const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 16ull;
+    uint4 d;
+    uint32_t cont, valid;
+    chunk_masks(chunk_abs, r.span_abs0, r.span_end, &d, &cont, &valid);
+    const uint32_t term = ~cont & valid;
+    uint32_t cnt = __popc(term);
+    // continuation mask of the previous 16 bytes (previous lane, or a re-load across warp / tile edges)
+    uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, cont, 1);
+    if (lane_id() == 0) {
+      uint4 pd;
+      uint32_t pv;
+      chunk_masks(chunk_abs - 16, r.span_abs0, r.span_end, &pd, &prev, &pv);
+    }
+    uint32_t x = (cont << 16) | prev;  // bit i..i+9 all set <=> ten continuation bytes in a row
+    x &= x >> 1;
+    x &= x >> 2;
+    x &= x >> 4;
+    x &= x >> 2;
+    if (x) {
+      const uint64_t at = chunk_abs > r.span_abs0 ? chunk_abs : r.span_abs0;
+      const uint64_t off = at - reinterpret_cast<uintptr_t>(T.wire) - T.msg_off[r.msg];
+      atomicMin(&T.err[r.msg], (static_cast<unsigned long long>(off) << 8) | TFS_ERR_INVALID_VARINT);
+    }
+    cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
+    if (lane_id() == 0) warp_cnt[warp_id()] = cnt;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t t = 0;
+#pragma unroll
+      for (int i = 0; i < kDecThreads / 32; ++i) t += warp_cnt[i];
+      T.tile_count[tile] = t;
+    }
+  }
+}
+
+// K4b: per varint span, exclusive scan of its tile counts (one warp per span) -> tile_base, n_elems
+__global__ void __launch_bounds__(256) k_span_scan(DecTables T, uint32_t n_spans, uint64_t n_vtiles) {
+  const uint32_t si = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (si >= n_spans) return;
+  if (T.spans[si].cls != SC_VARINT) return;
+  const uint64_t t0 = T.span_vtile0[si];
+  const uint64_t t1 = si + 1 < n_spans ? T.span_vtile0[si + 1] : n_vtiles;
+  const uint32_t nt = static_cast<uint32_t>(t1 - t0);
+  uint64_t carry = 0;
+  for (uint32_t base = 0; base < nt; base += 128) {
+    const uint32_t i0 = base + lane_id() * 4u;
+    uint32_t x[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) x[j] = (i0 + j < nt) ? T.tile_count[t0 + i0 + j] : 0u;
+    const uint32_t s = x[0] + x[1] + x[2] + x[3];
+    const uint32_t incl = warp_inclusive_scan(s);
+    uint64_t o = carry + (incl - s);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (i0 + j < nt) T.tile_base[t0 + i0 + j] = o;
+      o += x[j];
+    }
+    carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
+  }
+  if (lane_id() == 0) T.spans[si].n_elems = carry;
+}
+
+// Element type a slot is decoded to, and its size
+__device__ __forceinline__ int32_t slot_dst_type(uint32_t slot, int32_t dtype, uint32_t flags, uint64_t content_len) {
+  const bool half16 = dtype == 19 || dtype == 14;
+  switch (slot) {
+    case 0: return (half16 && (flags & TFS_F_CONTENT_HALF_TO_F32) && content_len % 2 == 0) ? TFS_T_F32 : TFS_T_U8;
+    case 1: case 5: return TFS_T_F32;
+    case 2: case 8: return TFS_T_F64;
+    case 3: return TFS_T_I32;
+    case 6: return TFS_T_I64;
+    case 7: return TFS_T_BOOL;
+    case 9: return (half16 && (flags & TFS_F_HALF_TO_F32)) ? TFS_T_F32 : TFS_T_I32;
+    case 10: return TFS_T_U32;
+    case 11: return TFS_T_U64;
+    default: return TFS_T_U8;
+  }
+}
+__device__ __forceinline__ uint32_t type_size_dev(int32_t t) {
+  switch (t) {
+    case TFS_T_U8: case TFS_T_I8: case TFS_T_BOOL: return 1;
+    case TFS_T_U16: case TFS_T_I16: case TFS_T_F16: case TFS_T_BF16: return 2;
+    case TFS_T_I32: case TFS_T_U32: case TFS_T_F32: return 4;
+    default: return 8;
+  }
+}
+// bytes a slot occupies in the pool
+__device__ __forceinline__ uint64_t slot_pool_bytes(uint32_t slot, int32_t type, uint64_t n) {
+  if (slot == 0) return type == TFS_T_F32 ? n * 2 : n;  // n = wire bytes of tensor_content
+  return n * type_size_dev(type);
+}
+
+// K6e: per message, in wire order: element base of every span inside its (tensor, slot) vector, element
+// totals per slot, final status (walk errors + varint errors found by K4a), pool bytes per tensor.
+__global__ void __launch_bounds__(128) k_dec_finalize(DecTables T) {
+  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (mi >= T.n_msgs) return;
+  tfs_msg_out_t& mo = T.msgs[mi];
+  const unsigned long long e = T.err[mi];
+  if (mo.status == TFS_OK && e != ~0ull) {
+    mo.status = static_cast<int32_t>(e & 0xFF);
+    mo.err_offset = e >> 8;
+  }
+  const uint32_t s0 = T.cnt_spans[mi];
+  const uint32_t s1 = mi + 1 < T.n_msgs ? T.cnt_spans[mi + 1] : static_cast<uint32_t>(T.totals[TOT_SPANS]);
+  for (uint32_t si = s0; si < s1; ++si) {
+    DecSpan& s = T.spans[si];
+    tfs_tensor_out_t& t = T.tensors[s.tensor];
+    s.elem_base = t.n_elems[s.slot];
+    t.n_elems[s.slot] += s.n_elems;
+  }
+  for (uint32_t ti = mo.first_tensor; ti < mo.first_tensor + mo.n_tensors; ++ti) {
+    tfs_tensor_out_t& t = T.tensors[ti];
+    uint64_t bytes = 0;
+    for (uint32_t sl = 0; sl < TFS_N_SLOTS; ++sl) {
+      const int32_t ty = slot_dst_type(sl, t.dtype, T.flags, t.n_elems[sl]);
+      t.dst_type[sl] = ty;
+      t.dst_off[sl] = bytes;  // relative to the tensor's base for now
+      bytes += (slot_pool_bytes(sl, ty, t.n_elems[sl]) + 63u) & ~static_cast<uint64_t>(63);
+    }
+    T.tensor_pool[ti] = bytes;
+  }
+  if (mo.status != TFS_OK) {  // a failed message exposes nothing
+    mo.n_tensors = 0;
+    mo.n_filters = 0;
+    mo.has_model_spec = 0;
+    atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_FAILED]), 1ull);
+  }
+}
+
+// exclusive scan of the per-tensor pool bytes, then absolute slot offsets. Single CTA.
+__global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_tensors) {
+  __shared__ uint64_t smem[33];
+  uint64_t carry = 0;
+  for (uint32_t base = 0; base < n_tensors; base += 1024) {
+    const uint32_t i = base + threadIdx.x;
+    const uint64_t v = i < n_tensors ? T.tensor_pool[i] : 0ull;
+    uint64_t total;
+    const uint64_t ex = block_exclusive_scan<uint64_t, 32>(v, smem, &total);
+    if (i < n_tensors) {
+      const uint64_t b = carry + ex;
+      for (uint32_t sl = 0; sl < TFS_N_SLOTS; ++sl) T.tensors[i].dst_off[sl] += b;
+    }
+    carry += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) T.totals[TOT_POOL] = carry;
+}
+
+// at decode time: bind every copy-class span to its place in the caller's pool
+__global__ void __launch_bounds__(256) k_dec_bind(DecTables T, uint32_t n_spans, uint8_t* pool) {
+  const uint32_t si = blockIdx.x * blockDim.x + threadIdx.x;
+  if (si >= n_spans) return;
+  const DecSpan& s = T.spans[si];
+  CopySeg g;
+  g.first_tile = T.span_ctile0[si];
+  g.src = T.wire + s.wire_off;
+  g.dst = nullptr;
+  g.n = 0;
+  g.op = CP_BYTES;
+  g.param = 0.f;
+  if (s.cls == SC_COPY && s.len != 0 && T.msgs[s.msg].status == TFS_OK) {
+    const tfs_tensor_out_t& t = T.tensors[s.tensor];
+    const int32_t ty = t.dst_type[s.slot];
+    if (s.slot == 0) {
+      if (ty == TFS_T_F32) {
+        g.op = t.dtype == 19 ? CP_F16_F32 : CP_BF16_F32;
+        g.n = s.len / 2;
+      } else {
+        g.n = s.len;
+      }
+      g.dst = pool + t.dst_off[0];
+    } else {
+      g.n = s.len;  // fixed-width values are copied as bytes
+      g.dst = pool + t.dst_off[s.slot] + s.elem_base * type_size_dev(ty);
+    }
+  }
+  T.segs[si] = g;
+}
+
+// =====================================================================================================
+// K4c: gather.  Every thread owns 16 wire bytes; each terminator in them ends one value, which is
+// reassembled by walking back over at most 9 continuation bytes (shared memory, 16-byte halo).
+// The value index = span element base + tile base + block-exclusive count of terminators.
+// =====================================================================================================
+struct GatherRef {
+  TileRef r;
+  uint8_t* dst;        // pool address of element 0 of this tile
+  int32_t dst_type;
+  int32_t half_kind;   // 19 = f16, 14 = bf16 (only with dst_type F32 on the half_val slot)
+  uint32_t live;
+};
+
+__device__ __forceinline__ void store_value(uint8_t* dst, uint64_t idx, uint64_t v, int32_t type, int32_t half_kind) {
+  switch (type) {
+    case TFS_T_I32: case TFS_T_U32: reinterpret_cast<uint32_t*>(dst)[idx] = static_cast<uint32_t>(v); break;  // `as i32` truncates
+    case TFS_T_I64: case TFS_T_U64: reinterpret_cast<uint64_t*>(dst)[idx] = v; break;
+    case TFS_T_BOOL: dst[idx] = v != 0; break;
+    case TFS_T_F32: {
+      const uint32_t h = static_cast<uint32_t>(v) & 0xFFFFu;
+      reinterpret_cast<float*>(dst)[idx] = half_kind == 19 ? f16_bits_to_f32(h) : bf16_bits_to_f32(h);
+      break;
+    }
+    default: break;
+  }
+}
+
+__global__ void __launch_bounds__(kDecThreads) k_varint_gather(DecTables T, uint32_t n_spans, uint64_t n_tiles, uint8_t* pool) {
+  __shared__ __align__(16) uint8_t sm[16 + kDecTileBytes];
+  __shared__ GatherRef s_ref;
+  __shared__ uint32_t scan_smem[kDecThreads / 32 + 1];
+  for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      GatherRef g;
+      g.r = locate_vtile(T, n_spans, tile);
+      const DecSpan& s = T.spans[g.r.span];
+      const tfs_tensor_out_t& t = T.tensors[s.tensor];
+      g.dst_type = t.dst_type[s.slot];
+      g.half_kind = t.dtype;
+      g.live = T.msgs[s.msg].status == TFS_OK;
+      g.dst = pool + t.dst_off[s.slot] + (s.elem_base + T.tile_base[tile]) * type_size_dev(g.dst_type);
+      s_ref = g;
+    }
+    __syncthreads();
+    const GatherRef g = s_ref;
+    if (!g.live) continue;
+    const TileRef& r = g.r;
+    const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 16ull;
+    uint4 d;
+    uint32_t cont, valid;
+    chunk_masks(chunk_abs, r.span_abs0, r.span_end, &d, &cont, &valid);
+    *reinterpret_cast<uint4*>(sm + 16 + threadIdx.x * 16) = d;
+    if (threadIdx.x == 0) {
+      uint4 h;
+      uint32_t hc, hv;
+      chunk_masks(r.tile_abs - 16, r.span_abs0, r.span_end, &h, &hc, &hv);
+      *reinterpret_cast<uint4*>(sm) = h;
+    }
+    uint32_t term = ~cont & valid;
+    uint32_t total;
+    uint32_t idx = block_exclusive_scan<uint32_t, kDecThreads / 32>(__popc(term), scan_smem, &total);
+    // first byte of the span in tile coordinates (never walk back across it)
+    const int32_t lo = r.span_abs0 > r.tile_abs ? static_cast<int32_t>(r.span_abs0 - r.tile_abs) : -16;
+    while (term) {
+      const int32_t j = __ffs(term) - 1;
+      term &= term - 1;
+      const int32_t p = static_cast<int32_t>(threadIdx.x) * 16 + j;
+      uint64_t v = sm[16 + p];
+#pragma unroll 1
+      for (int32_t k = 1; k <= 9; ++k) {
+        const int32_t q = p - k;
+        if (q < lo) break;
+        const uint8_t b = sm[16 + q];
+        if (b < 0x80) break;
+        v = (v << 7) | (b & 0x7Fu);
+      }
+      store_value(g.dst, idx, v, g.dst_type, g.half_kind);
+      ++idx;
+    }
+  }
+}
+
+// =====================================================================================================
+// host orchestration
+// =====================================================================================================
+size_t carve(size_t* cur, size_t bytes, size_t align = 64) {
+  size_t off = align_up(*cur, align);
+  *cur = off + bytes;
+  return off;
+}
+
+}  // namespace
+
+tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off,
+                                const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, tfs_decoded** out) {
+  TFS_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (msg_kind < TFS_MSG_TENSOR_PROTO || msg_kind > TFS_MSG_PREDICT_RESPONSE) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad msg_kind");
+  tfs_decoded* dec = new (std::nothrow) tfs_decoded();
+  if (!dec) return TFS_ERR_NOMEM;
+  dec->owner = ctx;
+  dec->generation = ++ctx->dec_generation;
+  DecTables& T = dec->T;
+  std::memset(&T, 0, sizeof(T));
+  auto bail = [&](tfs_status_t st) {
+    delete dec;
+    return st;
+  };
+#define DEC_TRY(expr)                         \
+  do {                                        \
+    tfs_status_t st__ = (expr);               \
+    if (st__ != TFS_OK) return bail(st__);    \
+  } while (0)
+#define DEC_CUDA(call)                                                  \
+  do {                                                                  \
+    cudaError_t e__ = (call);                                           \
+    if (e__ != cudaSuccess) return bail(cuda_fail(ctx, e__, #call));    \
+  } while (0)
+
+  // ---- pass 1 tables: message ranges, counters, per-message status (msgs[]) and error words
+  size_t cur = 0;
+  const size_t o_off = carve(&cur, 8ull * n_msgs), o_len = carve(&cur, 8ull * n_msgs), o_ct = carve(&cur, 4ull * n_msgs),
+               o_cf = carve(&cur, 4ull * n_msgs), o_cs = carve(&cur, 4ull * n_msgs), o_cb = carve(&cur, 4ull * n_msgs),
+               o_cv = carve(&cur, 4ull * n_msgs), o_cc = carve(&cur, 4ull * n_msgs), o_tot = carve(&cur, 64),
+               o_msgs = carve(&cur, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs)), o_err = carve(&cur, 8ull * n_msgs);
+  DEC_TRY(dev_reserve(ctx, &ctx->d_dec1, cur + 64));
+  DEC_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, 16ull * n_msgs + 64));
+  uint8_t* d1 = static_cast<uint8_t*>(ctx->d_dec1.p);
+  uint64_t* h = static_cast<uint64_t*>(ctx->h_up);
+  if (n_msgs) {
+    std::memcpy(h, msg_off, 8ull * n_msgs);
+    std::memcpy(h + n_msgs, msg_len, 8ull * n_msgs);
+    DEC_CUDA(cudaMemcpyAsync(d1 + o_off, h, 8ull * n_msgs, cudaMemcpyHostToDevice, ctx->stream));
+    DEC_CUDA(cudaMemcpyAsync(d1 + o_len, h + n_msgs, 8ull * n_msgs, cudaMemcpyHostToDevice, ctx->stream));
+    DEC_CUDA(cudaMemsetAsync(d1 + o_err, 0xFF, 8ull * n_msgs, ctx->stream));
+  }
+  T.wire = static_cast<const uint8_t*>(wire_dev);
+  T.wire_bytes = wire_bytes;
+  T.msg_off = reinterpret_cast<const uint64_t*>(d1 + o_off);
+  T.msg_len = reinterpret_cast<const uint64_t*>(d1 + o_len);
+  T.n_msgs = n_msgs;
+  T.msg_kind = msg_kind;
+  T.flags = flags;
+  T.cnt_tensors = reinterpret_cast<uint32_t*>(d1 + o_ct);
+  T.cnt_filters = reinterpret_cast<uint32_t*>(d1 + o_cf);
+  T.cnt_spans = reinterpret_cast<uint32_t*>(d1 + o_cs);
+  T.cnt_strbytes = reinterpret_cast<uint32_t*>(d1 + o_cb);
+  T.cnt_vtiles = reinterpret_cast<uint32_t*>(d1 + o_cv);
+  T.cnt_ctiles = reinterpret_cast<uint32_t*>(d1 + o_cc);
+  T.totals = reinterpret_cast<uint64_t*>(d1 + o_tot);
+  T.msgs = reinterpret_cast<tfs_msg_out_t*>(d1 + o_msgs);
+  T.err = reinterpret_cast<unsigned long long*>(d1 + o_err);
+
+  const uint32_t mblocks = (n_msgs + 127) / 128;
+  if (n_msgs) {
+    k_walk<false><<<mblocks, 128, 0, ctx->stream>>>(T);
+    ctx->launches++;
+  }
+  k_scan_counts<<<1, 1024, 0, ctx->stream>>>(T);
+  ctx->launches++;
+  DEC_CUDA(cudaGetLastError());
+  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, 64));
+  DEC_CUDA(cudaMemcpyAsync(ctx->h_down, T.totals, 64, cudaMemcpyDeviceToHost, ctx->stream));
+  DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1: the sizes of the pass-2 tables
+  std::memcpy(dec->totals, ctx->h_down, 64);
+  const uint64_t n_tensors = dec->totals[TOT_TENSORS], n_filters = dec->totals[TOT_FILTERS], n_spans = dec->totals[TOT_SPANS],
+                 n_str = dec->totals[TOT_STR], n_vt = dec->totals[TOT_VTILES];
+  if (n_tensors > 0xFFFFFFF0ull || n_spans > 0xFFFFFFF0ull || n_vt > 0xFFFFFFF0ull) return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large"));
+
+  // ---- pass 2 tables
+  cur = 0;
+  const size_t p_ten = carve(&cur, sizeof(tfs_tensor_out_t) * n_tensors), p_flt = carve(&cur, sizeof(tfs_span_t) * n_filters),
+               p_str = carve(&cur, n_str), p_spn = carve(&cur, sizeof(DecSpan) * n_spans), p_sv = carve(&cur, 4 * (n_spans + 1)),
+               p_sc = carve(&cur, 4 * (n_spans + 1)), p_tc = carve(&cur, 4 * n_vt), p_tb = carve(&cur, 8 * n_vt),
+               p_seg = carve(&cur, sizeof(CopySeg) * n_spans), p_tp = carve(&cur, 8 * n_tensors);
+  DEC_TRY(dev_reserve(ctx, &ctx->d_dec2, cur + 64));
+  uint8_t* d2 = static_cast<uint8_t*>(ctx->d_dec2.p);
+  T.tensors = reinterpret_cast<tfs_tensor_out_t*>(d2 + p_ten);
+  T.filters = reinterpret_cast<tfs_span_t*>(d2 + p_flt);
+  T.strings = d2 + p_str;
+  T.spans = reinterpret_cast<DecSpan*>(d2 + p_spn);
+  T.span_vtile0 = reinterpret_cast<uint32_t*>(d2 + p_sv);
+  T.span_ctile0 = reinterpret_cast<uint32_t*>(d2 + p_sc);
+  T.tile_count = reinterpret_cast<uint32_t*>(d2 + p_tc);
+  T.tile_base = reinterpret_cast<uint64_t*>(d2 + p_tb);
+  T.segs = reinterpret_cast<CopySeg*>(d2 + p_seg);
+  T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);
+  if (n_tensors) DEC_CUDA(cudaMemsetAsync(T.tensors, 0, sizeof(tfs_tensor_out_t) * n_tensors, ctx->stream));
+  if (n_msgs) {
+    k_walk<true><<<mblocks, 128, 0, ctx->stream>>>(T);
+    ctx->launches++;
+  }
+  if (n_vt) {
+    const uint64_t cap = static_cast<uint64_t>(ctx->sm_count) * 8;
+    {
+      ProfScope prof(ctx, PK_VARINT_COUNT);
+      k_varint_count<<<static_cast<uint32_t>(n_vt < cap ? n_vt : cap), kDecThreads, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);
+    }
+    ctx->launches++;
+  }
+  if (n_spans) {
+    k_span_scan<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);
+    ctx->launches++;
+  }
+  if (n_msgs) {
+    k_dec_finalize<<<mblocks, 128, 0, ctx->stream>>>(T);
+    ctx->launches++;
+  }
+  k_pool_layout<<<1, 1024, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors));
+  ctx->launches++;
+  DEC_CUDA(cudaGetLastError());
+
+  // ---- results to the host
+  dec->msgs.resize(n_msgs);
+  dec->tensors.resize(n_tensors);
+  dec->filters.resize(n_filters);
+  dec->strings.resize(n_str);
+  size_t hc = 0;
+  const size_t h_msgs = carve(&hc, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs)), h_ten = carve(&hc, sizeof(tfs_tensor_out_t) * n_tensors),
+               h_flt = carve(&hc, sizeof(tfs_span_t) * n_filters), h_str = carve(&hc, n_str), h_tot = carve(&hc, 64);
+  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, hc + 64));
+  uint8_t* hd = static_cast<uint8_t*>(ctx->h_down);
+  if (n_msgs) DEC_CUDA(cudaMemcpyAsync(hd + h_msgs, T.msgs, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs), cudaMemcpyDeviceToHost, ctx->stream));
+  if (n_tensors) DEC_CUDA(cudaMemcpyAsync(hd + h_ten, T.tensors, sizeof(tfs_tensor_out_t) * n_tensors, cudaMemcpyDeviceToHost, ctx->stream));
+  if (n_filters) DEC_CUDA(cudaMemcpyAsync(hd + h_flt, T.filters, sizeof(tfs_span_t) * n_filters, cudaMemcpyDeviceToHost, ctx->stream));
+  if (n_str) DEC_CUDA(cudaMemcpyAsync(hd + h_str, T.strings, n_str, cudaMemcpyDeviceToHost, ctx->stream));
+  DEC_CUDA(cudaMemcpyAsync(hd + h_tot, T.totals, 64, cudaMemcpyDeviceToHost, ctx->stream));
+  DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #2: the caller needs the element counts to allocate
+  if (n_msgs) std::memcpy(dec->msgs.data(), hd + h_msgs, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs));
+  if (n_tensors) std::memcpy(dec->tensors.data(), hd + h_ten, sizeof(tfs_tensor_out_t) * n_tensors);
+  if (n_filters) std::memcpy(dec->filters.data(), hd + h_flt, sizeof(tfs_span_t) * n_filters);
+  if (n_str) std::memcpy(dec->strings.data(), hd + h_str, n_str);
+  std::memcpy(dec->totals, hd + h_tot, 64);
+  dec->n_failed = static_cast<uint32_t>(dec->totals[TOT_FAILED]);
+  *out = dec;
+#undef DEC_TRY
+#undef DEC_CUDA
+  return dec->n_failed ? TFS_ERR_BATCH : TFS_OK;
+}
+
+tfs_status_t decode_device(tfs_ctx* ctx, tfs_decoded* dec, void* pool_dev, uint64_t pool_bytes) {
+  TFS_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (dec->owner != ctx || dec->generation != ctx->dec_generation)
+    return set_err(ctx, TFS_ERR_INVALID_ARG, "stale decode handle: another tfs_decode_scan ran on this ctx since");
+  if (pool_bytes < dec->totals[TOT_POOL] || (!pool_dev && dec->totals[TOT_POOL]))
+    return set_err(ctx, TFS_ERR_NOMEM, "value pool is smaller than tfs_decoded_view().pool_bytes");
+  const DecTables& T = dec->T;
+  const uint64_t n_spans = dec->totals[TOT_SPANS], n_vt = dec->totals[TOT_VTILES], n_ct = dec->totals[TOT_CTILES];
+  uint8_t* pool = static_cast<uint8_t*>(pool_dev);
+  if (n_spans) {
+    k_dec_bind<<<static_cast<uint32_t>((n_spans + 255) / 256), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), pool);
+    ctx->launches++;
+  }
+  if (n_vt) {
+    const uint64_t cap = static_cast<uint64_t>(ctx->sm_count) * 8;
+    {
+      ProfScope prof(ctx, PK_VARINT_GATHER);
+      k_varint_gather<<<static_cast<uint32_t>(n_vt < cap ? n_vt : cap), kDecThreads, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt, pool);
+    }
+    ctx->launches++;
+  }
+  TFS_CUDA(ctx, cudaGetLastError());
+  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, nullptr, nullptr));
+  return TFS_OK;
+}
+
+uint64_t decoded_pool_bytes(const tfs_decoded* dec) { return dec->totals[TOT_POOL]; }
+void decoded_mark_host_staged(tfs_decoded* dec, uint64_t stage_generation) {
+  dec->host_staged = true;
+  dec->stage_generation = stage_generation;
+}
+bool decoded_stage_is_current(const tfs_decoded* dec, uint64_t stage_generation) {
+  return dec->host_staged && dec->stage_generation == stage_generation;
+}
+
+}  // namespace tfs
+
+using namespace tfs;
+
+extern "C" {
+
+tfs_status_t tfs_decode_scan(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off,
+                             const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, tfs_decoded_t** out) {
+  if (!ctx || !out || (n_msgs && (!msg_off || !msg_len)) || (wire_bytes && !wire_dev)) return TFS_ERR_INVALID_ARG;
+  *out = nullptr;
+  return decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, out);
+}
+
+tfs_status_t tfs_decoded_view(const tfs_decoded_t* dec, tfs_decoded_view_t* view) {
+  if (!dec || !view) return TFS_ERR_INVALID_ARG;
+  view->msgs = dec->msgs.data();
+  view->tensors = dec->tensors.data();
+  view->filters = dec->filters.data();
+  view->strings = dec->strings.data();
+  view->strings_bytes = dec->strings.size();
+  view->pool_bytes = dec->totals[TOT_POOL];
+  view->n_msgs = static_cast<uint32_t>(dec->msgs.size());
+  view->n_tensors = static_cast<uint32_t>(dec->tensors.size());
+  view->n_filters = static_cast<uint32_t>(dec->filters.size());
+  view->n_failed = dec->n_failed;
+  return TFS_OK;
+}
+
+tfs_status_t tfs_decode(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_dev, uint64_t pool_bytes) {
+  if (!ctx || !dec) return TFS_ERR_INVALID_ARG;
+  TFS_TRY(decode_device(ctx, dec, pool_dev, pool_bytes));
+  TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return TFS_OK;
+}
+
+tfs_status_t tfs_decoded_free(tfs_ctx_t* ctx, tfs_decoded_t* dec) {
+  (void)ctx;
+  delete dec;
+  return TFS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,132 @@
+// tfs_device.cuh — device-side building blocks (sm_100a).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include "tfs_internal.h"
+
+namespace tfs {
+
+// ---- varint arithmetic (prost encoded_len_varint: max(1, ceil(bits / 7)); reference path src/lib.rs:265) ----
+__device__ __forceinline__ uint32_t varint_len(uint64_t v) { return (70u - static_cast<uint32_t>(__clzll(static_cast<long long>(v | 1)))) / 7u; }
+
+__device__ __forceinline__ uint32_t key_len(int32_t field_number) { return field_number < 16 ? 1u : 2u; }
+
+// ---- 16-bit float casts: round-to-nearest-even in hardware, NaN -> quiet NaN keeping sign + top payload ----
+__device__ __forceinline__ uint32_t f32_to_f16_bits(float f) {
+  uint32_t x = __float_as_uint(f);
+  if ((x & 0x7FFFFFFFu) > 0x7F800000u) return ((x >> 16) & 0x8000u) | 0x7E00u | ((x >> 13) & 0x01FFu);
+  return static_cast<uint32_t>(__half_as_ushort(__float2half_rn(f)));
+}
+__device__ __forceinline__ uint32_t f32_to_bf16_bits(float f) {
+  uint32_t x = __float_as_uint(f);
+  if ((x & 0x7FFFFFFFu) > 0x7F800000u) return (x >> 16) | 0x0040u;
+  return static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(f)));
+}
+__device__ __forceinline__ float f16_bits_to_f32(uint32_t h) { return __half2float(__ushort_as_half(static_cast<unsigned short>(h))); }
+__device__ __forceinline__ float bf16_bits_to_f32(uint32_t h) { return __uint_as_float(h << 16); }
+
+// ---- element fetch for the varint encoder ---------------------------------------------------------
+template <int MODE>
+__device__ __forceinline__ uint64_t load_varint_value(const void* __restrict__ src, uint64_t i) {
+  if constexpr (MODE == VM_I64) return static_cast<uint64_t>(__ldg(static_cast<const long long*>(src) + i));
+  else if constexpr (MODE == VM_I32) return static_cast<uint64_t>(static_cast<int64_t>(__ldg(static_cast<const int32_t*>(src) + i)));
+  else if constexpr (MODE == VM_U32) return static_cast<uint64_t>(__ldg(static_cast<const uint32_t*>(src) + i));
+  else if constexpr (MODE == VM_I16) return static_cast<uint64_t>(static_cast<int64_t>(__ldg(static_cast<const int16_t*>(src) + i)));
+  else if constexpr (MODE == VM_U16) return static_cast<uint64_t>(__ldg(static_cast<const uint16_t*>(src) + i));
+  else if constexpr (MODE == VM_I8) return static_cast<uint64_t>(static_cast<int64_t>(__ldg(static_cast<const int8_t*>(src) + i)));
+  else if constexpr (MODE == VM_U8) return static_cast<uint64_t>(__ldg(static_cast<const uint8_t*>(src) + i));
+  else if constexpr (MODE == VM_F32_F16) return static_cast<uint64_t>(f32_to_f16_bits(__ldg(static_cast<const float*>(src) + i)));
+  else return static_cast<uint64_t>(f32_to_bf16_bits(__ldg(static_cast<const float*>(src) + i)));
+}
+
+// ---- warp / block scans -----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+__device__ __forceinline__ uint32_t warp_id() { return threadIdx.x >> 5; }
+
+template <class T>
+__device__ __forceinline__ T warp_inclusive_scan(T v) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    T n = __shfl_up_sync(0xFFFFFFFFu, v, d);
+    if (lane_id() >= static_cast<uint32_t>(d)) v += n;
+  }
+  return v;
+}
+
+// Exclusive scan of one value per thread over a block of NW warps. `smem` holds NW + 1 entries.
+// Returns the exclusive prefix; *total receives the block sum. Contains two __syncthreads().
+template <class T, int NW>
+__device__ __forceinline__ T block_exclusive_scan(T v, T* smem, T* total) {
+  T incl = warp_inclusive_scan(v);
+  if (lane_id() == 31) smem[warp_id()] = incl;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    T run = 0;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+      T t = smem[w];
+      smem[w] = run;
+      run += t;
+    }
+    smem[NW] = run;
+  }
+  __syncthreads();
+  T base = smem[warp_id()];
+  *total = smem[NW];
+  return base + incl - v;
+}
+
+// Largest i in [0, n) with a[i] <= x (a is non-decreasing, a[0] <= x).
+template <class T>
+__device__ __forceinline__ uint32_t find_segment(const T* __restrict__ a, uint32_t n, T x) {
+  uint32_t lo = 0, hi = n;  // invariant: a[lo] <= x, (hi == n or a[hi] > x)
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (a[mid] <= x) lo = mid;
+    else hi = mid;
+  }
+  return lo;
+}
+
+// ---- byte sinks used by the message framing traversal ------------------------------------------------
+struct CountSink {
+  uint64_t pos = 0;
+  __device__ __forceinline__ void put(uint8_t) { pos += 1; }
+  __device__ __forceinline__ void put_bytes(const uint8_t*, uint32_t n) { pos += n; }
+  __device__ __forceinline__ void skip(uint64_t n) { pos += n; }
+};
+struct ByteSink {
+  uint8_t* base;
+  uint64_t pos;
+  __device__ __forceinline__ void put(uint8_t b) { base[pos++] = b; }
+  __device__ __forceinline__ void put_bytes(const uint8_t* p, uint32_t n) {
+    for (uint32_t i = 0; i < n; ++i) base[pos + i] = p[i];
+    pos += n;
+  }
+  __device__ __forceinline__ void skip(uint64_t n) { pos += n; }
+};
+template <class Sink>
+__device__ __forceinline__ void put_varint(Sink& s, uint64_t v) {
+  while (v >= 0x80) {
+    s.put(static_cast<uint8_t>((v & 0x7F) | 0x80));
+    v >>= 7;
+  }
+  s.put(static_cast<uint8_t>(v));
+}
+template <class Sink>
+__device__ __forceinline__ void put_key(Sink& s, uint32_t field_number, uint32_t wire_type) {
+  put_varint(s, (static_cast<uint64_t>(field_number) << 3) | wire_type);
+}
+
+// ---- 16-byte global accesses that bypass L1 allocation (streaming data is touched once) -----------------
+__device__ __forceinline__ uint4 ld_stream16(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ void st_stream16(void* p, const uint4& v) {
+  asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+}  // namespace tfs

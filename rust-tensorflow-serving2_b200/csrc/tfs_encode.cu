@@ -1,0 +1,772 @@
+// tfs_encode.cu — batched TensorProto / PredictRequest / PredictResponse ENCODE on sm_100a.
+//
+// Replaces, on the reference path `self.prediction_client.predict(request)` (src/lib.rs:265), what tonic's
+// ProstEncoder does with the message built at src/lib.rs:249-263:
+//   prost Message::encoded_len  -> K1 k_varint_tiles<SIZE> + K2 k_field_scan + K6a k_msg_layout   (sized ONCE;
+//                                  prost re-walks a nested packed varint field 5 times)
+//   prost Message::encode_raw   -> K6b k_msg_scan + k_write_headers (framing bytes, device side)
+//                                  K3 k_varint_tiles<SCATTER>       (int32/int64/uint32/uint64/half_val bodies)
+//                                  K5 k_copy (tfs_copy.cu)          (float/double/complex/bool/tensor_content)
+// Nothing here is a contraction: integer / byte work bound by HBM bandwidth, no tensor cores.
+#include <algorithm>
+#include <cstring>
+
+#include "tfs_device.cuh"
+
+namespace tfs {
+
+namespace {
+
+// =====================================================================================================
+// K1 / K3: one CTA = one tile of 2048 elements = 8 warps x (8 rows x 32 lanes).
+// Row r of warp w holds elements tile*2048 + w*256 + r*32 + lane: every load is a fully coalesced
+// warp-wide access.  Lengths come from clz; the in-row prefix comes from ballots over the 4 bits of the
+// length (popc of the ballot below the lane), so no shuffle network traffic at all.
+// =====================================================================================================
+template <int MODE>
+__device__ __forceinline__ void load_rows(const EncField& f, uint64_t elem0, uint64_t (&v)[kVarintRows], uint32_t (&len)[kVarintRows]) {
+#pragma unroll
+  for (int r = 0; r < kVarintRows; ++r) {
+    uint64_t e = elem0 + static_cast<uint64_t>(r) * 32u + lane_id();
+    bool ok = e < f.n_elems;
+    v[r] = ok ? load_varint_value<MODE>(f.src, e) : 0ull;
+    len[r] = ok ? varint_len(v[r]) : 0u;
+  }
+}
+
+template <int MODE, bool SCATTER>
+__device__ __forceinline__ void varint_tile(const EncTables& T, const EncField& f, uint32_t tile, uint32_t tile_in_field,
+                                            uint8_t* __restrict__ dst_base, uint8_t* stage, uint32_t* warp_tot) {
+  const uint64_t elem0 = static_cast<uint64_t>(tile_in_field) * kVarintTile + warp_id() * (kVarintRows * 32u);
+  uint64_t v[kVarintRows];
+  uint32_t len[kVarintRows];
+  load_rows<MODE>(f, elem0, v, len);
+
+  if constexpr (!SCATTER) {
+    uint32_t s = 0;
+#pragma unroll
+    for (int r = 0; r < kVarintRows; ++r) s += len[r];
+    s = __reduce_add_sync(0xFFFFFFFFu, s);
+    if (lane_id() == 0) warp_tot[warp_id()] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      uint32_t t = 0;
+#pragma unroll
+      for (int w = 0; w < kVarintThreads / 32; ++w) t += warp_tot[w];
+      T.tile_bytes[tile] = t;
+    }
+    return;
+  } else {
+    const uint32_t lt = (1u << lane_id()) - 1u;
+    uint32_t off[kVarintRows];
+    uint32_t run = 0;
+#pragma unroll
+    for (int r = 0; r < kVarintRows; ++r) {
+      uint32_t b0 = __ballot_sync(0xFFFFFFFFu, len[r] & 1u);
+      uint32_t b1 = __ballot_sync(0xFFFFFFFFu, len[r] & 2u);
+      uint32_t b2 = __ballot_sync(0xFFFFFFFFu, len[r] & 4u);
+      uint32_t b3 = __ballot_sync(0xFFFFFFFFu, len[r] & 8u);
+      off[r] = run + __popc(b0 & lt) + 2u * __popc(b1 & lt) + 4u * __popc(b2 & lt) + 8u * __popc(b3 & lt);
+      run += __popc(b0) + 2u * __popc(b1) + 4u * __popc(b2) + 8u * __popc(b3);
+    }
+    if (lane_id() == 0) warp_tot[warp_id()] = run;
+    __syncthreads();
+    uint32_t wbase = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kVarintThreads / 32; ++w) {
+      uint32_t t = warp_tot[w];
+      if (w < static_cast<int>(warp_id())) wbase += t;
+      total += t;
+    }
+    uint8_t* g = dst_base + f.dst_off + T.tile_off[tile];
+    const uint32_t skew = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(g) & 15u);
+    // varint bytes into the CTA's staging window, positioned so that smem offset == global address mod 16
+#pragma unroll
+    for (int r = 0; r < kVarintRows; ++r) {
+      if (len[r]) {
+        uint8_t* p = stage + skew + wbase + off[r];
+        uint64_t x = v[r];
+        while (x >= 0x80) {
+          *p++ = static_cast<uint8_t>((x & 0x7F) | 0x80);
+          x >>= 7;
+        }
+        *p = static_cast<uint8_t>(x);
+      }
+    }
+    __syncthreads();
+    // flush: whole 16-byte words with vector stores, the ragged head / tail bytes one by one (a
+    // neighbouring tile owns the other bytes of those words and writes only its own)
+    uint8_t* ga = g - skew;
+    const uint32_t end = skew + total;
+    const uint32_t nchunks = (end + 15u) >> 4;
+    for (uint32_t c = threadIdx.x; c < nchunks; c += kVarintThreads) {
+      const uint32_t lo = c << 4, hi = lo + 16u;
+      if (lo >= skew && hi <= end) {
+        *reinterpret_cast<uint4*>(ga + lo) = *reinterpret_cast<const uint4*>(stage + lo);
+      } else {
+        const uint32_t b0 = lo > skew ? lo : skew, b1 = hi < end ? hi : end;
+        for (uint32_t b = b0; b < b1; ++b) ga[b] = stage[b];
+      }
+    }
+  }
+}
+
+template <bool SCATTER>
+__global__ void __launch_bounds__(kVarintThreads) k_varint_tiles(EncTables T, uint8_t* __restrict__ dst_base) {
+  __shared__ __align__(16) uint8_t stage[SCATTER ? (16 + kVarintTile * kVarintMaxLen + 16) : 16];
+  __shared__ uint32_t warp_tot[kVarintThreads / 32];
+  __shared__ uint32_t s_vf;
+  if (SCATTER && T.result[1] != 0) return;  // dst too small: nothing may be written
+  const uint32_t tile = blockIdx.x;
+  if (threadIdx.x == 0) s_vf = find_segment(T.vfield_first_tile, T.n_vfields, tile);
+  __syncthreads();
+  const uint32_t vf = s_vf;
+  const EncField f = T.fields[T.vfield_index[vf]];
+  const uint32_t tif = tile - T.vfield_first_tile[vf];
+  switch (f.mode) {
+    case VM_I64: varint_tile<VM_I64, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
+    case VM_I32: varint_tile<VM_I32, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
+    case VM_U32: varint_tile<VM_U32, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
+    case VM_I16: varint_tile<VM_I16, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
+    case VM_U16: varint_tile<VM_U16, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
+    case VM_I8: varint_tile<VM_I8, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
+    case VM_U8: varint_tile<VM_U8, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
+    case VM_F32_F16: varint_tile<VM_F32_F16, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
+    case VM_F32_BF16: varint_tile<VM_F32_BF16, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
+    default: break;
+  }
+}
+
+// =====================================================================================================
+// K2: per varint field, exclusive scan of its tile byte counts -> tile offsets + body length.
+// One warp per field; each lane takes 4 consecutive tiles per step.
+// =====================================================================================================
+__global__ void __launch_bounds__(256) k_field_scan(EncTables T) {
+  const uint32_t vf = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (vf >= T.n_vfields) return;
+  const uint32_t fi = T.vfield_index[vf];
+  const uint32_t t0 = T.vfield_first_tile[vf];
+  const uint32_t nt = T.vfield_first_tile[vf + 1] - t0;
+  uint64_t carry = 0;
+  for (uint32_t base = 0; base < nt; base += 128) {
+    const uint32_t i0 = base + lane_id() * 4u;
+    uint32_t x[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) x[j] = (i0 + j < nt) ? T.tile_bytes[t0 + i0 + j] : 0u;
+    const uint32_t s = x[0] + x[1] + x[2] + x[3];
+    const uint32_t incl = warp_inclusive_scan(s);
+    uint64_t o = carry + (incl - s);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (i0 + j < nt) T.tile_off[t0 + i0 + j] = o;
+      o += x[j];
+    }
+    carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
+  }
+  if (lane_id() == 0) T.fields[fi].body_len = carry;
+}
+
+// =====================================================================================================
+// K6: message framing.  One traversal template emits (or just counts) every byte of a message that
+// is not a bulk payload body, in prost's order: ascending field number, proto3 defaults skipped,
+// Option<Message> iff Some, oneof at its lowest tag, map entries in caller order.
+// =====================================================================================================
+__device__ __forceinline__ uint32_t dim_body_len(int64_t size) { return size != 0 ? 1u + varint_len(static_cast<uint64_t>(size)) : 0u; }
+
+__device__ __forceinline__ uint32_t shape_body_len(const EncTensor& t) {
+  uint32_t n = 0;
+  for (uint32_t i = 0; i < t.n_dims; ++i) n += 2u + dim_body_len(t.dims[i]);  // key + 1-byte length + Dim
+  if (t.unknown_rank) n += 2u;
+  return n;
+}
+
+__device__ __forceinline__ uint64_t str_field_len(uint32_t len) { return 1u + varint_len(len) + static_cast<uint64_t>(len); }
+
+__device__ __forceinline__ uint64_t spec_body_len(const EncMsg& m) {
+  uint64_t n = 0;
+  if (m.model_name.len) n += str_field_len(m.model_name.len);
+  if (m.version_choice == TFS_VERSION_NUMBER) n += 2u + (m.version != 0 ? 1u + varint_len(static_cast<uint64_t>(m.version)) : 0u);
+  else if (m.version_choice == TFS_VERSION_LABEL) n += str_field_len(m.version_label.len);
+  if (m.signature_name.len) n += str_field_len(m.signature_name.len);
+  return n;
+}
+
+__device__ __forceinline__ uint64_t tensor_body_len(const EncTables& T, const EncTensor& t) {
+  uint64_t n = 0;
+  if (t.dtype != 0) n += 1u + varint_len(static_cast<uint64_t>(static_cast<int64_t>(t.dtype)));
+  if (t.has_shape) {
+    uint32_t s = shape_body_len(t);
+    n += 1u + varint_len(s) + s;
+  }
+  if (t.version_number != 0) n += 1u + varint_len(static_cast<uint64_t>(static_cast<int64_t>(t.version_number)));
+  for (uint32_t i = 0; i < t.n_fields; ++i) {
+    const EncField& f = T.fields[t.first_field + i];
+    if (f.n_elems != 0) n += key_len(f.kind) + varint_len(f.body_len) + f.body_len;
+  }
+  return n;
+}
+
+template <class Sink>
+__device__ void emit_string(Sink& s, uint32_t field, const uint8_t* strings, StrRef r) {
+  put_key(s, field, 2);
+  put_varint(s, r.len);
+  s.put_bytes(strings + r.off, r.len);
+}
+
+template <class Sink>
+__device__ void emit_model_spec(Sink& s, const EncTables& T, const EncMsg& m, uint32_t field, uint64_t spec_len) {
+  put_key(s, field, 2);
+  put_varint(s, spec_len);
+  if (m.model_name.len) emit_string(s, 1, T.strings, m.model_name);
+  if (m.version_choice == TFS_VERSION_NUMBER) {
+    put_key(s, 2, 2);
+    if (m.version != 0) {
+      s.put(static_cast<uint8_t>(1u + varint_len(static_cast<uint64_t>(m.version))));
+      put_key(s, 1, 0);
+      put_varint(s, static_cast<uint64_t>(m.version));
+    } else {
+      s.put(0);
+    }
+  } else if (m.version_choice == TFS_VERSION_LABEL) {
+    emit_string(s, 4, T.strings, m.version_label);
+  }
+  if (m.signature_name.len) emit_string(s, 3, T.strings, m.signature_name);
+}
+
+// Emits the TensorProto body; for every payload field the body bytes are skipped (written by K3 / K5)
+// and `on_body(field_index, offset_of_body)` is called.
+template <class Sink, class OnBody>
+__device__ void emit_tensor_body(Sink& s, const EncTables& T, const EncTensor& t, OnBody on_body) {
+  if (t.dtype != 0) {
+    put_key(s, 1, 0);
+    put_varint(s, static_cast<uint64_t>(static_cast<int64_t>(t.dtype)));
+  }
+  if (t.has_shape) {
+    put_key(s, 2, 2);
+    put_varint(s, shape_body_len(t));
+    for (uint32_t i = 0; i < t.n_dims; ++i) {
+      put_key(s, 2, 2);
+      s.put(static_cast<uint8_t>(dim_body_len(t.dims[i])));
+      if (t.dims[i] != 0) {
+        put_key(s, 1, 0);
+        put_varint(s, static_cast<uint64_t>(t.dims[i]));
+      }
+    }
+    if (t.unknown_rank) {
+      put_key(s, 3, 0);
+      s.put(1);
+    }
+  }
+  if (t.version_number != 0) {
+    put_key(s, 3, 0);
+    put_varint(s, static_cast<uint64_t>(static_cast<int64_t>(t.version_number)));
+  }
+  for (uint32_t i = 0; i < t.n_fields; ++i) {
+    const uint32_t fi = t.first_field + i;
+    const EncField& f = T.fields[fi];
+    if (f.n_elems == 0) continue;
+    put_key(s, static_cast<uint32_t>(f.kind), 2);
+    put_varint(s, f.body_len);
+    on_body(fi, s.pos);
+    s.skip(f.body_len);
+  }
+}
+
+template <class Sink, class OnBody>
+__device__ void emit_message(Sink& s, const EncTables& T, uint32_t mi, OnBody on_body) {
+  const EncMsg& m = T.msgs[mi];
+  if (m.kind == TFS_MSG_TENSOR_PROTO) {
+    emit_tensor_body(s, T, T.tensors[m.first_tensor], on_body);
+    return;
+  }
+  const uint32_t map_field = m.kind == TFS_MSG_PREDICT_REQUEST ? 2u : 1u;
+  const uint32_t spec_field = m.kind == TFS_MSG_PREDICT_REQUEST ? 1u : 2u;
+  if (m.has_model_spec && spec_field == 1u) emit_model_spec(s, T, m, 1, T.spec_len[mi]);
+  for (uint32_t i = 0; i < m.n_tensors; ++i) {
+    const uint32_t ti = m.first_tensor + i;
+    const EncTensor& t = T.tensors[ti];
+    put_key(s, map_field, 2);
+    put_varint(s, T.entry_len[ti]);
+    if (t.name.len) emit_string(s, 1, T.strings, t.name);
+    if (T.tensor_len[ti] != 0) {  // TensorProto::default() <=> zero encoded length
+      put_key(s, 2, 2);
+      put_varint(s, T.tensor_len[ti]);
+      emit_tensor_body(s, T, t, on_body);
+    }
+  }
+  if (m.has_model_spec && spec_field == 2u) emit_model_spec(s, T, m, 2, T.spec_len[mi]);
+  if (m.kind == TFS_MSG_PREDICT_REQUEST)
+    for (uint32_t i = 0; i < m.n_filters; ++i) emit_string(s, 3, T.strings, T.filters[m.first_filter + i]);
+}
+
+// K6a: nested lengths bottom-up (once), then the message length and the offset of its largest bulk body.
+__global__ void __launch_bounds__(128) k_msg_layout(EncTables T) {
+  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (mi >= T.n_msgs) return;
+  const EncMsg& m = T.msgs[mi];
+  for (uint32_t i = 0; i < m.n_tensors; ++i) {
+    const uint32_t ti = m.first_tensor + i;
+    const EncTensor& t = T.tensors[ti];
+    const uint64_t tl = tensor_body_len(T, t);
+    T.tensor_len[ti] = tl;
+    uint64_t el = 0;
+    if (t.name.len) el += str_field_len(t.name.len);
+    if (tl != 0) el += 1u + varint_len(tl) + tl;
+    T.entry_len[ti] = el;
+  }
+  T.spec_len[mi] = m.has_model_spec ? spec_body_len(m) : 0;
+  CountSink s;
+  uint64_t best_len = 0, best_off = 0;
+  emit_message(s, T, mi, [&](uint32_t fi, uint64_t off) {
+    const EncField& f = T.fields[fi];
+    if (!f.is_varint && f.body_len > best_len) {
+      best_len = f.body_len;
+      best_off = off;
+    }
+  });
+  T.msg_len[mi] = s.pos;
+  T.msg_pay_off[mi] = best_off;
+}
+
+// K6b: exclusive scan of the message slots -> msg_off; total and overflow flag.  Single CTA.
+__global__ void __launch_bounds__(1024) k_msg_scan(EncTables T, uint32_t flags, uint32_t dst_skew, uint64_t dst_capacity) {
+  __shared__ uint64_t smem[33];
+  const uint32_t prefix = (flags & TFS_F_GRPC_PREFIX) ? 5u : 0u;
+  uint64_t carry = 0;
+  for (uint32_t base = 0; base < T.n_msgs; base += 1024) {
+    const uint32_t mi = base + threadIdx.x;
+    uint64_t slot = 0, pad = 0;
+    if (mi < T.n_msgs) {
+      const uint64_t len = T.msg_len[mi] + prefix;
+      if (flags & TFS_F_ALIGN_PAYLOAD) {
+        pad = (16u - ((dst_skew + prefix + T.msg_pay_off[mi]) & 15u)) & 15u;
+        slot = (pad + len + 15u) & ~static_cast<uint64_t>(15);
+      } else {
+        slot = len;
+      }
+    }
+    uint64_t total;
+    const uint64_t excl = block_exclusive_scan<uint64_t, 32>(slot, smem, &total);
+    if (mi < T.n_msgs) T.msg_off[mi] = carry + excl + pad;
+    carry += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    T.result[0] = carry;
+    T.result[1] = carry > dst_capacity ? 1u : 0u;
+  }
+}
+
+// K6c: write every framing byte, record where each payload body goes.
+__global__ void __launch_bounds__(128) k_write_headers(EncTables T, uint8_t* __restrict__ dst, uint32_t flags) {
+  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (mi >= T.n_msgs || T.result[1] != 0) return;
+  ByteSink s{dst, T.msg_off[mi]};
+  if (flags & TFS_F_GRPC_PREFIX) {  // tonic encode_client: 0x00, u32 big-endian length
+    const uint32_t l = static_cast<uint32_t>(T.msg_len[mi]);
+    s.put(0);
+    s.put(static_cast<uint8_t>(l >> 24));
+    s.put(static_cast<uint8_t>(l >> 16));
+    s.put(static_cast<uint8_t>(l >> 8));
+    s.put(static_cast<uint8_t>(l));
+  }
+  emit_message(s, T, mi, [&](uint32_t fi, uint64_t off) {
+    EncField& f = T.fields[fi];
+    f.dst_off = off;
+    if (!f.is_varint) T.segs[f.first_tile].dst = dst + off;
+  });
+}
+
+// =====================================================================================================
+// host: validate + compile the descriptors into one upload blob
+// =====================================================================================================
+struct Compiled {
+  std::vector<EncMsg> msgs;
+  std::vector<EncTensor> tensors;
+  std::vector<EncField> fields;
+  std::vector<StrRef> filters;
+  std::vector<uint8_t> strings;
+  std::vector<uint32_t> vfield_first_tile, vfield_index;
+  std::vector<CopySeg> segs;
+  uint64_t n_copy_tiles = 0;
+  uint64_t bound = 0;  // upper bound of the encoded bytes
+};
+
+StrRef add_str(Compiled& c, const tfs_str_t& s) {
+  StrRef r{static_cast<uint32_t>(c.strings.size()), s.len};
+  if (s.len) c.strings.insert(c.strings.end(), reinterpret_cast<const uint8_t*>(s.ptr), reinterpret_cast<const uint8_t*>(s.ptr) + s.len);
+  return r;
+}
+
+// Which conversions a payload field may ask for (mirrors the ABI comment on tfs_field_desc_t).
+bool compile_field(const tfs_field_desc_t& f, EncField* o, uint64_t* max_body) {
+  std::memset(o, 0, sizeof(*o));
+  o->src = f.data;
+  o->n_elems = f.n_elems;
+  o->kind = f.kind;
+  o->op_param = f.op_param;
+  const int32_t st = f.src_type, dt = f.dst_type;
+  if (f.n_elems != 0 && f.data == nullptr) return false;
+  const bool is_f32_kind = f.kind == TFS_KIND_FLOAT_VAL || f.kind == TFS_KIND_SCOMPLEX_VAL;
+  if (f.op != TFS_OP_NONE && !(st == TFS_T_U8 && is_f32_kind)) return false;
+  if (f.op < TFS_OP_NONE || f.op > TFS_OP_MUL) return false;
+  auto copy_class = [&](int32_t op, uint64_t out_bytes) {
+    o->is_varint = 0;
+    o->mode = op;
+    o->body_len = out_bytes;
+    *max_body = out_bytes;
+    return true;
+  };
+  auto varint_class = [&](int32_t mode, uint32_t max_len) {
+    o->is_varint = 1;
+    o->mode = mode;
+    *max_body = f.n_elems * max_len;
+    return true;
+  };
+  switch (f.kind) {
+    case TFS_KIND_FLOAT_VAL:
+    case TFS_KIND_SCOMPLEX_VAL:
+      if (dt != TFS_T_NONE && dt != TFS_T_F32) return false;
+      if (st == TFS_T_F32) return copy_class(CP_BYTES, f.n_elems * 4);
+      if (st == TFS_T_U8) return copy_class(f.op == TFS_OP_DIV ? CP_U8_F32_DIV : f.op == TFS_OP_MUL ? CP_U8_F32_MUL : CP_U8_F32, f.n_elems * 4);
+      return false;
+    case TFS_KIND_DOUBLE_VAL:
+    case TFS_KIND_DCOMPLEX_VAL:
+      if (st != TFS_T_F64 || (dt != TFS_T_NONE && dt != TFS_T_F64)) return false;
+      return copy_class(CP_BYTES, f.n_elems * 8);
+    case TFS_KIND_BOOL_VAL:
+      if ((st != TFS_T_BOOL && st != TFS_T_U8) || (dt != TFS_T_NONE && dt != TFS_T_BOOL)) return false;
+      return copy_class(CP_BOOL, f.n_elems);
+    case TFS_KIND_TENSOR_CONTENT: {
+      uint32_t w = tfs_type_size(st);
+      if (w == 0) return false;
+      if (dt == TFS_T_NONE || dt == st) return copy_class(CP_BYTES, f.n_elems * w);
+      if (st == TFS_T_F32 && dt == TFS_T_F16) return copy_class(CP_F32_F16, f.n_elems * 2);
+      if (st == TFS_T_F32 && dt == TFS_T_BF16) return copy_class(CP_F32_BF16, f.n_elems * 2);
+      return false;
+    }
+    case TFS_KIND_INT_VAL:
+      if (dt != TFS_T_NONE && dt != TFS_T_I32) return false;
+      switch (st) {
+        case TFS_T_I32: return varint_class(VM_I32, 10);
+        case TFS_T_I16: return varint_class(VM_I16, 10);
+        case TFS_T_I8: return varint_class(VM_I8, 10);
+        case TFS_T_U16: return varint_class(VM_U16, 3);
+        case TFS_T_U8: return varint_class(VM_U8, 2);
+        default: return false;
+      }
+    case TFS_KIND_INT64_VAL:
+      if (st != TFS_T_I64 || (dt != TFS_T_NONE && dt != TFS_T_I64)) return false;
+      return varint_class(VM_I64, 10);
+    case TFS_KIND_UINT64_VAL:
+      if (st != TFS_T_U64 || (dt != TFS_T_NONE && dt != TFS_T_U64)) return false;
+      return varint_class(VM_I64, 10);
+    case TFS_KIND_UINT32_VAL:
+      if (st != TFS_T_U32 || (dt != TFS_T_NONE && dt != TFS_T_U32)) return false;
+      return varint_class(VM_U32, 5);
+    case TFS_KIND_HALF_VAL:
+      if (st == TFS_T_I32 && (dt == TFS_T_NONE || dt == TFS_T_I32)) return varint_class(VM_I32, 10);
+      if ((st == TFS_T_U16 || st == TFS_T_F16 || st == TFS_T_BF16) && (dt == TFS_T_NONE || dt == st || dt == TFS_T_I32))
+        return varint_class(VM_U16, 3);
+      if (st == TFS_T_F32 && dt == TFS_T_F16) return varint_class(VM_F32_F16, 3);
+      if (st == TFS_T_F32 && dt == TFS_T_BF16) return varint_class(VM_F32_BF16, 3);
+      return false;
+    default: return false;  // string_val / message-typed fields: not on the encode ABI
+  }
+}
+
+tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, Compiled* c) {
+  if (!b) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch is null");
+  if ((b->n_msgs && !b->msgs) || (b->n_tensors && !b->tensors) || (b->n_fields && !b->fields) || (b->n_filters && !b->filters))
+    return set_err(ctx, TFS_ERR_INVALID_ARG, "batch array pointer is null");
+  c->msgs.resize(b->n_msgs);
+  c->tensors.resize(b->n_tensors);
+  c->fields.resize(b->n_fields);
+  c->filters.resize(b->n_filters);
+  std::vector<uint64_t> field_bound(b->n_fields, 0);
+  std::vector<uint8_t> tensor_used(b->n_tensors, 0), field_used(b->n_fields, 0);
+  for (uint32_t i = 0; i < b->n_filters; ++i) c->filters[i] = add_str(*c, b->filters[i]);
+  uint32_t vtiles = 0;
+  const uint32_t prefix = (flags & TFS_F_GRPC_PREFIX) ? 5u : 0u;
+  for (uint32_t mi = 0; mi < b->n_msgs; ++mi) {
+    const tfs_msg_desc_t& m = b->msgs[mi];
+    EncMsg& o = c->msgs[mi];
+    std::memset(&o, 0, sizeof(o));
+    if (m.kind < TFS_MSG_TENSOR_PROTO || m.kind > TFS_MSG_PREDICT_RESPONSE) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad message kind");
+    if (static_cast<uint64_t>(m.first_tensor) + m.n_tensors > b->n_tensors) return set_err(ctx, TFS_ERR_INVALID_ARG, "tensor range out of bounds");
+    if (static_cast<uint64_t>(m.first_filter) + m.n_filters > b->n_filters) return set_err(ctx, TFS_ERR_INVALID_ARG, "filter range out of bounds");
+    if (m.version_choice < TFS_VERSION_NONE || m.version_choice > TFS_VERSION_LABEL) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad version_choice");
+    if (m.kind == TFS_MSG_TENSOR_PROTO && (m.n_tensors != 1 || m.has_model_spec || m.n_filters))
+      return set_err(ctx, TFS_ERR_INVALID_ARG, "a bare TensorProto message has exactly one tensor and nothing else");
+    if (m.kind == TFS_MSG_PREDICT_RESPONSE && m.n_filters) return set_err(ctx, TFS_ERR_INVALID_ARG, "PredictResponse has no output_filter");
+    o.kind = m.kind;
+    o.has_model_spec = m.has_model_spec ? 1 : 0;
+    o.version_choice = m.version_choice;
+    o.version = m.version_choice == TFS_VERSION_NUMBER ? m.version : 0;
+    o.first_tensor = m.first_tensor;
+    o.n_tensors = m.n_tensors;
+    o.first_filter = m.first_filter;
+    o.n_filters = m.n_filters;
+    uint64_t bound = 64 + prefix;
+    if (m.has_model_spec) {
+      o.model_name = add_str(*c, m.model_name);
+      o.signature_name = add_str(*c, m.signature_name);
+      if (m.version_choice == TFS_VERSION_LABEL) o.version_label = add_str(*c, m.version_label);
+      bound += m.model_name.len + m.signature_name.len + m.version_label.len + 48;
+    }
+    for (uint32_t i = 0; i < m.n_filters; ++i) bound += b->filters[m.first_filter + i].len + 8;
+    for (uint32_t i = 0; i < m.n_tensors; ++i) {
+      const uint32_t ti = m.first_tensor + i;
+      if (tensor_used[ti]++) return set_err(ctx, TFS_ERR_INVALID_ARG, "a tensor descriptor is referenced twice");
+      const tfs_tensor_desc_t& t = b->tensors[ti];
+      EncTensor& ot = c->tensors[ti];
+      std::memset(&ot, 0, sizeof(ot));
+      if (t.n_dims > TFS_MAX_DIMS) return set_err(ctx, TFS_ERR_INVALID_ARG, "rank exceeds TFS_MAX_DIMS");
+      if (!t.has_shape && (t.n_dims || t.unknown_rank)) return set_err(ctx, TFS_ERR_INVALID_ARG, "dims without has_shape");
+      if (static_cast<uint64_t>(t.first_field) + t.n_fields > b->n_fields) return set_err(ctx, TFS_ERR_INVALID_ARG, "field range out of bounds");
+      ot.name = m.kind == TFS_MSG_TENSOR_PROTO ? StrRef{0, 0} : add_str(*c, t.name);
+      ot.dtype = t.dtype;
+      ot.version_number = t.version_number;
+      ot.has_shape = t.has_shape ? 1 : 0;
+      ot.unknown_rank = t.unknown_rank ? 1 : 0;
+      ot.n_dims = t.n_dims;
+      ot.first_field = t.first_field;
+      ot.n_fields = t.n_fields;
+      for (uint32_t d = 0; d < t.n_dims; ++d) ot.dims[d] = t.dims[d];
+      bound += t.name.len + 64 + 13ull * t.n_dims;
+      uint32_t seen = 0;
+      for (uint32_t k = 0; k < t.n_fields; ++k) {
+        const uint32_t fi = t.first_field + k;
+        if (field_used[fi]++) return set_err(ctx, TFS_ERR_INVALID_ARG, "a field descriptor is referenced twice");
+        const int32_t slot = tfs_slot_of_kind(b->fields[fi].kind);
+        if (slot < 0 || ((seen >> slot) & 1u)) return set_err(ctx, TFS_ERR_INVALID_ARG, "unknown or repeated payload kind in one tensor");
+        seen |= 1u << slot;
+        if (!compile_field(b->fields[fi], &c->fields[fi], &field_bound[fi]))
+          return set_err(ctx, TFS_ERR_INVALID_ARG, "payload field: conversion not allowed by the ABI");
+        bound += field_bound[fi] + 16;
+      }
+      // prost emits in ascending field number: order this tensor's fields by kind
+      std::sort(c->fields.begin() + t.first_field, c->fields.begin() + t.first_field + t.n_fields,
+                [](const EncField& x, const EncField& y) { return x.kind < y.kind; });
+    }
+    c->bound += (flags & TFS_F_ALIGN_PAYLOAD) ? align_up(bound + 16, 16) : bound;
+  }
+  // tile tables
+  for (uint32_t fi = 0; fi < b->n_fields; ++fi) {
+    EncField& f = c->fields[fi];
+    if (!field_used[fi] || f.n_elems == 0) {
+      f.n_elems = field_used[fi] ? f.n_elems : 0;
+      f.n_tiles = 0;
+      continue;
+    }
+    if (f.is_varint) {
+      uint64_t nt = (f.n_elems + kVarintTile - 1) / kVarintTile;
+      if (vtiles + nt > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (varint tiles)");
+      f.first_tile = vtiles;
+      f.n_tiles = static_cast<uint32_t>(nt);
+      c->vfield_first_tile.push_back(vtiles);
+      c->vfield_index.push_back(fi);
+      vtiles += static_cast<uint32_t>(nt);
+    } else {
+      CopySeg s;
+      s.src = static_cast<const uint8_t*>(f.src);
+      s.dst = nullptr;
+      s.op = f.mode;
+      s.param = f.op_param;
+      const uint32_t osz = (f.mode == CP_BYTES || f.mode == CP_BOOL) ? 1u : (f.mode == CP_F32_F16 || f.mode == CP_F32_BF16) ? 2u : 4u;
+      s.n = f.body_len / osz;
+      s.first_tile = c->n_copy_tiles;
+      f.first_tile = static_cast<uint32_t>(c->segs.size());
+      f.n_tiles = 0;
+      c->n_copy_tiles += (f.body_len + kCopyTileBytes - 1) / kCopyTileBytes;
+      c->segs.push_back(s);
+    }
+  }
+  c->vfield_first_tile.push_back(vtiles);
+  return TFS_OK;
+}
+
+struct Uploaded {
+  EncTables T;
+  uint64_t n_copy_tiles;
+};
+
+template <class V>
+size_t place(size_t* cursor, const V& v) {
+  size_t off = align_up(*cursor, 16);
+  *cursor = off + v.size() * sizeof(typename V::value_type);
+  return off;
+}
+
+tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
+  size_t cur = 0;
+  const size_t o_msgs = place(&cur, c.msgs), o_tensors = place(&cur, c.tensors), o_fields = place(&cur, c.fields),
+               o_filters = place(&cur, c.filters), o_strings = place(&cur, c.strings), o_vft = place(&cur, c.vfield_first_tile),
+               o_vfi = place(&cur, c.vfield_index), o_segs = place(&cur, c.segs);
+  const size_t total = align_up(cur, 16) + 16;
+  TFS_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, total));
+  TFS_TRY(dev_reserve(ctx, &ctx->d_tables, total));
+  uint8_t* h = static_cast<uint8_t*>(ctx->h_up);
+  auto put = [&](size_t off, const void* p, size_t n) {
+    if (n) std::memcpy(h + off, p, n);
+  };
+  put(o_msgs, c.msgs.data(), c.msgs.size() * sizeof(EncMsg));
+  put(o_tensors, c.tensors.data(), c.tensors.size() * sizeof(EncTensor));
+  put(o_fields, c.fields.data(), c.fields.size() * sizeof(EncField));
+  put(o_filters, c.filters.data(), c.filters.size() * sizeof(StrRef));
+  put(o_strings, c.strings.data(), c.strings.size());
+  put(o_vft, c.vfield_first_tile.data(), c.vfield_first_tile.size() * 4);
+  put(o_vfi, c.vfield_index.data(), c.vfield_index.size() * 4);
+  put(o_segs, c.segs.data(), c.segs.size() * sizeof(CopySeg));
+  TFS_CUDA(ctx, cudaMemcpyAsync(ctx->d_tables.p, h, total, cudaMemcpyHostToDevice, ctx->stream));
+
+  const uint32_t n_msgs = static_cast<uint32_t>(c.msgs.size()), n_tensors = static_cast<uint32_t>(c.tensors.size());
+  const uint32_t n_vtiles = c.vfield_first_tile.back();
+  size_t w = 0;
+  auto carve = [&](size_t bytes) {
+    size_t off = align_up(w, 16);
+    w = off + bytes;
+    return off;
+  };
+  const size_t w_tb = carve(4ull * n_vtiles), w_to = carve(8ull * n_vtiles), w_tl = carve(8ull * n_tensors),
+               w_el = carve(8ull * n_tensors), w_sl = carve(8ull * n_msgs), w_ml = carve(8ull * n_msgs),
+               w_mp = carve(8ull * n_msgs), w_mo = carve(8ull * n_msgs), w_res = carve(16);
+  TFS_TRY(dev_reserve(ctx, &ctx->d_work, w + 16));
+  uint8_t* d = static_cast<uint8_t*>(ctx->d_tables.p);
+  uint8_t* k = static_cast<uint8_t*>(ctx->d_work.p);
+  EncTables& T = u->T;
+  T.msgs = reinterpret_cast<EncMsg*>(d + o_msgs);
+  T.tensors = reinterpret_cast<EncTensor*>(d + o_tensors);
+  T.fields = reinterpret_cast<EncField*>(d + o_fields);
+  T.filters = reinterpret_cast<StrRef*>(d + o_filters);
+  T.strings = d + o_strings;
+  T.vfield_first_tile = reinterpret_cast<uint32_t*>(d + o_vft);
+  T.vfield_index = reinterpret_cast<uint32_t*>(d + o_vfi);
+  T.segs = reinterpret_cast<CopySeg*>(d + o_segs);
+  T.tile_bytes = reinterpret_cast<uint32_t*>(k + w_tb);
+  T.tile_off = reinterpret_cast<uint64_t*>(k + w_to);
+  T.tensor_len = reinterpret_cast<uint64_t*>(k + w_tl);
+  T.entry_len = reinterpret_cast<uint64_t*>(k + w_el);
+  T.spec_len = reinterpret_cast<uint64_t*>(k + w_sl);
+  T.msg_len = reinterpret_cast<uint64_t*>(k + w_ml);
+  T.msg_pay_off = reinterpret_cast<uint64_t*>(k + w_mp);
+  T.msg_off = reinterpret_cast<uint64_t*>(k + w_mo);
+  T.result = reinterpret_cast<uint64_t*>(k + w_res);
+  T.n_msgs = n_msgs;
+  T.n_tensors = n_tensors;
+  T.n_fields = static_cast<uint32_t>(c.fields.size());
+  T.n_filters = static_cast<uint32_t>(c.filters.size());
+  T.n_vfields = static_cast<uint32_t>(c.vfield_index.size());
+  T.n_vtiles = n_vtiles;
+  T.n_segs = static_cast<uint32_t>(c.segs.size());
+  T._pad = 0;
+  u->n_copy_tiles = c.n_copy_tiles;
+  return TFS_OK;
+}
+
+// size + layout: everything that replaces prost's encoded_len
+tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_t dst_skew, uint64_t dst_capacity) {
+  const EncTables& T = u.T;
+  if (T.n_vtiles) {
+    {
+      ProfScope prof(ctx, PK_VARINT_SIZE);
+      k_varint_tiles<false><<<T.n_vtiles, kVarintThreads, 0, ctx->stream>>>(T, nullptr);
+    }
+    ctx->launches++;
+    const uint32_t warps_per_block = 256 / 32;
+    k_field_scan<<<(T.n_vfields + warps_per_block - 1) / warps_per_block, 256, 0, ctx->stream>>>(T);
+    ctx->launches++;
+  }
+  if (T.n_msgs) {
+    k_msg_layout<<<(T.n_msgs + 127) / 128, 128, 0, ctx->stream>>>(T);
+    ctx->launches++;
+  }
+  k_msg_scan<<<1, 1024, 0, ctx->stream>>>(T, flags, dst_skew, dst_capacity);
+  ctx->launches++;
+  TFS_CUDA(ctx, cudaGetLastError());
+  return TFS_OK;
+}
+
+tfs_status_t fetch_results(tfs_ctx* ctx, const EncTables& T, uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out,
+                           bool* overflow) {
+  const size_t n = T.n_msgs;
+  TFS_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, 16 * n + 32));
+  uint64_t* h = static_cast<uint64_t*>(ctx->h_down);
+  if (n) {
+    TFS_CUDA(ctx, cudaMemcpyAsync(h, T.msg_off, 8 * n, cudaMemcpyDeviceToHost, ctx->stream));
+    TFS_CUDA(ctx, cudaMemcpyAsync(h + n, T.msg_len, 8 * n, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  TFS_CUDA(ctx, cudaMemcpyAsync(h + 2 * n, T.result, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (msg_off_out && n) std::memcpy(msg_off_out, h, 8 * n);
+  if (msg_len_out && n) std::memcpy(msg_len_out, h + n, 8 * n);
+  if (total_out) *total_out = h[2 * n];
+  *overflow = h[2 * n + 1] != 0;
+  return TFS_OK;
+}
+
+}  // namespace
+
+// Encode a compiled batch whose field data pointers are device pointers.  When `sync_out` the results
+// are fetched and the stream synchronised; otherwise the caller fetches later (host-staged path).
+tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev, uint64_t dst_capacity, uint32_t flags,
+                           uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out, bool size_only) {
+  TFS_CUDA(ctx, cudaSetDevice(ctx->device));
+  Compiled c;
+  TFS_TRY(compile_batch(ctx, batch, flags, &c));
+  Uploaded u;
+  TFS_TRY(upload(ctx, c, &u));
+  const uint32_t dst_skew = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(dst_dev) & 15u);
+  TFS_TRY(run_sizing(ctx, u, size_only ? 0u : flags, dst_skew, size_only ? ~0ull : dst_capacity));
+  if (!size_only) {
+    const EncTables& T = u.T;
+    uint8_t* dst = static_cast<uint8_t*>(dst_dev);
+    if (T.n_msgs) {
+      k_write_headers<<<(T.n_msgs + 127) / 128, 128, 0, ctx->stream>>>(T, dst, flags);
+      ctx->launches++;
+    }
+    if (T.n_vtiles) {
+      {
+        ProfScope prof(ctx, PK_VARINT_SCATTER);
+        k_varint_tiles<true><<<T.n_vtiles, kVarintThreads, 0, ctx->stream>>>(T, dst);
+      }
+      ctx->launches++;
+    }
+    TFS_CUDA(ctx, cudaGetLastError());
+    // gated on the overflow flag: when dst is too small segs[].dst were never filled in
+    if (T.n_segs) TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, nullptr, T.result + 1));
+  }
+  bool overflow = false;
+  TFS_TRY(fetch_results(ctx, u.T, msg_off_out, msg_len_out, total_out, &overflow));
+  if (overflow) return set_err(ctx, TFS_ERR_NOMEM, "dst_capacity is smaller than the encoded batch");
+  return TFS_OK;
+}
+
+uint64_t encode_bound(const tfs_batch_t* batch, uint32_t flags) {
+  tfs_ctx dummy;
+  Compiled c;
+  if (compile_batch(&dummy, batch, flags, &c) != TFS_OK) return 0;
+  return c.bound + 64;
+}
+
+}  // namespace tfs
+
+using namespace tfs;
+
+extern "C" {
+
+tfs_status_t tfs_encode_size(tfs_ctx_t* ctx, const tfs_batch_t* batch, uint64_t* msg_len_out) {
+  if (!ctx || !batch || (batch->n_msgs && !msg_len_out)) return TFS_ERR_INVALID_ARG;
+  uint64_t total = 0;
+  return encode_device(ctx, batch, nullptr, 0, 0, nullptr, msg_len_out, &total, true);
+}
+
+uint64_t tfs_encode_bound(const tfs_batch_t* batch, uint32_t flags) { return batch ? encode_bound(batch, flags) : 0; }
+
+tfs_status_t tfs_encode(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst_dev, uint64_t dst_capacity, uint32_t flags,
+                        uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out) {
+  if (!ctx || !batch || (!dst_dev && dst_capacity)) return TFS_ERR_INVALID_ARG;
+  return encode_device(ctx, batch, dst_dev, dst_capacity, flags, msg_off_out, msg_len_out, total_out, false);
+}
+
+}  // extern "C"

@@ -1,0 +1,256 @@
+// tfs_internal.h — structures shared by the host orchestration and the sm_100a kernels.
+// Nothing here is part of the ABI (include/tfs_gpu.h is).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/tfs_gpu.h"
+
+namespace tfs {
+
+// ---- geometry --------------------------------------------------------------------------------
+constexpr int kVarintThreads = 256;                  // 8 warps per CTA
+constexpr int kVarintRows = 8;                       // elements per lane (one per 32-element row)
+constexpr int kVarintTile = kVarintThreads * kVarintRows;  // 2048 elements per tile
+constexpr int kVarintMaxLen = 10;
+constexpr int kCopyThreads = 256;
+constexpr int kCopyTileBytes = 32768;                // output bytes per copy tile
+constexpr int kDecThreads = 256;
+constexpr int kDecTileBytes = 4096;                  // wire bytes per varint-decode tile (16 B per thread)
+
+// ---- element fetch modes of the varint encoder (source memory type -> u64 that is varint-coded) ----
+enum VarintMode : int32_t {
+  VM_I64 = 0,  // also u64: the bits are the value
+  VM_I32,      // sign-extended (`as u64` of an i32)
+  VM_U32,
+  VM_I16,
+  VM_U16,      // also f16 / bf16 bit patterns
+  VM_I8,
+  VM_U8,
+  VM_F32_F16,  // f32 -> binary16 pattern (RNE)
+  VM_F32_BF16, // f32 -> bfloat16 pattern (RNE)
+  VM_COUNT
+};
+
+// ---- bulk copy ops ------------------------------------------------------------------------------
+enum CopyOp : int32_t {
+  CP_BYTES = 0,
+  CP_BOOL,        // byte -> (byte != 0)
+  CP_U8_F32,      // u8 -> f32
+  CP_U8_F32_DIV,  // u8 -> f32 / param
+  CP_U8_F32_MUL,  // u8 -> f32 * param
+  CP_F32_F16,
+  CP_F32_BF16,
+  CP_F16_F32,
+  CP_BF16_F32,
+  CP_COUNT
+};
+
+struct StrRef {
+  uint32_t off;  // into the string blob
+  uint32_t len;
+};
+
+// One bulk copy / cast segment.  `n` counts OUTPUT elements of the op (bytes for CP_BYTES / CP_BOOL).
+struct CopySeg {
+  const uint8_t* src;
+  uint8_t* dst;
+  uint64_t n;
+  uint64_t first_tile;  // exclusive prefix of tiles over the segment table (host- or device-built)
+  int32_t op;
+  float param;
+};
+
+struct EncField {
+  const void* src;
+  uint64_t n_elems;
+  uint64_t body_len;   // wire bytes of the packed body (copy class: host-known; varint class: device scan)
+  uint64_t dst_off;    // absolute byte offset of the body in dst (written by the header kernel)
+  uint32_t first_tile; // varint class: first varint tile; copy class: index into the CopySeg table
+  uint32_t n_tiles;
+  int32_t kind;        // TFS_KIND_*
+  int32_t mode;        // VarintMode or CopyOp
+  float op_param;
+  uint32_t is_varint;
+};
+
+struct EncTensor {
+  StrRef name;
+  int32_t dtype;
+  int32_t version_number;
+  int32_t has_shape;
+  int32_t unknown_rank;
+  uint32_t n_dims;
+  uint32_t first_field;
+  uint32_t n_fields;  // sorted by kind (ascending tag order)
+  uint32_t _pad;
+  int64_t dims[TFS_MAX_DIMS];
+};
+
+struct EncMsg {
+  int32_t kind;
+  int32_t has_model_spec;
+  StrRef model_name;
+  StrRef signature_name;
+  StrRef version_label;
+  int32_t version_choice;
+  uint32_t _pad;
+  int64_t version;
+  uint32_t first_tensor;
+  uint32_t n_tensors;
+  uint32_t first_filter;
+  uint32_t n_filters;
+};
+
+// Device view of one compiled encode batch (all pointers are device pointers).
+struct EncTables {
+  EncMsg* msgs;
+  EncTensor* tensors;
+  EncField* fields;
+  StrRef* filters;
+  const uint8_t* strings;
+  uint32_t* vfield_first_tile;  // [n_vfields + 1]
+  uint32_t* vfield_index;       // [n_vfields] -> index into fields
+  CopySeg* segs;                // [n_segs]
+  // work arrays
+  uint32_t* tile_bytes;         // [n_vtiles]
+  uint64_t* tile_off;           // [n_vtiles] byte offset of the tile inside its field body
+  uint64_t* tensor_len;         // [n_tensors]
+  uint64_t* entry_len;          // [n_tensors]
+  uint64_t* spec_len;           // [n_msgs]
+  uint64_t* msg_len;            // [n_msgs]
+  uint64_t* msg_pay_off;        // [n_msgs] offset (inside the message) of its largest bulk payload
+  uint64_t* msg_off;            // [n_msgs]
+  uint64_t* result;             // [2]: total bytes, overflow flag
+  uint32_t n_msgs, n_tensors, n_fields, n_filters;
+  uint32_t n_vfields, n_vtiles, n_segs, _pad;
+};
+
+// ---- decode ---------------------------------------------------------------------------------------
+enum SpanClass : uint32_t {
+  SC_VARINT = 0,  // packed or single varint(s) -> slot element type
+  SC_COPY = 1,    // fixed-width packed body / tensor_content / single fixed value
+};
+
+// One contiguous run of payload bytes found by the structure walk.
+struct DecSpan {
+  uint64_t wire_off;   // absolute offset in the wire buffer
+  uint64_t len;        // bytes
+  uint64_t elem_base;  // index of its first element inside the (tensor, slot) vector (finalize kernel)
+  uint64_t n_elems;    // varint: terminators counted; copy: len / width
+  uint32_t tensor;     // global tensor index
+  uint32_t slot;
+  uint32_t msg;
+  uint32_t cls;        // SpanClass
+  uint64_t first_tile; // exclusive prefix of tiles (per class)
+  uint64_t elem_tile0; // varint: index into tile_count[] of its first tile (== first_tile)
+};
+
+struct DecTables {
+  const uint8_t* wire;
+  uint64_t wire_bytes;
+  const uint64_t* msg_off;  // device copies of the caller's arrays
+  const uint64_t* msg_len;
+  uint32_t n_msgs;
+  int32_t msg_kind;
+  uint32_t flags;
+  uint32_t _pad;
+  // pass-1 counts per message (then exclusive-scanned in place): tensors, filters, spans, string bytes
+  uint32_t* cnt_tensors;
+  uint32_t* cnt_filters;
+  uint32_t* cnt_spans;
+  uint32_t* cnt_strbytes;
+  uint32_t* cnt_vtiles;
+  uint32_t* cnt_ctiles;
+  uint64_t* totals;  // [8]: tensors, filters, spans, strbytes, varint tiles, copy tiles, pool bytes, failed
+  // pass-2 outputs
+  tfs_msg_out_t* msgs;
+  tfs_tensor_out_t* tensors;
+  tfs_span_t* filters;
+  uint8_t* strings;
+  DecSpan* spans;
+  uint32_t* span_vtile0;  // [n_spans] first varint tile of each span (non-decreasing over the table)
+  uint32_t* span_ctile0;  // [n_spans] first copy tile of each span (non-decreasing over the table)
+  uint64_t* tensor_pool;  // [n_tensors] pool bytes of each tensor
+  uint32_t* tile_count;  // [n varint tiles] terminators per tile
+  uint64_t* tile_base;   // [n varint tiles] exclusive prefix inside the span
+  CopySeg* segs;         // copy-class spans as segments (dst filled once the pool is known)
+  unsigned long long* err;  // [n_msgs] min over (offset << 8 | code) of device-detected errors, ~0 = none
+};
+
+}  // namespace tfs
+
+// ---- context ---------------------------------------------------------------------------------------
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+struct tfs_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t own_stream = nullptr;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  uint64_t launches = 0;
+  DevBuf d_tables, d_work, d_stage_in, d_stage_out;
+  DevBuf d_dec1, d_dec2;        // decode tables (pass 1 / pass 2); owned by the newest tfs_decoded handle
+  uint64_t dec_generation = 0;
+  uint64_t stage_generation = 0;  // bumped by every *_host call that reuses the staging buffers
+  void* h_up = nullptr;
+  size_t h_up_cap = 0;
+  void* h_down = nullptr;
+  size_t h_down_cap = 0;
+  void* h_slab = nullptr;  // pinned slab for *_host staging of pageable memory
+  size_t h_slab_cap = 0;
+  // optional per-kernel timing with CUDA events on the launching stream (tfs_prof_*)
+  bool prof_on = false;
+  std::vector<cudaEvent_t> prof_pool;                           // recycled events
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_open[8];  // (start, stop) pairs per kernel id, not yet read
+  uint64_t prof_launches[8] = {0};
+  double prof_ms[8] = {0};
+};
+
+namespace tfs {
+enum ProfKernel { PK_COPY = 0, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_FRAMING, PK_WALK, PK_COUNT_ };
+// Brackets one kernel launch with events when profiling is on (a no-op otherwise).
+struct ProfScope {
+  tfs_ctx* ctx;
+  int id;
+  cudaEvent_t start = nullptr, stop = nullptr;
+  ProfScope(tfs_ctx* c, int kernel_id);
+  ~ProfScope();
+};
+}  // namespace tfs
+
+namespace tfs {
+
+tfs_status_t set_err(tfs_ctx* ctx, tfs_status_t st, const std::string& what);
+tfs_status_t cuda_fail(tfs_ctx* ctx, cudaError_t e, const char* where);
+tfs_status_t dev_reserve(tfs_ctx* ctx, DevBuf* b, size_t bytes);
+tfs_status_t pinned_reserve(tfs_ctx* ctx, void** p, size_t* cap, size_t bytes);
+
+#define TFS_CUDA(ctx, call)                                       \
+  do {                                                            \
+    cudaError_t e__ = (call);                                     \
+    if (e__ != cudaSuccess) return tfs::cuda_fail(ctx, e__, #call); \
+  } while (0)
+
+#define TFS_TRY(expr)                      \
+  do {                                     \
+    tfs_status_t st__ = (expr);            \
+    if (st__ != TFS_OK) return st__;       \
+  } while (0)
+
+// Bulk copy / cast kernel over a segment table that already lives on the device.
+// With `n_tiles_dev` the tile count is read on the device (decode: the host does not know it yet);
+// with `gate` the kernel does nothing when *gate != 0.
+tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles,
+                         const uint64_t* n_tiles_dev, const uint64_t* gate);
+
+inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace tfs
