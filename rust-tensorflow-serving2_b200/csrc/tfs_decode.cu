@@ -253,6 +253,19 @@ struct Walker {
       if (len) {
         // does the last varint of the body end exactly at the limit?  prost reads on past it.
         if (w[rend - 1] & 0x80) {
+          // error path only: prost fails at the FIRST bad varint, so look for an over-long one (ten
+          // continuation bytes in a row) earlier in the body before classifying the trailing one
+          uint32_t run = 0;
+          for (uint64_t q = off; q < rend; ++q) {
+            if (w[q] & 0x80) {
+              if (++run == 10) {
+                pos = q + 1;
+                return fail(TFS_ERR_INVALID_VARINT);
+              }
+            } else {
+              run = 0;
+            }
+          }
           uint32_t k = 0;  // continuation bytes at the end of the body
           while (k < 10 && k < len && (w[rend - 1 - k] & 0x80)) ++k;
           pos = rend;
