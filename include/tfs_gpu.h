@@ -344,6 +344,34 @@ tfs_status_t tfs_decode_host(tfs_ctx_t* ctx, const void* wire_host, uint64_t wir
 tfs_status_t tfs_decode_host_finish(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_host, uint64_t pool_bytes);
 
 /* ----------------------------------------------------------------------------------------------
+ * Allocation-free packing of one int64 array (no counterpart in the reference: the reference never
+ * touches a GPU, so it has no notion of a caller that must not allocate device memory).
+ *
+ * Writes the packed-varint body of an `int64_val` field (tensor.proto:64; the bytes that follow the
+ * field's key and length) for src_dev[0 .. n_elems) to dst_dev, and the body's length in bytes to
+ * *body_len_dev.  All three pointers are device pointers supplied by the caller; the work is queued on
+ * `cuda_stream` (a cudaStream_t, NULL = the default stream) of the CURRENT device and the call returns
+ * without waiting.  The bytes equal what tfs_encode produces for the same values.
+ *
+ * It exists for callers that cannot afford, or are not allowed, a cudaMalloc: a codec running inside
+ * a request-serving poll loop (cudaMalloc synchronises the device and would stall every other request
+ * in flight), or a client sharing its GPU with a TensorFlow Serving process that has already taken
+ * nearly all device memory.  Its working tables live in a fixed block of device memory that belongs to
+ * the library image, so:
+ *   - n_elems may be at most TFS_NOALLOC_MAX_ELEMS; more returns TFS_ERR_TOO_LARGE and launches nothing;
+ *   - all calls share that block: calls that may overlap on the GPU (independent streams, several host
+ *     threads) race and must be ordered by the caller; calls queued on one stream are safe;
+ *   - the first call made while a given device is current looks up the block's address (one synchronous
+ *     runtime query): make that first call outside of any stream capture;
+ *   - if the body is longer than dst_capacity nothing is written to dst_dev; *body_len_dev still
+ *     receives the length that would be needed, so compare it with dst_capacity after synchronising.
+ * -------------------------------------------------------------------------------------------- */
+#define TFS_NOALLOC_MAX_ELEMS (1ull << 24)
+enum { TFS_ERR_TOO_LARGE = 24 }; /* input larger than the fixed working block of tfs_pack_int64_noalloc */
+tfs_status_t tfs_pack_int64_noalloc(const int64_t* src_dev, uint64_t n_elems, void* dst_dev, uint64_t dst_capacity,
+                                    uint64_t* body_len_dev, void* cuda_stream);
+
+/* ----------------------------------------------------------------------------------------------
  * Sharding helper (host only).  Requests are independent, so a batch is split across GPUs with no
  * collective: greedy largest-first balancing on bytes.  shard_out[i] in [0, n_shards).
  * -------------------------------------------------------------------------------------------- */

@@ -74,6 +74,7 @@ def lib():
     L.tfs_kind_of_slot.argtypes = [C.c_int32]
     L.tfs_type_size.restype = C.c_uint32
     L.tfs_type_size.argtypes = [C.c_int32]
+    L.tfs_pack_int64_noalloc.argtypes = [vp, C.c_uint64, vp, C.c_uint64, vp, vp]
     L.tfs_prof_enable.argtypes = [vp, C.c_int32]
     L.tfs_prof_read.argtypes = [vp, C.c_int32, u64p, C.POINTER(C.c_double), C.c_int32]
     for name in abi.EXPORTED_SYMBOLS:

@@ -122,6 +122,7 @@ const char* tfs_strerror(tfs_status_t status) {
     case TFS_ERR_NOMEM: return "out of memory or capacity too small";
     case TFS_ERR_CUDA: return "CUDA error";
     case TFS_ERR_BATCH: return "some messages of the batch failed";
+    case TFS_ERR_TOO_LARGE: return "input exceeds TFS_NOALLOC_MAX_ELEMS, the fixed working block of tfs_pack_int64_noalloc";
     default: return "unknown status";
   }
 }
