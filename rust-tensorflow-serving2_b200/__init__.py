@@ -5,7 +5,7 @@ Python here is only the harness above the C ABI (the role the Rust shim plays in
 message objects, descriptor building and a ctypes binding.  All compute is in csrc/ (CUDA, sm_100a).
 There is no CPU fallback: using the codec without the built library or without a GPU raises.
 """
-from . import abi, messages, workloads, _lib, codec  # noqa: F401  (all submodules, so aliases of the package see them)
+from . import abi, messages, workloads, _lib, codec, sharding  # noqa: F401  (all submodules, so aliases of the package see them)
 from ._lib import TfsError  # noqa: F401
 from .codec import GpuCodec, GpuContext, GpuDecoder, GpuEncoder  # noqa: F401
 from .messages import (  # noqa: F401
