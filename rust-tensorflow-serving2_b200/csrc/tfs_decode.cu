@@ -18,7 +18,7 @@ struct tfs_decoded {
   uint64_t generation = 0;
   tfs_ctx* owner = nullptr;
   tfs::DecTables T{};
-  uint64_t totals[8] = {0};
+  uint64_t totals[16] = {0};
   std::vector<tfs_msg_out_t> msgs;
   std::vector<tfs_tensor_out_t> tensors;
   std::vector<tfs_span_t> filters;
@@ -33,7 +33,9 @@ namespace tfs {
 namespace {
 
 enum { WT_VARINT = 0, WT_64 = 1, WT_LEN = 2, WT_SGROUP = 3, WT_EGROUP = 4, WT_32 = 5 };
-enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED };
+// TOT_GENERIC counts the copy-class spans the TMA ring cannot take (not congruent mod 16, tiny, or widened)
+enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_COUNT_ = 16 };
+constexpr size_t kTotalsBytes = sizeof(uint64_t) * TOT_COUNT_;
 
 __device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
   // 4..13 -> 0..9, 16 -> 10, 17 -> 11
@@ -221,7 +223,8 @@ struct Walker {
   }
   __device__ void add_span(uint32_t slot, uint32_t cls, uint64_t off, uint64_t len, uint64_t n_elems, uint32_t out_mult) {
     const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(w, off, len) : 0u;
-    const uint32_t ct = cls == SC_COPY ? static_cast<uint32_t>((len * out_mult + kCopyTileBytes - 1) / kCopyTileBytes) : 0u;
+    // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
+    const uint32_t ct = cls == SC_COPY ? static_cast<uint32_t>((len * out_mult + kCopyTileBytes - 1) / kCopyTileBytes) + 1u : 0u;
     if (FILL) {
       DecSpan s;
       s.wire_off = off;
@@ -614,6 +617,7 @@ __global__ void __launch_bounds__(1024) k_scan_counts(DecTables T) {
     T.totals[TOT_CTILES] = t5;
     T.totals[TOT_POOL] = 0;
     T.totals[TOT_FAILED] = 0;
+    T.totals[TOT_GENERIC] = 0;
   }
 }
 
@@ -793,6 +797,19 @@ __global__ void __launch_bounds__(128) k_dec_finalize(DecTables T) {
     }
     T.tensor_pool[ti] = bytes;
   }
+  // which copy-class spans need the generic copy kernel (slot regions start on 64-byte boundaries of the pool)
+  uint32_t generic = 0;
+  for (uint32_t si = s0; si < s1; ++si) {
+    const DecSpan& s = T.spans[si];
+    if (s.cls != SC_COPY || s.len == 0) continue;
+    const tfs_tensor_out_t& t = T.tensors[s.tensor];
+    const int32_t ty = t.dst_type[s.slot];
+    const bool widened = s.slot == 0 && ty == TFS_T_F32;
+    const uint64_t dst_low = s.slot == 0 ? 0 : s.elem_base * type_size_dev(ty);
+    const uint64_t src_addr = reinterpret_cast<uintptr_t>(T.wire) + s.wire_off;
+    if (widened || s.len < 4096 || ((src_addr ^ dst_low) & 15u) != 0) ++generic;
+  }
+  if (generic) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_GENERIC]), static_cast<unsigned long long>(generic));
   if (mo.status != TFS_OK) {  // a failed message exposes nothing
     mo.n_tensors = 0;
     mo.n_filters = 0;
@@ -974,7 +991,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   size_t cur = 0;
   const size_t o_off = carve(&cur, 8ull * n_msgs), o_len = carve(&cur, 8ull * n_msgs), o_ct = carve(&cur, 4ull * n_msgs),
                o_cf = carve(&cur, 4ull * n_msgs), o_cs = carve(&cur, 4ull * n_msgs), o_cb = carve(&cur, 4ull * n_msgs),
-               o_cv = carve(&cur, 4ull * n_msgs), o_cc = carve(&cur, 4ull * n_msgs), o_tot = carve(&cur, 64),
+               o_cv = carve(&cur, 4ull * n_msgs), o_cc = carve(&cur, 4ull * n_msgs), o_tot = carve(&cur, kTotalsBytes),
                o_msgs = carve(&cur, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs)), o_err = carve(&cur, 8ull * n_msgs);
   DEC_TRY(dev_reserve(ctx, &ctx->d_dec1, cur + 64));
   DEC_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, 16ull * n_msgs + 64));
@@ -1012,10 +1029,10 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   k_scan_counts<<<1, 1024, 0, ctx->stream>>>(T);
   ctx->launches++;
   DEC_CUDA(cudaGetLastError());
-  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, 64));
-  DEC_CUDA(cudaMemcpyAsync(ctx->h_down, T.totals, 64, cudaMemcpyDeviceToHost, ctx->stream));
+  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, kTotalsBytes));
+  DEC_CUDA(cudaMemcpyAsync(ctx->h_down, T.totals, kTotalsBytes, cudaMemcpyDeviceToHost, ctx->stream));
   DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1: the sizes of the pass-2 tables
-  std::memcpy(dec->totals, ctx->h_down, 64);
+  std::memcpy(dec->totals, ctx->h_down, kTotalsBytes);
   const uint64_t n_tensors = dec->totals[TOT_TENSORS], n_filters = dec->totals[TOT_FILTERS], n_spans = dec->totals[TOT_SPANS],
                  n_str = dec->totals[TOT_STR], n_vt = dec->totals[TOT_VTILES];
   if (n_tensors > 0xFFFFFFF0ull || n_spans > 0xFFFFFFF0ull || n_vt > 0xFFFFFFF0ull) return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large"));
@@ -1070,20 +1087,20 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   dec->strings.resize(n_str);
   size_t hc = 0;
   const size_t h_msgs = carve(&hc, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs)), h_ten = carve(&hc, sizeof(tfs_tensor_out_t) * n_tensors),
-               h_flt = carve(&hc, sizeof(tfs_span_t) * n_filters), h_str = carve(&hc, n_str), h_tot = carve(&hc, 64);
+               h_flt = carve(&hc, sizeof(tfs_span_t) * n_filters), h_str = carve(&hc, n_str), h_tot = carve(&hc, kTotalsBytes);
   DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, hc + 64));
   uint8_t* hd = static_cast<uint8_t*>(ctx->h_down);
   if (n_msgs) DEC_CUDA(cudaMemcpyAsync(hd + h_msgs, T.msgs, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs), cudaMemcpyDeviceToHost, ctx->stream));
   if (n_tensors) DEC_CUDA(cudaMemcpyAsync(hd + h_ten, T.tensors, sizeof(tfs_tensor_out_t) * n_tensors, cudaMemcpyDeviceToHost, ctx->stream));
   if (n_filters) DEC_CUDA(cudaMemcpyAsync(hd + h_flt, T.filters, sizeof(tfs_span_t) * n_filters, cudaMemcpyDeviceToHost, ctx->stream));
   if (n_str) DEC_CUDA(cudaMemcpyAsync(hd + h_str, T.strings, n_str, cudaMemcpyDeviceToHost, ctx->stream));
-  DEC_CUDA(cudaMemcpyAsync(hd + h_tot, T.totals, 64, cudaMemcpyDeviceToHost, ctx->stream));
+  DEC_CUDA(cudaMemcpyAsync(hd + h_tot, T.totals, kTotalsBytes, cudaMemcpyDeviceToHost, ctx->stream));
   DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #2: the caller needs the element counts to allocate
   if (n_msgs) std::memcpy(dec->msgs.data(), hd + h_msgs, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs));
   if (n_tensors) std::memcpy(dec->tensors.data(), hd + h_ten, sizeof(tfs_tensor_out_t) * n_tensors);
   if (n_filters) std::memcpy(dec->filters.data(), hd + h_flt, sizeof(tfs_span_t) * n_filters);
   if (n_str) std::memcpy(dec->strings.data(), hd + h_str, n_str);
-  std::memcpy(dec->totals, hd + h_tot, 64);
+  std::memcpy(dec->totals, hd + h_tot, kTotalsBytes);
   dec->n_failed = static_cast<uint32_t>(dec->totals[TOT_FAILED]);
   *out = dec;
 #undef DEC_TRY
@@ -1113,7 +1130,9 @@ tfs_status_t decode_device(tfs_ctx* ctx, tfs_decoded* dec, void* pool_dev, uint6
     ctx->launches++;
   }
   TFS_CUDA(ctx, cudaGetLastError());
-  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, nullptr, nullptr));
+  // the generic copy kernel is only needed for spans the TMA ring cannot take (counted by k_dec_finalize)
+  const bool need_generic = dec->totals[TOT_GENERIC] != 0 || (reinterpret_cast<uintptr_t>(pool_dev) & 15u) != 0;
+  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, nullptr, need_generic));
   return TFS_OK;
 }
 

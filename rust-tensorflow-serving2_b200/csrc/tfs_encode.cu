@@ -390,6 +390,9 @@ struct Compiled {
   std::vector<CopySeg> segs;
   uint64_t n_copy_tiles = 0;
   uint64_t bound = 0;  // upper bound of the encoded bytes
+  // true when the host can already tell that every bulk segment will be congruent mod 16 with its destination
+  // (TFS_F_ALIGN_PAYLOAD, one bulk field per message, 16-byte aligned plain-byte sources): TMA ring only
+  bool all_tma = true;
 };
 
 StrRef add_str(Compiled& c, const tfs_str_t& s) {
@@ -578,11 +581,30 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
       s.first_tile = c->n_copy_tiles;
       f.first_tile = static_cast<uint32_t>(c->segs.size());
       f.n_tiles = 0;
-      c->n_copy_tiles += (f.body_len + kCopyTileBytes - 1) / kCopyTileBytes;
+      // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
+      c->n_copy_tiles += (f.body_len + kCopyTileBytes - 1) / kCopyTileBytes + 1;
       c->segs.push_back(s);
     }
   }
   c->vfield_first_tile.push_back(vtiles);
+  // can the generic copy kernel be skipped?  Only the largest bulk body of a message is placed on a 16-byte
+  // boundary by TFS_F_ALIGN_PAYLOAD, so every message may carry at most one bulk field, a plain byte copy
+  // from a 16-byte aligned source, large enough for the TMA ring.
+  c->all_tma = (flags & TFS_F_ALIGN_PAYLOAD) != 0;
+  for (uint32_t mi = 0; mi < b->n_msgs && c->all_tma; ++mi) {
+    uint32_t bulk = 0;
+    const EncMsg& m = c->msgs[mi];
+    for (uint32_t ti = m.first_tensor; ti < m.first_tensor + m.n_tensors; ++ti) {
+      const EncTensor& t = c->tensors[ti];
+      for (uint32_t fi = t.first_field; fi < t.first_field + t.n_fields; ++fi) {
+        const EncField& f = c->fields[fi];
+        if (f.is_varint || f.n_elems == 0) continue;
+        ++bulk;
+        if (f.mode != CP_BYTES || f.body_len < 4096 || (reinterpret_cast<uintptr_t>(f.src) & 15u) != 0) c->all_tma = false;
+      }
+    }
+    if (bulk > 1) c->all_tma = false;
+  }
   return TFS_OK;
 }
 
@@ -734,7 +756,7 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
     }
     TFS_CUDA(ctx, cudaGetLastError());
     // gated on the overflow flag: when dst is too small segs[].dst were never filled in
-    if (T.n_segs) TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, nullptr, T.result + 1));
+    if (T.n_segs) TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, T.result + 1, !c.all_tma));
   }
   bool overflow = false;
   TFS_TRY(fetch_results(ctx, u.T, msg_off_out, msg_len_out, total_out, &overflow));

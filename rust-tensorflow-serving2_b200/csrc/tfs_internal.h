@@ -215,7 +215,7 @@ struct tfs_ctx {
 };
 
 namespace tfs {
-enum ProfKernel { PK_COPY = 0, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_FRAMING, PK_WALK, PK_COUNT_ };
+enum ProfKernel { PK_COPY = 0, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_COPY_TMA, PK_WALK, PK_COUNT_ };
 // Brackets one kernel launch with events when profiling is on (a no-op otherwise).
 struct ProfScope {
   tfs_ctx* ctx;
@@ -246,10 +246,10 @@ tfs_status_t pinned_reserve(tfs_ctx* ctx, void** p, size_t* cap, size_t bytes);
   } while (0)
 
 // Bulk copy / cast kernel over a segment table that already lives on the device.
-// With `n_tiles_dev` the tile count is read on the device (decode: the host does not know it yet);
-// with `gate` the kernel does nothing when *gate != 0.
-tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles,
-                         const uint64_t* n_tiles_dev, const uint64_t* gate);
+// With `gate` the kernels do nothing when *gate != 0.  `need_generic` = false promises that every non-empty
+// segment is a plain byte copy whose source and destination are congruent mod 16 (TMA ring only).
+tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
+                         bool need_generic);
 
 inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
