@@ -151,7 +151,7 @@ def run_ours(args):
         n = 0
         for v in VARIANTS:
             eb = enc.encode(built[v], kind, flags, dst=wire[v])
-            d = dec.decode(eb.wire, eb.offsets, eb.lengths, kind, 0, pool=pool[v])
+            d = dec.decode_into(eb.wire, eb.offsets, eb.lengths, kind, pool[v])
             n += 2 * sum(eb.lengths)
             d.close()
         return n
@@ -220,7 +220,7 @@ def run_ours(args):
             eb = enc.encode_host(hbuilt[v], kind, flags, dst=h_wire_np)
             h2d += Re * C2_ELEMS * 4
             d2h += eb.total
-            d = dec.decode_host(h_wire_np[: eb.total], eb.offsets, eb.lengths, kind, 0, pool=h_pool_np)
+            d = dec.decode_host_into(h_wire_np[: eb.total], eb.offsets, eb.lengths, kind, h_pool_np)
             h2d += eb.total
             d2h += d.pool_bytes
             n += 2 * sum(eb.lengths)
@@ -266,7 +266,7 @@ def run_ours(args):
                    "flags": "TFS_F_ALIGN_PAYLOAD", "sharding": f"dp{world}: independent requests per GPU, no collective"},
         "clocks": clocks,
         "e2e": {"value": round(world * e2e_bytes / e2e_s / 1e9, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "path": "tfs_encode_host + tfs_decode_host, pinned host buffers"},
+                "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "path": "tfs_encode_host + tfs_decode_host_into on pinned host buffers (kernels read and write host memory in place)"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "k_copy_tma (K5 bulk copy through the TMA ring; one launch per encode and per decode)",
                      "other_copy_kernel_avg_ms": round(ms_gen / max(1, n_gen), 4),

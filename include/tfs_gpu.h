@@ -336,6 +336,14 @@ tfs_status_t tfs_decoded_view(const tfs_decoded_t* dec, tfs_decoded_view_t* view
 tfs_status_t tfs_decode(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_dev, uint64_t pool_bytes);
 tfs_status_t tfs_decoded_free(tfs_ctx_t* ctx, tfs_decoded_t* dec);
 
+/* Both passes in one call, for callers that own a value pool of known capacity (the shim's staging pool):
+ * the values are written right behind the scan, without a round trip to the host in between.  When the pool
+ * turns out to be too small nothing is written and TFS_ERR_NOMEM is returned; the handle is still valid and
+ * its view says how many bytes are needed (then call tfs_decode with a larger pool). */
+tfs_status_t tfs_decode_into(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off,
+                             const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_dev,
+                             uint64_t pool_capacity, tfs_decoded_t** out);
+
 /* End to end: wire bytes in host memory, values written to a host pool (both pinned for full speed).
  * The pool is allocated by the caller after looking at the view: call with pool_host == NULL to get
  * the handle and the sizes (the wire stays staged on the device), then tfs_decode_host_finish. */
@@ -343,6 +351,11 @@ tfs_status_t tfs_decode_host(tfs_ctx_t* ctx, const void* wire_host, uint64_t wir
                              const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags,
                              tfs_decoded_t** out);
 tfs_status_t tfs_decode_host_finish(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_host, uint64_t pool_bytes);
+/* Host-memory form of tfs_decode_into.  Pinned buffers (tfs_host_alloc) are read and written in place by the
+ * kernels; pageable ones are staged through device memory. */
+tfs_status_t tfs_decode_host_into(tfs_ctx_t* ctx, const void* wire_host, uint64_t wire_bytes, const uint64_t* msg_off,
+                                  const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_host,
+                                  uint64_t pool_capacity, tfs_decoded_t** out);
 
 /* ----------------------------------------------------------------------------------------------
  * Allocation-free packing of one int64 array (no counterpart in the reference: the reference never

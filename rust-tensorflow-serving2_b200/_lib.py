@@ -69,6 +69,8 @@ def lib():
     L.tfs_decoded_free.argtypes = [vp, vp]
     L.tfs_decode_host.argtypes = [vp, vp, C.c_uint64, u64p, u64p, C.c_uint32, C.c_int32, C.c_uint32, C.POINTER(vp)]
     L.tfs_decode_host_finish.argtypes = [vp, vp, vp, C.c_uint64]
+    L.tfs_decode_into.argtypes = [vp, vp, C.c_uint64, u64p, u64p, C.c_uint32, C.c_int32, C.c_uint32, vp, C.c_uint64, C.POINTER(vp)]
+    L.tfs_decode_host_into.argtypes = [vp, vp, C.c_uint64, u64p, u64p, C.c_uint32, C.c_int32, C.c_uint32, vp, C.c_uint64, C.POINTER(vp)]
     L.tfs_shard_plan.argtypes = [u64p, C.c_uint32, C.c_uint32, u32p]
     L.tfs_slot_of_kind.argtypes = [C.c_int32]
     L.tfs_kind_of_slot.argtypes = [C.c_int32]

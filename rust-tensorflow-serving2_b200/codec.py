@@ -209,6 +209,32 @@ class GpuDecoder:
     def decode(self, wire, offsets, lengths, kind: int, flags: int = 0, pool=None) -> DecodedBatch:
         return self.values(self.scan(wire, offsets, lengths, kind, flags), pool)
 
+    def decode_into(self, wire, offsets, lengths, kind: int, pool, flags: int = 0) -> DecodedBatch:
+        """Both passes in one call into a device pool of known capacity (tfs_decode_into)."""
+        n, off, ln = self._arrays(offsets, lengths)
+        h = C.c_void_p()
+        st = lib().tfs_decode_into(self.ctx.handle, C.c_void_p(wire.data_ptr() if wire.numel() else 0), wire.numel(), off, ln, n, kind,
+                                   flags, C.c_void_p(pool.data_ptr()), pool.numel(), C.byref(h))
+        if st == abi.TFS_ERR_NOMEM and h:
+            lib().tfs_decoded_free(self.ctx.handle, h)
+        self.ctx.check(st, ok=(abi.TFS_OK, abi.TFS_ERR_BATCH))
+        dec = DecodedBatch(self.ctx, h, st, kind)
+        dec.pool = pool
+        return dec
+
+    def decode_host_into(self, wire: np.ndarray, offsets, lengths, kind: int, pool: np.ndarray, flags: int = 0) -> DecodedBatch:
+        """Host-memory form of decode_into: pinned buffers are read / written in place by the kernels."""
+        n, off, ln = self._arrays(offsets, lengths)
+        h = C.c_void_p()
+        st = lib().tfs_decode_host_into(self.ctx.handle, C.c_void_p(wire.ctypes.data if wire.size else 0), wire.size, off, ln, n, kind,
+                                        flags, C.c_void_p(pool.ctypes.data), pool.size, C.byref(h))
+        if st == abi.TFS_ERR_NOMEM and h:
+            lib().tfs_decoded_free(self.ctx.handle, h)
+        self.ctx.check(st, ok=(abi.TFS_OK, abi.TFS_ERR_BATCH))
+        dec = DecodedBatch(self.ctx, h, st, kind)
+        dec.pool = pool
+        return dec
+
     def decode_host(self, wire: np.ndarray, offsets, lengths, kind: int, flags: int = 0, pool: Optional[np.ndarray] = None) -> DecodedBatch:
         """End to end: wire bytes in host memory, values returned in a host pool."""
         wire = np.ascontiguousarray(wire, dtype=np.uint8)

@@ -34,7 +34,7 @@ namespace {
 
 enum { WT_VARINT = 0, WT_64 = 1, WT_LEN = 2, WT_SGROUP = 3, WT_EGROUP = 4, WT_32 = 5 };
 // TOT_GENERIC counts the copy-class spans the TMA ring cannot take (not congruent mod 16, tiny, or widened)
-enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_COUNT_ = 16 };
+enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_COUNT_ = 16 };
 constexpr size_t kTotalsBytes = sizeof(uint64_t) * TOT_COUNT_;
 
 __device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
@@ -43,24 +43,25 @@ __device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
 }
 
 // Rust core::str::from_utf8 validity (no overlongs, no surrogates, <= U+10FFFF)
-__device__ bool utf8_ok(const uint8_t* p, uint32_t n) {
+template <class Get>
+__device__ bool utf8_ok(Get p, uint32_t n) {  // p(i) = i-th byte
   uint32_t i = 0;
   while (i < n) {
-    const uint8_t b = p[i];
+    const uint8_t b = p(i);
     if (b < 0x80) {
       i += 1;
     } else if (b >= 0xC2 && b <= 0xDF) {
-      if (i + 1 >= n || (p[i + 1] & 0xC0) != 0x80) return false;
+      if (i + 1 >= n || (p(i + 1) & 0xC0) != 0x80) return false;
       i += 2;
     } else if (b >= 0xE0 && b <= 0xEF) {
       if (i + 2 >= n) return false;
-      const uint8_t c1 = p[i + 1], c2 = p[i + 2];
+      const uint8_t c1 = p(i + 1), c2 = p(i + 2);
       const uint8_t lo = b == 0xE0 ? 0xA0 : 0x80, hi = b == 0xED ? 0x9F : 0xBF;
       if (c1 < lo || c1 > hi || (c2 & 0xC0) != 0x80) return false;
       i += 3;
     } else if (b >= 0xF0 && b <= 0xF4) {
       if (i + 3 >= n) return false;
-      const uint8_t c1 = p[i + 1], c2 = p[i + 2], c3 = p[i + 3];
+      const uint8_t c1 = p(i + 1), c2 = p(i + 2), c3 = p(i + 3);
       const uint8_t lo = b == 0xF0 ? 0x90 : 0x80, hi = b == 0xF4 ? 0x8F : 0xBF;
       if (c1 < lo || c1 > hi || (c2 & 0xC0) != 0x80 || (c3 & 0xC0) != 0x80) return false;
       i += 4;
@@ -93,13 +94,31 @@ struct Walker {
   uint64_t err_pos = 0;
   bool soft_unsupported = false;
   // counters (COUNT) / cursors (FILL)
-  uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0;
+  uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0, n_generic = 0;
+  uint32_t seen_slots = 0;  // payload slots of the current tensor that already have a chunk
   // current tensor
   uint32_t cur = 0;
   uint32_t cur_dims = 0;
   uint32_t content_span = 0xFFFFFFFFu;
 
+  // 16-byte window over the wire: header bytes are read through it, one aligned vector load per 16 bytes
+  // instead of one dependent byte load per byte (the walk is a chain of dependent reads)
+  uint4 win = make_uint4(0, 0, 0, 0);
+  uint64_t win_base = ~0ull;
+
   __device__ Walker(const DecTables& t, uint32_t m) : T(t), w(t.wire), msg(m) {}
+
+  __device__ __forceinline__ uint8_t byte_at(uint64_t off) {
+    const uint64_t a = reinterpret_cast<uintptr_t>(w) + off;
+    const uint64_t base = a & ~static_cast<uint64_t>(15);
+    if (base != win_base) {  // the aligned 16 bytes around a valid byte never leave its page
+      win = *reinterpret_cast<const uint4*>(base);
+      win_base = base;
+    }
+    const uint32_t k = static_cast<uint32_t>(a >> 2) & 3u;
+    const uint32_t word = k == 0 ? win.x : k == 1 ? win.y : k == 2 ? win.z : win.w;
+    return static_cast<uint8_t>(word >> ((static_cast<uint32_t>(a) & 3u) * 8u));
+  }
 
   __device__ __forceinline__ bool fail(int32_t code) {
     if (!err) {
@@ -115,7 +134,7 @@ struct Walker {
     const uint64_t rem = end - pos;
     const uint32_t n = rem < 10 ? static_cast<uint32_t>(rem) : 10u;
     for (uint32_t i = 0; i < n; ++i) {
-      const uint8_t b = w[pos++];
+      const uint8_t b = byte_at(pos++);
       r |= static_cast<uint64_t>(b & 0x7F) << (7u * i);
       if (b < 0x80) {
         *v = r;
@@ -198,7 +217,7 @@ struct Walker {
     sp.len = len;
     sp._pad = 0;
     if (FILL)
-      for (uint32_t i = 0; i < len; ++i) T.strings[n_str + i] = w[off + i];
+      for (uint32_t i = 0; i < len; ++i) T.strings[n_str + i] = byte_at(off + i);
     n_str += len;
     return sp;
   }
@@ -210,7 +229,7 @@ struct Walker {
     if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
     const uint64_t off = pos;
     pos += len;
-    if (!utf8_ok(w + off, static_cast<uint32_t>(len))) return fail(TFS_ERR_UTF8);
+    if (!utf8_ok([&](uint32_t i) { return byte_at(off + i); }, static_cast<uint32_t>(len))) return fail(TFS_ERR_UTF8);
     *out = add_string(off, static_cast<uint32_t>(len));
     return true;
   }
@@ -219,10 +238,19 @@ struct Walker {
     cur = n_tensors++;
     cur_dims = 0;
     content_span = 0xFFFFFFFFu;
+    seen_slots = 0;
     if (FILL) T.tensors[cur].msg_index = msg;
   }
   __device__ void add_span(uint32_t slot, uint32_t cls, uint64_t off, uint64_t len, uint64_t n_elems, uint32_t out_mult) {
     const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(w, off, len) : 0u;
+    if (cls == SC_COPY && len) {
+      // Can the TMA ring take this span?  Its pool region starts on a 64-byte boundary, so the first chunk of
+      // a slot is congruent mod 16 with its source iff the source address is 16-byte aligned.  A conservative
+      // count (later chunks, tiny or widened spans count as "no") decides whether the generic kernel is launched.
+      const bool first = !((seen_slots >> slot) & 1u);
+      if (!first || len < 4096 || out_mult != 1 || ((reinterpret_cast<uintptr_t>(w) + off) & 15u) != 0) n_generic++;
+    }
+    seen_slots |= 1u << slot;
     // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
     const uint32_t ct = cls == SC_COPY ? static_cast<uint32_t>((len * out_mult + kCopyTileBytes - 1) / kCopyTileBytes) + 1u : 0u;
     if (FILL) {
@@ -255,12 +283,12 @@ struct Walker {
       const uint64_t off = pos, len = rend - pos;
       if (len) {
         // does the last varint of the body end exactly at the limit?  prost reads on past it.
-        if (w[rend - 1] & 0x80) {
+        if (byte_at(rend - 1) & 0x80) {
           // error path only: prost fails at the FIRST bad varint, so look for an over-long one (ten
           // continuation bytes in a row) earlier in the body before classifying the trailing one
           uint32_t run = 0;
           for (uint64_t q = off; q < rend; ++q) {
-            if (w[q] & 0x80) {
+            if (byte_at(q) & 0x80) {
               if (++run == 10) {
                 pos = q + 1;
                 return fail(TFS_ERR_INVALID_VARINT);
@@ -270,12 +298,12 @@ struct Walker {
             }
           }
           uint32_t k = 0;  // continuation bytes at the end of the body
-          while (k < 10 && k < len && (w[rend - 1 - k] & 0x80)) ++k;
+          while (k < 10 && k < len && (byte_at(rend - 1 - k) & 0x80)) ++k;
           pos = rend;
           if (k >= 10) return fail(TFS_ERR_INVALID_VARINT);
           for (uint32_t j = k; j < 10; ++j) {
             if (pos >= end) return fail(TFS_ERR_INVALID_VARINT);
-            if (!(w[pos++] & 0x80)) return fail(TFS_ERR_LENGTH_EXCEEDED);
+            if (!(byte_at(pos++) & 0x80)) return fail(TFS_ERR_LENGTH_EXCEEDED);
           }
           return fail(TFS_ERR_INVALID_VARINT);
         }
@@ -497,9 +525,9 @@ struct Walker {
     if (T.flags & TFS_F_GRPC_PREFIX) {  // tonic Streaming: flag byte 0, u32 big-endian length
       const uint64_t n = end - beg;
       if (n < 5) return fail(TFS_ERR_BUFFER_UNDERFLOW);
-      if (w[beg] != 0) return fail(TFS_ERR_GRPC_FLAG);
-      const uint64_t l = (static_cast<uint64_t>(w[beg + 1]) << 24) | (static_cast<uint64_t>(w[beg + 2]) << 16) |
-                         (static_cast<uint64_t>(w[beg + 3]) << 8) | w[beg + 4];
+      if (byte_at(beg) != 0) return fail(TFS_ERR_GRPC_FLAG);
+      const uint64_t l = (static_cast<uint64_t>(byte_at(beg + 1)) << 24) | (static_cast<uint64_t>(byte_at(beg + 2)) << 16) |
+                         (static_cast<uint64_t>(byte_at(beg + 3)) << 8) | byte_at(beg + 4);
       pos = beg + 1;
       if (l != n - 5) return fail(l > n - 5 ? TFS_ERR_BUFFER_UNDERFLOW : TFS_ERR_LENGTH_EXCEEDED);
       pos = beg + 5;
@@ -560,6 +588,7 @@ __global__ void __launch_bounds__(128) k_walk(DecTables T) {
     T.cnt_strbytes[mi] = ok ? wk.n_str : 0u;
     T.cnt_vtiles[mi] = ok ? wk.n_vt : 0u;
     T.cnt_ctiles[mi] = ok ? wk.n_ct : 0u;
+    if (ok && wk.n_generic) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_GENERIC]), static_cast<unsigned long long>(wk.n_generic));
   } else {
     const int32_t st = T.msgs[mi].status;
     const uint64_t eo = T.msgs[mi].err_offset;
@@ -617,7 +646,7 @@ __global__ void __launch_bounds__(1024) k_scan_counts(DecTables T) {
     T.totals[TOT_CTILES] = t5;
     T.totals[TOT_POOL] = 0;
     T.totals[TOT_FAILED] = 0;
-    T.totals[TOT_GENERIC] = 0;
+    // TOT_GENERIC was accumulated by the walk (the host zeroes the totals before pass 1)
   }
 }
 
@@ -797,19 +826,6 @@ __global__ void __launch_bounds__(128) k_dec_finalize(DecTables T) {
     }
     T.tensor_pool[ti] = bytes;
   }
-  // which copy-class spans need the generic copy kernel (slot regions start on 64-byte boundaries of the pool)
-  uint32_t generic = 0;
-  for (uint32_t si = s0; si < s1; ++si) {
-    const DecSpan& s = T.spans[si];
-    if (s.cls != SC_COPY || s.len == 0) continue;
-    const tfs_tensor_out_t& t = T.tensors[s.tensor];
-    const int32_t ty = t.dst_type[s.slot];
-    const bool widened = s.slot == 0 && ty == TFS_T_F32;
-    const uint64_t dst_low = s.slot == 0 ? 0 : s.elem_base * type_size_dev(ty);
-    const uint64_t src_addr = reinterpret_cast<uintptr_t>(T.wire) + s.wire_off;
-    if (widened || s.len < 4096 || ((src_addr ^ dst_low) & 15u) != 0) ++generic;
-  }
-  if (generic) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_GENERIC]), static_cast<unsigned long long>(generic));
   if (mo.status != TFS_OK) {  // a failed message exposes nothing
     mo.n_tensors = 0;
     mo.n_filters = 0;
@@ -819,7 +835,7 @@ __global__ void __launch_bounds__(128) k_dec_finalize(DecTables T) {
 }
 
 // exclusive scan of the per-tensor pool bytes, then absolute slot offsets. Single CTA.
-__global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_tensors) {
+__global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_tensors, uint64_t pool_capacity) {
   __shared__ uint64_t smem[33];
   uint64_t carry = 0;
   for (uint32_t base = 0; base < n_tensors; base += 1024) {
@@ -834,13 +850,16 @@ __global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_te
     carry += total;
     __syncthreads();
   }
-  if (threadIdx.x == 0) T.totals[TOT_POOL] = carry;
+  if (threadIdx.x == 0) {
+    T.totals[TOT_POOL] = carry;
+    T.totals[TOT_OVERFLOW] = carry > pool_capacity ? 1ull : 0ull;  // gates the value kernels of a one-call decode
+  }
 }
 
 // at decode time: bind every copy-class span to its place in the caller's pool
-__global__ void __launch_bounds__(256) k_dec_bind(DecTables T, uint32_t n_spans, uint8_t* pool) {
+__global__ void __launch_bounds__(256) k_dec_bind(DecTables T, uint32_t n_spans, uint8_t* pool, const uint64_t* __restrict__ gate) {
   const uint32_t si = blockIdx.x * blockDim.x + threadIdx.x;
-  if (si >= n_spans) return;
+  if (si >= n_spans || (gate && *gate != 0)) return;
   const DecSpan& s = T.spans[si];
   CopySeg g;
   g.first_tile = T.span_ctile0[si];
@@ -895,8 +914,10 @@ __device__ __forceinline__ void store_value(uint8_t* dst, uint64_t idx, uint64_t
   }
 }
 
-__global__ void __launch_bounds__(kDecThreads) k_varint_gather(DecTables T, uint32_t n_spans, uint64_t n_tiles, uint8_t* pool) {
+__global__ void __launch_bounds__(kDecThreads) k_varint_gather(DecTables T, uint32_t n_spans, uint64_t n_tiles, uint8_t* pool,
+                                                              const uint64_t* __restrict__ gate) {
   __shared__ __align__(16) uint8_t sm[16 + kDecTileBytes];
+  if (gate && *gate != 0) return;  // the pool of a one-call decode turned out to be too small
   __shared__ GatherRef s_ref;
   __shared__ uint32_t scan_smem[kDecThreads / 32 + 1];
   for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -960,10 +981,36 @@ size_t carve(size_t* cur, size_t bytes, size_t align = 64) {
   return off;
 }
 
+// value kernels: bind the copy spans to the pool, gather the varint spans, copy the bulk spans
+tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const uint64_t* gate) {
+  const DecTables& T = dec->T;
+  const uint64_t n_spans = dec->totals[TOT_SPANS], n_vt = dec->totals[TOT_VTILES], n_ct = dec->totals[TOT_CTILES];
+  if (n_spans) {
+    k_dec_bind<<<static_cast<uint32_t>((n_spans + 255) / 256), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), pool, gate);
+    ctx->launches++;
+  }
+  if (n_vt) {
+    const uint64_t cap = static_cast<uint64_t>(ctx->sm_count) * 8;
+    {
+      ProfScope prof(ctx, PK_VARINT_GATHER);
+      k_varint_gather<<<static_cast<uint32_t>(n_vt < cap ? n_vt : cap), kDecThreads, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt, pool, gate);
+    }
+    ctx->launches++;
+  }
+  TFS_CUDA(ctx, cudaGetLastError());
+  // the generic copy kernel is only needed for spans the TMA ring cannot take (counted by the walk)
+  const bool need_generic = dec->totals[TOT_GENERIC] != 0 || (reinterpret_cast<uintptr_t>(pool) & 15u) != 0;
+  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, gate, need_generic));
+  return TFS_OK;
+}
+
 }  // namespace
 
+// Scan (and, when `pool_dev` is given, decode the values too) with two host synchronisations: one for the table
+// sizes, one for the results.  pool_dev == nullptr: scan only (the caller allocates the pool from the view).
 tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off,
-                                const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, tfs_decoded** out) {
+                                const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_dev,
+                                uint64_t pool_capacity, tfs_decoded** out) {
   TFS_CUDA(ctx, cudaSetDevice(ctx->device));
   if (msg_kind < TFS_MSG_TENSOR_PROTO || msg_kind > TFS_MSG_PREDICT_RESPONSE) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad msg_kind");
   tfs_decoded* dec = new (std::nothrow) tfs_decoded();
@@ -987,12 +1034,13 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     if (e__ != cudaSuccess) return bail(cuda_fail(ctx, e__, #call));    \
   } while (0)
 
-  // ---- pass 1 tables: message ranges, counters, per-message status (msgs[]) and error words
+  // ---- pass 1 tables: message ranges, counters, totals + per-message records (contiguous: one D2H), error words
   size_t cur = 0;
   const size_t o_off = carve(&cur, 8ull * n_msgs), o_len = carve(&cur, 8ull * n_msgs), o_ct = carve(&cur, 4ull * n_msgs),
                o_cf = carve(&cur, 4ull * n_msgs), o_cs = carve(&cur, 4ull * n_msgs), o_cb = carve(&cur, 4ull * n_msgs),
                o_cv = carve(&cur, 4ull * n_msgs), o_cc = carve(&cur, 4ull * n_msgs), o_tot = carve(&cur, kTotalsBytes),
                o_msgs = carve(&cur, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs)), o_err = carve(&cur, 8ull * n_msgs);
+  const size_t res1_bytes = o_msgs + sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs) - o_tot;  // totals .. msgs
   DEC_TRY(dev_reserve(ctx, &ctx->d_dec1, cur + 64));
   DEC_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, 16ull * n_msgs + 64));
   uint8_t* d1 = static_cast<uint8_t*>(ctx->d_dec1.p);
@@ -1000,10 +1048,12 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   if (n_msgs) {
     std::memcpy(h, msg_off, 8ull * n_msgs);
     std::memcpy(h + n_msgs, msg_len, 8ull * n_msgs);
+    // o_off and o_len are adjacent only up to alignment: two copies keep the layout simple
     DEC_CUDA(cudaMemcpyAsync(d1 + o_off, h, 8ull * n_msgs, cudaMemcpyHostToDevice, ctx->stream));
     DEC_CUDA(cudaMemcpyAsync(d1 + o_len, h + n_msgs, 8ull * n_msgs, cudaMemcpyHostToDevice, ctx->stream));
     DEC_CUDA(cudaMemsetAsync(d1 + o_err, 0xFF, 8ull * n_msgs, ctx->stream));
   }
+  DEC_CUDA(cudaMemsetAsync(d1 + o_tot, 0, kTotalsBytes, ctx->stream));
   T.wire = static_cast<const uint8_t*>(wire_dev);
   T.wire_bytes = wire_bytes;
   T.msg_off = reinterpret_cast<const uint64_t*>(d1 + o_off);
@@ -1037,10 +1087,12 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
                  n_str = dec->totals[TOT_STR], n_vt = dec->totals[TOT_VTILES];
   if (n_tensors > 0xFFFFFFF0ull || n_spans > 0xFFFFFFF0ull || n_vt > 0xFFFFFFF0ull) return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large"));
 
-  // ---- pass 2 tables
+  // ---- pass 2 tables; tensors | filters | strings are contiguous: one D2H
   cur = 0;
   const size_t p_ten = carve(&cur, sizeof(tfs_tensor_out_t) * n_tensors), p_flt = carve(&cur, sizeof(tfs_span_t) * n_filters),
-               p_str = carve(&cur, n_str), p_spn = carve(&cur, sizeof(DecSpan) * n_spans), p_sv = carve(&cur, 4 * (n_spans + 1)),
+               p_str = carve(&cur, n_str);
+  const size_t res2_bytes = cur;
+  const size_t p_spn = carve(&cur, sizeof(DecSpan) * n_spans), p_sv = carve(&cur, 4 * (n_spans + 1)),
                p_sc = carve(&cur, 4 * (n_spans + 1)), p_tc = carve(&cur, 4 * n_vt), p_tb = carve(&cur, 8 * n_vt),
                p_seg = carve(&cur, sizeof(CopySeg) * n_spans), p_tp = carve(&cur, 8 * n_tensors);
   DEC_TRY(dev_reserve(ctx, &ctx->d_dec2, cur + 64));
@@ -1067,8 +1119,6 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       k_varint_count<<<static_cast<uint32_t>(n_vt < cap ? n_vt : cap), kDecThreads, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);
     }
     ctx->launches++;
-  }
-  if (n_spans) {
     k_span_scan<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);
     ctx->launches++;
   }
@@ -1076,35 +1126,33 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     k_dec_finalize<<<mblocks, 128, 0, ctx->stream>>>(T);
     ctx->launches++;
   }
-  k_pool_layout<<<1, 1024, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors));
+  k_pool_layout<<<1, 1024, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_dev ? pool_capacity : ~0ull);
   ctx->launches++;
   DEC_CUDA(cudaGetLastError());
+  // one-call decode: the value kernels follow at once, gated on the device by "the pool is large enough"
+  if (pool_dev) DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), T.totals + TOT_OVERFLOW));
 
-  // ---- results to the host
+  // ---- results to the host: (totals | msgs) and (tensors | filters | strings), two copies
   dec->msgs.resize(n_msgs);
   dec->tensors.resize(n_tensors);
   dec->filters.resize(n_filters);
   dec->strings.resize(n_str);
-  size_t hc = 0;
-  const size_t h_msgs = carve(&hc, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs)), h_ten = carve(&hc, sizeof(tfs_tensor_out_t) * n_tensors),
-               h_flt = carve(&hc, sizeof(tfs_span_t) * n_filters), h_str = carve(&hc, n_str), h_tot = carve(&hc, kTotalsBytes);
-  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, hc + 64));
+  const size_t h1 = 0, h2 = align_up(res1_bytes, 64);
+  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, h2 + res2_bytes + 64));
   uint8_t* hd = static_cast<uint8_t*>(ctx->h_down);
-  if (n_msgs) DEC_CUDA(cudaMemcpyAsync(hd + h_msgs, T.msgs, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs), cudaMemcpyDeviceToHost, ctx->stream));
-  if (n_tensors) DEC_CUDA(cudaMemcpyAsync(hd + h_ten, T.tensors, sizeof(tfs_tensor_out_t) * n_tensors, cudaMemcpyDeviceToHost, ctx->stream));
-  if (n_filters) DEC_CUDA(cudaMemcpyAsync(hd + h_flt, T.filters, sizeof(tfs_span_t) * n_filters, cudaMemcpyDeviceToHost, ctx->stream));
-  if (n_str) DEC_CUDA(cudaMemcpyAsync(hd + h_str, T.strings, n_str, cudaMemcpyDeviceToHost, ctx->stream));
-  DEC_CUDA(cudaMemcpyAsync(hd + h_tot, T.totals, kTotalsBytes, cudaMemcpyDeviceToHost, ctx->stream));
-  DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #2: the caller needs the element counts to allocate
-  if (n_msgs) std::memcpy(dec->msgs.data(), hd + h_msgs, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs));
-  if (n_tensors) std::memcpy(dec->tensors.data(), hd + h_ten, sizeof(tfs_tensor_out_t) * n_tensors);
-  if (n_filters) std::memcpy(dec->filters.data(), hd + h_flt, sizeof(tfs_span_t) * n_filters);
-  if (n_str) std::memcpy(dec->strings.data(), hd + h_str, n_str);
-  std::memcpy(dec->totals, hd + h_tot, kTotalsBytes);
+  DEC_CUDA(cudaMemcpyAsync(hd + h1, d1 + o_tot, res1_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  if (res2_bytes) DEC_CUDA(cudaMemcpyAsync(hd + h2, d2 + p_ten, res2_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #2: the caller needs the element counts (and, one-call, the values)
+  std::memcpy(dec->totals, hd + h1, kTotalsBytes);
+  if (n_msgs) std::memcpy(dec->msgs.data(), hd + h1 + (o_msgs - o_tot), sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs));
+  if (n_tensors) std::memcpy(dec->tensors.data(), hd + h2 + p_ten, sizeof(tfs_tensor_out_t) * n_tensors);
+  if (n_filters) std::memcpy(dec->filters.data(), hd + h2 + p_flt, sizeof(tfs_span_t) * n_filters);
+  if (n_str) std::memcpy(dec->strings.data(), hd + h2 + p_str, n_str);
   dec->n_failed = static_cast<uint32_t>(dec->totals[TOT_FAILED]);
   *out = dec;
 #undef DEC_TRY
 #undef DEC_CUDA
+  if (pool_dev && dec->totals[TOT_OVERFLOW]) return set_err(ctx, TFS_ERR_NOMEM, "value pool is smaller than tfs_decoded_view().pool_bytes; nothing was written");
   return dec->n_failed ? TFS_ERR_BATCH : TFS_OK;
 }
 
@@ -1114,26 +1162,7 @@ tfs_status_t decode_device(tfs_ctx* ctx, tfs_decoded* dec, void* pool_dev, uint6
     return set_err(ctx, TFS_ERR_INVALID_ARG, "stale decode handle: another tfs_decode_scan ran on this ctx since");
   if (pool_bytes < dec->totals[TOT_POOL] || (!pool_dev && dec->totals[TOT_POOL]))
     return set_err(ctx, TFS_ERR_NOMEM, "value pool is smaller than tfs_decoded_view().pool_bytes");
-  const DecTables& T = dec->T;
-  const uint64_t n_spans = dec->totals[TOT_SPANS], n_vt = dec->totals[TOT_VTILES], n_ct = dec->totals[TOT_CTILES];
-  uint8_t* pool = static_cast<uint8_t*>(pool_dev);
-  if (n_spans) {
-    k_dec_bind<<<static_cast<uint32_t>((n_spans + 255) / 256), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), pool);
-    ctx->launches++;
-  }
-  if (n_vt) {
-    const uint64_t cap = static_cast<uint64_t>(ctx->sm_count) * 8;
-    {
-      ProfScope prof(ctx, PK_VARINT_GATHER);
-      k_varint_gather<<<static_cast<uint32_t>(n_vt < cap ? n_vt : cap), kDecThreads, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt, pool);
-    }
-    ctx->launches++;
-  }
-  TFS_CUDA(ctx, cudaGetLastError());
-  // the generic copy kernel is only needed for spans the TMA ring cannot take (counted by k_dec_finalize)
-  const bool need_generic = dec->totals[TOT_GENERIC] != 0 || (reinterpret_cast<uintptr_t>(pool_dev) & 15u) != 0;
-  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, nullptr, need_generic));
-  return TFS_OK;
+  return launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), nullptr);
 }
 
 uint64_t decoded_pool_bytes(const tfs_decoded* dec) { return dec->totals[TOT_POOL]; }
@@ -1155,7 +1184,15 @@ tfs_status_t tfs_decode_scan(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire
                              const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, tfs_decoded_t** out) {
   if (!ctx || !out || (n_msgs && (!msg_off || !msg_len)) || (wire_bytes && !wire_dev)) return TFS_ERR_INVALID_ARG;
   *out = nullptr;
-  return decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, out);
+  return decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, nullptr, 0, out);
+}
+
+tfs_status_t tfs_decode_into(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off, const uint64_t* msg_len,
+                             uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_dev, uint64_t pool_capacity,
+                             tfs_decoded_t** out) {
+  if (!ctx || !out || !pool_dev || (n_msgs && (!msg_off || !msg_len)) || (wire_bytes && !wire_dev)) return TFS_ERR_INVALID_ARG;
+  *out = nullptr;
+  return decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, pool_dev, pool_capacity, out);
 }
 
 tfs_status_t tfs_decoded_view(const tfs_decoded_t* dec, tfs_decoded_view_t* view) {

@@ -711,19 +711,20 @@ tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_
 
 tfs_status_t fetch_results(tfs_ctx* ctx, const EncTables& T, uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out,
                            bool* overflow) {
+  // msg_len | msg_pay_off | msg_off | result were carved next to each other: one device -> host copy
   const size_t n = T.n_msgs;
-  TFS_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, 16 * n + 32));
-  uint64_t* h = static_cast<uint64_t*>(ctx->h_down);
-  if (n) {
-    TFS_CUDA(ctx, cudaMemcpyAsync(h, T.msg_off, 8 * n, cudaMemcpyDeviceToHost, ctx->stream));
-    TFS_CUDA(ctx, cudaMemcpyAsync(h + n, T.msg_len, 8 * n, cudaMemcpyDeviceToHost, ctx->stream));
-  }
-  TFS_CUDA(ctx, cudaMemcpyAsync(h + 2 * n, T.result, 16, cudaMemcpyDeviceToHost, ctx->stream));
+  const uint8_t* base = reinterpret_cast<const uint8_t*>(T.msg_len);
+  const size_t o_off = reinterpret_cast<const uint8_t*>(T.msg_off) - base, o_res = reinterpret_cast<const uint8_t*>(T.result) - base;
+  const size_t bytes = o_res + 16;
+  TFS_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, bytes));
+  uint8_t* h = static_cast<uint8_t*>(ctx->h_down);
+  TFS_CUDA(ctx, cudaMemcpyAsync(h, base, bytes, cudaMemcpyDeviceToHost, ctx->stream));
   TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  if (msg_off_out && n) std::memcpy(msg_off_out, h, 8 * n);
-  if (msg_len_out && n) std::memcpy(msg_len_out, h + n, 8 * n);
-  if (total_out) *total_out = h[2 * n];
-  *overflow = h[2 * n + 1] != 0;
+  if (msg_off_out && n) std::memcpy(msg_off_out, h + o_off, 8 * n);
+  if (msg_len_out && n) std::memcpy(msg_len_out, h, 8 * n);
+  const uint64_t* res = reinterpret_cast<const uint64_t*>(h + o_res);
+  if (total_out) *total_out = res[0];
+  *overflow = res[1] != 0;
   return TFS_OK;
 }
 

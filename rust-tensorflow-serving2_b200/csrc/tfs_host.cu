@@ -1,6 +1,17 @@
 // tfs_host.cu — the host-memory entry points: what the Rust shim calls from inside tonic's body stream,
-// where the message payloads (Vec<f32>, ...) and the BytesMut both live in host memory.  The ctx's device
-// staging buffers bridge them to HBM; host<->device copies are part of these calls (the `e2e` number).
+// where the message payloads (Vec<f32>, ...) and the BytesMut both live in host memory.  Host<->device traffic
+// is part of these calls (the `e2e` number of bench.py).
+//
+// Two ways across PCIe, chosen per buffer:
+//   * PINNED host memory (tfs_host_alloc / cudaHostAlloc / cudaHostRegister — the shim's staging pool) is
+//     addressable by the GPU, so the kernels read the payload from it and write the wire bytes into it directly:
+//     one kernel moves bytes in both directions at once, nothing is staged in HBM.  (Measured on this B200 box:
+//     the TMA ring and plain 16-byte loads/stores both run host->host at ~40 GB/s per direction concurrently,
+//     against 55 GB/s for a one-direction copy-engine transfer; scripts/copy_sweep.cu host.)
+//     Exception: arrays that are varint-coded are read twice (size pass + scatter pass), so they are first
+//     copied to HBM by the copy engine.
+//   * pageable host memory cannot be addressed by the GPU: it is staged through the ctx's device buffers with
+//     cudaMemcpyAsync in both directions.
 #include <cstring>
 
 #include "tfs_internal.h"
@@ -11,11 +22,46 @@ namespace tfs {
 tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev, uint64_t dst_capacity, uint32_t flags,
                            uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out, bool size_only);
 tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off,
-                                const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, tfs_decoded** out);
+                                const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_dev,
+                                uint64_t pool_capacity, tfs_decoded** out);
 tfs_status_t decode_device(tfs_ctx* ctx, tfs_decoded* dec, void* pool_dev, uint64_t pool_bytes);
 uint64_t decoded_pool_bytes(const tfs_decoded* dec);
 void decoded_mark_host_staged(tfs_decoded* dec, uint64_t stage_generation);
 bool decoded_stage_is_current(const tfs_decoded* dec, uint64_t stage_generation);
+
+namespace {
+
+// Device-usable address of a host pointer when the memory is pinned / registered, nullptr otherwise.
+void* device_alias(const void* p) {
+  if (!p) return nullptr;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();  // unregistered host memory reports an error on some drivers: not pinned
+    return nullptr;
+  }
+  if ((a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeManaged) && a.devicePointer) return a.devicePointer;
+  return nullptr;
+}
+
+bool is_varint_kind(int32_t kind) {
+  return kind == TFS_KIND_INT_VAL || kind == TFS_KIND_INT64_VAL || kind == TFS_KIND_HALF_VAL || kind == TFS_KIND_UINT32_VAL ||
+         kind == TFS_KIND_UINT64_VAL;
+}
+
+// wire bytes: pinned -> read in place; pageable -> copied to the device slab
+tfs_status_t wire_for_device(tfs_ctx* ctx, const void* wire_host, uint64_t wire_bytes, const void** out) {
+  void* alias = device_alias(wire_host);
+  if (alias || wire_bytes == 0) {
+    *out = alias;
+    return TFS_OK;
+  }
+  TFS_TRY(dev_reserve(ctx, &ctx->d_stage_in, wire_bytes + 256));
+  TFS_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage_in.p, wire_host, wire_bytes, cudaMemcpyHostToDevice, ctx->stream));
+  *out = ctx->d_stage_in.p;
+  return TFS_OK;
+}
+
+}  // namespace
 }  // namespace tfs
 
 using namespace tfs;
@@ -28,31 +74,44 @@ tfs_status_t tfs_encode_host(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst
   if ((batch->n_fields && !batch->fields)) return TFS_ERR_INVALID_ARG;
   TFS_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->stage_generation++;  // the staging buffers are reused: a pending tfs_decode_host handle becomes stale
-  // 1. stage every payload array into one device slab (256-byte aligned pieces), host -> device
+  // 1. payload arrays: pinned bulk arrays are read in place by the kernels; the rest is copied to a device slab
   std::vector<tfs_field_desc_t> fields(batch->fields, batch->fields + batch->n_fields);
-  std::vector<uint64_t> at(batch->n_fields, 0);
+  std::vector<uint64_t> at(batch->n_fields, ~0ull);
   uint64_t in_bytes = 0;
   for (uint32_t i = 0; i < batch->n_fields; ++i) {
-    const uint64_t b = fields[i].n_elems * tfs_type_size(fields[i].src_type);
-    if (b && (!fields[i].data || tfs_type_size(fields[i].src_type) == 0)) return set_err(ctx, TFS_ERR_INVALID_ARG, "payload field without data or type");
-    at[i] = in_bytes;
-    in_bytes = align_up(in_bytes + b, 256);
+    const uint32_t w = tfs_type_size(fields[i].src_type);
+    const uint64_t b = fields[i].n_elems * w;
+    if (b && (!fields[i].data || w == 0)) return set_err(ctx, TFS_ERR_INVALID_ARG, "payload field without data or type");
+    if (!b) continue;
+    void* alias = is_varint_kind(fields[i].kind) ? nullptr : device_alias(fields[i].data);
+    if (alias) {
+      fields[i].data = alias;
+    } else {
+      at[i] = in_bytes;
+      in_bytes = align_up(in_bytes + b, 256);
+    }
   }
-  TFS_TRY(dev_reserve(ctx, &ctx->d_stage_in, in_bytes + 256));
-  TFS_TRY(dev_reserve(ctx, &ctx->d_stage_out, dst_capacity + 256));
+  if (in_bytes) TFS_TRY(dev_reserve(ctx, &ctx->d_stage_in, in_bytes + 256));
   uint8_t* din = static_cast<uint8_t*>(ctx->d_stage_in.p);
   for (uint32_t i = 0; i < batch->n_fields; ++i) {
+    if (at[i] == ~0ull) continue;
     const uint64_t b = fields[i].n_elems * tfs_type_size(fields[i].src_type);
-    if (b) TFS_CUDA(ctx, cudaMemcpyAsync(din + at[i], fields[i].data, b, cudaMemcpyHostToDevice, ctx->stream));
-    fields[i].data = b ? din + at[i] : nullptr;
+    TFS_CUDA(ctx, cudaMemcpyAsync(din + at[i], fields[i].data, b, cudaMemcpyHostToDevice, ctx->stream));
+    fields[i].data = din + at[i];
   }
   tfs_batch_t dev_batch = *batch;
   dev_batch.fields = fields.data();
-  // 2. encode on the device, 3. wire bytes device -> host
+  // 2. encode; the wire bytes go straight into a pinned destination, else through a device slab + D2H
   uint64_t total = 0;
-  TFS_TRY(encode_device(ctx, &dev_batch, ctx->d_stage_out.p, dst_capacity, flags, msg_off_out, msg_len_out, &total, false));
-  if (total) TFS_CUDA(ctx, cudaMemcpyAsync(dst_host, ctx->d_stage_out.p, total, cudaMemcpyDeviceToHost, ctx->stream));
-  TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  void* dst_alias = device_alias(dst_host);
+  if (dst_alias) {
+    TFS_TRY(encode_device(ctx, &dev_batch, dst_alias, dst_capacity, flags, msg_off_out, msg_len_out, &total, false));
+  } else {
+    TFS_TRY(dev_reserve(ctx, &ctx->d_stage_out, dst_capacity + 256));
+    TFS_TRY(encode_device(ctx, &dev_batch, ctx->d_stage_out.p, dst_capacity, flags, msg_off_out, msg_len_out, &total, false));
+    if (total) TFS_CUDA(ctx, cudaMemcpyAsync(dst_host, ctx->d_stage_out.p, total, cudaMemcpyDeviceToHost, ctx->stream));
+    TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
   if (total_out) *total_out = total;
   return TFS_OK;
 }
@@ -62,10 +121,10 @@ tfs_status_t tfs_decode_host(tfs_ctx_t* ctx, const void* wire_host, uint64_t wir
   if (!ctx || !out || (n_msgs && (!msg_off || !msg_len)) || (wire_bytes && !wire_host)) return TFS_ERR_INVALID_ARG;
   *out = nullptr;
   TFS_CUDA(ctx, cudaSetDevice(ctx->device));
-  TFS_TRY(dev_reserve(ctx, &ctx->d_stage_in, wire_bytes + 256));
-  if (wire_bytes) TFS_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage_in.p, wire_host, wire_bytes, cudaMemcpyHostToDevice, ctx->stream));
   const uint64_t gen = ++ctx->stage_generation;
-  tfs_status_t st = decode_scan_device(ctx, ctx->d_stage_in.p, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, out);
+  const void* wire_dev = nullptr;
+  TFS_TRY(wire_for_device(ctx, wire_host, wire_bytes, &wire_dev));
+  tfs_status_t st = decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, nullptr, 0, out);
   if (*out) decoded_mark_host_staged(*out, gen);
   return st;
 }
@@ -76,11 +135,42 @@ tfs_status_t tfs_decode_host_finish(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* po
     return set_err(ctx, TFS_ERR_INVALID_ARG, "stale handle: another *_host call reused the staging buffers since tfs_decode_host");
   const uint64_t need = decoded_pool_bytes(dec);
   if (pool_bytes < need || (need && !pool_host)) return set_err(ctx, TFS_ERR_NOMEM, "value pool is smaller than tfs_decoded_view().pool_bytes");
-  TFS_TRY(dev_reserve(ctx, &ctx->d_stage_out, need + 256));
-  TFS_TRY(decode_device(ctx, dec, ctx->d_stage_out.p, need));
-  if (need) TFS_CUDA(ctx, cudaMemcpyAsync(pool_host, ctx->d_stage_out.p, need, cudaMemcpyDeviceToHost, ctx->stream));
+  void* alias = device_alias(pool_host);
+  if (alias) {
+    TFS_TRY(decode_device(ctx, dec, alias, need));
+  } else {
+    TFS_TRY(dev_reserve(ctx, &ctx->d_stage_out, need + 256));
+    TFS_TRY(decode_device(ctx, dec, ctx->d_stage_out.p, need));
+    if (need) TFS_CUDA(ctx, cudaMemcpyAsync(pool_host, ctx->d_stage_out.p, need, cudaMemcpyDeviceToHost, ctx->stream));
+  }
   TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return TFS_OK;
+}
+
+tfs_status_t tfs_decode_host_into(tfs_ctx_t* ctx, const void* wire_host, uint64_t wire_bytes, const uint64_t* msg_off,
+                                  const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_host,
+                                  uint64_t pool_capacity, tfs_decoded_t** out) {
+  if (!ctx || !out || !pool_host || (n_msgs && (!msg_off || !msg_len)) || (wire_bytes && !wire_host)) return TFS_ERR_INVALID_ARG;
+  *out = nullptr;
+  TFS_CUDA(ctx, cudaSetDevice(ctx->device));
+  const uint64_t gen = ++ctx->stage_generation;
+  const void* wire_dev = nullptr;
+  TFS_TRY(wire_for_device(ctx, wire_host, wire_bytes, &wire_dev));
+  void* alias = device_alias(pool_host);
+  tfs_status_t st;
+  if (alias) {
+    st = decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, alias, pool_capacity, out);
+  } else {
+    TFS_TRY(dev_reserve(ctx, &ctx->d_stage_out, pool_capacity + 256));
+    st = decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, ctx->d_stage_out.p, pool_capacity, out);
+    if (*out && (st == TFS_OK || st == TFS_ERR_BATCH)) {
+      const uint64_t need = decoded_pool_bytes(*out);
+      if (need) TFS_CUDA(ctx, cudaMemcpyAsync(pool_host, ctx->d_stage_out.p, need, cudaMemcpyDeviceToHost, ctx->stream));
+      TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+  }
+  if (*out) decoded_mark_host_staged(*out, gen);
+  return st;
 }
 
 }  // extern "C"

@@ -6,6 +6,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <string>
 #include <vector>
 
 #define CK(x)                                                                  \
@@ -205,7 +206,59 @@ float time_it(F f, int reps, uint8_t* flush, size_t flush_bytes) {
   return best;
 }
 
+// host <-> device over PCIe: copy engine vs SM loads/stores vs the TMA ring on pinned (mapped) host memory
+int host_mode() {
+  const uint64_t bytes = 256ull << 20;
+  uint8_t *hsrc, *hdst, *dsrc, *ddst;
+  CK(cudaHostAlloc(&hsrc, bytes, cudaHostAllocDefault));
+  CK(cudaHostAlloc(&hdst, bytes, cudaHostAllocDefault));
+  CK(cudaMalloc(&dsrc, bytes));
+  CK(cudaMalloc(&ddst, bytes));
+  for (uint64_t i = 0; i < bytes; i += 4096) hsrc[i] = 7;
+  int sms = 0;
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+  const uint64_t n16 = bytes / 16;
+  auto rep1 = [&](const char* name, float ms, double factor) { std::printf("  -> %-52s %8.2f GB/s\n", name, factor * bytes / (ms * 1e-3) / 1e9); };
+  std::printf("host mode: %.0f MB pinned; GB/s counts payload bytes once per direction\n", bytes / 1e6);
+  rep1("cudaMemcpyAsync H2D", time_it([&] { CK(cudaMemcpyAsync(ddst, hsrc, bytes, cudaMemcpyHostToDevice)); }, 5, nullptr, 0), 1);
+  rep1("cudaMemcpyAsync D2H", time_it([&] { CK(cudaMemcpyAsync(hdst, dsrc, bytes, cudaMemcpyDeviceToHost)); }, 5, nullptr, 0), 1);
+  cudaStream_t s2;
+  CK(cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking));
+  cudaEvent_t done2;
+  CK(cudaEventCreate(&done2));
+  rep1("cudaMemcpyAsync H2D + D2H concurrently (sum)", time_it([&] {
+         CK(cudaMemcpyAsync(hdst, dsrc, bytes, cudaMemcpyDeviceToHost, s2));
+         CK(cudaEventRecord(done2, s2));
+         CK(cudaMemcpyAsync(ddst, hsrc, bytes, cudaMemcpyHostToDevice));
+         CK(cudaStreamWaitEvent(0, done2));
+       }, 5, nullptr, 0), 2);
+  rep1("k_vec<8> host->host grid 16/SM (sum both dirs)", time_it([&] { k_vec<8><<<sms * 16, 256>>>((const uint4*)hsrc, (uint4*)hdst, n16); }, 5, nullptr, 0), 2);
+  for (int per_sm : {1, 2, 4, 8}) {
+    char nm[96];
+    std::snprintf(nm, sizeof nm, "k_vec<4> host->device grid %d/SM", per_sm);
+    rep1(nm, time_it([&] { k_vec<4><<<sms * per_sm, 256>>>((const uint4*)hsrc, (uint4*)ddst, n16); }, 5, nullptr, 0), 1);
+    std::snprintf(nm, sizeof nm, "k_vec<4> device->host grid %d/SM", per_sm);
+    rep1(nm, time_it([&] { k_vec<4><<<sms * per_sm, 256>>>((const uint4*)dsrc, (uint4*)hdst, n16); }, 5, nullptr, 0), 1);
+    std::snprintf(nm, sizeof nm, "k_vec<4> host->host grid %d/SM (sum both dirs)", per_sm);
+    rep1(nm, time_it([&] { k_vec<4><<<sms * per_sm, 256>>>((const uint4*)hsrc, (uint4*)hdst, n16); }, 5, nullptr, 0), 2);
+  }
+  rep1("k_vec_tile<32K> host->host one pass (sum)", time_it([&] { k_vec_tile<32768><<<(unsigned)(bytes / 32768), 256>>>((const uint4*)hsrc, (uint4*)hdst, n16); }, 5, nullptr, 0), 2);
+  CK(cudaFuncSetAttribute(k_tma_strided<3, 32768>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * 32768));
+  rep1("k_tma_strided<3,32K> host->device 1/SM", time_it([&] { k_tma_strided<3, 32768><<<sms, 32, 3 * 32768>>>(hsrc, ddst, bytes); }, 5, nullptr, 0), 1);
+  rep1("k_tma_strided<3,32K> device->host 1/SM", time_it([&] { k_tma_strided<3, 32768><<<sms, 32, 3 * 32768>>>(dsrc, hdst, bytes); }, 5, nullptr, 0), 1);
+  rep1("k_tma_strided<3,32K> host->host 1/SM (sum)", time_it([&] { k_tma_strided<3, 32768><<<sms, 32, 3 * 32768>>>(hsrc, hdst, bytes); }, 5, nullptr, 0), 2);
+  CK(cudaDeviceSynchronize());
+  for (uint64_t i = 0; i < bytes; i += 4096)
+    if (hdst[i] != 7) {
+      std::printf("HOST COPY WRONG at %llu\n", (unsigned long long)i);
+      return 1;
+    }
+  std::printf("host ok\n");
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc > 1 && std::string(argv[1]) == "host") return host_mode();
   const uint64_t bytes = argc > 1 ? std::strtoull(argv[1], nullptr, 10) : 16ull * 38535168ull;
   uint8_t *src, *dst, *flush;
   const size_t flush_bytes = 256u << 20;

@@ -34,7 +34,52 @@ def gpu_encode_both(codec, msgs, kind, flags=0):
     dev_msgs = workloads.to_device(msgs, kind, torch.device(f"cuda:{codec.ctx.device}"))
     dev = enc.encode(dev_msgs, kind, flags).all_bytes()
     assert host == dev, "host-staged and device-resident encode differ"
+    # pinned payloads and a pinned destination: the kernels read and write host memory in place
+    pmsgs, keep = pinned_like(msgs, kind)
+    built = tfs.build_batch(pmsgs, kind)
+    pdst = torch.empty(enc.bound(built, flags) + 16, dtype=torch.uint8).pin_memory()
+    pinned = enc.encode_host(built, kind, flags, dst=pdst.numpy()).all_bytes()
+    assert host == pinned, "pageable and pinned (in place) host encode differ"
     return host
+
+
+def pinned_like(msgs, kind):
+    """The same messages with every payload array moved to pinned host memory (numpy views of torch tensors)."""
+    import copy
+    import torch
+
+    def mv(v):
+        if v is None:
+            return None
+        if isinstance(v, tfs.Payload):
+            return tfs.Payload(mv(v.data), v.src_type if v.src_type != abi.T_NONE else tfs.messages._array_info(v.data)[2], v.dst_type, v.op, v.op_param)
+        a = np.ascontiguousarray(v)
+        if a.size == 0:
+            return a
+        t = torch.empty(a.nbytes + 16, dtype=torch.uint8).pin_memory()
+        view = t.numpy()[: a.nbytes].view(a.dtype if a.dtype != np.bool_ else np.uint8)
+        view[:] = a.reshape(-1) if a.dtype != np.bool_ else a.reshape(-1).view(np.uint8)
+        keep.append(t)
+        return view.view(np.bool_) if a.dtype == np.bool_ else view
+
+    keep = []
+
+    def mv_tensor(t):
+        t2 = copy.copy(t)
+        for k in abi.SLOT_KINDS:
+            name = abi.KIND_FIELD_NAMES[k]
+            setattr(t2, name, mv(getattr(t, name)))
+        return t2
+
+    out = []
+    for m in msgs:
+        if kind == abi.MSG_TENSOR_PROTO:
+            out.append(mv_tensor(m))
+        elif kind == abi.MSG_PREDICT_REQUEST:
+            out.append(tfs.PredictRequest(m.model_spec, [(k, mv_tensor(t)) for k, t in m.inputs], list(m.output_filter)))
+        else:
+            out.append(tfs.PredictResponse([(k, mv_tensor(t)) for k, t in m.outputs], m.model_spec))
+    return out, keep
 
 
 def first_diff(a: bytes, b: bytes):
@@ -217,6 +262,16 @@ def gpu_decode_both(codec, blobs, kind, flags=0):
     d = dec.decode(dwire[3: 3 + cur] if cur else dwire[:0], offs, lens, kind, flags)
     codec.ctx.sync()
     helpers.assert_same_decoded(host_msgs, d.messages(), helpers_kind(kind), "host vs device decode")
+    # one-call forms: device pool of exactly the needed size, and pinned host buffers used in place
+    pool = torch.empty(max(16, d.pool_bytes), dtype=torch.uint8, device=dwire.device)
+    d2 = dec.decode_into(dwire[3: 3 + cur] if cur else dwire[:0], offs, lens, kind, pool, flags)
+    helpers.assert_same_decoded(host_msgs, d2.messages(), helpers_kind(kind), "two-call vs one-call decode")
+    pwire = torch.empty(max(1, cur), dtype=torch.uint8).pin_memory()
+    pwire.numpy()[:cur] = wire
+    ppool = torch.zeros(max(16, d.pool_bytes), dtype=torch.uint8).pin_memory()
+    d3 = dec.decode_host_into(pwire.numpy()[:cur], offs, lens, kind, ppool.numpy(), flags)
+    helpers.assert_same_decoded(host_msgs, d3.messages(), helpers_kind(kind), "pageable vs pinned (in place) host decode")
+    assert d2.status == d3.status == host.status
     return host.status, host_msgs
 
 
