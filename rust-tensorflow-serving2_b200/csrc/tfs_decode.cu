@@ -568,9 +568,7 @@ struct Walker {
 };
 
 template <bool FILL>
-__global__ void __launch_bounds__(128) k_walk(DecTables T) {
-  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
-  if (mi >= T.n_msgs) return;
+__device__ void walk_body(const DecTables& T, uint32_t mi) {
   Walker<FILL> wk(T, mi);
   wk.beg = T.msg_off[mi];
   wk.end = wk.beg + T.msg_len[mi];
@@ -614,14 +612,21 @@ __global__ void __launch_bounds__(128) k_walk(DecTables T) {
   }
 }
 
-// exclusive scan of `a[0..n)` in place by one 1024-thread CTA; returns the total in every thread
+template <bool FILL>
+__global__ void __launch_bounds__(128) k_walk(DecTables T) {
+  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (mi < T.n_msgs) walk_body<FILL>(T, mi);
+}
+
+// exclusive scan of `a[0..n)` in place by one CTA of NW warps; returns the total in every thread
+template <int NW>
 __device__ uint64_t cta_scan_u32(uint32_t* a, uint32_t n, uint64_t* smem) {
   uint64_t carry = 0;
-  for (uint32_t base = 0; base < n; base += 1024) {
+  for (uint32_t base = 0; base < n; base += NW * 32) {
     const uint32_t i = base + threadIdx.x;
     const uint64_t v = i < n ? a[i] : 0u;
     uint64_t total;
-    const uint64_t ex = block_exclusive_scan<uint64_t, 32>(v, smem, &total);
+    const uint64_t ex = block_exclusive_scan<uint64_t, NW>(v, smem, &total);
     if (i < n) a[i] = static_cast<uint32_t>(carry + ex);
     carry += total;
     __syncthreads();
@@ -629,14 +634,14 @@ __device__ uint64_t cta_scan_u32(uint32_t* a, uint32_t n, uint64_t* smem) {
   return carry;
 }
 
-__global__ void __launch_bounds__(1024) k_scan_counts(DecTables T) {
-  __shared__ uint64_t smem[33];
-  const uint64_t t0 = cta_scan_u32(T.cnt_tensors, T.n_msgs, smem);
-  const uint64_t t1 = cta_scan_u32(T.cnt_filters, T.n_msgs, smem);
-  const uint64_t t2 = cta_scan_u32(T.cnt_spans, T.n_msgs, smem);
-  const uint64_t t3 = cta_scan_u32(T.cnt_strbytes, T.n_msgs, smem);
-  const uint64_t t4 = cta_scan_u32(T.cnt_vtiles, T.n_msgs, smem);
-  const uint64_t t5 = cta_scan_u32(T.cnt_ctiles, T.n_msgs, smem);
+template <int NW>
+__device__ void scan_counts_body(const DecTables& T, uint64_t* smem) {
+  const uint64_t t0 = cta_scan_u32<NW>(T.cnt_tensors, T.n_msgs, smem);
+  const uint64_t t1 = cta_scan_u32<NW>(T.cnt_filters, T.n_msgs, smem);
+  const uint64_t t2 = cta_scan_u32<NW>(T.cnt_spans, T.n_msgs, smem);
+  const uint64_t t3 = cta_scan_u32<NW>(T.cnt_strbytes, T.n_msgs, smem);
+  const uint64_t t4 = cta_scan_u32<NW>(T.cnt_vtiles, T.n_msgs, smem);
+  const uint64_t t5 = cta_scan_u32<NW>(T.cnt_ctiles, T.n_msgs, smem);
   if (threadIdx.x == 0) {
     T.totals[TOT_TENSORS] = t0;
     T.totals[TOT_FILTERS] = t1;
@@ -648,6 +653,19 @@ __global__ void __launch_bounds__(1024) k_scan_counts(DecTables T) {
     T.totals[TOT_FAILED] = 0;
     // TOT_GENERIC was accumulated by the walk (the host zeroes the totals before pass 1)
   }
+}
+__global__ void __launch_bounds__(1024) k_scan_counts(DecTables T) {
+  __shared__ uint64_t smem[33];
+  scan_counts_body<32>(T, smem);
+}
+
+// Small batches: pass-1 walk and the scans of its counters in ONE single-CTA launch
+constexpr uint32_t kSmallBatch = 256;
+__global__ void __launch_bounds__(kSmallBatch) k_walk_count_small(DecTables T) {
+  __shared__ uint64_t smem[kSmallBatch / 32 + 1];
+  if (threadIdx.x < T.n_msgs) walk_body<false>(T, threadIdx.x);
+  __syncthreads();
+  scan_counts_body<kSmallBatch / 32>(T, smem);
 }
 
 // =====================================================================================================
@@ -798,9 +816,7 @@ __device__ __forceinline__ uint64_t slot_pool_bytes(uint32_t slot, int32_t type,
 
 // K6e: per message, in wire order: element base of every span inside its (tensor, slot) vector, element
 // totals per slot, final status (walk errors + varint errors found by K4a), pool bytes per tensor.
-__global__ void __launch_bounds__(128) k_dec_finalize(DecTables T) {
-  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
-  if (mi >= T.n_msgs) return;
+__device__ void finalize_body(const DecTables& T, uint32_t mi) {
   tfs_msg_out_t& mo = T.msgs[mi];
   const unsigned long long e = T.err[mi];
   if (mo.status == TFS_OK && e != ~0ull) {
@@ -834,15 +850,20 @@ __global__ void __launch_bounds__(128) k_dec_finalize(DecTables T) {
   }
 }
 
-// exclusive scan of the per-tensor pool bytes, then absolute slot offsets. Single CTA.
-__global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_tensors, uint64_t pool_capacity) {
-  __shared__ uint64_t smem[33];
+__global__ void __launch_bounds__(128) k_dec_finalize(DecTables T) {
+  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (mi < T.n_msgs) finalize_body(T, mi);
+}
+
+// exclusive scan of the per-tensor pool bytes, then absolute slot offsets. One CTA of NW warps.
+template <int NW>
+__device__ void pool_layout_body(const DecTables& T, uint32_t n_tensors, uint64_t pool_capacity, uint64_t* smem) {
   uint64_t carry = 0;
-  for (uint32_t base = 0; base < n_tensors; base += 1024) {
+  for (uint32_t base = 0; base < n_tensors; base += NW * 32) {
     const uint32_t i = base + threadIdx.x;
     const uint64_t v = i < n_tensors ? T.tensor_pool[i] : 0ull;
     uint64_t total;
-    const uint64_t ex = block_exclusive_scan<uint64_t, 32>(v, smem, &total);
+    const uint64_t ex = block_exclusive_scan<uint64_t, NW>(v, smem, &total);
     if (i < n_tensors) {
       const uint64_t b = carry + ex;
       for (uint32_t sl = 0; sl < TFS_N_SLOTS; ++sl) T.tensors[i].dst_off[sl] += b;
@@ -854,6 +875,23 @@ __global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_te
     T.totals[TOT_POOL] = carry;
     T.totals[TOT_OVERFLOW] = carry > pool_capacity ? 1ull : 0ull;  // gates the value kernels of a one-call decode
   }
+}
+__global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_tensors, uint64_t pool_capacity) {
+  __shared__ uint64_t smem[33];
+  pool_layout_body<32>(T, n_tensors, pool_capacity, smem);
+}
+
+// Small batches: (pass-2 walk when no varint body has to be counted first,) finalize and pool layout in ONE
+// single-CTA launch
+__global__ void __launch_bounds__(kSmallBatch) k_fill_finalize_small(DecTables T, uint32_t n_tensors, uint64_t pool_capacity, int do_walk) {
+  __shared__ uint64_t smem[kSmallBatch / 32 + 1];
+  const uint32_t mi = threadIdx.x;
+  if (mi < T.n_msgs) {
+    if (do_walk) walk_body<true>(T, mi);
+    finalize_body(T, mi);  // reads only what this thread's own walk wrote (and the counted varint spans)
+  }
+  __syncthreads();
+  pool_layout_body<kSmallBatch / 32>(T, n_tensors, pool_capacity, smem);
 }
 
 // at decode time: bind every copy-class span to its place in the caller's pool
@@ -1072,12 +1110,16 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   T.err = reinterpret_cast<unsigned long long*>(d1 + o_err);
 
   const uint32_t mblocks = (n_msgs + 127) / 128;
-  if (n_msgs) {
+  const bool small = n_msgs <= kSmallBatch;
+  if (small) {
+    k_walk_count_small<<<1, kSmallBatch, 0, ctx->stream>>>(T);
+    ctx->launches++;
+  } else {
     k_walk<false><<<mblocks, 128, 0, ctx->stream>>>(T);
     ctx->launches++;
+    k_scan_counts<<<1, 1024, 0, ctx->stream>>>(T);
+    ctx->launches++;
   }
-  k_scan_counts<<<1, 1024, 0, ctx->stream>>>(T);
-  ctx->launches++;
   DEC_CUDA(cudaGetLastError());
   DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, kTotalsBytes));
   DEC_CUDA(cudaMemcpyAsync(ctx->h_down, T.totals, kTotalsBytes, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1108,7 +1150,8 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   T.segs = reinterpret_cast<CopySeg*>(d2 + p_seg);
   T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);
   if (n_tensors) DEC_CUDA(cudaMemsetAsync(T.tensors, 0, sizeof(tfs_tensor_out_t) * n_tensors, ctx->stream));
-  if (n_msgs) {
+  const bool fuse_walk = small && n_vt == 0;  // nothing has to run between the pass-2 walk and finalize
+  if (n_msgs && !fuse_walk) {
     k_walk<true><<<mblocks, 128, 0, ctx->stream>>>(T);
     ctx->launches++;
   }
@@ -1122,12 +1165,15 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     k_span_scan<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);
     ctx->launches++;
   }
-  if (n_msgs) {
+  if (small) {
+    k_fill_finalize_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_dev ? pool_capacity : ~0ull, fuse_walk ? 1 : 0);
+    ctx->launches++;
+  } else {
     k_dec_finalize<<<mblocks, 128, 0, ctx->stream>>>(T);
     ctx->launches++;
+    k_pool_layout<<<1, 1024, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_dev ? pool_capacity : ~0ull);
+    ctx->launches++;
   }
-  k_pool_layout<<<1, 1024, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_dev ? pool_capacity : ~0ull);
-  ctx->launches++;
   DEC_CUDA(cudaGetLastError());
   // one-call decode: the value kernels follow at once, gated on the device by "the pool is large enough"
   if (pool_dev) DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), T.totals + TOT_OVERFLOW));

@@ -300,9 +300,7 @@ __device__ void emit_message(Sink& s, const EncTables& T, uint32_t mi, OnBody on
 }
 
 // K6a: nested lengths bottom-up (once), then the message length and the offset of its largest bulk body.
-__global__ void __launch_bounds__(128) k_msg_layout(EncTables T) {
-  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
-  if (mi >= T.n_msgs) return;
+__device__ void msg_layout_body(const EncTables& T, uint32_t mi) {
   const EncMsg& m = T.msgs[mi];
   for (uint32_t i = 0; i < m.n_tensors; ++i) {
     const uint32_t ti = m.first_tensor + i;
@@ -328,12 +326,12 @@ __global__ void __launch_bounds__(128) k_msg_layout(EncTables T) {
   T.msg_pay_off[mi] = best_off;
 }
 
-// K6b: exclusive scan of the message slots -> msg_off; total and overflow flag.  Single CTA.
-__global__ void __launch_bounds__(1024) k_msg_scan(EncTables T, uint32_t flags, uint32_t dst_skew, uint64_t dst_capacity) {
-  __shared__ uint64_t smem[33];
+// K6b: exclusive scan of the message slots -> msg_off; total and overflow flag.  One CTA of NW warps.
+template <int NW>
+__device__ void msg_scan_body(const EncTables& T, uint32_t flags, uint32_t dst_skew, uint64_t dst_capacity, uint64_t* smem) {
   const uint32_t prefix = (flags & TFS_F_GRPC_PREFIX) ? 5u : 0u;
   uint64_t carry = 0;
-  for (uint32_t base = 0; base < T.n_msgs; base += 1024) {
+  for (uint32_t base = 0; base < T.n_msgs; base += NW * 32) {
     const uint32_t mi = base + threadIdx.x;
     uint64_t slot = 0, pad = 0;
     if (mi < T.n_msgs) {
@@ -346,7 +344,7 @@ __global__ void __launch_bounds__(1024) k_msg_scan(EncTables T, uint32_t flags, 
       }
     }
     uint64_t total;
-    const uint64_t excl = block_exclusive_scan<uint64_t, 32>(slot, smem, &total);
+    const uint64_t excl = block_exclusive_scan<uint64_t, NW>(slot, smem, &total);
     if (mi < T.n_msgs) T.msg_off[mi] = carry + excl + pad;
     carry += total;
     __syncthreads();
@@ -358,9 +356,7 @@ __global__ void __launch_bounds__(1024) k_msg_scan(EncTables T, uint32_t flags, 
 }
 
 // K6c: write every framing byte, record where each payload body goes.
-__global__ void __launch_bounds__(128) k_write_headers(EncTables T, uint8_t* __restrict__ dst, uint32_t flags) {
-  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
-  if (mi >= T.n_msgs || T.result[1] != 0) return;
+__device__ void write_headers_body(const EncTables& T, uint32_t mi, uint8_t* __restrict__ dst, uint32_t flags) {
   ByteSink s{dst, T.msg_off[mi]};
   if (flags & TFS_F_GRPC_PREFIX) {  // tonic encode_client: 0x00, u32 big-endian length
     const uint32_t l = static_cast<uint32_t>(T.msg_len[mi]);
@@ -375,6 +371,33 @@ __global__ void __launch_bounds__(128) k_write_headers(EncTables T, uint8_t* __r
     f.dst_off = off;
     if (!f.is_varint) T.segs[f.first_tile].dst = dst + off;
   });
+}
+
+__global__ void __launch_bounds__(128) k_msg_layout(EncTables T) {
+  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (mi < T.n_msgs) msg_layout_body(T, mi);
+}
+__global__ void __launch_bounds__(1024) k_msg_scan(EncTables T, uint32_t flags, uint32_t dst_skew, uint64_t dst_capacity) {
+  __shared__ uint64_t smem[33];
+  msg_scan_body<32>(T, flags, dst_skew, dst_capacity, smem);
+}
+__global__ void __launch_bounds__(128) k_write_headers(EncTables T, uint8_t* __restrict__ dst, uint32_t flags) {
+  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (mi >= T.n_msgs || T.result[1] != 0) return;
+  write_headers_body(T, mi, dst, flags);
+}
+
+// Small batches (<= kSmallBatch messages): layout, scan and framing bytes in ONE single-CTA launch
+constexpr uint32_t kSmallBatch = 256;
+__global__ void __launch_bounds__(kSmallBatch) k_frame_small(EncTables T, uint8_t* __restrict__ dst, uint32_t flags, uint32_t dst_skew,
+                                                             uint64_t dst_capacity, int write) {
+  __shared__ uint64_t smem[kSmallBatch / 32 + 1];
+  const uint32_t mi = threadIdx.x;
+  if (mi < T.n_msgs) msg_layout_body(T, mi);
+  __syncthreads();
+  msg_scan_body<kSmallBatch / 32>(T, flags, dst_skew, dst_capacity, smem);
+  __syncthreads();  // result[1] and msg_off[] were written by this CTA
+  if (write && mi < T.n_msgs && T.result[1] == 0) write_headers_body(T, mi, dst, flags);
 }
 
 // =====================================================================================================
@@ -686,8 +709,9 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   return TFS_OK;
 }
 
-// size + layout: everything that replaces prost's encoded_len
-tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_t dst_skew, uint64_t dst_capacity) {
+// size + layout (+ framing bytes when `dst` is given): everything that replaces prost's encoded_len / the
+// non-payload part of encode_raw
+tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_t dst_skew, uint64_t dst_capacity, uint8_t* dst) {
   const EncTables& T = u.T;
   if (T.n_vtiles) {
     {
@@ -699,12 +723,19 @@ tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_
     k_field_scan<<<(T.n_vfields + warps_per_block - 1) / warps_per_block, 256, 0, ctx->stream>>>(T);
     ctx->launches++;
   }
-  if (T.n_msgs) {
+  if (T.n_msgs <= kSmallBatch) {
+    k_frame_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, dst, flags, dst_skew, dst_capacity, dst != nullptr);
+    ctx->launches++;
+  } else {
     k_msg_layout<<<(T.n_msgs + 127) / 128, 128, 0, ctx->stream>>>(T);
     ctx->launches++;
+    k_msg_scan<<<1, 1024, 0, ctx->stream>>>(T, flags, dst_skew, dst_capacity);
+    ctx->launches++;
+    if (dst) {
+      k_write_headers<<<(T.n_msgs + 127) / 128, 128, 0, ctx->stream>>>(T, dst, flags);
+      ctx->launches++;
+    }
   }
-  k_msg_scan<<<1, 1024, 0, ctx->stream>>>(T, flags, dst_skew, dst_capacity);
-  ctx->launches++;
   TFS_CUDA(ctx, cudaGetLastError());
   return TFS_OK;
 }
@@ -740,14 +771,11 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
   Uploaded u;
   TFS_TRY(upload(ctx, c, &u));
   const uint32_t dst_skew = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(dst_dev) & 15u);
-  TFS_TRY(run_sizing(ctx, u, size_only ? 0u : flags, dst_skew, size_only ? ~0ull : dst_capacity));
+  TFS_TRY(run_sizing(ctx, u, size_only ? 0u : flags, dst_skew, size_only ? ~0ull : dst_capacity,
+                     size_only ? nullptr : static_cast<uint8_t*>(dst_dev)));
   if (!size_only) {
     const EncTables& T = u.T;
     uint8_t* dst = static_cast<uint8_t*>(dst_dev);
-    if (T.n_msgs) {
-      k_write_headers<<<(T.n_msgs + 127) / 128, 128, 0, ctx->stream>>>(T, dst, flags);
-      ctx->launches++;
-    }
     if (T.n_vtiles) {
       {
         ProfScope prof(ctx, PK_VARINT_SCATTER);
