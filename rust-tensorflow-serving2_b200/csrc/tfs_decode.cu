@@ -13,6 +13,7 @@
 #include <new>
 
 #include "tfs_device.cuh"
+#include "tfs_varint_dec.cuh"
 
 struct tfs_decoded {
   uint64_t generation = 0;
@@ -668,95 +669,6 @@ __global__ void __launch_bounds__(kSmallBatch) k_walk_count_small(DecTables T) {
   scan_counts_body<kSmallBatch / 32>(T, smem);
 }
 
-// =====================================================================================================
-// K4a: terminators per 4 KiB tile of a packed varint body (a terminator is a byte with its MSB clear),
-// plus detection of >10-byte varints: 10 consecutive continuation bytes inside the body.
-// Tiles are cut on 16-byte boundaries of the absolute address so every thread's 16-byte load is aligned.
-// =====================================================================================================
-struct TileRef {
-  uint64_t span_abs0;  // absolute address of the first byte of the span
-  uint64_t span_end;   // absolute address one past its last byte
-  uint64_t tile_abs;   // absolute (16-byte aligned) address of the tile's first byte
-  uint32_t span;
-  uint32_t msg;
-};
-
-__device__ __forceinline__ TileRef locate_vtile(const DecTables& T, uint32_t n_spans, uint64_t tile) {
-  const uint32_t si = find_segment(T.span_vtile0, n_spans, static_cast<uint32_t>(tile));
-  const DecSpan& s = T.spans[si];
-  TileRef r;
-  r.span = si;
-  r.msg = s.msg;
-  r.span_abs0 = reinterpret_cast<uintptr_t>(T.wire) + s.wire_off;
-  r.span_end = r.span_abs0 + s.len;
-  r.tile_abs = (r.span_abs0 & ~static_cast<uint64_t>(15)) + (tile - T.span_vtile0[si]) * kDecTileBytes;
-  return r;
-}
-
-// 16 bytes of the tile owned by this thread: continuation mask and validity mask (bit j = byte j)
-__device__ __forceinline__ void chunk_masks(uint64_t chunk_abs, uint64_t span_abs0, uint64_t span_end, uint4* data,
-                                            uint32_t* cont, uint32_t* valid) {
-  if (chunk_abs + 16 <= span_abs0 || chunk_abs >= span_end) {
-    *data = make_uint4(0, 0, 0, 0);
-    *cont = 0;
-    *valid = 0;
-    return;
-  }
-  const uint4 d = ld_stream16(reinterpret_cast<const void*>(chunk_abs));
-  *data = d;
-  // MSB of each byte -> one bit per byte
-  auto msb4 = [](uint32_t x) { return ((x >> 7) & 1u) | ((x >> 14) & 2u) | ((x >> 21) & 4u) | ((x >> 28) & 8u); };
-  const uint32_t m = msb4(d.x) | (msb4(d.y) << 4) | (msb4(d.z) << 8) | (msb4(d.w) << 12);
-  uint32_t v = 0xFFFFu;
-  if (chunk_abs < span_abs0) v &= 0xFFFFu << (span_abs0 - chunk_abs);
-  if (chunk_abs + 16 > span_end) v &= 0xFFFFu >> (chunk_abs + 16 - span_end);
-  *valid = v & 0xFFFFu;
-  *cont = m & *valid;
-}
-
-__global__ void __launch_bounds__(kDecThreads) k_varint_count(DecTables T, uint32_t n_spans, uint64_t n_tiles) {
-  __shared__ TileRef s_ref;
-  __shared__ uint32_t warp_cnt[kDecThreads / 32];
-  for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    __syncthreads();
-    if (threadIdx.x == 0) s_ref = locate_vtile(T, n_spans, tile);
-    __syncthreads();
-    const TileRef r = s_ref;
-    const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 16ull;
-    uint4 d;
-    uint32_t cont, valid;
-    chunk_masks(chunk_abs, r.span_abs0, r.span_end, &d, &cont, &valid);
-    const uint32_t term = ~cont & valid;
-    uint32_t cnt = __popc(term);
-    // continuation mask of the previous 16 bytes (previous lane, or a re-load across warp / tile edges)
-    uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, cont, 1);
-    if (lane_id() == 0) {
-      uint4 pd;
-      uint32_t pv;
-      chunk_masks(chunk_abs - 16, r.span_abs0, r.span_end, &pd, &prev, &pv);
-    }
-    uint32_t x = (cont << 16) | prev;  // bit i..i+9 all set <=> ten continuation bytes in a row
-    x &= x >> 1;
-    x &= x >> 2;
-    x &= x >> 4;
-    x &= x >> 2;
-    if (x) {
-      const uint64_t at = chunk_abs > r.span_abs0 ? chunk_abs : r.span_abs0;
-      const uint64_t off = at - reinterpret_cast<uintptr_t>(T.wire) - T.msg_off[r.msg];
-      atomicMin(&T.err[r.msg], (static_cast<unsigned long long>(off) << 8) | TFS_ERR_INVALID_VARINT);
-    }
-    cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
-    if (lane_id() == 0) warp_cnt[warp_id()] = cnt;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t t = 0;
-#pragma unroll
-      for (int i = 0; i < kDecThreads / 32; ++i) t += warp_cnt[i];
-      T.tile_count[tile] = t;
-    }
-  }
-}
-
 // K4b: per varint span, exclusive scan of its tile counts (one warp per span) -> tile_base, n_elems
 __global__ void __launch_bounds__(256) k_span_scan(DecTables T, uint32_t n_spans, uint64_t n_vtiles) {
   const uint32_t si = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -926,91 +838,6 @@ __global__ void __launch_bounds__(256) k_dec_bind(DecTables T, uint32_t n_spans,
 }
 
 // =====================================================================================================
-// K4c: gather.  Every thread owns 16 wire bytes; each terminator in them ends one value, which is
-// reassembled by walking back over at most 9 continuation bytes (shared memory, 16-byte halo).
-// The value index = span element base + tile base + block-exclusive count of terminators.
-// =====================================================================================================
-struct GatherRef {
-  TileRef r;
-  uint8_t* dst;        // pool address of element 0 of this tile
-  int32_t dst_type;
-  int32_t half_kind;   // 19 = f16, 14 = bf16 (only with dst_type F32 on the half_val slot)
-  uint32_t live;
-};
-
-__device__ __forceinline__ void store_value(uint8_t* dst, uint64_t idx, uint64_t v, int32_t type, int32_t half_kind) {
-  switch (type) {
-    case TFS_T_I32: case TFS_T_U32: reinterpret_cast<uint32_t*>(dst)[idx] = static_cast<uint32_t>(v); break;  // `as i32` truncates
-    case TFS_T_I64: case TFS_T_U64: reinterpret_cast<uint64_t*>(dst)[idx] = v; break;
-    case TFS_T_BOOL: dst[idx] = v != 0; break;
-    case TFS_T_F32: {
-      const uint32_t h = static_cast<uint32_t>(v) & 0xFFFFu;
-      reinterpret_cast<float*>(dst)[idx] = half_kind == 19 ? f16_bits_to_f32(h) : bf16_bits_to_f32(h);
-      break;
-    }
-    default: break;
-  }
-}
-
-__global__ void __launch_bounds__(kDecThreads) k_varint_gather(DecTables T, uint32_t n_spans, uint64_t n_tiles, uint8_t* pool,
-                                                              const uint64_t* __restrict__ gate) {
-  __shared__ __align__(16) uint8_t sm[16 + kDecTileBytes];
-  if (gate && *gate != 0) return;  // the pool of a one-call decode turned out to be too small
-  __shared__ GatherRef s_ref;
-  __shared__ uint32_t scan_smem[kDecThreads / 32 + 1];
-  for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      GatherRef g;
-      g.r = locate_vtile(T, n_spans, tile);
-      const DecSpan& s = T.spans[g.r.span];
-      const tfs_tensor_out_t& t = T.tensors[s.tensor];
-      g.dst_type = t.dst_type[s.slot];
-      g.half_kind = t.dtype;
-      g.live = T.msgs[s.msg].status == TFS_OK;
-      g.dst = pool + t.dst_off[s.slot] + (s.elem_base + T.tile_base[tile]) * type_size_dev(g.dst_type);
-      s_ref = g;
-    }
-    __syncthreads();
-    const GatherRef g = s_ref;
-    if (!g.live) continue;
-    const TileRef& r = g.r;
-    const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 16ull;
-    uint4 d;
-    uint32_t cont, valid;
-    chunk_masks(chunk_abs, r.span_abs0, r.span_end, &d, &cont, &valid);
-    *reinterpret_cast<uint4*>(sm + 16 + threadIdx.x * 16) = d;
-    if (threadIdx.x == 0) {
-      uint4 h;
-      uint32_t hc, hv;
-      chunk_masks(r.tile_abs - 16, r.span_abs0, r.span_end, &h, &hc, &hv);
-      *reinterpret_cast<uint4*>(sm) = h;
-    }
-    uint32_t term = ~cont & valid;
-    uint32_t total;
-    uint32_t idx = block_exclusive_scan<uint32_t, kDecThreads / 32>(__popc(term), scan_smem, &total);
-    // first byte of the span in tile coordinates (never walk back across it)
-    const int32_t lo = r.span_abs0 > r.tile_abs ? static_cast<int32_t>(r.span_abs0 - r.tile_abs) : -16;
-    while (term) {
-      const int32_t j = __ffs(term) - 1;
-      term &= term - 1;
-      const int32_t p = static_cast<int32_t>(threadIdx.x) * 16 + j;
-      uint64_t v = sm[16 + p];
-#pragma unroll 1
-      for (int32_t k = 1; k <= 9; ++k) {
-        const int32_t q = p - k;
-        if (q < lo) break;
-        const uint8_t b = sm[16 + q];
-        if (b < 0x80) break;
-        v = (v << 7) | (b & 0x7Fu);
-      }
-      store_value(g.dst, idx, v, g.dst_type, g.half_kind);
-      ++idx;
-    }
-  }
-}
-
-// =====================================================================================================
 // host orchestration
 // =====================================================================================================
 size_t carve(size_t* cur, size_t bytes, size_t align = 64) {
@@ -1028,10 +855,9 @@ tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const 
     ctx->launches++;
   }
   if (n_vt) {
-    const uint64_t cap = static_cast<uint64_t>(ctx->sm_count) * 8;
     {
       ProfScope prof(ctx, PK_VARINT_GATHER);
-      k_varint_gather<<<static_cast<uint32_t>(n_vt < cap ? n_vt : cap), kDecThreads, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt, pool, gate);
+      k_varint_gather<<<static_cast<uint32_t>(n_vt), kDecThreads, 0, ctx->stream>>>(T, pool, gate);
     }
     ctx->launches++;
   }
@@ -1135,7 +961,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
                p_str = carve(&cur, n_str);
   const size_t res2_bytes = cur;
   const size_t p_spn = carve(&cur, sizeof(DecSpan) * n_spans), p_sv = carve(&cur, 4 * (n_spans + 1)),
-               p_sc = carve(&cur, 4 * (n_spans + 1)), p_tc = carve(&cur, 4 * n_vt), p_tb = carve(&cur, 8 * n_vt),
+               p_sc = carve(&cur, 4 * (n_spans + 1)), p_tc = carve(&cur, 4 * n_vt), p_ts = carve(&cur, 4 * n_vt), p_tb = carve(&cur, 8 * n_vt),
                p_seg = carve(&cur, sizeof(CopySeg) * n_spans), p_tp = carve(&cur, 8 * n_tensors);
   DEC_TRY(dev_reserve(ctx, &ctx->d_dec2, cur + 64));
   uint8_t* d2 = static_cast<uint8_t*>(ctx->d_dec2.p);
@@ -1146,6 +972,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   T.span_vtile0 = reinterpret_cast<uint32_t*>(d2 + p_sv);
   T.span_ctile0 = reinterpret_cast<uint32_t*>(d2 + p_sc);
   T.tile_count = reinterpret_cast<uint32_t*>(d2 + p_tc);
+  T.tile_span = reinterpret_cast<uint32_t*>(d2 + p_ts);
   T.tile_base = reinterpret_cast<uint64_t*>(d2 + p_tb);
   T.segs = reinterpret_cast<CopySeg*>(d2 + p_seg);
   T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);
@@ -1156,10 +983,12 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     ctx->launches++;
   }
   if (n_vt) {
-    const uint64_t cap = static_cast<uint64_t>(ctx->sm_count) * 8;
+    DEC_CUDA(cudaMemsetAsync(T.tile_count, 0, 4 * n_vt, ctx->stream));
+    k_dtile_map<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), static_cast<uint32_t>(n_vt));
+    ctx->launches++;
     {
       ProfScope prof(ctx, PK_VARINT_COUNT);
-      k_varint_count<<<static_cast<uint32_t>(n_vt < cap ? n_vt : cap), kDecThreads, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);
+      k_varint_count<<<static_cast<uint32_t>(n_vt), kDecThreads, 0, ctx->stream>>>(T);
     }
     ctx->launches++;
     k_span_scan<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);

@@ -13,15 +13,19 @@ __device__ __forceinline__ uint32_t varint_len(uint64_t v) { return (70u - stati
 __device__ __forceinline__ uint32_t key_len(int32_t field_number) { return field_number < 16 ? 1u : 2u; }
 
 // ---- 16-bit float casts: round-to-nearest-even in hardware, NaN -> quiet NaN keeping sign + top payload ----
+// (written as selects, not branches: a branch per element stops the compiler from batching the loads of an
+// unrolled loop)
 __device__ __forceinline__ uint32_t f32_to_f16_bits(float f) {
-  uint32_t x = __float_as_uint(f);
-  if ((x & 0x7FFFFFFFu) > 0x7F800000u) return ((x >> 16) & 0x8000u) | 0x7E00u | ((x >> 13) & 0x01FFu);
-  return static_cast<uint32_t>(__half_as_ushort(__float2half_rn(f)));
+  const uint32_t x = __float_as_uint(f);
+  const uint32_t nan_bits = ((x >> 16) & 0x8000u) | 0x7E00u | ((x >> 13) & 0x01FFu);
+  const uint32_t cvt = static_cast<uint32_t>(__half_as_ushort(__float2half_rn(f)));
+  return (x & 0x7FFFFFFFu) > 0x7F800000u ? nan_bits : cvt;
 }
 __device__ __forceinline__ uint32_t f32_to_bf16_bits(float f) {
-  uint32_t x = __float_as_uint(f);
-  if ((x & 0x7FFFFFFFu) > 0x7F800000u) return (x >> 16) | 0x0040u;
-  return static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(f)));
+  const uint32_t x = __float_as_uint(f);
+  const uint32_t nan_bits = (x >> 16) | 0x0040u;
+  const uint32_t cvt = static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(f)));
+  return (x & 0x7FFFFFFFu) > 0x7F800000u ? nan_bits : cvt;
 }
 __device__ __forceinline__ float f16_bits_to_f32(uint32_t h) { return __half2float(__ushort_as_half(static_cast<unsigned short>(h))); }
 __device__ __forceinline__ float bf16_bits_to_f32(uint32_t h) { return __uint_as_float(h << 16); }

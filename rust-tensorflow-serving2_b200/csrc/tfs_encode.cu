@@ -12,130 +12,11 @@
 #include <cstring>
 
 #include "tfs_device.cuh"
+#include "tfs_varint_enc.cuh"
 
 namespace tfs {
 
 namespace {
-
-// =====================================================================================================
-// K1 / K3: one CTA = one tile of 2048 elements = 8 warps x (8 rows x 32 lanes).
-// Row r of warp w holds elements tile*2048 + w*256 + r*32 + lane: every load is a fully coalesced
-// warp-wide access.  Lengths come from clz; the in-row prefix comes from ballots over the 4 bits of the
-// length (popc of the ballot below the lane), so no shuffle network traffic at all.
-// =====================================================================================================
-template <int MODE>
-__device__ __forceinline__ void load_rows(const EncField& f, uint64_t elem0, uint64_t (&v)[kVarintRows], uint32_t (&len)[kVarintRows]) {
-#pragma unroll
-  for (int r = 0; r < kVarintRows; ++r) {
-    uint64_t e = elem0 + static_cast<uint64_t>(r) * 32u + lane_id();
-    bool ok = e < f.n_elems;
-    v[r] = ok ? load_varint_value<MODE>(f.src, e) : 0ull;
-    len[r] = ok ? varint_len(v[r]) : 0u;
-  }
-}
-
-template <int MODE, bool SCATTER>
-__device__ __forceinline__ void varint_tile(const EncTables& T, const EncField& f, uint32_t tile, uint32_t tile_in_field,
-                                            uint8_t* __restrict__ dst_base, uint8_t* stage, uint32_t* warp_tot) {
-  const uint64_t elem0 = static_cast<uint64_t>(tile_in_field) * kVarintTile + warp_id() * (kVarintRows * 32u);
-  uint64_t v[kVarintRows];
-  uint32_t len[kVarintRows];
-  load_rows<MODE>(f, elem0, v, len);
-
-  if constexpr (!SCATTER) {
-    uint32_t s = 0;
-#pragma unroll
-    for (int r = 0; r < kVarintRows; ++r) s += len[r];
-    s = __reduce_add_sync(0xFFFFFFFFu, s);
-    if (lane_id() == 0) warp_tot[warp_id()] = s;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      uint32_t t = 0;
-#pragma unroll
-      for (int w = 0; w < kVarintThreads / 32; ++w) t += warp_tot[w];
-      T.tile_bytes[tile] = t;
-    }
-    return;
-  } else {
-    const uint32_t lt = (1u << lane_id()) - 1u;
-    uint32_t off[kVarintRows];
-    uint32_t run = 0;
-#pragma unroll
-    for (int r = 0; r < kVarintRows; ++r) {
-      uint32_t b0 = __ballot_sync(0xFFFFFFFFu, len[r] & 1u);
-      uint32_t b1 = __ballot_sync(0xFFFFFFFFu, len[r] & 2u);
-      uint32_t b2 = __ballot_sync(0xFFFFFFFFu, len[r] & 4u);
-      uint32_t b3 = __ballot_sync(0xFFFFFFFFu, len[r] & 8u);
-      off[r] = run + __popc(b0 & lt) + 2u * __popc(b1 & lt) + 4u * __popc(b2 & lt) + 8u * __popc(b3 & lt);
-      run += __popc(b0) + 2u * __popc(b1) + 4u * __popc(b2) + 8u * __popc(b3);
-    }
-    if (lane_id() == 0) warp_tot[warp_id()] = run;
-    __syncthreads();
-    uint32_t wbase = 0, total = 0;
-#pragma unroll
-    for (int w = 0; w < kVarintThreads / 32; ++w) {
-      uint32_t t = warp_tot[w];
-      if (w < static_cast<int>(warp_id())) wbase += t;
-      total += t;
-    }
-    uint8_t* g = dst_base + f.dst_off + T.tile_off[tile];
-    const uint32_t skew = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(g) & 15u);
-    // varint bytes into the CTA's staging window, positioned so that smem offset == global address mod 16
-#pragma unroll
-    for (int r = 0; r < kVarintRows; ++r) {
-      if (len[r]) {
-        uint8_t* p = stage + skew + wbase + off[r];
-        uint64_t x = v[r];
-        while (x >= 0x80) {
-          *p++ = static_cast<uint8_t>((x & 0x7F) | 0x80);
-          x >>= 7;
-        }
-        *p = static_cast<uint8_t>(x);
-      }
-    }
-    __syncthreads();
-    // flush: whole 16-byte words with vector stores, the ragged head / tail bytes one by one (a
-    // neighbouring tile owns the other bytes of those words and writes only its own)
-    uint8_t* ga = g - skew;
-    const uint32_t end = skew + total;
-    const uint32_t nchunks = (end + 15u) >> 4;
-    for (uint32_t c = threadIdx.x; c < nchunks; c += kVarintThreads) {
-      const uint32_t lo = c << 4, hi = lo + 16u;
-      if (lo >= skew && hi <= end) {
-        *reinterpret_cast<uint4*>(ga + lo) = *reinterpret_cast<const uint4*>(stage + lo);
-      } else {
-        const uint32_t b0 = lo > skew ? lo : skew, b1 = hi < end ? hi : end;
-        for (uint32_t b = b0; b < b1; ++b) ga[b] = stage[b];
-      }
-    }
-  }
-}
-
-template <bool SCATTER>
-__global__ void __launch_bounds__(kVarintThreads) k_varint_tiles(EncTables T, uint8_t* __restrict__ dst_base) {
-  __shared__ __align__(16) uint8_t stage[SCATTER ? (16 + kVarintTile * kVarintMaxLen + 16) : 16];
-  __shared__ uint32_t warp_tot[kVarintThreads / 32];
-  __shared__ uint32_t s_vf;
-  if (SCATTER && T.result[1] != 0) return;  // dst too small: nothing may be written
-  const uint32_t tile = blockIdx.x;
-  if (threadIdx.x == 0) s_vf = find_segment(T.vfield_first_tile, T.n_vfields, tile);
-  __syncthreads();
-  const uint32_t vf = s_vf;
-  const EncField f = T.fields[T.vfield_index[vf]];
-  const uint32_t tif = tile - T.vfield_first_tile[vf];
-  switch (f.mode) {
-    case VM_I64: varint_tile<VM_I64, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
-    case VM_I32: varint_tile<VM_I32, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
-    case VM_U32: varint_tile<VM_U32, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
-    case VM_I16: varint_tile<VM_I16, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
-    case VM_U16: varint_tile<VM_U16, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
-    case VM_I8: varint_tile<VM_I8, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
-    case VM_U8: varint_tile<VM_U8, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
-    case VM_F32_F16: varint_tile<VM_F32_F16, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
-    case VM_F32_BF16: varint_tile<VM_F32_BF16, SCATTER>(T, f, tile, tif, dst_base, stage, warp_tot); break;
-    default: break;
-  }
-}
 
 // =====================================================================================================
 // K2: per varint field, exclusive scan of its tile byte counts -> tile offsets + body length.
@@ -673,6 +554,7 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
     w = off + bytes;
     return off;
   };
+  const size_t w_vt = carve(sizeof(VTile) * static_cast<size_t>(n_vtiles)), w_tf = carve(4ull * n_vtiles);
   const size_t w_tb = carve(4ull * n_vtiles), w_to = carve(8ull * n_vtiles), w_tl = carve(8ull * n_tensors),
                w_el = carve(8ull * n_tensors), w_sl = carve(8ull * n_msgs), w_ml = carve(8ull * n_msgs),
                w_mp = carve(8ull * n_msgs), w_mo = carve(8ull * n_msgs), w_res = carve(16);
@@ -688,6 +570,8 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   T.vfield_first_tile = reinterpret_cast<uint32_t*>(d + o_vft);
   T.vfield_index = reinterpret_cast<uint32_t*>(d + o_vfi);
   T.segs = reinterpret_cast<CopySeg*>(d + o_segs);
+  T.vtiles = reinterpret_cast<VTile*>(k + w_vt);
+  T.tile_field = reinterpret_cast<uint32_t*>(k + w_tf);
   T.tile_bytes = reinterpret_cast<uint32_t*>(k + w_tb);
   T.tile_off = reinterpret_cast<uint64_t*>(k + w_to);
   T.tensor_len = reinterpret_cast<uint64_t*>(k + w_tl);
@@ -715,8 +599,10 @@ tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_
   const EncTables& T = u.T;
   if (T.n_vtiles) {
     {
+      k_tile_map<<<(T.n_vfields + 7) / 8, 256, 0, ctx->stream>>>(T);
+      ctx->launches++;
       ProfScope prof(ctx, PK_VARINT_SIZE);
-      k_varint_tiles<false><<<T.n_vtiles, kVarintThreads, 0, ctx->stream>>>(T, nullptr);
+      k_varint_size<<<T.n_vtiles, kVarintThreads, 0, ctx->stream>>>(T);
     }
     ctx->launches++;
     const uint32_t warps_per_block = 256 / 32;
@@ -779,7 +665,7 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
     if (T.n_vtiles) {
       {
         ProfScope prof(ctx, PK_VARINT_SCATTER);
-        k_varint_tiles<true><<<T.n_vtiles, kVarintThreads, 0, ctx->stream>>>(T, dst);
+        k_varint_scatter<<<T.n_vtiles, kVarintThreads, 0, ctx->stream>>>(T, dst);
       }
       ctx->launches++;
     }

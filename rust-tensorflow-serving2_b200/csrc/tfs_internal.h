@@ -77,6 +77,14 @@ struct EncField {
   uint32_t is_varint;
 };
 
+// One 2048-element tile of a varint-coded field (built on the device by k_tile_map).
+struct VTile {
+  const uint8_t* src;  // first element of the tile
+  uint32_t n;          // elements in the tile (2048 except for a field's last tile)
+  uint16_t mode;       // VarintMode
+  uint16_t esize;      // bytes per source element
+};
+
 struct EncTensor {
   StrRef name;
   int32_t dtype;
@@ -116,6 +124,8 @@ struct EncTables {
   uint32_t* vfield_index;       // [n_vfields] -> index into fields
   CopySeg* segs;                // [n_segs]
   // work arrays
+  VTile* vtiles;                // [n_vtiles]
+  uint32_t* tile_field;         // [n_vtiles] index into fields
   uint32_t* tile_bytes;         // [n_vtiles]
   uint64_t* tile_off;           // [n_vtiles] byte offset of the tile inside its field body
   uint64_t* tensor_len;         // [n_tensors]
@@ -176,6 +186,7 @@ struct DecTables {
   uint32_t* span_ctile0;  // [n_spans] first copy tile of each span (non-decreasing over the table)
   uint64_t* tensor_pool;  // [n_tensors] pool bytes of each tensor
   uint32_t* tile_count;  // [n varint tiles] terminators per tile
+  uint32_t* tile_span;   // [n varint tiles] the span that owns the tile
   uint64_t* tile_base;   // [n varint tiles] exclusive prefix inside the span
   CopySeg* segs;         // copy-class spans as segments (dst filled once the pool is known)
   unsigned long long* err;  // [n_msgs] min over (offset << 8 | code) of device-detected errors, ~0 = none

@@ -1,0 +1,232 @@
+// tfs_varint_dec.cuh — K4: packed-varint DECODE (terminator count, gather).
+//
+// Replaces prost's {int32,int64,uint32,uint64,bool}::merge_repeated -> decode_varint + Vec::push per element
+// (reached from the reference at src/lib.rs:265-266).  Integer work bound by HBM bandwidth.
+//
+// A packed body is cut into 4 KiB tiles on 16-byte boundaries of the absolute address; one CTA per tile, one
+// aligned 16-byte load per thread.  A terminator is a byte with its MSB clear; a value belongs to the tile that
+// holds its terminator.
+//   K4a k_varint_count    terminators per tile (+ detection of 10 continuation bytes in a row = over-long varint).
+//   K4c k_varint_gather   value index = span base + tile base + block-exclusive count of terminators.
+//                         Fast path (no value of the tile longer than 4 bytes, i.e. < 2^28: token ids, half
+//                         patterns, bools): each thread keeps its 16 bytes and the 16 bytes before them in
+//                         registers; for each of its 16 byte positions the four bytes ending there are cut out with
+//                         one funnel shift, the 7-bit groups are packed with two mask/shift steps and shifted by
+//                         the value's length (from the continuation mask).  No byte loads, no data-dependent loop.
+//                         General path: bytes in shared memory, walk back over at most 9 continuation bytes.
+//                         Both paths write the tile's values to shared memory first; the CTA then stores them to
+//                         the pool with fully coalesced accesses (a direct store per thread would scatter 8-byte
+//                         writes over 32 sectors per instruction — that was the bottleneck of the first version).
+#pragma once
+#include "tfs_device.cuh"
+
+namespace tfs {
+namespace {
+
+// one warp per span: which span owns each varint tile
+__global__ void __launch_bounds__(256) k_dtile_map(DecTables T, uint32_t n_spans, uint32_t n_vtiles) {
+  const uint32_t si = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (si >= n_spans) return;
+  const uint32_t t0 = T.span_vtile0[si];
+  const uint32_t t1 = si + 1 < n_spans ? T.span_vtile0[si + 1] : n_vtiles;
+  for (uint32_t t = t0 + lane_id(); t < t1; t += 32) T.tile_span[t] = si;
+}
+
+struct TileRef {
+  uint64_t span_abs0;  // absolute address of the first byte of the span
+  uint64_t span_end;   // absolute address one past its last byte
+  uint64_t tile_abs;   // absolute (16-byte aligned) address of the tile's first byte
+  uint32_t span;
+  uint32_t msg;
+};
+
+// uniform over the CTA (broadcast loads): no search, no barrier
+__device__ __forceinline__ TileRef tile_ref(const DecTables& T, uint32_t tile) {
+  const uint32_t si = T.tile_span[tile];
+  const DecSpan& s = T.spans[si];
+  TileRef r;
+  r.span = si;
+  r.msg = s.msg;
+  r.span_abs0 = reinterpret_cast<uintptr_t>(T.wire) + s.wire_off;
+  r.span_end = r.span_abs0 + s.len;
+  r.tile_abs = (r.span_abs0 & ~static_cast<uint64_t>(15)) + static_cast<uint64_t>(tile - T.span_vtile0[si]) * kDecTileBytes;
+  return r;
+}
+
+// 16 bytes of the tile owned by this thread: continuation mask and validity mask (bit j = byte j)
+__device__ __forceinline__ void chunk_masks(uint64_t chunk_abs, uint64_t span_abs0, uint64_t span_end, uint4* data,
+                                            uint32_t* cont, uint32_t* valid) {
+  if (chunk_abs + 16 <= span_abs0 || chunk_abs >= span_end) {
+    *data = make_uint4(0, 0, 0, 0);
+    *cont = 0;
+    *valid = 0;
+    return;
+  }
+  const uint4 d = ld_stream16(reinterpret_cast<const void*>(chunk_abs));
+  *data = d;
+  // MSB of each byte -> one bit per byte
+  auto msb4 = [](uint32_t x) { return ((x >> 7) & 1u) | ((x >> 14) & 2u) | ((x >> 21) & 4u) | ((x >> 28) & 8u); };
+  const uint32_t m = msb4(d.x) | (msb4(d.y) << 4) | (msb4(d.z) << 8) | (msb4(d.w) << 12);
+  uint32_t v = 0xFFFFu;
+  if (chunk_abs < span_abs0) v &= 0xFFFFu << (span_abs0 - chunk_abs);
+  if (chunk_abs + 16 > span_end) v &= 0xFFFFu >> (chunk_abs + 16 - span_end);
+  *valid = v & 0xFFFFu;
+  *cont = m & *valid;
+}
+
+// continuation mask of the 16 bytes before this thread's chunk: the previous lane has it; lane 0 re-loads
+__device__ __forceinline__ void prev_chunk(const TileRef& r, uint64_t chunk_abs, const uint4& own, uint32_t own_cont, uint4* pdata,
+                                           uint32_t* pcont) {
+  uint4 p;
+  p.x = __shfl_up_sync(0xFFFFFFFFu, own.x, 1);
+  p.y = __shfl_up_sync(0xFFFFFFFFu, own.y, 1);
+  p.z = __shfl_up_sync(0xFFFFFFFFu, own.z, 1);
+  p.w = __shfl_up_sync(0xFFFFFFFFu, own.w, 1);
+  uint32_t pc = __shfl_up_sync(0xFFFFFFFFu, own_cont, 1);
+  if (lane_id() == 0) {
+    uint32_t pv;
+    chunk_masks(chunk_abs - 16, r.span_abs0, r.span_end, &p, &pc, &pv);
+  }
+  *pdata = p;
+  *pcont = pc;
+}
+
+__global__ void __launch_bounds__(kDecThreads) k_varint_count(DecTables T) {
+  const uint32_t tile = blockIdx.x;
+  const TileRef r = tile_ref(T, tile);
+  const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 16ull;
+  uint4 d, pd;
+  uint32_t cont, valid, prev;
+  chunk_masks(chunk_abs, r.span_abs0, r.span_end, &d, &cont, &valid);
+  prev_chunk(r, chunk_abs, d, cont, &pd, &prev);
+  uint32_t x = (cont << 16) | prev;  // bit i..i+9 all set <=> ten continuation bytes in a row
+  x &= x >> 1;
+  x &= x >> 2;
+  x &= x >> 4;
+  x &= x >> 2;
+  if (x) {
+    const uint64_t at = chunk_abs > r.span_abs0 ? chunk_abs : r.span_abs0;
+    const uint64_t off = at - reinterpret_cast<uintptr_t>(T.wire) - T.msg_off[r.msg];
+    atomicMin(&T.err[r.msg], (static_cast<unsigned long long>(off) << 8) | TFS_ERR_INVALID_VARINT);
+  }
+  const uint32_t cnt = __reduce_add_sync(0xFFFFFFFFu, __popc(~cont & valid));
+  if (lane_id() == 0 && cnt) atomicAdd(&T.tile_count[tile], cnt);  // tile_count[] is zeroed by the host
+}
+
+// ---- gather -----------------------------------------------------------------------------------------------
+enum OutKind : int { O_U32 = 0, O_U64, O_BOOL, O_F16_F32, O_BF16_F32 };
+
+template <int OUT>
+struct OutTraits {
+  using type = uint32_t;
+};
+template <>
+struct OutTraits<O_U64> {
+  using type = uint64_t;
+};
+template <>
+struct OutTraits<O_BOOL> {
+  using type = uint8_t;
+};
+
+template <int OUT>
+__device__ __forceinline__ typename OutTraits<OUT>::type convert_out(uint64_t v) {
+  if constexpr (OUT == O_U32) return static_cast<uint32_t>(v);  // `as i32` / `as u32` truncates
+  else if constexpr (OUT == O_U64) return v;
+  else if constexpr (OUT == O_BOOL) return static_cast<uint8_t>(v != 0);
+  else if constexpr (OUT == O_F16_F32) return __float_as_uint(f16_bits_to_f32(static_cast<uint32_t>(v) & 0xFFFFu));
+  else return __float_as_uint(bf16_bits_to_f32(static_cast<uint32_t>(v) & 0xFFFFu));
+}
+
+constexpr uint32_t kGatherOutBytes = kDecTileBytes * 8;  // at most one value per wire byte, 8 bytes each
+
+template <int OUT>
+__device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restrict__ dst, uint8_t* sm_out, uint8_t* sm_in, uint32_t* scan_smem) {
+  using out_t = typename OutTraits<OUT>::type;
+  out_t* out = reinterpret_cast<out_t*>(sm_out);
+  const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 16ull;
+  uint4 d, pd;
+  uint32_t cont, valid, pcont;
+  chunk_masks(chunk_abs, r.span_abs0, r.span_end, &d, &cont, &valid);
+  prev_chunk(r, chunk_abs, d, cont, &pd, &pcont);
+  const uint32_t term = ~cont & valid;
+  uint32_t total;
+  const uint32_t idx0 = block_exclusive_scan<uint32_t, kDecThreads / 32>(__popc(term), scan_smem, &total);
+  const uint32_t c32 = (cont << 16) | pcont;
+  const uint32_t run4 = c32 & (c32 >> 1) & (c32 >> 2) & (c32 >> 3);  // bit i: continuation bytes at i..i+3
+  const bool fast = __syncthreads_and((run4 & 0xFFFFF000u) == 0);       // no value ending in this tile is longer than 4 bytes
+  if (fast) {
+    const uint32_t w[5] = {pd.w, d.x, d.y, d.z, d.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const int pos = 4 * k + b;
+        if ((term >> pos) & 1u) {
+          const uint32_t x = b == 3 ? w[k + 1] : __funnelshift_r(w[k], w[k + 1], 8 * (b + 1));  // the 4 bytes ending at `pos`
+          const uint32_t t3 = (c32 >> (13 + pos)) & 7u;                                          // continuation bits of the 3 bytes before it
+          const uint32_t len = 1u + static_cast<uint32_t>(__clz(static_cast<int>(~(t3 << 29))));
+          uint32_t g = x & 0x7F7F7F7Fu;
+          g = (g & 0x007F007Fu) | ((g & 0x7F007F00u) >> 1);
+          g = (g & 0x00003FFFu) | ((g & 0x3FFF0000u) >> 2);
+          const uint32_t v = g >> (7u * (4u - len));
+          out[idx0 + __popc(term & ((1u << pos) - 1u))] = convert_out<OUT>(v);
+        }
+      }
+    }
+  } else {
+    // general path: bytes in shared memory (with the 16 bytes before the tile), walk back from each terminator
+    *reinterpret_cast<uint4*>(sm_in + 16 + threadIdx.x * 16) = d;
+    if (threadIdx.x == 0) *reinterpret_cast<uint4*>(sm_in) = pd;
+    __syncthreads();
+    const int32_t lo = r.span_abs0 > r.tile_abs ? static_cast<int32_t>(r.span_abs0 - r.tile_abs) : -16;
+    uint32_t t = term, idx = idx0;
+    while (t) {
+      const int32_t j = __ffs(t) - 1;
+      t &= t - 1;
+      const int32_t p = static_cast<int32_t>(threadIdx.x) * 16 + j;
+      uint64_t v = sm_in[16 + p];
+#pragma unroll 1
+      for (int32_t k = 1; k <= 9; ++k) {
+        const int32_t q = p - k;
+        if (q < lo) break;
+        const uint8_t b = sm_in[16 + q];
+        if (b < 0x80) break;
+        v = (v << 7) | (b & 0x7Fu);
+      }
+      out[idx++] = convert_out<OUT>(v);
+    }
+  }
+  __syncthreads();
+  // coalesced flush of the tile's values
+  out_t* gdst = reinterpret_cast<out_t*>(dst);
+  for (uint32_t i = threadIdx.x; i < total; i += kDecThreads) gdst[i] = out[i];
+}
+
+__global__ void __launch_bounds__(kDecThreads) k_varint_gather(DecTables T, uint8_t* pool, const uint64_t* __restrict__ gate) {
+  __shared__ __align__(16) uint8_t sm_out[kGatherOutBytes];
+  __shared__ __align__(16) uint8_t sm_in[16 + kDecTileBytes];
+  __shared__ uint32_t scan_smem[kDecThreads / 32 + 1];
+  if (gate && *gate != 0) return;  // the pool of a one-call decode turned out to be too small
+  const uint32_t tile = blockIdx.x;
+  const TileRef r = tile_ref(T, tile);
+  const DecSpan& s = T.spans[r.span];
+  if (T.msgs[s.msg].status != TFS_OK) return;  // uniform
+  const tfs_tensor_out_t& t = T.tensors[s.tensor];
+  const int32_t ty = t.dst_type[s.slot];
+  const uint32_t esz = ty == TFS_T_I64 || ty == TFS_T_U64 ? 8u : ty == TFS_T_BOOL ? 1u : 4u;
+  uint8_t* dst = pool + t.dst_off[s.slot] + (s.elem_base + T.tile_base[tile]) * esz;
+  switch (ty) {
+    case TFS_T_I32: case TFS_T_U32: gather_tile<O_U32>(r, dst, sm_out, sm_in, scan_smem); break;
+    case TFS_T_I64: case TFS_T_U64: gather_tile<O_U64>(r, dst, sm_out, sm_in, scan_smem); break;
+    case TFS_T_BOOL: gather_tile<O_BOOL>(r, dst, sm_out, sm_in, scan_smem); break;
+    case TFS_T_F32:
+      if (t.dtype == 19) gather_tile<O_F16_F32>(r, dst, sm_out, sm_in, scan_smem);
+      else gather_tile<O_BF16_F32>(r, dst, sm_out, sm_in, scan_smem);
+      break;
+    default: break;
+  }
+}
+
+}  // namespace
+}  // namespace tfs
