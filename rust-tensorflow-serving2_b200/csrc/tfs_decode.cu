@@ -855,6 +855,8 @@ tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const 
     ctx->launches++;
   }
   if (n_vt) {
+    k_dtile_bind<<<static_cast<uint32_t>((n_vt + 255) / 256), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_vt), pool, gate);
+    ctx->launches++;
     {
       ProfScope prof(ctx, PK_VARINT_GATHER);
       k_varint_gather<<<static_cast<uint32_t>(n_vt), kDecThreads, 0, ctx->stream>>>(T, pool, gate);
@@ -961,7 +963,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
                p_str = carve(&cur, n_str);
   const size_t res2_bytes = cur;
   const size_t p_spn = carve(&cur, sizeof(DecSpan) * n_spans), p_sv = carve(&cur, 4 * (n_spans + 1)),
-               p_sc = carve(&cur, 4 * (n_spans + 1)), p_tc = carve(&cur, 4 * n_vt), p_ts = carve(&cur, 4 * n_vt), p_tb = carve(&cur, 8 * n_vt),
+               p_sc = carve(&cur, 4 * (n_spans + 1)), p_tc = carve(&cur, 4 * n_vt), p_ts = carve(&cur, sizeof(TileRef) * n_vt), p_td = carve(&cur, sizeof(TileDst) * n_vt), p_tb = carve(&cur, 8 * n_vt),
                p_seg = carve(&cur, sizeof(CopySeg) * n_spans), p_tp = carve(&cur, 8 * n_tensors);
   DEC_TRY(dev_reserve(ctx, &ctx->d_dec2, cur + 64));
   uint8_t* d2 = static_cast<uint8_t*>(ctx->d_dec2.p);
@@ -972,7 +974,8 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   T.span_vtile0 = reinterpret_cast<uint32_t*>(d2 + p_sv);
   T.span_ctile0 = reinterpret_cast<uint32_t*>(d2 + p_sc);
   T.tile_count = reinterpret_cast<uint32_t*>(d2 + p_tc);
-  T.tile_span = reinterpret_cast<uint32_t*>(d2 + p_ts);
+  T.dtiles = reinterpret_cast<TileRef*>(d2 + p_ts);
+  T.dtile_dst = reinterpret_cast<TileDst*>(d2 + p_td);
   T.tile_base = reinterpret_cast<uint64_t*>(d2 + p_tb);
   T.segs = reinterpret_cast<CopySeg*>(d2 + p_seg);
   T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);

@@ -159,6 +159,20 @@ struct DecSpan {
   uint64_t elem_tile0; // varint: index into tile_count[] of its first tile (== first_tile)
 };
 
+// One 4 KiB tile of a packed varint body (k_dtile_map) and where its values go (k_dtile_bind).
+struct TileRef {
+  uint64_t span_abs0;  // absolute address of the first byte of the span
+  uint64_t span_end;   // absolute address one past its last byte
+  uint64_t tile_abs;   // absolute (16-byte aligned) address of the tile's first byte
+  uint32_t span;
+  uint32_t msg;
+};
+struct TileDst {
+  uint8_t* dst;    // pool address of the tile's first value
+  int32_t type;    // TFS_T_* the values are written as, TFS_T_NONE = skip (the message failed)
+  int32_t dtype;   // tensor dtype (19 / 14 select the f16 / bf16 widening)
+};
+
 struct DecTables {
   const uint8_t* wire;
   uint64_t wire_bytes;
@@ -186,7 +200,8 @@ struct DecTables {
   uint32_t* span_ctile0;  // [n_spans] first copy tile of each span (non-decreasing over the table)
   uint64_t* tensor_pool;  // [n_tensors] pool bytes of each tensor
   uint32_t* tile_count;  // [n varint tiles] terminators per tile
-  uint32_t* tile_span;   // [n varint tiles] the span that owns the tile
+  TileRef* dtiles;       // [n varint tiles]
+  TileDst* dtile_dst;    // [n varint tiles]
   uint64_t* tile_base;   // [n varint tiles] exclusive prefix inside the span
   CopySeg* segs;         // copy-class spans as segments (dst filled once the pool is known)
   unsigned long long* err;  // [n_msgs] min over (offset << 8 | code) of device-detected errors, ~0 = none

@@ -23,34 +23,41 @@
 namespace tfs {
 namespace {
 
-// one warp per span: which span owns each varint tile
+// one warp per span: a 32-byte record per varint tile, so that a CTA starts with one broadcast load instead of a
+// search over the span table
 __global__ void __launch_bounds__(256) k_dtile_map(DecTables T, uint32_t n_spans, uint32_t n_vtiles) {
   const uint32_t si = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (si >= n_spans) return;
   const uint32_t t0 = T.span_vtile0[si];
   const uint32_t t1 = si + 1 < n_spans ? T.span_vtile0[si + 1] : n_vtiles;
-  for (uint32_t t = t0 + lane_id(); t < t1; t += 32) T.tile_span[t] = si;
-}
-
-struct TileRef {
-  uint64_t span_abs0;  // absolute address of the first byte of the span
-  uint64_t span_end;   // absolute address one past its last byte
-  uint64_t tile_abs;   // absolute (16-byte aligned) address of the tile's first byte
-  uint32_t span;
-  uint32_t msg;
-};
-
-// uniform over the CTA (broadcast loads): no search, no barrier
-__device__ __forceinline__ TileRef tile_ref(const DecTables& T, uint32_t tile) {
-  const uint32_t si = T.tile_span[tile];
+  if (t0 >= t1) return;
   const DecSpan& s = T.spans[si];
   TileRef r;
   r.span = si;
   r.msg = s.msg;
   r.span_abs0 = reinterpret_cast<uintptr_t>(T.wire) + s.wire_off;
   r.span_end = r.span_abs0 + s.len;
-  r.tile_abs = (r.span_abs0 & ~static_cast<uint64_t>(15)) + static_cast<uint64_t>(tile - T.span_vtile0[si]) * kDecTileBytes;
-  return r;
+  for (uint32_t t = t0 + lane_id(); t < t1; t += 32) {
+    r.tile_abs = (r.span_abs0 & ~static_cast<uint64_t>(15)) + static_cast<uint64_t>(t - t0) * kDecTileBytes;
+    T.dtiles[t] = r;
+  }
+}
+
+__device__ __forceinline__ TileRef tile_ref(const DecTables& T, uint32_t tile) { return T.dtiles[tile]; }
+
+// at decode time, one thread per varint tile: where its values go and as what
+__global__ void __launch_bounds__(256) k_dtile_bind(DecTables T, uint32_t n_vtiles, uint8_t* pool, const uint64_t* __restrict__ gate) {
+  const uint32_t tile = blockIdx.x * blockDim.x + threadIdx.x;
+  if (tile >= n_vtiles || (gate && *gate != 0)) return;
+  const DecSpan& s = T.spans[T.dtiles[tile].span];
+  const tfs_tensor_out_t& t = T.tensors[s.tensor];
+  const int32_t ty = t.dst_type[s.slot];
+  const uint32_t esz = ty == TFS_T_I64 || ty == TFS_T_U64 ? 8u : ty == TFS_T_BOOL ? 1u : 4u;
+  TileDst d;
+  d.dst = pool + t.dst_off[s.slot] + (s.elem_base + T.tile_base[tile]) * esz;
+  d.type = T.msgs[s.msg].status == TFS_OK ? ty : TFS_T_NONE;  // NONE: the message failed, nothing is written
+  d.dtype = t.dtype;
+  T.dtile_dst[tile] = d;
 }
 
 // 16 bytes of the tile owned by this thread: continuation mask and validity mask (bit j = byte j)
@@ -64,8 +71,9 @@ __device__ __forceinline__ void chunk_masks(uint64_t chunk_abs, uint64_t span_ab
   }
   const uint4 d = ld_stream16(reinterpret_cast<const void*>(chunk_abs));
   *data = d;
-  // MSB of each byte -> one bit per byte
-  auto msb4 = [](uint32_t x) { return ((x >> 7) & 1u) | ((x >> 14) & 2u) | ((x >> 21) & 4u) | ((x >> 28) & 8u); };
+  // MSB of each byte -> one bit per byte: the four isolated bits are moved to bits 24..27 by one multiply
+  // (2^24, 2^17, 2^10, 2^3 put bytes 0..3 there; no two partial products meet, so there are no carries)
+  auto msb4 = [](uint32_t x) { return ((((x >> 7) & 0x01010101u) * 0x01020408u) >> 24) & 0xFu; };
   const uint32_t m = msb4(d.x) | (msb4(d.y) << 4) | (msb4(d.z) << 8) | (msb4(d.w) << 12);
   uint32_t v = 0xFFFFu;
   if (chunk_abs < span_abs0) v &= 0xFFFFu << (span_abs0 - chunk_abs);
@@ -138,7 +146,14 @@ __device__ __forceinline__ typename OutTraits<OUT>::type convert_out(uint64_t v)
   else return __float_as_uint(bf16_bits_to_f32(static_cast<uint32_t>(v) & 0xFFFFu));
 }
 
-constexpr uint32_t kGatherOutBytes = kDecTileBytes * 8;  // at most one value per wire byte, 8 bytes each
+// Output staging: 2048 values of up to 8 bytes.  A tile holds at most 4096 values (one per wire byte), so a dense
+// tile is written out in two rounds; keeping the buffer at 16 KiB lets 8 CTAs share an SM.
+constexpr uint32_t kRoundValues = 2048;
+// Value i sits at slot i + i / 16: a thread's values are consecutive, so lanes write at strides that are often
+// multiples of 16 slots (16 one-byte varints per 16-byte chunk is the dense case); the pad spreads them over
+// the banks, and the flush still reads (almost) consecutive slots.
+__device__ __forceinline__ uint32_t pad_slot(uint32_t i) { return i + (i >> 4); }
+constexpr uint32_t kGatherOutBytes = (kRoundValues + kRoundValues / 16 + 1) * 8;
 
 template <int OUT>
 __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restrict__ dst, uint8_t* sm_out, uint8_t* sm_in, uint32_t* scan_smem) {
@@ -155,6 +170,13 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
   const uint32_t c32 = (cont << 16) | pcont;
   const uint32_t run4 = c32 & (c32 >> 1) & (c32 >> 2) & (c32 >> 3);  // bit i: continuation bytes at i..i+3
   const bool fast = __syncthreads_and((run4 & 0xFFFFF000u) == 0);       // no value ending in this tile is longer than 4 bytes
+  out_t* gdst = reinterpret_cast<out_t*>(dst);
+  if (!fast) {
+    *reinterpret_cast<uint4*>(sm_in + 16 + threadIdx.x * 16) = d;
+    if (threadIdx.x == 0) *reinterpret_cast<uint4*>(sm_in) = pd;
+  }
+  for (uint32_t round0 = 0; round0 < total; round0 += kRoundValues) {  // uniform trip count (1, rarely 2)
+  if (round0) __syncthreads();  // the previous round's flush has read the staging buffer
   if (fast) {
     const uint32_t w[5] = {pd.w, d.x, d.y, d.z, d.w};
 #pragma unroll
@@ -162,7 +184,8 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
         const int pos = 4 * k + b;
-        if ((term >> pos) & 1u) {
+        const uint32_t slot = idx0 + __popc(term & ((1u << pos) - 1u)) - round0;  // wraps when before this round
+        if (((term >> pos) & 1u) && slot < kRoundValues) {
           const uint32_t x = b == 3 ? w[k + 1] : __funnelshift_r(w[k], w[k + 1], 8 * (b + 1));  // the 4 bytes ending at `pos`
           const uint32_t t3 = (c32 >> (13 + pos)) & 7u;                                          // continuation bits of the 3 bytes before it
           const uint32_t len = 1u + static_cast<uint32_t>(__clz(static_cast<int>(~(t3 << 29))));
@@ -170,20 +193,20 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
           g = (g & 0x007F007Fu) | ((g & 0x7F007F00u) >> 1);
           g = (g & 0x00003FFFu) | ((g & 0x3FFF0000u) >> 2);
           const uint32_t v = g >> (7u * (4u - len));
-          out[idx0 + __popc(term & ((1u << pos) - 1u))] = convert_out<OUT>(v);
+          out[pad_slot(slot)] = convert_out<OUT>(v);
         }
       }
     }
   } else {
     // general path: bytes in shared memory (with the 16 bytes before the tile), walk back from each terminator
-    *reinterpret_cast<uint4*>(sm_in + 16 + threadIdx.x * 16) = d;
-    if (threadIdx.x == 0) *reinterpret_cast<uint4*>(sm_in) = pd;
     __syncthreads();
     const int32_t lo = r.span_abs0 > r.tile_abs ? static_cast<int32_t>(r.span_abs0 - r.tile_abs) : -16;
     uint32_t t = term, idx = idx0;
     while (t) {
       const int32_t j = __ffs(t) - 1;
       t &= t - 1;
+      const uint32_t slot = idx++ - round0;
+      if (slot >= kRoundValues) continue;  // belongs to another round
       const int32_t p = static_cast<int32_t>(threadIdx.x) * 16 + j;
       uint64_t v = sm_in[16 + p];
 #pragma unroll 1
@@ -194,34 +217,33 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
         if (b < 0x80) break;
         v = (v << 7) | (b & 0x7Fu);
       }
-      out[idx++] = convert_out<OUT>(v);
+      out[pad_slot(slot)] = convert_out<OUT>(v);
     }
   }
   __syncthreads();
-  // coalesced flush of the tile's values
-  out_t* gdst = reinterpret_cast<out_t*>(dst);
-  for (uint32_t i = threadIdx.x; i < total; i += kDecThreads) gdst[i] = out[i];
+  // coalesced flush of this round's values
+  const uint32_t n_round = total - round0 < kRoundValues ? total - round0 : kRoundValues;
+  for (uint32_t i = threadIdx.x; i < n_round; i += kDecThreads) gdst[round0 + i] = out[pad_slot(i)];
+  }
 }
 
-__global__ void __launch_bounds__(kDecThreads) k_varint_gather(DecTables T, uint8_t* pool, const uint64_t* __restrict__ gate) {
+__global__ void __launch_bounds__(kDecThreads, 6) k_varint_gather(DecTables T, uint8_t* pool, const uint64_t* __restrict__ gate) {
   __shared__ __align__(16) uint8_t sm_out[kGatherOutBytes];
   __shared__ __align__(16) uint8_t sm_in[16 + kDecTileBytes];
   __shared__ uint32_t scan_smem[kDecThreads / 32 + 1];
   if (gate && *gate != 0) return;  // the pool of a one-call decode turned out to be too small
   const uint32_t tile = blockIdx.x;
-  const TileRef r = tile_ref(T, tile);
-  const DecSpan& s = T.spans[r.span];
-  if (T.msgs[s.msg].status != TFS_OK) return;  // uniform
-  const tfs_tensor_out_t& t = T.tensors[s.tensor];
-  const int32_t ty = t.dst_type[s.slot];
-  const uint32_t esz = ty == TFS_T_I64 || ty == TFS_T_U64 ? 8u : ty == TFS_T_BOOL ? 1u : 4u;
-  uint8_t* dst = pool + t.dst_off[s.slot] + (s.elem_base + T.tile_base[tile]) * esz;
+  const TileRef r = tile_ref(T, tile);       // two independent broadcast loads
+  const TileDst td = T.dtile_dst[tile];
+  (void)pool;
+  uint8_t* dst = td.dst;
+  const int32_t ty = td.type;
   switch (ty) {
     case TFS_T_I32: case TFS_T_U32: gather_tile<O_U32>(r, dst, sm_out, sm_in, scan_smem); break;
     case TFS_T_I64: case TFS_T_U64: gather_tile<O_U64>(r, dst, sm_out, sm_in, scan_smem); break;
     case TFS_T_BOOL: gather_tile<O_BOOL>(r, dst, sm_out, sm_in, scan_smem); break;
     case TFS_T_F32:
-      if (t.dtype == 19) gather_tile<O_F16_F32>(r, dst, sm_out, sm_in, scan_smem);
+      if (td.dtype == 19) gather_tile<O_F16_F32>(r, dst, sm_out, sm_in, scan_smem);
       else gather_tile<O_BF16_F32>(r, dst, sm_out, sm_in, scan_smem);
       break;
     default: break;
