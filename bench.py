@@ -277,9 +277,125 @@ def run_ours(args):
                      "step_frac_of_peak": round(2 * value / world / peak, 4)},
         "cpu_baseline": cpu_baseline(R, budget_s=args.cpu_budget),
     }
+    if world == 1 and not args.no_extras:
+        del src, wire, pool
+        torch.cuda.empty_cache()
+        line["other_configs"] = other_configs(codec, dev, peak)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+# =====================================================================================================
+# the other BASELINE configs (N = 1 only, a few repetitions each): parity-tested workloads, reported next to the
+# headline so that the varint kernels have measured numbers too
+# =====================================================================================================
+def other_configs(codec, dev, peak):
+    import torch
+    import tfs_b200 as tfs
+    from tfs_b200 import abi
+
+    ctx, enc, dec = codec.ctx, codec.encoder(), codec.decoder()
+    names = {abi.PK_COPY: "k_copy", abi.PK_VARINT_SIZE: "k_varint_size", abi.PK_VARINT_SCATTER: "k_varint_scatter",
+             abi.PK_VARINT_COUNT: "k_varint_count", abi.PK_VARINT_GATHER: "k_varint_gather", abi.PK_COPY_TMA: "k_copy_tma"}
+
+    def measure(msgs, kind, in_bytes, reps=5, dflags=0, decode_only=False):
+        built = tfs.build_batch(msgs, kind)
+        wire = torch.empty(enc.bound(built, 0), dtype=torch.uint8, device=dev)
+        eb = enc.encode(built, kind, 0, dst=wire)
+        W = sum(eb.lengths)
+        d = dec.scan(eb.wire, eb.offsets, eb.lengths, kind, dflags)
+        out_bytes = d.pool_bytes
+        pool = torch.empty(out_bytes + 64, dtype=torch.uint8, device=dev)
+        d.close()
+        for _ in range(2):
+            if not decode_only:
+                eb = enc.encode(built, kind, 0, dst=wire)
+            dec.decode_into(eb.wire, eb.offsets, eb.lengths, kind, pool, dflags).close()
+        ctx.prof_enable(True)
+        for k in names:
+            ctx.prof_read(k, reset=True)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        te = td = 0.0
+        for _ in range(reps):
+            ev[0].record()
+            if not decode_only:
+                eb = enc.encode(built, kind, 0, dst=wire)
+            ev[1].record()
+            dec.decode_into(eb.wire, eb.offsets, eb.lengths, kind, pool, dflags).close()
+            ev[2].record()
+            torch.cuda.synchronize()
+            te += ev[0].elapsed_time(ev[1]) / reps
+            td += ev[1].elapsed_time(ev[2]) / reps
+        ctx.prof_enable(False)
+        alg = {abi.PK_VARINT_SIZE: in_bytes, abi.PK_VARINT_SCATTER: in_bytes + W, abi.PK_VARINT_COUNT: W, abi.PK_VARINT_GATHER: W + out_bytes}
+        kernels = {}
+        for k, nm in names.items():
+            n, ms = ctx.prof_read(k, reset=True)
+            if n and k in alg and not decode_only:  # (C5's wire is mostly fixed-width payload: no per-kernel figure)
+                gbs = alg[k] / (ms / n * 1e-3) / 1e9
+                kernels[nm] = {"avg_launch_ms": round(ms / n, 4), "algorithmic_GBps": round(gbs, 1), "frac_of_measured_peak": round(gbs / peak, 3)}
+        res = {"messages": len(msgs), "wire_MB": round(W / 1e6, 2), "values_MB": round(out_bytes / 1e6, 2),
+               "decode_ms": round(td, 4), "decode_wire_GBps": round(W / (td * 1e-3) / 1e9, 1),
+               "decode_algorithmic_GBps": round((W + out_bytes) / (td * 1e-3) / 1e9, 1), "kernels": kernels}
+        if not decode_only:
+            res.update({"encode_ms": round(te, 4), "encode_wire_GBps": round(W / (te * 1e-3) / 1e9, 1),
+                        "encode_algorithmic_GBps": round((in_bytes + W) / (te * 1e-3) / 1e9, 1),
+                        "encode_decode_wire_GBps": round(2 * W / ((te + td) * 1e-3) / 1e9, 1)})
+        return res
+
+    out = {}
+    g = torch.Generator(device=dev)
+    g.manual_seed(3001)
+    R = 256
+    ids = torch.randint(0, 30522, (R, 256 * 512), device=dev, dtype=torch.int64, generator=g)
+    lens = torch.randint(1, 513, (R, 256, 1), device=dev, generator=g)
+    mask = (torch.arange(512, device=dev)[None, None, :] < lens).to(torch.int64).reshape(R, -1).contiguous()
+    shape = tfs.TensorShapeProto([256, 512])
+    msgs = [tfs.PredictRequest(tfs.ModelSpec("bert", signature_name="serving_default"),
+                               [("input_ids", tfs.TensorProto(dtype=abi.DT_INT64, tensor_shape=shape, int64_val=ids[i])),
+                                ("attention_mask", tfs.TensorProto(dtype=abi.DT_INT64, tensor_shape=shape, int64_val=mask[i]))]) for i in range(R)]
+    out["C3 BERT input_ids+attention_mask int64_val 256x512, 256 requests"] = measure(msgs, abi.MSG_PREDICT_REQUEST, 2 * R * 256 * 512 * 8)
+    del ids, mask, msgs
+    R4 = 64
+    x = torch.randn(R4, 1 << 20, device=dev, generator=g)
+    msgs = [tfs.TensorProto(dtype=abi.DT_HALF, tensor_shape=tfs.TensorShapeProto([1 << 20]), half_val=tfs.Payload(x[i], abi.T_F32, abi.T_F16))
+            for i in range(R4)]
+    out["C4 DT_HALF half_val 2^20 elements from f32 (decode widens to f32), 64 tensors"] = measure(
+        msgs, abi.MSG_TENSOR_PROTO, R4 * (1 << 22), dflags=abi.F_HALF_TO_F32)
+    del x, msgs
+    # C5: the per-GPU share (1024 of 8192) of mixed-dtype PredictResponses, decoded
+    import numpy as np
+    rng = np.random.default_rng(5001)
+    msgs = []
+    for _ in range(1024):
+        entries = []
+        for j in range(int(rng.integers(1, 4))):
+            n = int(2 ** rng.uniform(0, 18))
+            sh = tfs.TensorShapeProto([1] * int(rng.integers(0, 4)) + [n])
+            which = int(rng.integers(0, 7))
+            if which == 0:
+                t = tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=sh, float_val=torch.randn(n, device=dev, generator=g))
+            elif which == 1:
+                t = tfs.TensorProto(dtype=abi.DT_DOUBLE, tensor_shape=sh, double_val=torch.randn(n, device=dev, generator=g, dtype=torch.float64))
+            elif which == 2:
+                v = torch.randint(-(1 << 31), 1 << 31, (n,), device=dev, generator=g, dtype=torch.int64).to(torch.int32)
+                t = tfs.TensorProto(dtype=abi.DT_INT32, tensor_shape=sh, int_val=v)
+            elif which == 3:
+                v = torch.randint(-(1 << 62), 1 << 62, (n,), device=dev, generator=g, dtype=torch.int64)
+                t = tfs.TensorProto(dtype=abi.DT_INT64, tensor_shape=sh, int64_val=v)
+            elif which == 4:
+                h = torch.randn(n, device=dev, generator=g).to(torch.float16)
+                t = tfs.TensorProto(dtype=abi.DT_HALF, tensor_shape=sh, half_val=h)
+            elif which == 5:
+                t = tfs.TensorProto(dtype=abi.DT_BOOL, tensor_shape=sh, bool_val=torch.rand(n, device=dev, generator=g) < 0.5)
+            else:
+                t = tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=sh, tensor_content=torch.randn(n, device=dev, generator=g))
+            entries.append((f"out{j}", t))
+        msgs.append(tfs.PredictResponse(entries, tfs.ModelSpec("mixed", version=int(rng.integers(1, 100)), signature_name="serving_default")))
+    out["C5 mixed-dtype PredictResponses, 1024 messages (one GPU's share of 8192), decode"] = measure(
+        msgs, abi.MSG_PREDICT_RESPONSE, 0, decode_only=True)
+    return out
 
 
 # =====================================================================================================
@@ -368,6 +484,7 @@ def main():
     ap.add_argument("--requests", type=int, default=16, help="C2 requests per variant, per GPU and per step")
     ap.add_argument("--e2e-requests", type=int, default=4)
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU baseline sampling")
+    ap.add_argument("--no-extras", action="store_true", help="skip the C3 / C4 / C5 side measurements (N = 1 only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
