@@ -467,7 +467,8 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
             "warmup": min(args.warmup, 1), "ms_per_step": round(tot_s / steps * 1e3, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": workload_name(n_msgs), "requests_per_variant_per_gpu": n_msgs, "wire_bytes_per_request": C2_WIRE},
+            "config": {"workload": workload_name(args.requests), "requests_per_variant_per_gpu": args.requests,
+                       "wire_bytes_per_request": C2_WIRE, "sample_requests_per_variant_per_step": n_msgs},
             "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
                              "host_cores_available": cores},
             "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
