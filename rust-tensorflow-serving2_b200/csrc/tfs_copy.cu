@@ -259,12 +259,19 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       "DONE:\n"
       "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
 }
-__device__ __forceinline__ void tma_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
-               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+// The payload streams through L2 exactly once in each direction: mark its lines evict-first so that the small
+// tables and the code of the framing / walk kernels that run between two copies stay resident in the 126 MB L2.
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
 }
-__device__ __forceinline__ void tma_store(void* gdst, const void* smem_src, uint32_t bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+__device__ __forceinline__ void tma_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar, uint64_t pol) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;" ::"r"(smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void tma_store(void* gdst, const void* smem_src, uint32_t bytes, uint64_t pol) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes), "l"(pol) : "memory");
 }
 __device__ __forceinline__ void tma_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 template <int N>
@@ -322,6 +329,7 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 
+  const uint64_t pol = l2_evict_first_policy();
   TileWalk walk{segs, n_segs, 0u, blockIdx.x, n_tiles, gridDim.x};
   uint8_t* dsts[kTmaStages];
   uint32_t sizes[kTmaStages];
@@ -335,7 +343,7 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
     dsts[s] = dst;
     sizes[s] = bytes;
     mbar_expect_tx(&full_bar[s], bytes);
-    tma_load(ring + s * kTmaChunk, src, bytes, &full_bar[s]);
+    tma_load(ring + s * kTmaChunk, src, bytes, &full_bar[s], pol);
     ++issued;
     return true;
   };
@@ -345,7 +353,7 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
   while (stored < issued) {
     const uint32_t s = stored % kTmaStages;
     mbar_wait(&full_bar[s], (stored / kTmaStages) & 1u);
-    tma_store(dsts[s], ring + s * kTmaChunk, sizes[s]);
+    tma_store(dsts[s], ring + s * kTmaChunk, sizes[s], pol);
     tma_commit();
     ++stored;
     // all but the newest store have finished reading shared memory: the stage of store (stored - 2) is free,
@@ -362,11 +370,10 @@ tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs,
                          bool need_generic) {
   if (n_segs == 0 || n_tiles == 0) return TFS_OK;
   if (n_tiles > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (copy tiles)");
-  static bool attr_set = false;
   const uint32_t ring_bytes = kTmaStages * kTmaChunk;
-  if (!attr_set) {
+  if (!ctx->copy_attr_set) {  // a per-device attribute: once per context, not once per process
     TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ring_bytes)));
-    attr_set = true;
+    ctx->copy_attr_set = true;
   }
   if (need_generic) {  // segments that are not congruent mod 16, are tiny, or need arithmetic: one CTA per tile
     ProfScope prof(ctx, PK_COPY);

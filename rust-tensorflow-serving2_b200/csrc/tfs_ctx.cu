@@ -162,7 +162,7 @@ tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx) {
   if (!ctx) return TFS_OK;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  for (DevBuf* b : {&ctx->d_tables, &ctx->d_work, &ctx->d_stage_in, &ctx->d_stage_out, &ctx->d_dec1, &ctx->d_dec2})
+  for (DevBuf* b : {&ctx->d_tables, &ctx->d_work, &ctx->d_stage_in, &ctx->d_stage_out, &ctx->d_dec1, &ctx->d_dec2, &ctx->d_dec3})
     if (b->p) cudaFree(b->p);
   if (ctx->h_up) cudaFreeHost(ctx->h_up);
   if (ctx->h_down) cudaFreeHost(ctx->h_down);

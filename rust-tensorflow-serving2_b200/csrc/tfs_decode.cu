@@ -35,7 +35,7 @@ namespace {
 
 enum { WT_VARINT = 0, WT_64 = 1, WT_LEN = 2, WT_SGROUP = 3, WT_EGROUP = 4, WT_32 = 5 };
 // TOT_GENERIC counts the copy-class spans the TMA ring cannot take (not congruent mod 16, tiny, or widened)
-enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_COUNT_ = 16 };
+enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_RETRY, TOT_COUNT_ = 16 };
 constexpr size_t kTotalsBytes = sizeof(uint64_t) * TOT_COUNT_;
 
 __device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
@@ -806,6 +806,49 @@ __global__ void __launch_bounds__(kSmallBatch) k_fill_finalize_small(DecTables T
   pool_layout_body<kSmallBatch / 32>(T, n_tensors, pool_capacity, smem);
 }
 
+// host and device agree on where the result blob (tensors | filters | strings) keeps its three arrays
+__host__ __device__ inline void blob_layout(uint64_t n_tensors, uint64_t n_filters, uint64_t n_str, uint64_t* p_flt, uint64_t* p_str,
+                                            uint64_t* bytes) {
+  *p_flt = (sizeof(tfs_tensor_out_t) * n_tensors + 63u) & ~static_cast<uint64_t>(63);
+  *p_str = (*p_flt + sizeof(tfs_span_t) * n_filters + 63u) & ~static_cast<uint64_t>(63);
+  *bytes = *p_str + n_str;
+}
+
+// Small batches, planned optimistically: pass-1 walk, the scans, and - when the tables the host laid out from its
+// hints are large enough - the zeroing of the tensor records and the pass-2 walk, all in ONE single-CTA launch.
+// The second walk then runs out of warm caches, and a batch without varint bodies is finalized here too: one host
+// synchronisation per decode instead of two.  totals[TOT_RETRY] = 1 asks the host for larger tables.
+static_assert(sizeof(tfs_tensor_out_t) % 8 == 0, "tensor records are zeroed with 8-byte stores");
+__global__ void __launch_bounds__(kSmallBatch) k_plan_small(DecTables T, uint64_t blob_cap, uint32_t tensor_cap, uint32_t span_cap,
+                                                            uint64_t pool_capacity) {
+  __shared__ uint64_t smem[kSmallBatch / 32 + 1];
+  const uint32_t mi = threadIdx.x;
+  if (mi < T.n_msgs) walk_body<false>(T, mi);
+  __syncthreads();
+  scan_counts_body<kSmallBatch / 32>(T, smem);
+  __syncthreads();
+  const uint64_t n_tensors = T.totals[TOT_TENSORS], n_filters = T.totals[TOT_FILTERS], n_spans = T.totals[TOT_SPANS],
+                 n_str = T.totals[TOT_STR], n_vt = T.totals[TOT_VTILES];
+  uint64_t p_flt, p_str, bytes;
+  blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &bytes);
+  if (bytes > blob_cap || n_tensors > tensor_cap || n_spans > span_cap) {
+    if (mi == 0) T.totals[TOT_RETRY] = 1;
+    return;
+  }
+  DecTables L = T;
+  uint8_t* blob = reinterpret_cast<uint8_t*>(T.tensors);
+  L.filters = reinterpret_cast<tfs_span_t*>(blob + p_flt);
+  L.strings = blob + p_str;
+  unsigned long long* z = reinterpret_cast<unsigned long long*>(blob);
+  for (uint64_t i = mi, n = n_tensors * (sizeof(tfs_tensor_out_t) / 8); i < n; i += kSmallBatch) z[i] = 0ull;
+  __syncthreads();
+  if (mi < L.n_msgs) walk_body<true>(L, mi);
+  if (n_vt != 0) return;  // the varint bodies have to be counted before the element totals are known
+  if (mi < L.n_msgs) finalize_body(L, mi);
+  __syncthreads();
+  pool_layout_body<kSmallBatch / 32>(L, static_cast<uint32_t>(n_tensors), pool_capacity, smem);
+}
+
 // at decode time: bind every copy-class span to its place in the caller's pool
 __global__ void __launch_bounds__(256) k_dec_bind(DecTables T, uint32_t n_spans, uint8_t* pool, const uint64_t* __restrict__ gate) {
   const uint32_t si = blockIdx.x * blockDim.x + threadIdx.x;
@@ -939,91 +982,167 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
 
   const uint32_t mblocks = (n_msgs + 127) / 128;
   const bool small = n_msgs <= kSmallBatch;
+  const uint64_t pool_cap_arg = pool_dev ? pool_capacity : ~0ull;
+  const size_t h1 = 0, h2 = align_up(res1_bytes, 64);
+  uint64_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0;
+  uint64_t p_flt = 0, p_str = 0, res2_bytes = 0;  // the result blob: tensors | filters | strings (one D2H)
+  size_t blob_copied = 0;                           // bytes of the blob that already are in h_down
+  bool planned = false;                             // small path, no varint bodies: the tables are final after sync #1
+  uint8_t* d2 = nullptr;
+  auto load_totals = [&](const uint8_t* hd) {
+    std::memcpy(dec->totals, hd, kTotalsBytes);
+    n_tensors = dec->totals[TOT_TENSORS];
+    n_filters = dec->totals[TOT_FILTERS];
+    n_spans = dec->totals[TOT_SPANS];
+    n_str = dec->totals[TOT_STR];
+    n_vt = dec->totals[TOT_VTILES];
+  };
+
   if (small) {
-    k_walk_count_small<<<1, kSmallBatch, 0, ctx->stream>>>(T);
-    ctx->launches++;
+    // ---- optimistic plan: tables laid out from this context's hints, both walks in one launch
+    for (int attempt = 0;; ++attempt) {
+      const uint64_t t_cap = std::max<uint64_t>(ctx->dec_hint_tensors, 4ull * n_msgs + 16), f_cap = std::max<uint64_t>(ctx->dec_hint_filters, 4ull * n_msgs + 16),
+                     s_cap = std::max<uint64_t>(ctx->dec_hint_spans, 8ull * n_msgs + 32), str_cap = std::max<uint64_t>(ctx->dec_hint_str, 256ull * n_msgs + 1024);
+      uint64_t q_flt, q_str, blob_cap;
+      blob_layout(t_cap, f_cap, str_cap, &q_flt, &q_str, &blob_cap);
+      cur = 0;
+      const size_t p_blob = carve(&cur, blob_cap), p_spn = carve(&cur, sizeof(DecSpan) * s_cap), p_sv = carve(&cur, 4 * (s_cap + 1)),
+                   p_sc = carve(&cur, 4 * (s_cap + 1)), p_seg = carve(&cur, sizeof(CopySeg) * s_cap), p_tp = carve(&cur, 8 * t_cap);
+      DEC_TRY(dev_reserve(ctx, &ctx->d_dec2, cur + 64));
+      d2 = static_cast<uint8_t*>(ctx->d_dec2.p);
+      T.tensors = reinterpret_cast<tfs_tensor_out_t*>(d2 + p_blob);
+      T.filters = nullptr;  // placed by blob_layout() once the counts are known (kernel and host agree)
+      T.strings = nullptr;
+      T.spans = reinterpret_cast<DecSpan*>(d2 + p_spn);
+      T.span_vtile0 = reinterpret_cast<uint32_t*>(d2 + p_sv);
+      T.span_ctile0 = reinterpret_cast<uint32_t*>(d2 + p_sc);
+      T.segs = reinterpret_cast<CopySeg*>(d2 + p_seg);
+      T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);
+      k_plan_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, blob_cap, static_cast<uint32_t>(std::min<uint64_t>(t_cap, 0xFFFFFFF0ull)),
+                                                      static_cast<uint32_t>(std::min<uint64_t>(s_cap, 0xFFFFFFF0ull)), pool_cap_arg);
+      ctx->launches++;
+      DEC_CUDA(cudaGetLastError());
+      const size_t guess = static_cast<size_t>(std::min<uint64_t>(blob_cap, std::max<uint64_t>(ctx->dec_hint_blob, 4096 + 512ull * n_msgs)));
+      DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, h2 + guess + 64));
+      uint8_t* hd = static_cast<uint8_t*>(ctx->h_down);
+      DEC_CUDA(cudaMemcpyAsync(hd + h1, d1 + o_tot, res1_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+      DEC_CUDA(cudaMemcpyAsync(hd + h2, d2 + p_blob, guess, cudaMemcpyDeviceToHost, ctx->stream));
+      DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1 (the only one when the batch has no varint bodies)
+      load_totals(hd + h1);
+      blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &res2_bytes);
+      ctx->dec_hint_tensors = std::max(ctx->dec_hint_tensors, n_tensors + n_tensors / 4);
+      ctx->dec_hint_filters = std::max(ctx->dec_hint_filters, n_filters + n_filters / 4);
+      ctx->dec_hint_spans = std::max(ctx->dec_hint_spans, n_spans + n_spans / 4);
+      ctx->dec_hint_str = std::max(ctx->dec_hint_str, n_str + n_str / 4);
+      ctx->dec_hint_blob = std::max<uint64_t>(ctx->dec_hint_blob, res2_bytes + res2_bytes / 4);
+      if (dec->totals[TOT_RETRY]) {
+        if (attempt >= 1) return bail(set_err(ctx, TFS_ERR_NOMEM, "decode plan did not fit its own tables"));
+        DEC_CUDA(cudaMemsetAsync(d1 + o_tot, 0, kTotalsBytes, ctx->stream));
+        continue;
+      }
+      blob_copied = guess;
+      break;
+    }
+    if (n_vt > 0xFFFFFFF0ull) return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large"));
+    T.filters = reinterpret_cast<tfs_span_t*>(reinterpret_cast<uint8_t*>(T.tensors) + p_flt);
+    T.strings = reinterpret_cast<uint8_t*>(T.tensors) + p_str;
+    planned = n_vt == 0;
+    if (n_vt) {
+      cur = 0;
+      const size_t p_tc = carve(&cur, 4 * n_vt), p_ts = carve(&cur, sizeof(TileRef) * n_vt), p_td = carve(&cur, sizeof(TileDst) * n_vt),
+                   p_tb = carve(&cur, 8 * n_vt);
+      DEC_TRY(dev_reserve(ctx, &ctx->d_dec3, cur + 64));
+      uint8_t* d3 = static_cast<uint8_t*>(ctx->d_dec3.p);
+      T.tile_count = reinterpret_cast<uint32_t*>(d3 + p_tc);
+      T.dtiles = reinterpret_cast<TileRef*>(d3 + p_ts);
+      T.dtile_dst = reinterpret_cast<TileDst*>(d3 + p_td);
+      T.tile_base = reinterpret_cast<uint64_t*>(d3 + p_tb);
+    }
   } else {
     k_walk<false><<<mblocks, 128, 0, ctx->stream>>>(T);
     ctx->launches++;
     k_scan_counts<<<1, 1024, 0, ctx->stream>>>(T);
     ctx->launches++;
-  }
-  DEC_CUDA(cudaGetLastError());
-  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, kTotalsBytes));
-  DEC_CUDA(cudaMemcpyAsync(ctx->h_down, T.totals, kTotalsBytes, cudaMemcpyDeviceToHost, ctx->stream));
-  DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1: the sizes of the pass-2 tables
-  std::memcpy(dec->totals, ctx->h_down, kTotalsBytes);
-  const uint64_t n_tensors = dec->totals[TOT_TENSORS], n_filters = dec->totals[TOT_FILTERS], n_spans = dec->totals[TOT_SPANS],
-                 n_str = dec->totals[TOT_STR], n_vt = dec->totals[TOT_VTILES];
-  if (n_tensors > 0xFFFFFFF0ull || n_spans > 0xFFFFFFF0ull || n_vt > 0xFFFFFFF0ull) return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large"));
-
-  // ---- pass 2 tables; tensors | filters | strings are contiguous: one D2H
-  cur = 0;
-  const size_t p_ten = carve(&cur, sizeof(tfs_tensor_out_t) * n_tensors), p_flt = carve(&cur, sizeof(tfs_span_t) * n_filters),
-               p_str = carve(&cur, n_str);
-  const size_t res2_bytes = cur;
-  const size_t p_spn = carve(&cur, sizeof(DecSpan) * n_spans), p_sv = carve(&cur, 4 * (n_spans + 1)),
-               p_sc = carve(&cur, 4 * (n_spans + 1)), p_tc = carve(&cur, 4 * n_vt), p_ts = carve(&cur, sizeof(TileRef) * n_vt), p_td = carve(&cur, sizeof(TileDst) * n_vt), p_tb = carve(&cur, 8 * n_vt),
-               p_seg = carve(&cur, sizeof(CopySeg) * n_spans), p_tp = carve(&cur, 8 * n_tensors);
-  DEC_TRY(dev_reserve(ctx, &ctx->d_dec2, cur + 64));
-  uint8_t* d2 = static_cast<uint8_t*>(ctx->d_dec2.p);
-  T.tensors = reinterpret_cast<tfs_tensor_out_t*>(d2 + p_ten);
-  T.filters = reinterpret_cast<tfs_span_t*>(d2 + p_flt);
-  T.strings = d2 + p_str;
-  T.spans = reinterpret_cast<DecSpan*>(d2 + p_spn);
-  T.span_vtile0 = reinterpret_cast<uint32_t*>(d2 + p_sv);
-  T.span_ctile0 = reinterpret_cast<uint32_t*>(d2 + p_sc);
-  T.tile_count = reinterpret_cast<uint32_t*>(d2 + p_tc);
-  T.dtiles = reinterpret_cast<TileRef*>(d2 + p_ts);
-  T.dtile_dst = reinterpret_cast<TileDst*>(d2 + p_td);
-  T.tile_base = reinterpret_cast<uint64_t*>(d2 + p_tb);
-  T.segs = reinterpret_cast<CopySeg*>(d2 + p_seg);
-  T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);
-  if (n_tensors) DEC_CUDA(cudaMemsetAsync(T.tensors, 0, sizeof(tfs_tensor_out_t) * n_tensors, ctx->stream));
-  const bool fuse_walk = small && n_vt == 0;  // nothing has to run between the pass-2 walk and finalize
-  if (n_msgs && !fuse_walk) {
-    k_walk<true><<<mblocks, 128, 0, ctx->stream>>>(T);
-    ctx->launches++;
-  }
-  if (n_vt) {
-    DEC_CUDA(cudaMemsetAsync(T.tile_count, 0, 4 * n_vt, ctx->stream));
-    k_dtile_map<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), static_cast<uint32_t>(n_vt));
-    ctx->launches++;
-    {
-      ProfScope prof(ctx, PK_VARINT_COUNT);
-      k_varint_count<<<static_cast<uint32_t>(n_vt), kDecThreads, 0, ctx->stream>>>(T);
+    DEC_CUDA(cudaGetLastError());
+    DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, kTotalsBytes));
+    DEC_CUDA(cudaMemcpyAsync(ctx->h_down, T.totals, kTotalsBytes, cudaMemcpyDeviceToHost, ctx->stream));
+    DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1: the sizes of the pass-2 tables
+    load_totals(static_cast<const uint8_t*>(ctx->h_down));
+    if (n_tensors > 0xFFFFFFF0ull || n_spans > 0xFFFFFFF0ull || n_vt > 0xFFFFFFF0ull) return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large"));
+    // ---- pass 2 tables; tensors | filters | strings are contiguous: one D2H
+    blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &res2_bytes);
+    cur = 0;
+    const size_t p_blob = carve(&cur, res2_bytes), p_spn = carve(&cur, sizeof(DecSpan) * n_spans), p_sv = carve(&cur, 4 * (n_spans + 1)),
+                 p_sc = carve(&cur, 4 * (n_spans + 1)), p_tc = carve(&cur, 4 * n_vt), p_ts = carve(&cur, sizeof(TileRef) * n_vt),
+                 p_td = carve(&cur, sizeof(TileDst) * n_vt), p_tb = carve(&cur, 8 * n_vt), p_seg = carve(&cur, sizeof(CopySeg) * n_spans),
+                 p_tp = carve(&cur, 8 * n_tensors);
+    DEC_TRY(dev_reserve(ctx, &ctx->d_dec2, cur + 64));
+    d2 = static_cast<uint8_t*>(ctx->d_dec2.p);
+    T.tensors = reinterpret_cast<tfs_tensor_out_t*>(d2 + p_blob);
+    T.filters = reinterpret_cast<tfs_span_t*>(d2 + p_blob + p_flt);
+    T.strings = d2 + p_blob + p_str;
+    T.spans = reinterpret_cast<DecSpan*>(d2 + p_spn);
+    T.span_vtile0 = reinterpret_cast<uint32_t*>(d2 + p_sv);
+    T.span_ctile0 = reinterpret_cast<uint32_t*>(d2 + p_sc);
+    T.tile_count = reinterpret_cast<uint32_t*>(d2 + p_tc);
+    T.dtiles = reinterpret_cast<TileRef*>(d2 + p_ts);
+    T.dtile_dst = reinterpret_cast<TileDst*>(d2 + p_td);
+    T.tile_base = reinterpret_cast<uint64_t*>(d2 + p_tb);
+    T.segs = reinterpret_cast<CopySeg*>(d2 + p_seg);
+    T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);
+    if (n_tensors) DEC_CUDA(cudaMemsetAsync(T.tensors, 0, sizeof(tfs_tensor_out_t) * n_tensors, ctx->stream));
+    if (n_msgs) {
+      k_walk<true><<<mblocks, 128, 0, ctx->stream>>>(T);
+      ctx->launches++;
     }
-    ctx->launches++;
-    k_span_scan<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);
-    ctx->launches++;
   }
-  if (small) {
-    k_fill_finalize_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_dev ? pool_capacity : ~0ull, fuse_walk ? 1 : 0);
-    ctx->launches++;
-  } else {
-    k_dec_finalize<<<mblocks, 128, 0, ctx->stream>>>(T);
-    ctx->launches++;
-    k_pool_layout<<<1, 1024, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_dev ? pool_capacity : ~0ull);
-    ctx->launches++;
-  }
-  DEC_CUDA(cudaGetLastError());
-  // one-call decode: the value kernels follow at once, gated on the device by "the pool is large enough"
-  if (pool_dev) DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), T.totals + TOT_OVERFLOW));
 
-  // ---- results to the host: (totals | msgs) and (tensors | filters | strings), two copies
+  if (!planned) {
+    if (n_vt) {
+      DEC_CUDA(cudaMemsetAsync(T.tile_count, 0, 4 * n_vt, ctx->stream));
+      k_dtile_map<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), static_cast<uint32_t>(n_vt));
+      ctx->launches++;
+      {
+        ProfScope prof(ctx, PK_VARINT_COUNT);
+        k_varint_count<<<static_cast<uint32_t>(n_vt), kDecThreads, 0, ctx->stream>>>(T);
+      }
+      ctx->launches++;
+      k_span_scan<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);
+      ctx->launches++;
+    }
+    if (small) {
+      k_fill_finalize_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_cap_arg, 0);
+      ctx->launches++;
+    } else {
+      k_dec_finalize<<<mblocks, 128, 0, ctx->stream>>>(T);
+      ctx->launches++;
+      k_pool_layout<<<1, 1024, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_cap_arg);
+      ctx->launches++;
+    }
+    DEC_CUDA(cudaGetLastError());
+    // one-call decode: the value kernels follow at once, gated on the device by "the pool is large enough"
+    if (pool_dev) DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), T.totals + TOT_OVERFLOW));
+    blob_copied = 0;
+  } else if (pool_dev && !dec->totals[TOT_OVERFLOW]) {
+    // planned: the host already knows the layout, the value kernels need no gate
+    DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), nullptr));
+  }
+
+  // ---- results to the host: (totals | msgs) and the blob (tensors | filters | strings)
+  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, h2 + res2_bytes + 64));
+  uint8_t* hd = static_cast<uint8_t*>(ctx->h_down);
+  if (!planned || blob_copied < res2_bytes) {
+    if (!planned) DEC_CUDA(cudaMemcpyAsync(hd + h1, d1 + o_tot, res1_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    if (res2_bytes) DEC_CUDA(cudaMemcpyAsync(hd + h2, T.tensors, res2_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #2: the caller needs the element counts (and, one-call, the values)
+    std::memcpy(dec->totals, hd + h1, kTotalsBytes);
+  }
   dec->msgs.resize(n_msgs);
   dec->tensors.resize(n_tensors);
   dec->filters.resize(n_filters);
   dec->strings.resize(n_str);
-  const size_t h1 = 0, h2 = align_up(res1_bytes, 64);
-  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, h2 + res2_bytes + 64));
-  uint8_t* hd = static_cast<uint8_t*>(ctx->h_down);
-  DEC_CUDA(cudaMemcpyAsync(hd + h1, d1 + o_tot, res1_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-  if (res2_bytes) DEC_CUDA(cudaMemcpyAsync(hd + h2, d2 + p_ten, res2_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-  DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #2: the caller needs the element counts (and, one-call, the values)
-  std::memcpy(dec->totals, hd + h1, kTotalsBytes);
   if (n_msgs) std::memcpy(dec->msgs.data(), hd + h1 + (o_msgs - o_tot), sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs));
-  if (n_tensors) std::memcpy(dec->tensors.data(), hd + h2 + p_ten, sizeof(tfs_tensor_out_t) * n_tensors);
+  if (n_tensors) std::memcpy(dec->tensors.data(), hd + h2, sizeof(tfs_tensor_out_t) * n_tensors);
   if (n_filters) std::memcpy(dec->filters.data(), hd + h2 + p_flt, sizeof(tfs_span_t) * n_filters);
   if (n_str) std::memcpy(dec->strings.data(), hd + h2 + p_str, n_str);
   dec->n_failed = static_cast<uint32_t>(dec->totals[TOT_FAILED]);

@@ -223,7 +223,10 @@ struct tfs_ctx {
   std::string err;
   uint64_t launches = 0;
   DevBuf d_tables, d_work, d_stage_in, d_stage_out;
-  DevBuf d_dec1, d_dec2;        // decode tables (pass 1 / pass 2); owned by the newest tfs_decoded handle
+  DevBuf d_dec1, d_dec2, d_dec3;  // decode tables (pass 1 / pass 2 / varint tiles); owned by the newest tfs_decoded handle
+  // small-batch decode plans its tables optimistically from what earlier batches on this context needed
+  uint64_t dec_hint_tensors = 0, dec_hint_filters = 0, dec_hint_spans = 0, dec_hint_str = 0, dec_hint_blob = 0;
+  bool copy_attr_set = false;
   uint64_t dec_generation = 0;
   uint64_t stage_generation = 0;  // bumped by every *_host call that reuses the staging buffers
   void* h_up = nullptr;

@@ -323,6 +323,28 @@ def test_decode_bad_message_fails_alone(codec):
     assert [m.status for m in got] == [0, abi.TFS_ERR_BUFFER_UNDERFLOW, 0, abi.TFS_ERR_INVALID_VARINT, 0, 0]
 
 
+def test_decode_plan_outgrows_its_first_tables():
+    """A small batch is planned optimistically from the context's hints (k_plan_small); one message with far more
+    tensors, spans, filters and key bytes than a fresh context guesses has to take the grow-and-retry path, and the
+    next, ordinary batch on the same context must still be right."""
+    fresh = tfs.GpuCodec(tfs.GpuContext(0))
+    try:
+        rng = np.random.default_rng(77)
+        outs = [("output_with_a_rather_long_name_%04d_" % i + "x" * 40,
+                 tfs.TensorProto(dtype=3, tensor_shape=tfs.TensorShapeProto([3]), int_val=rng.integers(-5, 5, 3, dtype=np.int32),
+                                 float_val=rng.standard_normal(2).astype(np.float32)))
+                for i in range(150)]
+        big = tfs.PredictRequest(tfs.ModelSpec("m"), outs, output_filter=["f%d" % i for i in range(90)])
+        for msgs in ([big], [workloads.c1_request()], [big, workloads.c1_request(), big]):
+            blobs = ob.encode_messages(msgs, abi.MSG_PREDICT_REQUEST)
+            st, got = gpu_decode_both(fresh, blobs, abi.MSG_PREDICT_REQUEST)
+            st_o, want = ob.decode_bytes(blobs, abi.MSG_PREDICT_REQUEST)
+            assert st == st_o == 0
+            helpers.assert_same_decoded(want, got, "request", "plan retry")
+    finally:
+        fresh.ctx.close()
+
+
 def test_decode_long_varint_runs_inside_big_span(codec):
     # a >10-byte varint deep inside a multi-tile packed body is only visible to the terminator kernel
     for pos in (5, 4090, 4096, 8191, 20000):
