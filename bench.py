@@ -168,7 +168,7 @@ def run_ours(args):
     for _ in range(args.warmup):
         step()
     ctx.prof_enable(True)
-    for k in range(6):
+    for k in range(8):
         ctx.prof_read(k, reset=True)
     sampler = ClockSampler(local)
     if rank == 0:
@@ -189,6 +189,8 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
     n_copy, ms_copy = ctx.prof_read(abi.PK_COPY_TMA)   # the TMA ring moves every payload byte of this workload
     n_gen, ms_gen = ctx.prof_read(abi.PK_COPY)          # the generic kernel only finds nothing to do here
+    n_walk, ms_walk = ctx.prof_read(abi.PK_WALK)        # decode plan (both structure walks), one launch per decode
+    n_frame, ms_frame = ctx.prof_read(abi.PK_FRAME)     # encode framing, one launch per encode
     ctx.prof_enable(False)
     if world > 1:
         t = torch.tensor([ms], device=dev, dtype=torch.float64)
@@ -257,6 +259,14 @@ def run_ours(args):
     # R payloads (fixed / content encode or decode = N*w_src + N*w_dst)
     alg_per_launch = 2.0 * R * C2_ELEMS * 4
     achieved = alg_per_launch / (ms_copy / max(1, n_copy) * 1e-3) / 1e9 if n_copy else None
+    # DRAM bytes of one k_copy_tma launch from the committed `ncu --set full` capture (only if it is of this batch size)
+    traffic, traffic_src = None, None
+    try:
+        tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")))["k_copy_tma"]
+        if tj["requests_per_variant"] == R:
+            traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
+    except (OSError, KeyError, ValueError):
+        pass
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -272,9 +282,12 @@ def run_ours(args):
                      "other_copy_kernel_avg_ms": round(ms_gen / max(1, n_gen), 4),
                      "achieved": round(achieved, 1) if achieved else None,
                      "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4) if achieved else None, "peak_source": peak_src,
-                     "traffic": None, "launches_timed": n_copy, "avg_launch_ms": round(ms_copy / max(1, n_copy), 4),
+                     "traffic": traffic, "traffic_source": traffic_src, "launches_timed": n_copy, "avg_launch_ms": round(ms_copy / max(1, n_copy), 4),
                      "algorithmic_bytes_per_launch": alg_per_launch,
-                     "step_frac_of_peak": round(2 * value / world / peak, 4)},
+                     "step_frac_of_peak": round(2 * value / world / peak, 4),
+                     "step_breakdown_ms": {"k_copy_tma": round(ms_copy / args.steps, 4), "k_plan_small": round(ms_walk / args.steps, 4),
+                                           "k_frame_small": round(ms_frame / args.steps, 4),
+                                           "rest (host syncs, table copies, k_dec_bind)": round((ms - ms_copy - ms_walk - ms_frame) / args.steps, 4)}},
         "cpu_baseline": cpu_baseline(R, budget_s=args.cpu_budget),
     }
     if world == 1 and not args.no_extras:

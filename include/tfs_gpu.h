@@ -277,7 +277,9 @@ enum {
   TFS_PK_VARINT_SCATTER = 2, /* K3 */
   TFS_PK_VARINT_COUNT = 3,   /* K4a */
   TFS_PK_VARINT_GATHER = 4,  /* K4c */
-  TFS_PK_COPY_TMA = 5        /* K5, TMA ring (source and destination congruent mod 16) */
+  TFS_PK_COPY_TMA = 5,       /* K5, TMA ring (source and destination congruent mod 16) */
+  TFS_PK_WALK = 6,           /* K6d, small-batch decode plan (both structure walks) */
+  TFS_PK_FRAME = 7           /* K6a-c, small-batch encode framing */
 };
 tfs_status_t tfs_prof_enable(tfs_ctx_t* ctx, int32_t on);
 tfs_status_t tfs_prof_read(tfs_ctx_t* ctx, int32_t kernel_id, uint64_t* launches_out, double* ms_out, int32_t reset);

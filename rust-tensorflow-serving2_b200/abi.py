@@ -146,4 +146,4 @@ TFS_ERR_TOO_LARGE = 24
 TFS_NOALLOC_MAX_ELEMS = 1 << 24
 STATUS_NAMES[TFS_ERR_TOO_LARGE] = "input exceeds TFS_NOALLOC_MAX_ELEMS"
 
-PK_COPY, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_COPY_TMA = range(6)
+PK_COPY, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_COPY_TMA, PK_WALK, PK_FRAME = range(8)

@@ -660,14 +660,7 @@ __global__ void __launch_bounds__(1024) k_scan_counts(DecTables T) {
   scan_counts_body<32>(T, smem);
 }
 
-// Small batches: pass-1 walk and the scans of its counters in ONE single-CTA launch
 constexpr uint32_t kSmallBatch = 256;
-__global__ void __launch_bounds__(kSmallBatch) k_walk_count_small(DecTables T) {
-  __shared__ uint64_t smem[kSmallBatch / 32 + 1];
-  if (threadIdx.x < T.n_msgs) walk_body<false>(T, threadIdx.x);
-  __syncthreads();
-  scan_counts_body<kSmallBatch / 32>(T, smem);
-}
 
 // K4b: per varint span, exclusive scan of its tile counts (one warp per span) -> tile_base, n_elems
 __global__ void __launch_bounds__(256) k_span_scan(DecTables T, uint32_t n_spans, uint64_t n_vtiles) {
@@ -793,15 +786,11 @@ __global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_te
   pool_layout_body<32>(T, n_tensors, pool_capacity, smem);
 }
 
-// Small batches: (pass-2 walk when no varint body has to be counted first,) finalize and pool layout in ONE
-// single-CTA launch
-__global__ void __launch_bounds__(kSmallBatch) k_fill_finalize_small(DecTables T, uint32_t n_tensors, uint64_t pool_capacity, int do_walk) {
+// Small batches: finalize and pool layout in ONE single-CTA launch
+__global__ void __launch_bounds__(kSmallBatch) k_finalize_small(DecTables T, uint32_t n_tensors, uint64_t pool_capacity) {
   __shared__ uint64_t smem[kSmallBatch / 32 + 1];
   const uint32_t mi = threadIdx.x;
-  if (mi < T.n_msgs) {
-    if (do_walk) walk_body<true>(T, mi);
-    finalize_body(T, mi);  // reads only what this thread's own walk wrote (and the counted varint spans)
-  }
+  if (mi < T.n_msgs) finalize_body(T, mi);  // reads what this message's walk wrote and the counted varint spans
   __syncthreads();
   pool_layout_body<kSmallBatch / 32>(T, n_tensors, pool_capacity, smem);
 }
@@ -1018,8 +1007,11 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       T.span_ctile0 = reinterpret_cast<uint32_t*>(d2 + p_sc);
       T.segs = reinterpret_cast<CopySeg*>(d2 + p_seg);
       T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);
-      k_plan_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, blob_cap, static_cast<uint32_t>(std::min<uint64_t>(t_cap, 0xFFFFFFF0ull)),
-                                                      static_cast<uint32_t>(std::min<uint64_t>(s_cap, 0xFFFFFFF0ull)), pool_cap_arg);
+      {
+        ProfScope prof(ctx, PK_WALK);
+        k_plan_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, blob_cap, static_cast<uint32_t>(std::min<uint64_t>(t_cap, 0xFFFFFFF0ull)),
+                                                        static_cast<uint32_t>(std::min<uint64_t>(s_cap, 0xFFFFFFF0ull)), pool_cap_arg);
+      }
       ctx->launches++;
       DEC_CUDA(cudaGetLastError());
       const size_t guess = static_cast<size_t>(std::min<uint64_t>(blob_cap, std::max<uint64_t>(ctx->dec_hint_blob, 4096 + 512ull * n_msgs)));
@@ -1111,7 +1103,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       ctx->launches++;
     }
     if (small) {
-      k_fill_finalize_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_cap_arg, 0);
+      k_finalize_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_cap_arg);
       ctx->launches++;
     } else {
       k_dec_finalize<<<mblocks, 128, 0, ctx->stream>>>(T);

@@ -610,7 +610,10 @@ tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_
     ctx->launches++;
   }
   if (T.n_msgs <= kSmallBatch) {
-    k_frame_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, dst, flags, dst_skew, dst_capacity, dst != nullptr);
+    {
+      ProfScope prof(ctx, PK_FRAME);
+      k_frame_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, dst, flags, dst_skew, dst_capacity, dst != nullptr);
+    }
     ctx->launches++;
   } else {
     k_msg_layout<<<(T.n_msgs + 127) / 128, 128, 0, ctx->stream>>>(T);

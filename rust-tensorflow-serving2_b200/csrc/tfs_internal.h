@@ -244,7 +244,7 @@ struct tfs_ctx {
 };
 
 namespace tfs {
-enum ProfKernel { PK_COPY = 0, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_COPY_TMA, PK_WALK, PK_COUNT_ };
+enum ProfKernel { PK_COPY = 0, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_COPY_TMA, PK_WALK, PK_FRAME, PK_COUNT_ };
 // Brackets one kernel launch with events when profiling is on (a no-op otherwise).
 struct ProfScope {
   tfs_ctx* ctx;
