@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define TFS_ABI_VERSION 1
+#define TFS_ABI_VERSION 2
 #define TFS_MAX_DIMS 8   /* dims carried inline per tensor; larger ranks -> TFS_ERR_UNSUPPORTED */
 #define TFS_N_SLOTS 12   /* payload field slots of a TensorProto, see tfs_slot_of_kind() */
 
@@ -70,7 +70,7 @@ enum {
   TFS_KIND_FLOAT_VAL = 5,      /* packed fixed32 */
   TFS_KIND_DOUBLE_VAL = 6,     /* packed fixed64 */
   TFS_KIND_INT_VAL = 7,        /* packed varint, int32 sign-extended */
-  TFS_KIND_STRING_VAL = 8,     /* repeated bytes (not packed) */
+  TFS_KIND_STRING_VAL = 8,     /* repeated bytes (not packed): one `42 len bytes` record per element; TFS_T_RAGGED */
   TFS_KIND_SCOMPLEX_VAL = 9,   /* packed fixed32 */
   TFS_KIND_INT64_VAL = 10,     /* packed varint */
   TFS_KIND_BOOL_VAL = 11,      /* packed varint 0/1 */
@@ -95,7 +95,11 @@ enum {
   TFS_T_BF16 = 10, /* bfloat16 bit pattern */
   TFS_T_F32 = 11,
   TFS_T_F64 = 12,
-  TFS_T_BOOL = 13  /* one byte per element, non-zero = true (Rust `bool`) */
+  TFS_T_BOOL = 13, /* one byte per element, non-zero = true (Rust `bool`) */
+  TFS_T_RAGGED = 14 /* `repeated bytes` (string_val, Rust Vec<Vec<u8>>) flattened into ONE block:
+                       (n_elems + 1) little-endian u64 offsets, then the bytes of all elements back to back;
+                       element i is bytes[offsets[i] .. offsets[i+1]), offsets[0] = 0. The decoder writes the
+                       same block into the value pool, so a decoded string_val can be encoded again as is. */
 };
 
 /* Arithmetic fused into the u8 -> f32 widening of float_val (reference src/lib.rs:237-242:
@@ -156,6 +160,8 @@ typedef struct {
   uint32_t _pad;
   uint64_t n_elems; /* number of source elements (bytes for raw tensor_content with src_type U8) */
   const void* data; /* device pointer for tfs_encode, host pointer for tfs_encode_host */
+  uint64_t aux;     /* TFS_KIND_STRING_VAL (src_type TFS_T_RAGGED): total bytes of all elements, i.e. offsets[n_elems]
+                       (the host needs it for tfs_encode_bound and cannot read device memory); 0 otherwise */
 } tfs_field_desc_t;
 
 /* One TensorProto together with the map key it is stored under (src/lib.rs:256-257). */
@@ -334,14 +340,17 @@ tfs_status_t tfs_decode_scan(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire
                              const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags,
                              tfs_decoded_t** out);
 tfs_status_t tfs_decoded_view(const tfs_decoded_t* dec, tfs_decoded_view_t* view);
-/* Pass 2: write every payload value into the device pool (pool_bytes >= view.pool_bytes). */
+/* Pass 2: write every payload value into the device pool (pool_bytes >= view.pool_bytes).  Asynchronous: the
+ * kernels are queued on the context's stream; tfs_sync() (or stream order) before anything else reads the pool. */
 tfs_status_t tfs_decode(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_dev, uint64_t pool_bytes);
 tfs_status_t tfs_decoded_free(tfs_ctx_t* ctx, tfs_decoded_t* dec);
 
 /* Both passes in one call, for callers that own a value pool of known capacity (the shim's staging pool):
  * the values are written right behind the scan, without a round trip to the host in between.  When the pool
  * turns out to be too small nothing is written and TFS_ERR_NOMEM is returned; the handle is still valid and
- * its view says how many bytes are needed (then call tfs_decode with a larger pool). */
+ * its view says how many bytes are needed (then call tfs_decode with a larger pool).  Like tfs_decode the
+ * value kernels may still be running when the call returns (the view is complete): tfs_sync() before the pool
+ * is read from the host or from another stream. */
 tfs_status_t tfs_decode_into(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off,
                              const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_dev,
                              uint64_t pool_capacity, tfs_decoded_t** out);
@@ -354,7 +363,7 @@ tfs_status_t tfs_decode_host(tfs_ctx_t* ctx, const void* wire_host, uint64_t wir
                              tfs_decoded_t** out);
 tfs_status_t tfs_decode_host_finish(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_host, uint64_t pool_bytes);
 /* Host-memory form of tfs_decode_into.  Pinned buffers (tfs_host_alloc) are read and written in place by the
- * kernels; pageable ones are staged through device memory. */
+ * kernels; pageable ones are staged through device memory.  Synchronous: the values are in pool_host on return. */
 tfs_status_t tfs_decode_host_into(tfs_ctx_t* ctx, const void* wire_host, uint64_t wire_bytes, const uint64_t* msg_off,
                                   const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_host,
                                   uint64_t pool_capacity, tfs_decoded_t** out);

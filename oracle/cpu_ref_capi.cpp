@@ -140,7 +140,21 @@ bool build_field(const tfs_field_desc_t& f, TensorProto* t) {
       }
       return true;
     }
-    default: return false;  // string_val and the message-typed fields are not on the encode ABI yet
+    case TFS_KIND_STRING_VAL: {  // TFS_T_RAGGED block: (n + 1) u64 offsets, then the bytes (tensor.proto:57)
+      if (f.src_type != TFS_T_RAGGED || (dst != TFS_T_NONE && dst != TFS_T_RAGGED)) return false;
+      const uint8_t* blk = as<uint8_t>(f);
+      std::vector<uint64_t> off(n + 1);
+      std::memcpy(off.data(), blk, 8 * (n + 1));
+      if (off[0] != 0 || off[n] != f.aux) return false;
+      const uint8_t* bytes = blk + 8 * (n + 1);
+      t->string_val.resize(n);
+      for (uint64_t i = 0; i < n; ++i) {
+        if (off[i + 1] < off[i]) return false;
+        t->string_val[i].assign(bytes + off[i], bytes + off[i + 1]);
+      }
+      return true;
+    }
+    default: return false;  // the message-typed fields (resource_handle_val, variant_val) are not on the encode ABI
   }
 }
 
@@ -299,7 +313,7 @@ bool emit_tensor(Decoded& d, uint32_t msg_index, const std::string& key, const T
     }
     std::memcpy(&blob[n * 8], &acc, 8);
     for (const auto& s : t.string_val) blob.insert(blob.end(), s.begin(), s.end());
-    put(8, TFS_T_U8, blob.data(), n, n ? blob.size() : 0);
+    put(8, TFS_T_RAGGED, blob.data(), n, n ? blob.size() : 0);
   }
   put(9, TFS_T_F32, t.scomplex_val.data(), t.scomplex_val.size(), t.scomplex_val.size() * 4);
   put(10, TFS_T_I64, t.int64_val.data(), t.int64_val.size(), t.int64_val.size() * 8);

@@ -6,7 +6,7 @@ src/lib.rs would.
 """
 import ctypes as C
 
-TFS_ABI_VERSION = 1
+TFS_ABI_VERSION = 2
 TFS_MAX_DIMS = 8
 TFS_N_SLOTS = 12
 
@@ -58,7 +58,7 @@ KIND_FIELD_NAMES = {
 }
 
 # element types
-T_NONE, T_U8, T_I8, T_U16, T_I16, T_I32, T_U32, T_I64, T_U64, T_F16, T_BF16, T_F32, T_F64, T_BOOL = range(14)
+T_NONE, T_U8, T_I8, T_U16, T_I16, T_I32, T_U32, T_I64, T_U64, T_F16, T_BF16, T_F32, T_F64, T_BOOL, T_RAGGED = range(15)
 TYPE_SIZE = {T_NONE: 0, T_U8: 1, T_I8: 1, T_U16: 2, T_I16: 2, T_I32: 4, T_U32: 4, T_I64: 8, T_U64: 8,
              T_F16: 2, T_BF16: 2, T_F32: 4, T_F64: 8, T_BOOL: 1}
 # numpy view dtype of each element type (16-bit floats are carried as their bit patterns)
@@ -89,7 +89,8 @@ class Str(C.Structure):
 
 class FieldDesc(C.Structure):
     _fields_ = [("kind", C.c_int32), ("src_type", C.c_int32), ("dst_type", C.c_int32), ("op", C.c_int32),
-                ("op_param", C.c_float), ("_pad", C.c_uint32), ("n_elems", C.c_uint64), ("data", C.c_void_p)]
+                ("op_param", C.c_float), ("_pad", C.c_uint32), ("n_elems", C.c_uint64), ("data", C.c_void_p),
+                ("aux", C.c_uint64)]
 
 
 class TensorDesc(C.Structure):

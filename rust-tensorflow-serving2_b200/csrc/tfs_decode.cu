@@ -244,6 +244,7 @@ struct Walker {
   }
   __device__ void add_span(uint32_t slot, uint32_t cls, uint64_t off, uint64_t len, uint64_t n_elems, uint32_t out_mult) {
     const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(w, off, len) : 0u;
+    if (cls == SC_STR && len) n_generic++;  // string bytes land wherever the earlier elements end: generic kernel
     if (cls == SC_COPY && len) {
       // Can the TMA ring take this span?  Its pool region starts on a 64-byte boundary, so the first chunk of
       // a slot is congruent mod 16 with its source iff the source address is 16-byte aligned.  A conservative
@@ -253,7 +254,7 @@ struct Walker {
     }
     seen_slots |= 1u << slot;
     // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
-    const uint32_t ct = cls == SC_COPY ? static_cast<uint32_t>((len * out_mult + kCopyTileBytes - 1) / kCopyTileBytes) + 1u : 0u;
+    const uint32_t ct = cls != SC_VARINT ? static_cast<uint32_t>((len * out_mult + kCopyTileBytes - 1) / kCopyTileBytes) + 1u : 0u;
     if (FILL) {
       DecSpan s;
       s.wire_off = off;
@@ -437,7 +438,16 @@ struct Walker {
       case 5: case 9: return repeated_fixed(slot_of(tag), wt, 4);
       case 6: case 12: return repeated_fixed(slot_of(tag), wt, 8);
       case 7: case 10: case 11: case 13: case 16: case 17: return repeated_varint(slot_of(tag), wt);
-      case 8: case 14: case 15: return fail(TFS_ERR_UNSUPPORTED);  // string_val / resource / variant: left to prost
+      case 8: {  // repeated bytes: every occurrence appends one element (bytes::merge_repeated)
+        if (!check_wt(WT_LEN, wt)) return false;
+        uint64_t len;
+        if (!varint(&len)) return false;
+        if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+        add_span(slot_of(8), SC_STR, pos, len, 1, 1);
+        pos += len;
+        return true;
+      }
+      case 14: case 15: return fail(TFS_ERR_UNSUPPORTED);  // resource_handle_val / variant_val: left to prost
       default: return skip(wt, tag, ctx);
     }
   }
@@ -697,6 +707,7 @@ __device__ __forceinline__ int32_t slot_dst_type(uint32_t slot, int32_t dtype, u
     case 1: case 5: return TFS_T_F32;
     case 2: case 8: return TFS_T_F64;
     case 3: return TFS_T_I32;
+    case 4: return TFS_T_RAGGED;
     case 6: return TFS_T_I64;
     case 7: return TFS_T_BOOL;
     case 9: return (half16 && (flags & TFS_F_HALF_TO_F32)) ? TFS_T_F32 : TFS_T_I32;
@@ -730,20 +741,29 @@ __device__ void finalize_body(const DecTables& T, uint32_t mi) {
   }
   const uint32_t s0 = T.cnt_spans[mi];
   const uint32_t s1 = mi + 1 < T.n_msgs ? T.cnt_spans[mi + 1] : static_cast<uint32_t>(T.totals[TOT_SPANS]);
+  // tensor_pool[] doubles as the running byte count of each tensor's string_val elements until it is assigned below
+  for (uint32_t ti = mo.first_tensor; ti < mo.first_tensor + mo.n_tensors; ++ti) T.tensor_pool[ti] = 0;
   for (uint32_t si = s0; si < s1; ++si) {
     DecSpan& s = T.spans[si];
     tfs_tensor_out_t& t = T.tensors[s.tensor];
     s.elem_base = t.n_elems[s.slot];
     t.n_elems[s.slot] += s.n_elems;
+    if (s.cls == SC_STR) {
+      s.elem_tile0 = T.tensor_pool[s.tensor];
+      T.tensor_pool[s.tensor] += s.len;
+    }
   }
   for (uint32_t ti = mo.first_tensor; ti < mo.first_tensor + mo.n_tensors; ++ti) {
     tfs_tensor_out_t& t = T.tensors[ti];
     uint64_t bytes = 0;
+    const uint64_t str_bytes = T.tensor_pool[ti];
     for (uint32_t sl = 0; sl < TFS_N_SLOTS; ++sl) {
       const int32_t ty = slot_dst_type(sl, t.dtype, T.flags, t.n_elems[sl]);
       t.dst_type[sl] = ty;
       t.dst_off[sl] = bytes;  // relative to the tensor's base for now
-      bytes += (slot_pool_bytes(sl, ty, t.n_elems[sl]) + 63u) & ~static_cast<uint64_t>(63);
+      // string_val: (n + 1) u64 offsets, then the bytes of all elements (TFS_T_RAGGED)
+      const uint64_t need = sl == 4 ? (t.n_elems[4] ? 8ull * (t.n_elems[4] + 1) + str_bytes : 0ull) : slot_pool_bytes(sl, ty, t.n_elems[sl]);
+      bytes += (need + 63u) & ~static_cast<uint64_t>(63);
     }
     T.tensor_pool[ti] = bytes;
   }
@@ -865,6 +885,19 @@ __global__ void __launch_bounds__(256) k_dec_bind(DecTables T, uint32_t n_spans,
       g.n = s.len;  // fixed-width values are copied as bytes
       g.dst = pool + t.dst_off[s.slot] + s.elem_base * type_size_dev(ty);
     }
+  } else if (s.cls == SC_STR && T.msgs[s.msg].status == TFS_OK) {
+    // one string_val element: its start offset into the offsets array (byte stores: the pool may sit at any address),
+    // its bytes behind the offsets
+    const tfs_tensor_out_t& t = T.tensors[s.tensor];
+    const uint64_t n = t.n_elems[s.slot];
+    uint8_t* block = pool + t.dst_off[s.slot];
+    auto put_u64 = [](uint8_t* p, uint64_t v) {
+      for (int i = 0; i < 8; ++i) p[i] = static_cast<uint8_t>(v >> (8 * i));
+    };
+    put_u64(block + 8 * s.elem_base, s.elem_tile0);
+    if (s.elem_base + 1 == n) put_u64(block + 8 * n, s.elem_tile0 + s.len);
+    g.n = s.len;
+    g.dst = block + 8 * (n + 1) + s.elem_tile0;
   }
   T.segs[si] = g;
 }

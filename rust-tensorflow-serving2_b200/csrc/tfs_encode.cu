@@ -12,6 +12,7 @@
 #include <cstring>
 
 #include "tfs_device.cuh"
+#include "tfs_ragged.cuh"
 #include "tfs_varint_enc.cuh"
 
 namespace tfs {
@@ -82,7 +83,9 @@ __device__ __forceinline__ uint64_t tensor_body_len(const EncTables& T, const En
   if (t.version_number != 0) n += 1u + varint_len(static_cast<uint64_t>(static_cast<int64_t>(t.version_number)));
   for (uint32_t i = 0; i < t.n_fields; ++i) {
     const EncField& f = T.fields[t.first_field + i];
-    if (f.n_elems != 0) n += key_len(f.kind) + varint_len(f.body_len) + f.body_len;
+    if (f.n_elems == 0) continue;
+    // repeated bytes: the record area carries a key and a length per element, nothing in front of it
+    n += f.is_varint == FC_RAGGED ? f.body_len : key_len(f.kind) + varint_len(f.body_len) + f.body_len;
   }
   return n;
 }
@@ -146,8 +149,10 @@ __device__ void emit_tensor_body(Sink& s, const EncTables& T, const EncTensor& t
     const uint32_t fi = t.first_field + i;
     const EncField& f = T.fields[fi];
     if (f.n_elems == 0) continue;
-    put_key(s, static_cast<uint32_t>(f.kind), 2);
-    put_varint(s, f.body_len);
+    if (f.is_varint != FC_RAGGED) {
+      put_key(s, static_cast<uint32_t>(f.kind), 2);
+      put_varint(s, f.body_len);
+    }
     on_body(fi, s.pos);
     s.skip(f.body_len);
   }
@@ -291,6 +296,7 @@ struct Compiled {
   std::vector<StrRef> filters;
   std::vector<uint8_t> strings;
   std::vector<uint32_t> vfield_first_tile, vfield_index;
+  std::vector<uint32_t> rfield_first_tile, rfield_first_out, rfield_index;
   std::vector<CopySeg> segs;
   uint64_t n_copy_tiles = 0;
   uint64_t bound = 0;  // upper bound of the encoded bytes
@@ -378,7 +384,16 @@ bool compile_field(const tfs_field_desc_t& f, EncField* o, uint64_t* max_body) {
       if (st == TFS_T_F32 && dt == TFS_T_F16) return varint_class(VM_F32_F16, 3);
       if (st == TFS_T_F32 && dt == TFS_T_BF16) return varint_class(VM_F32_BF16, 3);
       return false;
-    default: return false;  // string_val / message-typed fields: not on the encode ABI
+    case TFS_KIND_STRING_VAL: {  // repeated bytes, flattened: (n + 1) u64 offsets, then the bytes
+      if (st != TFS_T_RAGGED || (dt != TFS_T_NONE && dt != TFS_T_RAGGED) || (reinterpret_cast<uintptr_t>(f.data) & 7u) != 0) return false;
+      o->is_varint = FC_RAGGED;
+      o->aux = f.aux;
+      uint32_t vl = 1;
+      for (uint64_t v = f.aux; v >= 0x80; v >>= 7) ++vl;  // no element is longer than all of them together
+      *max_body = f.n_elems * (1 + vl) + f.aux;
+      return true;
+    }
+    default: return false;  // message-typed fields (resource_handle_val, variant_val): not on the encode ABI
   }
 }
 
@@ -459,6 +474,7 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
     c->bound += (flags & TFS_F_ALIGN_PAYLOAD) ? align_up(bound + 16, 16) : bound;
   }
   // tile tables
+  uint64_t rtiles = 0, routs = 0;
   for (uint32_t fi = 0; fi < b->n_fields; ++fi) {
     EncField& f = c->fields[fi];
     if (!field_used[fi] || f.n_elems == 0) {
@@ -466,7 +482,17 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
       f.n_tiles = 0;
       continue;
     }
-    if (f.is_varint) {
+    if (f.is_varint == FC_RAGGED) {
+      const uint64_t nt = (f.n_elems + kRagTile - 1) / kRagTile, no = (field_bound[fi] + kRagOutTile - 1) / kRagOutTile;
+      if (rtiles + nt > 0x7FFFFFFFull || routs + no > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (string_val tiles)");
+      f.first_tile = static_cast<uint32_t>(rtiles);
+      f.n_tiles = static_cast<uint32_t>(nt);
+      c->rfield_first_tile.push_back(static_cast<uint32_t>(rtiles));
+      c->rfield_first_out.push_back(static_cast<uint32_t>(routs));
+      c->rfield_index.push_back(fi);
+      rtiles += nt;
+      routs += no;
+    } else if (f.is_varint) {
       uint64_t nt = (f.n_elems + kVarintTile - 1) / kVarintTile;
       if (vtiles + nt > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (varint tiles)");
       f.first_tile = vtiles;
@@ -491,6 +517,8 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
     }
   }
   c->vfield_first_tile.push_back(vtiles);
+  c->rfield_first_tile.push_back(static_cast<uint32_t>(rtiles));
+  c->rfield_first_out.push_back(static_cast<uint32_t>(routs));
   // can the generic copy kernel be skipped?  Only the largest bulk body of a message is placed on a 16-byte
   // boundary by TFS_F_ALIGN_PAYLOAD, so every message may carry at most one bulk field, a plain byte copy
   // from a 16-byte aligned source, large enough for the TMA ring.
@@ -528,7 +556,8 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   size_t cur = 0;
   const size_t o_msgs = place(&cur, c.msgs), o_tensors = place(&cur, c.tensors), o_fields = place(&cur, c.fields),
                o_filters = place(&cur, c.filters), o_strings = place(&cur, c.strings), o_vft = place(&cur, c.vfield_first_tile),
-               o_vfi = place(&cur, c.vfield_index), o_segs = place(&cur, c.segs);
+               o_vfi = place(&cur, c.vfield_index), o_segs = place(&cur, c.segs), o_rft = place(&cur, c.rfield_first_tile),
+               o_rfo = place(&cur, c.rfield_first_out), o_rfi = place(&cur, c.rfield_index);
   const size_t total = align_up(cur, 16) + 16;
   TFS_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, total));
   TFS_TRY(dev_reserve(ctx, &ctx->d_tables, total));
@@ -544,10 +573,14 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   put(o_vft, c.vfield_first_tile.data(), c.vfield_first_tile.size() * 4);
   put(o_vfi, c.vfield_index.data(), c.vfield_index.size() * 4);
   put(o_segs, c.segs.data(), c.segs.size() * sizeof(CopySeg));
+  put(o_rft, c.rfield_first_tile.data(), c.rfield_first_tile.size() * 4);
+  put(o_rfo, c.rfield_first_out.data(), c.rfield_first_out.size() * 4);
+  put(o_rfi, c.rfield_index.data(), c.rfield_index.size() * 4);
   TFS_CUDA(ctx, cudaMemcpyAsync(ctx->d_tables.p, h, total, cudaMemcpyHostToDevice, ctx->stream));
 
   const uint32_t n_msgs = static_cast<uint32_t>(c.msgs.size()), n_tensors = static_cast<uint32_t>(c.tensors.size());
   const uint32_t n_vtiles = c.vfield_first_tile.back();
+  const uint32_t n_rtiles = c.rfield_first_tile.back(), n_routs = c.rfield_first_out.back();
   size_t w = 0;
   auto carve = [&](size_t bytes) {
     size_t off = align_up(w, 16);
@@ -557,7 +590,8 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   const size_t w_vt = carve(sizeof(VTile) * static_cast<size_t>(n_vtiles)), w_tf = carve(4ull * n_vtiles);
   const size_t w_tb = carve(4ull * n_vtiles), w_to = carve(8ull * n_vtiles), w_tl = carve(8ull * n_tensors),
                w_el = carve(8ull * n_tensors), w_sl = carve(8ull * n_msgs), w_ml = carve(8ull * n_msgs),
-               w_mp = carve(8ull * n_msgs), w_mo = carve(8ull * n_msgs), w_res = carve(16);
+               w_mp = carve(8ull * n_msgs), w_mo = carve(8ull * n_msgs), w_res = carve(32), w_rb = carve(8ull * n_rtiles),
+               w_ro = carve(8ull * n_rtiles);
   TFS_TRY(dev_reserve(ctx, &ctx->d_work, w + 16));
   uint8_t* d = static_cast<uint8_t*>(ctx->d_tables.p);
   uint8_t* k = static_cast<uint8_t*>(ctx->d_work.p);
@@ -581,6 +615,15 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   T.msg_pay_off = reinterpret_cast<uint64_t*>(k + w_mp);
   T.msg_off = reinterpret_cast<uint64_t*>(k + w_mo);
   T.result = reinterpret_cast<uint64_t*>(k + w_res);
+  T.rtile_bytes = reinterpret_cast<uint64_t*>(k + w_rb);
+  T.rtile_off = reinterpret_cast<uint64_t*>(k + w_ro);
+  T.rfield_first_tile = reinterpret_cast<uint32_t*>(d + o_rft);
+  T.rfield_first_out = reinterpret_cast<uint32_t*>(d + o_rfo);
+  T.rfield_index = reinterpret_cast<uint32_t*>(d + o_rfi);
+  T.n_rfields = static_cast<uint32_t>(c.rfield_index.size());
+  T.n_rtiles = n_rtiles;
+  T.n_routs = n_routs;
+  TFS_CUDA(ctx, cudaMemsetAsync(T.result, 0, 32, ctx->stream));
   T.n_msgs = n_msgs;
   T.n_tensors = n_tensors;
   T.n_fields = static_cast<uint32_t>(c.fields.size());
@@ -588,7 +631,6 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   T.n_vfields = static_cast<uint32_t>(c.vfield_index.size());
   T.n_vtiles = n_vtiles;
   T.n_segs = static_cast<uint32_t>(c.segs.size());
-  T._pad = 0;
   u->n_copy_tiles = c.n_copy_tiles;
   return TFS_OK;
 }
@@ -607,6 +649,12 @@ tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_
     ctx->launches++;
     const uint32_t warps_per_block = 256 / 32;
     k_field_scan<<<(T.n_vfields + warps_per_block - 1) / warps_per_block, 256, 0, ctx->stream>>>(T);
+    ctx->launches++;
+  }
+  if (T.n_rtiles) {  // repeated bytes (string_val): record sizes per tile, then the record area length per field
+    k_ragged_size<<<T.n_rtiles, kRagThreads, 0, ctx->stream>>>(T);
+    ctx->launches++;
+    k_ragged_scan<<<(T.n_rfields + 7) / 8, 256, 0, ctx->stream>>>(T);
     ctx->launches++;
   }
   if (T.n_msgs <= kSmallBatch) {
@@ -635,7 +683,7 @@ tfs_status_t fetch_results(tfs_ctx* ctx, const EncTables& T, uint64_t* msg_off_o
   const size_t n = T.n_msgs;
   const uint8_t* base = reinterpret_cast<const uint8_t*>(T.msg_len);
   const size_t o_off = reinterpret_cast<const uint8_t*>(T.msg_off) - base, o_res = reinterpret_cast<const uint8_t*>(T.result) - base;
-  const size_t bytes = o_res + 16;
+  const size_t bytes = o_res + 32;
   TFS_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, bytes));
   uint8_t* h = static_cast<uint8_t*>(ctx->h_down);
   TFS_CUDA(ctx, cudaMemcpyAsync(h, base, bytes, cudaMemcpyDeviceToHost, ctx->stream));
@@ -645,6 +693,7 @@ tfs_status_t fetch_results(tfs_ctx* ctx, const EncTables& T, uint64_t* msg_off_o
   const uint64_t* res = reinterpret_cast<const uint64_t*>(h + o_res);
   if (total_out) *total_out = res[0];
   *overflow = res[1] != 0;
+  if (res[2] != 0) return set_err(ctx, TFS_ERR_INVALID_ARG, "string_val: the offsets in memory are not ascending from 0 to the stated total (aux)");
   return TFS_OK;
 }
 
@@ -670,6 +719,10 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
         ProfScope prof(ctx, PK_VARINT_SCATTER);
         k_varint_scatter<<<T.n_vtiles, kVarintThreads, 0, ctx->stream>>>(T, dst);
       }
+      ctx->launches++;
+    }
+    if (T.n_routs) {
+      k_ragged_copy<<<T.n_routs, kRagThreads, 0, ctx->stream>>>(T, dst);
       ctx->launches++;
     }
     TFS_CUDA(ctx, cudaGetLastError());

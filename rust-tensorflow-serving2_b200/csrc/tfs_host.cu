@@ -78,12 +78,17 @@ tfs_status_t tfs_encode_host(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst
   std::vector<tfs_field_desc_t> fields(batch->fields, batch->fields + batch->n_fields);
   std::vector<uint64_t> at(batch->n_fields, ~0ull);
   uint64_t in_bytes = 0;
+  auto src_bytes = [](const tfs_field_desc_t& f) -> uint64_t {
+    if (f.src_type == TFS_T_RAGGED) return f.n_elems ? 8ull * (f.n_elems + 1) + f.aux : 0ull;  // offsets, then the bytes
+    return f.n_elems * tfs_type_size(f.src_type);
+  };
   for (uint32_t i = 0; i < batch->n_fields; ++i) {
-    const uint32_t w = tfs_type_size(fields[i].src_type);
-    const uint64_t b = fields[i].n_elems * w;
+    const uint32_t w = fields[i].src_type == TFS_T_RAGGED ? 1u : tfs_type_size(fields[i].src_type);
+    const uint64_t b = src_bytes(fields[i]);
     if (b && (!fields[i].data || w == 0)) return set_err(ctx, TFS_ERR_INVALID_ARG, "payload field without data or type");
     if (!b) continue;
-    void* alias = is_varint_kind(fields[i].kind) ? nullptr : device_alias(fields[i].data);
+    // read more than once by the kernels (sizing + writing): varint-coded arrays and ragged blocks go to HBM first
+    void* alias = (is_varint_kind(fields[i].kind) || fields[i].src_type == TFS_T_RAGGED) ? nullptr : device_alias(fields[i].data);
     if (alias) {
       fields[i].data = alias;
     } else {
@@ -95,7 +100,7 @@ tfs_status_t tfs_encode_host(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst
   uint8_t* din = static_cast<uint8_t*>(ctx->d_stage_in.p);
   for (uint32_t i = 0; i < batch->n_fields; ++i) {
     if (at[i] == ~0ull) continue;
-    const uint64_t b = fields[i].n_elems * tfs_type_size(fields[i].src_type);
+    const uint64_t b = src_bytes(fields[i]);
     TFS_CUDA(ctx, cudaMemcpyAsync(din + at[i], fields[i].data, b, cudaMemcpyHostToDevice, ctx->stream));
     fields[i].data = din + at[i];
   }
@@ -160,6 +165,8 @@ tfs_status_t tfs_decode_host_into(tfs_ctx_t* ctx, const void* wire_host, uint64_
   tfs_status_t st;
   if (alias) {
     st = decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, alias, pool_capacity, out);
+    // the value kernels may still be writing the host pool (the device-pool form is asynchronous): wait for them
+    if (*out) TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   } else {
     TFS_TRY(dev_reserve(ctx, &ctx->d_stage_out, pool_capacity + 256));
     st = decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, ctx->d_stage_out.p, pool_capacity, out);

@@ -74,8 +74,10 @@ struct EncField {
   int32_t kind;        // TFS_KIND_*
   int32_t mode;        // VarintMode or CopyOp
   float op_param;
-  uint32_t is_varint;
+  uint32_t is_varint;  // FieldClass
+  uint64_t aux;        // ragged class: total bytes of the elements as the descriptor states them
 };
+enum FieldClass : uint32_t { FC_COPY = 0, FC_VARINT = 1, FC_RAGGED = 2 };
 
 // One 2048-element tile of a varint-coded field (built on the device by k_tile_map).
 struct VTile {
@@ -123,6 +125,9 @@ struct EncTables {
   uint32_t* vfield_first_tile;  // [n_vfields + 1]
   uint32_t* vfield_index;       // [n_vfields] -> index into fields
   CopySeg* segs;                // [n_segs]
+  uint32_t* rfield_first_tile;  // [n_rfields + 1] ragged fields: first sizing tile (2048 elements each)
+  uint32_t* rfield_first_out;   // [n_rfields + 1] first copy tile (16 KiB of records each, from the host's upper bound)
+  uint32_t* rfield_index;       // [n_rfields] -> index into fields
   // work arrays
   VTile* vtiles;                // [n_vtiles]
   uint32_t* tile_field;         // [n_vtiles] index into fields
@@ -134,15 +139,19 @@ struct EncTables {
   uint64_t* msg_len;            // [n_msgs]
   uint64_t* msg_pay_off;        // [n_msgs] offset (inside the message) of its largest bulk payload
   uint64_t* msg_off;            // [n_msgs]
-  uint64_t* result;             // [2]: total bytes, overflow flag
+  uint64_t* rtile_bytes;        // [n_rtiles] wire bytes of the records of each ragged sizing tile
+  uint64_t* rtile_off;          // [n_rtiles] exclusive prefix inside the field's record area
+  uint64_t* result;             // [4]: total bytes, overflow flag, ragged offsets invalid, -
   uint32_t n_msgs, n_tensors, n_fields, n_filters;
-  uint32_t n_vfields, n_vtiles, n_segs, _pad;
+  uint32_t n_vfields, n_vtiles, n_segs, n_rfields;
+  uint32_t n_rtiles, n_routs;
 };
 
 // ---- decode ---------------------------------------------------------------------------------------
 enum SpanClass : uint32_t {
   SC_VARINT = 0,  // packed or single varint(s) -> slot element type
   SC_COPY = 1,    // fixed-width packed body / tensor_content / single fixed value
+  SC_STR = 2,     // one string_val element (repeated bytes: one span per element, never packed)
 };
 
 // One contiguous run of payload bytes found by the structure walk.
@@ -156,7 +165,7 @@ struct DecSpan {
   uint32_t msg;
   uint32_t cls;        // SpanClass
   uint64_t first_tile; // exclusive prefix of tiles (per class)
-  uint64_t elem_tile0; // varint: index into tile_count[] of its first tile (== first_tile)
+  uint64_t elem_tile0; // varint: index into tile_count[] of its first tile (== first_tile); string: byte offset inside the tensor's string bytes
 };
 
 // One 4 KiB tile of a packed varint body (k_dtile_map) and where its values go (k_dtile_bind).

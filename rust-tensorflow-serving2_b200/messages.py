@@ -140,6 +140,27 @@ def _mk_str(s, keep):
     return abi.Str(C.cast(buf, C.c_void_p), len(b), 0)
 
 
+def ragged_block(strings) -> np.ndarray:
+    """`repeated bytes` (a list of bytes-like elements) flattened into the TFS_T_RAGGED block the ABI takes and the
+    decoder returns: (n + 1) little-endian u64 offsets, then the bytes of all elements."""
+    n = len(strings)
+    offs = np.zeros(n + 1, dtype="<u8")
+    if n:
+        offs[1:] = np.cumsum([len(s) for s in strings], dtype=np.uint64)
+    blob = np.empty(8 * (n + 1) + int(offs[n]), dtype=np.uint8)
+    blob[: 8 * (n + 1)] = offs.view(np.uint8)
+    blob[8 * (n + 1):] = np.frombuffer(b"".join(bytes(s) for s in strings), dtype=np.uint8)
+    return blob
+
+
+@dataclass
+class Ragged:
+    """A TFS_T_RAGGED block that already lives where the encoder needs it (host numpy array or torch tensor of uint8)."""
+    block: Any
+    n_elems: int
+    total_bytes: int
+
+
 def build_batch(messages, kind) -> BuiltBatch:
     """Turn a list of TensorProto / PredictRequest / PredictResponse into a tfs_batch_t."""
     keep: list = []
@@ -161,6 +182,20 @@ def build_batch(messages, kind) -> BuiltBatch:
         td.first_field = len(fld_l)
         n = 0
         for k, v in t.payloads():
+            if k == abi.KIND_STRING_VAL:  # repeated bytes: a list of bytes-like elements, or a ready block
+                if not isinstance(v, Ragged):
+                    blk = ragged_block(v)
+                    v = Ragged(blk, len(v), blk.size - 8 * (len(v) + 1))
+                ptr, _, ty, ka = _array_info(v.block)
+                if ty != abi.T_U8:
+                    raise TypeError("a ragged block is a uint8 array")
+                keep.append(ka)
+                fd = abi.FieldDesc()
+                fd.kind, fd.src_type, fd.dst_type, fd.op = k, abi.T_RAGGED, abi.T_NONE, abi.OP_NONE
+                fd.n_elems, fd.data, fd.aux = v.n_elems, ptr, v.total_bytes
+                fld_l.append(fd)
+                n += 1
+                continue
             p = v if isinstance(v, Payload) else Payload(v, abi.T_NONE)
             ptr, count, ty, ka = _array_info(p.data)
             keep.append(ka)

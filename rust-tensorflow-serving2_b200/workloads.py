@@ -11,7 +11,7 @@ from typing import List
 import numpy as np
 
 from . import abi
-from .messages import ModelSpec, Payload, PredictRequest, PredictResponse, TensorProto, TensorShapeProto
+from .messages import ModelSpec, Payload, PredictRequest, PredictResponse, Ragged, TensorProto, TensorShapeProto, ragged_block
 
 
 def c1_request() -> PredictRequest:
@@ -142,6 +142,11 @@ def to_device(messages, kind, device):
     def mv(v):
         if v is None:
             return None
+        if isinstance(v, Ragged):
+            return Ragged(torch.as_tensor(np.ascontiguousarray(v.block)).to(device), v.n_elems, v.total_bytes)
+        if isinstance(v, list):  # string_val given as a list of bytes-like elements
+            blk = ragged_block(v)
+            return Ragged(torch.from_numpy(blk).to(device), len(v), blk.size - 8 * (len(v) + 1))
         if isinstance(v, Payload):
             t, implied = mv_raw(v.data)
             return Payload(t, v.src_type if v.src_type != abi.T_NONE else implied, v.dst_type, v.op, v.op_param)

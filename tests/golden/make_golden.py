@@ -102,6 +102,9 @@ def tensor_desc(dtype=0, shape=None, unknown_rank=False, version_number=0, **fie
     d = {"dtype": int(dtype), "shape": None if shape is None else [int(x) for x in shape],
          "unknown_rank": bool(unknown_rank), "version_number": int(version_number), "fields": {}}
     for k, v in fields.items():
+        if k == "string_val":  # repeated bytes: a list of hex strings
+            d["fields"][k] = [bytes(x).hex() for x in v]
+            continue
         d["fields"][k] = arr_hex(np.asarray(v).astype(FIELD_NP[k]))
     return d
 
@@ -115,6 +118,9 @@ def fill_tensor(pb, d):
             pb.tensor_shape.dim.add().size = s
         pb.tensor_shape.unknown_rank = d["unknown_rank"]
     for k, hx in d["fields"].items():
+        if k == "string_val":
+            pb.string_val.extend([bytes.fromhex(x) for x in hx])
+            continue
         a = np.frombuffer(bytes.fromhex(hx), dtype=FIELD_NP[k])
         if k == "tensor_content":
             pb.tensor_content = a.tobytes()
@@ -176,6 +182,8 @@ def tensor_from_pb(pb):
     if pb.HasField("tensor_shape"):
         d["shape"] = [int(x.size) for x in pb.tensor_shape.dim]
         d["unknown_rank"] = bool(pb.tensor_shape.unknown_rank)
+    if len(pb.string_val):
+        d["fields"]["string_val"] = [bytes(x).hex() for x in pb.string_val]
     # re-serialise each repeated field alone to get exact bits (python float access quiets sNaNs)
     for k, npdt in FIELD_NP.items():
         if k == "tensor_content":
@@ -311,6 +319,17 @@ def encode_cases():
                     ["out3", tensor_desc(2, [1], tensor_content=np.array([3.5], np.float64).view(np.uint8))]]})
     add("utf8_names", "response", {"model_spec": {"name": "mödel-✓", "signature_name": "签名", "version": None, "version_label": None},
                                    "entries": [["ключ", tensor_desc(1, [1], float_val=[1.0])]]})
+    # string_val (tensor.proto:57): repeated bytes, one record per element, never packed
+    add("string_val_basic", "tensor", tensor_desc(7, [3], string_val=[b"hello", b"", b"world!!"]))
+    add("string_val_between_int_and_scomplex", "tensor", tensor_desc(7, [2], int_val=[1, -2], string_val=[b"a", b"\x00\xff\x80"], scomplex_val=[1.5, 2.5]))
+    add("string_val_len_127_128", "tensor", tensor_desc(7, [2], string_val=[bytes(range(127)), bytes(i % 251 for i in range(128))]))
+    srng = np.random.default_rng(808)
+    add("string_val_many_small", "tensor", tensor_desc(7, [300], string_val=[srng.integers(0, 256, int(srng.integers(0, 20)), dtype=np.uint8).tobytes() for _ in range(300)]))
+    add("string_val_one_16k", "tensor", tensor_desc(7, [1], string_val=[srng.integers(0, 256, 16384 + 3, dtype=np.uint8).tobytes()]))
+    add("string_request", "request", {
+        "model_spec": {"name": "text", "signature_name": "serving_default", "version": None, "version_label": None},
+        "entries": [["examples", tensor_desc(7, [2], string_val=["serialized example one".encode(), "zwei \u2713".encode()])],
+                    ["weights", tensor_desc(1, [2], float_val=[0.5, 0.25])]], "output_filter": ["scores"]})
     big = np.random.default_rng(2001).standard_normal(3 * 32 * 32).astype(np.float32)
     add("resnet_shape_small_image_float_val", "request", {
         "model_spec": {"name": "resnet", "signature_name": "serving_default", "version": None, "version_label": None},
@@ -343,6 +362,8 @@ def decode_cases():
     add("unpacked_and_chunks_int_val", "tensor", bytes.fromhex("38013a0202033a0104"))
     add("unpacked_floats", "tensor", key(5, 5) + f32le(1.0) + key(5, 5) + f32le(2.0) + ld(5, f32le(3.0, 4.0)))
     add("unpacked_doubles", "tensor", key(6, 1) + f64le(1.0) + ld(6, f64le(2.0)) + key(6, 1) + f64le(3.0))
+    add("string_val_interleaved", "tensor", ld(8, b"first") + vi(1, 7) + ld(8, b"") + ld(7, b"\x01\x02") + ld(8, b"third one") + vi(7, 3))
+    add("string_val_not_utf8", "tensor", ld(8, b"\xff\xfe\x80") + ld(8, b"\xc3\x28"))
     add("out_of_order_fields", "tensor", ld(5, f32le(1.0)) + vi(1, 1) + ld(2, ld(2, vi(1, 3))))
     add("scalar_last_wins", "tensor", vi(1, 1) + vi(1, 9) + vi(3, 7) + vi(3, 5))
     add("nonminimal_varints", "tensor", key(1, 0) + bytes.fromhex("8100") + ld(7, bytes.fromhex("818000ff8000")))
@@ -398,6 +419,9 @@ def error_cases():
         ("content_len_past_end", "tensor", "2205010203", E["underflow"]),
         ("dtype_wrong_wire_type", "tensor", "0a0101", E["wiretype"]),
         ("float_val_wrong_wire_type", "tensor", "2801", E["wiretype"]),
+        ("string_val_wrong_wire_type", "tensor", "4005", E["wiretype"]),
+        ("string_val_len_past_end", "tensor", "4205616263", E["underflow"]),
+        ("string_val_len_unterminated", "tensor", "42ff", E["varint"]),
         ("int_val_fixed32_wire_type", "tensor", "3d01000000", E["wiretype"]),
         ("content_varint_wire_type", "tensor", "2001", E["wiretype"]),
         ("wire_type_6", "tensor", "0e", E["wiretype_value"]),
@@ -443,7 +467,7 @@ def main():
         # upb must also read its own bytes back to the same description (sanity of this generator)
         back = upb_parse(c["kind"], bytes.fromhex(c["wire"]))
         if c["kind"] == "tensor":
-            ok = back == c["msg"] or any("7fa00001" in v or "0100a07f" in v or "f47f" in v for v in c["msg"]["fields"].values())
+            ok = back == c["msg"] or any("7fa00001" in v or "0100a07f" in v or "f47f" in v for v in c["msg"]["fields"].values() if isinstance(v, str))
             assert ok, (c["name"], back, c["msg"])
     doc = {"generator": "tests/golden/make_golden.py", "protobuf": __import__("google.protobuf").protobuf.__version__,
            "encode": enc, "decode": decode_cases(), "errors": error_cases()}

@@ -33,6 +33,9 @@ def tensor_from_desc(d) -> tfs.TensorProto:
     if d["shape"] is not None:
         t.tensor_shape = tfs.TensorShapeProto(list(d["shape"]), d["unknown_rank"])
     for k, hx in d["fields"].items():
+        if k == "string_val":
+            t.string_val = [bytes.fromhex(x) for x in hx]
+            continue
         a = np.frombuffer(bytes.fromhex(hx), dtype=FIELD_NP[k]).copy()
         if k == "bool_val":
             a = a.astype(np.bool_)

@@ -36,7 +36,7 @@ def test_exports_match_header():
 def test_struct_layouts_match_header():
     # sizes the C compiler gives the structs (spot-checked constants; a layout drift breaks the ABI)
     assert C.sizeof(abi.Span) == 16 and C.sizeof(abi.Str) == 16
-    assert C.sizeof(abi.FieldDesc) == 40
+    assert C.sizeof(abi.FieldDesc) == 48
     assert C.sizeof(abi.TensorDesc) == 16 + 4 * 8 + 8 * abi.TFS_MAX_DIMS
     assert C.sizeof(abi.MsgDesc) == 8 + 3 * 16 + 8 + 8 + 16
     assert C.sizeof(abi.TensorOut) == 16 + 6 * 4 + 8 * abi.TFS_MAX_DIMS + 20 * abi.TFS_N_SLOTS

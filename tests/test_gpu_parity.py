@@ -53,6 +53,9 @@ def pinned_like(msgs, kind):
             return None
         if isinstance(v, tfs.Payload):
             return tfs.Payload(mv(v.data), v.src_type if v.src_type != abi.T_NONE else tfs.messages._array_info(v.data)[2], v.dst_type, v.op, v.op_param)
+        if isinstance(v, list):  # string_val
+            blk = tfs.ragged_block(v)
+            return tfs.Ragged(mv(blk), len(v), blk.size - 8 * (len(v) + 1))
         a = np.ascontiguousarray(v)
         if a.size == 0:
             return a
@@ -265,6 +268,7 @@ def gpu_decode_both(codec, blobs, kind, flags=0):
     # one-call forms: device pool of exactly the needed size, and pinned host buffers used in place
     pool = torch.empty(max(16, d.pool_bytes), dtype=torch.uint8, device=dwire.device)
     d2 = dec.decode_into(dwire[3: 3 + cur] if cur else dwire[:0], offs, lens, kind, pool, flags)
+    codec.ctx.sync()  # the device-pool forms are asynchronous
     helpers.assert_same_decoded(host_msgs, d2.messages(), helpers_kind(kind), "two-call vs one-call decode")
     pwire = torch.empty(max(1, cur), dtype=torch.uint8).pin_memory()
     pwire.numpy()[:cur] = wire
@@ -426,15 +430,73 @@ def test_decode_fuzz_against_oracle(codec):
     st, got = gpu_decode_both(codec, blobs, abi.MSG_PREDICT_RESPONSE)
     mism = []
     for i, (w, g) in enumerate(zip(want, got)):
-        # string_val (tag 8) is decoded by the oracle but left to prost by the library for now: the
-        # library stops at the field with UNSUPPORTED, whatever follows it
-        if g.status == abi.TFS_ERR_UNSUPPORTED:
-            continue
         if w.status != g.status:
             mism.append((i, blobs[i].hex(), abi.STATUS_NAMES.get(w.status), abi.STATUS_NAMES.get(g.status)))
         elif w.status == 0:
             helpers.assert_same_decoded([w], [g], "response", f"fuzz {i}: {blobs[i].hex()}")
     assert not mism, mism[:5]
+
+
+# ---- string_val: repeated bytes -------------------------------------------------
+def _strings(rng, sizes):
+    return [rng.integers(0, 256, int(n), dtype=np.uint8).tobytes() for n in sizes]
+
+
+@pytest.mark.parametrize("shape", ["one_empty", "tiny_2047", "tiny_2048", "tiny_2049", "tiny_5000", "mixed_sizes", "big_1MiB", "edges_16k"])
+def test_string_val_roundtrip(codec, shape):
+    rng = np.random.default_rng(hash(shape) % 1000)
+    sizes = {
+        "one_empty": [0],
+        "tiny_2047": rng.integers(0, 12, 2047), "tiny_2048": rng.integers(0, 12, 2048), "tiny_2049": rng.integers(0, 12, 2049),
+        "tiny_5000": rng.integers(0, 40, 5000),
+        "mixed_sizes": [0, 1, 127, 128, 129, 16383, 16384, 16385, 70000, 3, 0, 0, 5, 200000, 15, 16, 17],
+        "big_1MiB": [1 << 20, 1, (1 << 20) + 7],
+        "edges_16k": [16384 - 2, 16384 - 3, 16384 - 1, 2 * 16384, 1],
+    }[shape]
+    strs = _strings(rng, sizes)
+    t = tfs.TensorProto(dtype=7, tensor_shape=tfs.TensorShapeProto([len(strs)]), string_val=strs)
+    mixed = tfs.TensorProto(dtype=7, int_val=np.arange(5, dtype=np.int32), string_val=strs[:50],
+                            scomplex_val=rng.standard_normal(6).astype(np.float32), tensor_content=np.arange(33, dtype=np.uint8))
+    roundtrip_check(codec, [t, mixed, t], abi.MSG_TENSOR_PROTO, f"string_val {shape}")
+    req = tfs.PredictRequest(tfs.ModelSpec("text", signature_name="serving_default"),
+                             [("examples", t), ("x", tfs.TensorProto(dtype=1, float_val=rng.standard_normal(9000).astype(np.float32)))],
+                             output_filter=["y"])
+    roundtrip_check(codec, [req, req], abi.MSG_PREDICT_REQUEST, f"string_val request {shape}", abi.F_GRPC_PREFIX)
+
+
+def test_string_val_decoded_block_encodes_again(codec):
+    """The decoder writes string_val as the same TFS_T_RAGGED block the encoder takes: feed it straight back (on the device)."""
+    import torch
+    rng = np.random.default_rng(5)
+    strs = _strings(rng, rng.integers(0, 300, 700))
+    wire = ob.encode_messages([tfs.TensorProto(dtype=7, string_val=strs)], abi.MSG_TENSOR_PROTO)[0]
+    dwire = torch.from_numpy(np.frombuffer(wire, dtype=np.uint8).copy()).cuda()
+    d = codec.decoder().decode(dwire, [0], [len(wire)], abi.MSG_TENSOR_PROTO)
+    codec.ctx.sync()
+    to = d.view.tensors[0]
+    slot = abi.SLOT_KINDS.index(abi.KIND_STRING_VAL)
+    n, off = int(to.n_elems[slot]), int(to.dst_off[slot])
+    assert n == len(strs) and int(to.dst_type[slot]) == abi.T_RAGGED
+    total = sum(len(x) for x in strs)
+    block = d.pool[off: off + 8 * (n + 1) + total]
+    again = tfs.TensorProto(dtype=7, string_val=tfs.Ragged(block, n, total))
+    eb = codec.encoder().encode([again], abi.MSG_TENSOR_PROTO)
+    assert eb.all_bytes() == [wire]
+
+
+def test_string_val_descriptor_must_match_memory(codec):
+    blk = tfs.ragged_block([b"abc", b"de"])
+    bad_total = tfs.TensorProto(dtype=7, string_val=tfs.Ragged(blk, 2, 6))  # the offsets end at 5
+    with pytest.raises(tfs.TfsError) as e:
+        codec.encoder().encode_host([bad_total], abi.MSG_TENSOR_PROTO)
+    assert e.value.status == abi.TFS_ERR_INVALID_ARG
+    desc = blk.copy()
+    desc[8:16] = np.array([4], dtype="<u8").view(np.uint8)   # offsets 0, 4, 5 -> fine; then make them descend
+    desc[16:24] = np.array([2], dtype="<u8").view(np.uint8)
+    with pytest.raises(tfs.TfsError):
+        codec.encoder().encode_host([tfs.TensorProto(dtype=7, string_val=tfs.Ragged(desc, 2, 2))], abi.MSG_TENSOR_PROTO)
+    # and the context is still usable
+    assert codec.encoder().encode_host([tfs.TensorProto(dtype=7, string_val=[b"ok"])], abi.MSG_TENSOR_PROTO).all_bytes() == [bytes.fromhex("0807" "42026f6b")]
 
 
 # ---- BASELINE configs ---------------------------------------------------------------------------------
