@@ -18,6 +18,7 @@
 #include <cstring>
 #include <map>
 #include <memory>
+#include <deque>
 #include <optional>
 #include <stdexcept>
 #include <string>
@@ -54,6 +55,7 @@ struct TensorProto {
   std::vector<float> float_val;
   std::vector<double> double_val;
   std::vector<int32_t> int_val;
+  std::vector<std::vector<uint8_t>> string_val;  // Vec<Vec<u8>>
   std::vector<float> scomplex_val;
   std::vector<int64_t> int64_val;
   std::vector<uint8_t> bool_val;  // Vec<bool>
@@ -105,8 +107,10 @@ namespace detail {
 
 inline tfs_str_t str(const std::string& s) { return tfs_str_t{s.data(), static_cast<uint32_t>(s.size()), 0}; }
 
-// plain-data picture of a batch of messages: nothing is copied, the descriptors point into the messages' vectors
+// plain-data picture of a batch of messages: the descriptors point into the messages' vectors; only string_val
+// (a vector of vectors) is flattened into a block of its own
 struct Described {
+  std::deque<std::vector<uint64_t>> ragged;  // flattened string_val blocks (stable addresses)
   std::vector<tfs_msg_desc_t> msgs;
   std::vector<tfs_tensor_desc_t> tensors;
   std::vector<tfs_field_desc_t> fields;
@@ -143,6 +147,23 @@ struct Described {
     push(TFS_KIND_FLOAT_VAL, TFS_T_F32, t.float_val.size(), t.float_val.data());
     push(TFS_KIND_DOUBLE_VAL, TFS_T_F64, t.double_val.size(), t.double_val.data());
     push(TFS_KIND_INT_VAL, TFS_T_I32, t.int_val.size(), t.int_val.data());
+    if (!t.string_val.empty()) {  // Vec<Vec<u8>> flattened into one TFS_T_RAGGED block: (n + 1) u64 offsets, then the bytes
+      const size_t n = t.string_val.size();
+      size_t total = 0;
+      for (const auto& e : t.string_val) total += e.size();
+      ragged.emplace_back((8 * (n + 1) + total + 7) / 8);  // uint64_t storage keeps the block 8-byte aligned
+      uint64_t* offs = ragged.back().data();
+      uint8_t* bytes = reinterpret_cast<uint8_t*>(offs + n + 1);
+      uint64_t at = 0;
+      for (size_t i = 0; i < n; ++i) {
+        offs[i] = at;
+        if (!t.string_val[i].empty()) std::memcpy(bytes + at, t.string_val[i].data(), t.string_val[i].size());
+        at += t.string_val[i].size();
+      }
+      offs[n] = at;
+      push(TFS_KIND_STRING_VAL, TFS_T_RAGGED, n, offs);
+      fields.back().aux = total;
+    }
     push(TFS_KIND_SCOMPLEX_VAL, TFS_T_F32, t.scomplex_val.size(), t.scomplex_val.data());
     push(TFS_KIND_INT64_VAL, TFS_T_I64, t.int64_val.size(), t.int64_val.data());
     push(TFS_KIND_BOOL_VAL, TFS_T_BOOL, t.bool_val.size(), t.bool_val.data());
@@ -202,6 +223,17 @@ inline TensorProto tensor_from(const tfs_tensor_out_t& t, const uint8_t* pool) {
   take(o.float_val, t, 1, pool);
   take(o.double_val, t, 2, pool);
   take(o.int_val, t, 3, pool);
+  if (const uint64_t n = t.n_elems[4]) {  // string_val comes back as the same flattened block
+    const uint8_t* block = pool + t.dst_off[4];
+    const uint8_t* bytes = block + 8 * (n + 1);
+    o.string_val.resize(n);
+    for (uint64_t i = 0; i < n; ++i) {
+      uint64_t a, b;
+      std::memcpy(&a, block + 8 * i, 8);
+      std::memcpy(&b, block + 8 * (i + 1), 8);
+      o.string_val[i].assign(bytes + a, bytes + b);
+    }
+  }
   take(o.scomplex_val, t, 5, pool);
   take(o.int64_val, t, 6, pool);
   take(o.bool_val, t, 7, pool);

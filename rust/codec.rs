@@ -46,23 +46,40 @@ impl Codec for GpuCodec {
 pub struct GpuEncoder { gpu: GpuHandle }
 pub struct GpuDecoder { gpu: GpuHandle }
 
-/// Plain-data picture of one PredictRequest: nothing is copied, the descriptors point into the message's Vecs.
-struct Described { msg: tfs_msg_desc_t, tensors: Vec<tfs_tensor_desc_t>, fields: Vec<tfs_field_desc_t> }
+/// Plain-data picture of one PredictRequest: the descriptors point into the message's Vecs; only string_val
+/// (`Vec<Vec<u8>>`) is flattened into a TFS_T_RAGGED block ((n + 1) u64 offsets, then the bytes) that `ragged` keeps alive.
+struct Described { msg: tfs_msg_desc_t, tensors: Vec<tfs_tensor_desc_t>, fields: Vec<tfs_field_desc_t>, ragged: Vec<Vec<u64>> }
 
 fn s(x: &str) -> tfs_str_t { tfs_str_t { ptr: x.as_ptr() as *const _, len: x.len() as u32, _pad: 0 } }
 
 fn describe(req: &PredictRequest) -> Described {
     let mut tensors = Vec::new();
     let mut fields = Vec::new();
+    let mut ragged: Vec<Vec<u64>> = Vec::new();
     for (name, t) in req.inputs.iter() {                    // HashMap order = the order prost itself would emit
         let first_field = fields.len() as u32;
         let mut push = |kind: i32, ty: i32, n: usize, p: *const c_void| if n > 0 {
-            fields.push(tfs_field_desc_t { kind, src_type: ty, dst_type: 0, op: 0, op_param: 0.0, _pad: 0, n_elems: n as u64, data: p });
+            fields.push(tfs_field_desc_t { kind, src_type: ty, dst_type: 0, op: 0, op_param: 0.0, _pad: 0, n_elems: n as u64, data: p, aux: 0 });
         };
         push(TFS_KIND_TENSOR_CONTENT, TFS_T_U8, t.tensor_content.len(), t.tensor_content.as_ptr() as *const _);
         push(TFS_KIND_FLOAT_VAL, TFS_T_F32, t.float_val.len(), t.float_val.as_ptr() as *const _);
         push(TFS_KIND_DOUBLE_VAL, TFS_T_F64, t.double_val.len(), t.double_val.as_ptr() as *const _);
         push(TFS_KIND_INT_VAL, TFS_T_I32, t.int_val.len(), t.int_val.as_ptr() as *const _);
+        if !t.string_val.is_empty() {
+            let n = t.string_val.len();
+            let total: usize = t.string_val.iter().map(|e| e.len()).sum();
+            let mut block = vec![0u64; n + 1 + (total + 7) / 8];         // u64 storage: the block is 8-byte aligned
+            let mut at = 0usize;
+            for (i, e) in t.string_val.iter().enumerate() {
+                block[i] = at as u64;
+                unsafe { std::ptr::copy_nonoverlapping(e.as_ptr(), (block.as_mut_ptr().add(n + 1) as *mut u8).add(at), e.len()) };
+                at += e.len();
+            }
+            block[n] = at as u64;
+            fields.push(tfs_field_desc_t { kind: TFS_KIND_STRING_VAL, src_type: TFS_T_RAGGED, dst_type: 0, op: 0, op_param: 0.0, _pad: 0,
+                                           n_elems: n as u64, data: block.as_ptr() as *const _, aux: total as u64 });
+            ragged.push(block);                                           // moving the Vec does not move its heap buffer
+        }
         push(TFS_KIND_SCOMPLEX_VAL, TFS_T_F32, t.scomplex_val.len(), t.scomplex_val.as_ptr() as *const _);
         push(TFS_KIND_INT64_VAL, TFS_T_I64, t.int64_val.len(), t.int64_val.as_ptr() as *const _);
         push(TFS_KIND_BOOL_VAL, TFS_T_BOOL, t.bool_val.len(), t.bool_val.as_ptr() as *const _);
@@ -96,7 +113,7 @@ fn describe(req: &PredictRequest) -> Described {
         version_choice: choice, _pad: 0, version,
         first_tensor: 0, n_tensors: tensors.len() as u32, first_filter: 0, n_filters: 0,
     };
-    Described { msg, tensors, fields }
+    Described { msg, tensors, fields, ragged }
 }
 
 impl tokio_util::codec::Encoder for GpuEncoder {
@@ -104,9 +121,9 @@ impl tokio_util::codec::Encoder for GpuEncoder {
     type Error = Status;
     /// Appends exactly the protobuf bytes of `item` (tonic adds the 5-byte frame prefix itself).
     fn encode(&mut self, item: PredictRequest, dst: &mut BytesMut) -> Result<(), Status> {
-        // messages that use what the GPU path leaves to prost (string_val, variant_val, resource handles, rank > 8,
-        // output_filter is supported) go through prost unchanged
-        if item.inputs.values().any(|t| !t.string_val.is_empty() || !t.variant_val.is_empty() || !t.resource_handle_val.is_empty()
+        // messages that use what the GPU path leaves to prost (variant_val, resource handles, rank > 8, named dims)
+        // go through prost unchanged
+        if item.inputs.values().any(|t| !t.variant_val.is_empty() || !t.resource_handle_val.is_empty()
             || t.tensor_shape.as_ref().map(|sh| sh.dim.len() > TFS_MAX_DIMS || sh.dim.iter().any(|d| !d.name.is_empty())).unwrap_or(false)) {
             return prost::Message::encode(&item, dst).map_err(|e| Status::internal(e.to_string()));
         }
@@ -168,6 +185,13 @@ impl tokio_util::codec::Decoder for GpuDecoder {
                 if n > 0 { let p = unsafe { pool.as_ptr().add(t.dst_off[$slot] as usize) } as *const $ty;
                            tp.$field = unsafe { std::slice::from_raw_parts(p, n) }.to_vec(); } }} }
             take!(0, tensor_content, u8); take!(1, float_val, f32); take!(2, double_val, f64); take!(3, int_val, i32);
+            let ns = t.n_elems[4] as usize;                          // string_val: the flattened block back into Vec<Vec<u8>>
+            if ns > 0 {
+                let block = unsafe { pool.as_ptr().add(t.dst_off[4] as usize) };
+                let off = |i: usize| unsafe { std::ptr::read_unaligned(block.add(8 * i) as *const u64) } as usize;
+                let bytes = unsafe { block.add(8 * (ns + 1)) };
+                tp.string_val = (0..ns).map(|i| unsafe { std::slice::from_raw_parts(bytes.add(off(i)), off(i + 1) - off(i)) }.to_vec()).collect();
+            }
             take!(5, scomplex_val, f32); take!(6, int64_val, i64); take!(7, bool_val, bool); take!(8, dcomplex_val, f64);
             take!(9, half_val, i32); take!(10, uint32_val, u32); take!(11, uint64_val, u64);
             outputs.insert(text(t.key), tp);                         // a repeated key: the last entry wins, as in prost

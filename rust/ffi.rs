@@ -17,6 +17,7 @@ pub const TFS_KIND_DOUBLE_VAL: i32 = 6;
 pub const TFS_KIND_INT_VAL: i32 = 7;
 pub const TFS_KIND_SCOMPLEX_VAL: i32 = 9;
 pub const TFS_KIND_INT64_VAL: i32 = 10;
+pub const TFS_KIND_STRING_VAL: i32 = 8;
 pub const TFS_KIND_BOOL_VAL: i32 = 11;
 pub const TFS_KIND_DCOMPLEX_VAL: i32 = 12;
 pub const TFS_KIND_HALF_VAL: i32 = 13;
@@ -31,6 +32,7 @@ pub const TFS_T_U64: i32 = 8;
 pub const TFS_T_F32: i32 = 11;
 pub const TFS_T_F64: i32 = 12;
 pub const TFS_T_BOOL: i32 = 13;
+pub const TFS_T_RAGGED: i32 = 14;
 
 pub const TFS_MSG_PREDICT_REQUEST: i32 = 1;
 pub const TFS_MSG_PREDICT_RESPONSE: i32 = 2;
@@ -50,6 +52,7 @@ pub struct tfs_str_t { pub ptr: *const c_char, pub len: u32, pub _pad: u32 }
 pub struct tfs_field_desc_t {
     pub kind: i32, pub src_type: i32, pub dst_type: i32, pub op: i32, pub op_param: f32, pub _pad: u32,
     pub n_elems: u64, pub data: *const c_void,
+    pub aux: u64, // string_val (TFS_T_RAGGED): total bytes of all elements
 }
 
 #[repr(C)] #[derive(Clone, Copy)]

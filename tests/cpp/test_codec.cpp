@@ -98,6 +98,11 @@ int main() {
     mix.uint64_val.push_back(rng() >> (rng() % 64));
     mix.tensor_content.push_back(static_cast<uint8_t>(rng()));
   }
+  for (int i = 0; i < 300; ++i) {  // string_val: Vec<Vec<u8>>, sizes 0 .. 70 000
+    std::vector<uint8_t> e(i % 7 == 0 ? 0 : (i == 150 ? 70000 : rng() % 60));
+    for (auto& b : e) b = static_cast<uint8_t>(rng());
+    mix.string_val.push_back(std::move(e));
+  }
   big.inputs.emplace_back("input_ids", ids);
   big.inputs.emplace_back("mix", mix);
   std::vector<uint8_t> w2;
@@ -111,6 +116,7 @@ int main() {
   CHECK(back->inputs[1].second.int_val == mix.int_val && back->inputs[1].second.half_val == mix.half_val);
   CHECK(back->inputs[1].second.bool_val == mix.bool_val && back->inputs[1].second.uint32_val == mix.uint32_val);
   CHECK(back->inputs[1].second.uint64_val == mix.uint64_val && back->inputs[1].second.tensor_content == mix.tensor_content);
+  CHECK(back->inputs[1].second.string_val == mix.string_val);
   CHECK(back->output_filter == big.output_filter && back->model_spec->version == 7);
 
   // a batch of requests in one launch; each message's bytes equal the single-message encoding
