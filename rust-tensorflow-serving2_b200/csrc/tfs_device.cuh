@@ -133,4 +133,97 @@ __device__ __forceinline__ void st_stream16(void* p, const uint4& v) {
   asm volatile("st.global.L1::no_allocate.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
+// ---- whole-CTA byte copy, any alignment on both sides (K5 generic path, K8 bulk path) ------------------------------
+__device__ __forceinline__ uint4 shift_window(const uint4& a, const uint4& b, uint32_t delta) {
+  // bytes [delta, delta+16) of the 32-byte little-endian window a:b, 0 < delta < 16
+  const uint32_t sh = (delta & 3u) * 8u;
+  uint4 r;
+  switch (delta >> 2) {
+    case 0:
+      r.x = __funnelshift_r(a.x, a.y, sh); r.y = __funnelshift_r(a.y, a.z, sh);
+      r.z = __funnelshift_r(a.z, a.w, sh); r.w = __funnelshift_r(a.w, b.x, sh);
+      break;
+    case 1:
+      r.x = __funnelshift_r(a.y, a.z, sh); r.y = __funnelshift_r(a.z, a.w, sh);
+      r.z = __funnelshift_r(a.w, b.x, sh); r.w = __funnelshift_r(b.x, b.y, sh);
+      break;
+    case 2:
+      r.x = __funnelshift_r(a.z, a.w, sh); r.y = __funnelshift_r(a.w, b.x, sh);
+      r.z = __funnelshift_r(b.x, b.y, sh); r.w = __funnelshift_r(b.y, b.z, sh);
+      break;
+    default:
+      r.x = __funnelshift_r(a.w, b.x, sh); r.y = __funnelshift_r(b.x, b.y, sh);
+      r.z = __funnelshift_r(b.y, b.z, sh); r.w = __funnelshift_r(b.z, b.w, sh);
+      break;
+  }
+  return r;
+}
+
+__device__ __forceinline__ uint4 shfl_down_u4(const uint4& v) {
+  uint4 r;
+  r.x = __shfl_down_sync(0xFFFFFFFFu, v.x, 1);
+  r.y = __shfl_down_sync(0xFFFFFFFFu, v.y, 1);
+  r.z = __shfl_down_sync(0xFFFFFFFFu, v.z, 1);
+  r.w = __shfl_down_sync(0xFFFFFFFFu, v.w, 1);
+  return r;
+}
+
+constexpr int kVecPerThread = kCopyTileBytes / 16 / kCopyThreads;  // 8 x 16 B per thread and tile
+
+// Copy `len` bytes src -> dst, any alignment on both sides, by the whole CTA (VPT 16-byte vectors in flight per thread).
+template <int VPT = kVecPerThread>
+__device__ __forceinline__ void cta_copy_bytes(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint32_t len) {
+  constexpr int kVecPerThread = VPT;  // 16-byte vectors in flight per thread (shadows the default)
+  const uint32_t tid = threadIdx.x;
+  uint32_t head = (16u - static_cast<uint32_t>(reinterpret_cast<uintptr_t>(dst) & 15u)) & 15u;
+  if (head > len) head = len;
+  if (tid < head) dst[tid] = src[tid];
+  const uint32_t nvec = (len - head) >> 4;
+  uint8_t* d = dst + head;
+  const uint8_t* s = src + head;
+  const uint32_t delta = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(s) & 15u);
+  if (delta == 0) {
+    for (uint32_t base = 0; base < nvec; base += kVecPerThread * kCopyThreads) {
+      uint4 v[kVecPerThread];
+#pragma unroll
+      for (int u = 0; u < kVecPerThread; ++u) {
+        const uint32_t c = base + u * kCopyThreads + tid;
+        if (c < nvec) v[u] = ld_stream16(s + 16ull * c);
+      }
+#pragma unroll
+      for (int u = 0; u < kVecPerThread; ++u) {
+        const uint32_t c = base + u * kCopyThreads + tid;
+        if (c < nvec) st_stream16(d + 16ull * c, v[u]);
+      }
+    }
+  } else {
+    // output word c needs the aligned source words c and c+1: word c+1 is what the next lane loaded
+    const uint8_t* sa = s - delta;  // 16-byte aligned; every word read below overlaps valid source bytes
+    for (uint32_t base = 0; base < nvec; base += kVecPerThread * kCopyThreads) {
+      uint4 a[kVecPerThread], b[kVecPerThread];
+#pragma unroll
+      for (int u = 0; u < kVecPerThread; ++u) {
+        const uint32_t c = base + u * kCopyThreads + tid;
+        // word nvec is read too: it is the upper neighbour of the last output word (it still overlaps
+        // valid source bytes because delta > 0)
+        a[u] = c <= nvec ? ld_stream16(sa + 16ull * c) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < kVecPerThread; ++u) {
+        const uint32_t c = base + u * kCopyThreads + tid;
+        b[u] = shfl_down_u4(a[u]);
+        if (lane_id() == 31 && c < nvec) b[u] = ld_stream16(sa + 16ull * c + 16);
+      }
+#pragma unroll
+      for (int u = 0; u < kVecPerThread; ++u) {
+        const uint32_t c = base + u * kCopyThreads + tid;
+        if (c < nvec) st_stream16(d + 16ull * c, shift_window(a[u], b[u], delta));
+      }
+    }
+  }
+  const uint32_t tail0 = head + (nvec << 4);
+  if (tid < len - tail0) dst[tail0 + tid] = src[tail0 + tid];
+}
+
+
 }  // namespace tfs

@@ -126,7 +126,7 @@ struct EncTables {
   uint32_t* vfield_index;       // [n_vfields] -> index into fields
   CopySeg* segs;                // [n_segs]
   uint32_t* rfield_first_tile;  // [n_rfields + 1] ragged fields: first sizing tile (2048 elements each)
-  uint32_t* rfield_first_out;   // [n_rfields + 1] first copy tile (16 KiB of records each, from the host's upper bound)
+  uint32_t* rfield_first_out;   // [n_rfields + 1] first copy tile (64 KiB of records each, from the host's upper bound)
   uint32_t* rfield_index;       // [n_rfields] -> index into fields
   // work arrays
   VTile* vtiles;                // [n_vtiles]

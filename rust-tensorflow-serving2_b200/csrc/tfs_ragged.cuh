@@ -5,7 +5,7 @@
 // (n + 1) u64 offsets, then the bytes).  Three kernels:
 //   K8a k_ragged_size   per tile of 2048 elements: the wire bytes of its records (and the validity of the offsets)
 //   K8b k_ragged_scan   per field: exclusive scan of the tile sizes -> record area length (EncField::body_len)
-//   K8c k_ragged_copy   OUTPUT-centric: one CTA per 16 KiB of a field's record area, whatever the element sizes
+//   K8c k_ragged_copy   OUTPUT-centric: one CTA per 64 KiB of a field's record area, whatever the element sizes
 //                       (a tile of two-byte labels and a single 100 MB blob are balanced the same way); every
 //                       thread assembles aligned 16-byte chunks of the destination, header bytes computed,
 //                       payload bytes fetched (one unaligned 16-byte fetch when the chunk lies inside one element).
@@ -16,8 +16,9 @@
 namespace tfs {
 
 constexpr int kRagThreads = 256;
+static_assert(kRagThreads == kCopyThreads, "cta_copy_bytes is written for kCopyThreads threads");
 constexpr int kRagTile = 2048;      // elements per sizing tile
-constexpr int kRagOutTile = 16384;  // record-area bytes per copy CTA
+constexpr int kRagOutTile = 65536;  // record-area bytes per copy CTA (amortises the ~10 dependent table reads each CTA starts with)
 
 __device__ __forceinline__ uint64_t rag_rec_len(uint64_t len) { return 1u + varint_len(len) + len; }
 
@@ -84,7 +85,7 @@ __device__ __forceinline__ uint4 load16_unaligned(const uint8_t* p) {
   return make_uint4(__funnelshift_r(w0, w1, r), __funnelshift_r(w1, w2, r), __funnelshift_r(w2, w3, r), __funnelshift_r(w3, w4, r));
 }
 
-__global__ void __launch_bounds__(kRagThreads) k_ragged_copy(EncTables T, uint8_t* __restrict__ dst) {
+__global__ void __launch_bounds__(kRagThreads, 3) k_ragged_copy(EncTables T, uint8_t* __restrict__ dst) {
   __shared__ uint64_t s_rec[kRagTile + 1];  // start of every record of the current element tile, inside the record area
   __shared__ uint64_t s_scan[kRagThreads / 32 + 1];
   if (T.result[1] != 0 || T.result[2] != 0) return;  // dst too small, or offsets that do not match the descriptor
@@ -126,6 +127,20 @@ __global__ void __launch_bounds__(kRagThreads) k_ragged_copy(EncTables T, uint8_
     __syncthreads();
     const uint64_t tile_end = tile_begin + total;
     const uint64_t lo = cursor, hi = b < tile_end ? b : tile_end;
+    {  // bulk path: the whole range lies inside the bytes of ONE element (encoded images, serialized Examples):
+       // a plain CTA-wide copy, any alignment on both sides
+      const uint32_t i0 = find_segment(s_rec, ne, lo);
+      const uint64_t r0 = s_rec[i0], so = offs[e0 + i0];
+      const uint64_t ln = offs[e0 + i0 + 1] - so;
+      const uint32_t h0 = 1u + varint_len(ln);
+      if (lo >= r0 + h0 && hi <= r0 + h0 + ln) {  // uniform across the CTA
+        cta_copy_bytes<4>(out + lo, bytes + so + (lo - r0 - h0), static_cast<uint32_t>(hi - lo));
+        cursor = hi;
+        ++et;
+        __syncthreads();
+        continue;
+      }
+    }
     // aligned 16-byte chunks of the destination (absolute addresses) that intersect [lo, hi)
     const uint64_t A_lo = D + lo, A_hi = D + hi;
     const uint64_t chunk0 = A_lo & ~static_cast<uint64_t>(15);
