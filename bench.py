@@ -276,7 +276,7 @@ def run_ours(args):
                    "flags": "TFS_F_ALIGN_PAYLOAD", "sharding": f"dp{world}: independent requests per GPU, no collective"},
         "clocks": clocks,
         "e2e": {"value": round(world * e2e_bytes / e2e_s / 1e9, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "path": "tfs_encode_host + tfs_decode_host_into on pinned host buffers (kernels read and write host memory in place)"},
+                "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "path": "tfs_encode_host + tfs_decode_host_into on pinned host buffers: copy engine brings the source to HBM in 8 MB chunks, the copy kernel follows chunk by chunk and stores straight into the pinned destination"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "k_copy_tma (K5 bulk copy through the TMA ring; one launch per encode and per decode)",
                      "other_copy_kernel_avg_ms": round(ms_gen / max(1, n_gen), 4),

@@ -18,6 +18,8 @@
 // [A0 + t*32 KiB, A0 + (t+1)*32 KiB) with A0 = dst & ~15), so every tile interior is vector / TMA aligned.
 // Tiles are dealt round-robin to the CTAs: at any moment all SMs work inside one compact window of addresses,
 // which measured 25 % faster on B200 than giving each CTA its own contiguous range (scripts/copy_sweep.cu).
+#include <algorithm>
+
 #include "tfs_device.cuh"
 
 namespace tfs {
@@ -118,10 +120,11 @@ __device__ __forceinline__ bool tma_eligible(const CopySeg& s) {
 }
 
 __global__ void __launch_bounds__(kCopyThreads) k_copy(const CopySeg* __restrict__ segs, uint32_t n_segs, uint64_t n_tiles,
-                                                        const uint64_t* __restrict__ gate) {
+                                                        const uint64_t* __restrict__ gate, uint64_t src_lo, uint64_t src_hi,
+                                                        uint64_t tile_begin) {
   __shared__ uint32_t s_seg;
   if (gate && *gate != 0) return;  // an earlier kernel of the batch refused to go on (dst too small)
-  const uint64_t tile = blockIdx.x;
+  const uint64_t tile = tile_begin + blockIdx.x;
   if (tile >= n_tiles) return;
   if (threadIdx.x == 0) s_seg = seg_from(segs, n_segs, 0, tile);
   __syncthreads();
@@ -130,6 +133,10 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy(const CopySeg* __restrict
   uint64_t e0, e1;
   tile_range(seg, tile - seg.first_tile, &e0, &e1);
   if (e0 >= e1) return;
+  {  // a pipelined launch owns the tiles whose source bytes end inside its window
+    const uint64_t src_end = reinterpret_cast<uintptr_t>(seg.src) + e1 * in_size_of(seg.op);
+    if (src_end <= src_lo || src_end > src_hi) return;
+  }
   const uint32_t n = static_cast<uint32_t>(e1 - e0);
   uint8_t* d = seg.dst + e0 * out_size_of(seg.op);
   const uint8_t* s = seg.src + e0 * in_size_of(seg.op);
@@ -195,6 +202,7 @@ struct TileWalk {
   const CopySeg* segs;
   uint32_t n_segs, si;
   uint64_t tile, n_tiles, stride;
+  uint64_t src_lo, src_hi;  // this launch owns the tiles whose source bytes END in (src_lo, src_hi]
 
   __device__ bool next(const uint8_t** src, uint8_t** dst, uint32_t* bytes) {
     for (; tile < n_tiles; tile += stride) {
@@ -204,6 +212,8 @@ struct TileWalk {
       uint64_t a, b;
       tile_range(seg, tile - seg.first_tile, &a, &b);
       if (a >= b) continue;
+      const uint64_t src_end = reinterpret_cast<uintptr_t>(seg.src) + b;
+      if (src_end <= src_lo || src_end > src_hi) continue;
       const uint64_t d = reinterpret_cast<uintptr_t>(seg.dst);
       const uint32_t head = static_cast<uint32_t>((16u - ((d + a) & 15u)) & 15u);  // only in a segment's first tile
       if (head) {
@@ -229,19 +239,20 @@ struct TileWalk {
 };
 
 __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ segs, uint32_t n_segs, uint64_t n_tiles,
-                                                 const uint64_t* __restrict__ gate) {
+                                                 const uint64_t* __restrict__ gate, uint64_t src_lo, uint64_t src_hi,
+                                                 uint64_t tile_begin) {
   extern __shared__ __align__(128) uint8_t ring[];  // kTmaStages x kTmaChunk
   __shared__ __align__(8) uint64_t full_bar[kTmaStages];
   if (threadIdx.x != 0) return;  // one thread drives the TMA engine; the warp exists only to own the CTA
   if (gate && *gate != 0) return;
-  if (blockIdx.x >= n_tiles) return;
+  if (tile_begin + blockIdx.x >= n_tiles) return;
 #pragma unroll
   for (uint32_t s = 0; s < kTmaStages; ++s) mbar_init(&full_bar[s], 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 
   const uint64_t pol = l2_evict_first_policy();
-  TileWalk walk{segs, n_segs, 0u, blockIdx.x, n_tiles, gridDim.x};
+  TileWalk walk{segs, n_segs, 0u, tile_begin + blockIdx.x, n_tiles, gridDim.x, src_lo, src_hi};
   uint8_t* dsts[kTmaStages];
   uint32_t sizes[kTmaStages];
   uint32_t issued = 0, stored = 0;
@@ -278,7 +289,7 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
 }  // namespace
 
 tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
-                         bool need_generic) {
+                         bool need_generic, const std::vector<HostSeg>* host_segs) {
   if (n_segs == 0 || n_tiles == 0) return TFS_OK;
   if (n_tiles > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (copy tiles)");
   const uint32_t ring_bytes = kTmaStages * kTmaChunk;
@@ -286,16 +297,50 @@ tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs,
     TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ring_bytes)));
     ctx->copy_attr_set = true;
   }
-  if (need_generic) {  // segments that are not congruent mod 16, are tiny, or need arithmetic: one CTA per tile
-    ProfScope prof(ctx, PK_COPY);
-    k_copy<<<static_cast<uint32_t>(n_tiles), kCopyThreads, 0, ctx->stream>>>(segs_dev, n_segs, n_tiles, gate);
-    ctx->launches++;
-  }
-  {  // the TMA ring: one CTA (96 KiB of shared memory, one driving thread) per SM
-    const uint64_t cap = static_cast<uint64_t>(ctx->sm_count);
-    ProfScope prof(ctx, PK_COPY_TMA);
-    k_copy_tma<<<static_cast<uint32_t>(n_tiles < cap ? n_tiles : cap), 32, ring_bytes, ctx->stream>>>(segs_dev, n_segs, n_tiles, gate);
-    ctx->launches++;
+  // tiles [tb, te), of which the kernels take those whose source bytes end in (src_lo, src_hi]
+  auto launch = [&](uint64_t src_lo, uint64_t src_hi, uint64_t tb, uint64_t te) {
+    if (te <= tb) return;
+    if (need_generic) {  // segments that are not congruent mod 16, are tiny, or need arithmetic: one CTA per tile
+      ProfScope prof(ctx, PK_COPY);
+      k_copy<<<static_cast<uint32_t>(te - tb), kCopyThreads, 0, ctx->stream>>>(segs_dev, n_segs, te, gate, src_lo, src_hi, tb);
+      ctx->launches++;
+    }
+    {  // the TMA ring: one CTA (96 KiB of shared memory, one driving thread) per SM
+      const uint64_t cap = static_cast<uint64_t>(ctx->sm_count);
+      ProfScope prof(ctx, PK_COPY_TMA);
+      k_copy_tma<<<static_cast<uint32_t>(te - tb < cap ? te - tb : cap), 32, ring_bytes, ctx->stream>>>(segs_dev, n_segs, te, gate, src_lo, src_hi, tb);
+      ctx->launches++;
+    }
+  };
+  if (ctx->pipe.empty()) {
+    launch(0, ~0ull, 0, n_tiles);
+  } else if (!host_segs) {
+    TFS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipe.back().ready, 0));
+    ctx->pipe.clear();
+    launch(0, ~0ull, 0, n_tiles);
+  } else {
+    // the sources are still arriving over PCIe, chunk by chunk: one launch per chunk, each behind its chunk's event,
+    // over the tiles that can end inside the chunk (two tiles of slack: the kernels apply the exact test)
+    uint64_t lo = 0;
+    for (size_t i = 0; i < ctx->pipe.size(); ++i) {
+      const uint64_t hi = i + 1 == ctx->pipe.size() ? ~0ull : ctx->pipe[i].src_hi;
+      uint64_t tb = ~0ull, te = 0;
+      for (const HostSeg& h : *host_segs) {
+        if (h.src_bytes == 0 || h.n_tiles == 0) continue;
+        const uint64_t s0 = h.src, s1 = h.src + h.src_bytes;
+        if (s1 <= lo || s0 > hi) continue;  // no source byte of this segment ends inside the window
+        const uint64_t from = lo > s0 ? (lo - s0) / h.src_tile_max : 0;
+        const uint64_t upto = hi >= s1 ? h.n_tiles : std::min<uint64_t>(h.n_tiles, (hi - s0) / h.src_tile_min + 2);
+        tb = std::min(tb, h.first_tile + (from > 1 ? from - 1 : 0));
+        te = std::max(te, h.first_tile + upto);
+      }
+      if (te > tb) {
+        TFS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipe[i].ready, 0));
+        launch(lo, hi, tb, std::min(te, n_tiles));
+      }
+      lo = hi;
+    }
+    ctx->pipe.clear();
   }
   TFS_CUDA(ctx, cudaGetLastError());
   return TFS_OK;

@@ -167,6 +167,8 @@ tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx) {
   if (ctx->h_up) cudaFreeHost(ctx->h_up);
   if (ctx->h_down) cudaFreeHost(ctx->h_down);
   if (ctx->h_slab) cudaFreeHost(ctx->h_slab);
+  for (cudaEvent_t e : ctx->pipe_events) cudaEventDestroy(e);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
   return TFS_OK;

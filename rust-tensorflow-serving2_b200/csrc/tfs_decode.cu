@@ -9,6 +9,8 @@
 //   float/double::merge_repeated, bytes::merge                                 -> K5 k_copy (tfs_copy.cu)
 // Element counts are known before any value is written (prost grows its Vecs by doubling instead).
 // Integer / byte work bound by HBM bandwidth: no tensor cores.
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 
@@ -19,7 +21,7 @@ struct tfs_decoded {
   uint64_t generation = 0;
   tfs_ctx* owner = nullptr;
   tfs::DecTables T{};
-  uint64_t totals[16] = {0};
+  uint64_t totals[24] = {0};
   std::vector<tfs_msg_out_t> msgs;
   std::vector<tfs_tensor_out_t> tensors;
   std::vector<tfs_span_t> filters;
@@ -35,7 +37,7 @@ namespace {
 
 enum { WT_VARINT = 0, WT_64 = 1, WT_LEN = 2, WT_SGROUP = 3, WT_EGROUP = 4, WT_32 = 5 };
 // TOT_GENERIC counts the copy-class spans the TMA ring cannot take (not congruent mod 16, tiny, or widened)
-enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_RETRY, TOT_COUNT_ = 16 };
+enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_RETRY, TOT_CLK0 = 16, TOT_COUNT_ = 24 };  // TOT_CLK0..: phase clocks of k_plan_small (TFS_PLAN_TIMING=1 prints them)
 constexpr size_t kTotalsBytes = sizeof(uint64_t) * TOT_COUNT_;
 
 __device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
@@ -88,7 +90,8 @@ __device__ __forceinline__ uint32_t varint_tiles_of(const uint8_t* wire, uint64_
 template <bool FILL>
 struct Walker {
   const DecTables& T;
-  const uint8_t* w;  // wire base
+  const uint8_t* w;   // wire base for the walk's own reads
+  const uint8_t* wv;  // wire base the value kernels will read from (their tile grids follow ITS alignment)
   uint64_t beg, end, pos;
   uint32_t msg;
   int32_t err = 0;
@@ -107,7 +110,7 @@ struct Walker {
   uint4 win = make_uint4(0, 0, 0, 0);
   uint64_t win_base = ~0ull;
 
-  __device__ Walker(const DecTables& t, uint32_t m) : T(t), w(t.wire), msg(m) {}
+  __device__ Walker(const DecTables& t, uint32_t m) : T(t), w(t.walk_wire), wv(t.wire), msg(m) {}
 
   __device__ __forceinline__ uint8_t byte_at(uint64_t off) {
     const uint64_t a = reinterpret_cast<uintptr_t>(w) + off;
@@ -243,14 +246,14 @@ struct Walker {
     if (FILL) T.tensors[cur].msg_index = msg;
   }
   __device__ void add_span(uint32_t slot, uint32_t cls, uint64_t off, uint64_t len, uint64_t n_elems, uint32_t out_mult) {
-    const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(w, off, len) : 0u;
+    const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(wv, off, len) : 0u;
     if (cls == SC_STR && len) n_generic++;  // string bytes land wherever the earlier elements end: generic kernel
     if (cls == SC_COPY && len) {
       // Can the TMA ring take this span?  Its pool region starts on a 64-byte boundary, so the first chunk of
       // a slot is congruent mod 16 with its source iff the source address is 16-byte aligned.  A conservative
       // count (later chunks, tiny or widened spans count as "no") decides whether the generic kernel is launched.
       const bool first = !((seen_slots >> slot) & 1u);
-      if (!first || len < 4096 || out_mult != 1 || ((reinterpret_cast<uintptr_t>(w) + off) & 15u) != 0) n_generic++;
+      if (!first || len < 4096 || out_mult != 1 || ((reinterpret_cast<uintptr_t>(wv) + off) & 15u) != 0) n_generic++;
     }
     seen_slots |= 1u << slot;
     // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
@@ -832,10 +835,14 @@ __global__ void __launch_bounds__(kSmallBatch) k_plan_small(DecTables T, uint64_
                                                             uint64_t pool_capacity) {
   __shared__ uint64_t smem[kSmallBatch / 32 + 1];
   const uint32_t mi = threadIdx.x;
+  long long clk[7];
+  clk[0] = clock64();
   if (mi < T.n_msgs) walk_body<false>(T, mi);
+  clk[1] = clock64();
   __syncthreads();
   scan_counts_body<kSmallBatch / 32>(T, smem);
   __syncthreads();
+  clk[2] = clock64();
   const uint64_t n_tensors = T.totals[TOT_TENSORS], n_filters = T.totals[TOT_FILTERS], n_spans = T.totals[TOT_SPANS],
                  n_str = T.totals[TOT_STR], n_vt = T.totals[TOT_VTILES];
   uint64_t p_flt, p_str, bytes;
@@ -851,11 +858,20 @@ __global__ void __launch_bounds__(kSmallBatch) k_plan_small(DecTables T, uint64_
   unsigned long long* z = reinterpret_cast<unsigned long long*>(blob);
   for (uint64_t i = mi, n = n_tensors * (sizeof(tfs_tensor_out_t) / 8); i < n; i += kSmallBatch) z[i] = 0ull;
   __syncthreads();
+  clk[3] = clock64();
   if (mi < L.n_msgs) walk_body<true>(L, mi);
-  if (n_vt != 0) return;  // the varint bodies have to be counted before the element totals are known
-  if (mi < L.n_msgs) finalize_body(L, mi);
-  __syncthreads();
-  pool_layout_body<kSmallBatch / 32>(L, static_cast<uint32_t>(n_tensors), pool_capacity, smem);
+  clk[4] = clock64();
+  if (n_vt == 0) {  // (with varint bodies the element totals are only known after K4a / K4b)
+    if (mi < L.n_msgs) finalize_body(L, mi);
+    __syncthreads();
+    clk[5] = clock64();
+    pool_layout_body<kSmallBatch / 32>(L, static_cast<uint32_t>(n_tensors), pool_capacity, smem);
+  } else {
+    clk[5] = clk[4];
+  }
+  clk[6] = clock64();
+  if (mi == 0)
+    for (int k = 0; k < 6; ++k) T.totals[TOT_CLK0 + k] = static_cast<uint64_t>(clk[k + 1] - clk[k]);
 }
 
 // at decode time: bind every copy-class span to its place in the caller's pool
@@ -912,7 +928,7 @@ size_t carve(size_t* cur, size_t bytes, size_t align = 64) {
 }
 
 // value kernels: bind the copy spans to the pool, gather the varint spans, copy the bulk spans
-tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const uint64_t* gate) {
+tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const uint64_t* gate, const std::vector<HostSeg>* host_segs = nullptr) {
   const DecTables& T = dec->T;
   const uint64_t n_spans = dec->totals[TOT_SPANS], n_vt = dec->totals[TOT_VTILES], n_ct = dec->totals[TOT_CTILES];
   if (n_spans) {
@@ -920,6 +936,8 @@ tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const 
     ctx->launches++;
   }
   if (n_vt) {
+    // the varint kernels read whole bodies: when the wire is still arriving in chunks, wait for the last one
+    if (!ctx->pipe.empty()) TFS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipe.back().ready, 0));
     k_dtile_bind<<<static_cast<uint32_t>((n_vt + 255) / 256), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_vt), pool, gate);
     ctx->launches++;
     {
@@ -931,7 +949,7 @@ tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const 
   TFS_CUDA(ctx, cudaGetLastError());
   // the generic copy kernel is only needed for spans the TMA ring cannot take (counted by the walk)
   const bool need_generic = dec->totals[TOT_GENERIC] != 0 || (reinterpret_cast<uintptr_t>(pool) & 15u) != 0;
-  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, gate, need_generic));
+  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, gate, need_generic, host_segs));
   return TFS_OK;
 }
 
@@ -941,7 +959,7 @@ tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const 
 // sizes, one for the results.  pool_dev == nullptr: scan only (the caller allocates the pool from the view).
 tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off,
                                 const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_dev,
-                                uint64_t pool_capacity, tfs_decoded** out) {
+                                uint64_t pool_capacity, tfs_decoded** out, const void* walk_wire_dev) {
   TFS_CUDA(ctx, cudaSetDevice(ctx->device));
   if (msg_kind < TFS_MSG_TENSOR_PROTO || msg_kind > TFS_MSG_PREDICT_RESPONSE) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad msg_kind");
   tfs_decoded* dec = new (std::nothrow) tfs_decoded();
@@ -986,6 +1004,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   }
   DEC_CUDA(cudaMemsetAsync(d1 + o_tot, 0, kTotalsBytes, ctx->stream));
   T.wire = static_cast<const uint8_t*>(wire_dev);
+  T.walk_wire = walk_wire_dev ? static_cast<const uint8_t*>(walk_wire_dev) : T.wire;
   T.wire_bytes = wire_bytes;
   T.msg_off = reinterpret_cast<const uint64_t*>(d1 + o_off);
   T.msg_len = reinterpret_cast<const uint64_t*>(d1 + o_len);
@@ -1054,6 +1073,10 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       DEC_CUDA(cudaMemcpyAsync(hd + h2, d2 + p_blob, guess, cudaMemcpyDeviceToHost, ctx->stream));
       DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1 (the only one when the batch has no varint bodies)
       load_totals(hd + h1);
+      if (std::getenv("TFS_PLAN_TIMING"))
+        std::fprintf(stderr, "k_plan_small cycles: walk1 %llu scan %llu zero %llu walk2 %llu finalize %llu layout %llu\n",
+                     (unsigned long long)dec->totals[TOT_CLK0], (unsigned long long)dec->totals[TOT_CLK0 + 1], (unsigned long long)dec->totals[TOT_CLK0 + 2],
+                     (unsigned long long)dec->totals[TOT_CLK0 + 3], (unsigned long long)dec->totals[TOT_CLK0 + 4], (unsigned long long)dec->totals[TOT_CLK0 + 5]);
       blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &res2_bytes);
       ctx->dec_hint_tensors = std::max(ctx->dec_hint_tensors, n_tensors + n_tensors / 4);
       ctx->dec_hint_filters = std::max(ctx->dec_hint_filters, n_filters + n_filters / 4);
@@ -1122,8 +1145,30 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     }
   }
 
+  // wire still arriving in chunks (tfs_decode_host_into): fetch the span table so that every chunk's copy launch can be
+  // limited to the tiles that can end inside the chunk
+  std::vector<HostSeg> hsegs;
+  auto fetch_host_segs = [&]() -> tfs_status_t {
+    if (ctx->pipe.empty() || !pool_dev || n_spans == 0 || n_spans > 65536) return TFS_OK;
+    std::vector<DecSpan> sp(n_spans);
+    std::vector<uint32_t> ct(n_spans);
+    TFS_CUDA(ctx, cudaMemcpyAsync(sp.data(), T.spans, sizeof(DecSpan) * n_spans, cudaMemcpyDeviceToHost, ctx->stream));
+    TFS_CUDA(ctx, cudaMemcpyAsync(ct.data(), T.span_ctile0, 4 * n_spans, cudaMemcpyDeviceToHost, ctx->stream));
+    TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const uint64_t n_ct = dec->totals[TOT_CTILES];
+    hsegs.reserve(n_spans);
+    for (uint64_t i = 0; i < n_spans; ++i) {
+      if (sp[i].cls == SC_VARINT) continue;
+      const uint64_t next = i + 1 < n_spans ? ct[i + 1] : n_ct;
+      // tensor_content may be widened 2 -> 4 bytes (half the source bytes per tile): bound both ways
+      hsegs.push_back({reinterpret_cast<uintptr_t>(T.wire) + sp[i].wire_off, sp[i].len, ct[i], next - ct[i],
+                       static_cast<uint64_t>(kCopyTileBytes) / 2, static_cast<uint64_t>(kCopyTileBytes)});
+    }
+    return TFS_OK;
+  };
   if (!planned) {
     if (n_vt) {
+      if (!ctx->pipe.empty()) DEC_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->pipe.back().ready, 0));  // whole bodies are read
       DEC_CUDA(cudaMemsetAsync(T.tile_count, 0, 4 * n_vt, ctx->stream));
       k_dtile_map<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), static_cast<uint32_t>(n_vt));
       ctx->launches++;
@@ -1146,11 +1191,15 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     }
     DEC_CUDA(cudaGetLastError());
     // one-call decode: the value kernels follow at once, gated on the device by "the pool is large enough"
-    if (pool_dev) DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), T.totals + TOT_OVERFLOW));
+    if (pool_dev) {
+      DEC_TRY(fetch_host_segs());
+      DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), T.totals + TOT_OVERFLOW, hsegs.empty() ? nullptr : &hsegs));
+    }
     blob_copied = 0;
   } else if (pool_dev && !dec->totals[TOT_OVERFLOW]) {
     // planned: the host already knows the layout, the value kernels need no gate
-    DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), nullptr));
+    DEC_TRY(fetch_host_segs());
+    DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), nullptr, hsegs.empty() ? nullptr : &hsegs));
   }
 
   // ---- results to the host: (totals | msgs) and the blob (tensors | filters | strings)
@@ -1206,7 +1255,7 @@ tfs_status_t tfs_decode_scan(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire
                              const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, tfs_decoded_t** out) {
   if (!ctx || !out || (n_msgs && (!msg_off || !msg_len)) || (wire_bytes && !wire_dev)) return TFS_ERR_INVALID_ARG;
   *out = nullptr;
-  return decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, nullptr, 0, out);
+  return decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, nullptr, 0, out, nullptr);
 }
 
 tfs_status_t tfs_decode_into(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off, const uint64_t* msg_len,
@@ -1214,7 +1263,7 @@ tfs_status_t tfs_decode_into(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire
                              tfs_decoded_t** out) {
   if (!ctx || !out || !pool_dev || (n_msgs && (!msg_off || !msg_len)) || (wire_bytes && !wire_dev)) return TFS_ERR_INVALID_ARG;
   *out = nullptr;
-  return decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, pool_dev, pool_capacity, out);
+  return decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, pool_dev, pool_capacity, out, nullptr);
 }
 
 tfs_status_t tfs_decoded_view(const tfs_decoded_t* dec, tfs_decoded_view_t* view) {

@@ -727,7 +727,21 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
     }
     TFS_CUDA(ctx, cudaGetLastError());
     // gated on the overflow flag: when dst is too small segs[].dst were never filled in
-    if (T.n_segs) TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, T.result + 1, !c.all_tma));
+    if (T.n_segs) {
+      std::vector<HostSeg> hs;
+      if (!ctx->pipe.empty()) {  // sources still arriving in chunks (tfs_encode_host): tell launch_copy where the segments are
+        hs.reserve(c.segs.size());
+        for (size_t i = 0; i < c.segs.size(); ++i) {
+          const CopySeg& g = c.segs[i];
+          const uint64_t next = i + 1 < c.segs.size() ? c.segs[i + 1].first_tile : c.n_copy_tiles;
+          const uint32_t in = (g.op == CP_F32_F16 || g.op == CP_F32_BF16) ? 4u : (g.op == CP_F16_F32 || g.op == CP_BF16_F32) ? 2u : 1u;
+          const uint32_t out = (g.op == CP_BYTES || g.op == CP_BOOL) ? 1u : (g.op == CP_F32_F16 || g.op == CP_F32_BF16) ? 2u : 4u;
+          const uint64_t stb = static_cast<uint64_t>(kCopyTileBytes) / out * in;
+          hs.push_back({reinterpret_cast<uintptr_t>(g.src), g.n * in, g.first_tile, next - g.first_tile, stb, stb});
+        }
+      }
+      TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, T.result + 1, !c.all_tma, hs.empty() ? nullptr : &hs));
+    }
   }
   bool overflow = false;
   TFS_TRY(fetch_results(ctx, u.T, msg_off_out, msg_len_out, total_out, &overflow));

@@ -2,14 +2,15 @@
 // where the message payloads (Vec<f32>, ...) and the BytesMut both live in host memory.  Host<->device traffic
 // is part of these calls (the `e2e` number of bench.py).
 //
-// Two ways across PCIe, chosen per buffer:
+// Ways across PCIe, chosen per buffer:
 //   * PINNED host memory (tfs_host_alloc / cudaHostAlloc / cudaHostRegister — the shim's staging pool) is
-//     addressable by the GPU, so the kernels read the payload from it and write the wire bytes into it directly:
-//     one kernel moves bytes in both directions at once, nothing is staged in HBM.  (Measured on this B200 box:
-//     the TMA ring and plain 16-byte loads/stores both run host->host at ~40 GB/s per direction concurrently,
-//     against 55 GB/s for a one-direction copy-engine transfer; scripts/copy_sweep.cu host.)
-//     Exception: arrays that are varint-coded are read twice (size pass + scatter pass), so they are first
-//     copied to HBM by the copy engine.
+//     addressable by the GPU.  The kernels always STORE their output straight into a pinned destination.  A pinned
+//     source is read in place when it is small; above 8 MB it is brought to HBM by the copy engine in 8 MB chunks on
+//     a second stream while the copy kernel follows chunk by chunk (one launch per chunk behind the chunk's event,
+//     limited to the tiles that can end inside it).  Measured on this B200 box (scripts/copy_sweep.cu host), summed
+//     over both directions: copy engine in + kernel stores out 92 GB/s, copy engine both ways 95, kernels reading AND
+//     writing host memory 78, kernel loads in + copy engine out 63-69 (SM loads from host memory are the weak leg).
+//     Arrays that are varint-coded or ragged are read more than once, so they always go to HBM first.
 //   * pageable host memory cannot be addressed by the GPU: it is staged through the ctx's device buffers with
 //     cudaMemcpyAsync in both directions.
 #include <cstring>
@@ -23,7 +24,7 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
                            uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out, bool size_only);
 tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wire_bytes, const uint64_t* msg_off,
                                 const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_dev,
-                                uint64_t pool_capacity, tfs_decoded** out);
+                                uint64_t pool_capacity, tfs_decoded** out, const void* walk_wire_dev = nullptr);
 tfs_status_t decode_device(tfs_ctx* ctx, tfs_decoded* dec, void* pool_dev, uint64_t pool_bytes);
 uint64_t decoded_pool_bytes(const tfs_decoded* dec);
 void decoded_mark_host_staged(tfs_decoded* dec, uint64_t stage_generation);
@@ -46,6 +47,47 @@ void* device_alias(const void* p) {
 bool is_varint_kind(int32_t kind) {
   return kind == TFS_KIND_INT_VAL || kind == TFS_KIND_INT64_VAL || kind == TFS_KIND_HALF_VAL || kind == TFS_KIND_UINT32_VAL ||
          kind == TFS_KIND_UINT64_VAL;
+}
+
+constexpr uint64_t kPipeChunk = 8ull << 20;    // bytes per copy-engine chunk
+constexpr uint64_t kPipeMinBytes = 8ull << 20;  // smaller transfers are not worth the extra launches
+
+// Queue `bytes` from pinned host memory to `dst_dev` on the copy stream, in chunks; every chunk gets an event and an
+// entry in ctx->pipe, which the next launch_copy turns into one gated kernel launch per chunk.  (Measured on this box,
+// scripts/copy_sweep.cu host: copy engine in + kernel stores out reach 92 GB/s summed, kernels reading AND writing host
+// memory 78, kernel loads in + copy engine out only 63-69.)
+tfs_status_t pipelined_h2d(tfs_ctx* ctx, uint8_t* dst_dev, const uint8_t* src_pinned, uint64_t bytes) {
+  if (!ctx->copy_stream) TFS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  auto event_at = [&](size_t i, cudaEvent_t* e) -> tfs_status_t {
+    while (ctx->pipe_events.size() <= i) {
+      cudaEvent_t ne;
+      TFS_CUDA(ctx, cudaEventCreateWithFlags(&ne, cudaEventDisableTiming));
+      ctx->pipe_events.push_back(ne);
+    }
+    *e = ctx->pipe_events[i];
+    return TFS_OK;
+  };
+  if (ctx->pipe.empty()) {  // the staging buffer may still be read by kernels of the previous call
+    cudaEvent_t fence;
+    TFS_TRY(event_at(0, &fence));
+    TFS_CUDA(ctx, cudaEventRecord(fence, ctx->stream));
+    TFS_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, fence, 0));
+  }
+  for (uint64_t off = 0; off < bytes; off += kPipeChunk) {
+    const uint64_t n = bytes - off < kPipeChunk ? bytes - off : kPipeChunk;
+    TFS_CUDA(ctx, cudaMemcpyAsync(dst_dev + off, src_pinned + off, n, cudaMemcpyHostToDevice, ctx->copy_stream));
+    cudaEvent_t e;
+    TFS_TRY(event_at(ctx->pipe.size() + 1, &e));  // slot 0 is the fence
+    TFS_CUDA(ctx, cudaEventRecord(e, ctx->copy_stream));
+    ctx->pipe.push_back({e, reinterpret_cast<uintptr_t>(dst_dev) + off + n});
+  }
+  return TFS_OK;
+}
+
+// whatever happened, the next call must not inherit chunk events; and nothing may still be in flight on the copy stream
+void pipe_reset(tfs_ctx* ctx) {
+  if (!ctx->pipe.empty() && ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+  ctx->pipe.clear();
 }
 
 // wire bytes: pinned -> read in place; pageable -> copied to the device slab
@@ -77,7 +119,10 @@ tfs_status_t tfs_encode_host(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst
   // 1. payload arrays: pinned bulk arrays are read in place by the kernels; the rest is copied to a device slab
   std::vector<tfs_field_desc_t> fields(batch->fields, batch->fields + batch->n_fields);
   std::vector<uint64_t> at(batch->n_fields, ~0ull);
+  std::vector<uint8_t> piped(batch->n_fields, 0);
   uint64_t in_bytes = 0;
+  pipe_reset(ctx);
+  const bool dst_pinned = device_alias(dst_host) != nullptr;
   auto src_bytes = [](const tfs_field_desc_t& f) -> uint64_t {
     if (f.src_type == TFS_T_RAGGED) return f.n_elems ? 8ull * (f.n_elems + 1) + f.aux : 0ull;  // offsets, then the bytes
     return f.n_elems * tfs_type_size(f.src_type);
@@ -89,6 +134,11 @@ tfs_status_t tfs_encode_host(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst
     if (!b) continue;
     // read more than once by the kernels (sizing + writing): varint-coded arrays and ragged blocks go to HBM first
     void* alias = (is_varint_kind(fields[i].kind) || fields[i].src_type == TFS_T_RAGGED) ? nullptr : device_alias(fields[i].data);
+    // large pinned bulk arrays headed for a pinned destination: copy engine in (chunked), kernel stores out, overlapped
+    if (alias && dst_pinned && b >= kPipeMinBytes) {
+      piped[i] = 1;
+      alias = nullptr;
+    }
     if (alias) {
       fields[i].data = alias;
     } else {
@@ -101,7 +151,15 @@ tfs_status_t tfs_encode_host(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst
   for (uint32_t i = 0; i < batch->n_fields; ++i) {
     if (at[i] == ~0ull) continue;
     const uint64_t b = src_bytes(fields[i]);
-    TFS_CUDA(ctx, cudaMemcpyAsync(din + at[i], fields[i].data, b, cudaMemcpyHostToDevice, ctx->stream));
+    if (piped[i]) {
+      tfs_status_t st = pipelined_h2d(ctx, din + at[i], static_cast<const uint8_t*>(fields[i].data), b);
+      if (st != TFS_OK) {
+        pipe_reset(ctx);
+        return st;
+      }
+    } else {
+      TFS_CUDA(ctx, cudaMemcpyAsync(din + at[i], fields[i].data, b, cudaMemcpyHostToDevice, ctx->stream));
+    }
     fields[i].data = din + at[i];
   }
   tfs_batch_t dev_batch = *batch;
@@ -110,7 +168,9 @@ tfs_status_t tfs_encode_host(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst
   uint64_t total = 0;
   void* dst_alias = device_alias(dst_host);
   if (dst_alias) {
-    TFS_TRY(encode_device(ctx, &dev_batch, dst_alias, dst_capacity, flags, msg_off_out, msg_len_out, &total, false));
+    const tfs_status_t st = encode_device(ctx, &dev_batch, dst_alias, dst_capacity, flags, msg_off_out, msg_len_out, &total, false);
+    pipe_reset(ctx);
+    if (st != TFS_OK) return st;
   } else {
     TFS_TRY(dev_reserve(ctx, &ctx->d_stage_out, dst_capacity + 256));
     TFS_TRY(encode_device(ctx, &dev_batch, ctx->d_stage_out.p, dst_capacity, flags, msg_off_out, msg_len_out, &total, false));
@@ -159,10 +219,24 @@ tfs_status_t tfs_decode_host_into(tfs_ctx_t* ctx, const void* wire_host, uint64_
   *out = nullptr;
   TFS_CUDA(ctx, cudaSetDevice(ctx->device));
   const uint64_t gen = ++ctx->stage_generation;
+  pipe_reset(ctx);
+  void* alias = device_alias(pool_host);
+  void* wire_alias = device_alias(wire_host);
+  tfs_status_t st;
+  if (alias && wire_alias && wire_bytes >= kPipeMinBytes) {
+    // both buffers pinned, a large batch: the walk reads the few header bytes straight from host memory while the copy
+    // engine brings the wire to HBM in chunks; the copy kernel follows chunk by chunk and stores into the host pool
+    TFS_TRY(dev_reserve(ctx, &ctx->d_stage_in, wire_bytes + 256));
+    st = pipelined_h2d(ctx, static_cast<uint8_t*>(ctx->d_stage_in.p), static_cast<const uint8_t*>(wire_host), wire_bytes);
+    if (st == TFS_OK)
+      st = decode_scan_device(ctx, ctx->d_stage_in.p, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, alias, pool_capacity, out, wire_alias);
+    if (*out) cudaStreamSynchronize(ctx->stream);
+    pipe_reset(ctx);
+    if (*out) decoded_mark_host_staged(*out, gen);
+    return st;
+  }
   const void* wire_dev = nullptr;
   TFS_TRY(wire_for_device(ctx, wire_host, wire_bytes, &wire_dev));
-  void* alias = device_alias(pool_host);
-  tfs_status_t st;
   if (alias) {
     st = decode_scan_device(ctx, wire_dev, wire_bytes, msg_off, msg_len, n_msgs, msg_kind, flags, alias, pool_capacity, out);
     // the value kernels may still be writing the host pool (the device-pool form is asynchronous): wait for them

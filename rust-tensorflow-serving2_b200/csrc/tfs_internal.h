@@ -183,7 +183,9 @@ struct TileDst {
 };
 
 struct DecTables {
-  const uint8_t* wire;
+  const uint8_t* wire;       // where the value kernels read the wire bytes (tile grids are cut on THESE addresses)
+  const uint8_t* walk_wire;  // where the structure walk reads them: the same, or the pinned host copy while `wire` is
+                             // still being filled by the copy engine (tfs_decode_host_into)
   uint64_t wire_bytes;
   const uint64_t* msg_off;  // device copies of the caller's arrays
   const uint64_t* msg_len;
@@ -236,6 +238,16 @@ struct tfs_ctx {
   // small-batch decode plans its tables optimistically from what earlier batches on this context needed
   uint64_t dec_hint_tensors = 0, dec_hint_filters = 0, dec_hint_spans = 0, dec_hint_str = 0, dec_hint_blob = 0;
   bool copy_attr_set = false;
+  // Host entry points with pinned buffers: the copy engine brings the source to HBM in chunks on `copy_stream` while the
+  // copy kernel already writes the finished chunks to the pinned destination.  `pipe` lists, for the NEXT launch_copy,
+  // the event of every chunk and the device address its bytes end at.
+  struct PipePiece {
+    cudaEvent_t ready;
+    uint64_t src_hi;
+  };
+  cudaStream_t copy_stream = nullptr;
+  std::vector<cudaEvent_t> pipe_events;  // recycled
+  std::vector<PipePiece> pipe;
   uint64_t dec_generation = 0;
   uint64_t stage_generation = 0;  // bumped by every *_host call that reuses the staging buffers
   void* h_up = nullptr;
@@ -286,8 +298,18 @@ tfs_status_t pinned_reserve(tfs_ctx* ctx, void** p, size_t* cap, size_t bytes);
 // Bulk copy / cast kernel over a segment table that already lives on the device.
 // With `gate` the kernels do nothing when *gate != 0.  `need_generic` = false promises that every non-empty
 // segment is a plain byte copy whose source and destination are congruent mod 16 (TMA ring only).
+// Host-side picture of a segment (only what a chunked launch needs to pick its tile range).
+struct HostSeg {
+  uint64_t src;             // device address of the first source byte
+  uint64_t src_bytes;
+  uint64_t first_tile;
+  uint64_t n_tiles;
+  uint64_t src_tile_min, src_tile_max;  // bounds of the source bytes one tile consumes (32 KiB for plain bytes, other for casts)
+};
+// `host_segs` is needed only while ctx->pipe is set (sources still arriving in chunks): each chunk's launch then walks
+// just the tiles that can end inside the chunk; without it the launch waits for the last chunk.
 tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
-                         bool need_generic);
+                         bool need_generic, const std::vector<HostSeg>* host_segs = nullptr);
 
 inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 

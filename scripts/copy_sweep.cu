@@ -247,6 +247,32 @@ int host_mode() {
   rep1("k_tma_strided<3,32K> host->device 1/SM", time_it([&] { k_tma_strided<3, 32768><<<sms, 32, 3 * 32768>>>(hsrc, ddst, bytes); }, 5, nullptr, 0), 1);
   rep1("k_tma_strided<3,32K> device->host 1/SM", time_it([&] { k_tma_strided<3, 32768><<<sms, 32, 3 * 32768>>>(dsrc, hdst, bytes); }, 5, nullptr, 0), 1);
   rep1("k_tma_strided<3,32K> host->host 1/SM (sum)", time_it([&] { k_tma_strided<3, 32768><<<sms, 32, 3 * 32768>>>(hsrc, hdst, bytes); }, 5, nullptr, 0), 2);
+  // hybrids: one direction by the copy engine, the other by SM stores / loads at the same time
+  cudaStream_t s3;
+  CK(cudaStreamCreateWithFlags(&s3, cudaStreamNonBlocking));
+  cudaEvent_t go, done3;
+  CK(cudaEventCreate(&go));
+  CK(cudaEventCreate(&done3));
+  auto both = [&](auto ce, auto sm) {
+    return time_it([&] {
+      CK(cudaEventRecord(go, 0));
+      CK(cudaStreamWaitEvent(s3, go));
+      ce(s3);
+      CK(cudaEventRecord(done3, s3));
+      sm();
+      CK(cudaStreamWaitEvent(0, done3));
+    }, 5, nullptr, 0);
+  };
+  rep1("CE H2D + CE D2H, two non-blocking streams (sum)", both([&](cudaStream_t st) { CK(cudaMemcpyAsync(ddst, hsrc, bytes, cudaMemcpyHostToDevice, st)); },
+                                                              [&] { CK(cudaMemcpyAsync(hdst, dsrc, bytes, cudaMemcpyDeviceToHost, s2)); CK(cudaEventRecord(done2, s2)); CK(cudaStreamWaitEvent(0, done2)); }), 2);
+  rep1("CE H2D + k_vec<4> device->host 2/SM (sum)", both([&](cudaStream_t st) { CK(cudaMemcpyAsync(ddst, hsrc, bytes, cudaMemcpyHostToDevice, st)); },
+                                                        [&] { k_vec<4><<<sms * 2, 256>>>((const uint4*)dsrc, (uint4*)hdst, n16); }), 2);
+  rep1("CE H2D + k_tma_strided device->host 1/SM (sum)", both([&](cudaStream_t st) { CK(cudaMemcpyAsync(ddst, hsrc, bytes, cudaMemcpyHostToDevice, st)); },
+                                                             [&] { k_tma_strided<3, 32768><<<sms, 32, 3 * 32768>>>(dsrc, hdst, bytes); }), 2);
+  rep1("CE D2H + k_vec<4> host->device 2/SM (sum)", both([&](cudaStream_t st) { CK(cudaMemcpyAsync(hdst, dsrc, bytes, cudaMemcpyDeviceToHost, st)); },
+                                                        [&] { k_vec<4><<<sms * 2, 256>>>((const uint4*)hsrc, (uint4*)ddst, n16); }), 2);
+  rep1("CE D2H + k_tma_strided host->device 1/SM (sum)", both([&](cudaStream_t st) { CK(cudaMemcpyAsync(hdst, dsrc, bytes, cudaMemcpyDeviceToHost, st)); },
+                                                             [&] { k_tma_strided<3, 32768><<<sms, 32, 3 * 32768>>>(hsrc, ddst, bytes); }), 2);
   CK(cudaDeviceSynchronize());
   for (uint64_t i = 0; i < bytes; i += 4096)
     if (hdst[i] != 7) {

@@ -526,6 +526,22 @@ def test_config_c2_full_size(codec, variant):
     roundtrip_check(codec, [workloads.c2_request(x, variant)], abi.MSG_PREDICT_REQUEST, f"C2 {variant}", abi.F_ALIGN_PAYLOAD)
 
 
+@pytest.mark.parametrize("flags", [0, abi.F_ALIGN_PAYLOAD])
+def test_pinned_buffers_take_the_chunked_copy_engine_path(codec, flags):
+    """Pinned sources / destinations above 8 MB are brought in by the copy engine in 4 MB chunks while the copy kernel
+    follows chunk by chunk (one gated launch per chunk); pageable and device paths must give the same bytes and values."""
+    rng = np.random.default_rng(4242)
+    msgs = []
+    for i in range(2):
+        msgs.append(tfs.PredictRequest(tfs.ModelSpec("big", signature_name="serving_default"), [
+            ("a", tfs.TensorProto(dtype=1, tensor_shape=tfs.TensorShapeProto([3_000_001]), float_val=rng.standard_normal(3_000_001).astype(np.float32))),
+            ("b", tfs.TensorProto(dtype=4, tensor_content=rng.integers(0, 256, 9_000_003 + i, dtype=np.uint8))),
+            ("ids", tfs.TensorProto(dtype=9, int64_val=rng.integers(-5, 1 << 40, 1_500_000, dtype=np.int64))),
+            ("small", tfs.TensorProto(dtype=2, double_val=rng.standard_normal(7))),
+            ("c", tfs.TensorProto(dtype=2, double_val=rng.standard_normal(1_200_000)))]))
+    roundtrip_check(codec, msgs, abi.MSG_PREDICT_REQUEST, "chunked pinned path", flags)
+
+
 def test_config_c2_batched_unaligned(codec):
     x = workloads.c2_payload(batch=4)
     msgs = [workloads.c2_request(x, v, batch=4) for v in ("float_val", "tensor_content", "float_val")]
