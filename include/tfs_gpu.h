@@ -66,6 +66,10 @@ enum {
 /* TensorProto payload fields, numbered by their proto field number (tensor.proto:36-83). */
 enum {
   TFS_KIND_NONE = 0,
+  /* 1..3: the members of Feature.kind (feature.proto:79-81); only inside TFS_MSG_INPUT / TFS_MSG_CLASSIFY_REQUEST */
+  TFS_KIND_BYTES_LIST = 1,     /* BytesList.value, repeated bytes: TFS_T_RAGGED block like string_val (aux = total bytes) */
+  TFS_KIND_FLOAT_LIST = 2,     /* FloatList.value, packed fixed32 (src TFS_T_F32) */
+  TFS_KIND_INT64_LIST = 3,     /* Int64List.value, packed varint (src TFS_T_I64) */
   TFS_KIND_TENSOR_CONTENT = 4, /* bytes */
   TFS_KIND_FLOAT_VAL = 5,      /* packed fixed32 */
   TFS_KIND_DOUBLE_VAL = 6,     /* packed fixed64 */
@@ -113,7 +117,15 @@ enum {
 enum {
   TFS_MSG_TENSOR_PROTO = 0,     /* bare tensorflow.TensorProto */
   TFS_MSG_PREDICT_REQUEST = 1,  /* predict.proto:12-31 */
-  TFS_MSG_PREDICT_RESPONSE = 2  /* predict.proto:34-40 */
+  TFS_MSG_PREDICT_RESPONSE = 2, /* predict.proto:34-40 */
+  /* Encode only (what the reference's build_input returns, src/lib.rs:413-431, and the request that carries it):
+   * tensorflow.serving.Input { example_list { examples: [Example { features { feature: map<string, Feature> } }] } }.
+   * Described with the same arrays: every FEATURE is one tfs_tensor_desc_t (name = map key; dtype / shape / version
+   * unused; 0 or 1 field of kind TFS_KIND_*_LIST, 0 = Feature { kind: None }), `version_number` = index of the Example
+   * it belongs to (ascending inside the message), and tfs_msg_desc_t.n_filters = number of Examples in the list
+   * (first_filter unused; an Example without features is an empty map). */
+  TFS_MSG_INPUT = 3,            /* input.proto:77-82 */
+  TFS_MSG_CLASSIFY_REQUEST = 4  /* classification.proto:33-40 = regression.proto:23-30: model_spec = 1, input = 2 */
 };
 
 enum { TFS_VERSION_NONE = 0, TFS_VERSION_NUMBER = 1, TFS_VERSION_LABEL = 2 }; /* model.proto:22-28 */

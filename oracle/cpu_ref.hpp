@@ -123,6 +123,33 @@ struct PredictResponse {
   std::optional<ModelSpec> model_spec;  // tag 2
 };
 
+// ---- Example / Features / Input (feature.proto:65-87, example.proto:88-90, input.proto:15-82, classification.proto:33-40;
+//      built by build_input + `impl From<Payload> for Feature`, src/lib.rs:413-431, 514-571) ----
+struct Feature {
+  // oneof kind { BytesList bytes_list = 1; FloatList float_list = 2; Int64List int64_list = 3 }
+  int32_t kind = 0;  // 0 = None
+  std::vector<std::vector<uint8_t>> bytes_list;  // BytesList.value (repeated bytes = 1)
+  std::vector<float> float_list;                 // FloatList.value (packed = 1)
+  std::vector<int64_t> int64_list;               // Int64List.value (packed = 1)
+};
+using FeatureMap = std::vector<std::pair<std::string, Feature>>;  // HashMap in caller order
+struct Example {
+  std::optional<FeatureMap> features;  // Option<Features>; build_input always sets Some (src/lib.rs:420)
+};
+struct Input {
+  // oneof kind { ExampleList example_list = 1; ExampleListWithContext example_list_with_context = 2 }: only the first
+  bool has_example_list = true;
+  std::vector<Example> examples;
+};
+struct ClassificationRequest {  // RegressionRequest has the same fields (regression.proto:23-30)
+  std::optional<ModelSpec> model_spec;  // tag 1
+  std::optional<Input> input;           // tag 2
+};
+size_t encoded_len(const Input& m);
+size_t encoded_len(const ClassificationRequest& m);
+void encode_raw(const Input& m, BufMut& buf);
+void encode_raw(const ClassificationRequest& m, BufMut& buf);
+
 // ---- prost::encoding primitives ----
 size_t encoded_len_varint(uint64_t value);
 void encode_varint(uint64_t value, BufMut& buf);

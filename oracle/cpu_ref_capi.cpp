@@ -199,25 +199,100 @@ struct AnyMsg {
   TensorProto tensor;
   PredictRequest req;
   PredictResponse resp;
+  Input input;
+  ClassificationRequest classify;
   size_t encoded_len() const {
-    return kind == TFS_MSG_TENSOR_PROTO ? cpu_ref::encoded_len(tensor)
-           : kind == TFS_MSG_PREDICT_REQUEST ? cpu_ref::encoded_len(req) : cpu_ref::encoded_len(resp);
+    switch (kind) {
+      case TFS_MSG_TENSOR_PROTO: return cpu_ref::encoded_len(tensor);
+      case TFS_MSG_PREDICT_REQUEST: return cpu_ref::encoded_len(req);
+      case TFS_MSG_INPUT: return cpu_ref::encoded_len(input);
+      case TFS_MSG_CLASSIFY_REQUEST: return cpu_ref::encoded_len(classify);
+      default: return cpu_ref::encoded_len(resp);
+    }
   }
   void prost_encode(std::vector<uint8_t>& dst) const {
-    if (kind == TFS_MSG_TENSOR_PROTO) prost_encoder_encode(tensor, dst);
-    else if (kind == TFS_MSG_PREDICT_REQUEST) prost_encoder_encode(req, dst);
-    else prost_encoder_encode(resp, dst);
+    switch (kind) {
+      case TFS_MSG_TENSOR_PROTO: prost_encoder_encode(tensor, dst); break;
+      case TFS_MSG_PREDICT_REQUEST: prost_encoder_encode(req, dst); break;
+      case TFS_MSG_INPUT: prost_encoder_encode(input, dst); break;
+      case TFS_MSG_CLASSIFY_REQUEST: prost_encoder_encode(classify, dst); break;
+      default: prost_encoder_encode(resp, dst);
+    }
   }
 };
+
+// Feature from its descriptor (`impl From<Payload> for Feature`, src/lib.rs:514-540)
+bool build_feature(const tfs_batch_t& b, const tfs_tensor_desc_t& td, Feature* f) {
+  if (td.dtype != 0 || td.has_shape || td.n_dims || td.n_fields > 1) return false;
+  if (static_cast<uint64_t>(td.first_field) + td.n_fields > b.n_fields) return false;
+  if (td.n_fields == 0) return true;  // kind: None
+  const tfs_field_desc_t& d = b.fields[td.first_field];
+  if (d.op != TFS_OP_NONE || (d.n_elems && !d.data)) return false;
+  const uint64_t n = d.n_elems;
+  switch (d.kind) {
+    case TFS_KIND_BYTES_LIST: {
+      if (d.src_type != TFS_T_RAGGED) return false;
+      f->kind = 1;
+      if (n == 0) return true;
+      const uint8_t* blk = static_cast<const uint8_t*>(d.data);
+      std::vector<uint64_t> off(n + 1);
+      std::memcpy(off.data(), blk, 8 * (n + 1));
+      if (off[0] != 0 || off[n] != d.aux) return false;
+      const uint8_t* bytes = blk + 8 * (n + 1);
+      f->bytes_list.resize(n);
+      for (uint64_t i = 0; i < n; ++i) {
+        if (off[i + 1] < off[i]) return false;
+        f->bytes_list[i].assign(bytes + off[i], bytes + off[i + 1]);
+      }
+      return true;
+    }
+    case TFS_KIND_FLOAT_LIST:
+      if (d.src_type != TFS_T_F32) return false;
+      f->kind = 2;
+      f->float_list.assign(static_cast<const float*>(d.data), static_cast<const float*>(d.data) + n);
+      return true;
+    case TFS_KIND_INT64_LIST:
+      if (d.src_type != TFS_T_I64) return false;
+      f->kind = 3;
+      f->int64_list.assign(static_cast<const int64_t*>(d.data), static_cast<const int64_t*>(d.data) + n);
+      return true;
+    default: return false;
+  }
+}
+
+bool build_input(const tfs_batch_t& b, const tfs_msg_desc_t& m, Input* in) {
+  in->examples.assign(m.n_filters, Example{});
+  for (auto& e : in->examples) e.features = FeatureMap{};  // Some(Features), as build_input does (src/lib.rs:420)
+  int64_t last = 0;
+  for (uint32_t i = 0; i < m.n_tensors; ++i) {
+    const tfs_tensor_desc_t& td = b.tensors[m.first_tensor + i];
+    if (td.version_number < last || static_cast<uint32_t>(td.version_number) >= m.n_filters) return false;
+    last = td.version_number;
+    Feature f;
+    if (!build_feature(b, td, &f)) return false;
+    in->examples[td.version_number].features->emplace_back(str(td.name), std::move(f));
+  }
+  return true;
+}
 
 bool build_msg(const tfs_batch_t& b, const tfs_msg_desc_t& m, AnyMsg* out) {
   out->kind = m.kind;
   if (static_cast<uint64_t>(m.first_tensor) + m.n_tensors > b.n_tensors) return false;
-  if (static_cast<uint64_t>(m.first_filter) + m.n_filters > b.n_filters) return false;
+  const bool input_kind = m.kind == TFS_MSG_INPUT || m.kind == TFS_MSG_CLASSIFY_REQUEST;  // n_filters counts Examples there
+  if (!input_kind && static_cast<uint64_t>(m.first_filter) + m.n_filters > b.n_filters) return false;
   if (m.version_choice < 0 || m.version_choice > 2) return false;
   if (m.kind == TFS_MSG_TENSOR_PROTO) {
     if (m.n_tensors != 1 || m.has_model_spec || m.n_filters) return false;
     return build_tensor(b, b.tensors[m.first_tensor], &out->tensor);
+  }
+  if (m.kind == TFS_MSG_INPUT) {
+    if (m.has_model_spec) return false;
+    return build_input(b, m, &out->input);
+  }
+  if (m.kind == TFS_MSG_CLASSIFY_REQUEST) {
+    if (m.has_model_spec) out->classify.model_spec = build_model_spec(m);
+    out->classify.input = Input{};
+    return build_input(b, m, &*out->classify.input);
   }
   if (m.kind != TFS_MSG_PREDICT_REQUEST && m.kind != TFS_MSG_PREDICT_RESPONSE) return false;
   TensorMap map;

@@ -9,7 +9,7 @@ from . import abi, messages, workloads, _lib, codec, sharding  # noqa: F401  (al
 from ._lib import TfsError  # noqa: F401
 from .codec import GpuCodec, GpuContext, GpuDecoder, GpuEncoder  # noqa: F401
 from .messages import (  # noqa: F401
-    ModelSpec, Payload, PredictRequest, PredictResponse, Ragged, TensorProto, TensorShapeProto, build_batch, ragged_block,
+    ClassificationRequest, Feature, Input, ModelSpec, Payload, PredictRequest, PredictResponse, Ragged, TensorProto, TensorShapeProto, build_batch, ragged_block,
     messages_from_view,
 )
 

@@ -66,7 +66,8 @@ TYPE_NUMPY = {T_U8: "u1", T_I8: "i1", T_U16: "<u2", T_I16: "<i2", T_I32: "<i4", 
               T_U64: "<u8", T_F16: "<u2", T_BF16: "<u2", T_F32: "<f4", T_F64: "<f8", T_BOOL: "u1"}
 
 OP_NONE, OP_DIV, OP_MUL = 0, 1, 2
-MSG_TENSOR_PROTO, MSG_PREDICT_REQUEST, MSG_PREDICT_RESPONSE = 0, 1, 2
+MSG_TENSOR_PROTO, MSG_PREDICT_REQUEST, MSG_PREDICT_RESPONSE, MSG_INPUT, MSG_CLASSIFY_REQUEST = 0, 1, 2, 3, 4
+KIND_BYTES_LIST, KIND_FLOAT_LIST, KIND_INT64_LIST = 1, 2, 3  # Feature.kind members (feature.proto:79-81)
 VERSION_NONE, VERSION_NUMBER, VERSION_LABEL = 0, 1, 2
 
 F_GRPC_PREFIX = 1 << 0

@@ -158,9 +158,95 @@ __device__ void emit_tensor_body(Sink& s, const EncTables& T, const EncTensor& t
   }
 }
 
+// ---- Input { example_list { examples: [Example { features { feature: map<string, Feature> } }] } } (TFS_MSG_INPUT) and
+//      the request around it (TFS_MSG_CLASSIFY_REQUEST): build_input, src/lib.rs:413-431.  Every feature is one EncTensor
+//      (version_number = index of its Example, ascending), EncMsg::n_filters = number of Examples.
+__device__ __forceinline__ bool is_input_kind(int32_t k) { return k == TFS_MSG_INPUT || k == TFS_MSG_CLASSIFY_REQUEST; }
+
+// body of the BytesList / FloatList / Int64List message of a feature
+__device__ __forceinline__ uint64_t feature_list_len(const EncTables& T, const EncTensor& t) {
+  const EncField& f = T.fields[t.first_field];
+  if (f.n_elems == 0) return 0;
+  return f.is_varint == FC_RAGGED ? f.body_len : 1u + varint_len(f.body_len) + f.body_len;
+}
+// body of the Feature message: the oneof member is written even when its list is empty; kind None -> nothing
+__device__ __forceinline__ uint64_t feature_body_len(const EncTables& T, const EncTensor& t) {
+  if (t.n_fields == 0) return 0;
+  const uint64_t l = feature_list_len(T, t);
+  return 1u + varint_len(l) + l;
+}
+// length of the Features map of the Example that starts at feature `ti`; *next = first feature of the next Example
+__device__ __forceinline__ uint64_t features_len_from(const EncTables& T, uint32_t ti, uint32_t te, int32_t example, uint32_t* next) {
+  uint64_t n = 0;
+  while (ti < te && T.tensors[ti].version_number == example) {
+    const uint64_t el = T.entry_len[ti];
+    n += 1u + varint_len(el) + el;
+    ++ti;
+  }
+  *next = ti;
+  return n;
+}
+__device__ uint64_t example_list_len(const EncTables& T, const EncMsg& m) {
+  const uint32_t te = m.first_tensor + m.n_tensors;
+  uint32_t ti = m.first_tensor;
+  uint64_t n = 0;
+  for (uint32_t e = 0; e < m.n_filters; ++e) {
+    const uint64_t fl = features_len_from(T, ti, te, static_cast<int32_t>(e), &ti);
+    const uint64_t xl = 1u + varint_len(fl) + fl;  // Example { features: Some(..) }
+    n += 1u + varint_len(xl) + xl;
+  }
+  return n;
+}
+template <class Sink, class OnBody>
+__device__ void emit_input(Sink& s, const EncTables& T, uint32_t mi, OnBody on_body) {
+  const EncMsg& m = T.msgs[mi];
+  const uint64_t list_len = example_list_len(T, m);
+  if (m.kind == TFS_MSG_CLASSIFY_REQUEST) {
+    if (m.has_model_spec) emit_model_spec(s, T, m, 1, T.spec_len[mi]);
+    put_key(s, 2, 2);  // input = 2
+    put_varint(s, 1u + varint_len(list_len) + list_len);
+  }
+  put_key(s, 1, 2);  // oneof kind: example_list = 1
+  put_varint(s, list_len);
+  const uint32_t te = m.first_tensor + m.n_tensors;
+  uint32_t ti = m.first_tensor;
+  for (uint32_t e = 0; e < m.n_filters; ++e) {
+    uint32_t next;
+    const uint64_t fl = features_len_from(T, ti, te, static_cast<int32_t>(e), &next);
+    put_key(s, 1, 2);  // examples = 1
+    put_varint(s, 1u + varint_len(fl) + fl);
+    put_key(s, 1, 2);  // features = 1
+    put_varint(s, fl);
+    for (; ti < next; ++ti) {
+      const EncTensor& t = T.tensors[ti];
+      put_key(s, 1, 2);  // map entry of `feature`
+      put_varint(s, T.entry_len[ti]);
+      if (t.name.len) emit_string(s, 1, T.strings, t.name);
+      if (t.n_fields == 0) continue;  // Feature::default(): the value is left out of the entry
+      put_key(s, 2, 2);
+      put_varint(s, T.tensor_len[ti]);
+      const uint32_t fi = t.first_field;
+      const EncField& f = T.fields[fi];
+      put_key(s, static_cast<uint32_t>(f.kind), 2);  // bytes_list = 1 / float_list = 2 / int64_list = 3
+      put_varint(s, feature_list_len(T, t));
+      if (f.n_elems == 0) continue;
+      if (f.is_varint != FC_RAGGED) {  // packed `value = 1`
+        put_key(s, 1, 2);
+        put_varint(s, f.body_len);
+      }
+      on_body(fi, s.pos);
+      s.skip(f.body_len);
+    }
+  }
+}
+
 template <class Sink, class OnBody>
 __device__ void emit_message(Sink& s, const EncTables& T, uint32_t mi, OnBody on_body) {
   const EncMsg& m = T.msgs[mi];
+  if (is_input_kind(m.kind)) {
+    emit_input(s, T, mi, on_body);
+    return;
+  }
   if (m.kind == TFS_MSG_TENSOR_PROTO) {
     emit_tensor_body(s, T, T.tensors[m.first_tensor], on_body);
     return;
@@ -191,6 +277,12 @@ __device__ void msg_layout_body(const EncTables& T, uint32_t mi) {
   for (uint32_t i = 0; i < m.n_tensors; ++i) {
     const uint32_t ti = m.first_tensor + i;
     const EncTensor& t = T.tensors[ti];
+    if (is_input_kind(m.kind)) {  // a feature: tensor_len = Feature body, entry_len = map entry body
+      const uint64_t fl = feature_body_len(T, t);
+      T.tensor_len[ti] = fl;
+      T.entry_len[ti] = (t.name.len ? str_field_len(t.name.len) : 0) + (t.n_fields ? 1u + varint_len(fl) + fl : 0);
+      continue;
+    }
     const uint64_t tl = tensor_body_len(T, t);
     T.tensor_len[ti] = tl;
     uint64_t el = 0;
@@ -384,6 +476,13 @@ bool compile_field(const tfs_field_desc_t& f, EncField* o, uint64_t* max_body) {
       if (st == TFS_T_F32 && dt == TFS_T_F16) return varint_class(VM_F32_F16, 3);
       if (st == TFS_T_F32 && dt == TFS_T_BF16) return varint_class(VM_F32_BF16, 3);
       return false;
+    case TFS_KIND_FLOAT_LIST:  // FloatList.value: packed fixed32
+      if (st != TFS_T_F32 || (dt != TFS_T_NONE && dt != TFS_T_F32)) return false;
+      return copy_class(CP_BYTES, f.n_elems * 4);
+    case TFS_KIND_INT64_LIST:  // Int64List.value: packed varint
+      if (st != TFS_T_I64 || (dt != TFS_T_NONE && dt != TFS_T_I64)) return false;
+      return varint_class(VM_I64, 10);
+    case TFS_KIND_BYTES_LIST:  // BytesList.value = 1: the record key byte (1 << 3 | 2) is this kind's own number
     case TFS_KIND_STRING_VAL: {  // repeated bytes, flattened: (n + 1) u64 offsets, then the bytes
       if (st != TFS_T_RAGGED || (dt != TFS_T_NONE && dt != TFS_T_RAGGED) || (reinterpret_cast<uintptr_t>(f.data) & 7u) != 0) return false;
       o->is_varint = FC_RAGGED;
@@ -414,9 +513,11 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
     const tfs_msg_desc_t& m = b->msgs[mi];
     EncMsg& o = c->msgs[mi];
     std::memset(&o, 0, sizeof(o));
-    if (m.kind < TFS_MSG_TENSOR_PROTO || m.kind > TFS_MSG_PREDICT_RESPONSE) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad message kind");
+    if (m.kind < TFS_MSG_TENSOR_PROTO || m.kind > TFS_MSG_CLASSIFY_REQUEST) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad message kind");
+    const bool input_kind = m.kind == TFS_MSG_INPUT || m.kind == TFS_MSG_CLASSIFY_REQUEST;  // n_filters counts Examples there
     if (static_cast<uint64_t>(m.first_tensor) + m.n_tensors > b->n_tensors) return set_err(ctx, TFS_ERR_INVALID_ARG, "tensor range out of bounds");
-    if (static_cast<uint64_t>(m.first_filter) + m.n_filters > b->n_filters) return set_err(ctx, TFS_ERR_INVALID_ARG, "filter range out of bounds");
+    if (!input_kind && static_cast<uint64_t>(m.first_filter) + m.n_filters > b->n_filters) return set_err(ctx, TFS_ERR_INVALID_ARG, "filter range out of bounds");
+    if (m.kind == TFS_MSG_INPUT && m.has_model_spec) return set_err(ctx, TFS_ERR_INVALID_ARG, "Input has no model_spec");
     if (m.version_choice < TFS_VERSION_NONE || m.version_choice > TFS_VERSION_LABEL) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad version_choice");
     if (m.kind == TFS_MSG_TENSOR_PROTO && (m.n_tensors != 1 || m.has_model_spec || m.n_filters))
       return set_err(ctx, TFS_ERR_INVALID_ARG, "a bare TensorProto message has exactly one tensor and nothing else");
@@ -427,16 +528,17 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
     o.version = m.version_choice == TFS_VERSION_NUMBER ? m.version : 0;
     o.first_tensor = m.first_tensor;
     o.n_tensors = m.n_tensors;
-    o.first_filter = m.first_filter;
+    o.first_filter = input_kind ? 0 : m.first_filter;
     o.n_filters = m.n_filters;
-    uint64_t bound = 64 + prefix;
+    uint64_t bound = 64 + prefix + (input_kind ? 24ull * m.n_filters : 0);
+    int32_t last_example = 0;
     if (m.has_model_spec) {
       o.model_name = add_str(*c, m.model_name);
       o.signature_name = add_str(*c, m.signature_name);
       if (m.version_choice == TFS_VERSION_LABEL) o.version_label = add_str(*c, m.version_label);
       bound += m.model_name.len + m.signature_name.len + m.version_label.len + 48;
     }
-    for (uint32_t i = 0; i < m.n_filters; ++i) bound += b->filters[m.first_filter + i].len + 8;
+    for (uint32_t i = 0; i < m.n_filters && !input_kind; ++i) bound += b->filters[m.first_filter + i].len + 8;
     for (uint32_t i = 0; i < m.n_tensors; ++i) {
       const uint32_t ti = m.first_tensor + i;
       if (tensor_used[ti]++) return set_err(ctx, TFS_ERR_INVALID_ARG, "a tensor descriptor is referenced twice");
@@ -446,6 +548,12 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
       if (t.n_dims > TFS_MAX_DIMS) return set_err(ctx, TFS_ERR_INVALID_ARG, "rank exceeds TFS_MAX_DIMS");
       if (!t.has_shape && (t.n_dims || t.unknown_rank)) return set_err(ctx, TFS_ERR_INVALID_ARG, "dims without has_shape");
       if (static_cast<uint64_t>(t.first_field) + t.n_fields > b->n_fields) return set_err(ctx, TFS_ERR_INVALID_ARG, "field range out of bounds");
+      if (input_kind) {  // a Feature: no dtype / shape, at most one list, Example index ascending
+        if (t.dtype || t.has_shape || t.n_fields > 1) return set_err(ctx, TFS_ERR_INVALID_ARG, "a feature has no dtype / shape and at most one list");
+        if (t.version_number < last_example || static_cast<uint32_t>(t.version_number) >= m.n_filters)
+          return set_err(ctx, TFS_ERR_INVALID_ARG, "feature: Example index not ascending or out of range");
+        last_example = t.version_number;
+      }
       ot.name = m.kind == TFS_MSG_TENSOR_PROTO ? StrRef{0, 0} : add_str(*c, t.name);
       ot.dtype = t.dtype;
       ot.version_number = t.version_number;
@@ -460,7 +568,10 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
       for (uint32_t k = 0; k < t.n_fields; ++k) {
         const uint32_t fi = t.first_field + k;
         if (field_used[fi]++) return set_err(ctx, TFS_ERR_INVALID_ARG, "a field descriptor is referenced twice");
-        const int32_t slot = tfs_slot_of_kind(b->fields[fi].kind);
+        const int32_t fk = b->fields[fi].kind;
+        if (input_kind != (fk >= TFS_KIND_BYTES_LIST && fk <= TFS_KIND_INT64_LIST))
+          return set_err(ctx, TFS_ERR_INVALID_ARG, "list kinds belong to features, *_val kinds to tensors");
+        const int32_t slot = input_kind ? 0 : tfs_slot_of_kind(fk);
         if (slot < 0 || ((seen >> slot) & 1u)) return set_err(ctx, TFS_ERR_INVALID_ARG, "unknown or repeated payload kind in one tensor");
         seen |= 1u << slot;
         if (!compile_field(b->fields[fi], &c->fields[fi], &field_bound[fi]))

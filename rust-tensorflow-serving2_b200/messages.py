@@ -88,6 +88,30 @@ class PredictResponse:
     model_spec: Optional[ModelSpec] = None
 
 
+@dataclass
+class Feature:
+    """feature.proto:76-83: oneof kind { bytes_list = 1, float_list = 2, int64_list = 3 } (`Payload` at src/lib.rs:497-512).
+    bytes_list: list of bytes-like (or a Ragged block); float_list: float32 array; int64_list: int64 array; all None =
+    Feature { kind: None }."""
+    bytes_list: Any = None
+    float_list: Any = None
+    int64_list: Any = None
+
+
+@dataclass
+class Input:
+    """tensorflow.serving.Input with an ExampleList (input.proto:77-82), as build_input makes it (src/lib.rs:413-431):
+    `examples` is a list of Examples, each an ordered list of (feature name, Feature)."""
+    examples: List[List[Tuple[str, Feature]]] = field(default_factory=list)
+
+
+@dataclass
+class ClassificationRequest:
+    """classification.proto:33-40 (RegressionRequest is field-for-field the same, regression.proto:23-30)."""
+    model_spec: Optional[ModelSpec] = None
+    input: Input = field(default_factory=Input)
+
+
 _NP_TYPES = {
     "uint8": abi.T_U8, "int8": abi.T_I8, "uint16": abi.T_U16, "int16": abi.T_I16, "int32": abi.T_I32,
     "uint32": abi.T_U32, "int64": abi.T_I64, "uint64": abi.T_U64, "float16": abi.T_F16, "float32": abi.T_F32,
@@ -213,11 +237,61 @@ def build_batch(messages, kind) -> BuiltBatch:
         td.n_fields = n
         ten_l.append(td)
 
+    def add_feature(name, ft: Feature, example_index: int):
+        td = abi.TensorDesc()
+        td.name = _mk_str(name, keep)
+        td.version_number = example_index  # which Example of the list the feature belongs to
+        td.first_field = len(fld_l)
+        set_ = [(k, v) for k, v in ((abi.KIND_BYTES_LIST, ft.bytes_list), (abi.KIND_FLOAT_LIST, ft.float_list),
+                                    (abi.KIND_INT64_LIST, ft.int64_list)) if v is not None]
+        if len(set_) > 1:
+            raise ValueError("Feature.kind is a oneof: set at most one list")
+        for k, v in set_:
+            fd = abi.FieldDesc()
+            fd.kind, fd.dst_type, fd.op = k, abi.T_NONE, abi.OP_NONE
+            if k == abi.KIND_BYTES_LIST:
+                if not isinstance(v, Ragged):
+                    blk = ragged_block(v)
+                    v = Ragged(blk, len(v), blk.size - 8 * (len(v) + 1))
+                ptr, _, ty, ka = _array_info(v.block)
+                fd.src_type, fd.n_elems, fd.data, fd.aux = abi.T_RAGGED, v.n_elems, ptr, v.total_bytes
+            else:
+                ptr, count, ty, ka = _array_info(v)
+                want = abi.T_F32 if k == abi.KIND_FLOAT_LIST else abi.T_I64
+                if ty != want:
+                    raise TypeError("float_list takes float32, int64_list takes int64")
+                fd.src_type, fd.n_elems, fd.data = ty, count, ptr
+            keep.append(ka)
+            fld_l.append(fd)
+        td.n_fields = len(set_)
+        ten_l.append(td)
+
     for m in messages:
         md = abi.MsgDesc()
         md.kind = kind
         md.first_tensor = len(ten_l)
         md.first_filter = len(flt_l)
+        if kind in (abi.MSG_INPUT, abi.MSG_CLASSIFY_REQUEST):
+            inp = m if kind == abi.MSG_INPUT else m.input
+            for ei, ex in enumerate(inp.examples):
+                for name, ft in ex:
+                    add_feature(name, ft, ei)
+            if kind == abi.MSG_CLASSIFY_REQUEST and m.model_spec is not None:
+                ms = m.model_spec
+                md.has_model_spec = 1
+                md.model_name = _mk_str(ms.name, keep)
+                md.signature_name = _mk_str(ms.signature_name, keep)
+                if ms.version is not None:
+                    md.version_choice = abi.VERSION_NUMBER
+                    md.version = int(ms.version)
+                elif ms.version_label is not None:
+                    md.version_choice = abi.VERSION_LABEL
+                    md.version_label = _mk_str(ms.version_label, keep)
+            md.n_tensors = len(ten_l) - md.first_tensor
+            md.first_filter = 0
+            md.n_filters = len(inp.examples)  # number of Examples (see TFS_MSG_INPUT in tfs_gpu.h)
+            msg_l.append(md)
+            continue
         if kind == abi.MSG_TENSOR_PROTO:
             add_tensor("", m)
         else:

@@ -11,7 +11,7 @@ from typing import List
 import numpy as np
 
 from . import abi
-from .messages import ModelSpec, Payload, PredictRequest, PredictResponse, Ragged, TensorProto, TensorShapeProto, ragged_block
+from .messages import ClassificationRequest, Feature, Input, ModelSpec, Payload, PredictRequest, PredictResponse, Ragged, TensorProto, TensorShapeProto, ragged_block
 
 
 def c1_request() -> PredictRequest:
@@ -160,12 +160,19 @@ def to_device(messages, kind, device):
             setattr(t2, name, mv(getattr(t, name)))
         return t2
 
+    def mv_input(inp: Input) -> Input:
+        return Input([[(k, Feature(mv(f.bytes_list), mv(f.float_list), mv(f.int64_list))) for k, f in ex] for ex in inp.examples])
+
     out = []
     for m in messages:
         if kind == abi.MSG_TENSOR_PROTO:
             out.append(mv_tensor(m))
         elif kind == abi.MSG_PREDICT_REQUEST:
             out.append(PredictRequest(m.model_spec, [(k, mv_tensor(t)) for k, t in m.inputs], list(m.output_filter)))
+        elif kind == abi.MSG_INPUT:
+            out.append(mv_input(m))
+        elif kind == abi.MSG_CLASSIFY_REQUEST:
+            out.append(ClassificationRequest(m.model_spec, mv_input(m.input)))
         else:
             out.append(PredictResponse([(k, mv_tensor(t)) for k, t in m.outputs], m.model_spec))
     return out

@@ -94,6 +94,141 @@ PredictRequestPB, PredictResponsePB = build_predict_classes()
 
 
 # ---- plain-dict message descriptions <-> upb messages ---------------------------------------------
+def build_example_classes():
+    """Feature / Features / Example (feature.proto:65-87, example.proto:88-90), ExampleList / Input (input.proto:15-82) and
+    ClassificationRequest (classification.proto:33-40), rebuilt at run time like the predict messages above."""
+    pool = descriptor_pool.Default()
+    f = descriptor_pb2.FileDescriptorProto()
+    f.name, f.package, f.syntax = "golden/tf_example.proto", "tensorflow", "proto3"
+
+    def scalar_list(name, typ, packed):
+        m = f.message_type.add()
+        m.name = name
+        fd = m.field.add()
+        fd.name, fd.number, fd.type, fd.label = "value", 1, typ, 3
+        if packed:
+            fd.options.packed = True
+    scalar_list("BytesList", 12, False)
+    scalar_list("FloatList", 2, True)
+    scalar_list("Int64List", 3, True)
+    ft = f.message_type.add()
+    ft.name = "Feature"
+    ft.oneof_decl.add().name = "kind"
+    for name, num, tname in (("bytes_list", 1, "BytesList"), ("float_list", 2, "FloatList"), ("int64_list", 3, "Int64List")):
+        fd = ft.field.add()
+        fd.name, fd.number, fd.type, fd.label, fd.type_name, fd.oneof_index = name, num, 11, 1, ".tensorflow." + tname, 0
+    fs = f.message_type.add()
+    fs.name = "Features"
+    e = fs.nested_type.add()
+    e.name = "FeatureEntry"
+    e.options.map_entry = True
+    k = e.field.add()
+    k.name, k.number, k.type, k.label = "key", 1, 9, 1
+    v = e.field.add()
+    v.name, v.number, v.type, v.label, v.type_name = "value", 2, 11, 1, ".tensorflow.Feature"
+    fd = fs.field.add()
+    fd.name, fd.number, fd.type, fd.label, fd.type_name = "feature", 1, 11, 3, ".tensorflow.Features.FeatureEntry"
+    ex = f.message_type.add()
+    ex.name = "Example"
+    fd = ex.field.add()
+    fd.name, fd.number, fd.type, fd.label, fd.type_name = "features", 1, 11, 1, ".tensorflow.Features"
+    pool.Add(f)
+
+    g = descriptor_pb2.FileDescriptorProto()
+    g.name, g.package, g.syntax = "golden/tfs_input.proto", "tensorflow.serving", "proto3"
+    g.dependency.extend(["golden/tf_example.proto", "golden/tfs_model.proto"])
+    el = g.message_type.add()
+    el.name = "ExampleList"
+    fd = el.field.add()
+    fd.name, fd.number, fd.type, fd.label, fd.type_name = "examples", 1, 11, 3, ".tensorflow.Example"
+    inp = g.message_type.add()
+    inp.name = "Input"
+    inp.oneof_decl.add().name = "kind"
+    fd = inp.field.add()
+    fd.name, fd.number, fd.type, fd.label, fd.type_name, fd.oneof_index = "example_list", 1, 11, 1, ".tensorflow.serving.ExampleList", 0
+    cr = g.message_type.add()
+    cr.name = "ClassificationRequest"
+    fd = cr.field.add()
+    fd.name, fd.number, fd.type, fd.label, fd.type_name = "model_spec", 1, 11, 1, ".tensorflow.serving.ModelSpec"
+    fd = cr.field.add()
+    fd.name, fd.number, fd.type, fd.label, fd.type_name = "input", 2, 11, 1, ".tensorflow.serving.Input"
+    pool.Add(g)
+    get = lambda n: message_factory.GetMessageClass(pool.FindMessageTypeByName(n))
+    return get("tensorflow.serving.Input"), get("tensorflow.serving.ClassificationRequest")
+
+
+def fill_input(pb, examples):
+    pb.example_list.SetInParent()
+    for ex in examples:
+        e = pb.example_list.examples.add()
+        e.features.SetInParent()
+        for key, ft in ex:
+            dst = e.features.feature[key]
+            if "bytes_list" in ft:
+                dst.bytes_list.SetInParent()
+                dst.bytes_list.value.extend([bytes.fromhex(x) for x in ft["bytes_list"]])
+            elif "float_list" in ft:
+                # through the wire form so that NaN payloads survive
+                a = np.frombuffer(bytes.fromhex(ft["float_list"]), dtype="<f4")
+                dst.float_list.SetInParent()
+                if a.size:
+                    dst.float_list.MergeFromString(bytes([0x0a]) + varint(a.nbytes) + a.tobytes())
+            else:
+                dst.int64_list.SetInParent()
+                dst.int64_list.value.extend([int(x) for x in np.frombuffer(bytes.fromhex(ft["int64_list"]), dtype="<i8")])
+
+
+def input_cases():
+    """Encode-only: what build_input produces (src/lib.rs:413-431).  Feature keys are listed in sorted order (upb's
+    deterministic map order) and never empty, every Feature has a kind: the default-key / default-value cases where
+    upb and prost differ are hand-written in tests/test_oracle.py."""
+    rng = np.random.default_rng(777)
+    i64 = lambda v: np.asarray(v, dtype="<i8").tobytes().hex()
+    f4 = lambda v: np.asarray(v, dtype="<f4").tobytes().hex()
+    cases = []
+    one = [[["age", {"int64_list": i64([29])}], ["name", {"bytes_list": [b"bob".hex(), b"".hex()]}], ["w", {"float_list": f4([1.5, 2.5])}]]]
+    cases.append({"name": "input_one_example", "kind": "input", "msg": {"model_spec": None, "examples": one}})
+    cases.append({"name": "input_no_examples", "kind": "input", "msg": {"model_spec": None, "examples": []}})
+    cases.append({"name": "input_empty_examples_and_lists", "kind": "input", "msg": {"model_spec": None, "examples": [
+        [], [["a", {"float_list": f4([])}], ["b", {"int64_list": i64([])}], ["c", {"bytes_list": []}]], []]}})
+    many = []
+    for e in range(40):
+        feats = []
+        for j in range(int(rng.integers(0, 6))):
+            which = int(rng.integers(0, 3))
+            n = int(rng.integers(0, 50))
+            if which == 0:
+                ft = {"int64_list": i64(rng.integers(-(1 << 40), 1 << 40, n))}
+            elif which == 1:
+                ft = {"float_list": f4(rng.standard_normal(n))}
+            else:
+                ft = {"bytes_list": [rng.integers(0, 256, int(rng.integers(0, 30)), dtype=np.uint8).tobytes().hex() for _ in range(n % 7)]}
+            feats.append(["f%02d" % j, ft])
+        many.append(feats)
+    cases.append({"name": "input_40_examples", "kind": "input", "msg": {"model_spec": None, "examples": many}})
+    cases.append({"name": "classify_request", "kind": "classify", "msg": {
+        "model_spec": {"name": "census", "signature_name": "classify", "version": 3, "version_label": None}, "examples": one + many[:5]}})
+    cases.append({"name": "classify_big_lists", "kind": "classify", "msg": {
+        "model_spec": {"name": "wide", "signature_name": "", "version": None, "version_label": None},
+        "examples": [[["ids", {"int64_list": i64(rng.integers(0, 30522, 2100))}], ["img", {"bytes_list": [rng.integers(0, 256, 5000, dtype=np.uint8).tobytes().hex()]}],
+                      ["x", {"float_list": f4(rng.standard_normal(1000))}]]]}})
+    for c in cases:
+        if c["kind"] == "input":
+            pb = InputPB()
+            fill_input(pb, c["msg"]["examples"])
+        else:
+            pb = ClassificationRequestPB()
+            if c["msg"]["model_spec"] is not None:
+                fill_model_spec(pb.model_spec, c["msg"]["model_spec"])
+            pb.input.SetInParent()
+            fill_input(pb.input, c["msg"]["examples"])
+        c["wire"] = pb.SerializeToString(deterministic=True).hex()
+    return cases
+
+
+InputPB, ClassificationRequestPB = build_example_classes()
+
+
 def arr_hex(a):
     return np.ascontiguousarray(a).tobytes().hex()
 
@@ -470,7 +605,7 @@ def main():
             ok = back == c["msg"] or any("7fa00001" in v or "0100a07f" in v or "f47f" in v for v in c["msg"]["fields"].values() if isinstance(v, str))
             assert ok, (c["name"], back, c["msg"])
     doc = {"generator": "tests/golden/make_golden.py", "protobuf": __import__("google.protobuf").protobuf.__version__,
-           "encode": enc, "decode": decode_cases(), "errors": error_cases()}
+           "encode": enc, "decode": decode_cases(), "errors": error_cases(), "input": input_cases()}
     path = os.path.join(HERE, "upb_vectors.json")
     with open(path, "w") as f:
         json.dump(doc, f, indent=0, ensure_ascii=True)

@@ -15,7 +15,30 @@ FIELD_NP = {
     "int64_val": "<i8", "bool_val": "u1", "dcomplex_val": "<f8", "half_val": "<i4", "uint32_val": "<u4",
     "uint64_val": "<u8",
 }
-KIND_OF = {"tensor": abi.MSG_TENSOR_PROTO, "request": abi.MSG_PREDICT_REQUEST, "response": abi.MSG_PREDICT_RESPONSE}
+KIND_OF = {"tensor": abi.MSG_TENSOR_PROTO, "request": abi.MSG_PREDICT_REQUEST, "response": abi.MSG_PREDICT_RESPONSE,
+           "input": abi.MSG_INPUT, "classify": abi.MSG_CLASSIFY_REQUEST}
+
+
+def feature_from_desc(d) -> tfs.Feature:
+    if "bytes_list" in d:
+        return tfs.Feature(bytes_list=[bytes.fromhex(x) for x in d["bytes_list"]])
+    if "float_list" in d:
+        return tfs.Feature(float_list=np.frombuffer(bytes.fromhex(d["float_list"]), dtype="<f4").copy())
+    if "int64_list" in d:
+        return tfs.Feature(int64_list=np.frombuffer(bytes.fromhex(d["int64_list"]), dtype="<i8").copy())
+    return tfs.Feature()
+
+
+def input_from_desc(kind: str, m):
+    """Golden "input" section -> tfs.Input / tfs.ClassificationRequest."""
+    inp = tfs.Input([[(k, feature_from_desc(ft)) for k, ft in ex] for ex in m["examples"]])
+    if kind == "input":
+        return inp
+    ms = None
+    if m["model_spec"] is not None:
+        s = m["model_spec"]
+        ms = tfs.ModelSpec(s["name"], s.get("version"), s.get("version_label"), s["signature_name"])
+    return tfs.ClassificationRequest(ms, inp)
 
 _golden = None
 

@@ -74,12 +74,19 @@ def pinned_like(msgs, kind):
             setattr(t2, name, mv(getattr(t, name)))
         return t2
 
+    def mv_input(inp):
+        return tfs.Input([[(k, tfs.Feature(mv(f.bytes_list), mv(f.float_list), mv(f.int64_list))) for k, f in ex] for ex in inp.examples])
+
     out = []
     for m in msgs:
         if kind == abi.MSG_TENSOR_PROTO:
             out.append(mv_tensor(m))
         elif kind == abi.MSG_PREDICT_REQUEST:
             out.append(tfs.PredictRequest(m.model_spec, [(k, mv_tensor(t)) for k, t in m.inputs], list(m.output_filter)))
+        elif kind == abi.MSG_INPUT:
+            out.append(mv_input(m))
+        elif kind == abi.MSG_CLASSIFY_REQUEST:
+            out.append(tfs.ClassificationRequest(m.model_spec, mv_input(m.input)))
         else:
             out.append(tfs.PredictResponse([(k, mv_tensor(t)) for k, t in m.outputs], m.model_spec))
     return out, keep
@@ -497,6 +504,78 @@ def test_string_val_descriptor_must_match_memory(codec):
         codec.encoder().encode_host([tfs.TensorProto(dtype=7, string_val=tfs.Ragged(desc, 2, 2))], abi.MSG_TENSOR_PROTO)
     # and the context is still usable
     assert codec.encoder().encode_host([tfs.TensorProto(dtype=7, string_val=[b"ok"])], abi.MSG_TENSOR_PROTO).all_bytes() == [bytes.fromhex("0807" "42026f6b")]
+
+
+# ---- Example / Features / Input framing, encode only ---------------------------------
+@pytest.mark.parametrize("kind_name", ["input", "classify"])
+def test_input_golden_vectors(codec, kind_name):
+    cases = [c for c in G["input"] if c["kind"] == kind_name]
+    msgs = [helpers.input_from_desc(kind_name, c["msg"]) for c in cases]
+    got = gpu_encode_both(codec, msgs, helpers.KIND_OF[kind_name])
+    for c, g in zip(cases, got):
+        assert_bytes_equal([g], [bytes.fromhex(c["wire"])], c["name"])
+
+
+def _random_input(rng, n_examples, max_feats, max_vals, with_defaults=True):
+    exs = []
+    for _ in range(n_examples):
+        feats = []
+        for j in range(int(rng.integers(0, max_feats + 1))):
+            which = int(rng.integers(0, 4 if with_defaults else 3))
+            n = int(rng.integers(0, max_vals + 1))
+            name = "" if (with_defaults and rng.integers(0, 9) == 0) else "feature_%d" % j
+            if which == 0:
+                ft = tfs.Feature(int64_list=rng.integers(-(1 << 50), 1 << 50, n, dtype=np.int64))
+            elif which == 1:
+                ft = tfs.Feature(float_list=rng.standard_normal(n).astype(np.float32))
+            elif which == 2:
+                ft = tfs.Feature(bytes_list=_strings(rng, rng.integers(0, 60, n % 9)))
+            else:
+                ft = tfs.Feature()  # kind: None
+            feats.append((name, ft))
+        exs.append(feats)
+    return tfs.Input(exs)
+
+
+@pytest.mark.parametrize("flags", [0, abi.F_GRPC_PREFIX, abi.F_ALIGN_PAYLOAD])
+def test_input_random_batches_match_the_oracle(codec, flags):
+    rng = np.random.default_rng(31 + flags)
+    inputs = [_random_input(rng, int(rng.integers(0, 12)), 5, 300) for _ in range(40)]
+    got = gpu_encode_both(codec, inputs, abi.MSG_INPUT, flags)
+    assert_bytes_equal(got, ob.encode_messages(inputs, abi.MSG_INPUT, flags & abi.F_GRPC_PREFIX), "Input batch")
+    reqs = [tfs.ClassificationRequest(tfs.ModelSpec("m%d" % i, version=i if i % 3 else None, signature_name="classify" if i % 2 else ""), inp)
+            for i, inp in enumerate(inputs)]
+    got = gpu_encode_both(codec, reqs, abi.MSG_CLASSIFY_REQUEST, flags)
+    assert_bytes_equal(got, ob.encode_messages(reqs, abi.MSG_CLASSIFY_REQUEST, flags & abi.F_GRPC_PREFIX), "ClassificationRequest batch")
+
+
+def test_input_large_lists_and_many_messages(codec):
+    rng = np.random.default_rng(8)
+    big = tfs.Input([[("ids", tfs.Feature(int64_list=rng.integers(0, 30522, 300_000, dtype=np.int64))),
+                      ("image", tfs.Feature(bytes_list=_strings(rng, [200_000, 0, 70_001]))),
+                      ("x", tfs.Feature(float_list=rng.standard_normal(1_000_000).astype(np.float32)))],
+                     [("ids", tfs.Feature(int64_list=rng.integers(-9, 9, 5000, dtype=np.int64)))]])
+    got = gpu_encode_both(codec, [big], abi.MSG_INPUT, abi.F_ALIGN_PAYLOAD)
+    assert_bytes_equal(got, ob.encode_messages([big], abi.MSG_INPUT), "big Input")
+    many = [_random_input(rng, 2, 3, 20, with_defaults=False) for _ in range(700)]   # > 256 messages: the multi-kernel framing path
+    got = gpu_encode_both(codec, many, abi.MSG_INPUT)
+    assert_bytes_equal(got, ob.encode_messages(many, abi.MSG_INPUT), "700 Inputs")
+
+
+def test_input_descriptor_errors(codec):
+    enc = codec.encoder()
+    bad_order = tfs.build_batch([tfs.Input([[("a", tfs.Feature())], [("b", tfs.Feature())]])], abi.MSG_INPUT)
+    bad_order.tensors[0].version_number = 1
+    bad_order.tensors[1].version_number = 0   # Example indices must ascend
+    with pytest.raises(tfs.TfsError) as e:
+        enc.encode_host(bad_order, abi.MSG_INPUT)
+    assert e.value.status == abi.TFS_ERR_INVALID_ARG
+    mixed = tfs.build_batch([tfs.TensorProto(dtype=1, float_val=np.ones(3, np.float32))], abi.MSG_TENSOR_PROTO)
+    mixed.fields[0].kind = abi.KIND_FLOAT_LIST   # a list kind outside an Input
+    with pytest.raises(tfs.TfsError):
+        enc.encode_host(mixed, abi.MSG_TENSOR_PROTO)
+    with pytest.raises(tfs.TfsError):            # decode of Input is not provided: the reference only builds Inputs
+        codec.decoder().decode_host(np.zeros(4, np.uint8), [0], [4], abi.MSG_INPUT)
 
 
 # ---- BASELINE configs ---------------------------------------------------------------------------------
