@@ -428,6 +428,37 @@ def other_configs(codec, dev, peak):
     msgs, nb = string_requests(64, 32, 100_000, 300_000)
     out["DT_STRING string_val, 64 requests x 32 encoded images of 100-300 kB"] = measure(msgs, abi.MSG_PREDICT_REQUEST, nb, reps=3)
     del msgs
+    # Classify / Regress inputs (section 8(f) row 1), encode only: 64 requests x 64 Examples x {ids int64[128], weights f32[128], tag bytes}
+    def classify_requests(n_req, n_ex, n_val):
+        reqs, in_bytes = [], 0
+        for r in range(n_req):
+            ids = torch.randint(0, 30522, (n_ex, n_val), device=dev, generator=g, dtype=torch.int64)
+            w = torch.randn(n_ex, n_val, device=dev, generator=g)
+            tag = tfs.ragged_block([b"label-%d" % (r % 7)])
+            tag_dev = torch.from_numpy(tag).to(dev)
+            exs = [[("ids", tfs.Feature(int64_list=ids[e])), ("weights", tfs.Feature(float_list=w[e])),
+                    ("tag", tfs.Feature(bytes_list=tfs.Ragged(tag_dev, 1, tag.size - 16)))] for e in range(n_ex)]
+            reqs.append(tfs.ClassificationRequest(tfs.ModelSpec("wide_deep", signature_name="classify"), tfs.Input(exs)))
+            in_bytes += n_ex * n_val * 12
+        return reqs, in_bytes
+    reqs, nb = classify_requests(64, 64, 128)
+    built = tfs.build_batch(reqs, abi.MSG_CLASSIFY_REQUEST)
+    wire = torch.empty(enc.bound(built, 0), dtype=torch.uint8, device=dev)
+    for _ in range(2):
+        eb = enc.encode(built, abi.MSG_CLASSIFY_REQUEST, 0, dst=wire)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(3):
+        eb = enc.encode(built, abi.MSG_CLASSIFY_REQUEST, 0, dst=wire)
+    ev1.record()
+    torch.cuda.synchronize()
+    te = ev0.elapsed_time(ev1) / 3
+    W = sum(eb.lengths)
+    out["ClassificationRequest, 64 requests x 64 Examples x (int64[128] + f32[128] + 1 tag), encode"] = {
+        "messages": 64, "features": 64 * 64 * 3, "wire_MB": round(W / 1e6, 2), "encode_ms": round(te, 4),
+        "encode_wire_GBps": round(W / (te * 1e-3) / 1e9, 1), "encode_algorithmic_GBps": round((nb + W) / (te * 1e-3) / 1e9, 1),
+        "note": "framing is one thread per message: 12 288 features are walked by 64 threads"}
+    del reqs, built, wire
     msgs, nb = string_requests(64, 512, 0, 40)
     out["DT_STRING string_val, 64 requests x 512 tokens of 0-40 bytes (decode walks each message serially: ~3.6 us per element)"] = measure(msgs, abi.MSG_PREDICT_REQUEST, nb, reps=3)
     return out

@@ -1107,7 +1107,10 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       T.tile_base = reinterpret_cast<uint64_t*>(d3 + p_tb);
     }
   } else {
-    k_walk<false><<<mblocks, 128, 0, ctx->stream>>>(T);
+    {
+      ProfScope prof(ctx, PK_WALK);
+      k_walk<false><<<mblocks, 128, 0, ctx->stream>>>(T);
+    }
     ctx->launches++;
     k_scan_counts<<<1, 1024, 0, ctx->stream>>>(T);
     ctx->launches++;
@@ -1140,6 +1143,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);
     if (n_tensors) DEC_CUDA(cudaMemsetAsync(T.tensors, 0, sizeof(tfs_tensor_out_t) * n_tensors, ctx->stream));
     if (n_msgs) {
+      ProfScope prof(ctx, PK_WALK);
       k_walk<true><<<mblocks, 128, 0, ctx->stream>>>(T);
       ctx->launches++;
     }

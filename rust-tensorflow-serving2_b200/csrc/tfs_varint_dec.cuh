@@ -198,24 +198,41 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
       }
     }
   } else {
-    // general path: bytes in shared memory (with the 16 bytes before the tile), walk back from each terminator
+    // general path (some value of the tile is longer than 4 bytes): the tile's bytes are in shared memory behind the 16
+    // bytes that precede it.  Per terminator: its length from the run of continuation bits below it, the 12 bytes that
+    // end at it as three registers (four aligned word loads + funnel shifts), the 7-bit groups packed 4 / 4 / 2 at a
+    // time, and the groups of the previous value shifted out.
     __syncthreads();
-    const int32_t lo = r.span_abs0 > r.tile_abs ? static_cast<int32_t>(r.span_abs0 - r.tile_abs) : -16;
+    const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(sm_in);
     uint32_t t = term, idx = idx0;
     while (t) {
-      const int32_t j = __ffs(t) - 1;
+      const uint32_t j = static_cast<uint32_t>(__ffs(t)) - 1u;
       t &= t - 1;
       const uint32_t slot = idx++ - round0;
       if (slot >= kRoundValues) continue;  // belongs to another round
-      const int32_t p = static_cast<int32_t>(threadIdx.x) * 16 + j;
-      uint64_t v = sm_in[16 + p];
-#pragma unroll 1
-      for (int32_t k = 1; k <= 9; ++k) {
-        const int32_t q = p - k;
-        if (q < lo) break;
-        const uint8_t b = sm_in[16 + q];
-        if (b < 0x80) break;
-        v = (v << 7) | (b & 0x7Fu);
+      const uint32_t run = static_cast<uint32_t>(__clz(static_cast<int>(~(c32 << (16u - j)))));  // continuation bytes right below it
+      const uint32_t len = 1u + (run < 9u ? run : 9u);
+      const uint32_t a = 16u + threadIdx.x * 16u + j - 11u;  // first of the 12 bytes that end at the terminator
+      const uint32_t w0 = a >> 2, sh = (a & 3u) * 8u;
+      const uint32_t W0 = sm_w[w0], W1 = sm_w[w0 + 1], W2 = sm_w[w0 + 2], W3 = sm_w[w0 + 3];
+      const uint32_t x0 = __funnelshift_r(W0, W1, sh), x1 = __funnelshift_r(W1, W2, sh), x2 = __funnelshift_r(W2, W3, sh);
+      auto pack4 = [](uint32_t x) {
+        uint32_t g = x & 0x7F7F7F7Fu;
+        g = (g & 0x007F007Fu) | ((g & 0x7F007F00u) >> 1);
+        return (g & 0x00003FFFu) | ((g & 0x3FFF0000u) >> 2);
+      };
+      // the value is the top `len` groups of the 70-bit string (x0's two oldest bytes, x1, x2): pick the window by length
+      // so that nothing is shifted out of 64 bits before it is needed (only a 10-byte value may wrap, as in prost)
+      const uint64_t A = pack4(x2), B = pack4(x1);
+      uint64_t v;
+      if (len <= 4u) {
+        v = A >> (7u * (4u - len));
+      } else if (len <= 8u) {
+        v = ((A << 28) | B) >> (7u * (8u - len));
+      } else {
+        const uint32_t hi2 = x0 >> 16;  // the two oldest bytes
+        const uint64_t c = (hi2 & 0x7Fu) | ((hi2 & 0x7F00u) >> 1);
+        v = len == 9u ? ((A << 35) | (B << 7) | (c >> 7)) : ((A << 42) | (B << 14) | c);
       }
       out[pad_slot(slot)] = convert_out<OUT>(v);
     }
@@ -229,7 +246,7 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
 
 __global__ void __launch_bounds__(kDecThreads, 6) k_varint_gather(DecTables T, uint8_t* pool, const uint64_t* __restrict__ gate) {
   __shared__ __align__(16) uint8_t sm_out[kGatherOutBytes];
-  __shared__ __align__(16) uint8_t sm_in[16 + kDecTileBytes];
+  __shared__ __align__(16) uint8_t sm_in[16 + kDecTileBytes + 16];  // 16 bytes before the tile, the tile, slack for word loads
   __shared__ uint32_t scan_smem[kDecThreads / 32 + 1];
   if (gate && *gate != 0) return;  // the pool of a one-call decode turned out to be too small
   const uint32_t tile = blockIdx.x;
