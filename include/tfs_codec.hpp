@@ -84,6 +84,36 @@ struct PredictResponse {
   std::optional<ModelSpec> model_spec;
 };
 
+// ---- Classify / Regress inputs: `Payload`, `impl From<Payload> for Feature`, `build_input` (reference src/lib.rs:413-431,
+//      497-571) ----
+struct Payload {  // enum Payload { Bytes(Vec<Vec<u8>>), Ints(Vec<i64>), Floats(Vec<f32>) }
+  enum Kind { None = 0, Bytes = 1, Floats = 2, Ints = 3 } kind = None;  // numbered like Feature.kind (feature.proto:79-81)
+  std::vector<std::vector<uint8_t>> bytes;
+  std::vector<float> floats;
+  std::vector<int64_t> ints;
+  static Payload Of(std::vector<std::vector<uint8_t>> v) { Payload p; p.kind = Bytes; p.bytes = std::move(v); return p; }
+  static Payload Of(std::vector<float> v) { Payload p; p.kind = Floats; p.floats = std::move(v); return p; }
+  static Payload Of(std::vector<int64_t> v) { Payload p; p.kind = Ints; p.ints = std::move(v); return p; }
+};
+using Feature = Payload;                                                // Feature { kind: Some(list) } carries exactly a Payload
+using Features = std::vector<std::pair<std::string, Feature>>;          // map<string, Feature>, in the caller's order
+struct Example {
+  Features features;  // Option<Features> is always Some in build_input
+};
+struct Input {
+  std::vector<Example> examples;  // kind: Some(ExampleList { examples })
+};
+// `fn build_input(&self, payload_map: HashMap<S, V>) -> Input`: one Example holding the whole map
+inline Input build_input(Features payload_map) {
+  Input in;
+  in.examples.push_back(Example{std::move(payload_map)});
+  return in;
+}
+struct ClassificationRequest {  // RegressionRequest has the same two fields
+  std::optional<ModelSpec> model_spec;
+  Input input;
+};
+
 // One tfs_ctx_t (one GPU); shared by the codecs made from it, like the client's channels are shared by its clones.
 class GpuContext {
  public:
@@ -173,6 +203,76 @@ struct Described {
     push(TFS_KIND_UINT64_VAL, TFS_T_U64, t.uint64_val.size(), t.uint64_val.data());
     d.n_fields = static_cast<uint32_t>(fields.size()) - d.first_field;
     tensors.push_back(d);
+  }
+  std::vector<uint64_t>* flatten(const std::vector<std::vector<uint8_t>>& v, uint64_t* total_out) {
+    const size_t n = v.size();
+    size_t total = 0;
+    for (const auto& e : v) total += e.size();
+    ragged.emplace_back((8 * (n + 1) + total + 7) / 8);
+    uint64_t* offs = ragged.back().data();
+    uint8_t* bytes = reinterpret_cast<uint8_t*>(offs + n + 1);
+    uint64_t at = 0;
+    for (size_t i = 0; i < n; ++i) {
+      offs[i] = at;
+      if (!v[i].empty()) std::memcpy(bytes + at, v[i].data(), v[i].size());
+      at += v[i].size();
+    }
+    offs[n] = at;
+    *total_out = total;
+    return &ragged.back();
+  }
+  // TFS_MSG_INPUT / TFS_MSG_CLASSIFY_REQUEST: one descriptor per feature, version_number = index of its Example
+  void add_input(int32_t kind, const std::optional<ModelSpec>& ms, const Input& in) {
+    tfs_msg_desc_t m;
+    std::memset(&m, 0, sizeof(m));
+    m.kind = kind;
+    m.first_tensor = static_cast<uint32_t>(tensors.size());
+    for (size_t e = 0; e < in.examples.size(); ++e) {
+      for (const auto& kv : in.examples[e].features) {
+        tfs_tensor_desc_t d;
+        std::memset(&d, 0, sizeof(d));
+        d.name = str(kv.first);
+        d.version_number = static_cast<int32_t>(e);
+        d.first_field = static_cast<uint32_t>(fields.size());
+        const Feature& ft = kv.second;
+        if (ft.kind != Payload::None) {
+          tfs_field_desc_t f;
+          std::memset(&f, 0, sizeof(f));
+          f.kind = static_cast<int32_t>(ft.kind);
+          if (ft.kind == Payload::Bytes) {
+            f.src_type = TFS_T_RAGGED;
+            f.n_elems = ft.bytes.size();
+            f.data = flatten(ft.bytes, &f.aux)->data();
+          } else if (ft.kind == Payload::Floats) {
+            f.src_type = TFS_T_F32;
+            f.n_elems = ft.floats.size();
+            f.data = ft.floats.data();
+          } else {
+            f.src_type = TFS_T_I64;
+            f.n_elems = ft.ints.size();
+            f.data = ft.ints.data();
+          }
+          fields.push_back(f);
+          d.n_fields = 1;
+        }
+        tensors.push_back(d);
+      }
+    }
+    if (ms && kind == TFS_MSG_CLASSIFY_REQUEST) {
+      m.has_model_spec = 1;
+      m.model_name = str(ms->name);
+      m.signature_name = str(ms->signature_name);
+      if (ms->version) {
+        m.version_choice = TFS_VERSION_NUMBER;
+        m.version = *ms->version;
+      } else if (ms->version_label) {
+        m.version_choice = TFS_VERSION_LABEL;
+        m.version_label = str(*ms->version_label);
+      }
+    }
+    m.n_tensors = static_cast<uint32_t>(tensors.size()) - m.first_tensor;
+    m.n_filters = static_cast<uint32_t>(in.examples.size());  // the number of Examples (see TFS_MSG_INPUT)
+    msgs.push_back(m);
   }
   void add_message(int32_t kind, const std::optional<ModelSpec>& ms, const TensorMap& map, const std::vector<std::string>* filter) {
     tfs_msg_desc_t m;
@@ -278,6 +378,17 @@ class GpuEncoder {
   void encode(const PredictResponse& item, std::vector<uint8_t>& dst) const {
     detail::Described d;
     d.add_message(TFS_MSG_PREDICT_RESPONSE, item.model_spec, item.outputs, nullptr);
+    run(d, dst, nullptr);
+  }
+  // Classify / Regress: what `build_input` returns, and the request around it
+  void encode(const Input& item, std::vector<uint8_t>& dst) const {
+    detail::Described d;
+    d.add_input(TFS_MSG_INPUT, std::nullopt, item);
+    run(d, dst, nullptr);
+  }
+  void encode(const ClassificationRequest& item, std::vector<uint8_t>& dst) const {
+    detail::Described d;
+    d.add_input(TFS_MSG_CLASSIFY_REQUEST, item.model_spec, item.input);
     run(d, dst, nullptr);
   }
   // the batched form the shim uses for the requests of one window: message i occupies

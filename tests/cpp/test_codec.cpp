@@ -128,6 +128,31 @@ int main() {
   CHECK(std::vector<uint8_t>(w3.begin() + spans[1].first, w3.begin() + spans[1].first + spans[1].second) == w2);
   CHECK(std::vector<uint8_t>(w3.begin() + spans[2].first, w3.begin() + spans[2].first + spans[2].second) == wire);
 
+  // Classify / Regress input: build_input(HashMap<name, Payload>) -> Input, known-answer bytes (hand-checked, tests/test_oracle.py)
+  {
+    Features fm;
+    fm.emplace_back("age", Payload::Of(std::vector<int64_t>{29}));
+    fm.emplace_back("w", Payload::Of(std::vector<float>{1.5f, 2.5f}));
+    fm.emplace_back("name", Payload::Of(std::vector<std::vector<uint8_t>>{{'b', 'o', 'b'}, {}}));
+    Input in = build_input(fm);
+    in.examples.push_back(Example{});
+    Features third;
+    third.emplace_back("", Feature{});
+    third.emplace_back("e", Payload::Of(std::vector<float>{}));
+    in.examples.push_back(Example{third});
+    std::vector<uint8_t> wi;
+    enc.encode(in, wi);
+    const std::string want =
+        "0a4b0a360a340a0c0a0361676512051a030a011d0a110a0177120c120a0a080000c03f000020400a110a046e616d6512090a070a03626f620a000a020a000a0d0a0b0a000a070a016512021200";
+    CHECK(hex(wi) == want);
+    ClassificationRequest cr;
+    cr.model_spec = ModelSpec{"m", std::nullopt, std::nullopt, "s"};
+    cr.input = in;
+    std::vector<uint8_t> wc;
+    enc.encode(cr, wc);
+    CHECK(hex(wc) == "0a060a016d1a0173124d" + want);
+  }
+
   // malformed input surfaces as a Status carrying prost's DecodeError class
   std::vector<uint8_t> bad = {0x0a, 0x10, 0x0a, 0x01, 0x6b};
   try {

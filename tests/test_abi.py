@@ -102,3 +102,24 @@ def test_product_package_does_not_touch_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp", ".hpp", ".rs")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "oracle" not in text.lower() or f == "workloads.py" and "oracle" not in text, os.path.join(dirpath, f)
+
+
+def test_constants_match_header():
+    """Every enum constant of include/tfs_gpu.h that the Python harness mirrors has the header's value."""
+    import re
+    text = open(os.path.join(ROOT, "include", "tfs_gpu.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    found = {}
+    for name, val in re.findall(r"\b(TFS_[A-Z0-9_]+)\s*=\s*(1u\s*<<\s*\d+|\d+)", text):
+        found[name] = eval(val.replace("u", ""))
+    for m in re.findall(r"#define\s+(TFS_[A-Z0-9_]+)\s+(\d+)\b", text):
+        found[m[0]] = int(m[1])
+    assert len(found) > 60
+    checked = 0
+    for name, val in found.items():
+        for cand in (name, name[4:]):  # TFS_ERR_* keep their prefix in abi.py, the others drop "TFS_"
+            if hasattr(abi, cand):
+                assert getattr(abi, cand) == val, (name, getattr(abi, cand), val)
+                checked += 1
+                break
+    assert checked > 50, checked
