@@ -100,6 +100,27 @@ class ClockSampler:
 # =====================================================================================================
 # our arm
 # =====================================================================================================
+def pin_to_gpu_numa_node(index):
+    """Bind this process to the CPUs NVML names as local to GPU `index` (one process per GPU: its pinned staging buffers
+    are then first-touched on that socket).  Returns a short description for the bench line; failing is harmless."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w in range(words) for b in range(64) if (mask[w] >> b) & 1}
+        everything = os.sched_getaffinity(0)
+        cpus &= everything
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            pin_to_gpu_numa_node.restore = lambda: os.sched_setaffinity(0, everything)
+            return f"{len(cpus)} of {len(everything)} cpus (local to gpu {index}) during the GPU measurements"
+    except Exception as e:  # noqa: BLE001
+        return f"not bound ({type(e).__name__})"
+    return "not bound"
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -114,6 +135,7 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the codec has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
+    numa = pin_to_gpu_numa_node(local)  # before any pinned allocation: the staging buffers should be local to the GPU's socket
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -276,7 +298,7 @@ def run_ours(args):
                    "flags": "TFS_F_ALIGN_PAYLOAD", "sharding": f"dp{world}: independent requests per GPU, no collective"},
         "clocks": clocks,
         "e2e": {"value": round(world * e2e_bytes / e2e_s / 1e9, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "path": "tfs_encode_host + tfs_decode_host_into on pinned host buffers: copy engine brings the source to HBM in 8 MB chunks, the copy kernel follows chunk by chunk and stores straight into the pinned destination"},
+                "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "host_affinity": numa, "path": "tfs_encode_host + tfs_decode_host_into on pinned host buffers: copy engine brings the source to HBM in 8 MB chunks, the copy kernel follows chunk by chunk and stores straight into the pinned destination"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "k_copy_tma (K5 bulk copy through the TMA ring; one launch per encode and per decode)",
                      "other_copy_kernel_avg_ms": round(ms_gen / max(1, n_gen), 4),
@@ -288,8 +310,9 @@ def run_ours(args):
                      "step_breakdown_ms": {"k_copy_tma": round(ms_copy / args.steps, 4), "k_plan_small": round(ms_walk / args.steps, 4),
                                            "k_frame_small": round(ms_frame / args.steps, 4),
                                            "rest (host syncs, table copies, k_dec_bind)": round((ms - ms_copy - ms_walk - ms_frame) / args.steps, 4)}},
-        "cpu_baseline": cpu_baseline(R, budget_s=args.cpu_budget),
     }
+    getattr(pin_to_gpu_numa_node, "restore", lambda: None)()  # the CPU baseline gets every host core again
+    line["cpu_baseline"] = cpu_baseline(R, budget_s=args.cpu_budget)
     if world == 1 and not args.no_extras:
         del src, wire, pool
         torch.cuda.empty_cache()
