@@ -352,7 +352,9 @@ tfs_status_t tfs_decode_scan(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire
                              const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags,
                              tfs_decoded_t** out);
 tfs_status_t tfs_decoded_view(const tfs_decoded_t* dec, tfs_decoded_view_t* view);
-/* Pass 2: write every payload value into the device pool (pool_bytes >= view.pool_bytes).  Asynchronous: the
+/* Pass 2: write every payload value into the device pool (pool_bytes >= view.pool_bytes; 16-byte aligned, since it
+ * holds typed arrays - every (tensor, field) region starts on a 64-byte multiple from the pool's base; an unaligned
+ * device or pinned pool is TFS_ERR_INVALID_ARG, a pageable host pool may sit anywhere).  Asynchronous: the
  * kernels are queued on the context's stream; tfs_sync() (or stream order) before anything else reads the pool. */
 tfs_status_t tfs_decode(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_dev, uint64_t pool_bytes);
 tfs_status_t tfs_decoded_free(tfs_ctx_t* ctx, tfs_decoded_t* dec);

@@ -962,6 +962,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
                                 uint64_t pool_capacity, tfs_decoded** out, const void* walk_wire_dev) {
   TFS_CUDA(ctx, cudaSetDevice(ctx->device));
   if (msg_kind < TFS_MSG_TENSOR_PROTO || msg_kind > TFS_MSG_PREDICT_RESPONSE) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad msg_kind");
+  if (reinterpret_cast<uintptr_t>(pool_dev) & 15u) return set_err(ctx, TFS_ERR_INVALID_ARG, "the value pool must be 16-byte aligned (it holds typed arrays)");
   tfs_decoded* dec = new (std::nothrow) tfs_decoded();
   if (!dec) return TFS_ERR_NOMEM;
   dec->owner = ctx;
@@ -1235,6 +1236,7 @@ tfs_status_t decode_device(tfs_ctx* ctx, tfs_decoded* dec, void* pool_dev, uint6
   TFS_CUDA(ctx, cudaSetDevice(ctx->device));
   if (dec->owner != ctx || dec->generation != ctx->dec_generation)
     return set_err(ctx, TFS_ERR_INVALID_ARG, "stale decode handle: another tfs_decode_scan ran on this ctx since");
+  if (reinterpret_cast<uintptr_t>(pool_dev) & 15u) return set_err(ctx, TFS_ERR_INVALID_ARG, "the value pool must be 16-byte aligned (it holds typed arrays)");
   if (pool_bytes < dec->totals[TOT_POOL] || (!pool_dev && dec->totals[TOT_POOL]))
     return set_err(ctx, TFS_ERR_NOMEM, "value pool is smaller than tfs_decoded_view().pool_bytes");
   return launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), nullptr);

@@ -1,0 +1,101 @@
+"""Out-of-bounds WRITE check of our own (compute-sanitizer is not available on the GPU pool): every output buffer sits
+inside a larger allocation filled with a canary byte; after encode / decode the canaries on both sides must be intact
+and the bytes between them must equal the oracle's."""
+import numpy as np
+import pytest
+
+import tfs_b200 as tfs
+from tfs_b200 import abi, workloads
+
+import helpers
+import oracle_bind as ob
+
+pytestmark = pytest.mark.gpu
+CANARY = 0xA5
+GUARD = 4096
+
+
+@pytest.fixture(scope="module")
+def codec():
+    c = tfs.GpuCodec(tfs.GpuContext(0))
+    yield c
+    c.ctx.close()
+
+
+def _cases():
+    rng = np.random.default_rng(2024)
+    strs = [rng.integers(0, 256, int(n), dtype=np.uint8).tobytes() for n in [0, 1, 15, 16, 17, 4095, 70001, 3, 0, 65536 - 3, 9]]
+    tensors = [
+        tfs.TensorProto(dtype=9, int64_val=rng.integers(-3, 1 << 45, 6145, dtype=np.int64)),
+        tfs.TensorProto(dtype=3, int_val=rng.integers(-100, 100, 2049, dtype=np.int32), float_val=rng.standard_normal(8191).astype(np.float32)),
+        tfs.TensorProto(dtype=7, string_val=strs, tensor_content=rng.integers(0, 256, 33333, dtype=np.uint8)),
+        tfs.TensorProto(dtype=19, half_val=rng.integers(0, 65536, 4097).astype(np.int32), bool_val=rng.integers(0, 2, 1001).astype(np.bool_)),
+        tfs.TensorProto(dtype=2, double_val=rng.standard_normal(5000)),
+    ]
+    reqs = [tfs.PredictRequest(tfs.ModelSpec("m", version=3, signature_name="s"), [("a", tensors[0]), ("b", tensors[2])], ["y"]),
+            tfs.PredictRequest(None, [("", tensors[1]), ("k", tensors[3]), ("d", tensors[4])])]
+    inputs = [tfs.Input([[("ids", tfs.Feature(int64_list=rng.integers(0, 9999, 3000, dtype=np.int64))),
+                          ("img", tfs.Feature(bytes_list=strs)), ("w", tfs.Feature(float_list=rng.standard_normal(777).astype(np.float32)))], []])]
+    return [("tensor", abi.MSG_TENSOR_PROTO, tensors), ("request", abi.MSG_PREDICT_REQUEST, reqs), ("input", abi.MSG_INPUT, inputs)]
+
+
+@pytest.mark.parametrize("flags", [0, abi.F_GRPC_PREFIX, abi.F_ALIGN_PAYLOAD])
+@pytest.mark.parametrize("skew", [0, 1, 7])
+def test_encode_writes_only_its_own_bytes(codec, flags, skew):
+    import torch
+    enc = codec.encoder()
+    for name, kind, msgs in _cases():
+        want = ob.encode_messages(msgs, kind, flags & abi.F_GRPC_PREFIX)
+        dev_msgs = workloads.to_device(msgs, kind, torch.device("cuda:0"))
+        built = tfs.build_batch(dev_msgs, kind)
+        # learn the exact total at the same address skew (TFS_F_ALIGN_PAYLOAD pads according to dst mod 16)
+        probe_buf = torch.empty(GUARD + skew + enc.bound(built, flags), dtype=torch.uint8, device="cuda:0")
+        total = enc.encode(built, kind, flags, dst=probe_buf[GUARD + skew:]).total
+        buf = torch.full((GUARD + skew + total + GUARD,), CANARY, dtype=torch.uint8, device="cuda:0")
+        dst = buf[GUARD + skew: GUARD + skew + total]     # capacity == exactly what is needed
+        eb = enc.encode(built, kind, flags, dst=dst)
+        codec.ctx.sync()
+        host = buf.cpu().numpy()
+        assert (host[: GUARD + skew] == CANARY).all(), f"{name}: bytes written BEFORE dst (flags {flags}, skew {skew})"
+        assert (host[GUARD + skew + total:] == CANARY).all(), f"{name}: bytes written AFTER dst (flags {flags}, skew {skew})"
+        got = [bytes(host[GUARD + skew + o: GUARD + skew + o + n + (5 if flags & abi.F_GRPC_PREFIX else 0)]) for o, n in zip(eb.offsets, eb.lengths)]
+        assert [len(g) for g in got] == [len(w) for w in want], name
+        assert got == want, f"{name}: encoded bytes differ (flags {flags}, skew {skew})"
+
+
+def test_decode_rejects_an_unaligned_device_pool(codec):
+    import torch
+    wire = torch.from_numpy(np.frombuffer(bytes.fromhex("3a03010203"), dtype=np.uint8).copy()).cuda()
+    buf = torch.empty(4096, dtype=torch.uint8, device="cuda:0")
+    with pytest.raises(tfs.TfsError) as e:
+        codec.decoder().decode_into(wire, [0], [5], abi.MSG_TENSOR_PROTO, buf[3:])
+    assert e.value.status == abi.TFS_ERR_INVALID_ARG
+
+
+@pytest.mark.parametrize("skew", [0, 16, 48])
+def test_decode_writes_only_its_own_pool(codec, skew):
+    import torch
+    dec = codec.decoder()
+    for name, kind, msgs in _cases():
+        if kind == abi.MSG_INPUT:
+            continue  # encode only
+        blobs = ob.encode_messages(msgs, kind)
+        offs, lens, cur = [], [], 0
+        for b in blobs:
+            offs.append(cur)
+            lens.append(len(b))
+            cur += len(b)
+        wire = torch.from_numpy(np.frombuffer(b"".join(blobs), dtype=np.uint8).copy()).cuda()
+        d0 = dec.scan(wire, offs, lens, kind)
+        need = d0.pool_bytes
+        d0.close()
+        buf = torch.full((GUARD + skew + need + GUARD,), CANARY, dtype=torch.uint8, device="cuda:0")
+        pool = buf[GUARD + skew: GUARD + skew + need]
+        d = dec.decode_into(wire, offs, lens, kind, pool)
+        codec.ctx.sync()
+        host = buf.cpu().numpy()
+        assert (host[: GUARD + skew] == CANARY).all(), f"{name}: bytes written BEFORE the pool (skew {skew})"
+        assert (host[GUARD + skew + need:] == CANARY).all(), f"{name}: bytes written AFTER the pool (skew {skew})"
+        st, want = ob.decode_bytes(blobs, kind)
+        helpers.assert_same_decoded(want, d.messages(), "tensor" if kind == abi.MSG_TENSOR_PROTO else "request", f"guarded decode {name}")
+        d.close()
