@@ -171,7 +171,9 @@ typedef struct {
   float op_param;
   uint32_t _pad;
   uint64_t n_elems; /* number of source elements (bytes for raw tensor_content with src_type U8) */
-  const void* data; /* device pointer for tfs_encode, host pointer for tfs_encode_host */
+  const void* data; /* device pointer for tfs_encode, host pointer for tfs_encode_host.  Device arrays that are
+                       varint-coded (int_val, int64_val, half_val, uint32/64_val, Int64List) must be aligned to their
+                       element size, ragged blocks to 8 bytes; byte-copied fields and host arrays may sit anywhere */
   uint64_t aux;     /* TFS_KIND_STRING_VAL (src_type TFS_T_RAGGED): total bytes of all elements, i.e. offsets[n_elems]
                        (the host needs it for tfs_encode_bound and cannot read device memory); 0 otherwise */
 } tfs_field_desc_t;

@@ -423,6 +423,8 @@ bool compile_field(const tfs_field_desc_t& f, EncField* o, uint64_t* max_body) {
     return true;
   };
   auto varint_class = [&](int32_t mode, uint32_t max_len) {
+    // the varint kernels load whole elements: the array has to be aligned to its element size
+    if (reinterpret_cast<uintptr_t>(f.data) & (tfs_type_size(st) - 1u)) return false;
     o->is_varint = 1;
     o->mode = mode;
     *max_body = f.n_elems * max_len;

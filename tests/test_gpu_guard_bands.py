@@ -99,3 +99,24 @@ def test_decode_writes_only_its_own_pool(codec, skew):
         st, want = ob.decode_bytes(blobs, kind)
         helpers.assert_same_decoded(want, d.messages(), "tensor" if kind == abi.MSG_TENSOR_PROTO else "request", f"guarded decode {name}")
         d.close()
+
+
+def test_encode_rejects_a_misaligned_varint_source(codec):
+    """int64 / int32 arrays are loaded element-wise by the varint kernels: an address that is not a multiple of the
+    element size is refused (INVALID_ARG), not dereferenced."""
+    import torch
+    x = torch.arange(64, dtype=torch.int64, device="cuda:0")
+    built = tfs.build_batch([tfs.TensorProto(dtype=9, int64_val=x)], abi.MSG_TENSOR_PROTO)
+    built.fields[0].data += 4
+    built.fields[0].n_elems = 60
+    with pytest.raises(tfs.TfsError) as e:
+        codec.encoder().encode(built, abi.MSG_TENSOR_PROTO)
+    assert e.value.status == abi.TFS_ERR_INVALID_ARG
+    # byte-copied fields may sit anywhere
+    f = torch.arange(64, dtype=torch.float32, device="cuda:0")
+    built = tfs.build_batch([tfs.TensorProto(dtype=1, float_val=f)], abi.MSG_TENSOR_PROTO)
+    built.fields[0].data += 1
+    built.fields[0].n_elems = 60
+    got = codec.encoder().encode(built, abi.MSG_TENSOR_PROTO).all_bytes()[0]
+    raw = f.cpu().numpy().tobytes()[1: 1 + 240]
+    assert got == bytes.fromhex("08012af001") + raw
