@@ -480,7 +480,7 @@ def other_configs(codec, dev, peak):
     out["ClassificationRequest, 64 requests x 64 Examples x (int64[128] + f32[128] + 1 tag), encode"] = {
         "messages": 64, "features": 64 * 64 * 3, "wire_MB": round(W / 1e6, 2), "encode_ms": round(te, 4),
         "encode_wire_GBps": round(W / (te * 1e-3) / 1e9, 1), "encode_algorithmic_GBps": round((nb + W) / (te * 1e-3) / 1e9, 1),
-        "note": "framing is one thread per message: 12 288 features are walked by 64 threads"}
+        "note": "12 288 features: framed by one GPU thread each (k_feature_layout / k_feature_write); most of the call is the host walking 12 288 descriptors and their name strings"}
     del reqs, built, wire
     msgs, nb = string_requests(64, 512, 0, 40)
     out["DT_STRING string_val, 64 requests x 512 tokens of 0-40 bytes (decode walks each message serially: ~3.6 us per element)"] = measure(msgs, abi.MSG_PREDICT_REQUEST, nb, reps=3)

@@ -99,6 +99,7 @@ struct CountSink {
   __device__ __forceinline__ void put(uint8_t) { pos += 1; }
   __device__ __forceinline__ void put_bytes(const uint8_t*, uint32_t n) { pos += n; }
   __device__ __forceinline__ void skip(uint64_t n) { pos += n; }
+  __device__ __forceinline__ void note(uint64_t*) {}  // only the writing pass records positions
 };
 struct ByteSink {
   uint8_t* base;
@@ -109,6 +110,7 @@ struct ByteSink {
     pos += n;
   }
   __device__ __forceinline__ void skip(uint64_t n) { pos += n; }
+  __device__ __forceinline__ void note(uint64_t* slot) { *slot = pos; }
 };
 template <class Sink>
 __device__ __forceinline__ void put_varint(Sink& s, uint64_t v) {

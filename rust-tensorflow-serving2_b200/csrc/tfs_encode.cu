@@ -178,9 +178,8 @@ __device__ __forceinline__ uint64_t feature_body_len(const EncTables& T, const E
 // length of the Features map of the Example that starts at feature `ti`; *next = first feature of the next Example
 __device__ __forceinline__ uint64_t features_len_from(const EncTables& T, uint32_t ti, uint32_t te, int32_t example, uint32_t* next) {
   uint64_t n = 0;
-  while (ti < te && T.tensors[ti].version_number == example) {
-    const uint64_t el = T.entry_len[ti];
-    n += 1u + varint_len(el) + el;
+  while (ti < te && T.feat_ex[ti] == example) {  // compact arrays: one cache line serves 16 features of this serial loop
+    n += T.feat_rec[ti];
     ++ti;
   }
   *next = ti;
@@ -217,27 +216,52 @@ __device__ void emit_input(Sink& s, const EncTables& T, uint32_t mi, OnBody on_b
     put_varint(s, 1u + varint_len(fl) + fl);
     put_key(s, 1, 2);  // features = 1
     put_varint(s, fl);
-    for (; ti < next; ++ti) {
-      const EncTensor& t = T.tensors[ti];
-      put_key(s, 1, 2);  // map entry of `feature`
-      put_varint(s, T.entry_len[ti]);
-      if (t.name.len) emit_string(s, 1, T.strings, t.name);
-      if (t.n_fields == 0) continue;  // Feature::default(): the value is left out of the entry
-      put_key(s, 2, 2);
-      put_varint(s, T.tensor_len[ti]);
-      const uint32_t fi = t.first_field;
-      const EncField& f = T.fields[fi];
-      put_key(s, static_cast<uint32_t>(f.kind), 2);  // bytes_list = 1 / float_list = 2 / int64_list = 3
-      put_varint(s, feature_list_len(T, t));
-      if (f.n_elems == 0) continue;
-      if (f.is_varint != FC_RAGGED) {  // packed `value = 1`
-        put_key(s, 1, 2);
-        put_varint(s, f.body_len);
-      }
-      on_body(fi, s.pos);
-      s.skip(f.body_len);
+    for (; ti < next; ++ti) {  // the entries themselves are written by k_feature_write, one thread per feature
+      s.note(&T.entry_off[ti]);
+      s.skip(T.feat_rec[ti]);
     }
   }
+  (void)on_body;
+}
+
+// K6f: nested lengths of every feature of an Input (one thread per feature; messages of other kinds are skipped)
+__global__ void __launch_bounds__(256) k_feature_layout(EncTables T) {
+  const uint32_t ti = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ti >= T.n_tensors) return;
+  const EncTensor& t = T.tensors[ti];
+  if (!is_input_kind(T.msgs[t._pad].kind)) return;  // _pad = index of the message the descriptor belongs to
+  const uint64_t fl = feature_body_len(T, t);
+  T.tensor_len[ti] = fl;
+  const uint64_t el = (t.name.len ? str_field_len(t.name.len) : 0) + (t.n_fields ? 1u + varint_len(fl) + fl : 0);
+  T.entry_len[ti] = el;
+  T.feat_rec[ti] = 1u + varint_len(el) + el;
+  T.feat_ex[ti] = t.version_number;
+}
+
+// K6g: the map entry of every feature (key, Feature, list header) at the place the per-message pass reserved for it;
+// records where the list body goes for K3 / K5 / K8
+__global__ void __launch_bounds__(256) k_feature_write(EncTables T, uint8_t* __restrict__ dst) {
+  const uint32_t ti = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ti >= T.n_tensors || T.result[1] != 0) return;
+  const EncTensor& t = T.tensors[ti];
+  if (!is_input_kind(T.msgs[t._pad].kind)) return;
+  ByteSink s{dst, T.entry_off[ti]};
+  put_key(s, 1, 2);  // map entry of `feature`
+  put_varint(s, T.entry_len[ti]);
+  if (t.name.len) emit_string(s, 1, T.strings, t.name);
+  if (t.n_fields == 0) return;  // Feature::default(): the value is left out of the entry
+  put_key(s, 2, 2);
+  put_varint(s, T.tensor_len[ti]);
+  EncField& f = T.fields[t.first_field];
+  put_key(s, static_cast<uint32_t>(f.kind), 2);  // bytes_list = 1 / float_list = 2 / int64_list = 3
+  put_varint(s, feature_list_len(T, t));
+  if (f.n_elems == 0) return;
+  if (f.is_varint != FC_RAGGED) {  // packed `value = 1`
+    put_key(s, 1, 2);
+    put_varint(s, f.body_len);
+  }
+  f.dst_off = s.pos;
+  if (!f.is_varint) T.segs[f.first_tile].dst = dst + s.pos;
 }
 
 template <class Sink, class OnBody>
@@ -277,12 +301,7 @@ __device__ void msg_layout_body(const EncTables& T, uint32_t mi) {
   for (uint32_t i = 0; i < m.n_tensors; ++i) {
     const uint32_t ti = m.first_tensor + i;
     const EncTensor& t = T.tensors[ti];
-    if (is_input_kind(m.kind)) {  // a feature: tensor_len = Feature body, entry_len = map entry body
-      const uint64_t fl = feature_body_len(T, t);
-      T.tensor_len[ti] = fl;
-      T.entry_len[ti] = (t.name.len ? str_field_len(t.name.len) : 0) + (t.n_fields ? 1u + varint_len(fl) + fl : 0);
-      continue;
-    }
+    if (is_input_kind(m.kind)) break;  // features were laid out by k_feature_layout
     const uint64_t tl = tensor_body_len(T, t);
     T.tensor_len[ti] = tl;
     uint64_t el = 0;
@@ -395,6 +414,7 @@ struct Compiled {
   // true when the host can already tell that every bulk segment will be congruent mod 16 with its destination
   // (TFS_F_ALIGN_PAYLOAD, one bulk field per message, 16-byte aligned plain-byte sources): TMA ring only
   bool all_tma = true;
+  bool has_input = false;  // some message is an Input / ClassificationRequest: features are framed by their own kernels
 };
 
 StrRef add_str(Compiled& c, const tfs_str_t& s) {
@@ -557,6 +577,8 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
         last_example = t.version_number;
       }
       ot.name = m.kind == TFS_MSG_TENSOR_PROTO ? StrRef{0, 0} : add_str(*c, t.name);
+      ot._pad = mi;  // the message this descriptor belongs to
+      c->has_input |= input_kind;
       ot.dtype = t.dtype;
       ot.version_number = t.version_number;
       ot.has_shape = t.has_shape ? 1 : 0;
@@ -635,7 +657,8 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
   // can the generic copy kernel be skipped?  Only the largest bulk body of a message is placed on a 16-byte
   // boundary by TFS_F_ALIGN_PAYLOAD, so every message may carry at most one bulk field, a plain byte copy
   // from a 16-byte aligned source, large enough for the TMA ring.
-  c->all_tma = (flags & TFS_F_ALIGN_PAYLOAD) != 0;
+  // (TFS_F_ALIGN_PAYLOAD places tensor payloads; the lists of an Input are not aligned by it)
+  c->all_tma = (flags & TFS_F_ALIGN_PAYLOAD) != 0 && !c->has_input;
   for (uint32_t mi = 0; mi < b->n_msgs && c->all_tma; ++mi) {
     uint32_t bulk = 0;
     const EncMsg& m = c->msgs[mi];
@@ -656,6 +679,7 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
 struct Uploaded {
   EncTables T;
   uint64_t n_copy_tiles;
+  bool has_input;
 };
 
 template <class V>
@@ -702,7 +726,7 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   };
   const size_t w_vt = carve(sizeof(VTile) * static_cast<size_t>(n_vtiles)), w_tf = carve(4ull * n_vtiles);
   const size_t w_tb = carve(4ull * n_vtiles), w_to = carve(8ull * n_vtiles), w_tl = carve(8ull * n_tensors),
-               w_el = carve(8ull * n_tensors), w_sl = carve(8ull * n_msgs), w_ml = carve(8ull * n_msgs),
+               w_el = carve(8ull * n_tensors), w_eo = carve(8ull * n_tensors), w_fr = carve(8ull * n_tensors), w_fx = carve(4ull * n_tensors), w_sl = carve(8ull * n_msgs), w_ml = carve(8ull * n_msgs),
                w_mp = carve(8ull * n_msgs), w_mo = carve(8ull * n_msgs), w_res = carve(32), w_rb = carve(8ull * n_rtiles),
                w_ro = carve(8ull * n_rtiles);
   TFS_TRY(dev_reserve(ctx, &ctx->d_work, w + 16));
@@ -723,6 +747,9 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   T.tile_off = reinterpret_cast<uint64_t*>(k + w_to);
   T.tensor_len = reinterpret_cast<uint64_t*>(k + w_tl);
   T.entry_len = reinterpret_cast<uint64_t*>(k + w_el);
+  T.entry_off = reinterpret_cast<uint64_t*>(k + w_eo);
+  T.feat_rec = reinterpret_cast<uint64_t*>(k + w_fr);
+  T.feat_ex = reinterpret_cast<int32_t*>(k + w_fx);
   T.spec_len = reinterpret_cast<uint64_t*>(k + w_sl);
   T.msg_len = reinterpret_cast<uint64_t*>(k + w_ml);
   T.msg_pay_off = reinterpret_cast<uint64_t*>(k + w_mp);
@@ -745,6 +772,7 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   T.n_vtiles = n_vtiles;
   T.n_segs = static_cast<uint32_t>(c.segs.size());
   u->n_copy_tiles = c.n_copy_tiles;
+  u->has_input = c.has_input;
   return TFS_OK;
 }
 
@@ -770,6 +798,10 @@ tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_
     k_ragged_scan<<<(T.n_rfields + 7) / 8, 256, 0, ctx->stream>>>(T);
     ctx->launches++;
   }
+  if (u.has_input && T.n_tensors) {  // Input / ClassificationRequest: lengths of every feature, one thread each
+    k_feature_layout<<<(T.n_tensors + 255) / 256, 256, 0, ctx->stream>>>(T);
+    ctx->launches++;
+  }
   if (T.n_msgs <= kSmallBatch) {
     {
       ProfScope prof(ctx, PK_FRAME);
@@ -785,6 +817,10 @@ tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_
       k_write_headers<<<(T.n_msgs + 127) / 128, 128, 0, ctx->stream>>>(T, dst, flags);
       ctx->launches++;
     }
+  }
+  if (u.has_input && T.n_tensors && dst) {  // the map entries themselves, at the places the per-message pass reserved
+    k_feature_write<<<(T.n_tensors + 255) / 256, 256, 0, ctx->stream>>>(T, dst);
+    ctx->launches++;
   }
   TFS_CUDA(ctx, cudaGetLastError());
   return TFS_OK;

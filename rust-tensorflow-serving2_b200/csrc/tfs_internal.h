@@ -135,6 +135,9 @@ struct EncTables {
   uint64_t* tile_off;           // [n_vtiles] byte offset of the tile inside its field body
   uint64_t* tensor_len;         // [n_tensors]
   uint64_t* entry_len;          // [n_tensors]
+  uint64_t* feat_rec;           // [n_tensors] Input kinds: bytes of the feature's map entry record (key + length + entry)
+  int32_t* feat_ex;             // [n_tensors] Input kinds: index of the Example (compact copy for the per-message pass)
+  uint64_t* entry_off;          // [n_tensors] Input kinds: where the feature's map entry starts in dst (per-message pass)
   uint64_t* spec_len;           // [n_msgs]
   uint64_t* msg_len;            // [n_msgs]
   uint64_t* msg_pay_off;        // [n_msgs] offset (inside the message) of its largest bulk payload
