@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
 }  // namespace
 
 tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
-                         bool need_generic, const std::vector<HostSeg>* host_segs) {
+                         bool need_generic, const std::vector<HostSeg>* host_segs, bool need_tma) {
   if (n_segs == 0 || n_tiles == 0) return TFS_OK;
   if (n_tiles > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (copy tiles)");
   const uint32_t ring_bytes = kTmaStages * kTmaChunk;
@@ -305,7 +305,7 @@ tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs,
       k_copy<<<static_cast<uint32_t>(te - tb), kCopyThreads, 0, ctx->stream>>>(segs_dev, n_segs, te, gate, src_lo, src_hi, tb);
       ctx->launches++;
     }
-    {  // the TMA ring: one CTA (96 KiB of shared memory, one driving thread) per SM
+    if (need_tma) {  // the TMA ring: one CTA (96 KiB of shared memory, one driving thread) per SM
       const uint64_t cap = static_cast<uint64_t>(ctx->sm_count);
       ProfScope prof(ctx, PK_COPY_TMA);
       k_copy_tma<<<static_cast<uint32_t>(te - tb < cap ? te - tb : cap), 32, ring_bytes, ctx->stream>>>(segs_dev, n_segs, te, gate, src_lo, src_hi, tb);

@@ -37,7 +37,7 @@ namespace {
 
 enum { WT_VARINT = 0, WT_64 = 1, WT_LEN = 2, WT_SGROUP = 3, WT_EGROUP = 4, WT_32 = 5 };
 // TOT_GENERIC counts the copy-class spans the TMA ring cannot take (not congruent mod 16, tiny, or widened)
-enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_RETRY, TOT_CLK0 = 16, TOT_COUNT_ = 24 };  // TOT_CLK0..: phase clocks of k_plan_small (TFS_PLAN_TIMING=1 prints them)
+enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_RETRY, TOT_BULK, TOT_CLK0 = 16, TOT_COUNT_ = 24 };  // TOT_CLK0..: phase clocks of k_plan_small (TFS_PLAN_TIMING=1 prints them)
 constexpr size_t kTotalsBytes = sizeof(uint64_t) * TOT_COUNT_;
 
 __device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
@@ -98,7 +98,7 @@ struct Walker {
   uint64_t err_pos = 0;
   bool soft_unsupported = false;
   // counters (COUNT) / cursors (FILL)
-  uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0, n_generic = 0;
+  uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0, n_generic = 0, n_bulk = 0;
   uint32_t seen_slots = 0;  // payload slots of the current tensor that already have a chunk
   // current tensor
   uint32_t cur = 0;
@@ -248,6 +248,7 @@ struct Walker {
   __device__ void add_span(uint32_t slot, uint32_t cls, uint64_t off, uint64_t len, uint64_t n_elems, uint32_t out_mult) {
     const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(wv, off, len) : 0u;
     if (cls == SC_STR && len) n_generic++;  // string bytes land wherever the earlier elements end: generic kernel
+    if (cls != SC_VARINT && len >= 4096) n_bulk++;  // large enough for the TMA ring (if it turns out congruent mod 16)
     if (cls == SC_COPY && len) {
       // Can the TMA ring take this span?  Its pool region starts on a 64-byte boundary, so the first chunk of
       // a slot is congruent mod 16 with its source iff the source address is 16-byte aligned.  A conservative
@@ -601,6 +602,7 @@ __device__ void walk_body(const DecTables& T, uint32_t mi) {
     T.cnt_vtiles[mi] = ok ? wk.n_vt : 0u;
     T.cnt_ctiles[mi] = ok ? wk.n_ct : 0u;
     if (ok && wk.n_generic) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_GENERIC]), static_cast<unsigned long long>(wk.n_generic));
+    if (ok && wk.n_bulk) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_BULK]), static_cast<unsigned long long>(wk.n_bulk));
   } else {
     const int32_t st = T.msgs[mi].status;
     const uint64_t eo = T.msgs[mi].err_offset;
@@ -949,7 +951,7 @@ tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const 
   TFS_CUDA(ctx, cudaGetLastError());
   // the generic copy kernel is only needed for spans the TMA ring cannot take (counted by the walk)
   const bool need_generic = dec->totals[TOT_GENERIC] != 0 || (reinterpret_cast<uintptr_t>(pool) & 15u) != 0;
-  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, gate, need_generic, host_segs));
+  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, gate, need_generic, host_segs, dec->totals[TOT_BULK] != 0));
   return TFS_OK;
 }
 

@@ -414,6 +414,7 @@ struct Compiled {
   // true when the host can already tell that every bulk segment will be congruent mod 16 with its destination
   // (TFS_F_ALIGN_PAYLOAD, one bulk field per message, 16-byte aligned plain-byte sources): TMA ring only
   bool all_tma = true;
+  bool any_bulk = false;   // some copy segment is >= 4 KiB of plain bytes (a candidate for the TMA ring)
   bool has_input = false;  // some message is an Input / ClassificationRequest: features are framed by their own kernels
 };
 
@@ -648,6 +649,7 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
       f.n_tiles = 0;
       // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
       c->n_copy_tiles += (f.body_len + kCopyTileBytes - 1) / kCopyTileBytes + 1;
+      c->any_bulk |= f.mode == CP_BYTES && f.body_len >= 4096;
       c->segs.push_back(s);
     }
   }
@@ -889,7 +891,7 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
           hs.push_back({reinterpret_cast<uintptr_t>(g.src), g.n * in, g.first_tile, next - g.first_tile, stb, stb});
         }
       }
-      TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, T.result + 1, !c.all_tma, hs.empty() ? nullptr : &hs));
+      TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, T.result + 1, !c.all_tma, hs.empty() ? nullptr : &hs, c.any_bulk));
     }
   }
   bool overflow = false;

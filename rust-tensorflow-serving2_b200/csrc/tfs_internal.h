@@ -309,10 +309,11 @@ struct HostSeg {
   uint64_t n_tiles;
   uint64_t src_tile_min, src_tile_max;  // bounds of the source bytes one tile consumes (32 KiB for plain bytes, other for casts)
 };
+// `need_tma` = false promises that no segment is large enough for the TMA ring (>= 4 KiB of plain bytes).
 // `host_segs` is needed only while ctx->pipe is set (sources still arriving in chunks): each chunk's launch then walks
 // just the tiles that can end inside the chunk; without it the launch waits for the last chunk.
 tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
-                         bool need_generic, const std::vector<HostSeg>* host_segs = nullptr);
+                         bool need_generic, const std::vector<HostSeg>* host_segs = nullptr, bool need_tma = true);
 
 inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
