@@ -572,7 +572,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--requests", type=int, default=32, help="C2 requests per variant, per GPU and per step")
-    ap.add_argument("--e2e-requests", type=int, default=4)
+    ap.add_argument("--e2e-requests", type=int, default=8)
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU baseline sampling")
     ap.add_argument("--no-extras", action="store_true", help="skip the C3 / C4 / C5 side measurements (N = 1 only)")
     args = ap.parse_args()
