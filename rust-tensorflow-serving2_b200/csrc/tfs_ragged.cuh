@@ -127,14 +127,23 @@ __global__ void __launch_bounds__(kRagThreads, 3) k_ragged_copy(EncTables T, uin
     __syncthreads();
     const uint64_t tile_end = tile_begin + total;
     const uint64_t lo = cursor, hi = b < tile_end ? b : tile_end;
-    {  // bulk path: the whole range lies inside the bytes of ONE element (encoded images, serialized Examples):
-       // a plain CTA-wide copy, any alignment on both sides
-      const uint32_t i0 = find_segment(s_rec, ne, lo);
-      const uint64_t r0 = s_rec[i0], so = offs[e0 + i0];
-      const uint64_t ln = offs[e0 + i0 + 1] - so;
-      const uint32_t h0 = 1u + varint_len(ln);
-      if (lo >= r0 + h0 && hi <= r0 + h0 + ln) {  // uniform across the CTA
-        cta_copy_bytes<4>(out + lo, bytes + so + (lo - r0 - h0), static_cast<uint32_t>(hi - lo));
+    {  // few, large elements in the range (encoded images, serialized Examples): element by element, the header bytes by
+       // a handful of threads, the payload piece by a CTA-wide copy (any alignment on both sides)
+      const uint32_t i0 = find_segment(s_rec, ne, lo), i1 = find_segment(s_rec, ne, hi - 1);  // uniform across the CTA
+      if (i1 - i0 < 16u) {
+        for (uint32_t idx = i0; idx <= i1; ++idx) {
+          const uint64_t r0 = s_rec[idx], so = offs[e0 + idx];
+          const uint64_t ln = offs[e0 + idx + 1] - so;
+          const uint32_t h0 = 1u + varint_len(ln);
+          if (threadIdx.x < h0) {
+            const uint64_t p = r0 + threadIdx.x;
+            if (p >= lo && p < hi)
+              out[p] = threadIdx.x == 0 ? key
+                                        : static_cast<uint8_t>(((ln >> (7u * (threadIdx.x - 1u))) & 0x7Fu) | (threadIdx.x + 1u < h0 ? 0x80u : 0u));
+          }
+          const uint64_t pa = lo > r0 + h0 ? lo : r0 + h0, pb = hi < r0 + h0 + ln ? hi : r0 + h0 + ln;
+          if (pa < pb) cta_copy_bytes<4>(out + pa, bytes + so + (pa - r0 - h0), static_cast<uint32_t>(pb - pa));
+        }
         cursor = hi;
         ++et;
         __syncthreads();
