@@ -304,6 +304,7 @@ def run_ours(args):
                      "other_copy_kernel_avg_ms": round(ms_gen / max(1, n_gen), 4),
                      "achieved": round(achieved, 1) if achieved else None,
                      "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4) if achieved else None, "peak_source": peak_src,
+                     "frac_of_nominal_8000_GBps": round(achieved / 8000.0, 4) if achieved else None,
                      "traffic": traffic, "traffic_source": traffic_src, "launches_timed": n_copy, "avg_launch_ms": round(ms_copy / max(1, n_copy), 4),
                      "algorithmic_bytes_per_launch": alg_per_launch,
                      "step_frac_of_peak": round(2 * value / world / peak, 4),
