@@ -187,7 +187,9 @@ typedef struct {
   int32_t unknown_rank;    /* tensor_shape.proto:45 */
   uint32_t n_dims;         /* <= TFS_MAX_DIMS; Dim.name is always "" (src/lib.rs:233) */
   uint32_t first_field;    /* index into tfs_batch_t.fields */
-  uint32_t n_fields;       /* payload fields of this tensor, any order, at most one per kind */
+  uint32_t n_fields;       /* payload fields of this tensor, any order.  A kind may appear more than once: the arrays are
+                              then ONE field on the wire, concatenated in descriptor order (e.g. a [B,H,W,3] float_val
+                              assembled from B separately stored u8 images, each with its own fused u8 -> f32 scale) */
   uint32_t _pad;
   int64_t dims[TFS_MAX_DIMS];
 } tfs_tensor_desc_t;

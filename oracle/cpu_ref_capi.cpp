@@ -175,7 +175,25 @@ bool build_tensor(const tfs_batch_t& b, const tfs_tensor_desc_t& td, TensorProto
   for (uint32_t i = 0; i < td.n_fields; ++i) {
     const tfs_field_desc_t& f = b.fields[td.first_field + i];
     int slot = slot_of_kind(f.kind);
-    if (slot < 0 || (seen >> slot) & 1u) return false;
+    if (slot < 0) return false;
+    if ((seen >> slot) & 1u) {  // the same kind again: concatenated in descriptor order (what the caller's Vec would hold)
+      TensorProto more;
+      if (!build_field(f, &more)) return false;
+      auto app = [](auto& dst, auto& src) { dst.insert(dst.end(), src.begin(), src.end()); };
+      app(t->tensor_content, more.tensor_content);
+      app(t->half_val, more.half_val);
+      app(t->float_val, more.float_val);
+      app(t->double_val, more.double_val);
+      app(t->int_val, more.int_val);
+      app(t->string_val, more.string_val);
+      app(t->scomplex_val, more.scomplex_val);
+      app(t->int64_val, more.int64_val);
+      app(t->bool_val, more.bool_val);
+      app(t->dcomplex_val, more.dcomplex_val);
+      app(t->uint32_val, more.uint32_val);
+      app(t->uint64_val, more.uint64_val);
+      continue;
+    }
     seen |= 1u << slot;
     if (!build_field(f, t)) return false;
   }

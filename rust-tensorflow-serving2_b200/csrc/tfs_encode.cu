@@ -73,6 +73,19 @@ __device__ __forceinline__ uint64_t spec_body_len(const EncMsg& m) {
   return n;
 }
 
+// Several descriptors of the same kind in one tensor are ONE field on the wire: their bodies concatenated in descriptor
+// order under a single key + length (a [B,H,W,3] tensor assembled from B separately stored images).
+// Returns the summed body length of the group that starts at field i and the index one past its last member.
+__device__ __forceinline__ uint64_t group_body_len(const EncTables& T, const EncTensor& t, uint32_t i, uint32_t* end) {
+  const int32_t kind = T.fields[t.first_field + i].kind;
+  uint64_t n = 0;
+  uint32_t j = i;
+  for (; j < t.n_fields && T.fields[t.first_field + j].kind == kind; ++j)
+    if (T.fields[t.first_field + j].n_elems != 0) n += T.fields[t.first_field + j].body_len;
+  *end = j;
+  return n;
+}
+
 __device__ __forceinline__ uint64_t tensor_body_len(const EncTables& T, const EncTensor& t) {
   uint64_t n = 0;
   if (t.dtype != 0) n += 1u + varint_len(static_cast<uint64_t>(static_cast<int64_t>(t.dtype)));
@@ -81,11 +94,14 @@ __device__ __forceinline__ uint64_t tensor_body_len(const EncTables& T, const En
     n += 1u + varint_len(s) + s;
   }
   if (t.version_number != 0) n += 1u + varint_len(static_cast<uint64_t>(static_cast<int64_t>(t.version_number)));
-  for (uint32_t i = 0; i < t.n_fields; ++i) {
+  for (uint32_t i = 0; i < t.n_fields;) {
     const EncField& f = T.fields[t.first_field + i];
-    if (f.n_elems == 0) continue;
+    uint32_t end;
+    const uint64_t body = group_body_len(T, t, i, &end);
+    i = end;
+    if (body == 0) continue;  // (a packed field or a record area is never empty when it has elements)
     // repeated bytes: the record area carries a key and a length per element, nothing in front of it
-    n += f.is_varint == FC_RAGGED ? f.body_len : key_len(f.kind) + varint_len(f.body_len) + f.body_len;
+    n += f.is_varint == FC_RAGGED ? body : key_len(f.kind) + varint_len(body) + body;
   }
   return n;
 }
@@ -145,16 +161,26 @@ __device__ void emit_tensor_body(Sink& s, const EncTables& T, const EncTensor& t
     put_key(s, 3, 0);
     put_varint(s, static_cast<uint64_t>(static_cast<int64_t>(t.version_number)));
   }
+  uint32_t s_group_open = 0;  // a key + length has been written for the current run of same-kind descriptors
   for (uint32_t i = 0; i < t.n_fields; ++i) {
     const uint32_t fi = t.first_field + i;
     const EncField& f = T.fields[fi];
-    if (f.n_elems == 0) continue;
-    if (f.is_varint != FC_RAGGED) {
-      put_key(s, static_cast<uint32_t>(f.kind), 2);
-      put_varint(s, f.body_len);
+    if (f.n_elems == 0) {
+      if (i + 1 >= t.n_fields || T.fields[fi + 1].kind != f.kind) s_group_open = 0;
+      continue;
+    }
+    if (s_group_open == 0) {  // first non-empty descriptor of its kind: one key + length for the whole run
+      uint32_t end;
+      const uint64_t body = group_body_len(T, t, i, &end);
+      if (f.is_varint != FC_RAGGED) {
+        put_key(s, static_cast<uint32_t>(f.kind), 2);
+        put_varint(s, body);
+      }
+      s_group_open = 1;
     }
     on_body(fi, s.pos);
     s.skip(f.body_len);
+    if (i + 1 >= t.n_fields || T.fields[fi + 1].kind != f.kind) s_group_open = 0;
   }
 }
 
@@ -597,15 +623,16 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
         if (input_kind != (fk >= TFS_KIND_BYTES_LIST && fk <= TFS_KIND_INT64_LIST))
           return set_err(ctx, TFS_ERR_INVALID_ARG, "list kinds belong to features, *_val kinds to tensors");
         const int32_t slot = input_kind ? 0 : tfs_slot_of_kind(fk);
-        if (slot < 0 || ((seen >> slot) & 1u)) return set_err(ctx, TFS_ERR_INVALID_ARG, "unknown or repeated payload kind in one tensor");
+        // a kind may come more than once in a TENSOR: the arrays are concatenated in descriptor order (batch assembly)
+        if (slot < 0 || (input_kind && ((seen >> slot) & 1u))) return set_err(ctx, TFS_ERR_INVALID_ARG, "unknown payload kind, or two lists in one feature");
         seen |= 1u << slot;
         if (!compile_field(b->fields[fi], &c->fields[fi], &field_bound[fi]))
           return set_err(ctx, TFS_ERR_INVALID_ARG, "payload field: conversion not allowed by the ABI");
         bound += field_bound[fi] + 16;
       }
       // prost emits in ascending field number: order this tensor's fields by kind
-      std::sort(c->fields.begin() + t.first_field, c->fields.begin() + t.first_field + t.n_fields,
-                [](const EncField& x, const EncField& y) { return x.kind < y.kind; });
+      std::stable_sort(c->fields.begin() + t.first_field, c->fields.begin() + t.first_field + t.n_fields,
+                       [](const EncField& x, const EncField& y) { return x.kind < y.kind; });
     }
     c->bound += (flags & TFS_F_ALIGN_PAYLOAD) ? align_up(bound + 16, 16) : bound;
   }

@@ -220,22 +220,31 @@ def build_batch(messages, kind) -> BuiltBatch:
                 fld_l.append(fd)
                 n += 1
                 continue
-            p = v if isinstance(v, Payload) else Payload(v, abi.T_NONE)
-            ptr, count, ty, ka = _array_info(p.data)
-            keep.append(ka)
-            fd = abi.FieldDesc()
-            fd.kind = k
-            fd.src_type = p.src_type if p.src_type != abi.T_NONE else ty
-            fd.dst_type = p.dst_type
-            fd.op = p.op
-            fd.op_param = float(p.op_param)
-            # a source array viewed as a wider / narrower type than it is stored in
-            fd.n_elems = count * abi.TYPE_SIZE[ty] // abi.TYPE_SIZE[fd.src_type]
-            fd.data = ptr
-            fld_l.append(fd)
-            n += 1
+            if isinstance(v, tuple):  # several arrays = ONE field on the wire, concatenated in order (batch assembly)
+                parts = v
+            else:
+                parts = (v,)
+            for part in parts:
+                n += _add_field(fld_l, keep, k, part)
+            continue
         td.n_fields = n
         ten_l.append(td)
+
+    def _add_field(fld_l, keep, k, v):
+        p = v if isinstance(v, Payload) else Payload(v, abi.T_NONE)
+        ptr, count, ty, ka = _array_info(p.data)
+        keep.append(ka)
+        fd = abi.FieldDesc()
+        fd.kind = k
+        fd.src_type = p.src_type if p.src_type != abi.T_NONE else ty
+        fd.dst_type = p.dst_type
+        fd.op = p.op
+        fd.op_param = float(p.op_param)
+        # a source array viewed as a wider / narrower type than it is stored in
+        fd.n_elems = count * abi.TYPE_SIZE[ty] // abi.TYPE_SIZE[fd.src_type]
+        fd.data = ptr
+        fld_l.append(fd)
+        return 1
 
     def add_feature(name, ft: Feature, example_index: int):
         td = abi.TensorDesc()

@@ -142,6 +142,8 @@ def to_device(messages, kind, device):
     def mv(v):
         if v is None:
             return None
+        if isinstance(v, tuple):  # several arrays concatenated into one field
+            return tuple(mv(x) for x in v)
         if isinstance(v, Ragged):
             return Ragged(torch.as_tensor(np.ascontiguousarray(v.block)).to(device), v.n_elems, v.total_bytes)
         if isinstance(v, list):  # string_val given as a list of bytes-like elements

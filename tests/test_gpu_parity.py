@@ -53,6 +53,8 @@ def pinned_like(msgs, kind):
             return None
         if isinstance(v, tfs.Payload):
             return tfs.Payload(mv(v.data), v.src_type if v.src_type != abi.T_NONE else tfs.messages._array_info(v.data)[2], v.dst_type, v.op, v.op_param)
+        if isinstance(v, tuple):
+            return tuple(mv(x) for x in v)
         if isinstance(v, list):  # string_val
             blk = tfs.ragged_block(v)
             return tfs.Ragged(mv(blk), len(v), blk.size - 8 * (len(v) + 1))
@@ -576,6 +578,32 @@ def test_input_descriptor_errors(codec):
         enc.encode_host(mixed, abi.MSG_TENSOR_PROTO)
     with pytest.raises(tfs.TfsError):            # decode of Input is not provided: the reference only builds Inputs
         codec.decoder().decode_host(np.zeros(4, np.uint8), [0], [4], abi.MSG_INPUT)
+
+
+# ---- batch assembly: several source arrays, one field on the wire ----------------------
+def test_same_kind_descriptors_are_concatenated(codec):
+    rng = np.random.default_rng(12)
+    imgs = [rng.integers(0, 256, 3 * 17 * 17 + i, dtype=np.uint8) for i in range(5)]  # five "images" of slightly different size
+    n = sum(x.size for x in imgs)
+    fused = tfs.TensorProto(dtype=1, tensor_shape=tfs.TensorShapeProto([n]),
+                            float_val=tuple(tfs.Payload(x, abi.T_U8, abi.T_F32, abi.OP_DIV, 255.0) for x in imgs))
+    plain = tfs.TensorProto(dtype=1, tensor_shape=tfs.TensorShapeProto([n]),
+                            float_val=(np.concatenate(imgs).astype(np.float32) / np.float32(255.0)).astype(np.float32))
+    want = ob.encode_messages([plain], abi.MSG_TENSOR_PROTO)
+    assert ob.encode_messages([fused], abi.MSG_TENSOR_PROTO) == want          # the oracle agrees with itself
+    assert_bytes_equal(gpu_encode_both(codec, [fused], abi.MSG_TENSOR_PROTO), want, "u8 images -> one float_val")
+    # every class: varint (with an empty part and parts that cross tile edges), fixed, raw bytes, strings; big parts too
+    parts64 = (rng.integers(-9, 1 << 33, 3000, dtype=np.int64), np.zeros(0, np.int64), rng.integers(0, 99, 2049, dtype=np.int64))
+    t = tfs.TensorProto(dtype=9, int64_val=parts64, double_val=(rng.standard_normal(7), rng.standard_normal(100_000)),
+                        tensor_content=(rng.integers(0, 256, 70_001, dtype=np.uint8), rng.integers(0, 256, 5, dtype=np.uint8)),
+                        half_val=(np.arange(5, dtype=np.int32), np.arange(40000, 40100, dtype=np.int32)))
+    flat = tfs.TensorProto(dtype=9, int64_val=np.concatenate(parts64), double_val=np.concatenate(t.double_val),
+                           tensor_content=np.concatenate(t.tensor_content), half_val=np.concatenate(t.half_val))
+    for flags in (0, abi.F_ALIGN_PAYLOAD):
+        req = [tfs.PredictRequest(tfs.ModelSpec("m"), [("a", t), ("b", fused)]), tfs.PredictRequest(None, [("c", t)])]
+        req_flat = [tfs.PredictRequest(tfs.ModelSpec("m"), [("a", flat), ("b", plain)]), tfs.PredictRequest(None, [("c", flat)])]
+        want = ob.encode_messages(req_flat, abi.MSG_PREDICT_REQUEST)
+        assert_bytes_equal(gpu_encode_both(codec, req, abi.MSG_PREDICT_REQUEST, flags), want, f"concatenated parts (flags {flags})")
 
 
 # ---- BASELINE configs ---------------------------------------------------------------------------------
