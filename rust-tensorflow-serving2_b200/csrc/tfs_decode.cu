@@ -97,6 +97,7 @@ struct Walker {
   int32_t err = 0;
   uint64_t err_pos = 0;
   bool soft_unsupported = false;
+  bool verify = false;  // error path only: also look inside packed varint bodies (see walk_body)
   // counters (COUNT) / cursors (FILL)
   uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0, n_generic = 0, n_bulk = 0;
   uint32_t seen_slots = 0;  // payload slots of the current tensor that already have a chunk
@@ -246,6 +247,22 @@ struct Walker {
     if (FILL) T.tensors[cur].msg_index = msg;
   }
   __device__ void add_span(uint32_t slot, uint32_t cls, uint64_t off, uint64_t len, uint64_t n_elems, uint32_t out_mult) {
+    if (verify && cls == SC_VARINT && !err) {  // an over-long varint inside this body comes BEFORE whatever failed later
+      uint32_t run = 0;
+      for (uint64_t q = off; q < off + len; ++q) {
+        if (byte_at(q) & 0x80) {
+          if (++run == 10) {
+            const uint64_t keep = pos;
+            pos = q + 1;
+            fail(TFS_ERR_INVALID_VARINT);
+            pos = keep;
+            break;
+          }
+        } else {
+          run = 0;
+        }
+      }
+    }
     const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(wv, off, len) : 0u;
     if (cls == SC_STR && len) n_generic++;  // string bytes land wherever the earlier elements end: generic kernel
     if (cls != SC_VARINT && len >= 4096) n_bulk++;  // large enough for the TMA ring (if it turns out congruent mod 16)
@@ -593,6 +610,22 @@ __device__ void walk_body(const DecTables& T, uint32_t mi) {
   if (!FILL) {
     const bool in_bounds = wk.end <= T.wire_bytes && wk.end >= wk.beg;
     bool ok = in_bounds ? wk.run(&mo) : wk.fail(TFS_ERR_BUFFER_UNDERFLOW);
+    if (!ok && in_bounds) {
+      // prost stops at the FIRST error in stream order.  The walk does not look inside packed varint bodies (K4a does,
+      // but only for messages that pass the walk), so a failed message is walked once more with those bodies checked.
+      Walker<false> v(T, mi);
+      v.beg = wk.beg;
+      v.end = wk.end;
+      v.pos = wk.beg;
+      v.verify = true;
+      tfs_msg_out_t scratch;
+      memset(&scratch, 0, sizeof(scratch));
+      v.run(&scratch);
+      if (v.err) {
+        wk.err = v.err;
+        wk.err_pos = v.err_pos;
+      }
+    }
     T.msgs[mi].status = ok ? TFS_OK : wk.err;
     T.msgs[mi].err_offset = ok ? 0 : wk.err_pos;
     T.cnt_tensors[mi] = ok ? wk.n_tensors : 0u;

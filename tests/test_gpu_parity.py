@@ -358,6 +358,20 @@ def test_decode_plan_outgrows_its_first_tables():
         fresh.ctx.close()
 
 
+def test_decode_reports_the_first_error_in_stream_order(codec):
+    """An over-long varint INSIDE a packed body comes before a structural error later in the message: prost fails at the
+    first one (found by a longer fuzz run: the walk used to report the later one)."""
+    long_run = b"\x3a\x0c" + b"\x80" * 11 + b"\x01"
+    blobs = [long_run + b"\x2a\x05\x00",                     # ... then float_val longer than the buffer
+             b"\x08\x01" + long_run + b"\x28\x01",            # ... then a wrong wire type
+             b"\x3a\x02\x01\x02" + long_run + b"\x0a",        # a good body, the bad one, then a truncated key/len
+             b"\x2a\x09\x00" + long_run[:4]]                 # the structural error comes first here
+    st, got = gpu_decode_both(codec, blobs, abi.MSG_TENSOR_PROTO)
+    st_o, want = ob.decode_bytes(blobs, abi.MSG_TENSOR_PROTO)
+    assert [m.status for m in got] == [m.status for m in want]
+    assert [m.status for m in got] == [abi.TFS_ERR_INVALID_VARINT] * 3 + [abi.TFS_ERR_BUFFER_UNDERFLOW]  # (len 9 > 4 bytes left)
+
+
 def test_decode_long_varint_runs_inside_big_span(codec):
     # a >10-byte varint deep inside a multi-tile packed body is only visible to the terminator kernel
     for pos in (5, 4090, 4096, 8191, 20000):
@@ -417,10 +431,11 @@ def test_grpc_prefix_roundtrip(codec):
 
 def test_decode_fuzz_against_oracle(codec):
     """Random truncations / byte flips of valid messages: same status class, same values when OK."""
-    rng = np.random.default_rng(99)
+    import os
+    rng = np.random.default_rng(int(os.environ.get("TFS_FUZZ_SEED", "99")))   # TFS_FUZZ_SEED / TFS_FUZZ_CASES: a longer hunt
     base = ob.encode_messages(workloads.c5_responses(24, seed=31, max_log2=7), abi.MSG_PREDICT_RESPONSE)
     blobs = []
-    for i in range(400):
+    for i in range(int(os.environ.get("TFS_FUZZ_CASES", "400"))):
         b = bytearray(base[i % len(base)])
         op = rng.integers(0, 4)
         if op == 0 and len(b) > 1:
