@@ -139,3 +139,66 @@ def test_random_requests_encode_and_decode_like_the_oracle(codec, seed):
     d2 = codec.decoder().decode(dw, offs, lens, abi.MSG_PREDICT_REQUEST)
     codec.ctx.sync()
     helpers.assert_same_decoded(want_dec, d2.messages(), "request", f"stress seed {seed} device")
+
+
+def _mutate(rng, b):
+    b = bytearray(b)
+    op = rng.integers(0, 5)
+    if op == 0 and len(b) > 1:
+        b = b[: rng.integers(0, len(b))]
+    elif op == 1 and len(b):
+        for _ in range(int(rng.integers(1, 4))):
+            b[rng.integers(0, len(b))] = rng.integers(0, 256)
+    elif op == 2 and len(b):
+        j = rng.integers(0, len(b))
+        b[j:j] = bytes(rng.integers(0, 256, rng.integers(1, 5), dtype=np.uint8))
+    elif op == 3 and len(b) > 2:
+        j = rng.integers(0, min(len(b), 60))
+        b[j] ^= 1 << int(rng.integers(0, 8))
+    elif len(b) > 4:  # a run of continuation bytes somewhere (over-long varints, lengths that swallow what follows)
+        j = rng.integers(0, len(b) - 1)
+        n = int(rng.integers(1, 13))
+        b[j: j + n] = b"\xff" * min(n, len(b) - j)
+    return bytes(b)
+
+
+@pytest.mark.parametrize("kind", [abi.MSG_TENSOR_PROTO, abi.MSG_PREDICT_REQUEST])
+def test_mutated_messages_fail_like_the_oracle(codec, kind):
+    """Byte-level mutations of valid messages with every payload kind (strings included): the same status per message as
+    the oracle, the same values where the message still parses."""
+    rng = np.random.default_rng(int(os.environ.get("TFS_FUZZ_SEED", "7")) + kind)
+    small = []
+    for i in range(30):
+        t = random_tensor(rng)
+        for k in abi.SLOT_KINDS:  # keep the fuzz corpus small: mutations should hit structure, not megabytes of payload
+            name = abi.KIND_FIELD_NAMES[k]
+            v = getattr(t, name)
+            if isinstance(v, tuple):
+                v = np.concatenate(v)
+            if v is not None:
+                setattr(t, name, v[:50])
+        small.append(t)
+    if kind == abi.MSG_TENSOR_PROTO:
+        base = ob.encode_messages(small, kind)
+    else:
+        reqs = [tfs.PredictRequest(tfs.ModelSpec("m", signature_name="s") if i % 2 else None,
+                                   [("k%d" % j, small[(i + j) % len(small)]) for j in range(i % 4)], ["f"] * (i % 3)) for i in range(20)]
+        base = ob.encode_messages(reqs, kind)
+    n_cases = int(os.environ.get("TFS_FUZZ_CASES", "600"))
+    blobs = [_mutate(rng, base[i % len(base)]) for i in range(n_cases)]
+    st_o, want = ob.decode_bytes(blobs, kind)
+    offs, lens, cur = [], [], 0
+    for b in blobs:
+        offs.append(cur)
+        lens.append(len(b))
+        cur += len(b)
+    wire_np = np.frombuffer(b"".join(blobs), dtype=np.uint8)
+    d = codec.decoder().decode_host(wire_np, offs, lens, kind)
+    got = d.messages()
+    mism = [(i, blobs[i].hex()[:400], abi.STATUS_NAMES.get(w.status), abi.STATUS_NAMES.get(g.status))
+            for i, (w, g) in enumerate(zip(want, got)) if w.status != g.status]
+    assert not mism, mism[:4]
+    name = "tensor" if kind == abi.MSG_TENSOR_PROTO else "request"
+    for i, (w, g) in enumerate(zip(want, got)):
+        if w.status == 0:
+            helpers.assert_same_decoded([w], [g], name, f"mutation {i}: {blobs[i].hex()[:200]}")
