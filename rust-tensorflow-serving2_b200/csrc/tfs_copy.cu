@@ -77,6 +77,26 @@ __device__ __forceinline__ uint32_t seg_from(const CopySeg* __restrict__ segs, u
   return lo;
 }
 
+// Segment owning `tile`, found by one warp: every round the 32 lanes probe 32 evenly spaced table entries at once, so a
+// table of up to 32^3 segments costs three dependent memory round trips instead of fifteen (a CTA that copies a few
+// hundred bytes spends most of its life in this lookup).  All 32 lanes must call it; all return the same index.
+__device__ __forceinline__ uint32_t seg_of_tile_warp(const CopySeg* __restrict__ segs, uint32_t n_segs, uint64_t tile, uint32_t from = 0) {
+  uint32_t lo = from, hi = n_segs;  // invariant: segs[lo].first_tile <= tile, (hi == n_segs or segs[hi].first_tile > tile)
+  while (hi - lo > 1) {
+    const uint32_t span = hi - lo;
+    const uint32_t step = (span + 31u) / 32u;
+    const uint32_t idx = lo + lane_id() * step;  // lane 0 probes `lo` itself (true by the invariant)
+    const bool le = idx < hi && segs[idx].first_tile <= tile;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, le);
+    const uint32_t k = 31u - static_cast<uint32_t>(__clz(static_cast<int>(m)));  // last lane whose probe is <= tile (m has bit 0)
+    const uint32_t nlo = lo + k * step;
+    const uint32_t nhi = nlo + step < hi ? nlo + step : hi;
+    lo = nlo;
+    hi = nhi;
+  }
+  return lo;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // generic path: one CTA per tile
 // ---------------------------------------------------------------------------------------------------
@@ -126,7 +146,10 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy(const CopySeg* __restrict
   if (gate && *gate != 0) return;  // an earlier kernel of the batch refused to go on (dst too small)
   const uint64_t tile = tile_begin + blockIdx.x;
   if (tile >= n_tiles) return;
-  if (threadIdx.x == 0) s_seg = seg_from(segs, n_segs, 0, tile);
+  if (threadIdx.x < 32) {
+    const uint32_t si = seg_of_tile_warp(segs, n_segs, tile);
+    if (threadIdx.x == 0) s_seg = si;
+  }
   __syncthreads();
   const CopySeg seg = segs[s_seg];
   if (seg.n == 0 || tma_eligible(seg)) return;  // the TMA ring owns this segment
@@ -204,9 +227,19 @@ struct TileWalk {
   uint64_t tile, n_tiles, stride;
   uint64_t src_lo, src_hi;  // this launch owns the tiles whose source bytes END in (src_lo, src_hi]
 
+  // COOP = false: one thread walks alone (few segments: the hint almost always hits).  COOP = true: called by all 32
+  // lanes of the CTA's warp in lockstep (every lane computes the same result): the segment lookup is a warp-wide
+  // search, the < 16 ragged bytes at a segment's ends are split over the lanes.
+  template <bool COOP>
   __device__ bool next(const uint8_t** src, uint8_t** dst, uint32_t* bytes) {
+    if (COOP) __syncwarp();  // the leader may come from a TMA-only block: reconverge before the warp-wide search
+    const uint32_t l0 = COOP ? lane_id() : 0u, lstep = COOP ? 32u : 1u;
     for (; tile < n_tiles; tile += stride) {
-      si = seg_from(segs, n_segs, si, tile);
+      if (COOP) {
+        if (si + 1 < n_segs && segs[si + 1].first_tile <= tile) si = seg_of_tile_warp(segs, n_segs, tile, si + 1);
+      } else {
+        si = seg_from(segs, n_segs, si, tile);
+      }
       const CopySeg seg = segs[si];
       if (seg.n == 0 || !tma_eligible(seg)) continue;
       uint64_t a, b;
@@ -218,13 +251,13 @@ struct TileWalk {
       const uint32_t head = static_cast<uint32_t>((16u - ((d + a) & 15u)) & 15u);  // only in a segment's first tile
       if (head) {
         const uint64_t h1 = a + head < b ? a + head : b;
-        for (uint64_t i = a; i < h1; ++i) seg.dst[i] = seg.src[i];
+        for (uint64_t i = a + l0; i < h1; i += lstep) seg.dst[i] = seg.src[i];
         a = h1;
       }
       const uint32_t tail = static_cast<uint32_t>((d + b) & 15u);  // only in its last tile
       if (tail && b > a) {
         const uint64_t t0 = b - tail > a ? b - tail : a;
-        for (uint64_t i = t0; i < b; ++i) seg.dst[i] = seg.src[i];
+        for (uint64_t i = t0 + l0; i < b; i += lstep) seg.dst[i] = seg.src[i];
         b = t0;
       }
       if (a >= b) continue;
@@ -238,18 +271,26 @@ struct TileWalk {
   }
 };
 
+template <bool COOP>
 __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ segs, uint32_t n_segs, uint64_t n_tiles,
                                                  const uint64_t* __restrict__ gate, uint64_t src_lo, uint64_t src_hi,
                                                  uint64_t tile_begin) {
   extern __shared__ __align__(128) uint8_t ring[];  // kTmaStages x kTmaChunk
   __shared__ __align__(8) uint64_t full_bar[kTmaStages];
-  if (threadIdx.x != 0) return;  // one thread drives the TMA engine; the warp exists only to own the CTA
+  // Lane 0 drives the TMA engine.  COOP = false (few segments, the C2 shape): the other lanes leave at once.  COOP = true
+  // (hundreds of segments): they stay to help find the tiles (warp-wide segment search) and copy the ragged ends; all
+  // lanes then run the same control flow on the same values.
+  if (!COOP && threadIdx.x != 0) return;
+  const bool leader = threadIdx.x == 0;
   if (gate && *gate != 0) return;
   if (tile_begin + blockIdx.x >= n_tiles) return;
+  if (leader) {
 #pragma unroll
-  for (uint32_t s = 0; s < kTmaStages; ++s) mbar_init(&full_bar[s], 1);
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    for (uint32_t s = 0; s < kTmaStages; ++s) mbar_init(&full_bar[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (COOP) __syncwarp();
 
   const uint64_t pol = l2_evict_first_policy();
   TileWalk walk{segs, n_segs, 0u, tile_begin + blockIdx.x, n_tiles, gridDim.x, src_lo, src_hi};
@@ -260,12 +301,14 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
     const uint8_t* src;
     uint8_t* dst;
     uint32_t bytes;
-    if (!walk.next(&src, &dst, &bytes)) return false;
+    if (!walk.template next<COOP>(&src, &dst, &bytes)) return false;
     const uint32_t s = issued % kTmaStages;
     dsts[s] = dst;
     sizes[s] = bytes;
-    mbar_expect_tx(&full_bar[s], bytes);
-    tma_load(ring + s * kTmaChunk, src, bytes, &full_bar[s], pol);
+    if (leader) {
+      mbar_expect_tx(&full_bar[s], bytes);
+      tma_load(ring + s * kTmaChunk, src, bytes, &full_bar[s], pol);
+    }
     ++issued;
     return true;
   };
@@ -274,16 +317,19 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
     if (!issue()) break;
   while (stored < issued) {
     const uint32_t s = stored % kTmaStages;
-    mbar_wait(&full_bar[s], (stored / kTmaStages) & 1u);
-    tma_store(dsts[s], ring + s * kTmaChunk, sizes[s], pol);
-    tma_commit();
+    if (leader) {
+      mbar_wait(&full_bar[s], (stored / kTmaStages) & 1u);
+      tma_store(dsts[s], ring + s * kTmaChunk, sizes[s], pol);
+      tma_commit();
+      // all but the newest store have finished reading shared memory: the stage of store (stored - 1) is free,
+      // and it is exactly the stage the next load (index `issued`) maps to
+      tma_wait_read<1>();
+    }
     ++stored;
-    // all but the newest store have finished reading shared memory: the stage of store (stored - 2) is free,
-    // and it is exactly the stage the next load (index `issued`) maps to
-    tma_wait_read<1>();
+    if (COOP) __syncwarp();
     issue();
   }
-  tma_wait_all();
+  if (leader) tma_wait_all();
 }
 
 }  // namespace
@@ -294,7 +340,8 @@ tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs,
   if (n_tiles > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (copy tiles)");
   const uint32_t ring_bytes = kTmaStages * kTmaChunk;
   if (!ctx->copy_attr_set) {  // a per-device attribute: once per context, not once per process
-    TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ring_bytes)));
+    TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_tma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ring_bytes)));
+    TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_tma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ring_bytes)));
     ctx->copy_attr_set = true;
   }
   // tiles [tb, te), of which the kernels take those whose source bytes end in (src_lo, src_hi]
@@ -308,7 +355,9 @@ tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs,
     if (need_tma) {  // the TMA ring: one CTA (96 KiB of shared memory, one driving thread) per SM
       const uint64_t cap = static_cast<uint64_t>(ctx->sm_count);
       ProfScope prof(ctx, PK_COPY_TMA);
-      k_copy_tma<<<static_cast<uint32_t>(te - tb < cap ? te - tb : cap), 32, ring_bytes, ctx->stream>>>(segs_dev, n_segs, te, gate, src_lo, src_hi, tb);
+      const uint32_t grid = static_cast<uint32_t>(te - tb < cap ? te - tb : cap);
+      if (n_segs > 64) k_copy_tma<true><<<grid, 32, ring_bytes, ctx->stream>>>(segs_dev, n_segs, te, gate, src_lo, src_hi, tb);
+      else k_copy_tma<false><<<grid, 32, ring_bytes, ctx->stream>>>(segs_dev, n_segs, te, gate, src_lo, src_hi, tb);
       ctx->launches++;
     }
   };
