@@ -146,6 +146,15 @@ __device__ __forceinline__ typename OutTraits<OUT>::type convert_out(uint64_t v)
   else return __float_as_uint(bf16_bits_to_f32(static_cast<uint32_t>(v) & 0xFFFFu));
 }
 
+// the 32-bit word a value of at most 4 wire bytes is staged as (widened / narrowed to the output type by the flush)
+template <int OUT>
+__device__ __forceinline__ uint32_t convert_word(uint32_t v) {
+  if constexpr (OUT == O_U32 || OUT == O_U64) return v;  // non-negative and < 2^28: the upper half of an i64 is zero
+  else if constexpr (OUT == O_BOOL) return v != 0 ? 1u : 0u;
+  else if constexpr (OUT == O_F16_F32) return __float_as_uint(f16_bits_to_f32(v & 0xFFFFu));
+  else return __float_as_uint(bf16_bits_to_f32(v & 0xFFFFu));
+}
+
 // Output staging: 2048 values of up to 8 bytes.  A tile holds at most 4096 values (one per wire byte), so a dense
 // tile is written out in two rounds; keeping the buffer at 16 KiB lets 8 CTAs share an SM.
 constexpr uint32_t kRoundValues = 2048;
@@ -153,23 +162,50 @@ constexpr uint32_t kRoundValues = 2048;
 // multiples of 16 slots (16 one-byte varints per 16-byte chunk is the dense case); the pad spreads them over
 // the banks, and the flush still reads (almost) consecutive slots.
 __device__ __forceinline__ uint32_t pad_slot(uint32_t i) { return i + (i >> 4); }
+// The fast paths stage 32-bit words, 16 bytes of pad per 16 values: a thread with 16 one-byte values then owns four
+// aligned 16-byte vectors (80-byte stride between threads: the eight lanes of a 128-bit store phase hit all 32 banks).
+__device__ __forceinline__ uint32_t pad_word(uint32_t i) { return i + 4u * (i >> 4); }
 constexpr uint32_t kGatherOutBytes = (kRoundValues + kRoundValues / 16 + 1) * 8;
 
 template <int OUT>
-__device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restrict__ dst, uint8_t* sm_out, uint8_t* sm_in, uint32_t* scan_smem) {
+__device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restrict__ dst, uint8_t* sm_out, uint8_t* sm_in, uint32_t* scan_smem, uint32_t* edge) {
   using out_t = typename OutTraits<OUT>::type;
   out_t* out = reinterpret_cast<out_t*>(sm_out);
+  uint32_t* out32 = reinterpret_cast<uint32_t*>(sm_out);
   const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 16ull;
   uint4 d, pd;
   uint32_t cont, valid, pcont;
   chunk_masks(chunk_abs, r.span_abs0, r.span_end, &d, &cont, &valid);
-  prev_chunk(r, chunk_abs, d, cont, &pd, &pcont);
+  // The 16 bytes before this thread's chunk: the previous lane has them.  Lane 0 of warps 1..7 gets the previous warp's
+  // last lane through shared memory (its last word and continuation mask are all the fast path needs; the general path
+  // reads the staged tile), only thread 0 has to go back to global memory for the bytes in front of the tile.
+  pd.x = __shfl_up_sync(0xFFFFFFFFu, d.x, 1);
+  pd.y = __shfl_up_sync(0xFFFFFFFFu, d.y, 1);
+  pd.z = __shfl_up_sync(0xFFFFFFFFu, d.z, 1);
+  pd.w = __shfl_up_sync(0xFFFFFFFFu, d.w, 1);
+  pcont = __shfl_up_sync(0xFFFFFFFFu, cont, 1);
+  if (lane_id() == 31) {
+    edge[2 * warp_id()] = d.w;
+    edge[2 * warp_id() + 1] = cont;
+  }
+  if (threadIdx.x == 0) {
+    uint32_t pv;
+    chunk_masks(chunk_abs - 16, r.span_abs0, r.span_end, &pd, &pcont, &pv);
+  }
   const uint32_t term = ~cont & valid;
   uint32_t total;
-  const uint32_t idx0 = block_exclusive_scan<uint32_t, kDecThreads / 32>(__popc(term), scan_smem, &total);
+  const uint32_t idx0 = block_exclusive_scan<uint32_t, kDecThreads / 32>(__popc(term), scan_smem, &total);  // two barriers
+  if (lane_id() == 0 && warp_id() != 0) {
+    pd.w = edge[2 * warp_id() - 2];
+    pcont = edge[2 * warp_id() - 1];
+  }
   const uint32_t c32 = (cont << 16) | pcont;
   const uint32_t run4 = c32 & (c32 >> 1) & (c32 >> 2) & (c32 >> 3);  // bit i: continuation bytes at i..i+3
   const bool fast = __syncthreads_and((run4 & 0xFFFFF000u) == 0);       // no value ending in this tile is longer than 4 bytes
+  // every byte of the span inside this tile is a terminator <=> every value is ONE byte (masks, bools, small ids)
+  const uint64_t v_lo = r.span_abs0 > r.tile_abs ? r.span_abs0 : r.tile_abs;
+  const uint64_t v_hi = r.span_end < r.tile_abs + kDecTileBytes ? r.span_end : r.tile_abs + kDecTileBytes;
+  const bool all1 = total == static_cast<uint32_t>(v_hi - v_lo);
   out_t* gdst = reinterpret_cast<out_t*>(dst);
   if (!fast) {
     *reinterpret_cast<uint4*>(sm_in + 16 + threadIdx.x * 16) = d;
@@ -177,23 +213,46 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
   }
   for (uint32_t round0 = 0; round0 < total; round0 += kRoundValues) {  // uniform trip count (1, rarely 2)
   if (round0) __syncthreads();  // the previous round's flush has read the staging buffer
-  if (fast) {
+  if (all1) {  // masks, bools, small ids: the byte IS the value
+    const uint32_t w4[4] = {d.x, d.y, d.z, d.w};
+    uint32_t slot = idx0 - round0;  // wraps when before this round
+    if (total == kDecTileBytes) {   // a full tile of one-byte values: every thread owns 16 consecutive slots
+      if (slot < kRoundValues) {
+        uint4* v4 = reinterpret_cast<uint4*>(out32 + pad_word(slot));
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          v4[k] = make_uint4(convert_word<OUT>(w4[k] & 0xFFu), convert_word<OUT>((w4[k] >> 8) & 0xFFu),
+                             convert_word<OUT>((w4[k] >> 16) & 0xFFu), convert_word<OUT>(w4[k] >> 24));
+      }
+    } else {
+#pragma unroll
+      for (int pos = 0; pos < 16; ++pos) {
+        if ((valid >> pos) & 1u) {
+          if (slot < kRoundValues) out32[pad_word(slot)] = convert_word<OUT>((w4[pos >> 2] >> (8 * (pos & 3))) & 0xFFu);
+          ++slot;
+        }
+      }
+    }
+  } else if (fast) {
     const uint32_t w[5] = {pd.w, d.x, d.y, d.z, d.w};
+    uint32_t slot = idx0 - round0;  // wraps when before this round
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
 #pragma unroll
       for (int b = 0; b < 4; ++b) {
         const int pos = 4 * k + b;
-        const uint32_t slot = idx0 + __popc(term & ((1u << pos) - 1u)) - round0;  // wraps when before this round
-        if (((term >> pos) & 1u) && slot < kRoundValues) {
-          const uint32_t x = b == 3 ? w[k + 1] : __funnelshift_r(w[k], w[k + 1], 8 * (b + 1));  // the 4 bytes ending at `pos`
-          const uint32_t t3 = (c32 >> (13 + pos)) & 7u;                                          // continuation bits of the 3 bytes before it
-          const uint32_t len = 1u + static_cast<uint32_t>(__clz(static_cast<int>(~(t3 << 29))));
-          uint32_t g = x & 0x7F7F7F7Fu;
-          g = (g & 0x007F007Fu) | ((g & 0x7F007F00u) >> 1);
-          g = (g & 0x00003FFFu) | ((g & 0x3FFF0000u) >> 2);
-          const uint32_t v = g >> (7u * (4u - len));
-          out[pad_slot(slot)] = convert_out<OUT>(v);
+        if ((term >> pos) & 1u) {
+          if (slot < kRoundValues) {
+            const uint32_t x = b == 3 ? w[k + 1] : __funnelshift_r(w[k], w[k + 1], 8 * (b + 1));  // the 4 bytes ending at `pos`
+            const uint32_t t3 = (c32 >> (13 + pos)) & 7u;                                          // continuation bits of the 3 bytes before it
+            const uint32_t len = 1u + static_cast<uint32_t>(__clz(static_cast<int>(~(t3 << 29))));
+            uint32_t g = x & 0x7F7F7F7Fu;
+            g = (g & 0x007F007Fu) | ((g & 0x7F007F00u) >> 1);
+            g = (g & 0x00003FFFu) | ((g & 0x3FFF0000u) >> 2);
+            const uint32_t v = g >> (7u * (4u - len));
+            out32[pad_word(slot)] = convert_word<OUT>(v);
+          }
+          ++slot;
         }
       }
     }
@@ -240,7 +299,11 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
   __syncthreads();
   // coalesced flush of this round's values
   const uint32_t n_round = total - round0 < kRoundValues ? total - round0 : kRoundValues;
-  for (uint32_t i = threadIdx.x; i < n_round; i += kDecThreads) gdst[round0 + i] = out[pad_slot(i)];
+  if (fast) {  // (all1 implies fast) staged as 32-bit words
+    for (uint32_t i = threadIdx.x; i < n_round; i += kDecThreads) gdst[round0 + i] = static_cast<out_t>(out32[pad_word(i)]);
+  } else {
+    for (uint32_t i = threadIdx.x; i < n_round; i += kDecThreads) gdst[round0 + i] = out[pad_slot(i)];
+  }
   }
 }
 
@@ -248,6 +311,7 @@ __global__ void __launch_bounds__(kDecThreads, 6) k_varint_gather(DecTables T, u
   __shared__ __align__(16) uint8_t sm_out[kGatherOutBytes];
   __shared__ __align__(16) uint8_t sm_in[16 + kDecTileBytes + 16];  // 16 bytes before the tile, the tile, slack for word loads
   __shared__ uint32_t scan_smem[kDecThreads / 32 + 1];
+  __shared__ uint32_t edge[2 * (kDecThreads / 32)];  // last word and continuation mask of every warp's last lane
   if (gate && *gate != 0) return;  // the pool of a one-call decode turned out to be too small
   const uint32_t tile = blockIdx.x;
   const TileRef r = tile_ref(T, tile);       // two independent broadcast loads
@@ -256,12 +320,12 @@ __global__ void __launch_bounds__(kDecThreads, 6) k_varint_gather(DecTables T, u
   uint8_t* dst = td.dst;
   const int32_t ty = td.type;
   switch (ty) {
-    case TFS_T_I32: case TFS_T_U32: gather_tile<O_U32>(r, dst, sm_out, sm_in, scan_smem); break;
-    case TFS_T_I64: case TFS_T_U64: gather_tile<O_U64>(r, dst, sm_out, sm_in, scan_smem); break;
-    case TFS_T_BOOL: gather_tile<O_BOOL>(r, dst, sm_out, sm_in, scan_smem); break;
+    case TFS_T_I32: case TFS_T_U32: gather_tile<O_U32>(r, dst, sm_out, sm_in, scan_smem, edge); break;
+    case TFS_T_I64: case TFS_T_U64: gather_tile<O_U64>(r, dst, sm_out, sm_in, scan_smem, edge); break;
+    case TFS_T_BOOL: gather_tile<O_BOOL>(r, dst, sm_out, sm_in, scan_smem, edge); break;
     case TFS_T_F32:
-      if (td.dtype == 19) gather_tile<O_F16_F32>(r, dst, sm_out, sm_in, scan_smem);
-      else gather_tile<O_BF16_F32>(r, dst, sm_out, sm_in, scan_smem);
+      if (td.dtype == 19) gather_tile<O_F16_F32>(r, dst, sm_out, sm_in, scan_smem, edge);
+      else gather_tile<O_BF16_F32>(r, dst, sm_out, sm_in, scan_smem, edge);
       break;
     default: break;
   }
