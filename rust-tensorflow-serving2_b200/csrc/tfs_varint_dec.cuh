@@ -234,27 +234,33 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
       }
     }
   } else if (fast) {
-    const uint32_t w[5] = {pd.w, d.x, d.y, d.z, d.w};
+    // The 20 bytes {last word before the chunk, the chunk} go to a thread-private strip of shared memory so that the
+    // loop can run over the terminators that exist (5-7 per chunk for 2-3 byte values) instead of over all 16 byte
+    // positions: the 4 bytes ending at terminator j are two word loads + one funnel shift.
+    uint32_t* win = reinterpret_cast<uint32_t*>(sm_in) + threadIdx.x * 5u;
+    if (round0 == 0) {
+      win[0] = pd.w;
+      win[1] = d.x;
+      win[2] = d.y;
+      win[3] = d.z;
+      win[4] = d.w;
+    }
     uint32_t slot = idx0 - round0;  // wraps when before this round
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-#pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        const int pos = 4 * k + b;
-        if ((term >> pos) & 1u) {
-          if (slot < kRoundValues) {
-            const uint32_t x = b == 3 ? w[k + 1] : __funnelshift_r(w[k], w[k + 1], 8 * (b + 1));  // the 4 bytes ending at `pos`
-            const uint32_t t3 = (c32 >> (13 + pos)) & 7u;                                          // continuation bits of the 3 bytes before it
-            const uint32_t len = 1u + static_cast<uint32_t>(__clz(static_cast<int>(~(t3 << 29))));
-            uint32_t g = x & 0x7F7F7F7Fu;
-            g = (g & 0x007F007Fu) | ((g & 0x7F007F00u) >> 1);
-            g = (g & 0x00003FFFu) | ((g & 0x3FFF0000u) >> 2);
-            const uint32_t v = g >> (7u * (4u - len));
-            out32[pad_word(slot)] = convert_word<OUT>(v);
-          }
-          ++slot;
-        }
+    uint32_t t = term;
+    while (t) {
+      const uint32_t j = static_cast<uint32_t>(__ffs(t)) - 1u;
+      t &= t - 1;
+      if (slot < kRoundValues) {
+        const uint32_t q = j + 1u;  // offset of the first of the 4 bytes inside the 20-byte strip
+        const uint32_t x = __funnelshift_r(win[q >> 2], win[(q >> 2) + 1u], 8u * (q & 3u));  // (q = 16: shift 0, the upper word is not used)
+        const uint32_t t3 = (c32 >> (13u + j)) & 7u;  // continuation bits of the 3 bytes before the terminator
+        const uint32_t len = 1u + static_cast<uint32_t>(__clz(static_cast<int>(~(t3 << 29))));
+        uint32_t g = x & 0x7F7F7F7Fu;
+        g = (g & 0x007F007Fu) | ((g & 0x7F007F00u) >> 1);
+        g = (g & 0x00003FFFu) | ((g & 0x3FFF0000u) >> 2);
+        out32[pad_word(slot)] = convert_word<OUT>(g >> (7u * (4u - len)));
       }
+      ++slot;
     }
   } else {
     // general path (some value of the tile is longer than 4 bytes): the tile's bytes are in shared memory behind the 16
@@ -309,7 +315,9 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
 
 __global__ void __launch_bounds__(kDecThreads, 6) k_varint_gather(DecTables T, uint8_t* pool, const uint64_t* __restrict__ gate) {
   __shared__ __align__(16) uint8_t sm_out[kGatherOutBytes];
-  __shared__ __align__(16) uint8_t sm_in[16 + kDecTileBytes + 16];  // 16 bytes before the tile, the tile, slack for word loads
+  // general path: 16 bytes before the tile, the tile, slack for word loads; fast path: a 20-byte strip per thread (+ 1 word)
+  __shared__ __align__(16) uint8_t sm_in[kDecThreads * 20 + 16];
+  static_assert(kDecThreads * 20 + 16 >= 16 + kDecTileBytes + 16, "the staged tile must fit too");
   __shared__ uint32_t scan_smem[kDecThreads / 32 + 1];
   __shared__ uint32_t edge[2 * (kDecThreads / 32)];  // last word and continuation mask of every warp's last lane
   if (gate && *gate != 0) return;  // the pool of a one-call decode turned out to be too small
