@@ -123,3 +123,14 @@ def test_constants_match_header():
                 checked += 1
                 break
     assert checked > 50, checked
+
+
+def test_cpp_mirror_header_compiles():
+    """include/tfs_codec.hpp (the C++ mirror of the reference's codec seam) and its test program compile cleanly."""
+    import shutil
+    import subprocess
+    if not shutil.which("g++"):
+        pytest.skip("no g++")
+    src = os.path.join(ROOT, "tests", "cpp", "test_codec.cpp")
+    r = subprocess.run(["g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-fsyntax-only", src], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[:2000]
