@@ -256,6 +256,8 @@ __device__ __forceinline__ bool staged_values(const uint8_t* in, uint32_t (&v)[8
   return ok;
 }
 
+constexpr uint32_t kUnskewed = 0x80000000u;  // flag in scatter_tile's return value: the bytes sit at stage + 16, not at stage + skew
+
 // fast path: every thread concatenates the varints of its 8 consecutive elements in a register window and
 // stores aligned 32-bit words
 __device__ __forceinline__ uint32_t scatter_fast(const uint32_t (&v)[8], uint8_t* stage, uint32_t skew, uint32_t* warp_tot) {
@@ -274,6 +276,15 @@ __device__ __forceinline__ uint32_t scatter_fast(const uint32_t (&v)[8], uint8_t
     const uint32_t t = warp_tot[w];
     if (w < static_cast<int>(warp_id())) wbase += t;
     total += t;
+  }
+  if (total == static_cast<uint32_t>(kVarintTile)) {
+    // every value of the tile is ONE byte (masks, segment ids, bools held as integers): the output is the low byte of
+    // each value.  Staged without the destination skew, 8 bytes per thread in one store; the flush shifts (kUnskewed).
+    uint2 w;
+    w.x = v[0] | (v[1] << 8) | (v[2] << 16) | (v[3] << 24);
+    w.y = v[4] | (v[5] << 8) | (v[6] << 16) | (v[7] << 24);
+    *reinterpret_cast<uint2*>(stage + 16u + 8u * threadIdx.x) = w;
+    return total | kUnskewed;
   }
   const uint32_t o = skew + wbase + (incl - tsum);  // byte offset of this thread's run in `stage`
   const uint32_t f0 = o & 3u;                        // bytes of the first word that belong to the thread before
@@ -364,16 +375,33 @@ __global__ void __launch_bounds__(kVarintThreads, 6) k_varint_scatter(EncTables 
   __syncthreads();
   // flush: whole 16-byte words with vector stores, the ragged head / tail bytes one by one (a neighbouring
   // tile owns the other bytes of those words and writes only its own)
+  const bool unskewed = (total & kUnskewed) != 0;
+  total &= ~kUnskewed;
   uint8_t* ga = g - skew;
   const uint32_t end = skew + total;
   const uint32_t nchunks = (end + 15u) >> 4;
-  for (uint32_t c = threadIdx.x; c < nchunks; c += kVarintThreads) {
-    const uint32_t lo = c << 4, hi = lo + 16u;
-    if (lo >= skew && hi <= end) {
-      *reinterpret_cast<uint4*>(ga + lo) = *reinterpret_cast<const uint4*>(stage + lo);
-    } else {
-      const uint32_t b0 = lo > skew ? lo : skew, b1 = hi < end ? hi : end;
-      for (uint32_t b = b0; b < b1; ++b) ga[b] = stage[b];
+  if (!unskewed) {
+    for (uint32_t c = threadIdx.x; c < nchunks; c += kVarintThreads) {
+      const uint32_t lo = c << 4, hi = lo + 16u;
+      if (lo >= skew && hi <= end) {
+        *reinterpret_cast<uint4*>(ga + lo) = *reinterpret_cast<const uint4*>(stage + lo);
+      } else {
+        const uint32_t b0 = lo > skew ? lo : skew, b1 = hi < end ? hi : end;
+        for (uint32_t b = b0; b < b1; ++b) ga[b] = stage[b];
+      }
+    }
+  } else {  // a tile of one-byte values: stream byte i sits at stage + 16 + i; shift it to the destination's 16-byte grid
+    for (uint32_t c = threadIdx.x; c < nchunks; c += kVarintThreads) {
+      const uint32_t lo = c << 4, hi = lo + 16u;
+      if (lo >= skew && hi <= end) {
+        const uint32_t s0 = lo - skew, sh = s0 & 15u;
+        const uint4 a = *reinterpret_cast<const uint4*>(stage + 16u + (s0 & ~15u));
+        const uint4 b = *reinterpret_cast<const uint4*>(stage + 32u + (s0 & ~15u));
+        *reinterpret_cast<uint4*>(ga + lo) = sh ? shift_window(a, b, sh) : a;
+      } else {
+        const uint32_t b0 = lo > skew ? lo : skew, b1 = hi < end ? hi : end;
+        for (uint32_t b = b0; b < b1; ++b) ga[b] = stage[16u + b - skew];
+      }
     }
   }
 }
