@@ -664,6 +664,37 @@ def test_pinned_buffers_take_the_chunked_copy_engine_path(codec, flags):
     roundtrip_check(codec, msgs, abi.MSG_PREDICT_REQUEST, "chunked pinned path", flags)
 
 
+def test_chunked_pinned_decode_with_bad_messages_and_prefix(codec):
+    """The chunked copy-engine path of tfs_decode_host_into (pinned wire >= 8 MB, walk reading host memory while the wire
+    is still arriving) with the gRPC prefix and with malformed messages between good ones."""
+    import torch
+    rng = np.random.default_rng(77)
+    good = [tfs.PredictResponse([("y", tfs.TensorProto(dtype=1, float_val=rng.standard_normal(1_500_000).astype(np.float32))),
+                                 ("i", tfs.TensorProto(dtype=9, int64_val=rng.integers(-3, 1 << 20, 200_000, dtype=np.int64))),
+                                 ("s", tfs.TensorProto(dtype=7, string_val=[b"abc" * 1000, b"", b"z" * 70000]))],
+                                tfs.ModelSpec("m", version=i)) for i in range(3)]
+    for flags in (0, abi.F_GRPC_PREFIX):
+        blobs = ob.encode_messages(good, abi.MSG_PREDICT_RESPONSE, flags)
+        bad1 = blobs[1][: len(blobs[1]) // 2]                      # truncated in the middle of a payload
+        bad2 = bytearray(blobs[2]); bad2[9 if flags else 4] ^= 0x07  # a damaged key near the front
+        msgs = [blobs[0], bad1, blobs[1], bytes(bad2), blobs[2]]
+        offs, lens, cur = [], [], 0
+        for b in msgs:
+            offs.append(cur)
+            lens.append(len(b))
+            cur += len(b)
+        assert cur >= (8 << 20)
+        st_o, want = ob.decode_bytes(msgs, abi.MSG_PREDICT_RESPONSE, flags)
+        pwire = torch.empty(cur, dtype=torch.uint8).pin_memory()
+        pwire.numpy()[:] = np.frombuffer(b"".join(msgs), dtype=np.uint8)
+        ppool = torch.zeros(cur * 2 + 4096, dtype=torch.uint8).pin_memory()
+        d = codec.decoder().decode_host_into(pwire.numpy(), offs, lens, abi.MSG_PREDICT_RESPONSE, ppool.numpy(), flags)
+        assert d.status == st_o == abi.TFS_ERR_BATCH
+        helpers.assert_same_decoded(want, d.messages(), "response", f"chunked pinned decode, flags {flags}")
+        assert [m.status for m in d.messages()] == [m.status for m in want]
+        d.close()
+
+
 def test_config_c2_batched_unaligned(codec):
     x = workloads.c2_payload(batch=4)
     msgs = [workloads.c2_request(x, v, batch=4) for v in ("float_val", "tensor_content", "float_val")]
