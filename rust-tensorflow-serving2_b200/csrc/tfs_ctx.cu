@@ -167,7 +167,14 @@ tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx) {
   if (ctx->h_up) cudaFreeHost(ctx->h_up);
   if (ctx->h_down) cudaFreeHost(ctx->h_down);
   if (ctx->h_slab) cudaFreeHost(ctx->h_slab);
+  if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
   for (cudaEvent_t e : ctx->pipe_events) cudaEventDestroy(e);
+  for (cudaEvent_t e : ctx->prof_pool) cudaEventDestroy(e);
+  for (auto& open : ctx->prof_open)
+    for (auto& pr : open) {
+      cudaEventDestroy(pr.first);
+      cudaEventDestroy(pr.second);
+    }
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
