@@ -120,3 +120,22 @@ def test_encode_rejects_a_misaligned_varint_source(codec):
     got = codec.encoder().encode(built, abi.MSG_TENSOR_PROTO).all_bytes()[0]
     raw = f.cpu().numpy().tobytes()[1: 1 + 240]
     assert got == bytes.fromhex("08012af001") + raw
+
+
+def test_encode_into_a_too_small_buffer_writes_nothing(codec):
+    """dst_capacity one byte short: TFS_ERR_NOMEM, and not a single byte of (or around) the buffer is touched - the
+    framing, varint, string and copy kernels are all gated on the layout kernel's overflow flag."""
+    import torch
+    enc = codec.encoder()
+    for name, kind, msgs in _cases():
+        dev_msgs = workloads.to_device(msgs, kind, torch.device("cuda:0"))
+        built = tfs.build_batch(dev_msgs, kind)
+        total = enc.encode(built, kind, 0).total
+        buf = torch.full((GUARD + total + GUARD,), CANARY, dtype=torch.uint8, device="cuda:0")
+        with pytest.raises(tfs.TfsError) as e:
+            enc.encode(built, kind, 0, dst=buf[GUARD: GUARD + total - 1])
+        assert e.value.status == abi.TFS_ERR_NOMEM, name
+        codec.ctx.sync()
+        assert bool((buf == CANARY).all()), f"{name}: bytes were written although the buffer was too small"
+        # the context is fine afterwards
+        assert enc.encode(built, kind, 0).all_bytes() == ob.encode_messages(msgs, kind)
