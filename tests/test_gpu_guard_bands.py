@@ -139,3 +139,27 @@ def test_encode_into_a_too_small_buffer_writes_nothing(codec):
         assert bool((buf == CANARY).all()), f"{name}: bytes were written although the buffer was too small"
         # the context is fine afterwards
         assert enc.encode(built, kind, 0).all_bytes() == ob.encode_messages(msgs, kind)
+
+
+def test_decode_into_a_too_small_pool_writes_nothing(codec):
+    import torch
+    dec = codec.decoder()
+    for name, kind, msgs in _cases():
+        if kind == abi.MSG_INPUT:
+            continue
+        blobs = ob.encode_messages(msgs, kind)
+        offs, lens, cur = [], [], 0
+        for b in blobs:
+            offs.append(cur)
+            lens.append(len(b))
+            cur += len(b)
+        wire = torch.from_numpy(np.frombuffer(b"".join(blobs), dtype=np.uint8).copy()).cuda()
+        d0 = dec.scan(wire, offs, lens, kind)
+        need = d0.pool_bytes
+        d0.close()
+        buf = torch.full((GUARD + need + GUARD,), CANARY, dtype=torch.uint8, device="cuda:0")
+        with pytest.raises(tfs.TfsError) as e:
+            dec.decode_into(wire, offs, lens, kind, buf[GUARD: GUARD + need - 64])
+        assert e.value.status == abi.TFS_ERR_NOMEM, name
+        codec.ctx.sync()
+        assert bool((buf == CANARY).all()), f"{name}: values were written although the pool was too small"
