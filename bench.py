@@ -434,6 +434,16 @@ def other_configs(codec, dev, peak):
         msgs, abi.MSG_PREDICT_RESPONSE, 0, decode_only=True)
     del msgs
 
+    # C1: the half_plus_two request (63 wire bytes), a large batch of copies: latency / descriptor bound by construction
+    x3 = torch.tensor([1.0, 2.0, 5.0], device=dev)
+    c1 = [tfs.PredictRequest(tfs.ModelSpec("half_plus_two", signature_name="serving_default"),
+                             [("x", tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=tfs.TensorShapeProto([3]), float_val=x3))]) for _ in range(16384)]
+    r1 = measure(c1, abi.MSG_PREDICT_REQUEST, 12 * 16384, reps=3)
+    r1["encode_msgs_per_s"] = round(16384 / (r1["encode_ms"] * 1e-3))
+    r1["decode_msgs_per_s"] = round(16384 / (r1["decode_ms"] * 1e-3))
+    out["C1 half_plus_two PredictRequest (63 B), 16 384 copies in one batch"] = r1
+    del c1
+
     # DT_STRING tensors (string_val): encoded images, and short tokens
     def string_requests(n_req, n_str, lo, hi):
         msgs, in_bytes = [], 0
