@@ -555,6 +555,7 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
   c->filters.resize(b->n_filters);
   std::vector<uint64_t> field_bound(b->n_fields, 0);
   std::vector<uint8_t> tensor_used(b->n_tensors, 0), field_used(b->n_fields, 0);
+  c->strings.reserve(64ull * b->n_msgs + 16ull * b->n_tensors + 16ull * b->n_filters);
   for (uint32_t i = 0; i < b->n_filters; ++i) c->filters[i] = add_str(*c, b->filters[i]);
   uint32_t vtiles = 0;
   const uint32_t prefix = (flags & TFS_F_GRPC_PREFIX) ? 5u : 0u;
@@ -631,8 +632,9 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
         bound += field_bound[fi] + 16;
       }
       // prost emits in ascending field number: order this tensor's fields by kind
-      std::stable_sort(c->fields.begin() + t.first_field, c->fields.begin() + t.first_field + t.n_fields,
-                       [](const EncField& x, const EncField& y) { return x.kind < y.kind; });
+      if (t.n_fields > 1)  // (std::stable_sort allocates a scratch buffer even for one element)
+        std::stable_sort(c->fields.begin() + t.first_field, c->fields.begin() + t.first_field + t.n_fields,
+                         [](const EncField& x, const EncField& y) { return x.kind < y.kind; });
     }
     c->bound += (flags & TFS_F_ALIGN_PAYLOAD) ? align_up(bound + 16, 16) : bound;
   }
