@@ -1020,25 +1020,28 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   } while (0)
 
   // ---- pass 1 tables: message ranges, counters, totals + per-message records (contiguous: one D2H), error words
+  // (message ranges, error words = all ones, totals = zero) are adjacent and come up in ONE host -> device copy
   size_t cur = 0;
-  const size_t o_off = carve(&cur, 8ull * n_msgs), o_len = carve(&cur, 8ull * n_msgs), o_ct = carve(&cur, 4ull * n_msgs),
+  const size_t o_off = carve(&cur, 8ull * n_msgs), o_len = carve(&cur, 8ull * n_msgs), o_err = carve(&cur, 8ull * n_msgs),
+               o_tot = carve(&cur, kTotalsBytes);
+  const size_t up_bytes = cur;
+  const size_t o_msgs = carve(&cur, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs)), o_ct = carve(&cur, 4ull * n_msgs),
                o_cf = carve(&cur, 4ull * n_msgs), o_cs = carve(&cur, 4ull * n_msgs), o_cb = carve(&cur, 4ull * n_msgs),
-               o_cv = carve(&cur, 4ull * n_msgs), o_cc = carve(&cur, 4ull * n_msgs), o_tot = carve(&cur, kTotalsBytes),
-               o_msgs = carve(&cur, sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs)), o_err = carve(&cur, 8ull * n_msgs);
-  const size_t res1_bytes = o_msgs + sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs) - o_tot;  // totals .. msgs
+               o_cv = carve(&cur, 4ull * n_msgs), o_cc = carve(&cur, 4ull * n_msgs);
+  const size_t res1_bytes = o_msgs + sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs) - o_tot;  // totals .. msgs: one D2H
   DEC_TRY(dev_reserve(ctx, &ctx->d_dec1, cur + 64));
-  DEC_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, 16ull * n_msgs + 64));
+  DEC_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, up_bytes + 64));
   uint8_t* d1 = static_cast<uint8_t*>(ctx->d_dec1.p);
-  uint64_t* h = static_cast<uint64_t*>(ctx->h_up);
-  if (n_msgs) {
-    std::memcpy(h, msg_off, 8ull * n_msgs);
-    std::memcpy(h + n_msgs, msg_len, 8ull * n_msgs);
-    // o_off and o_len are adjacent only up to alignment: two copies keep the layout simple
-    DEC_CUDA(cudaMemcpyAsync(d1 + o_off, h, 8ull * n_msgs, cudaMemcpyHostToDevice, ctx->stream));
-    DEC_CUDA(cudaMemcpyAsync(d1 + o_len, h + n_msgs, 8ull * n_msgs, cudaMemcpyHostToDevice, ctx->stream));
-    DEC_CUDA(cudaMemsetAsync(d1 + o_err, 0xFF, 8ull * n_msgs, ctx->stream));
+  {
+    uint8_t* h = static_cast<uint8_t*>(ctx->h_up);
+    if (n_msgs) {
+      std::memcpy(h + o_off, msg_off, 8ull * n_msgs);
+      std::memcpy(h + o_len, msg_len, 8ull * n_msgs);
+      std::memset(h + o_err, 0xFF, 8ull * n_msgs);
+    }
+    std::memset(h + o_tot, 0, kTotalsBytes);
+    DEC_CUDA(cudaMemcpyAsync(d1, h, up_bytes, cudaMemcpyHostToDevice, ctx->stream));
   }
-  DEC_CUDA(cudaMemsetAsync(d1 + o_tot, 0, kTotalsBytes, ctx->stream));
   T.wire = static_cast<const uint8_t*>(wire_dev);
   T.walk_wire = walk_wire_dev ? static_cast<const uint8_t*>(walk_wire_dev) : T.wire;
   T.wire_bytes = wire_bytes;
