@@ -853,66 +853,8 @@ __global__ void __launch_bounds__(kSmallBatch) k_finalize_small(DecTables T, uin
   pool_layout_body<kSmallBatch / 32>(T, n_tensors, pool_capacity, smem);
 }
 
-// host and device agree on where the result blob (tensors | filters | strings) keeps its three arrays
-__host__ __device__ inline void blob_layout(uint64_t n_tensors, uint64_t n_filters, uint64_t n_str, uint64_t* p_flt, uint64_t* p_str,
-                                            uint64_t* bytes) {
-  *p_flt = (sizeof(tfs_tensor_out_t) * n_tensors + 63u) & ~static_cast<uint64_t>(63);
-  *p_str = (*p_flt + sizeof(tfs_span_t) * n_filters + 63u) & ~static_cast<uint64_t>(63);
-  *bytes = *p_str + n_str;
-}
-
-// Small batches, planned optimistically: pass-1 walk, the scans, and - when the tables the host laid out from its
-// hints are large enough - the zeroing of the tensor records and the pass-2 walk, all in ONE single-CTA launch.
-// The second walk then runs out of warm caches, and a batch without varint bodies is finalized here too: one host
-// synchronisation per decode instead of two.  totals[TOT_RETRY] = 1 asks the host for larger tables.
-static_assert(sizeof(tfs_tensor_out_t) % 8 == 0, "tensor records are zeroed with 8-byte stores");
-__global__ void __launch_bounds__(kSmallBatch) k_plan_small(DecTables T, uint64_t blob_cap, uint32_t tensor_cap, uint32_t span_cap,
-                                                            uint64_t pool_capacity) {
-  __shared__ uint64_t smem[kSmallBatch / 32 + 1];
-  const uint32_t mi = threadIdx.x;
-  long long clk[7];
-  clk[0] = clock64();
-  if (mi < T.n_msgs) walk_body<false>(T, mi);
-  clk[1] = clock64();
-  __syncthreads();
-  scan_counts_body<kSmallBatch / 32>(T, smem);
-  __syncthreads();
-  clk[2] = clock64();
-  const uint64_t n_tensors = T.totals[TOT_TENSORS], n_filters = T.totals[TOT_FILTERS], n_spans = T.totals[TOT_SPANS],
-                 n_str = T.totals[TOT_STR], n_vt = T.totals[TOT_VTILES];
-  uint64_t p_flt, p_str, bytes;
-  blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &bytes);
-  if (bytes > blob_cap || n_tensors > tensor_cap || n_spans > span_cap) {
-    if (mi == 0) T.totals[TOT_RETRY] = 1;
-    return;
-  }
-  DecTables L = T;
-  uint8_t* blob = reinterpret_cast<uint8_t*>(T.tensors);
-  L.filters = reinterpret_cast<tfs_span_t*>(blob + p_flt);
-  L.strings = blob + p_str;
-  unsigned long long* z = reinterpret_cast<unsigned long long*>(blob);
-  for (uint64_t i = mi, n = n_tensors * (sizeof(tfs_tensor_out_t) / 8); i < n; i += kSmallBatch) z[i] = 0ull;
-  __syncthreads();
-  clk[3] = clock64();
-  if (mi < L.n_msgs) walk_body<true>(L, mi);
-  clk[4] = clock64();
-  if (n_vt == 0) {  // (with varint bodies the element totals are only known after K4a / K4b)
-    if (mi < L.n_msgs) finalize_body(L, mi);
-    __syncthreads();
-    clk[5] = clock64();
-    pool_layout_body<kSmallBatch / 32>(L, static_cast<uint32_t>(n_tensors), pool_capacity, smem);
-  } else {
-    clk[5] = clk[4];
-  }
-  clk[6] = clock64();
-  if (mi == 0)
-    for (int k = 0; k < 6; ++k) T.totals[TOT_CLK0 + k] = static_cast<uint64_t>(clk[k + 1] - clk[k]);
-}
-
-// at decode time: bind every copy-class span to its place in the caller's pool
-__global__ void __launch_bounds__(256) k_dec_bind(DecTables T, uint32_t n_spans, uint8_t* pool, const uint64_t* __restrict__ gate) {
-  const uint32_t si = blockIdx.x * blockDim.x + threadIdx.x;
-  if (si >= n_spans || (gate && *gate != 0)) return;
+// at decode time: bind one copy-class span / string element to its place in the caller's pool
+__device__ void bind_span(const DecTables& T, uint32_t si, uint8_t* pool) {
   const DecSpan& s = T.spans[si];
   CopySeg g;
   g.first_tile = T.span_ctile0[si];
@@ -953,6 +895,74 @@ __global__ void __launch_bounds__(256) k_dec_bind(DecTables T, uint32_t n_spans,
   T.segs[si] = g;
 }
 
+// host and device agree on where the result blob (tensors | filters | strings) keeps its three arrays
+__host__ __device__ inline void blob_layout(uint64_t n_tensors, uint64_t n_filters, uint64_t n_str, uint64_t* p_flt, uint64_t* p_str,
+                                            uint64_t* bytes) {
+  *p_flt = (sizeof(tfs_tensor_out_t) * n_tensors + 63u) & ~static_cast<uint64_t>(63);
+  *p_str = (*p_flt + sizeof(tfs_span_t) * n_filters + 63u) & ~static_cast<uint64_t>(63);
+  *bytes = *p_str + n_str;
+}
+
+// Small batches, planned optimistically: pass-1 walk, the scans, and - when the tables the host laid out from its
+// hints are large enough - the zeroing of the tensor records and the pass-2 walk, all in ONE single-CTA launch.
+// The second walk then runs out of warm caches, and a batch without varint bodies is finalized here too: one host
+// synchronisation per decode instead of two.  totals[TOT_RETRY] = 1 asks the host for larger tables.
+static_assert(sizeof(tfs_tensor_out_t) % 8 == 0, "tensor records are zeroed with 8-byte stores");
+__global__ void __launch_bounds__(kSmallBatch) k_plan_small(DecTables T, uint64_t blob_cap, uint32_t tensor_cap, uint32_t span_cap,
+                                                            uint64_t pool_capacity, uint8_t* pool) {
+  __shared__ uint64_t smem[kSmallBatch / 32 + 1];
+  const uint32_t mi = threadIdx.x;
+  long long clk[7];
+  clk[0] = clock64();
+  if (mi < T.n_msgs) walk_body<false>(T, mi);
+  clk[1] = clock64();
+  __syncthreads();
+  scan_counts_body<kSmallBatch / 32>(T, smem);
+  __syncthreads();
+  clk[2] = clock64();
+  const uint64_t n_tensors = T.totals[TOT_TENSORS], n_filters = T.totals[TOT_FILTERS], n_spans = T.totals[TOT_SPANS],
+                 n_str = T.totals[TOT_STR], n_vt = T.totals[TOT_VTILES];
+  uint64_t p_flt, p_str, bytes;
+  blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &bytes);
+  if (bytes > blob_cap || n_tensors > tensor_cap || n_spans > span_cap) {
+    if (mi == 0) T.totals[TOT_RETRY] = 1;
+    return;
+  }
+  DecTables L = T;
+  uint8_t* blob = reinterpret_cast<uint8_t*>(T.tensors);
+  L.filters = reinterpret_cast<tfs_span_t*>(blob + p_flt);
+  L.strings = blob + p_str;
+  unsigned long long* z = reinterpret_cast<unsigned long long*>(blob);
+  for (uint64_t i = mi, n = n_tensors * (sizeof(tfs_tensor_out_t) / 8); i < n; i += kSmallBatch) z[i] = 0ull;
+  __syncthreads();
+  clk[3] = clock64();
+  if (mi < L.n_msgs) walk_body<true>(L, mi);
+  clk[4] = clock64();
+  if (n_vt == 0) {  // (with varint bodies the element totals are only known after K4a / K4b)
+    if (mi < L.n_msgs) finalize_body(L, mi);
+    __syncthreads();
+    clk[5] = clock64();
+    pool_layout_body<kSmallBatch / 32>(L, static_cast<uint32_t>(n_tensors), pool_capacity, smem);
+    if (pool) {  // one-call decode: the copy segments are bound here too (saves the k_dec_bind launch)
+      __syncthreads();
+      if (L.totals[TOT_OVERFLOW] == 0)
+        for (uint32_t si = mi, n = static_cast<uint32_t>(L.totals[TOT_SPANS]); si < n; si += kSmallBatch) bind_span(L, si, pool);
+    }
+  } else {
+    clk[5] = clk[4];
+  }
+  clk[6] = clock64();
+  if (mi == 0)
+    for (int k = 0; k < 6; ++k) T.totals[TOT_CLK0 + k] = static_cast<uint64_t>(clk[k + 1] - clk[k]);
+}
+
+// at decode time: bind every copy-class span to its place in the caller's pool
+__global__ void __launch_bounds__(256) k_dec_bind(DecTables T, uint32_t n_spans, uint8_t* pool, const uint64_t* __restrict__ gate) {
+  const uint32_t si = blockIdx.x * blockDim.x + threadIdx.x;
+  if (si >= n_spans || (gate && *gate != 0)) return;
+  bind_span(T, si, pool);
+}
+
 // =====================================================================================================
 // host orchestration
 // =====================================================================================================
@@ -963,10 +973,11 @@ size_t carve(size_t* cur, size_t bytes, size_t align = 64) {
 }
 
 // value kernels: bind the copy spans to the pool, gather the varint spans, copy the bulk spans
-tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const uint64_t* gate, const std::vector<HostSeg>* host_segs = nullptr) {
+tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const uint64_t* gate, const std::vector<HostSeg>* host_segs = nullptr,
+                           bool spans_bound = false) {
   const DecTables& T = dec->T;
   const uint64_t n_spans = dec->totals[TOT_SPANS], n_vt = dec->totals[TOT_VTILES], n_ct = dec->totals[TOT_CTILES];
-  if (n_spans) {
+  if (n_spans && !spans_bound) {
     k_dec_bind<<<static_cast<uint32_t>((n_spans + 255) / 256), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), pool, gate);
     ctx->launches++;
   }
@@ -1101,7 +1112,8 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       {
         ProfScope prof(ctx, PK_WALK);
         k_plan_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, blob_cap, static_cast<uint32_t>(std::min<uint64_t>(t_cap, 0xFFFFFFF0ull)),
-                                                        static_cast<uint32_t>(std::min<uint64_t>(s_cap, 0xFFFFFFF0ull)), pool_cap_arg);
+                                                        static_cast<uint32_t>(std::min<uint64_t>(s_cap, 0xFFFFFFF0ull)), pool_cap_arg,
+                                                        static_cast<uint8_t*>(pool_dev));
       }
       ctx->launches++;
       DEC_CUDA(cudaGetLastError());
@@ -1242,7 +1254,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   } else if (pool_dev && !dec->totals[TOT_OVERFLOW]) {
     // planned: the host already knows the layout, the value kernels need no gate
     DEC_TRY(fetch_host_segs());
-    DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), nullptr, hsegs.empty() ? nullptr : &hsegs));
+    DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), nullptr, hsegs.empty() ? nullptr : &hsegs, true));
   }
 
   // ---- results to the host: (totals | msgs) and the blob (tensors | filters | strings)

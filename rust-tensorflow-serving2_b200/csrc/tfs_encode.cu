@@ -794,7 +794,8 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   T.n_rfields = static_cast<uint32_t>(c.rfield_index.size());
   T.n_rtiles = n_rtiles;
   T.n_routs = n_routs;
-  TFS_CUDA(ctx, cudaMemsetAsync(T.result, 0, 32, ctx->stream));
+  // result[0..1] are always written by the layout kernel; result[2] ("ragged offsets invalid") only accumulates
+  if (n_rtiles) TFS_CUDA(ctx, cudaMemsetAsync(T.result, 0, 32, ctx->stream));
   T.n_msgs = n_msgs;
   T.n_tensors = n_tensors;
   T.n_fields = static_cast<uint32_t>(c.fields.size());
@@ -873,7 +874,7 @@ tfs_status_t fetch_results(tfs_ctx* ctx, const EncTables& T, uint64_t* msg_off_o
   const uint64_t* res = reinterpret_cast<const uint64_t*>(h + o_res);
   if (total_out) *total_out = res[0];
   *overflow = res[1] != 0;
-  if (res[2] != 0) return set_err(ctx, TFS_ERR_INVALID_ARG, "string_val: the offsets in memory are not ascending from 0 to the stated total (aux)");
+  if (T.n_rtiles && res[2] != 0) return set_err(ctx, TFS_ERR_INVALID_ARG, "string_val: the offsets in memory are not ascending from 0 to the stated total (aux)");
   return TFS_OK;
 }
 
