@@ -105,6 +105,7 @@ struct Walker {
   uint32_t cur = 0;
   uint32_t cur_dims = 0;
   uint32_t content_span = 0xFFFFFFFFu;
+  uint64_t tend = 0;  // end of the TensorProto being merged (the limit of its merge loop)
 
   // 16-byte window over the wire: header bytes are read through it, one aligned vector load per 16 bytes
   // instead of one dependent byte load per byte (the walk is a chain of dependent reads)
@@ -466,6 +467,33 @@ struct Walker {
         if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
         add_span(slot_of(8), SC_STR, pos, len, 1, 1);
         pos += len;
+        // A string tensor is a run of these.  While the next field is another string_val with a one-byte length
+        // that stays inside the tensor, take it here: the same bookkeeping as above without a trip through the
+        // key / wire-type / field dispatch per element.  Anything else (and every error) is left to the general path.
+        while (pos + 2 <= tend && byte_at(pos) == 0x42) {
+          const uint32_t l = byte_at(pos + 1);
+          if (l >= 0x80u || l > tend - (pos + 2)) break;
+          if (FILL) {
+            DecSpan s;
+            s.wire_off = pos + 2;
+            s.len = l;
+            s.elem_base = 0;
+            s.n_elems = 1;
+            s.tensor = cur;
+            s.slot = slot_of(8);
+            s.msg = msg;
+            s.cls = SC_STR;
+            s.first_tile = n_ct;
+            s.elem_tile0 = n_vt;
+            T.spans[n_spans] = s;
+            T.span_vtile0[n_spans] = n_vt;
+            T.span_ctile0[n_spans] = n_ct;
+          }
+          n_spans++;
+          n_generic += l != 0;
+          n_ct += (l != 0) + 1u;  // as add_span counts a span shorter than a copy tile
+          pos += 2 + l;
+        }
         return true;
       }
       case 14: case 15: return fail(TFS_ERR_UNSUPPORTED);  // resource_handle_val / variant_val: left to prost
@@ -476,6 +504,7 @@ struct Walker {
     if (!check_wt(WT_LEN, wt)) return false;
     uint64_t rend;
     if (!loop_begin(&rend)) return false;
+    tend = rend;
     while (pos < rend) {
       uint32_t t2, w2;
       if (!key(&t2, &w2)) return false;
@@ -565,7 +594,10 @@ struct Walker {
       pos = beg + 5;
     }
     const uint64_t body = pos;
-    if (T.msg_kind == TFS_MSG_TENSOR_PROTO) begin_tensor();
+    if (T.msg_kind == TFS_MSG_TENSOR_PROTO) {
+      begin_tensor();
+      tend = end;
+    }
     while (pos < end) {
       uint32_t tag, wt;
       if (!key(&tag, &wt)) return false;
@@ -781,15 +813,49 @@ __device__ void finalize_body(const DecTables& T, uint32_t mi) {
   const uint32_t s1 = mi + 1 < T.n_msgs ? T.cnt_spans[mi + 1] : static_cast<uint32_t>(T.totals[TOT_SPANS]);
   // tensor_pool[] doubles as the running byte count of each tensor's string_val elements until it is assigned below
   for (uint32_t ti = mo.first_tensor; ti < mo.first_tensor + mo.n_tensors; ++ti) T.tensor_pool[ti] = 0;
-  for (uint32_t si = s0; si < s1; ++si) {
-    DecSpan& s = T.spans[si];
-    tfs_tensor_out_t& t = T.tensors[s.tensor];
-    s.elem_base = t.n_elems[s.slot];
-    t.n_elems[s.slot] += s.n_elems;
-    if (s.cls == SC_STR) {
-      s.elem_tile0 = T.tensor_pool[s.tensor];
-      T.tensor_pool[s.tensor] += s.len;
+  // A run of spans of one (tensor, slot) - every element of a string_val, every chunk of a packed field - keeps its
+  // running counts in registers: a round trip through global memory per span would make each iteration wait for the last.
+  uint32_t run_tensor = ~0u, run_slot = 0;
+  uint64_t run_elems = 0, run_str = 0;
+  constexpr uint32_t kAhead = 4;  // spans whose fields are loaded before the first of them is used
+  uint32_t nx_tensor[kAhead], nx_slot[kAhead];
+  uint64_t nx_n[kAhead], nx_len[kAhead];
+  for (uint32_t sb = s0; sb < s1; sb += kAhead) {
+#pragma unroll
+    for (uint32_t j = 0; j < kAhead; ++j) {
+      const DecSpan& q = T.spans[min(sb + j, s1 - 1)];
+      nx_tensor[j] = q.tensor;
+      nx_slot[j] = q.slot;
+      nx_n[j] = q.n_elems;
+      nx_len[j] = q.len;
     }
+#pragma unroll
+    for (uint32_t j = 0; j < kAhead; ++j) {
+      const uint32_t si = sb + j;
+      if (si >= s1) break;
+      DecSpan& s = T.spans[si];
+      const uint32_t st = nx_tensor[j], ss = nx_slot[j];
+      if (st != run_tensor || ss != run_slot) {
+        if (run_tensor != ~0u) {
+          T.tensors[run_tensor].n_elems[run_slot] = run_elems;
+          if (run_slot == 4) T.tensor_pool[run_tensor] = run_str;
+        }
+        run_tensor = st;
+        run_slot = ss;
+        run_elems = T.tensors[st].n_elems[ss];
+        run_str = ss == 4 ? T.tensor_pool[st] : 0;
+      }
+      s.elem_base = run_elems;
+      run_elems += nx_n[j];
+      if (ss == 4) {  // string_val: the only slot whose spans are SC_STR
+        s.elem_tile0 = run_str;
+        run_str += nx_len[j];
+      }
+    }
+  }
+  if (run_tensor != ~0u) {
+    T.tensors[run_tensor].n_elems[run_slot] = run_elems;
+    if (run_slot == 4) T.tensor_pool[run_tensor] = run_str;
   }
   for (uint32_t ti = mo.first_tensor; ti < mo.first_tensor + mo.n_tensors; ++ti) {
     tfs_tensor_out_t& t = T.tensors[ti];

@@ -386,6 +386,41 @@ def test_decode_long_varint_runs_inside_big_span(codec):
         assert got[0].status == abi.TFS_ERR_INVALID_VARINT and got[1].status == 0
 
 
+def test_string_run_edges_decode_like_the_oracle(codec):
+    """The walk takes a run of string_val elements with one-byte lengths in a tight loop; whatever ends the run - the
+    tensor's end, a longer length, another field, an element that overshoots the tensor - goes the general way and
+    must come out exactly as prost has it."""
+    el = lambda b: b"\x42" + helpers_varint(len(b)) + b  # noqa: E731
+    run = b"".join(el(bytes([65 + i]) * i) for i in range(20))
+    def entry(tensor, key=b"k"):
+        body = b"\x0a" + helpers_varint(len(key)) + key + b"\x12" + helpers_varint(len(tensor)) + tensor
+        return b"\x12" + helpers_varint(len(body)) + body
+    tensors = [
+        b"\x08\x07" + run,                                              # the run ends with the tensor
+        b"\x08\x07" + run + b"\x42",                                    # a key with nothing behind it
+        b"\x08\x07" + run + b"\x42\x05ab",                               # the last element overshoots
+        b"\x08\x07" + run + el(b"x" * 127) + el(b"y" * 128) + el(b"z" * 3),  # a two-byte length inside the run
+        b"\x08\x07" + run + b"\x42\x80\x00" + el(b"after"),              # a non-canonical zero length
+        b"\x08\x07" + run + b"\x3a\x02\x01\x02" + run,                   # another field between two runs
+        b"\x08\x07" + run + b"\x45\x00\x00\x00\x00",                    # field 8 with a wrong wire type
+        run[:-3],                                                        # cut inside the last element
+    ]
+    st, got = gpu_decode_both(codec, tensors, abi.MSG_TENSOR_PROTO)
+    st_o, want = ob.decode_bytes(tensors, abi.MSG_TENSOR_PROTO)
+    assert [m.status for m in got] == [m.status for m in want]
+    helpers.assert_same_decoded(want, got, "tensor", "string run edges (tensor)")
+    assert [m.status for m in got][:2] == [0, abi.TFS_ERR_INVALID_VARINT]
+    # inside a request: what follows the tensor begins with the same byte (an unknown field 8 of the request), and an
+    # element that overshoots its tensor but not the request is "delimited length exceeded"
+    reqs = [entry(t) + b"\x42\x02hi" + entry(tensors[0], b"second") + b"\x1a\x01f" for t in tensors]
+    reqs.append(entry(b"\x08\x07" + run + b"\x42\x05ab") + b"\x42\x03abc")
+    st, got = gpu_decode_both(codec, reqs, abi.MSG_PREDICT_REQUEST)
+    st_o, want = ob.decode_bytes(reqs, abi.MSG_PREDICT_REQUEST)
+    assert [m.status for m in got] == [m.status for m in want]
+    helpers.assert_same_decoded(want, got, "request", "string run edges (request)")
+    assert got[0].status == 0 and got[-1].status == abi.TFS_ERR_LENGTH_EXCEEDED
+
+
 def helpers_varint(v):
     out = bytearray()
     while v >= 0x80:
