@@ -470,29 +470,55 @@ struct Walker {
         // A string tensor is a run of these.  While the next field is another string_val with a one-byte length
         // that stays inside the tensor, take it here: the same bookkeeping as above without a trip through the
         // key / wire-type / field dispatch per element.  Anything else (and every error) is left to the general path.
-        while (pos + 2 <= tend && byte_at(pos) == 0x42) {
-          const uint32_t l = byte_at(pos + 1);
-          if (l >= 0x80u || l > tend - (pos + 2)) break;
-          if (FILL) {
-            DecSpan s;
-            s.wire_off = pos + 2;
-            s.len = l;
-            s.elem_base = 0;
-            s.n_elems = 1;
-            s.tensor = cur;
-            s.slot = slot_of(8);
-            s.msg = msg;
-            s.cls = SC_STR;
-            s.first_tile = n_ct;
-            s.elem_tile0 = n_vt;
-            T.spans[n_spans] = s;
-            T.span_vtile0[n_spans] = n_vt;
-            T.span_ctile0[n_spans] = n_ct;
+        // The loop keeps what it touches in registers: the walker itself lives in local memory (its methods are
+        // real calls), and with one or two warps per batch every instruction of this chain is paid in full.
+        {
+          static_assert(sizeof(DecSpan) == 64 && offsetof(DecSpan, elem_base) == 16 && offsetof(DecSpan, tensor) == 32 &&
+                        offsetof(DecSpan, first_tile) == 48, "string spans are written as four 16-byte stores");
+          const uint64_t wa = reinterpret_cast<uintptr_t>(w), te = tend;
+          uint64_t p = pos, lwb = win_base;
+          uint4 lw = win;
+          uint32_t ns = n_spans, ng = n_generic, nc = n_ct;
+          const uint32_t nv = n_vt;
+          const uint4 ids = make_uint4(cur, slot_of(8), msg, SC_STR);
+          uint4* const spans = reinterpret_cast<uint4*>(T.spans);
+          uint32_t* const sv = T.span_vtile0;
+          uint32_t* const sc = T.span_ctile0;
+          auto rd = [&](uint64_t off) -> uint32_t {  // byte_at() on the local copy of the window
+            const uint64_t a = wa + off, base = a & ~static_cast<uint64_t>(15);
+            if (base != lwb) {
+              lw = *reinterpret_cast<const uint4*>(base);
+              lwb = base;
+            }
+            const uint32_t k = static_cast<uint32_t>(a >> 2) & 3u;
+            const uint32_t word = k == 0 ? lw.x : k == 1 ? lw.y : k == 2 ? lw.z : lw.w;
+            return (word >> ((static_cast<uint32_t>(a) & 3u) * 8u)) & 0xFFu;
+          };
+          while (p + 2 <= te) {
+            if (rd(p) != 0x42u) break;
+            const uint32_t l = rd(p + 1);
+            if (l >= 0x80u || l > te - (p + 2)) break;
+            if (FILL) {
+              const uint64_t off = p + 2;
+              uint4* d = spans + 4ull * ns;
+              d[0] = make_uint4(static_cast<uint32_t>(off), static_cast<uint32_t>(off >> 32), l, 0u);  // wire_off, len
+              d[1] = make_uint4(0u, 0u, 1u, 0u);                                                     // elem_base, n_elems
+              d[2] = ids;                                                                            // tensor, slot, msg, cls
+              d[3] = make_uint4(nc, 0u, nv, 0u);                                                     // first_tile, elem_tile0
+              sv[ns] = nv;
+              sc[ns] = nc;
+            }
+            ns++;
+            ng += l != 0;
+            nc += (l != 0) + 1u;  // as add_span counts a span shorter than a copy tile
+            p += 2 + l;
           }
-          n_spans++;
-          n_generic += l != 0;
-          n_ct += (l != 0) + 1u;  // as add_span counts a span shorter than a copy tile
-          pos += 2 + l;
+          pos = p;
+          win = lw;
+          win_base = lwb;
+          n_spans = ns;
+          n_generic = ng;
+          n_ct = nc;
         }
         return true;
       }
