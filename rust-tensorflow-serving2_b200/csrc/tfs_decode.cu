@@ -484,19 +484,26 @@ struct Walker {
           uint4* const spans = reinterpret_cast<uint4*>(T.spans);
           uint32_t* const sv = T.span_vtile0;
           uint32_t* const sc = T.span_ctile0;
-          auto rd = [&](uint64_t off) -> uint32_t {  // byte_at() on the local copy of the window
+          // word `k` of the window without a branch (the lanes of a warp sit at different offsets: a branch per
+          // word would run all four arms one after the other)
+          auto word_of = [&](uint32_t k) -> uint32_t {
+            const uint32_t s01 = 0x3210u + (k & 1u) * 0x4444u;
+            return __byte_perm(__byte_perm(lw.x, lw.y, s01), __byte_perm(lw.z, lw.w, s01), 0x3210u + (k >> 1) * 0x4444u);
+          };
+          // the (up to) four bytes at `off`, through the local copy of the window; bytes beyond the window are junk
+          auto rd4 = [&](uint64_t off) -> uint32_t {
             const uint64_t a = wa + off, base = a & ~static_cast<uint64_t>(15);
             if (base != lwb) {
               lw = *reinterpret_cast<const uint4*>(base);
               lwb = base;
             }
             const uint32_t k = static_cast<uint32_t>(a >> 2) & 3u;
-            const uint32_t word = k == 0 ? lw.x : k == 1 ? lw.y : k == 2 ? lw.z : lw.w;
-            return (word >> ((static_cast<uint32_t>(a) & 3u) * 8u)) & 0xFFu;
+            return __funnelshift_r(word_of(k), word_of(min(k + 1u, 3u)), (static_cast<uint32_t>(a) & 3u) * 8u);
           };
           while (p + 2 <= te) {
-            if (rd(p) != 0x42u) break;
-            const uint32_t l = rd(p + 1);
+            const uint32_t kl = rd4(p);  // key byte, length byte
+            if ((kl & 0xFFu) != 0x42u) break;
+            const uint32_t l = ((wa + p) & 15u) != 15u ? (kl >> 8) & 0xFFu : rd4(p + 1) & 0xFFu;
             if (l >= 0x80u || l > te - (p + 2)) break;
             if (FILL) {
               const uint64_t off = p + 2;
@@ -945,10 +952,21 @@ __global__ void __launch_bounds__(kSmallBatch) k_finalize_small(DecTables T, uin
   pool_layout_body<kSmallBatch / 32>(T, n_tensors, pool_capacity, smem);
 }
 
-// at decode time: bind one copy-class span / string element to its place in the caller's pool
-__device__ void bind_span(const DecTables& T, uint32_t si, uint8_t* pool) {
-  const DecSpan& s = T.spans[si];
+// at decode time: bind one copy-class span / string element to its place in the caller's pool.  In two steps, all the
+// loads and then all the stores, so that a caller with several spans in hand can have their loads in flight together.
+struct SpanBinding {
   CopySeg g;
+  uint64_t* off_slot;  // string element: where its start offset goes (nullptr otherwise) ...
+  uint64_t* end_slot;  // ... and, for the last element of a string_val, where the total goes
+  uint64_t off_value, end_value;
+};
+__device__ __forceinline__ SpanBinding bind_prepare(const DecTables& T, uint32_t si, uint8_t* pool) {
+  const DecSpan& s = T.spans[si];
+  SpanBinding b;
+  b.off_slot = nullptr;
+  b.end_slot = nullptr;
+  b.off_value = b.end_value = 0;
+  CopySeg& g = b.g;
   g.first_tile = T.span_ctile0[si];
   g.src = T.wire + s.wire_off;
   g.dst = nullptr;
@@ -971,21 +989,29 @@ __device__ void bind_span(const DecTables& T, uint32_t si, uint8_t* pool) {
       g.dst = pool + t.dst_off[s.slot] + s.elem_base * type_size_dev(ty);
     }
   } else if (s.cls == SC_STR && T.msgs[s.msg].status == TFS_OK) {
-    // one string_val element: its start offset into the offsets array (byte stores: the pool may sit at any address),
-    // its bytes behind the offsets
+    // one string_val element: its start offset into the offsets array (the pool is 16-byte aligned and slots start
+    // on 64-byte boundaries, so the offsets are aligned words), its bytes behind the offsets
     const tfs_tensor_out_t& t = T.tensors[s.tensor];
     const uint64_t n = t.n_elems[s.slot];
     uint8_t* block = pool + t.dst_off[s.slot];
-    auto put_u64 = [](uint8_t* p, uint64_t v) {
-      for (int i = 0; i < 8; ++i) p[i] = static_cast<uint8_t>(v >> (8 * i));
-    };
-    put_u64(block + 8 * s.elem_base, s.elem_tile0);
-    if (s.elem_base + 1 == n) put_u64(block + 8 * n, s.elem_tile0 + s.len);
+    uint64_t* offs = reinterpret_cast<uint64_t*>(block);
+    b.off_slot = offs + s.elem_base;
+    b.off_value = s.elem_tile0;
+    if (s.elem_base + 1 == n) {
+      b.end_slot = offs + n;
+      b.end_value = s.elem_tile0 + s.len;
+    }
     g.n = s.len;
     g.dst = block + 8 * (n + 1) + s.elem_tile0;
   }
-  T.segs[si] = g;
+  return b;
 }
+__device__ __forceinline__ void bind_commit(const DecTables& T, uint32_t si, const SpanBinding& b) {
+  if (b.off_slot) *b.off_slot = b.off_value;
+  if (b.end_slot) *b.end_slot = b.end_value;
+  T.segs[si] = b.g;
+}
+__device__ __forceinline__ void bind_span(const DecTables& T, uint32_t si, uint8_t* pool) { bind_commit(T, si, bind_prepare(T, si, pool)); }
 
 // host and device agree on where the result blob (tensors | filters | strings) keeps its three arrays
 __host__ __device__ inline void blob_layout(uint64_t n_tensors, uint64_t n_filters, uint64_t n_str, uint64_t* p_flt, uint64_t* p_str,
@@ -1037,8 +1063,18 @@ __global__ void __launch_bounds__(kSmallBatch) k_plan_small(DecTables T, uint64_
     pool_layout_body<kSmallBatch / 32>(L, static_cast<uint32_t>(n_tensors), pool_capacity, smem);
     if (pool) {  // one-call decode: the copy segments are bound here too (saves the k_dec_bind launch)
       __syncthreads();
-      if (L.totals[TOT_OVERFLOW] == 0)
-        for (uint32_t si = mi, n = static_cast<uint32_t>(L.totals[TOT_SPANS]); si < n; si += kSmallBatch) bind_span(L, si, pool);
+      if (L.totals[TOT_OVERFLOW] == 0) {
+        const uint32_t n = static_cast<uint32_t>(L.totals[TOT_SPANS]);
+        uint32_t si = mi;
+        for (; si + 3 * kSmallBatch < n; si += 4 * kSmallBatch) {  // four spans' loads in flight, then their stores
+          SpanBinding b[4];
+#pragma unroll
+          for (uint32_t j = 0; j < 4; ++j) b[j] = bind_prepare(L, si + j * kSmallBatch, pool);
+#pragma unroll
+          for (uint32_t j = 0; j < 4; ++j) bind_commit(L, si + j * kSmallBatch, b[j]);
+        }
+        for (; si < n; si += kSmallBatch) bind_span(L, si, pool);
+      }
     }
   } else {
     clk[5] = clk[4];
