@@ -946,7 +946,7 @@ __global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_te
 // Small batches: finalize and pool layout in ONE single-CTA launch
 __global__ void __launch_bounds__(kSmallBatch) k_finalize_small(DecTables T, uint32_t n_tensors, uint64_t pool_capacity) {
   __shared__ uint64_t smem[kSmallBatch / 32 + 1];
-  const uint32_t mi = threadIdx.x;
+  const uint32_t mi = (threadIdx.x & 31u) * (kSmallBatch / 32) + (threadIdx.x >> 5);  // dealt round the warps (k_plan_small)
   if (mi < T.n_msgs) finalize_body(T, mi);  // reads what this message's walk wrote and the counted varint spans
   __syncthreads();
   pool_layout_body<kSmallBatch / 32>(T, n_tensors, pool_capacity, smem);
@@ -1030,9 +1030,12 @@ __global__ void __launch_bounds__(kSmallBatch) k_plan_small(DecTables T, uint64_
                                                             uint64_t pool_capacity, uint8_t* pool) {
   __shared__ uint64_t smem[kSmallBatch / 32 + 1];
   const uint32_t mi = threadIdx.x;
+  // Per-message work (the walks, finalize) deals the messages round the warps instead of filling warp 0 first: the
+  // threads of a warp wait for each other at every load, so 64 messages walk faster as 8 warps of 8 than as 2 of 32.
+  const uint32_t mw = (threadIdx.x & 31u) * (kSmallBatch / 32) + (threadIdx.x >> 5);
   long long clk[7];
   clk[0] = clock64();
-  if (mi < T.n_msgs) walk_body<false>(T, mi);
+  if (mw < T.n_msgs) walk_body<false>(T, mw);
   clk[1] = clock64();
   __syncthreads();
   scan_counts_body<kSmallBatch / 32>(T, smem);
@@ -1054,10 +1057,10 @@ __global__ void __launch_bounds__(kSmallBatch) k_plan_small(DecTables T, uint64_
   for (uint64_t i = mi, n = n_tensors * (sizeof(tfs_tensor_out_t) / 8); i < n; i += kSmallBatch) z[i] = 0ull;
   __syncthreads();
   clk[3] = clock64();
-  if (mi < L.n_msgs) walk_body<true>(L, mi);
+  if (mw < L.n_msgs) walk_body<true>(L, mw);
   clk[4] = clock64();
   if (n_vt == 0) {  // (with varint bodies the element totals are only known after K4a / K4b)
-    if (mi < L.n_msgs) finalize_body(L, mi);
+    if (mw < L.n_msgs) finalize_body(L, mw);
     __syncthreads();
     clk[5] = clock64();
     pool_layout_body<kSmallBatch / 32>(L, static_cast<uint32_t>(n_tensors), pool_capacity, smem);
