@@ -60,6 +60,24 @@ __global__ void __launch_bounds__(256) k_dtile_bind(DecTables T, uint32_t n_vtil
   T.dtile_dst[tile] = d;
 }
 
+// continuation and validity masks of 16 loaded bytes (bit j = byte j); a chunk wholly outside the span has none
+__device__ __forceinline__ void masks_of(const uint4& d, uint64_t chunk_abs, uint64_t span_abs0, uint64_t span_end, uint32_t* cont,
+                                         uint32_t* valid) {
+  // MSB of each byte -> one bit per byte: the four isolated bits are moved to bits 24..27 by one multiply
+  // (2^24, 2^17, 2^10, 2^3 put bytes 0..3 there; no two partial products meet, so there are no carries)
+  auto msb4 = [](uint32_t x) { return ((((x >> 7) & 0x01010101u) * 0x01020408u) >> 24) & 0xFu; };
+  const uint32_t m = msb4(d.x) | (msb4(d.y) << 4) | (msb4(d.z) << 8) | (msb4(d.w) << 12);
+  uint32_t v = 0xFFFFu;
+  if (chunk_abs + 16 <= span_abs0 || chunk_abs >= span_end) {
+    v = 0;
+  } else {
+    if (chunk_abs < span_abs0) v &= 0xFFFFu << (span_abs0 - chunk_abs);
+    if (chunk_abs + 16 > span_end) v &= 0xFFFFu >> (chunk_abs + 16 - span_end);
+  }
+  *valid = v & 0xFFFFu;
+  *cont = m & *valid;
+}
+
 // 16 bytes of the tile owned by this thread: continuation mask and validity mask (bit j = byte j)
 __device__ __forceinline__ void chunk_masks(uint64_t chunk_abs, uint64_t span_abs0, uint64_t span_end, uint4* data,
                                             uint32_t* cont, uint32_t* valid) {
@@ -71,15 +89,7 @@ __device__ __forceinline__ void chunk_masks(uint64_t chunk_abs, uint64_t span_ab
   }
   const uint4 d = ld_stream16(reinterpret_cast<const void*>(chunk_abs));
   *data = d;
-  // MSB of each byte -> one bit per byte: the four isolated bits are moved to bits 24..27 by one multiply
-  // (2^24, 2^17, 2^10, 2^3 put bytes 0..3 there; no two partial products meet, so there are no carries)
-  auto msb4 = [](uint32_t x) { return ((((x >> 7) & 0x01010101u) * 0x01020408u) >> 24) & 0xFu; };
-  const uint32_t m = msb4(d.x) | (msb4(d.y) << 4) | (msb4(d.z) << 8) | (msb4(d.w) << 12);
-  uint32_t v = 0xFFFFu;
-  if (chunk_abs < span_abs0) v &= 0xFFFFu << (span_abs0 - chunk_abs);
-  if (chunk_abs + 16 > span_end) v &= 0xFFFFu >> (chunk_abs + 16 - span_end);
-  *valid = v & 0xFFFFu;
-  *cont = m & *valid;
+  masks_of(d, chunk_abs, span_abs0, span_end, cont, valid);
 }
 
 // continuation mask of the 16 bytes before this thread's chunk: the previous lane has it; lane 0 re-loads
@@ -99,25 +109,62 @@ __device__ __forceinline__ void prev_chunk(const TileRef& r, uint64_t chunk_abs,
   *pcont = pc;
 }
 
+// The kernel is bound by instruction issue, not by latency (four tiles per CTA with all loads up front measured no
+// faster), so the common case is kept short: a chunk wholly inside its span counts its terminators with one popcount
+// of the MSBs, and the exact over-long check (ten continuation bytes in a row) runs only in warps where some aligned
+// 4-byte word of a chunk, or of the chunk before it, is all continuation bytes - a run of ten covers such a word.
 __global__ void __launch_bounds__(kDecThreads) k_varint_count(DecTables T) {
+  __shared__ uint32_t warp_tail[kDecThreads / 32];  // does the last chunk of each warp hold an all-continuation word?
   const uint32_t tile = blockIdx.x;
   const TileRef r = tile_ref(T, tile);
   const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 16ull;
-  uint4 d, pd;
-  uint32_t cont, valid, prev;
-  chunk_masks(chunk_abs, r.span_abs0, r.span_end, &d, &cont, &valid);
-  prev_chunk(r, chunk_abs, d, cont, &pd, &prev);
-  uint32_t x = (cont << 16) | prev;  // bit i..i+9 all set <=> ten continuation bytes in a row
-  x &= x >> 1;
-  x &= x >> 2;
-  x &= x >> 4;
-  x &= x >> 2;
-  if (x) {
-    const uint64_t at = chunk_abs > r.span_abs0 ? chunk_abs : r.span_abs0;
-    const uint64_t off = at - reinterpret_cast<uintptr_t>(T.wire) - T.msg_off[r.msg];
-    atomicMin(&T.err[r.msg], (static_cast<unsigned long long>(off) << 8) | TFS_ERR_INVALID_VARINT);
+  const bool inside = chunk_abs >= r.span_abs0 && chunk_abs + 16 <= r.span_end;
+  const bool touches = chunk_abs + 16 > r.span_abs0 && chunk_abs < r.span_end;
+  uint4 d = make_uint4(0, 0, 0, 0);
+  if (touches) d = ld_stream16(reinterpret_cast<const void*>(chunk_abs));
+  constexpr uint32_t kMsb = 0x80808080u;
+  const uint32_t hx = d.x & kMsb, hy = d.y & kMsb, hz = d.z & kMsb, hw = d.w & kMsb;
+  // (bytes outside the span may make this true for an edge chunk: that only sends the warp to the exact check)
+  const bool own_word = hx == kMsb || hy == kMsb || hz == kMsb || hw == kMsb;
+  uint32_t cnt;
+  if (inside) {
+    cnt = 16u - __popc((hx >> 7) | (hy >> 6) | (hz >> 5) | (hw >> 4));
+  } else {  // first / last chunk of the span, or outside it
+    uint32_t cont, valid;
+    masks_of(d, chunk_abs, r.span_abs0, r.span_end, &cont, &valid);
+    cnt = __popc(~cont & valid);
   }
-  const uint32_t cnt = __reduce_add_sync(0xFFFFFFFFu, __popc(~cont & valid));
+  if (lane_id() == 31) warp_tail[threadIdx.x >> 5] = own_word;
+  __syncthreads();
+  bool prev_word = __shfl_up_sync(0xFFFFFFFFu, own_word, 1);
+  if (lane_id() == 0) {
+    if (threadIdx.x != 0) {
+      prev_word = warp_tail[(threadIdx.x >> 5) - 1] != 0;
+    } else {  // the chunk before the tile
+      prev_word = false;
+      if (chunk_abs > r.span_abs0) {
+        const uint4 p = ld_stream16(reinterpret_cast<const void*>(chunk_abs - 16));
+        prev_word = (p.x & kMsb) == kMsb || (p.y & kMsb) == kMsb || (p.z & kMsb) == kMsb || (p.w & kMsb) == kMsb;
+      }
+    }
+  }
+  if (__any_sync(0xFFFFFFFFu, own_word || prev_word)) {
+    uint4 pd;
+    uint32_t cont, valid, prev;
+    masks_of(d, chunk_abs, r.span_abs0, r.span_end, &cont, &valid);
+    prev_chunk(r, chunk_abs, d, cont, &pd, &prev);
+    uint32_t x = (cont << 16) | prev;  // bit i..i+9 all set <=> ten continuation bytes in a row
+    x &= x >> 1;
+    x &= x >> 2;
+    x &= x >> 4;
+    x &= x >> 2;
+    if (x) {
+      const uint64_t at = chunk_abs > r.span_abs0 ? chunk_abs : r.span_abs0;
+      const uint64_t off = at - reinterpret_cast<uintptr_t>(T.wire) - T.msg_off[r.msg];
+      atomicMin(&T.err[r.msg], (static_cast<unsigned long long>(off) << 8) | TFS_ERR_INVALID_VARINT);
+    }
+  }
+  cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
   if (lane_id() == 0 && cnt) atomicAdd(&T.tile_count[tile], cnt);  // tile_count[] is zeroed by the host
 }
 
