@@ -202,3 +202,50 @@ def test_mutated_messages_fail_like_the_oracle(codec, kind):
     for i, (w, g) in enumerate(zip(want, got)):
         if w.status == 0:
             helpers.assert_same_decoded([w], [g], name, f"mutation {i}: {blobs[i].hex()[:200]}")
+
+
+def test_contexts_on_separate_threads_do_not_disturb_each_other():
+    """The reference serves requests from a multi-threaded runtime; the contract here is one ctx per thread.  Four threads,
+    each with its own ctx (its own streams, tables and staging buffers), encode and decode different batches at the same
+    time (ctypes releases the GIL for the duration of a call): every result equals the oracle's."""
+    import threading
+
+    import torch
+    errors = []
+
+    def worker(tid):
+        try:
+            c = tfs.GpuCodec(tfs.GpuContext(0))
+            try:
+                rng = np.random.default_rng(500 + tid)
+                for it in range(6):
+                    msgs = [tfs.PredictRequest(tfs.ModelSpec("m%d" % tid, signature_name="s"),
+                                               [("t%d" % j, random_tensor(rng)) for j in range(int(rng.integers(1, 4)))])
+                            for _ in range(int(rng.integers(1, 40)))]
+                    flat = [tfs.PredictRequest(m.model_spec, [(k, flatten_parts(t)) for k, t in m.inputs], m.output_filter) for m in msgs]
+                    want = ob.encode_messages(flat, abi.MSG_PREDICT_REQUEST)
+                    got = c.encoder().encode_host(msgs, abi.MSG_PREDICT_REQUEST).all_bytes()
+                    if got != want:
+                        raise AssertionError(f"thread {tid} iteration {it}: encode differs")
+                    dev = workloads.to_device(msgs, abi.MSG_PREDICT_REQUEST, torch.device("cuda:0"))
+                    if c.encoder().encode(dev, abi.MSG_PREDICT_REQUEST).all_bytes() != want:
+                        raise AssertionError(f"thread {tid} iteration {it}: device encode differs")
+                    offs, lens, cur = [], [], 0
+                    for b in want:
+                        offs.append(cur)
+                        lens.append(len(b))
+                        cur += len(b)
+                    st_o, want_dec = ob.decode_bytes(want, abi.MSG_PREDICT_REQUEST)
+                    d = c.decoder().decode_host(np.frombuffer(b"".join(want), dtype=np.uint8), offs, lens, abi.MSG_PREDICT_REQUEST)
+                    helpers.assert_same_decoded(want_dec, d.messages(), "request", f"thread {tid} iteration {it}")
+            finally:
+                c.ctx.close()
+        except BaseException as e:  # noqa: BLE001 - reported in the main thread
+            errors.append((tid, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
