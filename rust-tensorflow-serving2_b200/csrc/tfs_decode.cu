@@ -727,8 +727,12 @@ __device__ void walk_body(const DecTables& T, uint32_t mi) {
 }
 
 template <bool FILL>
-__global__ void __launch_bounds__(128) k_walk(DecTables T) {
-  const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
+// `lanes` (a power of two) threads of each warp take a message: the lanes of a warp wait for each other at every load of
+// this serial walk, and a batch too small to fill the GPU loses nothing by spreading over more warps.
+__global__ void __launch_bounds__(128) k_walk(DecTables T, uint32_t lanes) {
+  const uint32_t lane = threadIdx.x & 31u, warp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (lane >= lanes) return;
+  const uint32_t mi = warp * lanes + lane;
   if (mi < T.n_msgs) walk_body<FILL>(T, mi);
 }
 
@@ -1203,6 +1207,10 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   T.err = reinterpret_cast<unsigned long long*>(d1 + o_err);
 
   const uint32_t mblocks = (n_msgs + 127) / 128;
+  // walk kernels: as few messages per warp as keeps the grid within what the GPU holds at once (3 CTAs of 4 warps per SM)
+  uint32_t walk_lanes = 1;
+  while (walk_lanes < 32 && (n_msgs + walk_lanes - 1) / walk_lanes > static_cast<uint64_t>(ctx->sm_count) * 12) walk_lanes *= 2;
+  const uint32_t wblocks = static_cast<uint32_t>(((n_msgs + walk_lanes - 1) / walk_lanes + 3) / 4);
   const bool small = n_msgs <= kSmallBatch;
   const uint64_t pool_cap_arg = pool_dev ? pool_capacity : ~0ull;
   const size_t h1 = 0, h2 = align_up(res1_bytes, 64);
@@ -1291,7 +1299,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   } else {
     {
       ProfScope prof(ctx, PK_WALK);
-      k_walk<false><<<mblocks, 128, 0, ctx->stream>>>(T);
+      k_walk<false><<<wblocks, 128, 0, ctx->stream>>>(T, walk_lanes);
     }
     ctx->launches++;
     k_scan_counts<<<1, 1024, 0, ctx->stream>>>(T);
@@ -1326,7 +1334,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     if (n_tensors) DEC_CUDA(cudaMemsetAsync(T.tensors, 0, sizeof(tfs_tensor_out_t) * n_tensors, ctx->stream));
     if (n_msgs) {
       ProfScope prof(ctx, PK_WALK);
-      k_walk<true><<<mblocks, 128, 0, ctx->stream>>>(T);
+      k_walk<true><<<wblocks, 128, 0, ctx->stream>>>(T, walk_lanes);
       ctx->launches++;
     }
   }

@@ -126,10 +126,10 @@ __global__ void __launch_bounds__(kDecThreads) k_varint_count(DecTables T) {
   const uint32_t hx = d.x & kMsb, hy = d.y & kMsb, hz = d.z & kMsb, hw = d.w & kMsb;
   // (bytes outside the span may make this true for an edge chunk: that only sends the warp to the exact check)
   const bool own_word = hx == kMsb || hy == kMsb || hz == kMsb || hw == kMsb;
-  uint32_t cnt;
+  uint32_t cnt = 0;
   if (inside) {
     cnt = 16u - __popc((hx >> 7) | (hy >> 6) | (hz >> 5) | (hw >> 4));
-  } else {  // first / last chunk of the span, or outside it
+  } else if (touches) {  // first / last chunk of the span
     uint32_t cont, valid;
     masks_of(d, chunk_abs, r.span_abs0, r.span_end, &cont, &valid);
     cnt = __popc(~cont & valid);
