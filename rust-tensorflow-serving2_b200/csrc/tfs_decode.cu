@@ -126,6 +126,18 @@ struct Walker {
     return static_cast<uint8_t>(word >> ((static_cast<uint32_t>(a) & 3u) * 8u));
   }
 
+  // the (up to) four bytes at `off`, read through the window without a branch per word; bytes that lie beyond the
+  // window's 16 are junk
+  __device__ __forceinline__ uint32_t bytes4_at(uint64_t off) {
+    (void)byte_at(off);  // brings the window in
+    const uint32_t a = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(w) + off);
+    auto word_of = [&](uint32_t k) -> uint32_t {
+      const uint32_t s01 = 0x3210u + (k & 1u) * 0x4444u;
+      return __byte_perm(__byte_perm(win.x, win.y, s01), __byte_perm(win.z, win.w, s01), 0x3210u + (k >> 1) * 0x4444u);
+    };
+    const uint32_t k = (a >> 2) & 3u;
+    return __funnelshift_r(word_of(k), word_of(min(k + 1u, 3u)), (a & 3u) * 8u);
+  }
   __device__ __forceinline__ bool fail(int32_t code) {
     if (!err) {
       err = code;
@@ -222,8 +234,19 @@ struct Walker {
     sp.off = n_str;
     sp.len = len;
     sp._pad = 0;
-    if (FILL)
-      for (uint32_t i = 0; i < len; ++i) T.strings[n_str + i] = byte_at(off + i);
+    if (FILL) {
+      uint8_t* dst = T.strings + n_str;
+      for (uint32_t i = 0; i < len;) {
+        const uint32_t in_window = 16u - (static_cast<uint32_t>(reinterpret_cast<uintptr_t>(w) + off + i) & 15u);
+        const uint32_t n = min(min(4u, in_window), len - i);
+        const uint32_t v = bytes4_at(off + i);
+        dst[i] = static_cast<uint8_t>(v);
+        if (n > 1) dst[i + 1] = static_cast<uint8_t>(v >> 8);
+        if (n > 2) dst[i + 2] = static_cast<uint8_t>(v >> 16);
+        if (n > 3) dst[i + 3] = static_cast<uint8_t>(v >> 24);
+        i += n;
+      }
+    }
     n_str += len;
     return sp;
   }

@@ -415,7 +415,9 @@ constexpr uint32_t kSmallBatch = 256;
 __global__ void __launch_bounds__(kSmallBatch) k_frame_small(EncTables T, uint8_t* __restrict__ dst, uint32_t flags, uint32_t dst_skew,
                                                              uint64_t dst_capacity, int write) {
   __shared__ uint64_t smem[kSmallBatch / 32 + 1];
-  const uint32_t mi = threadIdx.x;
+  // per-message work deals the messages round the warps (the lanes of a warp wait for each other, and messages of
+  // different shapes diverge): 64 messages run as 8 warps of 8 rather than 2 of 32
+  const uint32_t mi = (threadIdx.x & 31u) * (kSmallBatch / 32) + (threadIdx.x >> 5);
   if (mi < T.n_msgs) msg_layout_body(T, mi);
   __syncthreads();
   msg_scan_body<kSmallBatch / 32>(T, flags, dst_skew, dst_capacity, smem);
