@@ -31,6 +31,8 @@ def _cases():
         tfs.TensorProto(dtype=7, string_val=strs, tensor_content=rng.integers(0, 256, 33333, dtype=np.uint8)),
         tfs.TensorProto(dtype=19, half_val=rng.integers(0, 65536, 4097).astype(np.int32), bool_val=rng.integers(0, 2, 1001).astype(np.bool_)),
         tfs.TensorProto(dtype=2, double_val=rng.standard_normal(5000)),
+        # many short elements: the decode walk's run loop, one table entry and one offset word per element
+        tfs.TensorProto(dtype=7, string_val=[rng.integers(0, 256, int(n), dtype=np.uint8).tobytes() for n in rng.integers(0, 41, 700)]),
     ]
     reqs = [tfs.PredictRequest(tfs.ModelSpec("m", version=3, signature_name="s"), [("a", tensors[0]), ("b", tensors[2])], ["y"]),
             tfs.PredictRequest(None, [("", tensors[1]), ("k", tensors[3]), ("d", tensors[4])])]
