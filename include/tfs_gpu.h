@@ -19,6 +19,12 @@
  *     pinned slabs (host<->device copies are inside those calls).
  *   - output bytes are byte-identical to prost 0.6.0's encoding of the same message with map entries
  *     in the caller's order; decoded values are value-identical.
+ *   - over-read contract: the kernels fetch whole ALIGNED 16-byte words, so up to 15 bytes before the first and
+ *     after the last byte of a source range (payload arrays on encode, the wire buffer on decode) may be READ; they are
+ *     never written and never influence the output.  Any cudaMalloc'd / cudaHostAlloc'd / torch-allocated buffer
+ *     satisfies this (allocations are at least 256-byte granular); a hand-made sub-allocation must not end closer than
+ *     that to unmapped memory, and a neighbouring sub-allocation that another stream is writing is only ever read,
+ *     and the bytes read from it are discarded.
  *   - there is no CPU fallback anywhere behind this header: without a usable CUDA device every
  *     compute entry point fails with TFS_ERR_CUDA.
  */
@@ -284,7 +290,14 @@ tfs_status_t tfs_ctx_create(int32_t device, uint64_t pinned_bytes, tfs_ctx_t** o
 tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx);
 /* Text of the last failure on this ctx (CUDA error string, offending argument, ...). */
 const char* tfs_last_error_detail(const tfs_ctx_t* ctx);
-/* Run the ctx's work on `cuda_stream` (a cudaStream_t; NULL = the ctx's own stream). */
+/* After a decode call returned TFS_ERR_BATCH: index of the FIRST failed message of that batch and the byte offset inside
+ * it where the error was detected (what prost's DecodeError would point at; for an over-long varint inside a packed body
+ * the offset is that of the 16-byte chunk holding it).  TFS_ERR_INVALID_ARG when the last call on this ctx had no failed
+ * message.  Every message's own status / err_offset is in tfs_decoded_view_t.msgs[]. */
+tfs_status_t tfs_last_error_location(const tfs_ctx_t* ctx, uint32_t* msg_index, uint64_t* byte_offset);
+/* Run the ctx's work on `cuda_stream` (a cudaStream_t; NULL = the ctx's own non-blocking stream, which is NOT ordered
+ * against the default stream).  The CUDA runtime's special handles are accepted as they are: cudaStreamLegacy
+ * ((void*)1, the default stream torch and most libraries report as "stream 0") and cudaStreamPerThread ((void*)2). */
 tfs_status_t tfs_ctx_set_stream(tfs_ctx_t* ctx, void* cuda_stream);
 tfs_status_t tfs_sync(tfs_ctx_t* ctx);
 /* Number of kernels this ctx has launched since creation (bench.py's gpu_launches). */
@@ -358,8 +371,8 @@ tfs_status_t tfs_decode_scan(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire
 tfs_status_t tfs_decoded_view(const tfs_decoded_t* dec, tfs_decoded_view_t* view);
 /* Pass 2: write every payload value into the device pool (pool_bytes >= view.pool_bytes; 16-byte aligned, since it
  * holds typed arrays - every (tensor, field) region starts on a 64-byte multiple from the pool's base; an unaligned
- * device or pinned pool is TFS_ERR_INVALID_ARG, a pageable host pool may sit anywhere).  Asynchronous: the
- * kernels are queued on the context's stream; tfs_sync() (or stream order) before anything else reads the pool. */
+ * device or pinned pool is TFS_ERR_INVALID_ARG, a pageable host pool may sit anywhere).  Synchronous: the values
+ * are in the pool when the call returns (tfs_decode_into is the form whose value kernels run on behind the call). */
 tfs_status_t tfs_decode(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_dev, uint64_t pool_bytes);
 tfs_status_t tfs_decoded_free(tfs_ctx_t* ctx, tfs_decoded_t* dec);
 
@@ -374,8 +387,10 @@ tfs_status_t tfs_decode_into(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire
                              uint64_t pool_capacity, tfs_decoded_t** out);
 
 /* End to end: wire bytes in host memory, values written to a host pool (both pinned for full speed).
- * The pool is allocated by the caller after looking at the view: call with pool_host == NULL to get
- * the handle and the sizes (the wire stays staged on the device), then tfs_decode_host_finish. */
+ * The pool is allocated by the caller after looking at the view: call tfs_decode_host to get the handle and the
+ * sizes, then tfs_decode_host_finish.  A pageable wire buffer is staged on the device by the first call; a pinned /
+ * registered one is read IN PLACE by both calls, so it must stay alive and unmodified until tfs_decode_host_finish
+ * has returned. */
 tfs_status_t tfs_decode_host(tfs_ctx_t* ctx, const void* wire_host, uint64_t wire_bytes, const uint64_t* msg_off,
                              const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags,
                              tfs_decoded_t** out);

@@ -48,6 +48,7 @@ def lib():
     L.tfs_ctx_destroy.argtypes = [vp]
     L.tfs_last_error_detail.restype = C.c_char_p
     L.tfs_last_error_detail.argtypes = [vp]
+    L.tfs_last_error_location.argtypes = [vp, u32p, u64p]
     L.tfs_ctx_set_stream.argtypes = [vp, vp]
     L.tfs_sync.argtypes = [vp]
     L.tfs_launch_count.restype = C.c_uint64

@@ -143,6 +143,7 @@ EXPORTED_SYMBOLS = (
     "tfs_encode_host", "tfs_decode_scan", "tfs_decoded_view", "tfs_decode", "tfs_decoded_free",
     "tfs_decode_host", "tfs_decode_host_finish", "tfs_shard_plan", "tfs_slot_of_kind", "tfs_kind_of_slot",
     "tfs_type_size", "tfs_prof_enable", "tfs_prof_read", "tfs_pack_int64_noalloc", "tfs_decode_into", "tfs_decode_host_into",
+    "tfs_last_error_location",
 )
 TFS_ERR_TOO_LARGE = 24
 TFS_NOALLOC_MAX_ELEMS = 1 << 24

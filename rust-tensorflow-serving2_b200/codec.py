@@ -43,7 +43,9 @@ class GpuContext:
             raise TfsError(st, "tfs_ctx_create failed: no usable CUDA device (this package has no CPU fallback)")
         if use_torch_stream and torch is not None and torch.cuda.is_available():
             torch.cuda.set_device(device)
-            self.set_stream(torch.cuda.current_stream(device).cuda_stream)
+            # torch reports its default stream as handle 0, which the ABI reads as "the ctx's own stream": name the
+            # legacy default stream explicitly (cudaStreamLegacy = 1) so that the codec is ordered after torch's work
+            self.set_stream(torch.cuda.current_stream(device).cuda_stream or 1)
 
     @property
     def handle(self):

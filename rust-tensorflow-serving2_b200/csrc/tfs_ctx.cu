@@ -183,6 +183,13 @@ tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx) {
 
 const char* tfs_last_error_detail(const tfs_ctx_t* ctx) { return ctx ? ctx->err.c_str() : ""; }
 
+tfs_status_t tfs_last_error_location(const tfs_ctx_t* ctx, uint32_t* msg_index, uint64_t* byte_offset) {
+  if (!ctx || !ctx->err_has_location) return TFS_ERR_INVALID_ARG;
+  if (msg_index) *msg_index = ctx->err_msg_index;
+  if (byte_offset) *byte_offset = ctx->err_byte_offset;
+  return TFS_OK;
+}
+
 tfs_status_t tfs_ctx_set_stream(tfs_ctx_t* ctx, void* cuda_stream) {
   if (!ctx) return TFS_ERR_INVALID_ARG;
   TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

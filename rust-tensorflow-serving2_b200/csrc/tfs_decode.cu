@@ -697,8 +697,11 @@ __device__ void walk_body(const DecTables& T, uint32_t mi) {
   memset(&mo, 0, sizeof(mo));
   if (!FILL) {
     const bool in_bounds = wk.end <= T.wire_bytes && wk.end >= wk.beg;
-    bool ok = in_bounds ? wk.run(&mo) : wk.fail(TFS_ERR_BUFFER_UNDERFLOW);
-    if (!ok && in_bounds) {
+    // the per-message counters (string bytes, spans, tiles) and string lengths are 32-bit: a message of 4 GiB or more
+    // (more than a gRPC frame can carry) is left to prost instead of wrapping silently
+    const bool too_long = T.msg_len[mi] > 0xFFFFFFF0ull;
+    bool ok = !in_bounds ? wk.fail(TFS_ERR_BUFFER_UNDERFLOW) : too_long ? wk.fail(TFS_ERR_UNSUPPORTED) : wk.run(&mo);
+    if (!ok && in_bounds && !too_long) {
       // prost stops at the FIRST error in stream order.  The walk does not look inside packed varint bodies (K4a does,
       // but only for messages that pass the walk), so a failed message is walked once more with those bodies checked.
       Walker<false> v(T, mi);
@@ -1304,7 +1307,8 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       blob_copied = guess;
       break;
     }
-    if (n_vt > 0xFFFFFFF0ull) return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large"));
+    if (n_vt > 0xFFFFFFF0ull || n_str > 0xFFFFFFF0ull || dec->totals[TOT_CTILES] > 0xFFFFFFF0ull)
+      return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large (32-bit table offsets)"));
     T.filters = reinterpret_cast<tfs_span_t*>(reinterpret_cast<uint8_t*>(T.tensors) + p_flt);
     T.strings = reinterpret_cast<uint8_t*>(T.tensors) + p_str;
     planned = n_vt == 0;
@@ -1332,7 +1336,8 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     DEC_CUDA(cudaMemcpyAsync(ctx->h_down, T.totals, kTotalsBytes, cudaMemcpyDeviceToHost, ctx->stream));
     DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1: the sizes of the pass-2 tables
     load_totals(static_cast<const uint8_t*>(ctx->h_down));
-    if (n_tensors > 0xFFFFFFF0ull || n_spans > 0xFFFFFFF0ull || n_vt > 0xFFFFFFF0ull) return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large"));
+    if (n_tensors > 0xFFFFFFF0ull || n_spans > 0xFFFFFFF0ull || n_vt > 0xFFFFFFF0ull || n_str > 0xFFFFFFF0ull || dec->totals[TOT_CTILES] > 0xFFFFFFF0ull)
+      return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large (32-bit table offsets)"));
     // ---- pass 2 tables; tensors | filters | strings are contiguous: one D2H
     blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &res2_bytes);
     cur = 0;
@@ -1437,6 +1442,18 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   if (n_filters) std::memcpy(dec->filters.data(), hd + h2 + p_flt, sizeof(tfs_span_t) * n_filters);
   if (n_str) std::memcpy(dec->strings.data(), hd + h2 + p_str, n_str);
   dec->n_failed = static_cast<uint32_t>(dec->totals[TOT_FAILED]);
+  ctx->err_has_location = false;
+  if (dec->n_failed) {  // the first failed message, for tfs_last_error_detail / tfs_last_error_location
+    for (uint32_t i = 0; i < n_msgs; ++i) {
+      if (dec->msgs[i].status == TFS_OK) continue;
+      ctx->err_has_location = true;
+      ctx->err_msg_index = i;
+      ctx->err_byte_offset = dec->msgs[i].err_offset;
+      ctx->err = std::string("message ") + std::to_string(i) + ": " + tfs_strerror(dec->msgs[i].status) + " near byte " +
+                 std::to_string(dec->msgs[i].err_offset) + " (" + std::to_string(dec->n_failed) + " of " + std::to_string(n_msgs) + " messages failed)";
+      break;
+    }
+  }
   *out = dec;
 #undef DEC_TRY
 #undef DEC_CUDA

@@ -235,6 +235,10 @@ struct tfs_ctx {
   cudaStream_t own_stream = nullptr;
   cudaStream_t stream = nullptr;
   std::string err;
+  // where the last batch decode failed first: message index and byte offset inside that message (tfs_last_error_location)
+  bool err_has_location = false;
+  uint32_t err_msg_index = 0;
+  uint64_t err_byte_offset = 0;
   uint64_t launches = 0;
   DevBuf d_tables, d_work, d_stage_in, d_stage_out;
   DevBuf d_dec1, d_dec2, d_dec3;  // decode tables (pass 1 / pass 2 / varint tiles); owned by the newest tfs_decoded handle

@@ -157,3 +157,73 @@ def _first_diff(dx, dy, path=""):
         n = next((i for i in range(min(len(dx), len(dy))) if dx[i] != dy[i]), min(len(dx), len(dy)))
         return f"{path}: hex differs at nibble {n} (byte {n // 2}) of {len(dx) // 2}/{len(dy) // 2}: ...{dx[max(0, n - 16): n + 32]} vs ...{dy[max(0, n - 16): n + 32]}"
     return f"{path}: {dx!r} vs {dy!r}"
+
+
+def assert_same_decoded_fast(a, b, kind: str, ctx=""):
+    """Same contract as assert_same_decoded for batches too large for hex descriptions (hundreds of MB): statuses,
+    model specs, keys, dtypes, shapes, and every payload compared as raw little-endian bytes."""
+    assert len(a) == len(b), f"{ctx}: message count {len(a)} != {len(b)}"
+    for i, (x, y) in enumerate(zip(a, b)):
+        assert x.status == y.status, f"{ctx}: msg {i} status {x.status} != {y.status}"
+        if x.status != 0:
+            continue
+        mx, my = x.message, y.message
+        if kind == "tensor":
+            ex, ey = [("", mx)], [("", my)]
+        else:
+            assert mx.model_spec == my.model_spec, f"{ctx}: msg {i} model_spec {mx.model_spec} != {my.model_spec}"
+            ex, ey = (mx.inputs, my.inputs) if kind == "request" else (mx.outputs, my.outputs)
+            if kind == "request":
+                assert list(mx.output_filter) == list(my.output_filter), f"{ctx}: msg {i} output_filter"
+        assert len(ex) == len(ey), f"{ctx}: msg {i} has {len(ex)} vs {len(ey)} entries"
+        for j, ((kx, tx), (ky, ty)) in enumerate(zip(ex, ey)):
+            where = f"{ctx}: msg {i} entry {j} ({kx!r})"
+            assert kx == ky and tx.dtype == ty.dtype and tx.version_number == ty.version_number and tx.tensor_shape == ty.tensor_shape, where
+            px, py = dict(tx.payloads()), dict(ty.payloads())
+            px = {k: v for k, v in px.items() if len(v)}
+            py = {k: v for k, v in py.items() if len(v)}
+            assert sorted(px) == sorted(py), f"{where}: fields {sorted(px)} vs {sorted(py)}"
+            for k in px:
+                name = abi.KIND_FIELD_NAMES[k]
+                if name == "string_val":
+                    assert [bytes(e) for e in px[k]] == [bytes(e) for e in py[k]], f"{where}: {name}"
+                    continue
+                ax = np.ascontiguousarray(px[k]).astype(FIELD_NP[name], copy=False) if np.asarray(px[k]).dtype.kind != "b" else np.asarray(px[k]).astype("u1")
+                ay = np.ascontiguousarray(py[k]).astype(FIELD_NP[name], copy=False) if np.asarray(py[k]).dtype.kind != "b" else np.asarray(py[k]).astype("u1")
+                if ax.size != ay.size or ax.tobytes() != ay.tobytes():
+                    bad = -1
+                    if ax.size == ay.size:
+                        d = np.nonzero(ax.view("u1") != ay.view("u1"))[0]
+                        bad = int(d[0]) if d.size else -1
+                    raise AssertionError(f"{where}: {name} differs ({ax.size} vs {ay.size} elements, first differing byte {bad})")
+
+
+def mutation_corpus(kind: str, n_cases: int, seed: int = 99):
+    """Byte-level mutations (truncation, byte replacement, insertion, a bit flip near the front) of valid
+    PredictResponses / PredictRequests: the corpus the GPU fuzz test and the upb accept / reject test share."""
+    from tfs_b200 import workloads
+    import oracle_bind as ob
+    rng = np.random.default_rng(seed)
+    resp = workloads.c5_responses(24, seed=31, max_log2=7)
+    if kind == "response":
+        base = ob.encode_messages(resp, abi.MSG_PREDICT_RESPONSE)
+    else:
+        reqs = [tfs.PredictRequest(r.model_spec, r.outputs, ["a", "filter-%d" % i][: i % 3]) for i, r in enumerate(resp)]
+        base = ob.encode_messages(reqs, abi.MSG_PREDICT_REQUEST)
+    blobs = []
+    for i in range(n_cases):
+        b = bytearray(base[i % len(base)])
+        op = rng.integers(0, 4)
+        if op == 0 and len(b) > 1:
+            b = b[: rng.integers(0, len(b))]
+        elif op == 1 and len(b):
+            for _ in range(int(rng.integers(1, 4))):
+                b[rng.integers(0, len(b))] = rng.integers(0, 256)
+        elif op == 2 and len(b):
+            j = rng.integers(0, len(b))
+            b[j:j] = bytes(rng.integers(0, 256, rng.integers(1, 5), dtype=np.uint8))
+        elif len(b) > 2:
+            j = rng.integers(0, min(len(b), 40))
+            b[j] ^= 1 << int(rng.integers(0, 8))
+        blobs.append(bytes(b))
+    return blobs

@@ -464,35 +464,21 @@ def test_grpc_prefix_roundtrip(codec):
     helpers.assert_same_decoded(want, got, "response", "grpc bad")
 
 
-def test_decode_fuzz_against_oracle(codec):
-    """Random truncations / byte flips of valid messages: same status class, same values when OK."""
+@pytest.mark.parametrize("kind", ["response", "request"])
+def test_decode_fuzz_against_oracle(codec, kind):
+    """Random truncations / byte flips of valid messages: same status class, same values when OK.  The corpus is the one
+    tests/test_oracle_upb_messages.py runs through upb for accept / reject agreement (helpers.mutation_corpus)."""
     import os
-    rng = np.random.default_rng(int(os.environ.get("TFS_FUZZ_SEED", "99")))   # TFS_FUZZ_SEED / TFS_FUZZ_CASES: a longer hunt
-    base = ob.encode_messages(workloads.c5_responses(24, seed=31, max_log2=7), abi.MSG_PREDICT_RESPONSE)
-    blobs = []
-    for i in range(int(os.environ.get("TFS_FUZZ_CASES", "400"))):
-        b = bytearray(base[i % len(base)])
-        op = rng.integers(0, 4)
-        if op == 0 and len(b) > 1:
-            b = b[: rng.integers(0, len(b))]
-        elif op == 1 and len(b):
-            for _ in range(int(rng.integers(1, 4))):
-                b[rng.integers(0, len(b))] = rng.integers(0, 256)
-        elif op == 2 and len(b):
-            j = rng.integers(0, len(b))
-            b[j:j] = bytes(rng.integers(0, 256, rng.integers(1, 5), dtype=np.uint8))
-        elif len(b) > 2:
-            j = rng.integers(0, min(len(b), 40))
-            b[j] ^= 1 << int(rng.integers(0, 8))
-        blobs.append(bytes(b))
-    st_o, want = ob.decode_bytes(blobs, abi.MSG_PREDICT_RESPONSE)
-    st, got = gpu_decode_both(codec, blobs, abi.MSG_PREDICT_RESPONSE)
+    blobs = helpers.mutation_corpus(kind, int(os.environ.get("TFS_FUZZ_CASES", "400")), int(os.environ.get("TFS_FUZZ_SEED", "99")))
+    mk = helpers.KIND_OF[kind]
+    st_o, want = ob.decode_bytes(blobs, mk)
+    st, got = gpu_decode_both(codec, blobs, mk)
     mism = []
     for i, (w, g) in enumerate(zip(want, got)):
         if w.status != g.status:
             mism.append((i, blobs[i].hex(), abi.STATUS_NAMES.get(w.status), abi.STATUS_NAMES.get(g.status)))
         elif w.status == 0:
-            helpers.assert_same_decoded([w], [g], "response", f"fuzz {i}: {blobs[i].hex()}")
+            helpers.assert_same_decoded([w], [g], kind, f"fuzz {i}: {blobs[i].hex()}")
     assert not mism, mism[:5]
 
 
@@ -751,6 +737,33 @@ def test_config_c4_full_size(codec, fmt):
 def test_config_c5_mixed_responses(codec):
     msgs = workloads.c5_responses(512, seed=5001, max_log2=14)
     roundtrip_check(codec, msgs, abi.MSG_PREDICT_RESPONSE, "C5")
+
+
+def test_config_c5_at_benchmarked_scale(codec):
+    """C5 exactly as bench.py times it: one GPU's share (1 024 of the 8 192 responses, seed 5001, element counts
+    log-uniform up to 2^18, ~200 MB of wire), the wire produced by the oracle, decoded in one call into a device
+    pool; every status and every value against the oracle's decode."""
+    import torch
+    msgs = workloads.c5_responses(1024, seed=5001, max_log2=18)
+    built = tfs.build_batch(msgs, abi.MSG_PREDICT_RESPONSE)
+    wire, offs, lens = ob.encode(built)
+    st_o, want = ob.decode(wire, offs, lens, abi.MSG_PREDICT_RESPONSE)
+    assert st_o == 0
+    dev = torch.device(f"cuda:{codec.ctx.device}")
+    dwire = torch.from_numpy(wire).to(dev)
+    d = codec.decoder().scan(dwire, offs, lens, abi.MSG_PREDICT_RESPONSE)
+    pool = torch.empty(d.pool_bytes + 64, dtype=torch.uint8, device=dev)
+    d.close()
+    d = codec.decoder().decode_into(dwire, offs, lens, abi.MSG_PREDICT_RESPONSE, pool)
+    codec.ctx.sync()
+    assert d.status == 0
+    helpers.assert_same_decoded_fast(want, d.messages(), "response", "C5 at bench scale")
+    d.close()
+    # and the GPU's own encoding of the same responses is the oracle's wire, byte for byte
+    eb = codec.encoder().encode(workloads.to_device(msgs, abi.MSG_PREDICT_RESPONSE, dev), abi.MSG_PREDICT_RESPONSE)
+    assert eb.lengths == lens
+    got = eb.wire[: eb.total].cpu().numpy()
+    assert eb.offsets == offs and got.tobytes() == wire.tobytes()
 
 
 def test_full_size_properties(codec):

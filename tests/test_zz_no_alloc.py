@@ -4,7 +4,8 @@ It serves callers that cannot call cudaMalloc — a codec inside a serving poll 
 synchronise the device and stall other requests), or a client whose GPU memory has already been claimed by a
 co-located TensorFlow Serving process — by keeping its tables in a fixed block inside the library image.
 Here it is called through the C ABI (ctypes) and its output is compared byte for byte with what the regular
-entry point tfs_encode produces for the same values, on consecutive calls that reuse the shared block.
+entry point tfs_encode produces for the same values AND with the CPU oracle's packed `int64_val` body (the
+restatement of prost's int64::encode_packed), on consecutive calls that reuse the shared block.
 
 The file name sorts last on purpose: with `pytest -x` every other test has already run if this one fails.
 """
@@ -52,11 +53,9 @@ def pack_noalloc(values, capacity=None):
     return st, None, blen
 
 
-def body_from_regular_entry_point(codec, values):
-    """The same values through tfs_encode (a bare TensorProto holding only int64_val): key, length, body."""
-    eb = codec.encoder().encode([tfs.TensorProto(int64_val=values)], abi.MSG_TENSOR_PROTO)
-    wire = eb.all_bytes()[0]
-    if values.numel() == 0:
+def strip_key_and_length(wire, n):
+    """A bare TensorProto holding only int64_val is `52 varint(len) body`: returns the body."""
+    if n == 0:
         assert wire == b""
         return b""
     assert wire[0] == 0x52
@@ -71,6 +70,19 @@ def body_from_regular_entry_point(codec, values):
             break
     assert len(wire) == i + blen
     return wire[i:]
+
+
+def body_from_regular_entry_point(codec, values):
+    """The same values through tfs_encode (a bare TensorProto holding only int64_val)."""
+    eb = codec.encoder().encode([tfs.TensorProto(int64_val=values)], abi.MSG_TENSOR_PROTO)
+    return strip_key_and_length(eb.all_bytes()[0], values.numel())
+
+
+def body_from_oracle(values):
+    """The same values through the CPU oracle (oracle/cpu_ref.cpp, prost's int64::encode_packed restated)."""
+    import oracle_bind as ob
+    wire = ob.encode_messages([tfs.TensorProto(int64_val=values.cpu().numpy())], abi.MSG_TENSOR_PROTO)[0]
+    return strip_key_and_length(wire, values.numel())
 
 
 def test_no_alloc_matches_regular_entry_point_on_consecutive_calls():
@@ -94,11 +106,12 @@ def test_no_alloc_matches_regular_entry_point_on_consecutive_calls():
         want = body_from_regular_entry_point(codec, vals)
         assert blen == len(want), (call, n, blen, len(want))
         assert body == want, f"call {call} (n={n}): packed bytes differ from tfs_encode"
+        assert body == body_from_oracle(vals), f"call {call} (n={n}): packed bytes differ from the oracle"
     # twice in a row on the very same input: identical output both times
     vals = torch.arange(-5000, 5000, device=dev, dtype=torch.int64) * 123457
     first = pack_noalloc(vals)
     second = pack_noalloc(vals)
-    assert first == second and first[1] == body_from_regular_entry_point(codec, vals)
+    assert first == second and first[1] == body_from_regular_entry_point(codec, vals) == body_from_oracle(vals)
     codec.ctx.close()
 
 
