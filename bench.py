@@ -12,6 +12,11 @@ the host-memory entry points (payloads and wire in pinned host memory, H2D/D2H i
 
 Requests are independent, so N GPUs each take their own shard of the batch: no collective on the data
 path; torch.distributed (nccl) is only used for the barrier and the max-over-ranks time.
+
+Next to the headline the line carries, for the other BASELINE configs (C1, C3, C4, C5) and for the C2 variants that
+do not ride the aligned fast path (back-to-back wire, fused u8 -> f32, fused f32 -> bf16), call-level roofline
+fractions, the dominant kernel's fraction, the CPU port on the same inputs (1 thread and all cores) and an end-to-end
+figure for pinned and for pageable host buffers: nested under `per_config` and, flattened to scalars, inside `roofline`.
 """
 import argparse
 import json
@@ -36,8 +41,22 @@ VARIANTS = ("float_val", "tensor_content")
 
 
 def workload_name(r):
-    return (f"C2 ResNet-50 input 64x224x224x3 DT_FLOAT as float_val and as tensor_content; per step and per GPU: "
-            f"{r} PredictRequests per variant encoded, then decoded")
+    return f"C2 ResNet-50 input 64x224x224x3 f32 as float_val + tensor_content, {r} requests per variant: encode then decode"
+
+
+def config_of(args, world):
+    """The `config` object: the same keys in both arms (the driver compares them)."""
+    return {"workload": workload_name(args.requests), "requests_per_variant_per_gpu": args.requests, "wire_bytes_per_request": C2_WIRE,
+            "l2": "inputs larger than L2 (126 MB): each pass streams %d MB" % (args.requests * C2_WIRE // 1000000),
+            "flags": "TFS_F_ALIGN_PAYLOAD", "sharding": f"dp{world}: independent requests per GPU, no collective"}
+
+
+def host_threads():
+    """One rule for every CPU number of this file: all the host cores the process may use."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
 
 
 def load_peaks():
@@ -100,33 +119,12 @@ class ClockSampler:
 # =====================================================================================================
 # our arm
 # =====================================================================================================
-def pin_to_gpu_numa_node(index):
-    """Bind this process to the CPUs NVML names as local to GPU `index` (one process per GPU: its pinned staging buffers
-    are then first-touched on that socket).  Returns a short description for the bench line; failing is harmless."""
-    try:
-        import pynvml
-        pynvml.nvmlInit()
-        h = pynvml.nvmlDeviceGetHandleByIndex(index)
-        words = (os.cpu_count() + 63) // 64
-        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
-        cpus = {64 * w + b for w in range(words) for b in range(64) if (mask[w] >> b) & 1}
-        everything = os.sched_getaffinity(0)
-        cpus &= everything
-        if cpus:
-            os.sched_setaffinity(0, cpus)
-            pin_to_gpu_numa_node.restore = lambda: os.sched_setaffinity(0, everything)
-            return f"{len(cpus)} of {len(everything)} cpus (local to gpu {index}) during the GPU measurements"
-    except Exception as e:  # noqa: BLE001
-        return f"not bound ({type(e).__name__})"
-    return "not bound"
-
-
 def run_ours(args):
     import torch
     import torch.distributed as dist
 
     import tfs_b200 as tfs
-    from tfs_b200 import abi, workloads
+    from tfs_b200 import abi
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -135,7 +133,6 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: the codec has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device(f"cuda:{local}")
-    numa = pin_to_gpu_numa_node(local)  # before any pinned allocation: the staging buffers should be local to the GPU's socket
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -144,6 +141,17 @@ def run_ours(args):
         if world > 1:
             dist.barrier()
 
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # the codec runs on torch's CURRENT stream, a stream of our own (the legacy default stream serialises against every other
+    # blocking stream of the process); the events below are recorded on the same stream
+    side = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(side)
     codec = tfs.GpuCodec(tfs.GpuContext(local))
     ctx, enc, dec = codec.ctx, codec.encoder(), codec.decoder()
     R = args.requests
@@ -155,16 +163,16 @@ def run_ours(args):
     g.manual_seed(2001 + rank)
     src = torch.randn(R, C2_ELEMS, device=dev, generator=g)
 
-    def requests(payload_rows, variant):
+    def c2_requests(rows, variant, n):
         out = []
-        for i in range(R):
+        for i in range(n):
             shape = tfs.TensorShapeProto([64, 224, 224, 3])
-            t = (tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, float_val=payload_rows[i]) if variant == "float_val"
-                 else tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, tensor_content=payload_rows[i]))
+            t = (tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, float_val=rows[i]) if variant == "float_val"
+                 else tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, tensor_content=rows[i]))
             out.append(tfs.PredictRequest(tfs.ModelSpec("resnet", signature_name="serving_default"), [("input", t)]))
         return out
 
-    built = {v: tfs.build_batch(requests(src, v), kind) for v in VARIANTS}  # the "prost structs", built once
+    built = {v: tfs.build_batch(c2_requests(src, v, R), kind) for v in VARIANTS}  # the "prost structs", built once
     cap = enc.bound(built["float_val"], flags)
     wire = {v: torch.empty(cap, dtype=torch.uint8, device=dev) for v in VARIANTS}
     pool = {v: torch.empty(R * (C2_ELEMS * 4 + 4096), dtype=torch.uint8, device=dev) for v in VARIANTS}
@@ -190,7 +198,7 @@ def run_ours(args):
     for _ in range(args.warmup):
         step()
     ctx.prof_enable(True)
-    for k in range(8):
+    for k in range(abi.PK_COUNT):
         ctx.prof_read(k, reset=True)
     sampler = ClockSampler(local)
     if rank == 0:
@@ -203,6 +211,7 @@ def run_ours(args):
     wire_bytes = 0
     for _ in range(args.steps):
         wire_bytes += step()
+    ctx.sync()
     e1.record()
     torch.cuda.synchronize()
     barrier()
@@ -211,31 +220,37 @@ def run_ours(args):
     clocks = sampler.stop() if rank == 0 else None
     n_copy, ms_copy = ctx.prof_read(abi.PK_COPY_TMA)   # the TMA ring moves every payload byte of this workload
     n_gen, ms_gen = ctx.prof_read(abi.PK_COPY)          # the generic kernel only finds nothing to do here
-    n_walk, ms_walk = ctx.prof_read(abi.PK_WALK)        # decode plan (both structure walks), one launch per decode
+    n_walk, ms_walk = ctx.prof_read(abi.PK_WALK)        # decode plan (structure walk), one launch per decode
     n_frame, ms_frame = ctx.prof_read(abi.PK_FRAME)     # encode framing, one launch per encode
     ctx.prof_enable(False)
-    if world > 1:
-        t = torch.tensor([ms], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    ms = max_over_ranks(ms)
 
-    # ---- end to end: pinned host payloads -> host wire -> host values, smaller batch (PCIe-bound)
+    # ---- a sustained side figure: the same step for >= 1 s, with its own clock samples
+    sustained = None
+    if rank == 0 and world == 1 and args.sustain_s > 0:
+        s2 = ClockSampler(local)
+        s2.start()
+        torch.cuda.synchronize()
+        e0.record()
+        t_begin, nb, ns = time.perf_counter(), 0, 0
+        while time.perf_counter() - t_begin < args.sustain_s:
+            nb += step()
+            ns += 1
+        ctx.sync()
+        e1.record()
+        torch.cuda.synchronize()
+        sms = e0.elapsed_time(e1)
+        ck = s2.stop()
+        sustained = {"GBps": round(nb / (sms * 1e-3) / 1e9, 1), "seconds": round(sms * 1e-3, 2), "steps": ns, "sm_mhz": ck.get("sm_mhz"),
+                     "reasons": ",".join(ck.get("reasons") or [])}
+
+    # ---- end to end: pinned host payloads -> host wire -> host values (PCIe-bound), same batch size as `value`
     Re = min(args.e2e_requests, R)
     h_src = torch.randn(Re, C2_ELEMS).pin_memory()
     h_wire = torch.empty(enc.bound(built["float_val"], flags) // R * Re + 4096, dtype=torch.uint8).pin_memory()
     h_pool = torch.empty(Re * (C2_ELEMS * 4 + 4096), dtype=torch.uint8).pin_memory()
     rows = [h_src[i].numpy() for i in range(Re)]
-
-    def host_requests(variant):
-        out = []
-        for i in range(Re):
-            shape = tfs.TensorShapeProto([64, 224, 224, 3])
-            t = (tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, float_val=rows[i]) if variant == "float_val"
-                 else tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape, tensor_content=rows[i]))
-            out.append(tfs.PredictRequest(tfs.ModelSpec("resnet", signature_name="serving_default"), [("input", t)]))
-        return out
-
-    hbuilt = {v: tfs.build_batch(host_requests(v), kind) for v in VARIANTS}
+    hbuilt = {v: tfs.build_batch(c2_requests(rows, v, Re), kind) for v in VARIANTS}
     h_wire_np, h_pool_np = h_wire.numpy(), h_pool.numpy()
 
     def e2e_step():
@@ -262,13 +277,9 @@ def run_ours(args):
         e2e_bytes += a
         h2d, d2h = b, c
     torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t_start
-    if world > 1:
-        t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    last = pool_check = h_pool[: 16].clone()  # touch the result (device -> host read is part of every step)
-    del last, pool_check
+    e2e_s = max_over_ranks(time.perf_counter() - t_start)
+    assert np.array_equal(h_pool_np[: 16], h_pool_np[: 16])  # the result is read on the host (device -> host is part of every step)
+    del h_src, h_wire, h_pool, hbuilt
 
     if rank != 0:
         if world > 1:
@@ -277,224 +288,314 @@ def run_ours(args):
 
     peak, peak_src = load_peaks()
     value = world * wire_bytes / (ms * 1e-3) / 1e9
-    # K5 k_copy: one launch per encode and per decode; algorithmic bytes of one launch = read + write of
+    # K5 k_copy_tma: one launch per encode and per decode; algorithmic bytes of one launch = read + write of
     # R payloads (fixed / content encode or decode = N*w_src + N*w_dst)
     alg_per_launch = 2.0 * R * C2_ELEMS * 4
     achieved = alg_per_launch / (ms_copy / max(1, n_copy) * 1e-3) / 1e9 if n_copy else None
-    # DRAM bytes of one k_copy_tma launch from the committed `ncu --set full` capture (only if it is of this batch size)
-    traffic, traffic_src = None, None
+    traffic = None
     try:
-        tj = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")))["k_copy_tma"]
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_copy_tma"]
         if tj["requests_per_variant"] == R:
-            traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
+            traffic = tj["dram_bytes_per_launch"]
     except (OSError, KeyError, ValueError):
         pass
+    roof = {"bound": "hbm", "kernel": "k_copy_tma (K5 bulk copy through the TMA ring; one launch per encode and per decode)",
+            "achieved": round(achieved, 1) if achieved else None, "peak": peak, "unit": "GB/s",
+            "frac": round(achieved / peak, 4) if achieved else None, "peak_source": peak_src,
+            "frac_of_nominal_8000_GBps": round(achieved / 8000.0, 4) if achieved else None,
+            "traffic": traffic, "launches_timed": n_copy, "avg_launch_ms": round(ms_copy / max(1, n_copy), 4),
+            "algorithmic_bytes_per_launch": alg_per_launch, "step_frac_of_peak": round(2 * value / world / peak, 4),
+            "step_ms_k_copy_tma": round(ms_copy / args.steps, 4), "step_ms_walk": round(ms_walk / args.steps, 4),
+            "step_ms_frame": round(ms_frame / args.steps, 4), "step_ms_other_copy": round(ms_gen / args.steps, 4),
+            "step_ms_rest": round((ms - ms_copy - ms_walk - ms_frame - ms_gen) / args.steps, 4)}
+    if sustained:
+        roof.update({"sustained_GBps": sustained["GBps"], "sustained_seconds": sustained["seconds"], "sustained_sm_mhz": sustained["sm_mhz"],
+                     "sustained_reasons": sustained["reasons"]})
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u8", "data": "synthetic",
-        "config": {"workload": workload_name(R), "requests_per_variant_per_gpu": R, "wire_bytes_per_request": C2_WIRE,
-                   "l2": f"inputs larger than L2: each pass streams {R * C2_WIRE / 1e6:.0f} MB in and out (L2 is 126 MB)",
-                   "flags": "TFS_F_ALIGN_PAYLOAD", "sharding": f"dp{world}: independent requests per GPU, no collective"},
-        "clocks": clocks,
+        "dtype": "u8", "data": "synthetic", "config": config_of(args, world), "clocks": clocks,
         "e2e": {"value": round(world * e2e_bytes / e2e_s / 1e9, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "host_affinity": numa, "path": "tfs_encode_host + tfs_decode_host_into on pinned host buffers: copy engine brings the source to HBM in 8 MB chunks, the copy kernel follows chunk by chunk and stores straight into the pinned destination"},
-        "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "k_copy_tma (K5 bulk copy through the TMA ring; one launch per encode and per decode)",
-                     "other_copy_kernel_avg_ms": round(ms_gen / max(1, n_gen), 4),
-                     "achieved": round(achieved, 1) if achieved else None,
-                     "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4) if achieved else None, "peak_source": peak_src,
-                     "frac_of_nominal_8000_GBps": round(achieved / 8000.0, 4) if achieved else None,
-                     "traffic": traffic, "traffic_source": traffic_src, "launches_timed": n_copy, "avg_launch_ms": round(ms_copy / max(1, n_copy), 4),
-                     "algorithmic_bytes_per_launch": alg_per_launch,
-                     "step_frac_of_peak": round(2 * value / world / peak, 4),
-                     "step_breakdown_ms": {"k_copy_tma": round(ms_copy / args.steps, 4), "k_plan_small": round(ms_walk / args.steps, 4),
-                                           "k_frame_small": round(ms_frame / args.steps, 4),
-                                           "rest (host syncs, table copies, k_dec_bind)": round((ms - ms_copy - ms_walk - ms_frame) / args.steps, 4)}},
+                "requests_per_variant_per_gpu": Re, "steps": e2e_steps,
+                "path": "tfs_encode_host + tfs_decode_host_into, pinned host buffers"},
+        "gpu_launches": int(launches), "roofline": roof,
     }
-    getattr(pin_to_gpu_numa_node, "restore", lambda: None)()  # the CPU baseline gets every host core again
-    line["cpu_baseline"] = cpu_baseline(R, budget_s=args.cpu_budget)
+    del src, wire, pool, built
+    torch.cuda.empty_cache()
+    line["cpu_baseline"] = cpu_baseline_c2(budget_s=args.cpu_budget)
     if world == 1 and not args.no_extras:
-        del src, wire, pool
-        torch.cuda.empty_cache()
-        line["other_configs"] = other_configs(codec, dev, peak)
+        pc = per_config(codec, dev, peak, args)
+        line["per_config"] = pc
+        for name, res in pc.items():  # the driver's parser keeps scalars inside `roofline`: a flat copy
+            for k, v in res.items():
+                if isinstance(v, (int, float)) or v is None:
+                    roof[f"pc_{name}_{k}"] = v
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
 # =====================================================================================================
-# the other BASELINE configs (N = 1 only, a few repetitions each): parity-tested workloads, reported next to the
-# headline so that the varint kernels have measured numbers too
+# the other configs (N = 1 only): per direction the call-level algorithmic GB/s and fraction of the measured copy
+# peak, the dominant kernel's fraction, the CPU port on the same inputs, end to end for pinned and pageable buffers
 # =====================================================================================================
-def other_configs(codec, dev, peak):
+def _pin(a):
+    import torch
+    t = torch.from_numpy(a).pin_memory()
+    return t, t.numpy()
+
+
+def per_config(codec, dev, peak, args):
     import torch
     import tfs_b200 as tfs
-    from tfs_b200 import abi
+    from tfs_b200 import abi, workloads
+    import oracle_bind as ob
 
     ctx, enc, dec = codec.ctx, codec.encoder(), codec.decoder()
-    names = {abi.PK_COPY: "k_copy", abi.PK_VARINT_SIZE: "k_varint_size", abi.PK_VARINT_SCATTER: "k_varint_scatter",
-             abi.PK_VARINT_COUNT: "k_varint_count", abi.PK_VARINT_GATHER: "k_varint_gather", abi.PK_COPY_TMA: "k_copy_tma"}
+    names = dict(abi.PK_NAMES)
+    threads = host_threads()
 
-    def measure(msgs, kind, in_bytes, reps=5, dflags=0, decode_only=False):
-        built = tfs.build_batch(msgs, kind)
-        wire = torch.empty(enc.bound(built, 0), dtype=torch.uint8, device=dev)
-        eb = enc.encode(built, kind, 0, dst=wire)
-        W = sum(eb.lengths)
-        d = dec.scan(eb.wire, eb.offsets, eb.lengths, kind, dflags)
-        out_bytes = d.pool_bytes
-        pool = torch.empty(out_bytes + 64, dtype=torch.uint8, device=dev)
-        d.close()
-        for _ in range(2):
-            if not decode_only:
-                eb = enc.encode(built, kind, 0, dst=wire)
-            dec.decode_into(eb.wire, eb.offsets, eb.lengths, kind, pool, dflags).close()
-        ctx.prof_enable(True)
-        for k in names:
-            ctx.prof_read(k, reset=True)
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-        te = td = 0.0
-        for _ in range(reps):
+    def device_side(msgs_dev, kind, in_bytes, eflags=0, dflags=0, reps=5, decode_wire=None, encode=True, decode=True):
+        """-> dict with call-level times and the largest kernel of each direction"""
+        res = {}
+        if encode:
+            built = tfs.build_batch(msgs_dev, kind) if not isinstance(msgs_dev, tfs.BuiltBatch) else msgs_dev
+            wire = torch.empty(enc.bound(built, eflags), dtype=torch.uint8, device=dev)
+            eb = enc.encode(built, kind, eflags, dst=wire)
+            W = sum(eb.lengths)
+            wire_t, offs, lens = eb.wire, eb.offsets, eb.lengths
+        else:
+            wire_t, offs, lens = decode_wire
+            W = sum(lens)
+        out_bytes = 0
+        if decode:
+            d = dec.scan(wire_t, offs, lens, kind, dflags)
+            out_bytes = d.pool_bytes
+            pool = torch.empty(out_bytes + 64, dtype=torch.uint8, device=dev)
+            d.close()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
+        def timed(fn, alg):
+            for _ in range(2):
+                fn()
+            ctx.prof_enable(True)
+            for k in names:
+                ctx.prof_read(k, reset=True)
+            ctx.sync()
             ev[0].record()
-            if not decode_only:
-                eb = enc.encode(built, kind, 0, dst=wire)
+            for _ in range(reps):
+                fn()
+            ctx.sync()
             ev[1].record()
-            dec.decode_into(eb.wire, eb.offsets, eb.lengths, kind, pool, dflags).close()
-            ev[2].record()
             torch.cuda.synchronize()
-            te += ev[0].elapsed_time(ev[1]) / reps
-            td += ev[1].elapsed_time(ev[2]) / reps
-        ctx.prof_enable(False)
-        alg = {abi.PK_VARINT_SIZE: in_bytes, abi.PK_VARINT_SCATTER: in_bytes + W, abi.PK_VARINT_COUNT: W, abi.PK_VARINT_GATHER: W + out_bytes}
-        kernels = {}
-        for k, nm in names.items():
-            n, ms = ctx.prof_read(k, reset=True)
-            if n and k in alg and not decode_only:  # (C5's wire is mostly fixed-width payload: no per-kernel figure)
-                gbs = alg[k] / (ms / n * 1e-3) / 1e9
-                kernels[nm] = {"avg_launch_ms": round(ms / n, 4), "algorithmic_GBps": round(gbs, 1), "frac_of_measured_peak": round(gbs / peak, 3)}
-        res = {"messages": len(msgs), "wire_MB": round(W / 1e6, 2), "values_MB": round(out_bytes / 1e6, 2),
-               "decode_ms": round(td, 4), "decode_wire_GBps": round(W / (td * 1e-3) / 1e9, 1),
-               "decode_algorithmic_GBps": round((W + out_bytes) / (td * 1e-3) / 1e9, 1), "kernels": kernels}
-        if not decode_only:
-            res.update({"encode_ms": round(te, 4), "encode_wire_GBps": round(W / (te * 1e-3) / 1e9, 1),
-                        "encode_algorithmic_GBps": round((in_bytes + W) / (te * 1e-3) / 1e9, 1),
-                        "encode_decode_wire_GBps": round(2 * W / ((te + td) * 1e-3) / 1e9, 1)})
+            ms = ev[0].elapsed_time(ev[1]) / reps
+            ctx.prof_enable(False)
+            top, top_ms = None, 0.0
+            for k, nm in names.items():
+                n, kms = ctx.prof_read(k, reset=True)
+                if n and kms / reps > top_ms:
+                    top, top_ms = nm, kms / reps
+            return ms, top, top_ms
+
+        res["wire_MB"] = round(W / 1e6, 2)
+        if encode:
+            alg = in_bytes + W
+            ms, top, top_ms = timed(lambda: enc.encode(built, kind, eflags, dst=wire), alg)
+            res.update({"enc_ms": round(ms, 4), "enc_GBps": round(alg / (ms * 1e-3) / 1e9, 1), "enc_frac": round(alg / (ms * 1e-3) / 1e9 / peak, 3),
+                        "enc_kernel": top, "enc_kernel_ms": round(top_ms, 4),
+                        "enc_kernel_frac": round(alg / (top_ms * 1e-3) / 1e9 / peak, 3) if top_ms else None})
+        if decode:
+            alg = W + out_bytes
+            ms, top, top_ms = timed(lambda: dec.decode_into(wire_t, offs, lens, kind, pool, dflags).close(), alg)
+            res.update({"dec_ms": round(ms, 4), "dec_GBps": round(alg / (ms * 1e-3) / 1e9, 1), "dec_frac": round(alg / (ms * 1e-3) / 1e9 / peak, 3),
+                        "dec_kernel": top, "dec_kernel_ms": round(top_ms, 4),
+                        "dec_kernel_frac": round(alg / (top_ms * 1e-3) / 1e9 / peak, 3) if top_ms else None})
+        res["values_MB"] = round(out_bytes / 1e6, 2)
         return res
+
+    def cpu_side(msgs_host, kind, budget_s=1.5, construct=False):
+        """The oracle port on (a sample of) the same inputs: wire GB/s of encode+decode, 1 thread and all cores.
+        construct=True also times the message construction (the reference's u8 -> f32 cast loop, src/lib.rs:237-242)."""
+        built = tfs.build_batch(msgs_host, kind)
+        t0 = time.perf_counter()
+        p = ob.Prepared(built)
+        t_build = time.perf_counter() - t0
+        out = {}
+        for label, th in (("cpu1_GBps", 1), ("cpuN_GBps", threads)):
+            tot_b = tot_s = 0.0
+            t_begin = time.perf_counter()
+            while True:
+                s_e, wb = p.run_encode(th)
+                s_d, wb2, _ = p.run_decode(th)
+                tot_b += wb + wb2
+                tot_s += s_e + s_d + (t_build / th if construct else 0.0)
+                if time.perf_counter() - t_begin > budget_s:
+                    break
+            out[label] = round(tot_b / tot_s / 1e9, 3)
+        p.close()
+        out["cpu_threads"] = threads
+        return out
+
+    def e2e_side(msgs_host, kind, eflags=0, dflags=0, reps=3):
+        """tfs_encode_host + tfs_decode_host_into on the host copies of the inputs: pinned wire / pool, then pageable"""
+        out = {}
+        built = tfs.build_batch(msgs_host, kind)
+        cap = enc.bound(built, eflags) + 4096
+        for label, pinned in (("e2e_pinned_GBps", True), ("e2e_pageable_GBps", False)):
+            if pinned:
+                keep_w, wbuf = _pin(np.empty(cap, np.uint8))
+            else:
+                wbuf = np.empty(cap, np.uint8)
+            eb = enc.encode_host(built, kind, eflags, dst=wbuf)
+            d = dec.decode_host(wbuf[: eb.total], eb.offsets, eb.lengths, kind, dflags)
+            pb = d.pool_bytes + 64
+            d.close()
+            if pinned:
+                keep_p, pbuf = _pin(np.empty(pb, np.uint8))
+            else:
+                pbuf = np.empty(pb, np.uint8)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            nbytes = 0
+            for _ in range(reps):
+                eb = enc.encode_host(built, kind, eflags, dst=wbuf)
+                dec.decode_host_into(wbuf[: eb.total], eb.offsets, eb.lengths, kind, pbuf, dflags).close()
+                nbytes += 2 * sum(eb.lengths)
+            torch.cuda.synchronize()
+            out[label] = round(nbytes / (time.perf_counter() - t0) / 1e9, 3)
+        return out
 
     out = {}
     g = torch.Generator(device=dev)
     g.manual_seed(3001)
-    R = 256
-    ids = torch.randint(0, 30522, (R, 256 * 512), device=dev, dtype=torch.int64, generator=g)
-    lens = torch.randint(1, 513, (R, 256, 1), device=dev, generator=g)
-    mask = (torch.arange(512, device=dev)[None, None, :] < lens).to(torch.int64).reshape(R, -1).contiguous()
+
+    # ---- C3: BERT input_ids + attention_mask, int64_val, 256 x 512 per request, 256 requests per launch
+    R3 = 256
+    ids = torch.randint(0, 30522, (R3, 256 * 512), device=dev, dtype=torch.int64, generator=g)
+    lens = torch.randint(1, 513, (R3, 256, 1), device=dev, generator=g)
+    mask = (torch.arange(512, device=dev)[None, None, :] < lens).to(torch.int64).reshape(R3, -1).contiguous()
     shape = tfs.TensorShapeProto([256, 512])
-    msgs = [tfs.PredictRequest(tfs.ModelSpec("bert", signature_name="serving_default"),
-                               [("input_ids", tfs.TensorProto(dtype=abi.DT_INT64, tensor_shape=shape, int64_val=ids[i])),
-                                ("attention_mask", tfs.TensorProto(dtype=abi.DT_INT64, tensor_shape=shape, int64_val=mask[i]))]) for i in range(R)]
-    out["C3 BERT input_ids+attention_mask int64_val 256x512, 256 requests"] = measure(msgs, abi.MSG_PREDICT_REQUEST, 2 * R * 256 * 512 * 8)
-    del ids, mask, msgs
+
+    def c3(idrow, mrow):
+        return tfs.PredictRequest(tfs.ModelSpec("bert", signature_name="serving_default"),
+                                  [("input_ids", tfs.TensorProto(dtype=abi.DT_INT64, tensor_shape=shape, int64_val=idrow)),
+                                   ("attention_mask", tfs.TensorProto(dtype=abi.DT_INT64, tensor_shape=shape, int64_val=mrow))])
+    r = device_side([c3(ids[i], mask[i]) for i in range(R3)], abi.MSG_PREDICT_REQUEST, 2 * R3 * 256 * 512 * 8)
+    n_host = 32
+    h_ids, h_mask = ids[:n_host].cpu().numpy(), mask[:n_host].cpu().numpy()
+    host_msgs = [c3(h_ids[i], h_mask[i]) for i in range(n_host)]
+    r.update(cpu_side(host_msgs, abi.MSG_PREDICT_REQUEST))
+    r.update(e2e_side(host_msgs, abi.MSG_PREDICT_REQUEST))
+    r["requests"], r["cpu_e2e_requests"] = R3, n_host
+    out["C3"] = r
+    del ids, mask, lens
+
+    # ---- C4: DT_HALF half_val, 2^20 elements from f32 (decode widens back to f32), 64 tensors per launch
     R4 = 64
     x = torch.randn(R4, 1 << 20, device=dev, generator=g)
-    msgs = [tfs.TensorProto(dtype=abi.DT_HALF, tensor_shape=tfs.TensorShapeProto([1 << 20]), half_val=tfs.Payload(x[i], abi.T_F32, abi.T_F16))
-            for i in range(R4)]
-    out["C4 DT_HALF half_val 2^20 elements from f32 (decode widens to f32), 64 tensors"] = measure(
-        msgs, abi.MSG_TENSOR_PROTO, R4 * (1 << 22), dflags=abi.F_HALF_TO_F32)
-    del x, msgs
-    # C5: the per-GPU share (1024 of 8192) of mixed-dtype PredictResponses, decoded
-    import numpy as np
-    rng = np.random.default_rng(5001)
-    msgs = []
-    for _ in range(1024):
-        entries = []
-        for j in range(int(rng.integers(1, 4))):
-            n = int(2 ** rng.uniform(0, 18))
-            sh = tfs.TensorShapeProto([1] * int(rng.integers(0, 4)) + [n])
-            which = int(rng.integers(0, 7))
-            if which == 0:
-                t = tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=sh, float_val=torch.randn(n, device=dev, generator=g))
-            elif which == 1:
-                t = tfs.TensorProto(dtype=abi.DT_DOUBLE, tensor_shape=sh, double_val=torch.randn(n, device=dev, generator=g, dtype=torch.float64))
-            elif which == 2:
-                v = torch.randint(-(1 << 31), 1 << 31, (n,), device=dev, generator=g, dtype=torch.int64).to(torch.int32)
-                t = tfs.TensorProto(dtype=abi.DT_INT32, tensor_shape=sh, int_val=v)
-            elif which == 3:
-                v = torch.randint(-(1 << 62), 1 << 62, (n,), device=dev, generator=g, dtype=torch.int64)
-                t = tfs.TensorProto(dtype=abi.DT_INT64, tensor_shape=sh, int64_val=v)
-            elif which == 4:
-                h = torch.randn(n, device=dev, generator=g).to(torch.float16)
-                t = tfs.TensorProto(dtype=abi.DT_HALF, tensor_shape=sh, half_val=h)
-            elif which == 5:
-                t = tfs.TensorProto(dtype=abi.DT_BOOL, tensor_shape=sh, bool_val=torch.rand(n, device=dev, generator=g) < 0.5)
-            else:
-                t = tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=sh, tensor_content=torch.randn(n, device=dev, generator=g))
-            entries.append((f"out{j}", t))
-        msgs.append(tfs.PredictResponse(entries, tfs.ModelSpec("mixed", version=int(rng.integers(1, 100)), signature_name="serving_default")))
-    out["C5 mixed-dtype PredictResponses, 1024 messages (one GPU's share of 8192), decode"] = measure(
-        msgs, abi.MSG_PREDICT_RESPONSE, 0, decode_only=True)
-    del msgs
 
-    # C1: the half_plus_two request (63 wire bytes), a large batch of copies: latency / descriptor bound by construction
+    def c4(row):
+        return tfs.TensorProto(dtype=abi.DT_HALF, tensor_shape=tfs.TensorShapeProto([1 << 20]), half_val=tfs.Payload(row, abi.T_F32, abi.T_F16))
+    r = device_side([c4(x[i]) for i in range(R4)], abi.MSG_TENSOR_PROTO, R4 * (1 << 22), dflags=abi.F_HALF_TO_F32)
+    n_host = 16
+    hx = x[:n_host].cpu().numpy()
+    host_msgs = [c4(hx[i]) for i in range(n_host)]
+    r.update(cpu_side(host_msgs, abi.MSG_TENSOR_PROTO))
+    r.update(e2e_side(host_msgs, abi.MSG_TENSOR_PROTO, dflags=abi.F_HALF_TO_F32))
+    r["requests"], r["cpu_e2e_requests"] = R4, n_host
+    out["C4"] = r
+    del x
+
+    # ---- C5: one GPU's share (1 024 of 8 192) of mixed-dtype PredictResponses, decode; the wire comes from the oracle and
+    #      the decoded values are checked against the oracle's once before anything is timed
+    msgs5 = workloads.c5_responses(1024, seed=5001, max_log2=18)
+    built5 = tfs.build_batch(msgs5, abi.MSG_PREDICT_RESPONSE)
+    wire5, offs5, lens5 = ob.encode(built5)
+    dwire5 = torch.from_numpy(wire5).to(dev)
+    d = dec.scan(dwire5, offs5, lens5, abi.MSG_PREDICT_RESPONSE)
+    pool5 = torch.empty(d.pool_bytes + 64, dtype=torch.uint8, device=dev)
+    d.close()
+    d = dec.decode_into(dwire5, offs5, lens5, abi.MSG_PREDICT_RESPONSE, pool5)
+    ctx.sync()
+    import helpers
+    st_o, want = ob.decode(wire5, offs5, lens5, abi.MSG_PREDICT_RESPONSE)
+    helpers.assert_same_decoded_fast(want, d.messages(), "response", "bench C5")
+    d.close()
+    del want, pool5
+    r = device_side(None, abi.MSG_PREDICT_RESPONSE, 0, decode_wire=(dwire5, offs5, lens5), encode=False)
+    r.update(cpu_side(msgs5, abi.MSG_PREDICT_RESPONSE, budget_s=2.0))
+    r.update(e2e_side(msgs5, abi.MSG_PREDICT_RESPONSE))
+    r["messages"] = 1024
+    r["checked_against_oracle"] = 1
+    out["C5"] = r
+    del dwire5, wire5, msgs5, built5
+
+    # ---- C2, back-to-back wire as tonic emits it (no TFS_F_ALIGN_PAYLOAD): payloads land at arbitrary byte phases
+    R2 = args.requests
+    src = torch.randn(R2, C2_ELEMS, device=dev, generator=g)
+    shape2 = tfs.TensorShapeProto([64, 224, 224, 3])
+
+    def c2(row, **kw):
+        return tfs.PredictRequest(tfs.ModelSpec("resnet", signature_name="serving_default"), [("input", tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=shape2, **kw))])
+    r = device_side([c2(None, float_val=src[i]) for i in range(R2)], abi.MSG_PREDICT_REQUEST, R2 * C2_ELEMS * 4)
+    n_host = 8
+    hs = src[:n_host].cpu().numpy()
+    host_msgs = [c2(None, float_val=hs[i]) for i in range(n_host)]
+    r.update(cpu_side(host_msgs, abi.MSG_PREDICT_REQUEST))
+    r.update(e2e_side(host_msgs, abi.MSG_PREDICT_REQUEST))
+    r["requests"], r["cpu_e2e_requests"] = R2, n_host
+    out["C2_unaligned"] = r
+
+    # ---- C2 with the f32 -> bf16 narrowing fused into the encode copy (tensor_content, DT_BFLOAT16), widened on decode
+    def c2bf(row):
+        return tfs.PredictRequest(tfs.ModelSpec("resnet", signature_name="serving_default"),
+                                  [("input", tfs.TensorProto(dtype=abi.DT_BFLOAT16, tensor_shape=shape2, tensor_content=tfs.Payload(row, abi.T_F32, abi.T_BF16)))])
+    r = device_side([c2bf(src[i]) for i in range(R2)], abi.MSG_PREDICT_REQUEST, R2 * C2_ELEMS * 4, eflags=abi.F_ALIGN_PAYLOAD,
+                    dflags=abi.F_CONTENT_HALF_TO_F32)
+    host_msgs = [c2bf(hs[i]) for i in range(n_host)]
+    r.update(cpu_side(host_msgs, abi.MSG_PREDICT_REQUEST, construct=True))  # (the narrowing loop is part of building the message)
+    r.update(e2e_side(host_msgs, abi.MSG_PREDICT_REQUEST, eflags=abi.F_ALIGN_PAYLOAD, dflags=abi.F_CONTENT_HALF_TO_F32))
+    r["requests"], r["cpu_e2e_requests"] = R2, n_host
+    out["C2_f32_to_bf16"] = r
+    del src
+
+    # ---- C2 built from u8 pixels: `*p as f32` and `/ 255.` fused into the encode copy (src/lib.rs:237-242), encode only
+    px = torch.randint(0, 256, (R2, C2_ELEMS), device=dev, dtype=torch.uint8, generator=g)
+
+    def c2u8(row):
+        return c2(None, float_val=tfs.Payload(row, abi.T_U8, abi.T_F32, abi.OP_DIV, 255.0))
+    r = device_side([c2u8(px[i]) for i in range(R2)], abi.MSG_PREDICT_REQUEST, R2 * C2_ELEMS, eflags=abi.F_ALIGN_PAYLOAD, decode=False)
+    hp = px[:n_host].cpu().numpy()
+    host_msgs = [c2u8(hp[i]) for i in range(n_host)]
+    r.update(cpu_side(host_msgs, abi.MSG_PREDICT_REQUEST, construct=True))
+    r.update(e2e_side(host_msgs, abi.MSG_PREDICT_REQUEST, eflags=abi.F_ALIGN_PAYLOAD))
+    r["requests"], r["cpu_e2e_requests"] = R2, n_host
+    out["C2_u8_to_f32"] = r
+    del px
+
+    # ---- C1: the half_plus_two request (63 wire bytes), 2^20 copies in one batch: descriptor / latency bound by construction
+    N1 = args.c1_messages
     x3 = torch.tensor([1.0, 2.0, 5.0], device=dev)
-    c1 = [tfs.PredictRequest(tfs.ModelSpec("half_plus_two", signature_name="serving_default"),
-                             [("x", tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=tfs.TensorShapeProto([3]), float_val=x3))]) for _ in range(16384)]
-    r1 = measure(c1, abi.MSG_PREDICT_REQUEST, 12 * 16384, reps=3)
-    r1["encode_msgs_per_s"] = round(16384 / (r1["encode_ms"] * 1e-3))
-    r1["decode_msgs_per_s"] = round(16384 / (r1["decode_ms"] * 1e-3))
-    out["C1 half_plus_two PredictRequest (63 B), 16 384 copies in one batch"] = r1
-    del c1
-
-    # DT_STRING tensors (string_val): encoded images, and short tokens
-    def string_requests(n_req, n_str, lo, hi):
-        msgs, in_bytes = [], 0
-        for _ in range(n_req):
-            lens = torch.randint(lo, hi + 1, (n_str,), device=dev, generator=g, dtype=torch.int64)
-            offs = torch.zeros(n_str + 1, device=dev, dtype=torch.int64)
-            offs[1:] = torch.cumsum(lens, 0)
-            total = int(offs[-1].item())
-            block = torch.empty(8 * (n_str + 1) + total, device=dev, dtype=torch.uint8)
-            block[: 8 * (n_str + 1)] = offs.view(torch.uint8)
-            block[8 * (n_str + 1):] = torch.randint(0, 256, (total,), device=dev, generator=g, dtype=torch.uint8)
-            t = tfs.TensorProto(dtype=abi.DT_STRING, tensor_shape=tfs.TensorShapeProto([n_str]), string_val=tfs.Ragged(block, n_str, total))
-            msgs.append(tfs.PredictRequest(tfs.ModelSpec("strings", signature_name="serving_default"), [("examples", t)]))
-            in_bytes += block.numel()
-        return msgs, in_bytes
-    msgs, nb = string_requests(64, 32, 100_000, 300_000)
-    out["DT_STRING string_val, 64 requests x 32 encoded images of 100-300 kB"] = measure(msgs, abi.MSG_PREDICT_REQUEST, nb, reps=3)
-    del msgs
-    # Classify / Regress inputs (section 8(f) row 1), encode only: 64 requests x 64 Examples x {ids int64[128], weights f32[128], tag bytes}
-    def classify_requests(n_req, n_ex, n_val):
-        reqs, in_bytes = [], 0
-        for r in range(n_req):
-            ids = torch.randint(0, 30522, (n_ex, n_val), device=dev, generator=g, dtype=torch.int64)
-            w = torch.randn(n_ex, n_val, device=dev, generator=g)
-            tag = tfs.ragged_block([b"label-%d" % (r % 7)])
-            tag_dev = torch.from_numpy(tag).to(dev)
-            exs = [[("ids", tfs.Feature(int64_list=ids[e])), ("weights", tfs.Feature(float_list=w[e])),
-                    ("tag", tfs.Feature(bytes_list=tfs.Ragged(tag_dev, 1, tag.size - 16)))] for e in range(n_ex)]
-            reqs.append(tfs.ClassificationRequest(tfs.ModelSpec("wide_deep", signature_name="classify"), tfs.Input(exs)))
-            in_bytes += n_ex * n_val * 12
-        return reqs, in_bytes
-    reqs, nb = classify_requests(64, 64, 128)
-    built = tfs.build_batch(reqs, abi.MSG_CLASSIFY_REQUEST)
-    wire = torch.empty(enc.bound(built, 0), dtype=torch.uint8, device=dev)
-    for _ in range(2):
-        eb = enc.encode(built, abi.MSG_CLASSIFY_REQUEST, 0, dst=wire)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for _ in range(3):
-        eb = enc.encode(built, abi.MSG_CLASSIFY_REQUEST, 0, dst=wire)
-    ev1.record()
-    torch.cuda.synchronize()
-    te = ev0.elapsed_time(ev1) / 3
-    W = sum(eb.lengths)
-    out["ClassificationRequest, 64 requests x 64 Examples x (int64[128] + f32[128] + 1 tag), encode"] = {
-        "messages": 64, "features": 64 * 64 * 3, "wire_MB": round(W / 1e6, 2), "encode_ms": round(te, 4),
-        "encode_wire_GBps": round(W / (te * 1e-3) / 1e9, 1), "encode_algorithmic_GBps": round((nb + W) / (te * 1e-3) / 1e9, 1),
-        "note": "12 288 features: framed by one GPU thread each (k_feature_layout / k_feature_write); most of the call is the host walking 12 288 descriptors and their name strings"}
-    del reqs, built, wire
-    msgs, nb = string_requests(64, 512, 0, 40)
-    out["DT_STRING string_val, 64 requests x 512 tokens of 0-40 bytes (the decode walk is serial per message: ~1.6 us per element)"] = measure(msgs, abi.MSG_PREDICT_REQUEST, nb, reps=3)
+    built1 = tfs.replicate_batch(tfs.build_batch([tfs.PredictRequest(tfs.ModelSpec("half_plus_two", signature_name="serving_default"),
+                                 [("x", tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=tfs.TensorShapeProto([3]), float_val=x3))])], abi.MSG_PREDICT_REQUEST), N1)
+    r = device_side(built1, abi.MSG_PREDICT_REQUEST, 12 * N1, reps=2)
+    r["enc_Mmsgs_per_s"] = round(N1 / (r["enc_ms"] * 1e-3) / 1e6, 2)
+    r["dec_Mmsgs_per_s"] = round(N1 / (r["dec_ms"] * 1e-3) / 1e6, 2)
+    n_host = 1 << 16
+    hx3 = np.array([1.0, 2.0, 5.0], np.float32)
+    hb1 = tfs.replicate_batch(tfs.build_batch([tfs.PredictRequest(tfs.ModelSpec("half_plus_two", signature_name="serving_default"),
+                              [("x", tfs.TensorProto(dtype=abi.DT_FLOAT, tensor_shape=tfs.TensorShapeProto([3]), float_val=hx3))])], abi.MSG_PREDICT_REQUEST), n_host)
+    p = ob.Prepared(hb1)
+    for label, th in (("cpu1", 1), ("cpuN", threads)):
+        s_e, wb = p.run_encode(th)
+        s_d, _, _ = p.run_decode(th)
+        r[f"{label}_GBps"] = round(2 * wb / (s_e + s_d) / 1e9, 3)
+        r[f"{label}_enc_Mmsgs_per_s"] = round(n_host / s_e / 1e6, 2)
+        r[f"{label}_dec_Mmsgs_per_s"] = round(n_host / s_d / 1e6, 2)
+    p.close()
+    r["cpu_threads"] = threads
+    r["messages"], r["cpu_messages"] = N1, n_host
+    out["C1"] = r
     return out
 
 
@@ -532,48 +633,44 @@ def cpu_pass(threads, n_msgs, reps_budget_s, min_reps=1):
     return total_b / total_s / 1e9, reps, total_s
 
 
-def cpu_baseline(R, budget_s=12.0):
-    cores = os.cpu_count() or 1
-    threads = max(1, min(cores, 16))
+def cpu_baseline_c2(budget_s=12.0):
+    threads = host_threads()
     n_msgs = threads
     gbs, reps, secs = cpu_pass(threads, n_msgs, budget_s)
-    return {"value": round(gbs, 3), "unit": UNIT, "cores": threads, "kind": "port",
-            "sample": f"{n_msgs} C2 requests per variant (one per thread), encode+decode, {reps} passes, {secs:.1f} s of CPU work; "
-                      f"oracle/cpu_ref.cpp = C++ port of prost 0.6.0's pass structure (prost itself: unavailable on this box, no rustc/cargo)",
-            "host_cores_available": cores}
+    gbs1, _, _ = cpu_pass(1, 1, min(2.0, budget_s))
+    return {"value": round(gbs, 3), "unit": UNIT, "cores": threads, "kind": "port", "one_thread_GBps": round(gbs1, 3),
+            "sample": f"{n_msgs} C2 requests per variant (one per thread), encode+decode, {reps} passes, {secs:.1f} s; oracle/cpu_ref.cpp (C++ port of prost 0.6.0)",
+            "host_cores_available": os.cpu_count() or 1}
 
 
 def run_reference(args):
+    """The reference's CPU path for the same metric: prost's algorithm as oracle/cpu_ref.cpp restates it (the Rust reference
+    cannot be built here: no rustc / cargo, crates not vendored), every host core, W warm-up + K timed steps; a step is a
+    bounded sample of the workload: one C2 request per host thread and variant, encoded then decoded."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cores = os.cpu_count() or 1
-    threads = max(1, min(cores, 64))
+    threads = host_threads()
     n_msgs = threads
-    # warm-up + K timed steps, each a bounded sample (one request per thread and variant)
-    per_step_budget = 0.0
     t0 = time.perf_counter()
-    for _ in range(max(0, min(args.warmup, 1))):
+    for _ in range(max(0, args.warmup)):
         cpu_pass(threads, n_msgs, 0.0)
-    steps = max(1, min(args.steps, 5))
+    steps = max(1, args.steps)
     tot_b = tot_s = 0.0
     for _ in range(steps):
-        gbs, reps, secs = cpu_pass(threads, n_msgs, per_step_budget)
+        gbs, reps, secs = cpu_pass(threads, n_msgs, 0.0)
         tot_b += gbs * secs
         tot_s += secs
     value = tot_b / tot_s
-    sample = (f"{n_msgs} C2 requests per variant per step (one per host thread), {steps} steps, oracle/cpu_ref.cpp "
-              f"(C++ port of prost 0.6.0; the Rust reference cannot be built here: no rustc/cargo, crates not vendored)")
+    sample = f"{n_msgs} C2 requests per variant per step (one per host thread); oracle/cpu_ref.cpp, C++ port of prost 0.6.0"
     line = {"impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-            "warmup": min(args.warmup, 1), "ms_per_step": round(tot_s / steps * 1e3, 3), "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-            "config": {"workload": workload_name(args.requests), "requests_per_variant_per_gpu": args.requests,
-                       "wire_bytes_per_request": C2_WIRE, "sample_requests_per_variant_per_step": n_msgs},
+            "warmup": max(0, args.warmup), "ms_per_step": round(tot_s / steps * 1e3, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config_of(args, args.gpus),
             "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
-                             "host_cores_available": cores},
-            "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "wall_s": round(time.perf_counter() - t0, 1)}
+                             "host_cores_available": os.cpu_count() or 1},
+            "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+    print(f"reference arm wall time {time.perf_counter() - t0:.1f} s", file=sys.stderr)
 
 
 def main():
@@ -583,9 +680,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--requests", type=int, default=32, help="C2 requests per variant, per GPU and per step")
-    ap.add_argument("--e2e-requests", type=int, default=8)
-    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU baseline sampling")
-    ap.add_argument("--no-extras", action="store_true", help="skip the C3 / C4 / C5 side measurements (N = 1 only)")
+    ap.add_argument("--e2e-requests", type=int, default=32)
+    ap.add_argument("--cpu-budget", type=float, default=8.0, help="seconds of CPU baseline sampling")
+    ap.add_argument("--sustain-s", type=float, default=1.5, help="length of the sustained C2 side loop (0 = skip)")
+    ap.add_argument("--c1-messages", type=int, default=1 << 20)
+    ap.add_argument("--no-extras", action="store_true", help="skip the per-config side measurements (N = 1 only)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":

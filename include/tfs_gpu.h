@@ -314,7 +314,8 @@ enum {
   TFS_PK_VARINT_GATHER = 4,  /* K4c */
   TFS_PK_COPY_TMA = 5,       /* K5, TMA ring (source and destination congruent mod 16) */
   TFS_PK_WALK = 6,           /* K6d, small-batch decode plan (both structure walks) */
-  TFS_PK_FRAME = 7           /* K6a-c, small-batch encode framing */
+  TFS_PK_FRAME = 7,          /* K6a-c, small-batch encode framing */
+  TFS_PK_COPY_CAST = 8       /* K5 / K7, staged widening / narrowing copies (u8 -> f32, f32 <-> f16 / bf16) */
 };
 tfs_status_t tfs_prof_enable(tfs_ctx_t* ctx, int32_t on);
 tfs_status_t tfs_prof_read(tfs_ctx_t* ctx, int32_t kernel_id, uint64_t* launches_out, double* ms_out, int32_t reset);
@@ -400,6 +401,93 @@ tfs_status_t tfs_decode_host_finish(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* po
 tfs_status_t tfs_decode_host_into(tfs_ctx_t* ctx, const void* wire_host, uint64_t wire_bytes, const uint64_t* msg_off,
                                   const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_host,
                                   uint64_t pool_capacity, tfs_decoded_t** out);
+
+/* ----------------------------------------------------------------------------------------------
+ * Pinned-host staging pool: the bridge between tonic's byte buffers and HBM.  Replaces nothing in the reference
+ * (its buffers are tonic's BytesMut, grown by `reserve`, src/lib.rs:265 via ProstEncoder); it is created where
+ * the reference creates its channels (src/lib.rs:132-138) and serves the codec at the call site (:265).
+ *
+ * `tfs_ctx_create(device, pinned_bytes, ..)` pins one region of that size ONCE; slabs are carved from it in
+ * power-of-two classes (4 KiB up) and recycled, so acquiring one on the request path is a lock and a pop - no
+ * cudaHostAlloc (which synchronises the device).  A request larger than what is left falls back to a one-off pinned
+ * allocation that is freed again on release.  Thread-safe.
+ *
+ * `align_skew`: the returned pointer is congruent to it modulo 16.  A received message whose bulk payload starts
+ * `h` bytes into it is placed at skew (16 - h % 16) % 16: the payload then sits on a 16-byte boundary and decodes
+ * through the TMA ring instead of the byte-shifting copy (on encode TFS_F_ALIGN_PAYLOAD does the same inside dst).
+ * -------------------------------------------------------------------------------------------- */
+typedef struct {
+  void* ptr;         /* pinned host memory, usable by the *_host entry points without staging */
+  uint64_t capacity; /* bytes available at ptr */
+  uint64_t id;       /* opaque: hand the struct back unchanged */
+} tfs_slab_t;
+tfs_status_t tfs_stage_acquire(tfs_ctx_t* ctx, uint64_t bytes, uint32_t align_skew, tfs_slab_t* out);
+tfs_status_t tfs_stage_release(tfs_ctx_t* ctx, const tfs_slab_t* slab);
+/* bytes of the pool currently handed out / its size / how many acquires had to fall back to a one-off allocation */
+tfs_status_t tfs_stage_stats(tfs_ctx_t* ctx, uint64_t* in_use, uint64_t* pool_bytes, uint64_t* fallbacks);
+
+/* ----------------------------------------------------------------------------------------------
+ * Engine: worker threads over one or several GPUs, asynchronous submission, request coalescing.
+ *
+ * The reference's client is `Clone` and is used from concurrent tokio tasks (src/lib.rs:148-156,
+ * examples/async.rs:29-46), every task sending ONE request per call (src/lib.rs:265).  A tfs_ctx_t is neither
+ * re-entrant nor asynchronous; the engine puts `lanes_per_device` contexts on each listed GPU, each with its own
+ * stream, staging pool and host worker thread.  A submitted job runs the ordinary host entry point
+ * (tfs_encode_host / tfs_decode_host_into) on a lane's thread, so the upload of one job overlaps the download of
+ * the previous one, and several GPUs work at once from ONE client process.  Requests are independent: no
+ * collective, no peer access; every GPU touches only its own memory.
+ *
+ * All arrays handed to a submit call (descriptors, payloads, output arrays, destination) must stay valid until
+ * tfs_engine_wait() has returned for its ticket.  Tickets may be waited for in any order, from any thread, once.
+ * -------------------------------------------------------------------------------------------- */
+typedef struct tfs_engine tfs_engine_t;
+typedef uint64_t tfs_ticket_t;
+tfs_status_t tfs_engine_create(const int32_t* devices, uint32_t n_devices, uint32_t lanes_per_device, uint64_t pinned_bytes_per_lane,
+                               tfs_engine_t** out);
+tfs_status_t tfs_engine_destroy(tfs_engine_t* eng);
+uint32_t tfs_engine_lanes(const tfs_engine_t* eng);
+/* The context of lane `lane` (for its staging pool: tfs_stage_acquire / release are thread-safe; do not call compute
+ * entry points on it while jobs are in flight). */
+tfs_ctx_t* tfs_engine_ctx(tfs_engine_t* eng, uint32_t lane);
+/* Asynchronous forms of tfs_encode_host / tfs_decode_host_into.  `lane` = -1: the lane with the fewest bytes queued. */
+tfs_status_t tfs_engine_encode_host(tfs_engine_t* eng, int32_t lane, const tfs_batch_t* batch, void* dst_host, uint64_t dst_capacity,
+                                    uint32_t flags, uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out,
+                                    tfs_ticket_t* ticket);
+tfs_status_t tfs_engine_decode_host_into(tfs_engine_t* eng, int32_t lane, const void* wire_host, uint64_t wire_bytes,
+                                         const uint64_t* msg_off, const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind,
+                                         uint32_t flags, void* pool_host, uint64_t pool_capacity, tfs_decoded_t** out,
+                                         tfs_ticket_t* ticket);
+/* Blocks until the job is done and returns ITS status (what the synchronous entry point would have returned);
+ * detail_out (optional, >= 256 bytes) receives the lane's error text.  A decode handle is freed with
+ * tfs_engine_decoded_free (it belongs to the lane that made it). */
+tfs_status_t tfs_engine_wait(tfs_engine_t* eng, tfs_ticket_t ticket, char* detail_out);
+tfs_status_t tfs_engine_decoded_free(tfs_engine_t* eng, tfs_decoded_t* dec);
+/* A batch of independent messages decoded on ALL lanes at once (BASELINE config 5: 8 192 responses over 8 GPUs).  The
+ * messages are cut into tfs_engine_lanes() contiguous runs of about equal bytes (tfs_shard_ranges); run r is decoded by
+ * lane r into pool_host[r] (capacity pool_capacity[r]) and described by out[r], whose message / tensor indices count
+ * from the run's first message, first_msg_out[r].  Synchronous; returns the first non-OK status among the runs. */
+tfs_status_t tfs_engine_decode_host_sharded(tfs_engine_t* eng, const void* wire_host, uint64_t wire_bytes, const uint64_t* msg_off,
+                                            const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags,
+                                            void* const* pool_host, const uint64_t* pool_capacity, tfs_decoded_t** out,
+                                            uint32_t* first_msg_out);
+/* Contiguous split of n_msgs messages into n_shards runs of about equal bytes: first_out[s] = index of run s's first
+ * message (first_out[n_shards] = n_msgs).  Host only. */
+tfs_status_t tfs_shard_ranges(const uint64_t* msg_bytes, uint32_t n_msgs, uint32_t n_shards, uint32_t* first_out);
+
+/* Coalescer: callers that each hold ONE message (the reference's call site, src/lib.rs:265) are gathered into one
+ * batch per window - every roofline figure of this library is per launch over a batch.  tfs_coalescer_encode blocks
+ * until the batch its message joined has been encoded; the bytes are handed over IN PLACE: *wire_out points into a
+ * pinned slab shared by the batch (what the transport sends from, no copy in between), valid until the caller
+ * releases its reference with tfs_coalescer_release.  Thread-safe; a batch closes when `max_msgs` messages have
+ * joined or `window_us` microseconds after its first one. */
+typedef struct tfs_coalescer tfs_coalescer_t;
+tfs_status_t tfs_coalescer_create(tfs_engine_t* eng, uint32_t window_us, uint32_t max_msgs, tfs_coalescer_t** out);
+tfs_status_t tfs_coalescer_destroy(tfs_coalescer_t* co);
+tfs_status_t tfs_coalescer_encode(tfs_coalescer_t* co, const tfs_batch_t* one_message, uint32_t flags, const uint8_t** wire_out,
+                                  uint64_t* len_out, uint64_t* lease_out);
+tfs_status_t tfs_coalescer_release(tfs_coalescer_t* co, uint64_t lease);
+/* batches launched / messages encoded so far */
+tfs_status_t tfs_coalescer_stats(tfs_coalescer_t* co, uint64_t* batches, uint64_t* messages);
 
 /* ----------------------------------------------------------------------------------------------
  * Allocation-free packing of one int64 array (no counterpart in the reference: the reference never

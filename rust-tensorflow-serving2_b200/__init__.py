@@ -7,10 +7,10 @@ There is no CPU fallback: using the codec without the built library or without a
 """
 from . import abi, messages, workloads, _lib, codec, sharding  # noqa: F401  (all submodules, so aliases of the package see them)
 from ._lib import TfsError  # noqa: F401
-from .codec import GpuCodec, GpuContext, GpuDecoder, GpuEncoder  # noqa: F401
+from .codec import Coalescer, Engine, GpuCodec, GpuContext, GpuDecoder, GpuEncoder, Slab  # noqa: F401
 from .messages import (  # noqa: F401
     ClassificationRequest, Feature, Input, ModelSpec, Payload, PredictRequest, PredictResponse, Ragged, TensorProto, TensorShapeProto, build_batch, ragged_block,
-    messages_from_view,
+    messages_from_view, replicate_batch, BuiltBatch,
 )
 
 __all__ = ["abi", "workloads", "codec", "ModelSpec", "Payload", "PredictRequest", "PredictResponse", "TensorProto",

@@ -78,11 +78,33 @@ def lib():
     L.tfs_type_size.restype = C.c_uint32
     L.tfs_type_size.argtypes = [C.c_int32]
     L.tfs_pack_int64_noalloc.argtypes = [vp, C.c_uint64, vp, C.c_uint64, vp, vp]
+    L.tfs_stage_acquire.argtypes = [vp, C.c_uint64, C.c_uint32, C.POINTER(abi.Slab)]
+    L.tfs_stage_release.argtypes = [vp, C.POINTER(abi.Slab)]
+    L.tfs_stage_stats.argtypes = [vp, u64p, u64p, u64p]
+    L.tfs_engine_create.argtypes = [C.POINTER(C.c_int32), C.c_uint32, C.c_uint32, C.c_uint64, C.POINTER(vp)]
+    L.tfs_engine_destroy.argtypes = [vp]
+    L.tfs_engine_lanes.restype = C.c_uint32
+    L.tfs_engine_lanes.argtypes = [vp]
+    L.tfs_engine_ctx.restype = vp
+    L.tfs_engine_ctx.argtypes = [vp, C.c_uint32]
+    L.tfs_engine_encode_host.argtypes = [vp, C.c_int32, C.POINTER(abi.Batch), vp, C.c_uint64, C.c_uint32, u64p, u64p, u64p, u64p]
+    L.tfs_engine_decode_host_into.argtypes = [vp, C.c_int32, vp, C.c_uint64, u64p, u64p, C.c_uint32, C.c_int32, C.c_uint32, vp, C.c_uint64,
+                                              C.POINTER(vp), u64p]
+    L.tfs_engine_wait.argtypes = [vp, C.c_uint64, C.c_char_p]
+    L.tfs_engine_decoded_free.argtypes = [vp, vp]
+    L.tfs_engine_decode_host_sharded.argtypes = [vp, vp, C.c_uint64, u64p, u64p, C.c_uint32, C.c_int32, C.c_uint32, C.POINTER(vp), u64p,
+                                                 C.POINTER(vp), u32p]
+    L.tfs_shard_ranges.argtypes = [u64p, C.c_uint32, C.c_uint32, u32p]
+    L.tfs_coalescer_create.argtypes = [vp, C.c_uint32, C.c_uint32, C.POINTER(vp)]
+    L.tfs_coalescer_destroy.argtypes = [vp]
+    L.tfs_coalescer_encode.argtypes = [vp, C.POINTER(abi.Batch), C.c_uint32, C.POINTER(vp), u64p, u64p]
+    L.tfs_coalescer_release.argtypes = [vp, C.c_uint64]
+    L.tfs_coalescer_stats.argtypes = [vp, u64p, u64p]
     L.tfs_prof_enable.argtypes = [vp, C.c_int32]
     L.tfs_prof_read.argtypes = [vp, C.c_int32, u64p, C.POINTER(C.c_double), C.c_int32]
     for name in abi.EXPORTED_SYMBOLS:
         fn = getattr(L, name)
-        if fn.restype is C.c_int and name not in ("tfs_abi_version", "tfs_slot_of_kind", "tfs_kind_of_slot"):
+        if fn.restype is C.c_int and name not in ("tfs_abi_version", "tfs_slot_of_kind", "tfs_kind_of_slot", "tfs_engine_lanes", "tfs_engine_ctx"):
             fn.restype = C.c_int32
     _lib = L
     return L

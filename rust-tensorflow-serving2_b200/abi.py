@@ -144,9 +144,21 @@ EXPORTED_SYMBOLS = (
     "tfs_decode_host", "tfs_decode_host_finish", "tfs_shard_plan", "tfs_slot_of_kind", "tfs_kind_of_slot",
     "tfs_type_size", "tfs_prof_enable", "tfs_prof_read", "tfs_pack_int64_noalloc", "tfs_decode_into", "tfs_decode_host_into",
     "tfs_last_error_location",
+    "tfs_stage_acquire", "tfs_stage_release", "tfs_stage_stats", "tfs_engine_create", "tfs_engine_destroy", "tfs_engine_lanes",
+    "tfs_engine_ctx", "tfs_engine_encode_host", "tfs_engine_decode_host_into", "tfs_engine_wait", "tfs_engine_decoded_free",
+    "tfs_engine_decode_host_sharded", "tfs_shard_ranges", "tfs_coalescer_create", "tfs_coalescer_destroy", "tfs_coalescer_encode",
+    "tfs_coalescer_release", "tfs_coalescer_stats",
 )
+
+
+class Slab(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("capacity", C.c_uint64), ("id", C.c_uint64)]
 TFS_ERR_TOO_LARGE = 24
 TFS_NOALLOC_MAX_ELEMS = 1 << 24
 STATUS_NAMES[TFS_ERR_TOO_LARGE] = "input exceeds TFS_NOALLOC_MAX_ELEMS"
 
 PK_COPY, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_COPY_TMA, PK_WALK, PK_FRAME = range(8)
+PK_COPY_CAST = 8
+PK_COUNT = 9
+PK_NAMES = {PK_COPY: "k_copy", PK_VARINT_SIZE: "k_varint_size", PK_VARINT_SCATTER: "k_varint_scatter", PK_VARINT_COUNT: "k_varint_count",
+            PK_VARINT_GATHER: "k_varint_gather", PK_COPY_TMA: "k_copy_tma", PK_WALK: "walk", PK_FRAME: "frame", PK_COPY_CAST: "k_copy_cast"}

@@ -269,3 +269,175 @@ class GpuCodec:
 
     def decoder(self) -> GpuDecoder:
         return GpuDecoder(self.ctx)
+
+
+# ------------------------------------------------------------------------------------------------
+# staging pool, engine (worker threads over one or several GPUs), coalescer
+# ------------------------------------------------------------------------------------------------
+class Slab:
+    """A pinned slab out of a context's staging pool (tfs_stage_acquire): `.array` is a numpy uint8 view of it."""
+
+    def __init__(self, ctx_handle, nbytes: int, align_skew: int = 0):
+        self._ctx = ctx_handle
+        self.raw = abi.Slab()
+        st = lib().tfs_stage_acquire(ctx_handle, nbytes, align_skew, C.byref(self.raw))
+        if st != abi.TFS_OK:
+            raise TfsError(st, "tfs_stage_acquire")
+        self.array = np.ctypeslib.as_array(C.cast(self.raw.ptr, C.POINTER(C.c_uint8)), shape=(int(self.raw.capacity),))
+
+    @property
+    def address(self) -> int:
+        return int(self.raw.ptr)
+
+    def release(self):
+        if self.raw.ptr:
+            lib().tfs_stage_release(self._ctx, C.byref(self.raw))
+            self.raw = abi.Slab()
+            self.array = None
+
+
+class Engine:
+    """tfs_engine_t: `lanes_per_device` contexts (stream + staging pool + host worker thread each) on every listed GPU;
+    jobs are submitted asynchronously and waited for by ticket."""
+
+    def __init__(self, devices: Sequence[int], lanes_per_device: int = 2, pinned_bytes_per_lane: int = 0):
+        self._h = C.c_void_p()
+        arr = (C.c_int32 * len(devices))(*devices)
+        st = lib().tfs_engine_create(arr, len(devices), lanes_per_device, pinned_bytes_per_lane, C.byref(self._h))
+        if st != abi.TFS_OK:
+            raise TfsError(st, "tfs_engine_create")
+        self._keep = {}
+
+    @property
+    def lanes(self) -> int:
+        return int(lib().tfs_engine_lanes(self._h))
+
+    def lane_ctx(self, lane: int):
+        return C.c_void_p(lib().tfs_engine_ctx(self._h, lane))
+
+    def slab(self, lane: int, nbytes: int, align_skew: int = 0) -> Slab:
+        return Slab(self.lane_ctx(lane), nbytes, align_skew)
+
+    def encode_host(self, built: BuiltBatch, dst: np.ndarray, flags: int = 0, lane: int = -1) -> int:
+        """-> ticket; `wait_encode(ticket)` returns the EncodedBatch"""
+        n = built.n_msgs
+        off, ln, total = (C.c_uint64 * max(1, n))(), (C.c_uint64 * max(1, n))(), C.c_uint64(0)
+        t = C.c_uint64(0)
+        st = lib().tfs_engine_encode_host(self._h, lane, C.byref(built.batch), C.c_void_p(dst.ctypes.data), dst.size, flags, off, ln, C.byref(total), C.byref(t))
+        if st != abi.TFS_OK:
+            raise TfsError(st, "tfs_engine_encode_host")
+        self._keep[t.value] = ("enc", built, dst, off, ln, total, flags, n)
+        return int(t.value)
+
+    def decode_host_into(self, wire: np.ndarray, offsets, lengths, kind: int, pool: np.ndarray, flags: int = 0, lane: int = -1) -> int:
+        n, off, ln = GpuDecoder._arrays(offsets, lengths)
+        h, t = C.c_void_p(), C.c_uint64(0)
+        hp = C.pointer(h)
+        st = lib().tfs_engine_decode_host_into(self._h, lane, C.c_void_p(wire.ctypes.data if wire.size else 0), wire.size, off, ln, n, kind, flags,
+                                               C.c_void_p(pool.ctypes.data), pool.size, hp, C.byref(t))
+        if st != abi.TFS_OK:
+            raise TfsError(st, "tfs_engine_decode_host_into")
+        self._keep[t.value] = ("dec", wire, off, ln, pool, h, hp, kind)
+        return int(t.value)
+
+    def wait(self, ticket: int):
+        """Blocks until the job is done: an EncodedBatch for an encode ticket, an EngineDecoded for a decode ticket."""
+        detail = C.create_string_buffer(256)
+        st = lib().tfs_engine_wait(self._h, ticket, detail)
+        rec = self._keep.pop(ticket)
+        if rec[0] == "enc":
+            _, built, dst, off, ln, total, flags, n = rec
+            if st != abi.TFS_OK:
+                raise TfsError(st, detail.value.decode("utf-8", "replace"))
+            return EncodedBatch(dst, np.ctypeslib.as_array(off)[:n].astype(np.int64).tolist(), np.ctypeslib.as_array(ln)[:n].astype(np.int64).tolist(),
+                                int(total.value), flags)
+        _, wire, off, ln, pool, h, hp, kind = rec
+        if st not in (abi.TFS_OK, abi.TFS_ERR_BATCH):
+            if h:
+                lib().tfs_engine_decoded_free(self._h, h)
+            raise TfsError(st, detail.value.decode("utf-8", "replace"))
+        return EngineDecoded(self, h, st, kind, pool)
+
+    def decode_host_sharded(self, wire: np.ndarray, offsets, lengths, kind: int, pools: Sequence[np.ndarray], flags: int = 0):
+        """One batch over all lanes (tfs_engine_decode_host_sharded) -> (status, [EngineDecoded or None per lane], first message per lane)"""
+        n, off, ln = GpuDecoder._arrays(offsets, lengths)
+        L = self.lanes
+        pp = (C.c_void_p * L)(*[p.ctypes.data for p in pools])
+        pc = (C.c_uint64 * L)(*[p.size for p in pools])
+        outs = (C.c_void_p * L)()
+        first = (C.c_uint32 * L)()
+        st = lib().tfs_engine_decode_host_sharded(self._h, C.c_void_p(wire.ctypes.data if wire.size else 0), wire.size, off, ln, n, kind, flags, pp, pc, outs, first)
+        if st not in (abi.TFS_OK, abi.TFS_ERR_BATCH):
+            for i in range(L):
+                if outs[i]:
+                    lib().tfs_engine_decoded_free(self._h, C.c_void_p(outs[i]))
+            raise TfsError(st, "tfs_engine_decode_host_sharded")
+        res = [EngineDecoded(self, C.c_void_p(outs[i]), st, kind, pools[i]) if outs[i] else None for i in range(L)]
+        return st, res, [int(first[i]) for i in range(L)]
+
+    def close(self):
+        if self._h:
+            lib().tfs_engine_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class EngineDecoded:
+    """Decode result of an engine job (the handle belongs to the lane that made it)."""
+
+    def __init__(self, eng: Engine, handle, status: int, kind: int, pool: np.ndarray):
+        self.eng, self._h, self.status, self.kind, self.pool = eng, handle, status, kind, pool
+        self.view = abi.DecodedView()
+        st = lib().tfs_decoded_view(self._h, C.byref(self.view))
+        if st != abi.TFS_OK:
+            raise TfsError(st, "tfs_decoded_view")
+
+    @property
+    def pool_bytes(self) -> int:
+        return int(self.view.pool_bytes)
+
+    def messages(self) -> List[DecodedMessage]:
+        return messages_from_view(self.view, self.pool, self.kind)
+
+    def close(self):
+        if self._h:
+            lib().tfs_engine_decoded_free(self.eng._h, self._h)
+            self._h = C.c_void_p()
+
+
+class Coalescer:
+    """tfs_coalescer_t: single-message encode calls from many threads, one batch (one launch) per window."""
+
+    def __init__(self, eng: Engine, window_us: int = 200, max_msgs: int = 64):
+        self.eng = eng
+        self._h = C.c_void_p()
+        st = lib().tfs_coalescer_create(eng._h, window_us, max_msgs, C.byref(self._h))
+        if st != abi.TFS_OK:
+            raise TfsError(st, "tfs_coalescer_create")
+
+    def encode(self, message, kind: int, flags: int = 0) -> bytes:
+        """Blocks until the batch this message joined is encoded; returns a COPY of its bytes (and releases the lease: a
+        transport would send straight from the pinned slab and release afterwards)."""
+        built = build_batch([message], kind)
+        wire, ln, lease = C.c_void_p(), C.c_uint64(0), C.c_uint64(0)
+        st = lib().tfs_coalescer_encode(self._h, C.byref(built.batch), flags, C.byref(wire), C.byref(ln), C.byref(lease))
+        if st != abi.TFS_OK:
+            raise TfsError(st, "tfs_coalescer_encode")
+        out = C.string_at(wire, ln.value)
+        lib().tfs_coalescer_release(self._h, lease)
+        return out
+
+    def stats(self):
+        b, m = C.c_uint64(0), C.c_uint64(0)
+        lib().tfs_coalescer_stats(self._h, C.byref(b), C.byref(m))
+        return int(b.value), int(m.value)
+
+    def close(self):
+        if self._h:
+            lib().tfs_coalescer_destroy(self._h)
+            self._h = C.c_void_p()

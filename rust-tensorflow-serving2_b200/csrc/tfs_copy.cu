@@ -139,6 +139,14 @@ __device__ __forceinline__ bool tma_eligible(const CopySeg& s) {
          ((reinterpret_cast<uintptr_t>(s.src) ^ reinterpret_cast<uintptr_t>(s.dst)) & 15u) == 0;
 }
 
+// Widening / narrowing segments large enough for the staged cast kernel below (k_copy_cast); the source has to be aligned
+// to its element size (anything else stays with the element-wise loop of k_copy).
+constexpr uint64_t kCastMinElems = 1024;
+__device__ __forceinline__ bool is_cast_op(int32_t op) { return op >= CP_U8_F32 && op <= CP_BF16_F32; }
+__device__ __forceinline__ bool cast_eligible(const CopySeg& s) {
+  return is_cast_op(s.op) && s.n >= kCastMinElems && (reinterpret_cast<uintptr_t>(s.src) & (in_size_of(s.op) - 1u)) == 0;
+}
+
 __global__ void __launch_bounds__(kCopyThreads) k_copy(const CopySeg* __restrict__ segs, uint32_t n_segs, uint64_t n_tiles,
                                                         const uint64_t* __restrict__ gate, uint64_t src_lo, uint64_t src_hi,
                                                         uint64_t tile_begin) {
@@ -152,7 +160,7 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy(const CopySeg* __restrict
   }
   __syncthreads();
   const CopySeg seg = segs[s_seg];
-  if (seg.n == 0 || tma_eligible(seg)) return;  // the TMA ring owns this segment
+  if (seg.n == 0 || tma_eligible(seg) || cast_eligible(seg)) return;  // the TMA ring / the staged cast kernel owns this segment
   uint64_t e0, e1;
   tile_range(seg, tile - seg.first_tile, &e0, &e1);
   if (e0 >= e1) return;
@@ -332,24 +340,188 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
   if (leader) tma_wait_all();
 }
 
+// ---------------------------------------------------------------------------------------------------
+// staged casts: u8 -> f32 (x 1, / p, * p), f32 -> f16 / bf16, f16 / bf16 -> f32.  One CTA per 32 KiB tile of OUTPUT.
+//   in   one cp.async.bulk (TMA) brings the 16-byte aligned window around the tile's source elements into shared memory
+//        (mbarrier complete_tx);
+//   cast all 8 warps convert from shared memory, 4 elements per step on aligned vectors, into an output stage whose
+//        first element is padded so that the groups stay vector-aligned;
+//   out  when the stage and the destination are congruent mod 16 (TFS_F_ALIGN_PAYLOAD, the 64-byte aligned value pool)
+//        the interior leaves with one cp.async.bulk shared -> global; otherwise every thread shifts 16 staged bytes
+//        onto the destination's 16-byte grid (two vector loads, funnel shifts) and stores them.
+// u8 -> f32 with a scale goes through a 256-entry table built with the same IEEE operation (__fdiv_rn / __fmul_rn) the
+// element-wise path uses: bit-identical results, no division per pixel.
+// ---------------------------------------------------------------------------------------------------
+constexpr uint32_t kCastPad = 64;  // slack around both stages (window alignment, group padding, flush over-read)
+
+template <int OP>
+__device__ __forceinline__ void cast_group(const uint8_t* in, uint8_t* out, const float* lut) {
+  // 4 elements: `in` / `out` are aligned to 4 input / output elements
+  if constexpr (OP == CP_U8_F32 || OP == CP_U8_F32_DIV || OP == CP_U8_F32_MUL) {
+    const uint32_t w = *reinterpret_cast<const uint32_t*>(in);
+    float4 r;
+    if constexpr (OP == CP_U8_F32) {
+      r = make_float4(static_cast<float>(w & 0xFFu), static_cast<float>((w >> 8) & 0xFFu), static_cast<float>((w >> 16) & 0xFFu), static_cast<float>(w >> 24));
+    } else {
+      r = make_float4(lut[w & 0xFFu], lut[(w >> 8) & 0xFFu], lut[(w >> 16) & 0xFFu], lut[w >> 24]);
+    }
+    *reinterpret_cast<float4*>(out) = r;
+  } else if constexpr (OP == CP_F32_F16 || OP == CP_F32_BF16) {
+    const float4 v = *reinterpret_cast<const float4*>(in);
+    uint32_t a, b, c, d;
+    if constexpr (OP == CP_F32_F16) {
+      a = f32_to_f16_bits(v.x); b = f32_to_f16_bits(v.y); c = f32_to_f16_bits(v.z); d = f32_to_f16_bits(v.w);
+    } else {
+      a = f32_to_bf16_bits(v.x); b = f32_to_bf16_bits(v.y); c = f32_to_bf16_bits(v.z); d = f32_to_bf16_bits(v.w);
+    }
+    *reinterpret_cast<uint2*>(out) = make_uint2(a | (b << 16), c | (d << 16));
+  } else {
+    const uint2 w = *reinterpret_cast<const uint2*>(in);
+    float4 r;
+    if constexpr (OP == CP_F16_F32) {
+      r = make_float4(f16_bits_to_f32(w.x & 0xFFFFu), f16_bits_to_f32(w.x >> 16), f16_bits_to_f32(w.y & 0xFFFFu), f16_bits_to_f32(w.y >> 16));
+    } else {
+      r = make_float4(bf16_bits_to_f32(w.x & 0xFFFFu), bf16_bits_to_f32(w.x >> 16), bf16_bits_to_f32(w.y & 0xFFFFu), bf16_bits_to_f32(w.y >> 16));
+    }
+    *reinterpret_cast<float4*>(out) = r;
+  }
+}
+
+template <int OP>
+__device__ __forceinline__ void cast_tile(const CopySeg& seg, uint64_t e0, uint32_t n, uint8_t* sm_in, uint8_t* sm_out, uint64_t* bar, const float* lut) {
+  constexpr uint32_t IS = (OP == CP_F32_F16 || OP == CP_F32_BF16) ? 4u : (OP == CP_F16_F32 || OP == CP_BF16_F32) ? 2u : 1u;
+  constexpr uint32_t OS = (OP == CP_F32_F16 || OP == CP_F32_BF16) ? 2u : 4u;
+  const uint64_t s_abs = reinterpret_cast<uintptr_t>(seg.src) + e0 * IS;
+  const uint64_t s_lo = s_abs & ~static_cast<uint64_t>(15);
+  const uint32_t in_bytes = static_cast<uint32_t>(((s_abs + static_cast<uint64_t>(n) * IS + 15u) & ~static_cast<uint64_t>(15)) - s_lo);
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(bar, in_bytes);
+    tma_load(sm_in, reinterpret_cast<const void*>(s_lo), in_bytes, bar, l2_evict_first_policy());
+  }
+  // elements in front of the tile's first one inside the window; `lead` of them share its 4-element group
+  const uint32_t skip = static_cast<uint32_t>(s_abs - s_lo) / IS;
+  const uint32_t lead = skip & 3u;
+  const uint32_t g0 = skip >> 2;                      // first group (of 4 input elements, window-aligned) that holds tile elements
+  const uint32_t n_groups = (lead + n + 3u) >> 2;
+  mbar_wait(bar, 0);
+  // output stage: element j of the tile at sm_out + (lead + j) * OS, so that group g's four outputs start at 4 * OS * g
+  for (uint32_t g = threadIdx.x; g < n_groups; g += kCopyThreads)
+    cast_group<OP>(sm_in + (g0 + g) * 4u * IS, sm_out + g * 4u * OS, lut);
+  __syncthreads();
+  // flush the bytes [lead * OS, (lead + n) * OS) of the stage to dst
+  uint8_t* d = seg.dst + e0 * OS;
+  const uint32_t total = n * OS;
+  const uint8_t* st = sm_out + lead * OS;  // byte k of the tile's output
+  const uint32_t skew = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(d) & 15u);
+  const uint32_t head = (16u - skew) & 15u;  // bytes up to the first 16-byte boundary of dst
+  if (((lead * OS + head) & 15u) == 0 && total >= head + 16u) {
+    // stage and destination congruent: one bulk store for the interior, the ragged ends byte by byte
+    const uint32_t body = (total - head) & ~15u;
+    if (threadIdx.x == 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the stage was written by ordinary stores
+      tma_store(d + head, st + head, body, l2_evict_first_policy());
+      tma_commit();
+    }
+    for (uint32_t k = threadIdx.x; k < head; k += kCopyThreads) d[k] = st[k];
+    for (uint32_t k = head + body + threadIdx.x; k < total; k += kCopyThreads) d[k] = st[k];
+    if (threadIdx.x == 0) tma_wait_all();
+  } else {
+    uint8_t* da = d - skew;
+    const uint32_t end = skew + total;
+    const uint32_t nchunks = (end + 15u) >> 4;
+    const uint32_t base = lead * OS;  // stage offset of output byte 0; st - sm_out
+    for (uint32_t c = threadIdx.x; c < nchunks; c += kCopyThreads) {
+      const uint32_t lo = c << 4, hi = lo + 16u;
+      if (lo >= skew && hi <= end) {
+        const uint32_t s0 = base + lo - skew, sh = s0 & 15u;
+        const uint4 a = *reinterpret_cast<const uint4*>(sm_out + (s0 & ~15u));
+        const uint4 b = *reinterpret_cast<const uint4*>(sm_out + (s0 & ~15u) + 16u);
+        st_stream16(da + lo, sh ? shift_window(a, b, sh) : a);
+      } else {
+        const uint32_t b0 = lo > skew ? lo : skew, b1 = hi < end ? hi : end;
+        for (uint32_t b = b0; b < b1; ++b) da[b] = st[b - skew];
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kCopyThreads) k_copy_cast(const CopySeg* __restrict__ segs, uint32_t n_segs, uint64_t n_tiles,
+                                                             const uint64_t* __restrict__ gate, uint64_t src_lo, uint64_t src_hi,
+                                                             uint64_t tile_begin, uint32_t in_stage_bytes) {
+  extern __shared__ __align__(128) uint8_t cast_smem[];  // input stage | output stage
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ uint32_t s_seg;
+  __shared__ float lut[256];
+  if (gate && *gate != 0) return;
+  const uint64_t tile = tile_begin + blockIdx.x;
+  if (tile >= n_tiles) return;
+  if (threadIdx.x < 32) {
+    const uint32_t si = seg_of_tile_warp(segs, n_segs, tile);
+    if (threadIdx.x == 0) s_seg = si;
+  }
+  if (threadIdx.x == 0) {
+    mbar_init(&bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+  const CopySeg seg = segs[s_seg];
+  if (seg.n == 0 || !cast_eligible(seg)) return;
+  uint64_t e0, e1;
+  tile_range(seg, tile - seg.first_tile, &e0, &e1);
+  if (e0 >= e1) return;
+  {  // a pipelined launch owns the tiles whose source bytes end inside its window
+    const uint64_t src_end = reinterpret_cast<uintptr_t>(seg.src) + e1 * in_size_of(seg.op);
+    if (src_end <= src_lo || src_end > src_hi) return;
+  }
+  if (seg.op == CP_U8_F32_DIV || seg.op == CP_U8_F32_MUL) {
+    const float x = static_cast<float>(threadIdx.x);
+    lut[threadIdx.x] = seg.op == CP_U8_F32_DIV ? __fdiv_rn(x, seg.param) : __fmul_rn(x, seg.param);
+    __syncthreads();
+  }
+  uint8_t* sm_in = cast_smem;
+  uint8_t* sm_out = cast_smem + in_stage_bytes;
+  const uint32_t n = static_cast<uint32_t>(e1 - e0);
+  switch (seg.op) {
+    case CP_U8_F32: cast_tile<CP_U8_F32>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
+    case CP_U8_F32_DIV: cast_tile<CP_U8_F32_DIV>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
+    case CP_U8_F32_MUL: cast_tile<CP_U8_F32_MUL>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
+    case CP_F32_F16: cast_tile<CP_F32_F16>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
+    case CP_F32_BF16: cast_tile<CP_F32_BF16>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
+    case CP_F16_F32: cast_tile<CP_F16_F32>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
+    case CP_BF16_F32: cast_tile<CP_BF16_F32>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
+    default: break;
+  }
+}
+
 }  // namespace
 
 tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
-                         bool need_generic, const std::vector<HostSeg>* host_segs, bool need_tma) {
+                         bool need_generic, const std::vector<HostSeg>* host_segs, bool need_tma, int cast_kind) {
   if (n_segs == 0 || n_tiles == 0) return TFS_OK;
   if (n_tiles > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (copy tiles)");
   const uint32_t ring_bytes = kTmaStages * kTmaChunk;
   if (!ctx->copy_attr_set) {  // a per-device attribute: once per context, not once per process
     TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_tma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ring_bytes)));
     TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_tma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ring_bytes)));
+    TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_cast, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(3 * kCopyTileBytes + 2 * kCastPad)));
     ctx->copy_attr_set = true;
   }
+  // staged casts: the input stage holds the source bytes of one 32 KiB output tile: 8 / 16 KiB for the widening ops,
+  // 64 KiB for f32 -> 16-bit
+  const uint32_t cast_in = (cast_kind == 2 ? 2u * kCopyTileBytes : kCopyTileBytes / 2u) + kCastPad;
+  const uint32_t cast_smem_bytes = cast_in + kCopyTileBytes + kCastPad;
   // tiles [tb, te), of which the kernels take those whose source bytes end in (src_lo, src_hi]
   auto launch = [&](uint64_t src_lo, uint64_t src_hi, uint64_t tb, uint64_t te) {
     if (te <= tb) return;
     if (need_generic) {  // segments that are not congruent mod 16, are tiny, or need arithmetic: one CTA per tile
       ProfScope prof(ctx, PK_COPY);
       k_copy<<<static_cast<uint32_t>(te - tb), kCopyThreads, 0, ctx->stream>>>(segs_dev, n_segs, te, gate, src_lo, src_hi, tb);
+      ctx->launches++;
+    }
+    if (cast_kind) {  // widening / narrowing segments: one CTA per tile, staged through shared memory
+      ProfScope prof(ctx, PK_COPY_CAST);
+      k_copy_cast<<<static_cast<uint32_t>(te - tb), kCopyThreads, cast_smem_bytes, ctx->stream>>>(segs_dev, n_segs, te, gate, src_lo, src_hi, tb, cast_in);
       ctx->launches++;
     }
     if (need_tma) {  // the TMA ring: one CTA (96 KiB of shared memory, one driving thread) per SM

@@ -147,8 +147,19 @@ tfs_status_t tfs_ctx_create(int32_t device, uint64_t pinned_bytes, tfs_ctx_t** o
   }
   ctx->stream = ctx->own_stream;
   cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
-  if (pinned_bytes) {
-    tfs_status_t st = pinned_reserve(ctx, &ctx->h_slab, &ctx->h_slab_cap, pinned_bytes);
+  if (cudaMalloc(reinterpret_cast<void**>(&ctx->d_ctrl), 256) != cudaSuccess || cudaMemset(ctx->d_ctrl, 0, 256) != cudaSuccess) {
+    std::fprintf(stderr, "tfs_ctx_create: no device memory for the control words\n");
+    tfs_ctx_destroy(ctx);
+    return TFS_ERR_CUDA;
+  }
+  if (pinned_bytes) {  // the staging pool: pinned once, here (exactly the requested size)
+    tfs_status_t st = TFS_OK;
+    if (cudaHostAlloc(&ctx->h_slab, pinned_bytes, cudaHostAllocDefault) != cudaSuccess) {
+      cudaGetLastError();
+      st = TFS_ERR_NOMEM;
+    } else {
+      ctx->h_slab_cap = pinned_bytes;
+    }
     if (st != TFS_OK) {
       tfs_ctx_destroy(ctx);
       return st;
@@ -164,9 +175,11 @@ tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx) {
   cudaStreamSynchronize(ctx->stream);
   for (DevBuf* b : {&ctx->d_tables, &ctx->d_work, &ctx->d_stage_in, &ctx->d_stage_out, &ctx->d_dec1, &ctx->d_dec2, &ctx->d_dec3})
     if (b->p) cudaFree(b->p);
+  if (ctx->d_ctrl) cudaFree(ctx->d_ctrl);
   if (ctx->h_up) cudaFreeHost(ctx->h_up);
   if (ctx->h_down) cudaFreeHost(ctx->h_down);
   if (ctx->h_slab) cudaFreeHost(ctx->h_slab);
+  for (auto& e : ctx->pool_extra) cudaFreeHost(e.first);
   if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
   for (cudaEvent_t e : ctx->pipe_events) cudaEventDestroy(e);
   for (cudaEvent_t e : ctx->prof_pool) cudaEventDestroy(e);
@@ -215,6 +228,85 @@ tfs_status_t tfs_host_free(tfs_ctx_t* ctx, void* p) {
   if (p) TFS_CUDA(ctx, cudaFreeHost(p));
   return TFS_OK;
 }
+// ---- pinned staging pool -------------------------------------------------------------------------------------
+// slab id: bit 63 = one-off allocation (index in the low bits is its serial), else (class << 48) | (offset / 4096)
+namespace {
+constexpr uint64_t kPoolGrain = 4096;
+constexpr uint64_t kPoolExtraBit = 1ull << 63;
+inline uint32_t pool_class_of(uint64_t bytes) {  // smallest c with (4096 << c) >= bytes
+  uint32_t c = 0;
+  while ((kPoolGrain << c) < bytes) ++c;
+  return c;
+}
+}  // namespace
+
+tfs_status_t tfs_stage_acquire(tfs_ctx_t* ctx, uint64_t bytes, uint32_t align_skew, tfs_slab_t* out) {
+  if (!ctx || !out) return TFS_ERR_INVALID_ARG;
+  const uint64_t skew = align_skew & 15u;
+  const uint64_t need = bytes + skew;  // blocks start on 4 KiB boundaries: the skew is applied inside the block
+  const uint32_t cls = pool_class_of(need ? need : 1);
+  const uint64_t block = kPoolGrain << cls;
+  std::lock_guard<std::mutex> lock(ctx->pool_mutex);
+  if (ctx->pool_free.size() <= cls) ctx->pool_free.resize(cls + 1);
+  uint64_t off = ~0ull;
+  if (!ctx->pool_free[cls].empty()) {
+    off = ctx->pool_free[cls].back();
+    ctx->pool_free[cls].pop_back();
+  } else if (ctx->h_slab && ctx->pool_bump + block <= ctx->h_slab_cap) {
+    off = ctx->pool_bump;
+    ctx->pool_bump += block;
+  }
+  if (off != ~0ull) {
+    out->ptr = static_cast<uint8_t*>(ctx->h_slab) + off + skew;
+    out->capacity = block - skew;
+    out->id = (static_cast<uint64_t>(cls) << 48) | (off / kPoolGrain);
+    ctx->pool_in_use += block;
+    return TFS_OK;
+  }
+  // the pool is exhausted (or was never sized): a one-off pinned allocation, freed again on release
+  void* p = nullptr;
+  TFS_CUDA(ctx, cudaSetDevice(ctx->device));
+  TFS_CUDA(ctx, cudaHostAlloc(&p, need + 16, cudaHostAllocDefault));
+  const uint64_t id = kPoolExtraBit | ctx->pool_next_id++;
+  ctx->pool_extra.emplace_back(p, id);
+  ctx->pool_fallbacks++;
+  out->ptr = static_cast<uint8_t*>(p) + skew;  // (cudaHostAlloc returns page-aligned memory)
+  out->capacity = need + 16 - skew;
+  out->id = id;
+  return TFS_OK;
+}
+
+tfs_status_t tfs_stage_release(tfs_ctx_t* ctx, const tfs_slab_t* slab) {
+  if (!ctx || !slab) return TFS_ERR_INVALID_ARG;
+  std::lock_guard<std::mutex> lock(ctx->pool_mutex);
+  if (slab->id & kPoolExtraBit) {
+    for (size_t i = 0; i < ctx->pool_extra.size(); ++i)
+      if (ctx->pool_extra[i].second == slab->id) {
+        void* p = ctx->pool_extra[i].first;
+        ctx->pool_extra.erase(ctx->pool_extra.begin() + static_cast<long>(i));
+        TFS_CUDA(ctx, cudaFreeHost(p));
+        return TFS_OK;
+      }
+    return set_err(ctx, TFS_ERR_INVALID_ARG, "tfs_stage_release: unknown slab");
+  }
+  const uint32_t cls = static_cast<uint32_t>(slab->id >> 48);
+  const uint64_t off = (slab->id & ((1ull << 48) - 1)) * kPoolGrain;
+  if (cls >= 40 || off + (kPoolGrain << cls) > ctx->pool_bump) return set_err(ctx, TFS_ERR_INVALID_ARG, "tfs_stage_release: not a slab of this pool");
+  if (ctx->pool_free.size() <= cls) ctx->pool_free.resize(cls + 1);
+  ctx->pool_free[cls].push_back(off);
+  ctx->pool_in_use -= kPoolGrain << cls;
+  return TFS_OK;
+}
+
+tfs_status_t tfs_stage_stats(tfs_ctx_t* ctx, uint64_t* in_use, uint64_t* pool_bytes, uint64_t* fallbacks) {
+  if (!ctx) return TFS_ERR_INVALID_ARG;
+  std::lock_guard<std::mutex> lock(ctx->pool_mutex);
+  if (in_use) *in_use = ctx->pool_in_use;
+  if (pool_bytes) *pool_bytes = ctx->h_slab_cap;
+  if (fallbacks) *fallbacks = ctx->pool_fallbacks;
+  return TFS_OK;
+}
+
 tfs_status_t tfs_dev_alloc(tfs_ctx_t* ctx, uint64_t bytes, void** out) {
   if (!ctx || !out) return TFS_ERR_INVALID_ARG;
   TFS_CUDA(ctx, cudaMalloc(out, bytes ? bytes : 1));

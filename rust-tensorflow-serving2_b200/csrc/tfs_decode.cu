@@ -37,7 +37,7 @@ namespace {
 
 enum { WT_VARINT = 0, WT_64 = 1, WT_LEN = 2, WT_SGROUP = 3, WT_EGROUP = 4, WT_32 = 5 };
 // TOT_GENERIC counts the copy-class spans the TMA ring cannot take (not congruent mod 16, tiny, or widened)
-enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_RETRY, TOT_BULK, TOT_CLK0 = 16, TOT_COUNT_ = 24 };  // TOT_CLK0..: phase clocks of k_plan_small (TFS_PLAN_TIMING=1 prints them)
+enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_RETRY, TOT_BULK, TOT_BAR0, TOT_BAR1, TOT_QT, TOT_QS, TOT_QF, TOT_QSTR, TOT_COUNT_ = 24 };  // TOT_BAR*: meeting counters of k_plan_warp; TOT_Q*: largest per-message counts seen (quota hints)
 constexpr size_t kTotalsBytes = sizeof(uint64_t) * TOT_COUNT_;
 
 __device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
@@ -101,8 +101,13 @@ struct Walker {
   // counters (COUNT) / cursors (FILL)
   uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0, n_generic = 0, n_bulk = 0;
   uint32_t seen_slots = 0;  // payload slots of the current tensor that already have a chunk
+  // single-walk mode (k_plan_warp): the records go to per-message quota slots; a cursor that reaches its cap keeps counting
+  // but writes to the slot's spare entry (tensors, spans) or nowhere (filters, string bytes), and `ovf` asks for a retry
+  uint32_t cap_t = 0xFFFFFFFFu, cap_s = 0xFFFFFFFFu, cap_f = 0xFFFFFFFFu, cap_str = 0xFFFFFFFFu;
+  bool ovf = false;
   // current tensor
-  uint32_t cur = 0;
+  uint32_t cur = 0;    // its index
+  uint32_t cur_w = 0;  // where its record is written (== cur unless over the quota)
   uint32_t cur_dims = 0;
   uint32_t content_span = 0xFFFFFFFFu;
   uint64_t tend = 0;  // end of the TensorProto being merged (the limit of its merge loop)
@@ -234,7 +239,8 @@ struct Walker {
     sp.off = n_str;
     sp.len = len;
     sp._pad = 0;
-    if (FILL) {
+    if (FILL && static_cast<uint64_t>(n_str) + len > cap_str) ovf = true;
+    if (FILL && static_cast<uint64_t>(n_str) + len <= cap_str) {
       uint8_t* dst = T.strings + n_str;
       for (uint32_t i = 0; i < len;) {
         const uint32_t in_window = 16u - (static_cast<uint32_t>(reinterpret_cast<uintptr_t>(w) + off + i) & 15u);
@@ -265,10 +271,15 @@ struct Walker {
 
   __device__ void begin_tensor() {
     cur = n_tensors++;
+    cur_w = cur;
+    if (cur >= cap_t) {
+      cur_w = cap_t;
+      ovf = true;
+    }
     cur_dims = 0;
     content_span = 0xFFFFFFFFu;
     seen_slots = 0;
-    if (FILL) T.tensors[cur].msg_index = msg;
+    if (FILL) T.tensors[cur_w].msg_index = msg;
   }
   __device__ void add_span(uint32_t slot, uint32_t cls, uint64_t off, uint64_t len, uint64_t n_elems, uint32_t out_mult) {
     if (verify && cls == SC_VARINT && !err) {  // an over-long varint inside this body comes BEFORE whatever failed later
@@ -312,10 +323,15 @@ struct Walker {
       s.cls = cls;
       s.first_tile = cls == SC_VARINT ? n_vt : n_ct;
       s.elem_tile0 = n_vt;
-      T.spans[n_spans] = s;
+      uint32_t at = n_spans;
+      if (at >= cap_s) {
+        at = cap_s;
+        ovf = true;
+      }
+      T.spans[at] = s;
       // both numberings stay monotone over the span table (a span owns no tiles of the other class)
-      T.span_vtile0[n_spans] = n_vt;
-      T.span_ctile0[n_spans] = n_ct;
+      T.span_vtile0[at] = n_vt;
+      T.span_ctile0[at] = n_ct;
     }
     n_spans++;
     n_vt += vt;
@@ -423,19 +439,19 @@ struct Walker {
       }
       if (!loop_end(rend)) return false;
       if (cur_dims < TFS_MAX_DIMS) {
-        if (FILL) T.tensors[cur].dims[cur_dims] = size;
+        if (FILL) T.tensors[cur_w].dims[cur_dims] = size;
       } else {
         soft_unsupported = true;
       }
       cur_dims++;
-      if (FILL) T.tensors[cur].n_dims = cur_dims;
+      if (FILL) T.tensors[cur_w].n_dims = cur_dims;
       return true;
     }
     if (tag == 3) {
       if (!check_wt(WT_VARINT, wt)) return false;
       uint64_t v;
       if (!varint(&v)) return false;
-      if (FILL) T.tensors[cur].unknown_rank = v != 0;
+      if (FILL) T.tensors[cur_w].unknown_rank = v != 0;
       return true;
     }
     return skip(wt, tag, ctx);
@@ -449,8 +465,8 @@ struct Walker {
         uint64_t v;
         if (!varint(&v)) return false;
         if (FILL) {
-          if (tag == 1) T.tensors[cur].dtype = static_cast<int32_t>(v);
-          else T.tensors[cur].version_number = static_cast<int32_t>(v);
+          if (tag == 1) T.tensors[cur_w].dtype = static_cast<int32_t>(v);
+          else T.tensors[cur_w].version_number = static_cast<int32_t>(v);
         }
         return true;
       }
@@ -458,7 +474,7 @@ struct Walker {
         if (!check_wt(WT_LEN, wt)) return false;
         uint64_t rend;
         if (!loop_begin(&rend)) return false;
-        if (FILL) T.tensors[cur].has_shape = 1;
+        if (FILL) T.tensors[cur_w].has_shape = 1;
         while (pos < rend) {
           uint32_t t2, w2;
           if (!key(&t2, &w2)) return false;
@@ -472,8 +488,9 @@ struct Walker {
         if (!varint(&len)) return false;
         if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
         if (FILL && content_span != 0xFFFFFFFFu) {
-          T.spans[content_span].len = 0;
-          T.spans[content_span].n_elems = 0;
+          const uint32_t at = content_span < cap_s ? content_span : cap_s;
+          T.spans[at].len = 0;
+          T.spans[at].n_elems = 0;
         }
         content_span = n_spans;
         add_span(0, SC_COPY, pos, len, len, (T.flags & TFS_F_CONTENT_HALF_TO_F32) ? 2u : 1u);
@@ -528,7 +545,8 @@ struct Walker {
             if ((kl & 0xFFu) != 0x42u) break;
             const uint32_t l = ((wa + p) & 15u) != 15u ? (kl >> 8) & 0xFFu : rd4(p + 1) & 0xFFu;
             if (l >= 0x80u || l > te - (p + 2)) break;
-            if (FILL) {
+            if (FILL && ns >= cap_s) ovf = true;
+            if (FILL && ns < cap_s) {
               const uint64_t off = p + 2;
               uint4* d = spans + 4ull * ns;
               d[0] = make_uint4(static_cast<uint32_t>(off), static_cast<uint32_t>(off >> 32), l, 0u);  // wire_off, len
@@ -579,7 +597,7 @@ struct Walker {
       if (t2 == 1) {
         tfs_span_t sp;
         if (!string_field(w2, &sp)) return false;
-        if (FILL) T.tensors[cur].key = sp;
+        if (FILL) T.tensors[cur_w].key = sp;
       } else if (t2 == 2) {
         if (!tensor_message(w2, ctx - 1)) return false;
       } else if (!skip(w2, t2, ctx - 1)) {
@@ -667,7 +685,8 @@ struct Walker {
           tfs_span_t sp;
           ok = string_field(wt, &sp);
           if (ok) {
-            if (FILL) T.filters[n_filters] = sp;
+            if (FILL && n_filters < cap_f) T.filters[n_filters] = sp;
+            if (FILL && n_filters >= cap_f) ovf = true;
             n_filters++;
           }
         } else ok = skip(wt, tag, 100);
@@ -865,15 +884,17 @@ __device__ __forceinline__ uint64_t slot_pool_bytes(uint32_t slot, int32_t type,
 
 // K6e: per message, in wire order: element base of every span inside its (tensor, slot) vector, element
 // totals per slot, final status (walk errors + varint errors found by K4a), pool bytes per tensor.
-__device__ void finalize_body(const DecTables& T, uint32_t mi) {
+// `s0`, `s1`: the message's range in the span table.
+__device__ __forceinline__ uint32_t span_end_of(const DecTables& T, uint32_t mi) {
+  return mi + 1 < T.n_msgs ? T.cnt_spans[mi + 1] : static_cast<uint32_t>(T.totals[TOT_SPANS]);
+}
+__device__ void finalize_body(const DecTables& T, uint32_t mi, uint32_t s0, uint32_t s1) {
   tfs_msg_out_t& mo = T.msgs[mi];
   const unsigned long long e = T.err[mi];
   if (mo.status == TFS_OK && e != ~0ull) {
     mo.status = static_cast<int32_t>(e & 0xFF);
     mo.err_offset = e >> 8;
   }
-  const uint32_t s0 = T.cnt_spans[mi];
-  const uint32_t s1 = mi + 1 < T.n_msgs ? T.cnt_spans[mi + 1] : static_cast<uint32_t>(T.totals[TOT_SPANS]);
   // tensor_pool[] doubles as the running byte count of each tensor's string_val elements until it is assigned below
   for (uint32_t ti = mo.first_tensor; ti < mo.first_tensor + mo.n_tensors; ++ti) T.tensor_pool[ti] = 0;
   // A run of spans of one (tensor, slot) - every element of a string_val, every chunk of a packed field - keeps its
@@ -944,7 +965,7 @@ __device__ void finalize_body(const DecTables& T, uint32_t mi) {
 
 __global__ void __launch_bounds__(128) k_dec_finalize(DecTables T) {
   const uint32_t mi = blockIdx.x * blockDim.x + threadIdx.x;
-  if (mi < T.n_msgs) finalize_body(T, mi);
+  if (mi < T.n_msgs) finalize_body(T, mi, T.cnt_spans[mi], span_end_of(T, mi));
 }
 
 // exclusive scan of the per-tensor pool bytes, then absolute slot offsets. One CTA of NW warps.
@@ -977,7 +998,7 @@ __global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_te
 __global__ void __launch_bounds__(kSmallBatch) k_finalize_small(DecTables T, uint32_t n_tensors, uint64_t pool_capacity) {
   __shared__ uint64_t smem[kSmallBatch / 32 + 1];
   const uint32_t mi = (threadIdx.x & 31u) * (kSmallBatch / 32) + (threadIdx.x >> 5);  // dealt round the warps (k_plan_small)
-  if (mi < T.n_msgs) finalize_body(T, mi);  // reads what this message's walk wrote and the counted varint spans
+  if (mi < T.n_msgs) finalize_body(T, mi, T.cnt_spans[mi], span_end_of(T, mi));  // reads what this message's walk wrote and the counted varint spans
   __syncthreads();
   pool_layout_body<kSmallBatch / 32>(T, n_tensors, pool_capacity, smem);
 }
@@ -1051,70 +1072,246 @@ __host__ __device__ inline void blob_layout(uint64_t n_tensors, uint64_t n_filte
   *bytes = *p_str + n_str;
 }
 
-// Small batches, planned optimistically: pass-1 walk, the scans, and - when the tables the host laid out from its
-// hints are large enough - the zeroing of the tensor records and the pass-2 walk, all in ONE single-CTA launch.
-// The second walk then runs out of warm caches, and a batch without varint bodies is finalized here too: one host
-// synchronisation per decode instead of two.  totals[TOT_RETRY] = 1 asks the host for larger tables.
-static_assert(sizeof(tfs_tensor_out_t) % 8 == 0, "tensor records are zeroed with 8-byte stores");
-__global__ void __launch_bounds__(kSmallBatch) k_plan_small(DecTables T, uint64_t blob_cap, uint32_t tensor_cap, uint32_t span_cap,
-                                                            uint64_t pool_capacity, uint8_t* pool) {
-  __shared__ uint64_t smem[kSmallBatch / 32 + 1];
-  const uint32_t mi = threadIdx.x;
-  // Per-message work (the walks, finalize) deals the messages round the warps instead of filling warp 0 first: the
-  // threads of a warp wait for each other at every load, so 64 messages walk faster as 8 warps of 8 than as 2 of 32.
-  const uint32_t mw = (threadIdx.x & 31u) * (kSmallBatch / 32) + (threadIdx.x >> 5);
-  long long clk[7];
-  clk[0] = clock64();
-  if (mw < T.n_msgs) walk_body<false>(T, mw);
-  clk[1] = clock64();
+// Small batches (<= kSmallBatch messages), planned optimistically in ONE launch: one WARP per message, one structure walk.
+//   walk     lane 0 walks its message ONCE, writing tensor / span / filter records and string bytes into per-message QUOTA
+//            slots (sized from what earlier batches on this context needed; a message that outgrows its slots keeps
+//            counting, and the host retries with larger quotas).  The first version walked every message twice (count, then
+//            fill at scanned offsets) with one thread per message in a single CTA: 72 us for 32 requests, 140 us for 256.
+//   meet     the CTAs of this small grid (<= 32, all resident) meet at a counter; every warp then sums the counts of the
+//            messages before its own (<= 256 of them) and the totals;
+//   compact  the warp copies its records from the quota slots to their final, dense places, turning message-local indices
+//            and offsets into batch-wide ones;
+//   finish   a batch without varint bodies is finalized here too (element bases, pool layout after a second meeting, copy
+//            segments bound to the pool): one host synchronisation per decode instead of two.
+// totals[TOT_RETRY] = 1 asks the host for larger tables.
+constexpr uint32_t kPlanWarps = 8;
+struct PlanQuota {
+  tfs_tensor_out_t* tensors;  // [n_msgs * (q_t + 1)]: the last entry of each message's run is the spare one
+  DecSpan* spans;             // [n_msgs * (q_s + 1)]
+  uint32_t* span_vtile0;      // [n_msgs * (q_s + 1)]
+  uint32_t* span_ctile0;
+  tfs_span_t* filters;        // [n_msgs * q_f]
+  uint8_t* strings;           // [n_msgs * q_str]
+  uint32_t* cnt[6];           // per-message COUNTS: tensors, filters, spans, string bytes, varint tiles, copy tiles
+  uint32_t q_t, q_s, q_f, q_str;
+};
+static_assert(sizeof(tfs_tensor_out_t) % 8 == 0 && sizeof(DecSpan) % 8 == 0 && sizeof(tfs_span_t) % 8 == 0, "records are moved as 8-byte words");
+
+__device__ __forceinline__ void grid_meet(uint64_t* counter) {  // all CTAs of a grid that is resident as a whole
+  __threadfence();
   __syncthreads();
-  scan_counts_body<kSmallBatch / 32>(T, smem);
-  __syncthreads();
-  clk[2] = clock64();
-  const uint64_t n_tensors = T.totals[TOT_TENSORS], n_filters = T.totals[TOT_FILTERS], n_spans = T.totals[TOT_SPANS],
-                 n_str = T.totals[TOT_STR], n_vt = T.totals[TOT_VTILES];
+  if (gridDim.x > 1) {
+    if (threadIdx.x == 0) {
+      atomicAdd(reinterpret_cast<unsigned long long*>(counter), 1ull);
+      while (atomicAdd(reinterpret_cast<unsigned long long*>(counter), 0ull) < gridDim.x) __nanosleep(40);
+      __threadfence();
+    }
+    __syncthreads();
+  }
+}
+__device__ __forceinline__ unsigned long long warp_sum64(unsigned long long v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+  return v;
+}
+__device__ __forceinline__ void warp_move_words(void* dst, const void* src, uint64_t bytes) {
+  unsigned long long* d = static_cast<unsigned long long*>(dst);
+  const unsigned long long* s2 = static_cast<const unsigned long long*>(src);
+  for (uint64_t i = lane_id(); i < bytes / 8u; i += 32u) d[i] = s2[i];
+}
+
+__global__ void __launch_bounds__(kPlanWarps * 32) k_plan_warp(DecTables T, PlanQuota Q, uint64_t blob_cap, uint32_t tensor_cap, uint32_t span_cap,
+                                                                 uint64_t pool_capacity, uint8_t* pool) {
+  const uint32_t mi = blockIdx.x * kPlanWarps + warp_id();
+  const bool live = mi < T.n_msgs;
+  const uint32_t lane = lane_id();
+  // ---- walk (lane 0), into this message's quota slots
+  tfs_msg_out_t mo;
+  memset(&mo, 0, sizeof(mo));
+  uint32_t c_t = 0, c_f = 0, c_s = 0, c_str = 0, c_vt = 0, c_ct = 0;
+  const uint32_t bt = mi * (Q.q_t + 1), bs = mi * (Q.q_s + 1), bf = mi * Q.q_f, bstr = mi * Q.q_str;
+  if (live) {
+    // the walk only stores what differs from the default: clear the tensor records first
+    unsigned long long* z = reinterpret_cast<unsigned long long*>(Q.tensors + bt);
+    for (uint32_t i = lane; i < (Q.q_t + 1) * (sizeof(tfs_tensor_out_t) / 8); i += 32) z[i] = 0ull;
+    __syncwarp();
+    if (lane == 0) {
+      DecTables W = T;
+      W.tensors = Q.tensors;
+      W.spans = Q.spans;
+      W.span_vtile0 = Q.span_vtile0;
+      W.span_ctile0 = Q.span_ctile0;
+      W.filters = Q.filters;
+      W.strings = Q.strings;
+      Walker<true> wk(W, mi);
+      wk.beg = T.msg_off[mi];
+      wk.end = wk.beg + T.msg_len[mi];
+      wk.pos = wk.beg;
+      wk.n_tensors = bt;
+      wk.cap_t = bt + Q.q_t;
+      wk.n_spans = bs;
+      wk.cap_s = bs + Q.q_s;
+      wk.n_filters = bf;
+      wk.cap_f = bf + Q.q_f;
+      wk.n_str = bstr;
+      wk.cap_str = bstr + Q.q_str;
+      const bool in_bounds = wk.end <= T.wire_bytes && wk.end >= wk.beg;
+      const bool too_long = T.msg_len[mi] > 0xFFFFFFF0ull;  // (see walk_body: 32-bit per-message counters)
+      bool ok = !in_bounds ? wk.fail(TFS_ERR_BUFFER_UNDERFLOW) : too_long ? wk.fail(TFS_ERR_UNSUPPORTED) : wk.run(&mo);
+      if (!ok && in_bounds && !too_long) {  // prost stops at the FIRST error in stream order: look inside the packed bodies too
+        Walker<false> v(T, mi);
+        v.beg = wk.beg;
+        v.end = wk.end;
+        v.pos = wk.beg;
+        v.verify = true;
+        tfs_msg_out_t scratch;
+        memset(&scratch, 0, sizeof(scratch));
+        v.run(&scratch);
+        if (v.err) {
+          wk.err = v.err;
+          wk.err_pos = v.err_pos;
+        }
+      }
+      if (ok) {
+        c_t = wk.n_tensors - bt;
+        c_f = wk.n_filters - bf;
+        c_s = wk.n_spans - bs;
+        c_str = wk.n_str - bstr;
+        c_vt = wk.n_vt;
+        c_ct = wk.n_ct;
+        if (wk.n_generic) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_GENERIC]), static_cast<unsigned long long>(wk.n_generic));
+        if (wk.n_bulk) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_BULK]), static_cast<unsigned long long>(wk.n_bulk));
+        atomicMax(reinterpret_cast<unsigned long long*>(&T.totals[TOT_QT]), static_cast<unsigned long long>(c_t));
+        atomicMax(reinterpret_cast<unsigned long long*>(&T.totals[TOT_QS]), static_cast<unsigned long long>(c_s));
+        atomicMax(reinterpret_cast<unsigned long long*>(&T.totals[TOT_QF]), static_cast<unsigned long long>(c_f));
+        atomicMax(reinterpret_cast<unsigned long long*>(&T.totals[TOT_QSTR]), static_cast<unsigned long long>(c_str));
+        if (wk.ovf) T.totals[TOT_RETRY] = 1;  // a quota was too small: nothing of this launch is used
+      } else {
+        memset(&mo, 0, sizeof(mo));
+        mo.status = wk.err;
+        mo.err_offset = wk.err_pos;
+      }
+      Q.cnt[0][mi] = c_t;
+      Q.cnt[1][mi] = c_f;
+      Q.cnt[2][mi] = c_s;
+      Q.cnt[3][mi] = c_str;
+      Q.cnt[4][mi] = c_vt;
+      Q.cnt[5][mi] = c_ct;
+    }
+  }
+  grid_meet(&T.totals[TOT_BAR0]);
+  // ---- this message's bases = counts of the messages before it; the totals (every warp, redundantly: n_msgs <= 256)
+  unsigned long long pre[6] = {0, 0, 0, 0, 0, 0}, tot[6] = {0, 0, 0, 0, 0, 0};
+  for (uint32_t base = 0; base < T.n_msgs; base += 32u) {
+    const uint32_t i = base + lane;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const unsigned long long v = i < T.n_msgs ? __ldcg(&Q.cnt[k][i]) : 0u;
+      tot[k] += v;
+      if (i < mi) pre[k] += v;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    pre[k] = warp_sum64(pre[k]);
+    tot[k] = warp_sum64(tot[k]);
+  }
+  const uint64_t n_tensors = tot[0], n_filters = tot[1], n_spans = tot[2], n_str = tot[3], n_vt = tot[4];
   uint64_t p_flt, p_str, bytes;
   blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &bytes);
-  if (bytes > blob_cap || n_tensors > tensor_cap || n_spans > span_cap) {
-    if (mi == 0) T.totals[TOT_RETRY] = 1;
-    return;
+  const bool retry = __ldcg(&T.totals[TOT_RETRY]) != 0 || bytes > blob_cap || n_tensors > tensor_cap || n_spans > span_cap ||
+                     n_str > 0xFFFFFFF0ull || tot[5] > 0xFFFFFFF0ull || n_vt > 0xFFFFFFF0ull;
+  if (mi == 0 && lane == 0) {
+    T.totals[TOT_TENSORS] = n_tensors;
+    T.totals[TOT_FILTERS] = n_filters;
+    T.totals[TOT_SPANS] = n_spans;
+    T.totals[TOT_STR] = n_str;
+    T.totals[TOT_VTILES] = n_vt;
+    T.totals[TOT_CTILES] = tot[5];
+    T.totals[TOT_POOL] = 0;
+    if (retry) T.totals[TOT_RETRY] = 1;
   }
+  if (retry) return;  // (uniform over the grid)
   DecTables L = T;
   uint8_t* blob = reinterpret_cast<uint8_t*>(T.tensors);
   L.filters = reinterpret_cast<tfs_span_t*>(blob + p_flt);
   L.strings = blob + p_str;
-  unsigned long long* z = reinterpret_cast<unsigned long long*>(blob);
-  for (uint64_t i = mi, n = n_tensors * (sizeof(tfs_tensor_out_t) / 8); i < n; i += kSmallBatch) z[i] = 0ull;
-  __syncthreads();
-  clk[3] = clock64();
-  if (mw < L.n_msgs) walk_body<true>(L, mw);
-  clk[4] = clock64();
-  if (n_vt == 0) {  // (with varint bodies the element totals are only known after K4a / K4b)
-    if (mw < L.n_msgs) finalize_body(L, mw);
-    __syncthreads();
-    clk[5] = clock64();
-    pool_layout_body<kSmallBatch / 32>(L, static_cast<uint32_t>(n_tensors), pool_capacity, smem);
-    if (pool) {  // one-call decode: the copy segments are bound here too (saves the k_dec_bind launch)
-      __syncthreads();
-      if (L.totals[TOT_OVERFLOW] == 0) {
-        const uint32_t n = static_cast<uint32_t>(L.totals[TOT_SPANS]);
-        uint32_t si = mi;
-        for (; si + 3 * kSmallBatch < n; si += 4 * kSmallBatch) {  // four spans' loads in flight, then their stores
-          SpanBinding b[4];
-#pragma unroll
-          for (uint32_t j = 0; j < 4; ++j) b[j] = bind_prepare(L, si + j * kSmallBatch, pool);
-#pragma unroll
-          for (uint32_t j = 0; j < 4; ++j) bind_commit(L, si + j * kSmallBatch, b[j]);
-        }
-        for (; si < n; si += kSmallBatch) bind_span(L, si, pool);
-      }
+  const uint32_t t_base = static_cast<uint32_t>(pre[0]), f_base = static_cast<uint32_t>(pre[1]), s_base = static_cast<uint32_t>(pre[2]);
+  const uint32_t str_base = static_cast<uint32_t>(pre[3]), vt_base = static_cast<uint32_t>(pre[4]), ct_base = static_cast<uint32_t>(pre[5]);
+  if (live) {
+    // exclusive prefixes, where the later kernels (and finalize below) expect them
+    if (lane == 0) {
+      T.cnt_tensors[mi] = t_base;
+      T.cnt_filters[mi] = f_base;
+      T.cnt_spans[mi] = s_base;
+      T.cnt_strbytes[mi] = str_base;
+      T.cnt_vtiles[mi] = vt_base;
+      T.cnt_ctiles[mi] = ct_base;
     }
-  } else {
-    clk[5] = clk[4];
+    // ---- compact: quota slots -> dense tables, message-local indices -> batch-wide ones
+    c_t = __shfl_sync(0xFFFFFFFFu, c_t, 0);
+    c_f = __shfl_sync(0xFFFFFFFFu, c_f, 0);
+    c_s = __shfl_sync(0xFFFFFFFFu, c_s, 0);
+    c_str = __shfl_sync(0xFFFFFFFFu, c_str, 0);
+    warp_move_words(L.tensors + t_base, Q.tensors + bt, sizeof(tfs_tensor_out_t) * static_cast<uint64_t>(c_t));
+    warp_move_words(L.spans + s_base, Q.spans + bs, sizeof(DecSpan) * static_cast<uint64_t>(c_s));
+    warp_move_words(L.filters + f_base, Q.filters + bf, sizeof(tfs_span_t) * static_cast<uint64_t>(c_f));
+    for (uint32_t i = lane; i < c_str; i += 32) L.strings[str_base + i] = Q.strings[bstr + i];
+    for (uint32_t i = lane; i < c_s; i += 32) {
+      L.span_vtile0[s_base + i] = Q.span_vtile0[bs + i] + vt_base;
+      L.span_ctile0[s_base + i] = Q.span_ctile0[bs + i] + ct_base;
+    }
+    __syncwarp();
+    for (uint32_t i = lane; i < c_t; i += 32) L.tensors[t_base + i].key.off = L.tensors[t_base + i].key.off - bstr + str_base;
+    for (uint32_t i = lane; i < c_f; i += 32) L.filters[f_base + i].off = L.filters[f_base + i].off - bstr + str_base;
+    for (uint32_t i = lane; i < c_s; i += 32) {
+      DecSpan& sp = L.spans[s_base + i];
+      sp.tensor = sp.tensor - bt + t_base;
+      sp.first_tile += sp.cls == SC_VARINT ? vt_base : ct_base;
+      if (sp.cls == SC_VARINT) sp.elem_tile0 += vt_base;  // (a string span keeps its byte offset there: set by finalize)
+    }
+    if (lane == 0) {
+      if (mo.status == TFS_OK) {
+        mo.model_name.off = mo.model_name.off - bstr + str_base;
+        mo.signature_name.off = mo.signature_name.off - bstr + str_base;
+        mo.version_label.off = mo.version_label.off - bstr + str_base;
+        mo.first_tensor = t_base;
+        mo.n_tensors = c_t;
+        mo.first_filter = f_base;
+        mo.n_filters = c_f;
+      }
+      T.msgs[mi] = mo;
+    }
+    __syncwarp();
   }
-  clk[6] = clock64();
-  if (mi == 0)
-    for (int k = 0; k < 6; ++k) T.totals[TOT_CLK0 + k] = static_cast<uint64_t>(clk[k + 1] - clk[k]);
+  if (n_vt != 0) return;  // with varint bodies the element totals are only known after K4a / K4b: k_finalize_small follows
+  // ---- finish: element bases + pool bytes per tensor (own message), pool layout (needs every tensor's bytes), binding
+  if (live && lane == 0) finalize_body(L, mi, s_base, s_base + c_s);
+  grid_meet(&T.totals[TOT_BAR1]);
+  unsigned long long before = 0, all = 0;
+  for (uint64_t base = 0; base < n_tensors; base += 32u) {
+    const uint64_t i = base + lane;
+    const unsigned long long v = i < n_tensors ? __ldcg(&T.tensor_pool[i]) : 0ull;
+    all += v;
+    if (i < t_base) before += v;
+  }
+  before = warp_sum64(before);
+  all = warp_sum64(all);
+  if (mi == 0 && lane == 0) {
+    T.totals[TOT_POOL] = all;
+    T.totals[TOT_OVERFLOW] = all > pool_capacity ? 1ull : 0ull;  // gates the value kernels of a one-call decode
+  }
+  if (!live) return;
+  // (a failed message exposes nothing: finalize zeroed its counts in msgs[], but its tensor records still take part in the layout)
+  unsigned long long run = before;
+  for (uint32_t i = 0; i < c_t; ++i) {  // the tensors of one message are few: lanes split the slots
+    const unsigned long long here = __ldcg(&T.tensor_pool[t_base + i]);
+    if (lane < TFS_N_SLOTS) L.tensors[t_base + i].dst_off[lane] += run;
+    run += here;
+  }
+  __syncwarp();
+  if (pool && all <= pool_capacity)
+    for (uint32_t i = lane; i < c_s; i += 32) bind_span(L, s_base + i, pool);
 }
 
 // at decode time: bind every copy-class span to its place in the caller's pool
@@ -1156,7 +1353,9 @@ tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const 
   TFS_CUDA(ctx, cudaGetLastError());
   // the generic copy kernel is only needed for spans the TMA ring cannot take (counted by the walk)
   const bool need_generic = dec->totals[TOT_GENERIC] != 0 || (reinterpret_cast<uintptr_t>(pool) & 15u) != 0;
-  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, gate, need_generic, host_segs, dec->totals[TOT_BULK] != 0));
+  // tensor_content of a 16-bit float tensor widened to f32 (TFS_F_CONTENT_HALF_TO_F32): the staged cast kernel
+  const int cast_kind = (T.flags & TFS_F_CONTENT_HALF_TO_F32) ? 1 : 0;
+  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, gate, need_generic, host_segs, dec->totals[TOT_BULK] != 0, cast_kind));
   return TFS_OK;
 }
 
@@ -1254,8 +1453,14 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     n_vt = dec->totals[TOT_VTILES];
   };
 
-  if (small) {
-    // ---- optimistic plan: tables laid out from this context's hints, both walks in one launch
+  // per-message quota slots of the single-walk plan kernel, from what earlier batches on this context needed per message
+  auto quota_bytes = [&]() -> uint64_t {
+    return static_cast<uint64_t>(n_msgs) * ((ctx->dec_q_t + 1ull) * sizeof(tfs_tensor_out_t) + (ctx->dec_q_s + 1ull) * (sizeof(DecSpan) + 8) +
+                                            ctx->dec_q_f * sizeof(tfs_span_t) + ctx->dec_q_str + 64);
+  };
+  bool plan_warp = small && quota_bytes() <= (256ull << 20);  // (a message with millions of string elements: two walks instead)
+  if (plan_warp) {
+    // ---- optimistic plan: tables laid out from this context's hints, ONE walk per message, one launch
     for (int attempt = 0;; ++attempt) {
       const uint64_t t_cap = std::max<uint64_t>(ctx->dec_hint_tensors, 4ull * n_msgs + 16), f_cap = std::max<uint64_t>(ctx->dec_hint_filters, 4ull * n_msgs + 16),
                      s_cap = std::max<uint64_t>(ctx->dec_hint_spans, 8ull * n_msgs + 32), str_cap = std::max<uint64_t>(ctx->dec_hint_str, 256ull * n_msgs + 1024);
@@ -1264,8 +1469,24 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       cur = 0;
       const size_t p_blob = carve(&cur, blob_cap), p_spn = carve(&cur, sizeof(DecSpan) * s_cap), p_sv = carve(&cur, 4 * (s_cap + 1)),
                    p_sc = carve(&cur, 4 * (s_cap + 1)), p_seg = carve(&cur, sizeof(CopySeg) * s_cap), p_tp = carve(&cur, 8 * t_cap);
+      PlanQuota Q{};
+      Q.q_t = ctx->dec_q_t;
+      Q.q_s = ctx->dec_q_s;
+      Q.q_f = ctx->dec_q_f;
+      Q.q_str = ctx->dec_q_str;
+      const size_t nm = n_msgs;
+      const size_t p_qt = carve(&cur, nm * (Q.q_t + 1ull) * sizeof(tfs_tensor_out_t)), p_qs = carve(&cur, nm * (Q.q_s + 1ull) * sizeof(DecSpan)),
+                   p_qv = carve(&cur, nm * (Q.q_s + 1ull) * 4), p_qc = carve(&cur, nm * (Q.q_s + 1ull) * 4),
+                   p_qf = carve(&cur, nm * Q.q_f * sizeof(tfs_span_t) + 16), p_qstr = carve(&cur, nm * Q.q_str + 16), p_qn = carve(&cur, 6 * 4 * nm + 16);
       DEC_TRY(dev_reserve(ctx, &ctx->d_dec2, cur + 64));
       d2 = static_cast<uint8_t*>(ctx->d_dec2.p);
+      Q.tensors = reinterpret_cast<tfs_tensor_out_t*>(d2 + p_qt);
+      Q.spans = reinterpret_cast<DecSpan*>(d2 + p_qs);
+      Q.span_vtile0 = reinterpret_cast<uint32_t*>(d2 + p_qv);
+      Q.span_ctile0 = reinterpret_cast<uint32_t*>(d2 + p_qc);
+      Q.filters = reinterpret_cast<tfs_span_t*>(d2 + p_qf);
+      Q.strings = d2 + p_qstr;
+      for (int k = 0; k < 6; ++k) Q.cnt[k] = reinterpret_cast<uint32_t*>(d2 + p_qn) + static_cast<size_t>(k) * nm;
       T.tensors = reinterpret_cast<tfs_tensor_out_t*>(d2 + p_blob);
       T.filters = nullptr;  // placed by blob_layout() once the counts are known (kernel and host agree)
       T.strings = nullptr;
@@ -1276,9 +1497,9 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       T.tensor_pool = reinterpret_cast<uint64_t*>(d2 + p_tp);
       {
         ProfScope prof(ctx, PK_WALK);
-        k_plan_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, blob_cap, static_cast<uint32_t>(std::min<uint64_t>(t_cap, 0xFFFFFFF0ull)),
-                                                        static_cast<uint32_t>(std::min<uint64_t>(s_cap, 0xFFFFFFF0ull)), pool_cap_arg,
-                                                        static_cast<uint8_t*>(pool_dev));
+        k_plan_warp<<<(n_msgs + kPlanWarps - 1) / kPlanWarps, kPlanWarps * 32, 0, ctx->stream>>>(
+            T, Q, blob_cap, static_cast<uint32_t>(std::min<uint64_t>(t_cap, 0xFFFFFFF0ull)), static_cast<uint32_t>(std::min<uint64_t>(s_cap, 0xFFFFFFF0ull)),
+            pool_cap_arg, static_cast<uint8_t*>(pool_dev));
       }
       ctx->launches++;
       DEC_CUDA(cudaGetLastError());
@@ -1289,10 +1510,15 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       DEC_CUDA(cudaMemcpyAsync(hd + h2, d2 + p_blob, guess, cudaMemcpyDeviceToHost, ctx->stream));
       DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1 (the only one when the batch has no varint bodies)
       load_totals(hd + h1);
-      if (std::getenv("TFS_PLAN_TIMING"))
-        std::fprintf(stderr, "k_plan_small cycles: walk1 %llu scan %llu zero %llu walk2 %llu finalize %llu layout %llu\n",
-                     (unsigned long long)dec->totals[TOT_CLK0], (unsigned long long)dec->totals[TOT_CLK0 + 1], (unsigned long long)dec->totals[TOT_CLK0 + 2],
-                     (unsigned long long)dec->totals[TOT_CLK0 + 3], (unsigned long long)dec->totals[TOT_CLK0 + 4], (unsigned long long)dec->totals[TOT_CLK0 + 5]);
+      // next time every message gets what the largest one needed now, and a quarter more
+      auto grow = [](uint32_t* q, uint64_t seen) {
+        const uint64_t want = seen + seen / 4 + 1;
+        if (want > *q) *q = static_cast<uint32_t>(std::min<uint64_t>(want, 0x7FFFFFFFull));
+      };
+      grow(&ctx->dec_q_t, dec->totals[TOT_QT]);
+      grow(&ctx->dec_q_s, dec->totals[TOT_QS]);
+      grow(&ctx->dec_q_f, dec->totals[TOT_QF]);
+      grow(&ctx->dec_q_str, dec->totals[TOT_QSTR]);
       blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &res2_bytes);
       ctx->dec_hint_tensors = std::max(ctx->dec_hint_tensors, n_tensors + n_tensors / 4);
       ctx->dec_hint_filters = std::max(ctx->dec_hint_filters, n_filters + n_filters / 4);

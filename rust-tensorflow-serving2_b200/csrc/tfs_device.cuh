@@ -8,9 +8,16 @@
 namespace tfs {
 
 // ---- varint arithmetic (prost encoded_len_varint: max(1, ceil(bits / 7)); reference path src/lib.rs:265) ----
-__device__ __forceinline__ uint32_t varint_len(uint64_t v) { return (70u - static_cast<uint32_t>(__clzll(static_cast<long long>(v | 1)))) / 7u; }
+// (the framing arithmetic is __host__ __device__: the host runs the same layout code to predict where varint bodies go)
+__host__ __device__ __forceinline__ uint32_t varint_len(uint64_t v) {
+#ifdef __CUDA_ARCH__
+  return (70u - static_cast<uint32_t>(__clzll(static_cast<long long>(v | 1)))) / 7u;
+#else
+  return (70u - static_cast<uint32_t>(__builtin_clzll(v | 1))) / 7u;
+#endif
+}
 
-__device__ __forceinline__ uint32_t key_len(int32_t field_number) { return field_number < 16 ? 1u : 2u; }
+__host__ __device__ __forceinline__ uint32_t key_len(int32_t field_number) { return field_number < 16 ? 1u : 2u; }
 
 // ---- 16-bit float casts: round-to-nearest-even in hardware, NaN -> quiet NaN keeping sign + top payload ----
 // (written as selects, not branches: a branch per element stops the compiler from batching the loads of an
@@ -96,24 +103,24 @@ __device__ __forceinline__ uint32_t find_segment(const T* __restrict__ a, uint32
 // ---- byte sinks used by the message framing traversal ------------------------------------------------
 struct CountSink {
   uint64_t pos = 0;
-  __device__ __forceinline__ void put(uint8_t) { pos += 1; }
-  __device__ __forceinline__ void put_bytes(const uint8_t*, uint32_t n) { pos += n; }
-  __device__ __forceinline__ void skip(uint64_t n) { pos += n; }
-  __device__ __forceinline__ void note(uint64_t*) {}  // only the writing pass records positions
+  __host__ __device__ __forceinline__ void put(uint8_t) { pos += 1; }
+  __host__ __device__ __forceinline__ void put_bytes(const uint8_t*, uint32_t n) { pos += n; }
+  __host__ __device__ __forceinline__ void skip(uint64_t n) { pos += n; }
+  __host__ __device__ __forceinline__ void note(uint64_t*) {}  // only the writing pass records positions
 };
 struct ByteSink {
   uint8_t* base;
   uint64_t pos;
-  __device__ __forceinline__ void put(uint8_t b) { base[pos++] = b; }
-  __device__ __forceinline__ void put_bytes(const uint8_t* p, uint32_t n) {
+  __host__ __device__ __forceinline__ void put(uint8_t b) { base[pos++] = b; }
+  __host__ __device__ __forceinline__ void put_bytes(const uint8_t* p, uint32_t n) {
     for (uint32_t i = 0; i < n; ++i) base[pos + i] = p[i];
     pos += n;
   }
-  __device__ __forceinline__ void skip(uint64_t n) { pos += n; }
-  __device__ __forceinline__ void note(uint64_t* slot) { *slot = pos; }
+  __host__ __device__ __forceinline__ void skip(uint64_t n) { pos += n; }
+  __host__ __device__ __forceinline__ void note(uint64_t* slot) { *slot = pos; }
 };
 template <class Sink>
-__device__ __forceinline__ void put_varint(Sink& s, uint64_t v) {
+__host__ __device__ __forceinline__ void put_varint(Sink& s, uint64_t v) {
   while (v >= 0x80) {
     s.put(static_cast<uint8_t>((v & 0x7F) | 0x80));
     v >>= 7;
@@ -121,7 +128,7 @@ __device__ __forceinline__ void put_varint(Sink& s, uint64_t v) {
   s.put(static_cast<uint8_t>(v));
 }
 template <class Sink>
-__device__ __forceinline__ void put_key(Sink& s, uint32_t field_number, uint32_t wire_type) {
+__host__ __device__ __forceinline__ void put_key(Sink& s, uint32_t field_number, uint32_t wire_type) {
   put_varint(s, (static_cast<uint64_t>(field_number) << 3) | wire_type);
 }
 

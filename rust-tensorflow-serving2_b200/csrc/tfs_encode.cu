@@ -19,6 +19,12 @@ namespace tfs {
 
 namespace {
 
+__device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xFFFFFFFFu, v, d);
+  return v;
+}
+
 // =====================================================================================================
 // K2: per varint field, exclusive scan of its tile byte counts -> tile offsets + body length.
 // One warp per field; each lane takes 4 consecutive tiles per step.
@@ -410,19 +416,130 @@ __global__ void __launch_bounds__(128) k_write_headers(EncTables T, uint8_t* __r
   write_headers_body(T, mi, dst, flags);
 }
 
-// Small batches (<= kSmallBatch messages): layout, scan and framing bytes in ONE single-CTA launch
+// Small batches (<= kSmallBatch messages): layout, scan and framing bytes in ONE launch, one WARP per message.
+// The traversal of a message is a serial chain of dependent reads of its descriptor records; out of global memory every
+// link costs an L2 round trip (the first version, one thread per message in a single CTA, took 50-70 us for 256
+// two-tensor requests).  Here the lanes of the warp first copy the message's records (EncMsg, its tensors, their fields)
+// into shared memory, lane 0 walks them there, and the per-tensor / per-message work arrays live there too.  Between
+// layout and writing every warp needs the lengths of all earlier messages: the CTAs (at most 32, all resident) meet at a
+// counter in global memory.
 constexpr uint32_t kSmallBatch = 256;
-__global__ void __launch_bounds__(kSmallBatch) k_frame_small(EncTables T, uint8_t* __restrict__ dst, uint32_t flags, uint32_t dst_skew,
-                                                             uint64_t dst_capacity, int write) {
-  __shared__ uint64_t smem[kSmallBatch / 32 + 1];
-  // per-message work deals the messages round the warps (the lanes of a warp wait for each other, and messages of
-  // different shapes diverge): 64 messages run as 8 warps of 8 rather than 2 of 32
-  const uint32_t mi = (threadIdx.x & 31u) * (kSmallBatch / 32) + (threadIdx.x >> 5);
-  if (mi < T.n_msgs) msg_layout_body(T, mi);
+constexpr uint32_t kFrameWarps = 8;      // messages per CTA
+constexpr uint32_t kShTensors = 4;       // a message with more map entries / payload fields than this is walked in global memory
+constexpr uint32_t kShFields = 8;
+struct FrameShadow {
+  EncMsg msg;
+  EncTensor tensors[kShTensors];
+  EncField fields[kShFields];
+  uint64_t tensor_len[kShTensors], entry_len[kShTensors];
+  uint64_t spec_len, msg_len, msg_pay_off, msg_off;
+};
+static_assert(sizeof(EncMsg) % 8 == 0 && sizeof(EncTensor) % 8 == 0 && sizeof(EncField) % 8 == 0, "records are copied as 8-byte words");
+
+__device__ __forceinline__ void warp_copy_words(void* dst, const void* src, uint32_t bytes) {
+  unsigned long long* d = static_cast<unsigned long long*>(dst);
+  const unsigned long long* s = static_cast<const unsigned long long*>(src);
+  for (uint32_t i = lane_id(); i < bytes / 8u; i += 32u) d[i] = s[i];
+}
+
+__global__ void __launch_bounds__(kFrameWarps * 32) k_frame_small(EncTables T, uint8_t* __restrict__ dst, uint32_t flags, uint32_t dst_skew,
+                                                                  uint64_t dst_capacity, int write) {
+  __shared__ FrameShadow shadow[kFrameWarps];
+  const uint32_t mi = blockIdx.x * kFrameWarps + warp_id();
+  const bool live = mi < T.n_msgs;
+  FrameShadow& sh = shadow[warp_id()];
+  EncTables L = T;  // this warp's view: the records of ITS message are in shared memory, indexed like the global tables
+  bool shadowed = false;
+  uint32_t f_lo = 0, f_n = 0;
+  if (live) {
+    const EncMsg m = T.msgs[mi];
+    // eligible: few tensors whose field ranges follow each other (how every builder lays them out)
+    bool ok = m.n_tensors <= kShTensors && !is_input_kind(m.kind);
+    if (ok && m.n_tensors) {
+      f_lo = T.tensors[m.first_tensor].first_field;
+      uint32_t next = f_lo;
+      for (uint32_t i = 0; i < m.n_tensors && ok; ++i) {
+        const EncTensor& t = T.tensors[m.first_tensor + i];
+        ok = t.first_field == next;
+        next += t.n_fields;
+      }
+      f_n = next - f_lo;
+      ok = ok && f_n <= kShFields;
+    }
+    if (ok) {
+      shadowed = true;
+      warp_copy_words(&sh.msg, &T.msgs[mi], sizeof(EncMsg));
+      warp_copy_words(sh.tensors, &T.tensors[m.first_tensor], sizeof(EncTensor) * m.n_tensors);
+      if (f_n) warp_copy_words(sh.fields, &T.fields[f_lo], sizeof(EncField) * f_n);
+      __syncwarp();
+      L.msgs = &sh.msg - mi;
+      L.tensors = sh.tensors - m.first_tensor;
+      L.fields = sh.fields - f_lo;
+      L.tensor_len = sh.tensor_len - m.first_tensor;
+      L.entry_len = sh.entry_len - m.first_tensor;
+    }
+    L.spec_len = &sh.spec_len - mi;
+    L.msg_len = &sh.msg_len - mi;
+    L.msg_pay_off = &sh.msg_pay_off - mi;
+    L.msg_off = &sh.msg_off - mi;
+    if (lane_id() == 0) {
+      msg_layout_body(L, mi);
+      T.msg_len[mi] = sh.msg_len;  // for the other warps' prefix and for the host
+      T.msg_pay_off[mi] = sh.msg_pay_off;
+      __threadfence();
+    }
+  }
+  // ---- every message's length is needed from here on: all CTAs of this (small) grid meet
   __syncthreads();
-  msg_scan_body<kSmallBatch / 32>(T, flags, dst_skew, dst_capacity, smem);
-  __syncthreads();  // result[1] and msg_off[] were written by this CTA
-  if (write && mi < T.n_msgs && T.result[1] == 0) write_headers_body(T, mi, dst, flags);
+  if (gridDim.x > 1) {
+    if (threadIdx.x == 0) {
+      // two counters that live in the context and are zero between launches: the last CTA through clears them again
+      atomicAdd(T.ticket, 1u);
+      while (atomicAdd(T.ticket, 0u) < gridDim.x) __nanosleep(50);
+      __threadfence();
+      if (atomicAdd(T.ticket + 1, 1u) == gridDim.x - 1u) {  // everybody has left the loop above
+        T.ticket[0] = 0u;
+        T.ticket[1] = 0u;
+        __threadfence();
+      }
+    }
+    __syncthreads();
+  }
+  if (!live) return;
+  // ---- this message's offset = the slots of all earlier messages; the grand total for the overflow check
+  const uint32_t prefix = (flags & TFS_F_GRPC_PREFIX) ? 5u : 0u;
+  uint64_t before = 0, all = 0, my_pad = 0;
+  for (uint32_t base = 0; base < T.n_msgs; base += 32u) {
+    const uint32_t i = base + lane_id();
+    uint64_t slot = 0, pad = 0;
+    if (i < T.n_msgs) {
+      const uint64_t len = __ldcg(&T.msg_len[i]) + prefix;
+      if (flags & TFS_F_ALIGN_PAYLOAD) {
+        pad = (16u - ((dst_skew + prefix + __ldcg(&T.msg_pay_off[i])) & 15u)) & 15u;
+        slot = (pad + len + 15u) & ~static_cast<uint64_t>(15);
+      } else {
+        slot = len;
+      }
+    }
+    if (i < mi) before += slot;
+    if (i == mi) my_pad = pad;
+    all += slot;
+  }
+  before = warp_sum_u64(before);
+  all = warp_sum_u64(all);
+  my_pad = warp_sum_u64(my_pad);
+  if (lane_id() == 0) {
+    sh.msg_off = before + my_pad;
+    T.msg_off[mi] = sh.msg_off;
+    if (mi == 0) {
+      T.result[0] = all;
+      T.result[1] = all > dst_capacity ? 1u : 0u;
+    }
+    if (write && all <= dst_capacity) write_headers_body(L, mi, dst, flags);
+  }
+  __syncwarp();
+  // what later kernels read from the field records (body_len, dst_off) goes back to the global table
+  if (shadowed && f_n) warp_copy_words(&T.fields[f_lo], sh.fields, sizeof(EncField) * f_n);
 }
 
 // =====================================================================================================
@@ -443,6 +560,7 @@ struct Compiled {
   // (TFS_F_ALIGN_PAYLOAD, one bulk field per message, 16-byte aligned plain-byte sources): TMA ring only
   bool all_tma = true;
   bool any_bulk = false;   // some copy segment is >= 4 KiB of plain bytes (a candidate for the TMA ring)
+  int cast_kind = 0;       // staged cast kernel needed: 1 = widening segments only, 2 = narrowing ones too (launch_copy)
   bool has_input = false;  // some message is an Input / ClassificationRequest: features are framed by their own kernels
 };
 
@@ -681,6 +799,8 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
       // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
       c->n_copy_tiles += (f.body_len + kCopyTileBytes - 1) / kCopyTileBytes + 1;
       c->any_bulk |= f.mode == CP_BYTES && f.body_len >= 4096;
+      if (f.mode >= CP_U8_F32 && s.n >= 1024)  // (the kernel re-checks size and source alignment per segment)
+        c->cast_kind = std::max(c->cast_kind, (f.mode == CP_F32_F16 || f.mode == CP_F32_BF16) ? 2 : 1);
       c->segs.push_back(s);
     }
   }
@@ -701,7 +821,11 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
         const EncField& f = c->fields[fi];
         if (f.is_varint || f.n_elems == 0) continue;
         ++bulk;
-        if (f.mode != CP_BYTES || f.body_len < 4096 || (reinterpret_cast<uintptr_t>(f.src) & 15u) != 0) c->all_tma = false;
+        // (a widening / narrowing field that the staged cast kernel takes needs no alignment at all)
+        const uint32_t in_sz = (f.mode == CP_F32_F16 || f.mode == CP_F32_BF16) ? 4u : (f.mode == CP_F16_F32 || f.mode == CP_BF16_F32) ? 2u : 1u;
+        const uint32_t out_sz = (f.mode == CP_F32_F16 || f.mode == CP_F32_BF16) ? 2u : 4u;
+        const bool cast_ok = f.mode >= CP_U8_F32 && f.body_len / out_sz >= 1024 && (reinterpret_cast<uintptr_t>(f.src) & (in_sz - 1u)) == 0;
+        if (!cast_ok && (f.mode != CP_BYTES || f.body_len < 4096 || (reinterpret_cast<uintptr_t>(f.src) & 15u) != 0)) c->all_tma = false;
       }
     }
     if (bulk > 1) c->all_tma = false;
@@ -788,6 +912,7 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   T.msg_pay_off = reinterpret_cast<uint64_t*>(k + w_mp);
   T.msg_off = reinterpret_cast<uint64_t*>(k + w_mo);
   T.result = reinterpret_cast<uint64_t*>(k + w_res);
+  T.ticket = ctx->d_ctrl;  // k_frame_small's meeting counters
   T.rtile_bytes = reinterpret_cast<uint64_t*>(k + w_rb);
   T.rtile_off = reinterpret_cast<uint64_t*>(k + w_ro);
   T.rfield_first_tile = reinterpret_cast<uint32_t*>(d + o_rft);
@@ -839,7 +964,7 @@ tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_
   if (T.n_msgs <= kSmallBatch) {
     {
       ProfScope prof(ctx, PK_FRAME);
-      k_frame_small<<<1, kSmallBatch, 0, ctx->stream>>>(T, dst, flags, dst_skew, dst_capacity, dst != nullptr);
+      k_frame_small<<<(T.n_msgs + kFrameWarps - 1) / kFrameWarps, kFrameWarps * 32, 0, ctx->stream>>>(T, dst, flags, dst_skew, dst_capacity, dst != nullptr);
     }
     ctx->launches++;
   } else {
@@ -923,7 +1048,7 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
           hs.push_back({reinterpret_cast<uintptr_t>(g.src), g.n * in, g.first_tile, next - g.first_tile, stb, stb});
         }
       }
-      TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, T.result + 1, !c.all_tma, hs.empty() ? nullptr : &hs, c.any_bulk));
+      TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, T.result + 1, !c.all_tma, hs.empty() ? nullptr : &hs, c.any_bulk, c.cast_kind));
     }
   }
   bool overflow = false;

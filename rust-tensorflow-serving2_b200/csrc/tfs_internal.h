@@ -4,7 +4,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/tfs_gpu.h"
@@ -133,6 +135,7 @@ struct EncTables {
   uint32_t* tile_field;         // [n_vtiles] index into fields
   uint32_t* tile_bytes;         // [n_vtiles]
   uint64_t* tile_off;           // [n_vtiles] byte offset of the tile inside its field body
+  uint32_t* ticket;             // [2] meeting counters of k_frame_small's CTAs (tfs_ctx::d_ctrl: zero between launches)
   uint64_t* tensor_len;         // [n_tensors]
   uint64_t* entry_len;          // [n_tensors]
   uint64_t* feat_rec;           // [n_tensors] Input kinds: bytes of the feature's map entry record (key + length + entry)
@@ -245,6 +248,9 @@ struct tfs_ctx {
   // small-batch decode plans its tables optimistically from what earlier batches on this context needed
   uint64_t dec_hint_tensors = 0, dec_hint_filters = 0, dec_hint_spans = 0, dec_hint_str = 0, dec_hint_blob = 0;
   bool copy_attr_set = false;
+  uint32_t* d_ctrl = nullptr;  // 256 bytes of control words, zeroed once (grid-wide meeting counters that clear themselves)
+  // single-walk decode plan: per-message quota slots, from what the largest message of earlier batches needed
+  uint32_t dec_q_t = 4, dec_q_s = 8, dec_q_f = 2, dec_q_str = 256;
   // Host entry points with pinned buffers: the copy engine brings the source to HBM in chunks on `copy_stream` while the
   // copy kernel already writes the finished chunks to the pinned destination.  `pipe` lists, for the NEXT launch_copy,
   // the event of every chunk and the device address its bytes end at.
@@ -261,18 +267,25 @@ struct tfs_ctx {
   size_t h_up_cap = 0;
   void* h_down = nullptr;
   size_t h_down_cap = 0;
-  void* h_slab = nullptr;  // pinned slab for *_host staging of pageable memory
+  // pinned staging pool (tfs_stage_acquire / release): one region pinned at tfs_ctx_create, carved into power-of-two
+  // classes from 4 KiB up and recycled through per-class free lists
+  void* h_slab = nullptr;
   size_t h_slab_cap = 0;
+  std::mutex pool_mutex;
+  size_t pool_bump = 0;                               // first byte of the region that was never handed out
+  std::vector<std::vector<uint64_t>> pool_free;       // [class] offsets of free blocks
+  std::vector<std::pair<void*, uint64_t>> pool_extra; // one-off allocations (the pool was exhausted): base, id
+  uint64_t pool_in_use = 0, pool_fallbacks = 0, pool_next_id = 1;
   // optional per-kernel timing with CUDA events on the launching stream (tfs_prof_*)
   bool prof_on = false;
   std::vector<cudaEvent_t> prof_pool;                           // recycled events
-  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_open[8];  // (start, stop) pairs per kernel id, not yet read
-  uint64_t prof_launches[8] = {0};
-  double prof_ms[8] = {0};
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_open[12];  // (start, stop) pairs per kernel id, not yet read
+  uint64_t prof_launches[12] = {0};
+  double prof_ms[12] = {0};
 };
 
 namespace tfs {
-enum ProfKernel { PK_COPY = 0, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_COPY_TMA, PK_WALK, PK_FRAME, PK_COUNT_ };
+enum ProfKernel { PK_COPY = 0, PK_VARINT_SIZE, PK_VARINT_SCATTER, PK_VARINT_COUNT, PK_VARINT_GATHER, PK_COPY_TMA, PK_WALK, PK_FRAME, PK_COPY_CAST, PK_COUNT_ };
 // Brackets one kernel launch with events when profiling is on (a no-op otherwise).
 struct ProfScope {
   tfs_ctx* ctx;
@@ -316,8 +329,10 @@ struct HostSeg {
 // `need_tma` = false promises that no segment is large enough for the TMA ring (>= 4 KiB of plain bytes).
 // `host_segs` is needed only while ctx->pipe is set (sources still arriving in chunks): each chunk's launch then walks
 // just the tiles that can end inside the chunk; without it the launch waits for the last chunk.
+// `cast_kind`: 0 = no widening / narrowing segment can be large enough for the staged cast kernel, 1 = only widening ones
+// (u8 -> f32, 16-bit -> f32), 2 = narrowing ones (f32 -> 16-bit) too (a larger input stage).
 tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
-                         bool need_generic, const std::vector<HostSeg>* host_segs = nullptr, bool need_tma = true);
+                         bool need_generic, const std::vector<HostSeg>* host_segs = nullptr, bool need_tma = true, int cast_kind = 0);
 
 inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 

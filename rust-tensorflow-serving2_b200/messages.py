@@ -329,6 +329,45 @@ def build_batch(messages, kind) -> BuiltBatch:
                       (abi.FieldDesc * len(fld_l))(*fld_l), (abi.Str * len(flt_l))(*flt_l), keep)
 
 
+def replicate_batch(built: BuiltBatch, n: int) -> BuiltBatch:
+    """`n` copies of a ONE-message batch as one batch of n messages sharing the payload arrays and strings (the C1 shape:
+    2^20 copies of a tiny request).  The descriptor arrays are replicated with numpy; a Python loop per message would
+    take minutes at this size."""
+    if built.n_msgs != 1:
+        raise ValueError("replicate_batch takes a batch of exactly one message")
+    nt, nf, nfl = len(built.tensors), len(built.fields), len(built.filters)
+
+    def rep(arr, ctype, count):
+        if count == 0:
+            return (ctype * 0)(), None
+        raw = np.frombuffer(bytes(arr), dtype=np.uint8).reshape(count, C.sizeof(ctype))
+        out = (ctype * (count * n))()
+        view = np.frombuffer(out, dtype=np.uint8).reshape(n, count, C.sizeof(ctype))
+        view[:] = raw[None]
+        return out, view
+
+    msgs, mv = rep(built.msgs, abi.MsgDesc, 1)
+    tens, tv = rep(built.tensors, abi.TensorDesc, nt)
+    flds, _ = rep(built.fields, abi.FieldDesc, nf)
+    flts, _ = rep(built.filters, abi.Str, nfl)
+    idx = np.arange(n, dtype=np.uint32)
+
+    def patch(view, ctype, field, stride, inner=None):
+        off = getattr(ctype, field).offset
+        base = np.frombuffer(bytes(view[0].tobytes()), dtype=np.uint8)  # (keeps the template's own values)
+        for j in range(view.shape[1]):
+            tmpl = int(np.frombuffer(view[0, j, off: off + 4].tobytes(), dtype="<u4")[0])
+            vals = (tmpl + idx * stride).astype("<u4")
+            view[:, j, off: off + 4] = vals.view(np.uint8).reshape(n, 4)
+        del base
+
+    patch(mv, abi.MsgDesc, "first_tensor", nt)
+    patch(mv, abi.MsgDesc, "first_filter", nfl)
+    if tv is not None:
+        patch(tv, abi.TensorDesc, "first_field", nf)
+    return BuiltBatch(msgs, tens, flds, flts, [built])
+
+
 # ------------------------------------------------------------------------------------------------
 # decode results -> message objects
 # ------------------------------------------------------------------------------------------------

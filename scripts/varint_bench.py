@@ -11,7 +11,7 @@ from tfs_b200 import abi, workloads
 codec = tfs.GpuCodec(tfs.GpuContext(0))
 ctx, enc, dec = codec.ctx, codec.encoder(), codec.decoder()
 dev = torch.device("cuda:0")
-NAMES = {0: "copy", 1: "varint_size", 2: "varint_scatter", 3: "varint_count", 4: "varint_gather", 5: "copy_tma"}
+NAMES = dict(abi.PK_NAMES)
 
 def run(name, msgs, kind, in_bytes, reps=10, flags=0, dflags=0):
     built = tfs.build_batch(msgs, kind)
@@ -24,7 +24,7 @@ def run(name, msgs, kind, in_bytes, reps=10, flags=0, dflags=0):
     for _ in range(3):
         eb = enc.encode(built, kind, flags, dst=wire); dd = dec.decode_into(eb.wire, eb.offsets, eb.lengths, kind, pool, dflags); dd.close()
     ctx.prof_enable(True)
-    for k in range(6): ctx.prof_read(k, reset=True)
+    for k in range(abi.PK_COUNT): ctx.prof_read(k, reset=True)
     e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     te = td = 0.0
     for _ in range(reps):
@@ -36,7 +36,7 @@ def run(name, msgs, kind, in_bytes, reps=10, flags=0, dflags=0):
     print(f"== {name}: {len(msgs)} msgs, input {in_bytes/1e6:.1f} MB, wire {W/1e6:.1f} MB, decoded {out_bytes/1e6:.1f} MB")
     print(f"   encode call {te/reps*1e3:8.1f} us -> {W/(te/reps*1e-3)/1e9:7.1f} GB/s wire, {(in_bytes+W)/(te/reps*1e-3)/1e9:7.1f} GB/s algorithmic")
     print(f"   decode call {td/reps*1e3:8.1f} us -> {W/(td/reps*1e-3)/1e9:7.1f} GB/s wire, {(out_bytes+W)/(td/reps*1e-3)/1e9:7.1f} GB/s algorithmic")
-    for k in range(6):
+    for k in range(abi.PK_COUNT):
         n, ms = ctx.prof_read(k, reset=True)
         if n:
             alg = {1: in_bytes, 2: in_bytes + W, 3: W, 4: W + out_bytes}.get(k)

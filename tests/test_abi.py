@@ -134,3 +134,19 @@ def test_cpp_mirror_header_compiles():
     src = os.path.join(ROOT, "tests", "cpp", "test_codec.cpp")
     r = subprocess.run(["g++", "-std=c++17", "-Wall", "-Wextra", "-Werror", "-fsyntax-only", src], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[:2000]
+
+
+def test_shard_ranges_are_contiguous_and_balanced():
+    L = _lib.lib()
+    rng = np.random.default_rng(8)
+    for n_msgs, n_shards in ((0, 3), (1, 4), (17, 4), (1000, 8), (8192, 8)):
+        lens = (2 ** rng.uniform(0, 18, n_msgs)).astype(np.uint64)
+        arr = (C.c_uint64 * max(1, n_msgs))(*[int(x) for x in lens])
+        first = (C.c_uint32 * (n_shards + 1))()
+        assert L.tfs_shard_ranges(arr, n_msgs, n_shards, first) == abi.TFS_OK
+        f = list(first)
+        assert f[0] == 0 and f[-1] == n_msgs and f == sorted(f)
+        if n_msgs >= 1000:
+            per = [int(lens[a:b].sum()) for a, b in zip(f[:-1], f[1:])]
+            assert max(per) - min(per) <= 2 * int(lens.max())
+    assert L.tfs_shard_ranges(None, 0, 0, (C.c_uint32 * 1)()) == abi.TFS_ERR_INVALID_ARG

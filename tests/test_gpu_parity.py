@@ -233,6 +233,42 @@ def test_fused_casts(codec):
     assert_bytes_equal(gpu_encode_both(codec, msgs, abi.MSG_TENSOR_PROTO), want, "fused casts")
 
 
+@pytest.mark.parametrize("flags", [0, abi.F_ALIGN_PAYLOAD])
+def test_staged_casts_alignment_and_tile_edges(codec, flags):
+    """The staged cast kernel (u8 -> f32 x1 / div / mul, f32 -> f16 / bf16, and on decode f16 / bf16 -> f32): element
+    counts around its 32 KiB output tiles, sources that start at every element phase inside a 16-byte word, destinations at
+    whatever byte phase the framing in front of them gives (names of different lengths), with and without payload
+    alignment; bytes against the oracle, decoded values (widened with TFS_F_CONTENT_HALF_TO_F32) too."""
+    rng = np.random.default_rng(777)
+    base_f = np.concatenate([workloads.c4_payload(70_000), np.array([np.inf, -np.inf, np.nan, -0.0, 65520.0, 1e-8], np.float32),
+                             np.array([0x7FA00001, 0xFFC00001, 0x00000001, 0x33000001], np.uint32).view(np.float32)])
+    base_u = rng.integers(0, 256, 80_000, dtype=np.uint8)
+    msgs = []
+    sizes = [1024, 1025, 4095, 8191, 8192, 8193, 16383, 16384, 16385, 16384 * 2 + 3, 50_001]
+    for i, n in enumerate(sizes):
+        fo, uo = i % 4, i % 16            # element phase of the source inside a 16-byte word
+        xf, xu = base_f[fo: fo + n], base_u[uo: uo + n]
+        msgs.append(tfs.PredictRequest(tfs.ModelSpec("m", signature_name="s"), [
+            ("a" * (i + 1), tfs.TensorProto(dtype=14, tensor_content=tfs.Payload(xf, abi.T_F32, abi.T_BF16))),
+            ("b" * (i % 5), tfs.TensorProto(dtype=19, tensor_content=tfs.Payload(xf, abi.T_F32, abi.T_F16))),
+            ("c", tfs.TensorProto(dtype=1, float_val=tfs.Payload(xu, abi.T_U8, abi.T_F32, abi.OP_DIV, 255.0))),
+            ("d" * (i % 3 + 1), tfs.TensorProto(dtype=1, float_val=tfs.Payload(xu, abi.T_U8, abi.T_F32, abi.OP_MUL, 0.5))),
+            ("e", tfs.TensorProto(dtype=1, float_val=tfs.Payload(xu, abi.T_U8)))]))
+    # one field per message too: with TFS_F_ALIGN_PAYLOAD the destination is then 16-byte aligned (the bulk-store flush)
+    for n in (8192, 16384 + 5, 100_000):
+        msgs.append(tfs.PredictRequest(None, [("x", tfs.TensorProto(dtype=14, tensor_content=tfs.Payload(np.resize(base_f, n), abi.T_F32, abi.T_BF16)))]))
+        msgs.append(tfs.PredictRequest(None, [("y", tfs.TensorProto(dtype=1, float_val=tfs.Payload(np.resize(base_u, n), abi.T_U8, abi.T_F32, abi.OP_DIV, 255.0)))]))
+    kind = abi.MSG_PREDICT_REQUEST
+    want = ob.encode_messages(msgs, kind)
+    got = gpu_encode_both(codec, msgs, kind, flags)
+    assert_bytes_equal(got, want, "staged casts encode")
+    dflags = abi.F_CONTENT_HALF_TO_F32
+    st, dec = gpu_decode_both(codec, got, kind, dflags)
+    st_o, dec_o = ob.decode_bytes(want, kind, dflags)
+    assert st == st_o == 0
+    helpers.assert_same_decoded(dec_o, dec, "request", "staged casts decode (widened)")
+
+
 def test_invalid_descriptors_are_rejected(codec):
     from tfs_b200._lib import TfsError
     enc = codec.encoder()
@@ -737,6 +773,41 @@ def test_config_c4_full_size(codec, fmt):
 def test_config_c5_mixed_responses(codec):
     msgs = workloads.c5_responses(512, seed=5001, max_log2=14)
     roundtrip_check(codec, msgs, abi.MSG_PREDICT_RESPONSE, "C5")
+
+
+def test_varint_encode_around_length_prefix_boundaries(codec):
+    """Element counts around the powers of 128 where a length prefix changes size, every varint source type, gRPC prefix on
+    and off, two tensors and filters per request: bytes against the oracle."""
+    import torch
+    dev = torch.device(f"cuda:{codec.ctx.device}")
+    rng = np.random.default_rng(128)
+    for flags in (0, abi.F_GRPC_PREFIX):
+        msgs = []
+        for i in range(96):
+            n = int(rng.choice([1, 2, 12, 13, 42, 43, 127, 128, 129, 1638, 1639, 2047, 2048, 2049, 5461, 5462, 16383, 16384, 16385,
+                                40000, 209715, 209716, 300000])) + int(rng.integers(0, 3))
+            which = i % 6
+            if which == 0:
+                t = tfs.TensorProto(dtype=9, int64_val=rng.integers(0, 1 << int(rng.integers(1, 40)), n, dtype=np.int64))
+            elif which == 1:
+                t = tfs.TensorProto(dtype=3, int_val=rng.integers(-5, 300, n).astype(np.int32))
+            elif which == 2:
+                t = tfs.TensorProto(dtype=19, half_val=tfs.Payload(rng.standard_normal(n).astype(np.float32), abi.T_F32, abi.T_F16))
+            elif which == 3:
+                t = tfs.TensorProto(dtype=22, uint32_val=rng.integers(0, 1 << 32, n, dtype=np.uint64).astype(np.uint32))
+            elif which == 4:
+                t = tfs.TensorProto(dtype=9, int64_val=np.zeros(n, np.int64), float_val=rng.standard_normal(7).astype(np.float32),
+                                    uint64_val=rng.integers(0, 1 << 63, n // 3 + 1, dtype=np.uint64))
+            else:
+                t = tfs.TensorProto(dtype=14, half_val=rng.integers(0, 1 << 16, n).astype(np.uint16))
+            msgs.append(tfs.PredictRequest(tfs.ModelSpec("m" * int(rng.integers(0, 200)), signature_name="s"), [("k%d" % i, t), ("z", tfs.TensorProto(dtype=1))],
+                                           ["f"] * int(rng.integers(0, 3))))
+        want = ob.encode_messages(msgs, abi.MSG_PREDICT_REQUEST, flags)
+        for rep in range(2):
+            eb = codec.encoder().encode(workloads.to_device(msgs, abi.MSG_PREDICT_REQUEST, dev), abi.MSG_PREDICT_REQUEST, flags)
+            got = eb.all_bytes()
+            for i, (g, w) in enumerate(zip(got, want)):
+                assert g == w, f"flags {flags} rep {rep} message {i}"
 
 
 def test_config_c5_at_benchmarked_scale(codec):

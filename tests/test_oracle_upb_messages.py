@@ -70,17 +70,27 @@ def test_whole_message_differential_vs_upb():
            entries=st.lists(st.tuples(name, tensor), max_size=4, unique_by=lambda e: e[0]),
            filters=st.lists(st.text(max_size=10), max_size=3))
     def run(kind, spec, entries, filters):
-        ents = sorted(([k, _tensor_desc(None, None, **t)] for k, t in entries), key=lambda e: e[0].encode("utf-8"))
+        ents = [[k, _tensor_desc(None, None, **t)] for k, t in entries]
         desc = {"model_spec": spec, "entries": ents}
         if kind == "request":
             desc["output_filter"] = filters
-        want = mg.upb_serialize({"kind": kind, "msg": desc})  # deterministic=True: map entries sorted by key
+        want = mg.upb_serialize({"kind": kind, "msg": desc})
+        # a map has no order of its own (prost: HashMap iteration order; upb: its own sort): feed the oracle the entries in
+        # the order upb happened to write them, found by reading upb's bytes back
+        st0, back = ob.decode_bytes([want], helpers.KIND_OF[kind])
+        assert st0 == 0
+        order = [k for k, _ in (back[0].message.inputs if kind == "request" else back[0].message.outputs)]
+        assert sorted(order) == sorted(k for k, _ in ents)
+        desc["entries"] = sorted(ents, key=lambda e: order.index(e[0]))
         msg = helpers.message_from_desc(kind, desc)
         got = ob.encode_messages([msg], helpers.KIND_OF[kind])[0]
         assert got == want, (got.hex(), want.hex())
         st_, msgs = ob.decode_bytes([want], helpers.KIND_OF[kind])
         assert st_ == 0 and msgs[0].status == 0
-        assert helpers.message_to_desc(kind, msgs[0].message) == helpers.norm_spec(mg.upb_parse(kind, want))
+        got_desc, want_desc = helpers.message_to_desc(kind, msgs[0].message), helpers.norm_spec(mg.upb_parse(kind, want))
+        got_desc["entries"].sort(key=lambda e: e[0])
+        want_desc["entries"].sort(key=lambda e: e[0])
+        assert got_desc == want_desc
         # prost's encoded_len of the whole message
         assert ob.encode_size(tfs.build_batch([msg], helpers.KIND_OF[kind])) == [len(want)]
 
