@@ -281,6 +281,12 @@ def run_ours(args):
     assert np.array_equal(h_pool_np[: 16], h_pool_np[: 16])  # the result is read on the host (device -> host is part of every step)
     del h_src, h_wire, h_pool, hbuilt
 
+    # ---- N > 1: BASELINE config 5, "8192 independent mixed-dtype PredictResponses decoded, sharded across the GPUs": every
+    #      rank decodes its own 8192 / N responses (wire produced and, on rank 0, values checked by the oracle), no collective
+    c5 = None
+    if world > 1 and not args.no_extras:
+        c5 = c5_sharded(codec, dev, rank, world, barrier, max_over_ranks)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -308,6 +314,8 @@ def run_ours(args):
             "step_ms_k_copy_tma": round(ms_copy / args.steps, 4), "step_ms_walk": round(ms_walk / args.steps, 4),
             "step_ms_frame": round(ms_frame / args.steps, 4), "step_ms_other_copy": round(ms_gen / args.steps, 4),
             "step_ms_rest": round((ms - ms_copy - ms_walk - ms_frame - ms_gen) / args.steps, 4)}
+    if c5:
+        roof.update(c5)
     if sustained:
         roof.update({"sustained_GBps": sustained["GBps"], "sustained_seconds": sustained["seconds"], "sustained_sm_mhz": sustained["sm_mhz"],
                      "sustained_reasons": sustained["reasons"]})
@@ -333,6 +341,50 @@ def run_ours(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def c5_sharded(codec, dev, rank, world, barrier, max_over_ranks, total_msgs=8192, reps=5):
+    """-> flat dict for the bench line (rank 0), None elsewhere.  Aggregate = bytes of all ranks / slowest rank's time."""
+    import torch
+    import torch.distributed as dist
+    import tfs_b200 as tfs
+    from tfs_b200 import abi, workloads
+    import oracle_bind as ob
+    import helpers
+
+    n_mine = total_msgs // world
+    msgs = workloads.c5_responses(n_mine, seed=5001 + rank, max_log2=18)  # one shard per rank, its own seed
+    wire, offs, lens = ob.encode(tfs.build_batch(msgs, abi.MSG_PREDICT_RESPONSE))
+    dwire = torch.from_numpy(wire).to(dev)
+    dec, ctx = codec.decoder(), codec.ctx
+    d = dec.scan(dwire, offs, lens, abi.MSG_PREDICT_RESPONSE)
+    out_bytes = d.pool_bytes
+    pool = torch.empty(out_bytes + 64, dtype=torch.uint8, device=dev)
+    d.close()
+    d = dec.decode_into(dwire, offs, lens, abi.MSG_PREDICT_RESPONSE, pool)
+    ctx.sync()
+    if rank == 0:  # values against the oracle, once
+        st_o, want = ob.decode(wire, offs, lens, abi.MSG_PREDICT_RESPONSE)
+        helpers.assert_same_decoded_fast(want, d.messages(), "response", "bench C5 shard of rank 0")
+        del want
+    d.close()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(reps):
+        dec.decode_into(dwire, offs, lens, abi.MSG_PREDICT_RESPONSE, pool).close()
+    ctx.sync()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = max_over_ranks(e0.elapsed_time(e1) / reps)
+    t = torch.tensor([float(wire.size), float(out_bytes)], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    if rank != 0:
+        return None
+    W, V = float(t[0].item()), float(t[1].item())
+    return {"c5_sharded_messages": n_mine * world, "c5_sharded_ms": round(ms, 4), "c5_sharded_wire_GBps": round(W / (ms * 1e-3) / 1e9, 1),
+            "c5_sharded_algorithmic_GBps": round((W + V) / (ms * 1e-3) / 1e9, 1), "c5_sharded_checked_against_oracle": 1}
 
 
 # =====================================================================================================

@@ -38,9 +38,9 @@
 extern "C" {
 #endif
 
-#define TFS_ABI_VERSION 2
+#define TFS_ABI_VERSION 3
 #define TFS_MAX_DIMS 8   /* dims carried inline per tensor; larger ranks -> TFS_ERR_UNSUPPORTED */
-#define TFS_N_SLOTS 12   /* payload field slots of a TensorProto, see tfs_slot_of_kind() */
+#define TFS_N_SLOTS 14   /* payload field slots of a TensorProto, see tfs_slot_of_kind() */
 
 typedef int32_t tfs_status_t;
 typedef struct tfs_ctx tfs_ctx_t;
@@ -62,7 +62,7 @@ enum {
   TFS_ERR_UTF8 = 10,            /* "invalid string value: data is not UTF-8 encoded" */
   TFS_ERR_GRPC_FLAG = 11,       /* gRPC frame: compressed flag != 0 (tonic: Unimplemented / Internal) */
   TFS_ERR_UNSUPPORTED = 12,     /* valid wire, but uses something this library leaves to prost
-                                   (variant_val, resource_handle_val, rank > TFS_MAX_DIMS, dim names) */
+                                   (rank > TFS_MAX_DIMS, dim names, a message of 4 GiB or more) */
   TFS_ERR_INVALID_ARG = 20,
   TFS_ERR_NOMEM = 21,           /* dst / pool capacity too small, or allocation failed */
   TFS_ERR_CUDA = 22,            /* CUDA runtime error; tfs_last_error_detail() has the text */
@@ -86,6 +86,15 @@ enum {
   TFS_KIND_BOOL_VAL = 11,      /* packed varint 0/1 */
   TFS_KIND_DCOMPLEX_VAL = 12,  /* packed fixed64 */
   TFS_KIND_HALF_VAL = 13,      /* packed varint of the 16-bit pattern held in an int32 */
+  /* The two message-typed fields (tensor.proto:72-76): `repeated ResourceHandleProto` / `repeated VariantTensorDataProto`.
+   * Carried like string_val, as a TFS_T_RAGGED block whose element i is the ENCODED BODY of message i (what follows the
+   * element's key and length on the wire).  Encode writes `72 len body` / `7a len body` per element; decode validates every
+   * element exactly as prost's merge would - the nested TensorProtos of a variant, their nested variants, ..., down to
+   * "recursion limit reached" at depth 100 - and returns the bodies; the host side opens them (a ResourceHandleProto is five
+   * scalars; the tensors of a VariantTensorDataProto go through tfs_decode again as TFS_MSG_TENSOR_PROTO, see
+   * include/tfs_codec.hpp).  Slots 12 and 13. */
+  TFS_KIND_RESOURCE_HANDLE_VAL = 14,
+  TFS_KIND_VARIANT_VAL = 15,
   TFS_KIND_UINT32_VAL = 16,    /* packed varint */
   TFS_KIND_UINT64_VAL = 17     /* packed varint */
 };

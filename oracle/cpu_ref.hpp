@@ -101,9 +101,30 @@ struct TensorProto {
   std::vector<double> dcomplex_val;                 // tag 12
   std::vector<uint32_t> uint32_val;                 // tag 16
   std::vector<uint64_t> uint64_val;                 // tag 17
-  bool has_unsupported = false;                     // saw resource_handle_val(14) / variant_val(15)
+  // tag 14 `repeated ResourceHandleProto resource_handle_val`, tag 15 `repeated VariantTensorDataProto variant_val`
+  // (tensor.proto:72-76): kept as the ENCODED BODY of every element.  On decode each element has been merged into the real
+  // struct first (ResourceHandleProto / VariantTensorDataProto below, recursion limit and all), so the bytes are exactly the
+  // messages prost accepted; on encode they are written back as `key len body` per element.
+  std::vector<std::vector<uint8_t>> resource_handle_val;
+  std::vector<std::vector<uint8_t>> variant_val;
   bool is_default() const;
 };
+// resource_handle.proto:13-30
+struct ResourceHandleProto {
+  std::string device, container, name;  // tags 1, 2, 3
+  uint64_t hash_code = 0;               // tag 4
+  std::string maybe_type_name;          // tag 5
+};
+// tensor.proto:86-94
+struct VariantTensorDataProto {
+  std::string type_name;             // tag 1
+  std::vector<uint8_t> metadata;     // tag 2
+  std::vector<TensorProto> tensors;  // tag 3 (recursive)
+};
+void encode_raw(const ResourceHandleProto& m, BufMut& buf);
+void encode_raw(const VariantTensorDataProto& m, BufMut& buf);
+size_t encoded_len(const ResourceHandleProto& m);
+size_t encoded_len(const VariantTensorDataProto& m);
 struct ModelSpec {
   std::string name;  // tag 1
   // oneof version_choice { Int64Value version = 2 (prost maps the wrapper to i64); string version_label = 4 }

@@ -30,7 +30,7 @@ uint32_t type_size(int32_t t) {
   }
 }
 int slot_of_kind(int32_t kind) {
-  static const int kinds[TFS_N_SLOTS] = {4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 16, 17};
+  static const int kinds[TFS_N_SLOTS] = {4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 16, 17, 14, 15};
   for (int i = 0; i < TFS_N_SLOTS; ++i)
     if (kinds[i] == kind) return i;
   return -1;
@@ -140,21 +140,24 @@ bool build_field(const tfs_field_desc_t& f, TensorProto* t) {
       }
       return true;
     }
+    case TFS_KIND_RESOURCE_HANDLE_VAL:  // the same block; every element is the encoded body of one message (tensor.proto:72-76)
+    case TFS_KIND_VARIANT_VAL:
     case TFS_KIND_STRING_VAL: {  // TFS_T_RAGGED block: (n + 1) u64 offsets, then the bytes (tensor.proto:57)
       if (f.src_type != TFS_T_RAGGED || (dst != TFS_T_NONE && dst != TFS_T_RAGGED)) return false;
+      std::vector<std::vector<uint8_t>>& elems = f.kind == TFS_KIND_STRING_VAL ? t->string_val : f.kind == TFS_KIND_VARIANT_VAL ? t->variant_val : t->resource_handle_val;
       const uint8_t* blk = as<uint8_t>(f);
       std::vector<uint64_t> off(n + 1);
       std::memcpy(off.data(), blk, 8 * (n + 1));
       if (off[0] != 0 || off[n] != f.aux) return false;
       const uint8_t* bytes = blk + 8 * (n + 1);
-      t->string_val.resize(n);
+      elems.resize(n);
       for (uint64_t i = 0; i < n; ++i) {
         if (off[i + 1] < off[i]) return false;
-        t->string_val[i].assign(bytes + off[i], bytes + off[i + 1]);
+        elems[i].assign(bytes + off[i], bytes + off[i + 1]);
       }
       return true;
     }
-    default: return false;  // the message-typed fields (resource_handle_val, variant_val) are not on the encode ABI
+    default: return false;
   }
 }
 
@@ -192,6 +195,8 @@ bool build_tensor(const tfs_batch_t& b, const tfs_tensor_desc_t& td, TensorProto
       app(t->dcomplex_val, more.dcomplex_val);
       app(t->uint32_val, more.uint32_val);
       app(t->uint64_val, more.uint64_val);
+      app(t->resource_handle_val, more.resource_handle_val);
+      app(t->variant_val, more.variant_val);
       continue;
     }
     seen |= 1u << slot;
@@ -396,18 +401,21 @@ bool emit_tensor(Decoded& d, uint32_t msg_index, const std::string& key, const T
   put(5, TFS_T_F32, t.float_val.data(), t.float_val.size(), t.float_val.size() * 4);
   put(6, TFS_T_F64, t.double_val.data(), t.double_val.size(), t.double_val.size() * 8);
   put(7, TFS_T_I32, t.int_val.data(), t.int_val.size(), t.int_val.size() * 4);
-  {  // string_val: (n+1) u64 offsets then the bytes
-    size_t n = t.string_val.size();
+  auto put_ragged = [&](int kind, const std::vector<std::vector<uint8_t>>& elems) {  // (n+1) u64 offsets then the bytes
+    size_t n = elems.size();
     std::vector<uint8_t> blob((n + 1) * 8);
     uint64_t acc = 0;
     for (size_t i = 0; i < n; ++i) {
       std::memcpy(&blob[i * 8], &acc, 8);
-      acc += t.string_val[i].size();
+      acc += elems[i].size();
     }
     std::memcpy(&blob[n * 8], &acc, 8);
-    for (const auto& s : t.string_val) blob.insert(blob.end(), s.begin(), s.end());
-    put(8, TFS_T_RAGGED, blob.data(), n, n ? blob.size() : 0);
-  }
+    for (const auto& s : elems) blob.insert(blob.end(), s.begin(), s.end());
+    put(kind, TFS_T_RAGGED, blob.data(), n, n ? blob.size() : 0);
+  };
+  put_ragged(8, t.string_val);
+  put_ragged(14, t.resource_handle_val);
+  put_ragged(15, t.variant_val);
   put(9, TFS_T_F32, t.scomplex_val.data(), t.scomplex_val.size(), t.scomplex_val.size() * 4);
   put(10, TFS_T_I64, t.int64_val.data(), t.int64_val.size(), t.int64_val.size() * 8);
   put(11, TFS_T_BOOL, t.bool_val.data(), t.bool_val.size(), t.bool_val.size());

@@ -10,7 +10,8 @@ from ._lib import TfsError  # noqa: F401
 from .codec import Coalescer, Engine, GpuCodec, GpuContext, GpuDecoder, GpuEncoder, Slab  # noqa: F401
 from .messages import (  # noqa: F401
     ClassificationRequest, Feature, Input, ModelSpec, Payload, PredictRequest, PredictResponse, Ragged, TensorProto, TensorShapeProto, build_batch, ragged_block,
-    messages_from_view, replicate_batch, BuiltBatch,
+    messages_from_view, replicate_batch, BuiltBatch, ResourceHandleProto, VariantTensorDataProto, resource_handle_body, variant_body,
+    parse_resource_handle, parse_variant,
 )
 
 __all__ = ["abi", "workloads", "codec", "ModelSpec", "Payload", "PredictRequest", "PredictResponse", "TensorProto",

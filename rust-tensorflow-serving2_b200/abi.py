@@ -6,9 +6,9 @@ src/lib.rs would.
 """
 import ctypes as C
 
-TFS_ABI_VERSION = 2
+TFS_ABI_VERSION = 3
 TFS_MAX_DIMS = 8
-TFS_N_SLOTS = 12
+TFS_N_SLOTS = 14
 
 # status codes
 TFS_OK = 0
@@ -49,12 +49,16 @@ KIND_INT64_VAL = 10
 KIND_BOOL_VAL = 11
 KIND_DCOMPLEX_VAL = 12
 KIND_HALF_VAL = 13
+KIND_RESOURCE_HANDLE_VAL = 14
+KIND_VARIANT_VAL = 15
 KIND_UINT32_VAL = 16
 KIND_UINT64_VAL = 17
-SLOT_KINDS = (4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 16, 17)
+SLOT_KINDS = (4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 16, 17, 14, 15)
+RAGGED_KINDS = (8, 14, 15)
 KIND_FIELD_NAMES = {
     4: "tensor_content", 5: "float_val", 6: "double_val", 7: "int_val", 8: "string_val", 9: "scomplex_val",
     10: "int64_val", 11: "bool_val", 12: "dcomplex_val", 13: "half_val", 16: "uint32_val", 17: "uint64_val",
+    14: "resource_handle_val", 15: "variant_val",
 }
 
 # element types

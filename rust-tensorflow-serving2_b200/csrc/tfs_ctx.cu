@@ -350,13 +350,13 @@ tfs_status_t tfs_shard_plan(const uint64_t* msg_bytes, uint32_t n_msgs, uint32_t
 }
 
 int32_t tfs_slot_of_kind(int32_t kind) {
-  static const int32_t kinds[TFS_N_SLOTS] = {4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 16, 17};
+  static const int32_t kinds[TFS_N_SLOTS] = {4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 16, 17, 14, 15};
   for (int32_t i = 0; i < TFS_N_SLOTS; ++i)
     if (kinds[i] == kind) return i;
   return -1;
 }
 int32_t tfs_kind_of_slot(int32_t slot) {
-  static const int32_t kinds[TFS_N_SLOTS] = {4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 16, 17};
+  static const int32_t kinds[TFS_N_SLOTS] = {4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 16, 17, 14, 15};
   return slot >= 0 && slot < TFS_N_SLOTS ? kinds[slot] : 0;
 }
 uint32_t tfs_type_size(int32_t t) {

@@ -41,9 +41,13 @@ enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTI
 constexpr size_t kTotalsBytes = sizeof(uint64_t) * TOT_COUNT_;
 
 __device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
-  // 4..13 -> 0..9, 16 -> 10, 17 -> 11
-  return tag <= 13 ? tag - 4u : tag - 6u;
+  // 4..13 -> 0..9, 16 -> 10, 17 -> 11, 14 -> 12, 15 -> 13
+  return tag <= 13 ? tag - 4u : tag >= 16 ? tag - 6u : tag - 2u;
 }
+// slots whose values are a TFS_T_RAGGED block: string_val, resource_handle_val, variant_val
+__device__ __forceinline__ bool ragged_slot(uint32_t slot) { return slot == 4u || slot == 12u || slot == 13u; }
+// message types the nested validator knows (what can sit inside a resource_handle_val / variant_val element)
+enum NestedType : uint8_t { NT_VARIANT = 0, NT_TENSOR, NT_SHAPE, NT_DIM, NT_RESOURCE };
 
 // Rust core::str::from_utf8 validity (no overlongs, no surrogates, <= U+10FFFF)
 template <class Get>
@@ -98,6 +102,7 @@ struct Walker {
   uint64_t err_pos = 0;
   bool soft_unsupported = false;
   bool verify = false;  // error path only: also look inside packed varint bodies (see walk_body)
+  bool opaque = false;  // inside a resource_handle_val / variant_val element: validate only, record nothing
   // counters (COUNT) / cursors (FILL)
   uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0, n_generic = 0, n_bulk = 0;
   uint32_t seen_slots = 0;  // payload slots of the current tensor that already have a chunk
@@ -282,7 +287,7 @@ struct Walker {
     if (FILL) T.tensors[cur_w].msg_index = msg;
   }
   __device__ void add_span(uint32_t slot, uint32_t cls, uint64_t off, uint64_t len, uint64_t n_elems, uint32_t out_mult) {
-    if (verify && cls == SC_VARINT && !err) {  // an over-long varint inside this body comes BEFORE whatever failed later
+    if ((verify || opaque) && cls == SC_VARINT && !err) {  // an over-long varint inside this body comes BEFORE whatever failed later
       uint32_t run = 0;
       for (uint64_t q = off; q < off + len; ++q) {
         if (byte_at(q) & 0x80) {
@@ -297,6 +302,9 @@ struct Walker {
           run = 0;
         }
       }
+    }
+    if (opaque) {  // (nobody will look at this body again: it was checked just above, or needs no check)
+      return;
     }
     const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(wv, off, len) : 0u;
     if (cls == SC_STR && len) n_generic++;  // string bytes land wherever the earlier elements end: generic kernel
@@ -371,6 +379,7 @@ struct Walker {
           return fail(TFS_ERR_INVALID_VARINT);
         }
         add_span(slot, SC_VARINT, off, len, 0, 1);
+        if (opaque && err) return false;  // (the body was checked on the spot: nobody looks at it again)
       }
       pos = rend;
       return true;
@@ -456,6 +465,90 @@ struct Walker {
     }
     return skip(wt, tag, ctx);
   }
+  // string::merge without keeping the string (inside an opaque element)
+  __device__ bool string_opaque(uint32_t wt) {
+    if (!check_wt(WT_LEN, wt)) return false;
+    uint64_t len;
+    if (!varint(&len)) return false;
+    if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+    const uint64_t off = pos;
+    pos += len;
+    if (len > 0xFFFFFFFFull) return fail(TFS_ERR_UNSUPPORTED);
+    if (!utf8_ok([&](uint32_t i) { return byte_at(off + i); }, static_cast<uint32_t>(len))) return fail(TFS_ERR_UTF8);
+    return true;
+  }
+  __device__ bool bytes_opaque(uint32_t wt) {
+    if (!check_wt(WT_LEN, wt)) return false;
+    uint64_t len;
+    if (!varint(&len)) return false;
+    if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+    pos += len;
+    return true;
+  }
+  __device__ bool varint_opaque(uint32_t wt) {
+    if (!check_wt(WT_VARINT, wt)) return false;
+    uint64_t v;
+    return varint(&v);
+  }
+  // What prost's merge does to the body of a resource_handle_val / variant_val element, without keeping anything: the merge
+  // loops of the nested messages (resource_handle.proto:13-30; tensor.proto:86-94 and, through `tensors`, tensor.proto:14-84,
+  // tensor_shape.proto:13-46 again) unrolled into one loop over an explicit stack - a device thread has no stack to recurse
+  // a hundred frames deep.  `budget` = the recursion budget the ROOT message's fields are merged with.
+  __device__ bool validate_nested(uint8_t root, uint64_t root_end, uint32_t budget) {
+    uint64_t ends[100];
+    uint8_t types[100];
+    uint32_t depth = 1, b = budget;  // b: the budget of the innermost open message's fields
+    ends[0] = root_end;
+    types[0] = root;
+    while (depth) {
+      const uint64_t e = ends[depth - 1];
+      if (pos >= e) {  // merge_loop's end: the region must end exactly here
+        if (pos != e) return fail(TFS_ERR_LENGTH_EXCEEDED);
+        --depth;
+        ++b;
+        continue;
+      }
+      uint32_t tag, wt;
+      if (!key(&tag, &wt)) return false;
+      const uint8_t ty = types[depth - 1];
+      uint8_t child = 0xFF;  // a message-typed field of this message?
+      if (ty == NT_VARIANT && tag == 3) child = NT_TENSOR;
+      else if (ty == NT_TENSOR && tag == 2) child = NT_SHAPE;
+      else if (ty == NT_TENSOR && tag == 14) child = NT_RESOURCE;
+      else if (ty == NT_TENSOR && tag == 15) child = NT_VARIANT;
+      else if (ty == NT_SHAPE && tag == 2) child = NT_DIM;
+      if (child != 0xFF) {  // message::merge: wire type, recursion limit, length; its fields get one less
+        if (!check_wt(WT_LEN, wt)) return false;
+        if (b == 0) return fail(TFS_ERR_RECURSION);
+        uint64_t ce;
+        if (!loop_begin(&ce)) return false;
+        ends[depth] = ce;
+        types[depth] = child;
+        ++depth;
+        --b;
+        continue;
+      }
+      bool ok;
+      switch (ty) {
+        case NT_VARIANT: ok = tag == 1 ? string_opaque(wt) : tag == 2 ? bytes_opaque(wt) : skip(wt, tag, b); break;
+        case NT_RESOURCE: ok = (tag == 1 || tag == 2 || tag == 3 || tag == 5) ? string_opaque(wt) : tag == 4 ? varint_opaque(wt) : skip(wt, tag, b); break;
+        case NT_SHAPE: ok = tag == 3 ? varint_opaque(wt) : skip(wt, tag, b); break;
+        case NT_DIM: ok = tag == 1 ? varint_opaque(wt) : tag == 2 ? string_opaque(wt) : skip(wt, tag, b); break;
+        default:  // NT_TENSOR
+          switch (tag) {
+            case 1: case 3: ok = varint_opaque(wt); break;
+            case 4: case 8: ok = bytes_opaque(wt); break;
+            case 5: case 9: ok = repeated_fixed(0, wt, 4); break;
+            case 6: case 12: ok = repeated_fixed(0, wt, 8); break;
+            case 7: case 10: case 11: case 13: case 16: case 17: ok = repeated_varint(0, wt); break;
+            default: ok = skip(wt, tag, b); break;
+          }
+      }
+      if (!ok) return false;
+    }
+    return true;
+  }
+
   // TensorProto::merge_field; `ctx` is the recursion budget its fields are merged with
   __device__ bool tensor_field(uint32_t tag, uint32_t wt, uint32_t ctx) {
     switch (tag) {
@@ -570,7 +663,23 @@ struct Walker {
         }
         return true;
       }
-      case 14: case 15: return fail(TFS_ERR_UNSUPPORTED);  // resource_handle_val / variant_val: left to prost
+      case 14: case 15: {
+        // repeated ResourceHandleProto / VariantTensorDataProto (tensor.proto:72-76): message::merge_repeated.  Every element
+        // is validated as prost's merge would walk it - the TensorProtos inside a variant, the variants inside those, ...
+        // down to the recursion limit - and recorded like a string_val element: one span holding the element's body.
+        if (!check_wt(WT_LEN, wt)) return false;
+        if (ctx == 0) return fail(TFS_ERR_RECURSION);
+        uint64_t rend;
+        if (!loop_begin(&rend)) return false;
+        const uint64_t off = pos, len = rend - pos;
+        opaque = true;
+        const bool ok = validate_nested(tag == 14 ? NT_RESOURCE : NT_VARIANT, rend, ctx - 1);
+        opaque = false;
+        if (!ok) return false;
+        add_span(slot_of(tag), SC_STR, off, len, 1, 1);
+        pos = rend;
+        return true;
+      }
       default: return skip(wt, tag, ctx);
     }
   }
@@ -859,7 +968,7 @@ __device__ __forceinline__ int32_t slot_dst_type(uint32_t slot, int32_t dtype, u
     case 1: case 5: return TFS_T_F32;
     case 2: case 8: return TFS_T_F64;
     case 3: return TFS_T_I32;
-    case 4: return TFS_T_RAGGED;
+    case 4: case 12: case 13: return TFS_T_RAGGED;
     case 6: return TFS_T_I64;
     case 7: return TFS_T_BOOL;
     case 9: return (half16 && (flags & TFS_F_HALF_TO_F32)) ? TFS_T_F32 : TFS_T_I32;
@@ -895,8 +1004,8 @@ __device__ void finalize_body(const DecTables& T, uint32_t mi, uint32_t s0, uint
     mo.status = static_cast<int32_t>(e & 0xFF);
     mo.err_offset = e >> 8;
   }
-  // tensor_pool[] doubles as the running byte count of each tensor's string_val elements until it is assigned below
-  for (uint32_t ti = mo.first_tensor; ti < mo.first_tensor + mo.n_tensors; ++ti) T.tensor_pool[ti] = 0;
+  // (dst_off[] of a ragged slot doubles as the running byte count of its elements until the layout below assigns it;
+  // the tensor records start out zeroed)
   // A run of spans of one (tensor, slot) - every element of a string_val, every chunk of a packed field - keeps its
   // running counts in registers: a round trip through global memory per span would make each iteration wait for the last.
   uint32_t run_tensor = ~0u, run_slot = 0;
@@ -922,16 +1031,16 @@ __device__ void finalize_body(const DecTables& T, uint32_t mi, uint32_t s0, uint
       if (st != run_tensor || ss != run_slot) {
         if (run_tensor != ~0u) {
           T.tensors[run_tensor].n_elems[run_slot] = run_elems;
-          if (run_slot == 4) T.tensor_pool[run_tensor] = run_str;
+          if (ragged_slot(run_slot)) T.tensors[run_tensor].dst_off[run_slot] = run_str;
         }
         run_tensor = st;
         run_slot = ss;
         run_elems = T.tensors[st].n_elems[ss];
-        run_str = ss == 4 ? T.tensor_pool[st] : 0;
+        run_str = ragged_slot(ss) ? T.tensors[st].dst_off[ss] : 0;
       }
       s.elem_base = run_elems;
       run_elems += nx_n[j];
-      if (ss == 4) {  // string_val: the only slot whose spans are SC_STR
+      if (ragged_slot(ss)) {  // string_val / resource_handle_val / variant_val: the slots whose spans are SC_STR
         s.elem_tile0 = run_str;
         run_str += nx_len[j];
       }
@@ -939,18 +1048,18 @@ __device__ void finalize_body(const DecTables& T, uint32_t mi, uint32_t s0, uint
   }
   if (run_tensor != ~0u) {
     T.tensors[run_tensor].n_elems[run_slot] = run_elems;
-    if (run_slot == 4) T.tensor_pool[run_tensor] = run_str;
+    if (ragged_slot(run_slot)) T.tensors[run_tensor].dst_off[run_slot] = run_str;
   }
   for (uint32_t ti = mo.first_tensor; ti < mo.first_tensor + mo.n_tensors; ++ti) {
     tfs_tensor_out_t& t = T.tensors[ti];
     uint64_t bytes = 0;
-    const uint64_t str_bytes = T.tensor_pool[ti];
     for (uint32_t sl = 0; sl < TFS_N_SLOTS; ++sl) {
       const int32_t ty = slot_dst_type(sl, t.dtype, T.flags, t.n_elems[sl]);
       t.dst_type[sl] = ty;
+      const uint64_t str_bytes = t.dst_off[sl];  // ragged slots: the running byte count of the slot's elements was kept here
       t.dst_off[sl] = bytes;  // relative to the tensor's base for now
-      // string_val: (n + 1) u64 offsets, then the bytes of all elements (TFS_T_RAGGED)
-      const uint64_t need = sl == 4 ? (t.n_elems[4] ? 8ull * (t.n_elems[4] + 1) + str_bytes : 0ull) : slot_pool_bytes(sl, ty, t.n_elems[sl]);
+      // ragged slots: (n + 1) u64 offsets, then the bytes of all elements (TFS_T_RAGGED)
+      const uint64_t need = ragged_slot(sl) ? (t.n_elems[sl] ? 8ull * (t.n_elems[sl] + 1) + str_bytes : 0ull) : slot_pool_bytes(sl, ty, t.n_elems[sl]);
       bytes += (need + 63u) & ~static_cast<uint64_t>(63);
     }
     T.tensor_pool[ti] = bytes;

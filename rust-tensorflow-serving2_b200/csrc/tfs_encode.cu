@@ -652,6 +652,8 @@ bool compile_field(const tfs_field_desc_t& f, EncField* o, uint64_t* max_body) {
       if (st != TFS_T_I64 || (dt != TFS_T_NONE && dt != TFS_T_I64)) return false;
       return varint_class(VM_I64, 10);
     case TFS_KIND_BYTES_LIST:  // BytesList.value = 1: the record key byte (1 << 3 | 2) is this kind's own number
+    case TFS_KIND_RESOURCE_HANDLE_VAL:  // repeated messages, every element the encoded body of one (tensor.proto:72-76):
+    case TFS_KIND_VARIANT_VAL:          // on the wire `key len body` per element, exactly the shape of repeated bytes
     case TFS_KIND_STRING_VAL: {  // repeated bytes, flattened: (n + 1) u64 offsets, then the bytes
       if (st != TFS_T_RAGGED || (dt != TFS_T_NONE && dt != TFS_T_RAGGED) || (reinterpret_cast<uintptr_t>(f.data) & 7u) != 0) return false;
       o->is_varint = FC_RAGGED;
@@ -661,7 +663,7 @@ bool compile_field(const tfs_field_desc_t& f, EncField* o, uint64_t* max_body) {
       *max_body = f.n_elems * (1 + vl) + f.aux;
       return true;
     }
-    default: return false;  // message-typed fields (resource_handle_val, variant_val): not on the encode ABI
+    default: return false;
   }
 }
 

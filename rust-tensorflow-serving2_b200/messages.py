@@ -58,9 +58,13 @@ class TensorProto:
     dcomplex_val: Any = None
     uint32_val: Any = None
     uint64_val: Any = None
+    # repeated ResourceHandleProto / VariantTensorDataProto (tensor.proto:72-76): a list whose element i is the ENCODED BODY of
+    # message i (bytes-like; `resource_handle_body` / `variant_body` below build them), or a ready Ragged block
+    resource_handle_val: Any = None
+    variant_val: Any = None
 
     def payloads(self):
-        """(kind, value) for every payload field that is set, ascending field number."""
+        """(kind, value) for every payload field that is set."""
         for kind in abi.SLOT_KINDS:
             v = getattr(self, abi.KIND_FIELD_NAMES[kind])
             if v is not None:
@@ -206,7 +210,7 @@ def build_batch(messages, kind) -> BuiltBatch:
         td.first_field = len(fld_l)
         n = 0
         for k, v in t.payloads():
-            if k == abi.KIND_STRING_VAL:  # repeated bytes: a list of bytes-like elements, or a ready block
+            if k in abi.RAGGED_KINDS:  # repeated bytes / repeated messages: a list of bytes-like elements, or a ready block
                 if not isinstance(v, Ragged):
                     blk = ragged_block(v)
                     v = Ragged(blk, len(v), blk.size - 8 * (len(v) + 1))
@@ -329,6 +333,130 @@ def build_batch(messages, kind) -> BuiltBatch:
                       (abi.FieldDesc * len(fld_l))(*fld_l), (abi.Str * len(flt_l))(*flt_l), keep)
 
 
+# ---- the two message-typed TensorProto fields: element bodies are framed on the host (a handful of strings and scalars),
+#      the TensorProtos INSIDE a variant are encoded / decoded by the library like any other tensor ----
+def _varint(v: int) -> bytes:
+    out = bytearray()
+    v &= (1 << 64) - 1
+    while v >= 0x80:
+        out.append((v & 0x7F) | 0x80)
+        v >>= 7
+    out.append(v)
+    return bytes(out)
+
+
+def _len_field(tag: int, payload: bytes) -> bytes:
+    return _varint((tag << 3) | 2) + _varint(len(payload)) + bytes(payload)
+
+
+@dataclass
+class ResourceHandleProto:
+    """resource_handle.proto:13-30"""
+    device: str = ""
+    container: str = ""
+    name: str = ""
+    hash_code: int = 0
+    maybe_type_name: str = ""
+
+
+@dataclass
+class VariantTensorDataProto:
+    """tensor.proto:86-94; `tensors` are TensorProto objects (recursive)"""
+    type_name: str = ""
+    metadata: bytes = b""
+    tensors: List[Any] = field(default_factory=list)
+
+
+def resource_handle_body(h: ResourceHandleProto) -> bytes:
+    """Encoded body of one resource_handle_val element: proto3 defaults skipped, ascending tags (prost's encode_raw)."""
+    out = b""
+    for tag, sv in ((1, h.device), (2, h.container), (3, h.name)):
+        if sv:
+            out += _len_field(tag, sv.encode("utf-8"))
+    if h.hash_code:
+        out += _varint((4 << 3) | 0) + _varint(h.hash_code)
+    if h.maybe_type_name:
+        out += _len_field(5, h.maybe_type_name.encode("utf-8"))
+    return out
+
+
+def variant_body(v: VariantTensorDataProto, encode_tensor) -> bytes:
+    """Encoded body of one variant_val element.  `encode_tensor(TensorProto) -> bytes` encodes the tensors it holds (the
+    codec itself: `lambda t: encoder.encode_host([t], abi.MSG_TENSOR_PROTO).all_bytes()[0]`)."""
+    out = b""
+    if v.type_name:
+        out += _len_field(1, v.type_name.encode("utf-8"))
+    if v.metadata:
+        out += _len_field(2, bytes(v.metadata))
+    for t in v.tensors:
+        out += _len_field(3, encode_tensor(t))
+    return out
+
+
+def parse_resource_handle(body: bytes) -> ResourceHandleProto:
+    """Opens one decoded resource_handle_val element (the library has validated it: no error handling needed here)."""
+    h, i = ResourceHandleProto(), 0
+    while i < len(body):
+        key, i = _read_varint(body, i)
+        tag, wt = key >> 3, key & 7
+        if wt == 2:
+            n, i = _read_varint(body, i)
+            val = bytes(body[i: i + n])
+            i += n
+            if tag in (1, 2, 3, 5):
+                setattr(h, {1: "device", 2: "container", 3: "name", 5: "maybe_type_name"}[tag], val.decode("utf-8"))
+        elif wt == 0:
+            val, i = _read_varint(body, i)
+            if tag == 4:
+                h.hash_code = val
+        elif wt == 1:
+            i += 8
+        elif wt == 5:
+            i += 4
+        else:
+            raise ValueError("groups inside a validated element are not expected here")
+    return h
+
+
+def parse_variant(body: bytes):
+    """-> (type_name, metadata, [encoded TensorProto bytes, ...]) of one decoded variant_val element; the tensors are
+    decoded by the library (TFS_MSG_TENSOR_PROTO)."""
+    type_name, metadata, tensors, i = "", b"", [], 0
+    while i < len(body):
+        key, i = _read_varint(body, i)
+        tag, wt = key >> 3, key & 7
+        if wt == 2:
+            n, i = _read_varint(body, i)
+            val = bytes(body[i: i + n])
+            i += n
+            if tag == 1:
+                type_name = val.decode("utf-8")
+            elif tag == 2:
+                metadata = val
+            elif tag == 3:
+                tensors.append(val)
+        elif wt == 0:
+            _, i = _read_varint(body, i)
+        elif wt == 1:
+            i += 8
+        elif wt == 5:
+            i += 4
+        else:
+            raise ValueError("groups inside a validated element are not expected here")
+    return type_name, metadata, tensors
+
+
+def _read_varint(b, i):
+    v, shift = 0, 0
+    while True:
+        c = b[i]
+        i += 1
+        v |= (c & 0x7F) << shift
+        shift += 7
+        if c < 0x80:
+            return v & ((1 << 64) - 1), i
+
+
 def replicate_batch(built: BuiltBatch, n: int) -> BuiltBatch:
     """`n` copies of a ONE-message batch as one batch of n messages sharing the payload arrays and strings (the C1 shape:
     2^20 copies of a tiny request).  The descriptor arrays are replicated with numpy; a Python loop per message would
@@ -393,7 +521,7 @@ def _tensor_from_out(to, strings: bytes, pool: np.ndarray) -> Tuple[str, TensorP
             continue
         ty = int(to.dst_type[slot])
         off = int(to.dst_off[slot])
-        if kind == abi.KIND_STRING_VAL:
+        if kind in abi.RAGGED_KINDS:
             offs = pool[off: off + 8 * (n + 1)].view("<u8")
             base = off + 8 * (n + 1)
             val = [bytes(pool[base + int(offs[i]): base + int(offs[i + 1])]) for i in range(n)]

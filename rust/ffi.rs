@@ -4,7 +4,7 @@
 use std::os::raw::{c_char, c_void};
 
 pub const TFS_MAX_DIMS: usize = 8;
-pub const TFS_N_SLOTS: usize = 12;
+pub const TFS_N_SLOTS: usize = 14;
 
 pub const TFS_OK: i32 = 0;
 pub const TFS_ERR_UNSUPPORTED: i32 = 12;

@@ -15,6 +15,7 @@ FIELD_NP = {
     "int64_val": "<i8", "bool_val": "u1", "dcomplex_val": "<f8", "half_val": "<i4", "uint32_val": "<u4",
     "uint64_val": "<u8",
 }
+RAGGED_FIELDS = ("string_val", "resource_handle_val", "variant_val")
 KIND_OF = {"tensor": abi.MSG_TENSOR_PROTO, "request": abi.MSG_PREDICT_REQUEST, "response": abi.MSG_PREDICT_RESPONSE,
            "input": abi.MSG_INPUT, "classify": abi.MSG_CLASSIFY_REQUEST}
 
@@ -56,8 +57,8 @@ def tensor_from_desc(d) -> tfs.TensorProto:
     if d["shape"] is not None:
         t.tensor_shape = tfs.TensorShapeProto(list(d["shape"]), d["unknown_rank"])
     for k, hx in d["fields"].items():
-        if k == "string_val":
-            t.string_val = [bytes.fromhex(x) for x in hx]
+        if k in RAGGED_FIELDS:
+            setattr(t, k, [bytes.fromhex(x) for x in hx])
             continue
         a = np.frombuffer(bytes.fromhex(hx), dtype=FIELD_NP[k]).copy()
         if k == "bool_val":
@@ -87,8 +88,9 @@ def tensor_to_desc(t: tfs.TensorProto):
         d["unknown_rank"] = bool(t.tensor_shape.unknown_rank)
     for kind, v in t.payloads():
         name = abi.KIND_FIELD_NAMES[kind]
-        if name == "string_val":
-            d["fields"][name] = [bytes(x).hex() for x in v]
+        if name in RAGGED_FIELDS:
+            if len(v):
+                d["fields"][name] = [bytes(x).hex() for x in v]
             continue
         a = np.ascontiguousarray(v)
         if a.size:
@@ -185,7 +187,7 @@ def assert_same_decoded_fast(a, b, kind: str, ctx=""):
             assert sorted(px) == sorted(py), f"{where}: fields {sorted(px)} vs {sorted(py)}"
             for k in px:
                 name = abi.KIND_FIELD_NAMES[k]
-                if name == "string_val":
+                if name in RAGGED_FIELDS:
                     assert [bytes(e) for e in px[k]] == [bytes(e) for e in py[k]], f"{where}: {name}"
                     continue
                 ax = np.ascontiguousarray(px[k]).astype(FIELD_NP[name], copy=False) if np.asarray(px[k]).dtype.kind != "b" else np.asarray(px[k]).astype("u1")

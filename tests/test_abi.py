@@ -47,7 +47,7 @@ def test_host_only_helpers():
     L = _lib.lib()
     assert [L.tfs_slot_of_kind(k) for k in abi.SLOT_KINDS] == list(range(abi.TFS_N_SLOTS))
     assert [L.tfs_kind_of_slot(s) for s in range(abi.TFS_N_SLOTS)] == list(abi.SLOT_KINDS)
-    assert L.tfs_slot_of_kind(14) == -1
+    assert L.tfs_slot_of_kind(18) == -1 and L.tfs_slot_of_kind(14) == 12 and L.tfs_slot_of_kind(15) == 13
     for t, size in abi.TYPE_SIZE.items():
         assert L.tfs_type_size(t) == size
     assert L.tfs_strerror(abi.TFS_ERR_INVALID_VARINT) == b"invalid varint"
