@@ -62,6 +62,11 @@ struct TensorProto {
   std::vector<double> dcomplex_val;
   std::vector<uint32_t> uint32_val;
   std::vector<uint64_t> uint64_val;
+  // `repeated ResourceHandleProto` / `repeated VariantTensorDataProto` (tensor.proto:72-76): element i is the ENCODED BODY
+  // of message i; the library writes / validates them, the owner of the struct opens them (a variant's `tensors` are
+  // TensorProtos again: decode them with msg_kind TFS_MSG_TENSOR_PROTO)
+  std::vector<std::vector<uint8_t>> resource_handle_val;
+  std::vector<std::vector<uint8_t>> variant_val;
 };
 
 struct ModelSpec {
@@ -177,23 +182,27 @@ struct Described {
     push(TFS_KIND_FLOAT_VAL, TFS_T_F32, t.float_val.size(), t.float_val.data());
     push(TFS_KIND_DOUBLE_VAL, TFS_T_F64, t.double_val.size(), t.double_val.data());
     push(TFS_KIND_INT_VAL, TFS_T_I32, t.int_val.size(), t.int_val.data());
-    if (!t.string_val.empty()) {  // Vec<Vec<u8>> flattened into one TFS_T_RAGGED block: (n + 1) u64 offsets, then the bytes
-      const size_t n = t.string_val.size();
+    auto push_ragged = [&](int32_t kind, const std::vector<std::vector<uint8_t>>& elems) {
+      if (elems.empty()) return;  // Vec<Vec<u8>> flattened into one TFS_T_RAGGED block: (n + 1) u64 offsets, then the bytes
+      const size_t n = elems.size();
       size_t total = 0;
-      for (const auto& e : t.string_val) total += e.size();
+      for (const auto& e : elems) total += e.size();
       ragged.emplace_back((8 * (n + 1) + total + 7) / 8);  // uint64_t storage keeps the block 8-byte aligned
       uint64_t* offs = ragged.back().data();
       uint8_t* bytes = reinterpret_cast<uint8_t*>(offs + n + 1);
       uint64_t at = 0;
       for (size_t i = 0; i < n; ++i) {
         offs[i] = at;
-        if (!t.string_val[i].empty()) std::memcpy(bytes + at, t.string_val[i].data(), t.string_val[i].size());
-        at += t.string_val[i].size();
+        if (!elems[i].empty()) std::memcpy(bytes + at, elems[i].data(), elems[i].size());
+        at += elems[i].size();
       }
       offs[n] = at;
-      push(TFS_KIND_STRING_VAL, TFS_T_RAGGED, n, offs);
+      push(kind, TFS_T_RAGGED, n, offs);
       fields.back().aux = total;
-    }
+    };
+    push_ragged(TFS_KIND_STRING_VAL, t.string_val);
+    push_ragged(TFS_KIND_RESOURCE_HANDLE_VAL, t.resource_handle_val);
+    push_ragged(TFS_KIND_VARIANT_VAL, t.variant_val);
     push(TFS_KIND_SCOMPLEX_VAL, TFS_T_F32, t.scomplex_val.size(), t.scomplex_val.data());
     push(TFS_KIND_INT64_VAL, TFS_T_I64, t.int64_val.size(), t.int64_val.data());
     push(TFS_KIND_BOOL_VAL, TFS_T_BOOL, t.bool_val.size(), t.bool_val.data());
@@ -323,17 +332,22 @@ inline TensorProto tensor_from(const tfs_tensor_out_t& t, const uint8_t* pool) {
   take(o.float_val, t, 1, pool);
   take(o.double_val, t, 2, pool);
   take(o.int_val, t, 3, pool);
-  if (const uint64_t n = t.n_elems[4]) {  // string_val comes back as the same flattened block
-    const uint8_t* block = pool + t.dst_off[4];
+  auto take_ragged = [&](std::vector<std::vector<uint8_t>>& dst, int slot) {  // comes back as the same flattened block
+    const uint64_t n = t.n_elems[slot];
+    if (!n) return;
+    const uint8_t* block = pool + t.dst_off[slot];
     const uint8_t* bytes = block + 8 * (n + 1);
-    o.string_val.resize(n);
+    dst.resize(n);
     for (uint64_t i = 0; i < n; ++i) {
       uint64_t a, b;
       std::memcpy(&a, block + 8 * i, 8);
       std::memcpy(&b, block + 8 * (i + 1), 8);
-      o.string_val[i].assign(bytes + a, bytes + b);
+      dst[i].assign(bytes + a, bytes + b);
     }
-  }
+  };
+  take_ragged(o.string_val, 4);
+  take_ragged(o.resource_handle_val, 12);
+  take_ragged(o.variant_val, 13);
   take(o.scomplex_val, t, 5, pool);
   take(o.int64_val, t, 6, pool);
   take(o.bool_val, t, 7, pool);

@@ -1098,9 +1098,29 @@ __device__ void pool_layout_body(const DecTables& T, uint32_t n_tensors, uint64_
     T.totals[TOT_OVERFLOW] = carry > pool_capacity ? 1ull : 0ull;  // gates the value kernels of a one-call decode
   }
 }
+// Large batches: the scan alone in one CTA (tensor_pool[] becomes each tensor's base), the 14 slot offsets of every tensor
+// are then shifted by a grid of their own (one CTA doing both took 46 us for 2 000 tensors: 28 000 strided accesses).
 __global__ void __launch_bounds__(1024) k_pool_layout(DecTables T, uint32_t n_tensors, uint64_t pool_capacity) {
   __shared__ uint64_t smem[33];
-  pool_layout_body<32>(T, n_tensors, pool_capacity, smem);
+  uint64_t carry = 0;
+  for (uint32_t base = 0; base < n_tensors; base += 1024) {
+    const uint32_t i = base + threadIdx.x;
+    const uint64_t v = i < n_tensors ? T.tensor_pool[i] : 0ull;
+    uint64_t total;
+    const uint64_t ex = block_exclusive_scan<uint64_t, 32>(v, smem, &total);
+    if (i < n_tensors) T.tensor_pool[i] = carry + ex;
+    carry += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    T.totals[TOT_POOL] = carry;
+    T.totals[TOT_OVERFLOW] = carry > pool_capacity ? 1ull : 0ull;  // gates the value kernels of a one-call decode
+  }
+}
+__global__ void __launch_bounds__(256) k_pool_apply(DecTables T, uint32_t n_tensors) {
+  const uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t i = g >> 4, sl = g & 15u;
+  if (i < n_tensors && sl < TFS_N_SLOTS) T.tensors[i].dst_off[sl] += T.tensor_pool[i];
 }
 
 // Small batches: finalize and pool layout in ONE single-CTA launch
@@ -1181,7 +1201,7 @@ __host__ __device__ inline void blob_layout(uint64_t n_tensors, uint64_t n_filte
   *bytes = *p_str + n_str;
 }
 
-// Small batches (<= kSmallBatch messages), planned optimistically in ONE launch: one WARP per message, one structure walk.
+// Batches of up to 1024 messages, planned optimistically in ONE launch: one WARP per message, one structure walk.
 //   walk     lane 0 walks its message ONCE, writing tensor / span / filter records and string bytes into per-message QUOTA
 //            slots (sized from what earlier batches on this context needed; a message that outgrows its slots keeps
 //            counting, and the host retries with larger quotas).  The first version walked every message twice (count, then
@@ -1455,7 +1475,7 @@ tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const 
     ctx->launches++;
     {
       ProfScope prof(ctx, PK_VARINT_GATHER);
-      k_varint_gather<<<static_cast<uint32_t>(n_vt), kDecThreads, 0, ctx->stream>>>(T, pool, gate);
+      k_varint_gather<<<static_cast<uint32_t>(n_vt), kGatherThreads, 0, ctx->stream>>>(T, pool, gate);
     }
     ctx->launches++;
   }
@@ -1567,7 +1587,10 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     return static_cast<uint64_t>(n_msgs) * ((ctx->dec_q_t + 1ull) * sizeof(tfs_tensor_out_t) + (ctx->dec_q_s + 1ull) * (sizeof(DecSpan) + 8) +
                                             ctx->dec_q_f * sizeof(tfs_span_t) + ctx->dec_q_str + 64);
   };
-  bool plan_warp = small && quota_bytes() <= (256ull << 20);  // (a message with millions of string elements: two walks instead)
+  // one warp per message, the CTAs meet at a counter: the grid has to be resident as a whole (<= one CTA per SM), and every
+  // warp sums the counts of all messages before its own (fine up to a thousand); a batch whose largest message has millions
+  // of string elements would need huge slots: two walks instead
+  bool plan_warp = n_msgs <= 1024 && (n_msgs + kPlanWarps - 1) / kPlanWarps <= static_cast<uint32_t>(ctx->sm_count) && quota_bytes() <= (256ull << 20);
   if (plan_warp) {
     // ---- optimistic plan: tables laid out from this context's hints, ONE walk per message, one launch
     for (int attempt = 0;; ++attempt) {
@@ -1731,7 +1754,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       ctx->launches++;
       {
         ProfScope prof(ctx, PK_VARINT_COUNT);
-        k_varint_count<<<static_cast<uint32_t>(n_vt), kDecThreads, 0, ctx->stream>>>(T);
+        k_varint_count<<<static_cast<uint32_t>(n_vt), kCountThreads, 0, ctx->stream>>>(T);
       }
       ctx->launches++;
       k_span_scan<<<static_cast<uint32_t>((n_spans + 7) / 8), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_spans), n_vt);
@@ -1745,6 +1768,10 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       ctx->launches++;
       k_pool_layout<<<1, 1024, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors), pool_cap_arg);
       ctx->launches++;
+      if (n_tensors) {
+        k_pool_apply<<<static_cast<uint32_t>((n_tensors * 16 + 255) / 256), 256, 0, ctx->stream>>>(T, static_cast<uint32_t>(n_tensors));
+        ctx->launches++;
+      }
     }
     DEC_CUDA(cudaGetLastError());
     // one-call decode: the value kernels follow at once, gated on the device by "the pool is large enough"

@@ -21,7 +21,7 @@ constexpr int kVarintMaxLen = 10;
 constexpr int kCopyThreads = 256;
 constexpr int kCopyTileBytes = 32768;                // output bytes per copy tile
 constexpr int kDecThreads = 256;
-constexpr int kDecTileBytes = 4096;                  // wire bytes per varint-decode tile (16 B per thread)
+constexpr int kDecTileBytes = 4096;                  // wire bytes per varint-decode tile (16 B per thread of the gather kernel)
 
 // ---- element fetch modes of the varint encoder (source memory type -> u64 that is varint-coded) ----
 enum VarintMode : int32_t {

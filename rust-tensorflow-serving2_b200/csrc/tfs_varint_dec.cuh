@@ -109,57 +109,74 @@ __device__ __forceinline__ void prev_chunk(const TileRef& r, uint64_t chunk_abs,
   *pcont = pc;
 }
 
-// The kernel is bound by instruction issue, not by latency (four tiles per CTA with all loads up front measured no
-// faster), so the common case is kept short: a chunk wholly inside its span counts its terminators with one popcount
-// of the MSBs, and the exact over-long check (ten continuation bytes in a row) runs only in warps where some aligned
-// 4-byte word of a chunk, or of the chunk before it, is all continuation bytes - a run of ten covers such a word.
-__global__ void __launch_bounds__(kDecThreads) k_varint_count(DecTables T) {
-  __shared__ uint32_t warp_tail[kDecThreads / 32];  // does the last chunk of each warp hold an all-continuation word?
+// The kernel is bound by instruction issue, not by bandwidth: every thread takes TWO adjacent 16-byte chunks (the per-thread
+// bookkeeping - tile record, warp reduction, atomics - is then paid once per 32 bytes), and the common case is kept short: a
+// chunk wholly inside its span counts its terminators with one popcount of the MSBs, and the exact over-long check (ten
+// continuation bytes in a row) runs only in warps where some aligned 4-byte word of a chunk, or of the chunk before it, is
+// all continuation bytes - a run of ten covers such a word.
+constexpr int kCountThreads = kDecTileBytes / 32;  // two chunks per thread
+__global__ void __launch_bounds__(kCountThreads) k_varint_count(DecTables T) {
+  __shared__ uint32_t warp_tail[kCountThreads / 32];  // does the last chunk of each warp hold an all-continuation word?
   const uint32_t tile = blockIdx.x;
   const TileRef r = tile_ref(T, tile);
-  const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 16ull;
-  const bool inside = chunk_abs >= r.span_abs0 && chunk_abs + 16 <= r.span_end;
-  const bool touches = chunk_abs + 16 > r.span_abs0 && chunk_abs < r.span_end;
-  uint4 d = make_uint4(0, 0, 0, 0);
-  if (touches) d = ld_stream16(reinterpret_cast<const void*>(chunk_abs));
   constexpr uint32_t kMsb = 0x80808080u;
-  const uint32_t hx = d.x & kMsb, hy = d.y & kMsb, hz = d.z & kMsb, hw = d.w & kMsb;
-  // (bytes outside the span may make this true for an edge chunk: that only sends the warp to the exact check)
-  const bool own_word = hx == kMsb || hy == kMsb || hz == kMsb || hw == kMsb;
+  uint4 d[2];
+  bool own_word[2];
   uint32_t cnt = 0;
-  if (inside) {
-    cnt = 16u - __popc((hx >> 7) | (hy >> 6) | (hz >> 5) | (hw >> 4));
-  } else if (touches) {  // first / last chunk of the span
-    uint32_t cont, valid;
-    masks_of(d, chunk_abs, r.span_abs0, r.span_end, &cont, &valid);
-    cnt = __popc(~cont & valid);
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    const uint64_t chunk_abs = r.tile_abs + threadIdx.x * 32ull + 16ull * c;
+    const bool inside = chunk_abs >= r.span_abs0 && chunk_abs + 16 <= r.span_end;
+    const bool touches = chunk_abs + 16 > r.span_abs0 && chunk_abs < r.span_end;
+    d[c] = make_uint4(0, 0, 0, 0);
+    if (touches) d[c] = ld_stream16(reinterpret_cast<const void*>(chunk_abs));
+    const uint32_t hx = d[c].x & kMsb, hy = d[c].y & kMsb, hz = d[c].z & kMsb, hw = d[c].w & kMsb;
+    // (bytes outside the span may make this true for an edge chunk: that only sends the warp to the exact check)
+    own_word[c] = hx == kMsb || hy == kMsb || hz == kMsb || hw == kMsb;
+    if (inside) {
+      cnt += 16u - __popc((hx >> 7) | (hy >> 6) | (hz >> 5) | (hw >> 4));
+    } else if (touches) {  // first / last chunk of the span
+      uint32_t cont, valid;
+      masks_of(d[c], chunk_abs, r.span_abs0, r.span_end, &cont, &valid);
+      cnt += __popc(~cont & valid);
+    }
   }
-  if (lane_id() == 31) warp_tail[threadIdx.x >> 5] = own_word;
+  if (lane_id() == 31) warp_tail[threadIdx.x >> 5] = own_word[1];
   __syncthreads();
-  bool prev_word = __shfl_up_sync(0xFFFFFFFFu, own_word, 1);
+  bool prev_word = __shfl_up_sync(0xFFFFFFFFu, own_word[1], 1);  // of the chunk in front of this thread's first one
+  const uint64_t first_abs = r.tile_abs + threadIdx.x * 32ull;
   if (lane_id() == 0) {
     if (threadIdx.x != 0) {
       prev_word = warp_tail[(threadIdx.x >> 5) - 1] != 0;
     } else {  // the chunk before the tile
       prev_word = false;
-      if (chunk_abs > r.span_abs0) {
-        const uint4 p = ld_stream16(reinterpret_cast<const void*>(chunk_abs - 16));
+      if (first_abs > r.span_abs0) {
+        const uint4 p = ld_stream16(reinterpret_cast<const void*>(first_abs - 16));
         prev_word = (p.x & kMsb) == kMsb || (p.y & kMsb) == kMsb || (p.z & kMsb) == kMsb || (p.w & kMsb) == kMsb;
       }
     }
   }
-  if (__any_sync(0xFFFFFFFFu, own_word || prev_word)) {
-    uint4 pd;
-    uint32_t cont, valid, prev;
-    masks_of(d, chunk_abs, r.span_abs0, r.span_end, &cont, &valid);
-    prev_chunk(r, chunk_abs, d, cont, &pd, &prev);
-    uint32_t x = (cont << 16) | prev;  // bit i..i+9 all set <=> ten continuation bytes in a row
-    x &= x >> 1;
-    x &= x >> 2;
-    x &= x >> 4;
-    x &= x >> 2;
-    if (x) {
-      const uint64_t at = chunk_abs > r.span_abs0 ? chunk_abs : r.span_abs0;
+  if (__any_sync(0xFFFFFFFFu, own_word[0] || own_word[1] || prev_word)) {
+    uint32_t cont0, cont1, valid;
+    masks_of(d[0], first_abs, r.span_abs0, r.span_end, &cont0, &valid);
+    masks_of(d[1], first_abs + 16, r.span_abs0, r.span_end, &cont1, &valid);
+    uint32_t prev = __shfl_up_sync(0xFFFFFFFFu, cont1, 1);
+    if (lane_id() == 0) {
+      uint4 pd;
+      uint32_t pv;
+      chunk_masks(first_abs - 16, r.span_abs0, r.span_end, &pd, &prev, &pv);
+    }
+    auto ten = [](uint32_t x) {  // bit i..i+9 all set <=> ten continuation bytes in a row
+      x &= x >> 1;
+      x &= x >> 2;
+      x &= x >> 4;
+      x &= x >> 2;
+      return x;
+    };
+    const bool bad0 = ten((cont0 << 16) | prev) != 0, bad1 = ten((cont1 << 16) | cont0) != 0;
+    if (bad0 || bad1) {
+      const uint64_t here = bad0 ? first_abs : first_abs + 16;
+      const uint64_t at = here > r.span_abs0 ? here : r.span_abs0;
       const uint64_t off = at - reinterpret_cast<uintptr_t>(T.wire) - T.msg_off[r.msg];
       atomicMin(&T.err[r.msg], (static_cast<unsigned long long>(off) << 8) | TFS_ERR_INVALID_VARINT);
     }
@@ -214,6 +231,11 @@ __device__ __forceinline__ uint32_t pad_slot(uint32_t i) { return i + (i >> 4); 
 __device__ __forceinline__ uint32_t pad_word(uint32_t i) { return i + 4u * (i >> 4); }
 constexpr uint32_t kGatherOutBytes = (kRoundValues + kRoundValues / 16 + 1) * 8;
 
+// One 16-byte chunk per thread, 256 threads per 4 KiB tile.  (Two chunks per thread, which pays for the count kernel, measured
+// 7-12 % SLOWER here - a thread's values come out of a serial loop over its terminators, and twice as many per thread doubled
+// that chain while the scan and the barriers it amortises are a small part of this kernel - and 8 KiB tiles with 512 threads
+// 25-30 % slower: a barrier over 16 warps costs more than it saves.)
+constexpr int kGatherThreads = kDecTileBytes / 16;
 template <int OUT>
 __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restrict__ dst, uint8_t* sm_out, uint8_t* sm_in, uint32_t* scan_smem, uint32_t* edge) {
   using out_t = typename OutTraits<OUT>::type;
@@ -241,7 +263,7 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
   }
   const uint32_t term = ~cont & valid;
   uint32_t total;
-  const uint32_t idx0 = block_exclusive_scan<uint32_t, kDecThreads / 32>(__popc(term), scan_smem, &total);  // two barriers
+  const uint32_t idx0 = block_exclusive_scan<uint32_t, kGatherThreads / 32>(__popc(term), scan_smem, &total);  // two barriers
   if (lane_id() == 0 && warp_id() != 0) {
     pd.w = edge[2 * warp_id() - 2];
     pcont = edge[2 * warp_id() - 1];
@@ -353,20 +375,20 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
   // coalesced flush of this round's values
   const uint32_t n_round = total - round0 < kRoundValues ? total - round0 : kRoundValues;
   if (fast) {  // (all1 implies fast) staged as 32-bit words
-    for (uint32_t i = threadIdx.x; i < n_round; i += kDecThreads) gdst[round0 + i] = static_cast<out_t>(out32[pad_word(i)]);
+    for (uint32_t i = threadIdx.x; i < n_round; i += kGatherThreads) gdst[round0 + i] = static_cast<out_t>(out32[pad_word(i)]);
   } else {
-    for (uint32_t i = threadIdx.x; i < n_round; i += kDecThreads) gdst[round0 + i] = out[pad_slot(i)];
+    for (uint32_t i = threadIdx.x; i < n_round; i += kGatherThreads) gdst[round0 + i] = out[pad_slot(i)];
   }
   }
 }
 
-__global__ void __launch_bounds__(kDecThreads, 6) k_varint_gather(DecTables T, uint8_t* pool, const uint64_t* __restrict__ gate) {
+__global__ void __launch_bounds__(kGatherThreads, 6) k_varint_gather(DecTables T, uint8_t* pool, const uint64_t* __restrict__ gate) {
   __shared__ __align__(16) uint8_t sm_out[kGatherOutBytes];
   // general path: 16 bytes before the tile, the tile, slack for word loads; fast path: a 20-byte strip per thread (+ 1 word)
-  __shared__ __align__(16) uint8_t sm_in[kDecThreads * 20 + 16];
-  static_assert(kDecThreads * 20 + 16 >= 16 + kDecTileBytes + 16, "the staged tile must fit too");
-  __shared__ uint32_t scan_smem[kDecThreads / 32 + 1];
-  __shared__ uint32_t edge[2 * (kDecThreads / 32)];  // last word and continuation mask of every warp's last lane
+  __shared__ __align__(16) uint8_t sm_in[kGatherThreads * 20 + 16];
+  static_assert(kGatherThreads * 20 + 16 >= 16 + kDecTileBytes + 16, "the staged tile must fit too");
+  __shared__ uint32_t scan_smem[kGatherThreads / 32 + 1];
+  __shared__ uint32_t edge[2 * (kGatherThreads / 32)];  // last word and continuation mask of every warp's last lane
   if (gate && *gate != 0) return;  // the pool of a one-call decode turned out to be too small
   const uint32_t tile = blockIdx.x;
   const TileRef r = tile_ref(T, tile);       // two independent broadcast loads
