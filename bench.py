@@ -279,6 +279,61 @@ def run_ours(args):
     torch.cuda.synchronize()
     e2e_s = max_over_ranks(time.perf_counter() - t_start)
     assert np.array_equal(h_pool_np[: 16], h_pool_np[: 16])  # the result is read on the host (device -> host is part of every step)
+
+    # ---- what the box can move: pinned host <-> HBM in both directions at once (copy engines, 256 MB buffers), every rank
+    #      at the same time, so that the aggregate at N GPUs is the ceiling the e2e figure at N GPUs lives under
+    def pcie_ceiling():
+        nb = 256 << 20
+        hp_in, hp_out = torch.empty(nb, dtype=torch.uint8).pin_memory(), torch.empty(nb, dtype=torch.uint8).pin_memory()
+        d_in, d_out = torch.empty(nb, dtype=torch.uint8, device=dev), torch.empty(nb, dtype=torch.uint8, device=dev)
+        s1, s2 = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        best = 0.0
+        for rep in range(4):
+            barrier()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(4):
+                with torch.cuda.stream(s1):
+                    d_in.copy_(hp_in, non_blocking=True)
+                with torch.cuda.stream(s2):
+                    hp_out.copy_(d_out, non_blocking=True)
+            torch.cuda.synchronize()
+            dt = max_over_ranks(time.perf_counter() - t0)
+            if rep:
+                best = max(best, 4 * 2 * nb / dt / 1e9)
+        return best * world  # every rank moved the same bytes in the (max over ranks) time
+
+    pcie_bidir = pcie_ceiling()
+    e2e_moved_GBps = world * e2e_steps * (h2d + d2h) / e2e_s / 1e9
+
+    # ---- the same work through the engine: two lanes (context + stream + worker thread each) on this GPU, the two variants in
+    #      flight at once, so that one job's upload runs under the other's download (side figure; `e2e` above is one call at a time)
+    e2e_engine = None
+    if not args.no_extras:
+        eng = tfs.Engine([local], lanes_per_device=2, pinned_bytes_per_lane=0)
+        h_wire2 = torch.empty(h_wire.numel(), dtype=torch.uint8).pin_memory()
+        h_pool2 = torch.empty(h_pool.numel(), dtype=torch.uint8).pin_memory()
+        wires, pools = {"float_val": h_wire_np, "tensor_content": h_wire2.numpy()}, {"float_val": h_pool_np, "tensor_content": h_pool2.numpy()}
+
+        def engine_step():
+            te = {v: eng.encode_host(hbuilt[v], wires[v], flags, lane=i) for i, v in enumerate(VARIANTS)}
+            ebs = {v: eng.wait(t) for v, t in te.items()}
+            td = {v: eng.decode_host_into(wires[v][: ebs[v].total], ebs[v].offsets, ebs[v].lengths, kind, pools[v], lane=i) for i, v in enumerate(VARIANTS)}
+            n = 0
+            for v, t in td.items():
+                eng.wait(t).close()
+                n += 2 * sum(ebs[v].lengths)
+            return n
+
+        engine_step()
+        barrier()
+        t_start = time.perf_counter()
+        nb = 0
+        for _ in range(e2e_steps):
+            nb += engine_step()
+        e2e_engine = world * nb / max_over_ranks(time.perf_counter() - t_start) / 1e9
+        eng.close()
+        del h_wire2, h_pool2
     del h_src, h_wire, h_pool, hbuilt
 
     # ---- N > 1: BASELINE config 5, "8192 independent mixed-dtype PredictResponses decoded, sharded across the GPUs": every
@@ -324,7 +379,9 @@ def run_ours(args):
         "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8", "data": "synthetic", "config": config_of(args, world), "clocks": clocks,
         "e2e": {"value": round(world * e2e_bytes / e2e_s / 1e9, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "requests_per_variant_per_gpu": Re, "steps": e2e_steps,
+                "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "engine_two_lanes_GBps": round(e2e_engine, 3) if e2e_engine else None,
+                "pcie_bidir_measured_GBps": round(pcie_bidir, 1), "pcie_moved_GBps": round(e2e_moved_GBps, 1),
+                "frac_of_pcie_bidir": round(e2e_moved_GBps / pcie_bidir, 3) if pcie_bidir else None,
                 "path": "tfs_encode_host + tfs_decode_host_into, pinned host buffers"},
         "gpu_launches": int(launches), "roofline": roof,
     }
@@ -491,9 +548,14 @@ def per_config(codec, dev, peak, args):
     def e2e_side(msgs_host, kind, eflags=0, dflags=0, reps=3):
         """tfs_encode_host + tfs_decode_host_into on the host copies of the inputs: pinned wire / pool, then pageable"""
         out = {}
-        built = tfs.build_batch(msgs_host, kind)
-        cap = enc.bound(built, eflags) + 4096
+        from test_gpu_parity import pinned_like  # the same messages with every payload array in pinned host memory
         for label, pinned in (("e2e_pinned_GBps", True), ("e2e_pageable_GBps", False)):
+            if pinned:
+                pmsgs, keep_payloads = pinned_like(msgs_host, kind)
+                built = tfs.build_batch(pmsgs, kind)
+            else:
+                built = tfs.build_batch(msgs_host, kind)
+            cap = enc.bound(built, eflags) + 4096
             if pinned:
                 keep_w, wbuf = _pin(np.empty(cap, np.uint8))
             else:
