@@ -3,8 +3,9 @@
 #![allow(non_camel_case_types, dead_code)]
 use std::os::raw::{c_char, c_void};
 
+pub const TFS_ABI_VERSION: i32 = 3;
 pub const TFS_MAX_DIMS: usize = 8;
-pub const TFS_N_SLOTS: usize = 14;
+pub const TFS_N_SLOTS: usize = 14;   // proto fields 4-13, 16, 17, 14, 15 (tfs_slot_of_kind)
 
 pub const TFS_OK: i32 = 0;
 pub const TFS_ERR_UNSUPPORTED: i32 = 12;
@@ -23,6 +24,8 @@ pub const TFS_KIND_DCOMPLEX_VAL: i32 = 12;
 pub const TFS_KIND_HALF_VAL: i32 = 13;
 pub const TFS_KIND_UINT32_VAL: i32 = 16;
 pub const TFS_KIND_UINT64_VAL: i32 = 17;
+pub const TFS_KIND_RESOURCE_HANDLE_VAL: i32 = 14;   // TFS_T_RAGGED: elements are ENCODED ResourceHandleProto bodies
+pub const TFS_KIND_VARIANT_VAL: i32 = 15;           // TFS_T_RAGGED: elements are ENCODED VariantTensorDataProto bodies
 
 pub const TFS_T_U8: i32 = 1;
 pub const TFS_T_I32: i32 = 5;
@@ -41,6 +44,9 @@ pub const TFS_F_ALIGN_PAYLOAD: u32 = 2;
 
 #[repr(C)] pub struct tfs_ctx_t { _private: [u8; 0] }
 #[repr(C)] pub struct tfs_decoded_t { _private: [u8; 0] }
+
+#[repr(C)] #[derive(Clone, Copy)]
+pub struct tfs_slab_t { pub ptr: *mut c_void, pub capacity: u64, pub id: u64 }
 
 #[repr(C)] #[derive(Clone, Copy, Default)]
 pub struct tfs_span_t { pub off: u64, pub len: u32, pub _pad: u32 }
@@ -101,6 +107,10 @@ extern "C" {
     pub fn tfs_ctx_create(device: i32, pinned_bytes: u64, out: *mut *mut tfs_ctx_t) -> i32;
     pub fn tfs_ctx_destroy(ctx: *mut tfs_ctx_t) -> i32;
     pub fn tfs_last_error_detail(ctx: *const tfs_ctx_t) -> *const c_char;
+    pub fn tfs_last_error_location(ctx: *const tfs_ctx_t, msg_index: *mut u32, offset: *mut u64) -> i32;
+    pub fn tfs_stage_acquire(ctx: *mut tfs_ctx_t, bytes: u64, align_skew: u32, out: *mut tfs_slab_t) -> i32;
+    pub fn tfs_stage_release(ctx: *mut tfs_ctx_t, slab: *const tfs_slab_t) -> i32;
+    pub fn tfs_stage_stats(ctx: *mut tfs_ctx_t, in_use: *mut u64, pool_bytes: *mut u64, fallbacks: *mut u64) -> i32;
     pub fn tfs_sync(ctx: *mut tfs_ctx_t) -> i32;
     pub fn tfs_host_alloc(ctx: *mut tfs_ctx_t, bytes: u64, out: *mut *mut c_void) -> i32;
     pub fn tfs_host_free(ctx: *mut tfs_ctx_t, p: *mut c_void) -> i32;
