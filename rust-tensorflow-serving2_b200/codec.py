@@ -14,7 +14,6 @@ from __future__ import annotations
 
 import ctypes as C
 import os
-from dataclasses import dataclass
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -86,13 +85,29 @@ class GpuContext:
             pass
 
 
-@dataclass
 class EncodedBatch:
-    wire: object            # torch.uint8 CUDA tensor (device path) or numpy uint8 array (host path)
-    offsets: List[int]      # first byte of each message (of its gRPC prefix with F_GRPC_PREFIX)
-    lengths: List[int]      # protobuf length of each message (prefix excluded)
-    total: int
-    flags: int = 0
+    """Result of an encode call.  `offsets` / `lengths` are Python lists built on first use; `offsets_np` / `lengths_np`
+    are the uint64 arrays the library filled (a batch of 10^6 tiny messages should never pay for the lists)."""
+
+    def __init__(self, wire, offsets, lengths, total: int, flags: int = 0):
+        self.wire = wire        # torch.uint8 CUDA tensor (device path) or numpy uint8 array (host path)
+        self.offsets_np = np.asarray(offsets, dtype=np.uint64)  # first byte of each message (of its gRPC prefix with F_GRPC_PREFIX)
+        self.lengths_np = np.asarray(lengths, dtype=np.uint64)  # protobuf length of each message (prefix excluded)
+        self.total = total
+        self.flags = flags
+        self._offsets = self._lengths = None
+
+    @property
+    def offsets(self) -> List[int]:
+        if self._offsets is None:
+            self._offsets = self.offsets_np.astype(np.int64).tolist()
+        return self._offsets
+
+    @property
+    def lengths(self) -> List[int]:
+        if self._lengths is None:
+            self._lengths = self.lengths_np.astype(np.int64).tolist()
+        return self._lengths
 
     def message_bytes(self, i: int) -> bytes:
         pre = 5 if self.flags & abi.F_GRPC_PREFIX else 0
@@ -133,7 +148,7 @@ class GpuEncoder:
         off, ln, total = (C.c_uint64 * max(1, n))(), (C.c_uint64 * max(1, n))(), C.c_uint64(0)
         self.ctx.check(lib().tfs_encode(self.ctx.handle, C.byref(built.batch), C.c_void_p(dst.data_ptr()), dst.numel(), flags,
                                         off, ln, C.byref(total)))
-        return EncodedBatch(dst, np.ctypeslib.as_array(off)[:n].astype(np.int64).tolist(), np.ctypeslib.as_array(ln)[:n].astype(np.int64).tolist(),
+        return EncodedBatch(dst, np.ctypeslib.as_array(off)[:n].copy(), np.ctypeslib.as_array(ln)[:n].copy(),
                             int(total.value), flags)
 
     def encode_host(self, messages: Sequence, kind: int, flags: int = 0, dst: Optional[np.ndarray] = None) -> EncodedBatch:
@@ -145,7 +160,7 @@ class GpuEncoder:
         off, ln, total = (C.c_uint64 * max(1, n))(), (C.c_uint64 * max(1, n))(), C.c_uint64(0)
         self.ctx.check(lib().tfs_encode_host(self.ctx.handle, C.byref(built.batch), C.c_void_p(dst.ctypes.data), dst.size, flags,
                                              off, ln, C.byref(total)))
-        return EncodedBatch(dst, np.ctypeslib.as_array(off)[:n].astype(np.int64).tolist(), np.ctypeslib.as_array(ln)[:n].astype(np.int64).tolist(),
+        return EncodedBatch(dst, np.ctypeslib.as_array(off)[:n].copy(), np.ctypeslib.as_array(ln)[:n].copy(),
                             int(total.value), flags)
 
 
@@ -349,7 +364,7 @@ class Engine:
             _, built, dst, off, ln, total, flags, n = rec
             if st != abi.TFS_OK:
                 raise TfsError(st, detail.value.decode("utf-8", "replace"))
-            return EncodedBatch(dst, np.ctypeslib.as_array(off)[:n].astype(np.int64).tolist(), np.ctypeslib.as_array(ln)[:n].astype(np.int64).tolist(),
+            return EncodedBatch(dst, np.ctypeslib.as_array(off)[:n].copy(), np.ctypeslib.as_array(ln)[:n].copy(),
                                 int(total.value), flags)
         _, wire, off, ln, pool, h, hp, kind = rec
         if st not in (abi.TFS_OK, abi.TFS_ERR_BATCH):

@@ -1,6 +1,7 @@
 // tfs_ctx.cu — context, memory plumbing and the small host-only helpers of include/tfs_gpu.h.
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -42,6 +43,56 @@ tfs_status_t pinned_reserve(tfs_ctx* ctx, void** p, size_t* cap, size_t bytes) {
   TFS_CUDA(ctx, cudaHostAlloc(p, want, cudaHostAllocDefault));
   *cap = want;
   return TFS_OK;
+}
+
+namespace {
+std::mutex g_down_mutex;
+std::vector<PinnedBlock> g_down_free;            // at most kDownKeep blocks, kDownKeepBytes in total
+constexpr size_t kDownKeep = 8;
+constexpr size_t kDownKeepBytes = size_t(2) << 30;
+}  // namespace
+
+tfs_status_t down_acquire(tfs_ctx* ctx, size_t bytes, PinnedBlock* out) {
+  {
+    std::lock_guard<std::mutex> lock(g_down_mutex);
+    int best = -1;
+    for (size_t i = 0; i < g_down_free.size(); ++i)
+      if (g_down_free[i].cap >= bytes && (best < 0 || g_down_free[i].cap < g_down_free[best].cap)) best = static_cast<int>(i);
+    if (best >= 0) {
+      *out = g_down_free[best];
+      g_down_free.erase(g_down_free.begin() + best);
+      return TFS_OK;
+    }
+  }
+  const size_t want = std::max(bytes + bytes / 2, static_cast<size_t>(1) << 16);
+  void* p = nullptr;
+  TFS_CUDA(ctx, cudaHostAlloc(&p, want, cudaHostAllocPortable));
+  out->p = p;
+  out->cap = want;
+  return TFS_OK;
+}
+
+void down_release(PinnedBlock b) {
+  if (!b.p) return;
+  PinnedBlock drop;
+  {
+    std::lock_guard<std::mutex> lock(g_down_mutex);
+    g_down_free.push_back(b);
+    size_t total = 0;
+    for (const PinnedBlock& x : g_down_free) total += x.cap;
+    if (g_down_free.size() > kDownKeep || total > kDownKeepBytes) {  // let the smallest go (a large one is the expensive one to get back)
+      size_t k = 0;
+      for (size_t i = 1; i < g_down_free.size(); ++i)
+        if (g_down_free[i].cap < g_down_free[k].cap) k = i;
+      if (total > kDownKeepBytes && g_down_free.size() <= kDownKeep) {  // over the byte budget: the largest goes instead
+        for (size_t i = 0; i < g_down_free.size(); ++i)
+          if (g_down_free[i].cap > g_down_free[k].cap) k = i;
+      }
+      drop = g_down_free[k];
+      g_down_free.erase(g_down_free.begin() + k);
+    }
+  }
+  if (drop.p) cudaFreeHost(drop.p);
 }
 
 ProfScope::ProfScope(tfs_ctx* c, int kernel_id) : ctx(c), id(kernel_id) {
@@ -140,6 +191,7 @@ tfs_status_t tfs_ctx_create(int32_t device, uint64_t pinned_bytes, tfs_ctx_t** o
   }
   tfs_ctx* ctx = new tfs_ctx();
   ctx->device = device;
+  ctx->trace = std::getenv("TFS_TRACE") != nullptr;
   if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking)) != cudaSuccess) {
     std::fprintf(stderr, "tfs_ctx_create: %s\n", cudaGetErrorString(e));
     delete ctx;
@@ -178,6 +230,7 @@ tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx) {
   if (ctx->d_ctrl) cudaFree(ctx->d_ctrl);
   if (ctx->h_up) cudaFreeHost(ctx->h_up);
   if (ctx->h_down) cudaFreeHost(ctx->h_down);
+  if (ctx->h_rec) cudaFreeHost(ctx->h_rec);
   if (ctx->h_slab) cudaFreeHost(ctx->h_slab);
   for (auto& e : ctx->pool_extra) cudaFreeHost(e.first);
   if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);

@@ -22,10 +22,13 @@ struct tfs_decoded {
   tfs_ctx* owner = nullptr;
   tfs::DecTables T{};
   uint64_t totals[24] = {0};
-  std::vector<tfs_msg_out_t> msgs;
-  std::vector<tfs_tensor_out_t> tensors;
-  std::vector<tfs_span_t> filters;
-  std::vector<uint8_t> strings;
+  // the result tables, in place in the pinned block they were copied into (owned by the handle, recycled on free)
+  tfs::PinnedBlock down;
+  const tfs_msg_out_t* msgs = nullptr;
+  const tfs_tensor_out_t* tensors = nullptr;
+  const tfs_span_t* filters = nullptr;
+  const uint8_t* strings = nullptr;
+  uint64_t n_msgs = 0, n_tensors = 0, n_filters = 0, n_strings = 0;
   uint32_t n_failed = 0;
   bool host_staged = false;  // wire was staged by tfs_decode_host
   uint64_t stage_generation = 0;
@@ -1502,11 +1505,24 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   if (!dec) return TFS_ERR_NOMEM;
   dec->owner = ctx;
   dec->generation = ++ctx->dec_generation;
+  HostTrace tr(ctx, "decode");
   DecTables& T = dec->T;
   std::memset(&T, 0, sizeof(T));
   auto bail = [&](tfs_status_t st) {
+    if (dec->down.p) cudaStreamSynchronize(ctx->stream);  // copies into the block may still be queued
+    down_release(dec->down);
     delete dec;
     return st;
+  };
+  // the handle's pinned result block: at least `bytes` (a block that has to grow loses its contents)
+  auto need_down = [&](size_t bytes) -> tfs_status_t {
+    if (dec->down.cap >= bytes) return TFS_OK;
+    if (dec->down.p) {
+      TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+      down_release(dec->down);
+      dec->down = PinnedBlock{};
+    }
+    return down_acquire(ctx, bytes, &dec->down);
   };
 #define DEC_TRY(expr)                         \
   do {                                        \
@@ -1636,8 +1652,8 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       ctx->launches++;
       DEC_CUDA(cudaGetLastError());
       const size_t guess = static_cast<size_t>(std::min<uint64_t>(blob_cap, std::max<uint64_t>(ctx->dec_hint_blob, 4096 + 512ull * n_msgs)));
-      DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, h2 + guess + 64));
-      uint8_t* hd = static_cast<uint8_t*>(ctx->h_down);
+      DEC_TRY(need_down(h2 + guess + 64));
+      uint8_t* hd = static_cast<uint8_t*>(dec->down.p);
       DEC_CUDA(cudaMemcpyAsync(hd + h1, d1 + o_tot, res1_bytes, cudaMemcpyDeviceToHost, ctx->stream));
       DEC_CUDA(cudaMemcpyAsync(hd + h2, d2 + p_blob, guess, cudaMemcpyDeviceToHost, ctx->stream));
       DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1 (the only one when the batch has no varint bodies)
@@ -1690,10 +1706,12 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
     k_scan_counts<<<1, 1024, 0, ctx->stream>>>(T);
     ctx->launches++;
     DEC_CUDA(cudaGetLastError());
-    DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, kTotalsBytes));
-    DEC_CUDA(cudaMemcpyAsync(ctx->h_down, T.totals, kTotalsBytes, cudaMemcpyDeviceToHost, ctx->stream));
+    DEC_TRY(need_down(kTotalsBytes));
+    DEC_CUDA(cudaMemcpyAsync(dec->down.p, T.totals, kTotalsBytes, cudaMemcpyDeviceToHost, ctx->stream));
+    tr.mark("setup");
     DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #1: the sizes of the pass-2 tables
-    load_totals(static_cast<const uint8_t*>(ctx->h_down));
+    tr.mark("sync1");
+    load_totals(static_cast<const uint8_t*>(dec->down.p));
     if (n_tensors > 0xFFFFFFF0ull || n_spans > 0xFFFFFFF0ull || n_vt > 0xFFFFFFF0ull || n_str > 0xFFFFFFF0ull || dec->totals[TOT_CTILES] > 0xFFFFFFF0ull)
       return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large (32-bit table offsets)"));
     // ---- pass 2 tables; tensors | filters | strings are contiguous: one D2H
@@ -1787,22 +1805,26 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   }
 
   // ---- results to the host: (totals | msgs) and the blob (tensors | filters | strings)
-  DEC_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, h2 + res2_bytes + 64));
-  uint8_t* hd = static_cast<uint8_t*>(ctx->h_down);
-  if (!planned || blob_copied < res2_bytes) {
-    if (!planned) DEC_CUDA(cudaMemcpyAsync(hd + h1, d1 + o_tot, res1_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  tr.mark("launch");
+  // (a block that had to grow starts empty: what the plan path already fetched is fetched again)
+  const bool regrown = dec->down.cap < h2 + res2_bytes + 64;
+  DEC_TRY(need_down(h2 + res2_bytes + 64));
+  uint8_t* hd = static_cast<uint8_t*>(dec->down.p);
+  if (!planned || regrown || blob_copied < res2_bytes) {
+    if (!planned || regrown) DEC_CUDA(cudaMemcpyAsync(hd + h1, d1 + o_tot, res1_bytes, cudaMemcpyDeviceToHost, ctx->stream));
     if (res2_bytes) DEC_CUDA(cudaMemcpyAsync(hd + h2, T.tensors, res2_bytes, cudaMemcpyDeviceToHost, ctx->stream));
     DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #2: the caller needs the element counts (and, one-call, the values)
     std::memcpy(dec->totals, hd + h1, kTotalsBytes);
   }
-  dec->msgs.resize(n_msgs);
-  dec->tensors.resize(n_tensors);
-  dec->filters.resize(n_filters);
-  dec->strings.resize(n_str);
-  if (n_msgs) std::memcpy(dec->msgs.data(), hd + h1 + (o_msgs - o_tot), sizeof(tfs_msg_out_t) * static_cast<size_t>(n_msgs));
-  if (n_tensors) std::memcpy(dec->tensors.data(), hd + h2, sizeof(tfs_tensor_out_t) * n_tensors);
-  if (n_filters) std::memcpy(dec->filters.data(), hd + h2 + p_flt, sizeof(tfs_span_t) * n_filters);
-  if (n_str) std::memcpy(dec->strings.data(), hd + h2 + p_str, n_str);
+  tr.mark("sync2");
+  dec->msgs = reinterpret_cast<const tfs_msg_out_t*>(hd + h1 + (o_msgs - o_tot));
+  dec->tensors = reinterpret_cast<const tfs_tensor_out_t*>(hd + h2);
+  dec->filters = reinterpret_cast<const tfs_span_t*>(hd + h2 + p_flt);
+  dec->strings = hd + h2 + p_str;
+  dec->n_msgs = n_msgs;
+  dec->n_tensors = n_tensors;
+  dec->n_filters = n_filters;
+  dec->n_strings = n_str;
   dec->n_failed = static_cast<uint32_t>(dec->totals[TOT_FAILED]);
   ctx->err_has_location = false;
   if (dec->n_failed) {  // the first failed message, for tfs_last_error_detail / tfs_last_error_location
@@ -1816,6 +1838,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       break;
     }
   }
+  tr.mark("copyout");
   *out = dec;
 #undef DEC_TRY
 #undef DEC_CUDA
@@ -1865,15 +1888,15 @@ tfs_status_t tfs_decode_into(tfs_ctx_t* ctx, const void* wire_dev, uint64_t wire
 
 tfs_status_t tfs_decoded_view(const tfs_decoded_t* dec, tfs_decoded_view_t* view) {
   if (!dec || !view) return TFS_ERR_INVALID_ARG;
-  view->msgs = dec->msgs.data();
-  view->tensors = dec->tensors.data();
-  view->filters = dec->filters.data();
-  view->strings = dec->strings.data();
-  view->strings_bytes = dec->strings.size();
+  view->msgs = dec->msgs;
+  view->tensors = dec->tensors;
+  view->filters = dec->filters;
+  view->strings = dec->strings;
+  view->strings_bytes = dec->n_strings;
   view->pool_bytes = dec->totals[TOT_POOL];
-  view->n_msgs = static_cast<uint32_t>(dec->msgs.size());
-  view->n_tensors = static_cast<uint32_t>(dec->tensors.size());
-  view->n_filters = static_cast<uint32_t>(dec->filters.size());
+  view->n_msgs = static_cast<uint32_t>(dec->n_msgs);
+  view->n_tensors = static_cast<uint32_t>(dec->n_tensors);
+  view->n_filters = static_cast<uint32_t>(dec->n_filters);
   view->n_failed = dec->n_failed;
   return TFS_OK;
 }
@@ -1887,6 +1910,7 @@ tfs_status_t tfs_decode(tfs_ctx_t* ctx, tfs_decoded_t* dec, void* pool_dev, uint
 
 tfs_status_t tfs_decoded_free(tfs_ctx_t* ctx, tfs_decoded_t* dec) {
   (void)ctx;
+  if (dec) down_release(dec->down);  // (the copies into it were waited for before the handle was handed out)
   delete dec;
   return TFS_OK;
 }

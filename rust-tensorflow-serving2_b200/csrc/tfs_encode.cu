@@ -9,7 +9,9 @@
 //                                  K5 k_copy (tfs_copy.cu)          (float/double/complex/bool/tensor_content)
 // Nothing here is a contraction: integer / byte work bound by HBM bandwidth, no tensor cores.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
 
 #include "tfs_device.cuh"
 #include "tfs_ragged.cuh"
@@ -545,15 +547,39 @@ __global__ void __launch_bounds__(kFrameWarps * 32) k_frame_small(EncTables T, u
 // =====================================================================================================
 // host: validate + compile the descriptors into one upload blob
 // =====================================================================================================
+// Host table that keeps its storage between batches (no allocation, no page faults on the request path); `n` entries valid.
+template <class T>
+struct GrowArray {
+  using value_type = T;
+  std::vector<T> store;
+  size_t n = 0;
+  void set_size(size_t k) {
+    if (store.size() < k) store.resize(k);
+    n = k;
+  }
+  size_t size() const { return n; }
+  T* data() { return store.data(); }
+  const T* data() const { return store.data(); }
+  T& operator[](size_t i) { return store[i]; }
+  const T& operator[](size_t i) const { return store[i]; }
+  const T& back() const { return store[n - 1]; }
+};
+
 struct Compiled {
-  std::vector<EncMsg> msgs;
-  std::vector<EncTensor> tensors;
-  std::vector<EncField> fields;
-  std::vector<StrRef> filters;
+  // the records sit in ONE block, msgs | tensors | fields (16-byte aligned each): the context's pinned record block when
+  // the batch is going to be encoded (uploaded from where it was compiled), `own` when only the bound is wanted
+  EncMsg* msgs = nullptr;
+  EncTensor* tensors = nullptr;
+  EncField* fields = nullptr;
+  size_t n_msgs = 0, n_tensors = 0, n_fields = 0, rec_bytes = 0;
+  std::vector<uint64_t> own;
+  GrowArray<StrRef> filters;
   std::vector<uint8_t> strings;
-  std::vector<uint32_t> vfield_first_tile, vfield_index;
-  std::vector<uint32_t> rfield_first_tile, rfield_first_out, rfield_index;
-  std::vector<CopySeg> segs;
+  GrowArray<uint32_t> vfield_first_tile, vfield_index;                    // (n + 1) tile prefixes / field index per varint field
+  GrowArray<uint32_t> rfield_first_tile, rfield_first_out, rfield_index;  // the same for ragged fields (+ output tiles)
+  GrowArray<CopySeg> segs;
+  GrowArray<uint64_t> field_bound;          // scratch of compile_batch: upper bound of every field's body
+  GrowArray<uint8_t> tensor_used, field_used;
   uint64_t n_copy_tiles = 0;
   uint64_t bound = 0;  // upper bound of the encoded bytes
   // true when the host can already tell that every bulk segment will be congruent mod 16 with its destination
@@ -562,11 +588,18 @@ struct Compiled {
   bool any_bulk = false;   // some copy segment is >= 4 KiB of plain bytes (a candidate for the TMA ring)
   int cast_kind = 0;       // staged cast kernel needed: 1 = widening segments only, 2 = narrowing ones too (launch_copy)
   bool has_input = false;  // some message is an Input / ClassificationRequest: features are framed by their own kernels
+  void reset() {  // a new batch in the same storage
+    strings.clear();
+    n_copy_tiles = bound = 0;
+    all_tma = true;
+    any_bulk = has_input = false;
+    cast_kind = 0;
+  }
 };
 
-StrRef add_str(Compiled& c, const tfs_str_t& s) {
-  StrRef r{static_cast<uint32_t>(c.strings.size()), s.len};
-  if (s.len) c.strings.insert(c.strings.end(), reinterpret_cast<const uint8_t*>(s.ptr), reinterpret_cast<const uint8_t*>(s.ptr) + s.len);
+StrRef add_str(std::vector<uint8_t>& strings, const tfs_str_t& s) {
+  StrRef r{static_cast<uint32_t>(strings.size()), s.len};
+  if (s.len) strings.insert(strings.end(), reinterpret_cast<const uint8_t*>(s.ptr), reinterpret_cast<const uint8_t*>(s.ptr) + s.len);
   return r;
 }
 
@@ -667,33 +700,39 @@ bool compile_field(const tfs_field_desc_t& f, EncField* o, uint64_t* max_body) {
   }
 }
 
-tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, Compiled* c) {
-  if (!b) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch is null");
-  if ((b->n_msgs && !b->msgs) || (b->n_tensors && !b->tensors) || (b->n_fields && !b->fields) || (b->n_filters && !b->filters))
-    return set_err(ctx, TFS_ERR_INVALID_ARG, "batch array pointer is null");
-  c->msgs.resize(b->n_msgs);
-  c->tensors.resize(b->n_tensors);
-  c->fields.resize(b->n_fields);
-  c->filters.resize(b->n_filters);
-  std::vector<uint64_t> field_bound(b->n_fields, 0);
-  std::vector<uint8_t> tensor_used(b->n_tensors, 0), field_used(b->n_fields, 0);
-  c->strings.reserve(64ull * b->n_msgs + 16ull * b->n_tensors + 16ull * b->n_filters);
-  for (uint32_t i = 0; i < b->n_filters; ++i) c->filters[i] = add_str(*c, b->filters[i]);
-  uint32_t vtiles = 0;
+// What compiling a range of messages yields besides the records themselves (which land at the descriptors' own indices).
+struct alignas(128) RangeOut {  // (one per worker, side by side in a vector: own cache lines)
+  const char* fail = nullptr;  // first descriptor error of the range (TFS_ERR_INVALID_ARG)
+  uint64_t bound = 0;
+  bool has_input = false;
+  std::vector<uint8_t> strings;  // a worker's strings; StrRef offsets are relative to it until the ranges are joined
+};
+
+// Messages [m0, m1) -> c->msgs / tensors / fields.  `strings` receives their names (offsets relative to its start).
+// Ranges of one batch run on several threads: every record index belongs to one message, the used-marks are atomic.
+void compile_range(const tfs_batch_t* b, uint32_t flags, Compiled* c, uint32_t m0, uint32_t m1, std::vector<uint8_t>& strings,
+                   uint64_t* field_bound, uint8_t* tensor_used, uint8_t* field_used, RangeOut* r) {
+#define RANGE_FAIL(msg) \
+  do {                  \
+    r->fail = (msg);    \
+    return;             \
+  } while (0)
   const uint32_t prefix = (flags & TFS_F_GRPC_PREFIX) ? 5u : 0u;
-  for (uint32_t mi = 0; mi < b->n_msgs; ++mi) {
+  uint64_t bound_sum = 0;
+  bool any_input = false;
+  for (uint32_t mi = m0; mi < m1; ++mi) {
     const tfs_msg_desc_t& m = b->msgs[mi];
     EncMsg& o = c->msgs[mi];
     std::memset(&o, 0, sizeof(o));
-    if (m.kind < TFS_MSG_TENSOR_PROTO || m.kind > TFS_MSG_CLASSIFY_REQUEST) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad message kind");
+    if (m.kind < TFS_MSG_TENSOR_PROTO || m.kind > TFS_MSG_CLASSIFY_REQUEST) RANGE_FAIL("bad message kind");
     const bool input_kind = m.kind == TFS_MSG_INPUT || m.kind == TFS_MSG_CLASSIFY_REQUEST;  // n_filters counts Examples there
-    if (static_cast<uint64_t>(m.first_tensor) + m.n_tensors > b->n_tensors) return set_err(ctx, TFS_ERR_INVALID_ARG, "tensor range out of bounds");
-    if (!input_kind && static_cast<uint64_t>(m.first_filter) + m.n_filters > b->n_filters) return set_err(ctx, TFS_ERR_INVALID_ARG, "filter range out of bounds");
-    if (m.kind == TFS_MSG_INPUT && m.has_model_spec) return set_err(ctx, TFS_ERR_INVALID_ARG, "Input has no model_spec");
-    if (m.version_choice < TFS_VERSION_NONE || m.version_choice > TFS_VERSION_LABEL) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad version_choice");
+    if (static_cast<uint64_t>(m.first_tensor) + m.n_tensors > b->n_tensors) RANGE_FAIL("tensor range out of bounds");
+    if (!input_kind && static_cast<uint64_t>(m.first_filter) + m.n_filters > b->n_filters) RANGE_FAIL("filter range out of bounds");
+    if (m.kind == TFS_MSG_INPUT && m.has_model_spec) RANGE_FAIL("Input has no model_spec");
+    if (m.version_choice < TFS_VERSION_NONE || m.version_choice > TFS_VERSION_LABEL) RANGE_FAIL("bad version_choice");
     if (m.kind == TFS_MSG_TENSOR_PROTO && (m.n_tensors != 1 || m.has_model_spec || m.n_filters))
-      return set_err(ctx, TFS_ERR_INVALID_ARG, "a bare TensorProto message has exactly one tensor and nothing else");
-    if (m.kind == TFS_MSG_PREDICT_RESPONSE && m.n_filters) return set_err(ctx, TFS_ERR_INVALID_ARG, "PredictResponse has no output_filter");
+      RANGE_FAIL("a bare TensorProto message has exactly one tensor and nothing else");
+    if (m.kind == TFS_MSG_PREDICT_RESPONSE && m.n_filters) RANGE_FAIL("PredictResponse has no output_filter");
     o.kind = m.kind;
     o.has_model_spec = m.has_model_spec ? 1 : 0;
     o.version_choice = m.version_choice;
@@ -705,30 +744,30 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
     uint64_t bound = 64 + prefix + (input_kind ? 24ull * m.n_filters : 0);
     int32_t last_example = 0;
     if (m.has_model_spec) {
-      o.model_name = add_str(*c, m.model_name);
-      o.signature_name = add_str(*c, m.signature_name);
-      if (m.version_choice == TFS_VERSION_LABEL) o.version_label = add_str(*c, m.version_label);
+      o.model_name = add_str(strings, m.model_name);
+      o.signature_name = add_str(strings, m.signature_name);
+      if (m.version_choice == TFS_VERSION_LABEL) o.version_label = add_str(strings, m.version_label);
       bound += m.model_name.len + m.signature_name.len + m.version_label.len + 48;
     }
     for (uint32_t i = 0; i < m.n_filters && !input_kind; ++i) bound += b->filters[m.first_filter + i].len + 8;
     for (uint32_t i = 0; i < m.n_tensors; ++i) {
       const uint32_t ti = m.first_tensor + i;
-      if (tensor_used[ti]++) return set_err(ctx, TFS_ERR_INVALID_ARG, "a tensor descriptor is referenced twice");
+      if (__atomic_fetch_add(&tensor_used[ti], 1, __ATOMIC_RELAXED)) RANGE_FAIL("a tensor descriptor is referenced twice");
       const tfs_tensor_desc_t& t = b->tensors[ti];
       EncTensor& ot = c->tensors[ti];
       std::memset(&ot, 0, sizeof(ot));
-      if (t.n_dims > TFS_MAX_DIMS) return set_err(ctx, TFS_ERR_INVALID_ARG, "rank exceeds TFS_MAX_DIMS");
-      if (!t.has_shape && (t.n_dims || t.unknown_rank)) return set_err(ctx, TFS_ERR_INVALID_ARG, "dims without has_shape");
-      if (static_cast<uint64_t>(t.first_field) + t.n_fields > b->n_fields) return set_err(ctx, TFS_ERR_INVALID_ARG, "field range out of bounds");
+      if (t.n_dims > TFS_MAX_DIMS) RANGE_FAIL("rank exceeds TFS_MAX_DIMS");
+      if (!t.has_shape && (t.n_dims || t.unknown_rank)) RANGE_FAIL("dims without has_shape");
+      if (static_cast<uint64_t>(t.first_field) + t.n_fields > b->n_fields) RANGE_FAIL("field range out of bounds");
       if (input_kind) {  // a Feature: no dtype / shape, at most one list, Example index ascending
-        if (t.dtype || t.has_shape || t.n_fields > 1) return set_err(ctx, TFS_ERR_INVALID_ARG, "a feature has no dtype / shape and at most one list");
+        if (t.dtype || t.has_shape || t.n_fields > 1) RANGE_FAIL("a feature has no dtype / shape and at most one list");
         if (t.version_number < last_example || static_cast<uint32_t>(t.version_number) >= m.n_filters)
-          return set_err(ctx, TFS_ERR_INVALID_ARG, "feature: Example index not ascending or out of range");
+          RANGE_FAIL("feature: Example index not ascending or out of range");
         last_example = t.version_number;
       }
-      ot.name = m.kind == TFS_MSG_TENSOR_PROTO ? StrRef{0, 0} : add_str(*c, t.name);
+      ot.name = m.kind == TFS_MSG_TENSOR_PROTO ? StrRef{0, 0} : add_str(strings, t.name);
       ot._pad = mi;  // the message this descriptor belongs to
-      c->has_input |= input_kind;
+      any_input |= input_kind;
       ot.dtype = t.dtype;
       ot.version_number = t.version_number;
       ot.has_shape = t.has_shape ? 1 : 0;
@@ -741,78 +780,245 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
       uint32_t seen = 0;
       for (uint32_t k = 0; k < t.n_fields; ++k) {
         const uint32_t fi = t.first_field + k;
-        if (field_used[fi]++) return set_err(ctx, TFS_ERR_INVALID_ARG, "a field descriptor is referenced twice");
+        if (__atomic_fetch_add(&field_used[fi], 1, __ATOMIC_RELAXED)) RANGE_FAIL("a field descriptor is referenced twice");
         const int32_t fk = b->fields[fi].kind;
         if (input_kind != (fk >= TFS_KIND_BYTES_LIST && fk <= TFS_KIND_INT64_LIST))
-          return set_err(ctx, TFS_ERR_INVALID_ARG, "list kinds belong to features, *_val kinds to tensors");
+          RANGE_FAIL("list kinds belong to features, *_val kinds to tensors");
         const int32_t slot = input_kind ? 0 : tfs_slot_of_kind(fk);
         // a kind may come more than once in a TENSOR: the arrays are concatenated in descriptor order (batch assembly)
-        if (slot < 0 || (input_kind && ((seen >> slot) & 1u))) return set_err(ctx, TFS_ERR_INVALID_ARG, "unknown payload kind, or two lists in one feature");
+        if (slot < 0 || (input_kind && ((seen >> slot) & 1u))) RANGE_FAIL("unknown payload kind, or two lists in one feature");
         seen |= 1u << slot;
-        if (!compile_field(b->fields[fi], &c->fields[fi], &field_bound[fi]))
-          return set_err(ctx, TFS_ERR_INVALID_ARG, "payload field: conversion not allowed by the ABI");
+        if (!compile_field(b->fields[fi], &c->fields[fi], &field_bound[fi])) RANGE_FAIL("payload field: conversion not allowed by the ABI");
         bound += field_bound[fi] + 16;
       }
       // prost emits in ascending field number: order this tensor's fields by kind
       if (t.n_fields > 1)  // (std::stable_sort allocates a scratch buffer even for one element)
-        std::stable_sort(c->fields.begin() + t.first_field, c->fields.begin() + t.first_field + t.n_fields,
+        std::stable_sort(c->fields + t.first_field, c->fields + t.first_field + t.n_fields,
                          [](const EncField& x, const EncField& y) { return x.kind < y.kind; });
     }
-    c->bound += (flags & TFS_F_ALIGN_PAYLOAD) ? align_up(bound + 16, 16) : bound;
+    bound_sum += (flags & TFS_F_ALIGN_PAYLOAD) ? align_up(bound + 16, 16) : bound;
   }
-  // tile tables
-  uint64_t rtiles = 0, routs = 0;
-  for (uint32_t fi = 0; fi < b->n_fields; ++fi) {
-    EncField& f = c->fields[fi];
-    if (!field_used[fi] || f.n_elems == 0) {
-      f.n_elems = field_used[fi] ? f.n_elems : 0;
-      f.n_tiles = 0;
-      continue;
+  r->bound = bound_sum;
+  r->has_input = any_input;
+#undef RANGE_FAIL
+}
+
+// a batch of tiny messages is host work: above this many messages the descriptors are compiled on
+// several threads
+constexpr uint32_t kParallelCompileMsgs = 8192;
+constexpr uint32_t kCompileThreadsMax = 8;
+
+tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, Compiled* c, bool pinned_records = false) {
+  if (!b) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch is null");
+  if ((b->n_msgs && !b->msgs) || (b->n_tensors && !b->tensors) || (b->n_fields && !b->fields) || (b->n_filters && !b->filters))
+    return set_err(ctx, TFS_ERR_INVALID_ARG, "batch array pointer is null");
+  HostTrace tr(ctx, "  compile");
+  c->n_msgs = b->n_msgs;
+  c->n_tensors = b->n_tensors;
+  c->n_fields = b->n_fields;
+  const size_t o_t = align_up(sizeof(EncMsg) * c->n_msgs, 16), o_f = align_up(o_t + sizeof(EncTensor) * c->n_tensors, 16);
+  c->rec_bytes = align_up(o_f + sizeof(EncField) * c->n_fields, 16);
+  uint8_t* rec = nullptr;
+  if (pinned_records) {  // no allocation, no page faults, and no copy before the upload (a batch of 10^6 requests: 300 MB)
+    TFS_TRY(pinned_reserve(ctx, &ctx->h_rec, &ctx->h_rec_cap, c->rec_bytes + 16));
+    rec = static_cast<uint8_t*>(ctx->h_rec);
+  } else {
+    c->own.resize(c->rec_bytes / 8 + 2);
+    rec = reinterpret_cast<uint8_t*>(c->own.data());
+  }
+  c->msgs = reinterpret_cast<EncMsg*>(rec);
+  c->tensors = reinterpret_cast<EncTensor*>(rec + o_t);
+  c->fields = reinterpret_cast<EncField*>(rec + o_f);
+  c->reset();
+  c->filters.set_size(b->n_filters);
+  c->field_bound.set_size(b->n_fields);
+  c->tensor_used.set_size(b->n_tensors);
+  c->field_used.set_size(b->n_fields);
+  uint64_t* const field_bound = c->field_bound.data();
+  uint8_t* const tensor_used = c->tensor_used.data();
+  uint8_t* const field_used = c->field_used.data();
+  if (b->n_fields) std::memset(field_bound, 0, 8ull * b->n_fields);
+  if (b->n_fields) std::memset(field_used, 0, b->n_fields);
+  if (b->n_tensors) std::memset(tensor_used, 0, b->n_tensors);
+  for (uint32_t i = 0; i < b->n_filters; ++i) c->filters[i] = add_str(c->strings, b->filters[i]);
+  uint32_t n_workers = 1;
+  tr.mark("alloc");
+  if (b->n_msgs >= kParallelCompileMsgs)
+    n_workers = std::min<uint32_t>({kCompileThreadsMax, std::max(1u, std::thread::hardware_concurrency() / 2), b->n_msgs / (kParallelCompileMsgs / 2)});
+  if (const char* e = std::getenv("TFS_COMPILE_THREADS")) n_workers = std::max(1, std::atoi(e));
+  if (n_workers <= 1) {
+    c->strings.reserve(c->strings.size() + 64ull * b->n_msgs + 16ull * b->n_tensors);
+    RangeOut r;
+    compile_range(b, flags, c, 0, b->n_msgs, c->strings, field_bound, tensor_used, field_used, &r);
+    if (r.fail) return set_err(ctx, TFS_ERR_INVALID_ARG, r.fail);
+    c->bound = r.bound;
+    c->has_input = r.has_input;
+  } else {
+    std::vector<RangeOut> outs(n_workers);
+    std::vector<std::thread> crew;
+    auto first_of = [&](uint32_t k) { return static_cast<uint32_t>(static_cast<uint64_t>(b->n_msgs) * k / n_workers); };
+    for (uint32_t k = 0; k < n_workers; ++k)
+      crew.emplace_back([&, k] {
+        outs[k].strings.reserve(64ull * (first_of(k + 1) - first_of(k)));
+        compile_range(b, flags, c, first_of(k), first_of(k + 1), outs[k].strings, field_bound, tensor_used, field_used, &outs[k]);
+      });
+    for (std::thread& t : crew) t.join();
+    for (uint32_t k = 0; k < n_workers; ++k)  // the error of the earliest message, as the one-thread walk reports it
+      if (outs[k].fail) return set_err(ctx, TFS_ERR_INVALID_ARG, outs[k].fail);
+    // join the string blocks and move every name reference of a range by where its block landed
+    std::vector<uint32_t> base(n_workers);
+    uint64_t total = c->strings.size();
+    for (uint32_t k = 0; k < n_workers; ++k) {
+      base[k] = static_cast<uint32_t>(total);
+      total += outs[k].strings.size();
+      c->bound += outs[k].bound;
+      c->has_input |= outs[k].has_input;
     }
-    if (f.is_varint == FC_RAGGED) {
-      const uint64_t nt = (f.n_elems + kRagTile - 1) / kRagTile, no = (field_bound[fi] + kRagOutTile - 1) / kRagOutTile;
-      if (rtiles + nt > 0x7FFFFFFFull || routs + no > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (string_val tiles)");
-      f.first_tile = static_cast<uint32_t>(rtiles);
-      f.n_tiles = static_cast<uint32_t>(nt);
-      c->rfield_first_tile.push_back(static_cast<uint32_t>(rtiles));
-      c->rfield_first_out.push_back(static_cast<uint32_t>(routs));
-      c->rfield_index.push_back(fi);
-      rtiles += nt;
-      routs += no;
-    } else if (f.is_varint) {
-      uint64_t nt = (f.n_elems + kVarintTile - 1) / kVarintTile;
-      if (vtiles + nt > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (varint tiles)");
-      f.first_tile = vtiles;
-      f.n_tiles = static_cast<uint32_t>(nt);
-      c->vfield_first_tile.push_back(vtiles);
-      c->vfield_index.push_back(fi);
-      vtiles += static_cast<uint32_t>(nt);
-    } else {
-      CopySeg s;
-      s.src = static_cast<const uint8_t*>(f.src);
-      s.dst = nullptr;
-      s.op = f.mode;
-      s.param = f.op_param;
-      const uint32_t osz = (f.mode == CP_BYTES || f.mode == CP_BOOL) ? 1u : (f.mode == CP_F32_F16 || f.mode == CP_F32_BF16) ? 2u : 4u;
-      s.n = f.body_len / osz;
-      s.first_tile = c->n_copy_tiles;
-      f.first_tile = static_cast<uint32_t>(c->segs.size());
-      f.n_tiles = 0;
-      // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
-      c->n_copy_tiles += (f.body_len + kCopyTileBytes - 1) / kCopyTileBytes + 1;
-      c->any_bulk |= f.mode == CP_BYTES && f.body_len >= 4096;
-      if (f.mode >= CP_U8_F32 && s.n >= 1024)  // (the kernel re-checks size and source alignment per segment)
-        c->cast_kind = std::max(c->cast_kind, (f.mode == CP_F32_F16 || f.mode == CP_F32_BF16) ? 2 : 1);
-      c->segs.push_back(s);
+    if (total > 0xFFFFFFF0ull) return set_err(ctx, TFS_ERR_TOO_LARGE, "names of the batch exceed 4 GiB");
+    c->strings.resize(total);
+    crew.clear();
+    for (uint32_t k = 0; k < n_workers; ++k)
+      crew.emplace_back([&, k] {
+        if (!outs[k].strings.empty()) std::memcpy(c->strings.data() + base[k], outs[k].strings.data(), outs[k].strings.size());
+        const uint32_t d = base[k];
+        for (uint32_t mi = first_of(k); mi < first_of(k + 1); ++mi) {
+          EncMsg& o = c->msgs[mi];
+          if (o.model_name.len) o.model_name.off += d;
+          if (o.signature_name.len) o.signature_name.off += d;
+          if (o.version_label.len) o.version_label.off += d;
+          for (uint32_t ti = o.first_tensor; ti < o.first_tensor + o.n_tensors; ++ti)
+            if (c->tensors[ti].name.len) c->tensors[ti].name.off += d;
+        }
+      });
+    for (std::thread& t : crew) t.join();
+  }
+  // descriptors no message refers to: the block is reused, give them a defined (empty) record
+  for (uint32_t ti = 0; ti < b->n_tensors; ++ti)
+    if (!tensor_used[ti]) std::memset(&c->tensors[ti], 0, sizeof(EncTensor));
+  for (uint32_t fi = 0; fi < b->n_fields; ++fi)
+    if (!field_used[fi]) std::memset(&c->fields[fi], 0, sizeof(EncField));
+  tr.mark("records");
+  // tile tables: every varint / ragged field gets a run of tiles, every copy-class field a segment; positions are running
+  // sums in field order.  Large batches: the sums of equal ranges of fields first (on several threads), then the fill.
+  struct TileSums {
+    uint64_t vt = 0, rt = 0, ro = 0, ct = 0;  // varint tiles, ragged tiles, ragged output tiles, copy tiles
+    uint64_t nseg = 0, nvf = 0, nrf = 0;      // copy segments, varint fields, ragged fields
+    bool any_bulk = false;
+    int cast_kind = 0;
+  };
+  // fields [f0, f1) starting at the sums `at`; FILL = false only counts.  Returns the sums at f1.
+  auto tile_range_pass = [&](uint32_t f0, uint32_t f1, TileSums at, bool fill) -> TileSums {
+    for (uint32_t fi = f0; fi < f1; ++fi) {
+      EncField& f = c->fields[fi];
+      if (!field_used[fi] || f.n_elems == 0) {
+        if (fill) {
+          f.n_elems = field_used[fi] ? f.n_elems : 0;
+          f.n_tiles = 0;
+        }
+        continue;
+      }
+      if (f.is_varint == FC_RAGGED) {
+        const uint64_t nt = (f.n_elems + kRagTile - 1) / kRagTile, no = (field_bound[fi] + kRagOutTile - 1) / kRagOutTile;
+        if (fill) {
+          f.first_tile = static_cast<uint32_t>(at.rt);
+          f.n_tiles = static_cast<uint32_t>(nt);
+          c->rfield_first_tile[at.nrf] = static_cast<uint32_t>(at.rt);
+          c->rfield_first_out[at.nrf] = static_cast<uint32_t>(at.ro);
+          c->rfield_index[at.nrf] = fi;
+        }
+        ++at.nrf;
+        at.rt += nt;
+        at.ro += no;
+      } else if (f.is_varint) {
+        const uint64_t nt = (f.n_elems + kVarintTile - 1) / kVarintTile;
+        if (fill) {
+          f.first_tile = static_cast<uint32_t>(at.vt);
+          f.n_tiles = static_cast<uint32_t>(nt);
+          c->vfield_first_tile[at.nvf] = static_cast<uint32_t>(at.vt);
+          c->vfield_index[at.nvf] = fi;
+        }
+        ++at.nvf;
+        at.vt += nt;
+      } else {
+        const uint32_t osz = (f.mode == CP_BYTES || f.mode == CP_BOOL) ? 1u : (f.mode == CP_F32_F16 || f.mode == CP_F32_BF16) ? 2u : 4u;
+        const uint64_t n = f.body_len / osz;
+        if (fill) {
+          CopySeg s;
+          s.src = static_cast<const uint8_t*>(f.src);
+          s.dst = nullptr;
+          s.op = f.mode;
+          s.param = f.op_param;
+          s.n = n;
+          s.first_tile = at.ct;
+          f.first_tile = static_cast<uint32_t>(at.nseg);
+          f.n_tiles = 0;
+          c->segs[at.nseg] = s;
+        }
+        ++at.nseg;
+        // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
+        at.ct += (f.body_len + kCopyTileBytes - 1) / kCopyTileBytes + 1;
+        at.any_bulk |= f.mode == CP_BYTES && f.body_len >= 4096;
+        if (f.mode >= CP_U8_F32 && n >= 1024)  // (the kernel re-checks size and source alignment per segment)
+          at.cast_kind = std::max(at.cast_kind, (f.mode == CP_F32_F16 || f.mode == CP_F32_BF16) ? 2 : 1);
+      }
+    }
+    return at;
+  };
+  const uint32_t tile_workers = b->n_fields >= 8 * kParallelCompileMsgs ? n_workers : 1;
+  auto field_first = [&](uint32_t k) { return static_cast<uint32_t>(static_cast<uint64_t>(b->n_fields) * k / tile_workers); };
+  std::vector<TileSums> at(tile_workers + 1);
+  if (tile_workers > 1) {
+    std::vector<TileSums> part(tile_workers);
+    std::vector<std::thread> crew;
+    for (uint32_t k = 0; k < tile_workers; ++k)
+      crew.emplace_back([&, k] { part[k] = tile_range_pass(field_first(k), field_first(k + 1), TileSums{}, false); });
+    for (std::thread& t : crew) t.join();
+    for (uint32_t k = 0; k < tile_workers; ++k) {
+      TileSums& n = at[k + 1];
+      n = at[k];
+      n.vt += part[k].vt, n.rt += part[k].rt, n.ro += part[k].ro, n.ct += part[k].ct;
+      n.nseg += part[k].nseg, n.nvf += part[k].nvf, n.nrf += part[k].nrf;
+      n.any_bulk |= part[k].any_bulk;
+      n.cast_kind = std::max(n.cast_kind, part[k].cast_kind);
     }
   }
-  c->vfield_first_tile.push_back(vtiles);
-  c->rfield_first_tile.push_back(static_cast<uint32_t>(rtiles));
-  c->rfield_first_out.push_back(static_cast<uint32_t>(routs));
+  // one thread: the tables are sized for the most there can be, the sums come out of the fill itself
+  const TileSums& cap = at[tile_workers];
+  c->segs.set_size(tile_workers > 1 ? cap.nseg : b->n_fields);
+  c->vfield_first_tile.set_size((tile_workers > 1 ? cap.nvf : b->n_fields) + 1);
+  c->vfield_index.set_size(tile_workers > 1 ? cap.nvf : b->n_fields);
+  c->rfield_first_tile.set_size((tile_workers > 1 ? cap.nrf : b->n_fields) + 1);
+  c->rfield_first_out.set_size((tile_workers > 1 ? cap.nrf : b->n_fields) + 1);
+  c->rfield_index.set_size(tile_workers > 1 ? cap.nrf : b->n_fields);
+  TileSums end;
+  if (tile_workers > 1) {
+    std::vector<std::thread> crew;
+    for (uint32_t k = 0; k < tile_workers; ++k)
+      crew.emplace_back([&, k] { tile_range_pass(field_first(k), field_first(k + 1), at[k], true); });
+    for (std::thread& t : crew) t.join();
+    end = cap;
+  } else {
+    end = tile_range_pass(0, b->n_fields, TileSums{}, true);
+  }
+  if (end.rt > 0x7FFFFFFFull || end.ro > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (string_val tiles)");
+  if (end.vt > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (varint tiles)");
+  c->segs.set_size(end.nseg);
+  c->vfield_index.set_size(end.nvf);
+  c->vfield_first_tile.set_size(end.nvf + 1);
+  c->vfield_first_tile[end.nvf] = static_cast<uint32_t>(end.vt);
+  c->rfield_index.set_size(end.nrf);
+  c->rfield_first_tile.set_size(end.nrf + 1);
+  c->rfield_first_out.set_size(end.nrf + 1);
+  c->rfield_first_tile[end.nrf] = static_cast<uint32_t>(end.rt);
+  c->rfield_first_out[end.nrf] = static_cast<uint32_t>(end.ro);
+  c->n_copy_tiles = end.ct;
+  c->any_bulk = end.any_bulk;
+  c->cast_kind = end.cast_kind;
   // can the generic copy kernel be skipped?  Only the largest bulk body of a message is placed on a 16-byte
   // boundary by TFS_F_ALIGN_PAYLOAD, so every message may carry at most one bulk field, a plain byte copy
   // from a 16-byte aligned source, large enough for the TMA ring.
   // (TFS_F_ALIGN_PAYLOAD places tensor payloads; the lists of an Input are not aligned by it)
+  tr.mark("tiles");
   c->all_tma = (flags & TFS_F_ALIGN_PAYLOAD) != 0 && !c->has_input;
   for (uint32_t mi = 0; mi < b->n_msgs && c->all_tma; ++mi) {
     uint32_t bulk = 0;
@@ -849,21 +1055,20 @@ size_t place(size_t* cursor, const V& v) {
 }
 
 tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
-  size_t cur = 0;
-  const size_t o_msgs = place(&cur, c.msgs), o_tensors = place(&cur, c.tensors), o_fields = place(&cur, c.fields),
-               o_filters = place(&cur, c.filters), o_strings = place(&cur, c.strings), o_vft = place(&cur, c.vfield_first_tile),
+  // device table block: the records (already in the pinned record block, msgs | tensors | fields) and the small tables
+  const size_t o_msgs = 0, o_tensors = reinterpret_cast<const uint8_t*>(c.tensors) - reinterpret_cast<const uint8_t*>(c.msgs),
+               o_fields = reinterpret_cast<const uint8_t*>(c.fields) - reinterpret_cast<const uint8_t*>(c.msgs);
+  size_t cur = c.rec_bytes;
+  const size_t o_filters = place(&cur, c.filters), o_strings = place(&cur, c.strings), o_vft = place(&cur, c.vfield_first_tile),
                o_vfi = place(&cur, c.vfield_index), o_segs = place(&cur, c.segs), o_rft = place(&cur, c.rfield_first_tile),
                o_rfo = place(&cur, c.rfield_first_out), o_rfi = place(&cur, c.rfield_index);
-  const size_t total = align_up(cur, 16) + 16;
-  TFS_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, total));
+  const size_t total = align_up(cur, 16) + 16, small = total - c.rec_bytes;
+  TFS_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, small));
   TFS_TRY(dev_reserve(ctx, &ctx->d_tables, total));
-  uint8_t* h = static_cast<uint8_t*>(ctx->h_up);
+  uint8_t* h = static_cast<uint8_t*>(ctx->h_up) - c.rec_bytes;  // (offsets below are those of the device block)
   auto put = [&](size_t off, const void* p, size_t n) {
     if (n) std::memcpy(h + off, p, n);
   };
-  put(o_msgs, c.msgs.data(), c.msgs.size() * sizeof(EncMsg));
-  put(o_tensors, c.tensors.data(), c.tensors.size() * sizeof(EncTensor));
-  put(o_fields, c.fields.data(), c.fields.size() * sizeof(EncField));
   put(o_filters, c.filters.data(), c.filters.size() * sizeof(StrRef));
   put(o_strings, c.strings.data(), c.strings.size());
   put(o_vft, c.vfield_first_tile.data(), c.vfield_first_tile.size() * 4);
@@ -872,9 +1077,10 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   put(o_rft, c.rfield_first_tile.data(), c.rfield_first_tile.size() * 4);
   put(o_rfo, c.rfield_first_out.data(), c.rfield_first_out.size() * 4);
   put(o_rfi, c.rfield_index.data(), c.rfield_index.size() * 4);
-  TFS_CUDA(ctx, cudaMemcpyAsync(ctx->d_tables.p, h, total, cudaMemcpyHostToDevice, ctx->stream));
+  if (c.rec_bytes) TFS_CUDA(ctx, cudaMemcpyAsync(ctx->d_tables.p, c.msgs, c.rec_bytes, cudaMemcpyHostToDevice, ctx->stream));
+  TFS_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(ctx->d_tables.p) + c.rec_bytes, ctx->h_up, small, cudaMemcpyHostToDevice, ctx->stream));
 
-  const uint32_t n_msgs = static_cast<uint32_t>(c.msgs.size()), n_tensors = static_cast<uint32_t>(c.tensors.size());
+  const uint32_t n_msgs = static_cast<uint32_t>(c.n_msgs), n_tensors = static_cast<uint32_t>(c.n_tensors);
   const uint32_t n_vtiles = c.vfield_first_tile.back();
   const uint32_t n_rtiles = c.rfield_first_tile.back(), n_routs = c.rfield_first_out.back();
   size_t w = 0;
@@ -927,7 +1133,7 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   if (n_rtiles) TFS_CUDA(ctx, cudaMemsetAsync(T.result, 0, 32, ctx->stream));
   T.n_msgs = n_msgs;
   T.n_tensors = n_tensors;
-  T.n_fields = static_cast<uint32_t>(c.fields.size());
+  T.n_fields = static_cast<uint32_t>(c.n_fields);
   T.n_filters = static_cast<uint32_t>(c.filters.size());
   T.n_vfields = static_cast<uint32_t>(c.vfield_index.size());
   T.n_vtiles = n_vtiles;
@@ -1014,10 +1220,14 @@ tfs_status_t fetch_results(tfs_ctx* ctx, const EncTables& T, uint64_t* msg_off_o
 tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev, uint64_t dst_capacity, uint32_t flags,
                            uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out, bool size_only) {
   TFS_CUDA(ctx, cudaSetDevice(ctx->device));
-  Compiled c;
-  TFS_TRY(compile_batch(ctx, batch, flags, &c));
+  HostTrace tr(ctx, "encode");
+  if (!ctx->enc_scratch) ctx->enc_scratch = std::make_shared<Compiled>();
+  Compiled& c = *static_cast<Compiled*>(ctx->enc_scratch.get());
+  TFS_TRY(compile_batch(ctx, batch, flags, &c, true));
+  tr.mark("compile");
   Uploaded u;
   TFS_TRY(upload(ctx, c, &u));
+  tr.mark("upload");
   const uint32_t dst_skew = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(dst_dev) & 15u);
   TFS_TRY(run_sizing(ctx, u, size_only ? 0u : flags, dst_skew, size_only ? ~0ull : dst_capacity,
                      size_only ? nullptr : static_cast<uint8_t*>(dst_dev)));
@@ -1054,13 +1264,16 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
     }
   }
   bool overflow = false;
+  tr.mark("launch");
   TFS_TRY(fetch_results(ctx, u.T, msg_off_out, msg_len_out, total_out, &overflow));
+  tr.mark("fetch");
   if (overflow) return set_err(ctx, TFS_ERR_NOMEM, "dst_capacity is smaller than the encoded batch");
   return TFS_OK;
 }
 
 uint64_t encode_bound(const tfs_batch_t* batch, uint32_t flags) {
   tfs_ctx dummy;
+  dummy.trace = std::getenv("TFS_TRACE") != nullptr;
   Compiled c;
   if (compile_batch(&dummy, batch, flags, &c) != TFS_OK) return 0;
   return c.bound + 64;

@@ -4,6 +4,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <chrono>
+#include <cstdio>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <utility>
@@ -243,6 +246,7 @@ struct tfs_ctx {
   uint32_t err_msg_index = 0;
   uint64_t err_byte_offset = 0;
   uint64_t launches = 0;
+  bool trace = false;  // TFS_TRACE=1 in the environment: host phase times of every batch call on stderr (HostTrace)
   DevBuf d_tables, d_work, d_stage_in, d_stage_out;
   DevBuf d_dec1, d_dec2, d_dec3;  // decode tables (pass 1 / pass 2 / varint tiles); owned by the newest tfs_decoded handle
   // small-batch decode plans its tables optimistically from what earlier batches on this context needed
@@ -267,6 +271,9 @@ struct tfs_ctx {
   size_t h_up_cap = 0;
   void* h_down = nullptr;
   size_t h_down_cap = 0;
+  std::shared_ptr<void> enc_scratch;  // the encoder's host tables (tfs_encode.cu: Compiled), kept between calls: grow-only
+  void* h_rec = nullptr;  // the encoder compiles its message / tensor / field records straight into this pinned block
+  size_t h_rec_cap = 0;
   // pinned staging pool (tfs_stage_acquire / release): one region pinned at tfs_ctx_create, carved into power-of-two
   // classes from 4 KiB up and recycled through per-class free lists
   void* h_slab = nullptr;
@@ -294,6 +301,28 @@ struct ProfScope {
   ProfScope(tfs_ctx* c, int kernel_id);
   ~ProfScope();
 };
+
+// Host phase times of one call on stderr when TFS_TRACE is set (a no-op otherwise): `mark("name")` closes a phase.
+struct HostTrace {
+  const bool on;
+  const char* what;
+  std::chrono::steady_clock::time_point t0, last;
+  std::string line;
+  HostTrace(const tfs_ctx* c, const char* w) : on(c->trace), what(w) {
+    if (on) t0 = last = std::chrono::steady_clock::now();
+  }
+  void mark(const char* phase) {
+    if (!on) return;
+    const auto now = std::chrono::steady_clock::now();
+    char buf[64];
+    std::snprintf(buf, sizeof buf, " %s %.3f", phase, std::chrono::duration<double, std::milli>(now - last).count());
+    line += buf;
+    last = now;
+  }
+  ~HostTrace() {
+    if (on) std::fprintf(stderr, "[tfs] %s: total %.3f ms |%s\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(), line.c_str());
+  }
+};
 }  // namespace tfs
 
 namespace tfs {
@@ -302,6 +331,15 @@ tfs_status_t set_err(tfs_ctx* ctx, tfs_status_t st, const std::string& what);
 tfs_status_t cuda_fail(tfs_ctx* ctx, cudaError_t e, const char* where);
 tfs_status_t dev_reserve(tfs_ctx* ctx, DevBuf* b, size_t bytes);
 tfs_status_t pinned_reserve(tfs_ctx* ctx, void** p, size_t* cap, size_t bytes);
+// Pinned result blocks of the decoder.  A decode handle OWNS the block its tables were copied into (the view points into
+// it: no second copy on the host); freed handles give their block to a small process-wide list (portable pinned memory,
+// usable from every device), so a steady decode / read / free loop allocates nothing.
+struct PinnedBlock {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+tfs_status_t down_acquire(tfs_ctx* ctx, size_t bytes, PinnedBlock* out);
+void down_release(PinnedBlock b);
 
 #define TFS_CUDA(ctx, call)                                       \
   do {                                                            \
