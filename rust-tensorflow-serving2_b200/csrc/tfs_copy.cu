@@ -187,6 +187,52 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy(const CopySeg* __restrict
 }
 
 // ---------------------------------------------------------------------------------------------------
+// small segments (<= kSmallSegBytes of output): they own no tiles; one WARP per segment of the table
+// ---------------------------------------------------------------------------------------------------
+template <class IN, class OUT, class F>
+__device__ __forceinline__ void warp_cast(uint8_t* __restrict__ dst, const uint8_t* __restrict__ src, uint32_t n, F f) {
+  const bool in_al = (reinterpret_cast<uintptr_t>(src) & (sizeof(IN) - 1)) == 0;
+  const bool out_al = (reinterpret_cast<uintptr_t>(dst) & (sizeof(OUT) - 1)) == 0;
+  for (uint32_t i = lane_id(); i < n; i += 32u) {
+    IN x = load_unaligned<IN>(src + static_cast<uint64_t>(i) * sizeof(IN), in_al);
+    store_unaligned<OUT>(dst + static_cast<uint64_t>(i) * sizeof(OUT), f(x), out_al);
+  }
+}
+
+__device__ __forceinline__ bool small_seg(const CopySeg& s) { return s.n * out_size_of(s.op) <= kSmallSegBytes; }
+
+__global__ void __launch_bounds__(kCopyThreads) k_copy_small(const CopySeg* __restrict__ segs, uint32_t n_segs, const uint64_t* __restrict__ gate) {
+  if (gate && *gate != 0) return;
+  const uint32_t si = (blockIdx.x * kCopyThreads + threadIdx.x) >> 5;
+  if (si >= n_segs) return;
+  const CopySeg seg = segs[si];
+  if (seg.n == 0 || !small_seg(seg)) return;
+  const uint32_t n = static_cast<uint32_t>(seg.n);
+  uint8_t* d = seg.dst;
+  const uint8_t* s = seg.src;
+  const float p = seg.param;
+  switch (seg.op) {
+    case CP_BYTES:
+      if (((reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(s)) & 3u) == 0) {  // words, then the tail
+        for (uint32_t i = lane_id(); i < (n >> 2); i += 32u) reinterpret_cast<uint32_t*>(d)[i] = reinterpret_cast<const uint32_t*>(s)[i];
+        for (uint32_t i = (n & ~3u) + lane_id(); i < n; i += 32u) d[i] = s[i];
+      } else {
+        for (uint32_t i = lane_id(); i < n; i += 32u) d[i] = s[i];
+      }
+      break;
+    case CP_BOOL: warp_cast<uint8_t, uint8_t>(d, s, n, [](uint8_t x) { return static_cast<uint8_t>(x != 0); }); break;
+    case CP_U8_F32: warp_cast<uint8_t, float>(d, s, n, [](uint8_t x) { return static_cast<float>(x); }); break;
+    case CP_U8_F32_DIV: warp_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return __fdiv_rn(static_cast<float>(x), p); }); break;
+    case CP_U8_F32_MUL: warp_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return __fmul_rn(static_cast<float>(x), p); }); break;
+    case CP_F32_F16: warp_cast<float, uint16_t>(d, s, n, [](float x) { return static_cast<uint16_t>(f32_to_f16_bits(x)); }); break;
+    case CP_F32_BF16: warp_cast<float, uint16_t>(d, s, n, [](float x) { return static_cast<uint16_t>(f32_to_bf16_bits(x)); }); break;
+    case CP_F16_F32: warp_cast<uint16_t, float>(d, s, n, [](uint16_t x) { return f16_bits_to_f32(x); }); break;
+    case CP_BF16_F32: warp_cast<uint16_t, float>(d, s, n, [](uint16_t x) { return bf16_bits_to_f32(x); }); break;
+    default: break;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // TMA path: cp.async.bulk global -> shared -> global, one driving thread per CTA, one CTA per SM
 // ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
@@ -497,8 +543,24 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy_cast(const CopySeg* __res
 }  // namespace
 
 tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
-                         bool need_generic, const std::vector<HostSeg>* host_segs, bool need_tma, int cast_kind) {
-  if (n_segs == 0 || n_tiles == 0) return TFS_OK;
+                         bool need_generic, const std::vector<HostSeg>* host_segs, bool need_tma, int cast_kind, bool any_small) {
+  if (n_segs == 0) return TFS_OK;
+  auto launch_small = [&]() -> tfs_status_t {
+    if (!any_small) return TFS_OK;
+    ProfScope prof(ctx, PK_COPY);
+    k_copy_small<<<static_cast<uint32_t>((static_cast<uint64_t>(n_segs) * 32u + kCopyThreads - 1) / kCopyThreads), kCopyThreads, 0, ctx->stream>>>(segs_dev, n_segs, gate);
+    ctx->launches++;
+    return TFS_OK;
+  };
+  if (n_tiles == 0) {  // nothing but small segments
+    if (!ctx->pipe.empty()) {
+      TFS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipe.back().ready, 0));
+      ctx->pipe.clear();
+    }
+    TFS_TRY(launch_small());
+    TFS_CUDA(ctx, cudaGetLastError());
+    return TFS_OK;
+  }
   if (n_tiles > 0x7FFFFFFFull) return set_err(ctx, TFS_ERR_INVALID_ARG, "batch too large (copy tiles)");
   const uint32_t ring_bytes = kTmaStages * kTmaChunk;
   if (!ctx->copy_attr_set) {  // a per-device attribute: once per context, not once per process
@@ -534,10 +596,12 @@ tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs,
     }
   };
   if (ctx->pipe.empty()) {
+    TFS_TRY(launch_small());
     launch(0, ~0ull, 0, n_tiles);
   } else if (!host_segs) {
     TFS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipe.back().ready, 0));
     ctx->pipe.clear();
+    TFS_TRY(launch_small());
     launch(0, ~0ull, 0, n_tiles);
   } else {
     // the sources are still arriving over PCIe, chunk by chunk: one launch per chunk, each behind its chunk's event,
@@ -561,7 +625,9 @@ tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs,
       }
       lo = hi;
     }
+    if (any_small) TFS_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pipe.back().ready, 0));  // (their sources may sit in any chunk)
     ctx->pipe.clear();
+    TFS_TRY(launch_small());
   }
   TFS_CUDA(ctx, cudaGetLastError());
   return TFS_OK;

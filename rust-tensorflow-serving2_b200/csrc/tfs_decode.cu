@@ -40,7 +40,7 @@ namespace {
 
 enum { WT_VARINT = 0, WT_64 = 1, WT_LEN = 2, WT_SGROUP = 3, WT_EGROUP = 4, WT_32 = 5 };
 // TOT_GENERIC counts the copy-class spans the TMA ring cannot take (not congruent mod 16, tiny, or widened)
-enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_RETRY, TOT_BULK, TOT_BAR0, TOT_BAR1, TOT_QT, TOT_QS, TOT_QF, TOT_QSTR, TOT_COUNT_ = 24 };  // TOT_BAR*: meeting counters of k_plan_warp; TOT_Q*: largest per-message counts seen (quota hints)
+enum Tot { TOT_TENSORS = 0, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES, TOT_POOL, TOT_FAILED, TOT_GENERIC, TOT_OVERFLOW, TOT_RETRY, TOT_BULK, TOT_BAR0, TOT_BAR1, TOT_QT, TOT_QS, TOT_QF, TOT_QSTR, TOT_SMALL, TOT_COUNT_ = 24 };  // TOT_BAR*: meeting counters of k_plan_warp; TOT_Q*: largest per-message counts seen (quota hints); TOT_SMALL: copy-class spans of at most kSmallSegBytes (no tiles, k_copy_small)
 constexpr size_t kTotalsBytes = sizeof(uint64_t) * TOT_COUNT_;
 
 __device__ __forceinline__ uint32_t slot_of(uint32_t tag) {
@@ -107,7 +107,7 @@ struct Walker {
   bool verify = false;  // error path only: also look inside packed varint bodies (see walk_body)
   bool opaque = false;  // inside a resource_handle_val / variant_val element: validate only, record nothing
   // counters (COUNT) / cursors (FILL)
-  uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0, n_generic = 0, n_bulk = 0;
+  uint32_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0, n_ct = 0, n_generic = 0, n_bulk = 0, n_small = 0;
   uint32_t seen_slots = 0;  // payload slots of the current tensor that already have a chunk
   // single-walk mode (k_plan_warp): the records go to per-message quota slots; a cursor that reaches its cap keeps counting
   // but writes to the slot's spare entry (tensors, spans) or nowhere (filters, string bytes), and `ovf` asks for a retry
@@ -310,9 +310,12 @@ struct Walker {
       return;
     }
     const uint32_t vt = cls == SC_VARINT ? varint_tiles_of(wv, off, len) : 0u;
-    if (cls == SC_STR && len) n_generic++;  // string bytes land wherever the earlier elements end: generic kernel
+    // at most kSmallSegBytes of output: the span owns no copy tiles, k_copy_small takes it (one warp per span)
+    const bool small = cls != SC_VARINT && len * out_mult <= kSmallSegBytes;
+    if (small && len) n_small++;
+    if (cls == SC_STR && len && !small) n_generic++;  // string bytes land wherever the earlier elements end: generic kernel
     if (cls != SC_VARINT && len >= 4096) n_bulk++;  // large enough for the TMA ring (if it turns out congruent mod 16)
-    if (cls == SC_COPY && len) {
+    if (cls == SC_COPY && len && !small) {
       // Can the TMA ring take this span?  Its pool region starts on a 64-byte boundary, so the first chunk of
       // a slot is congruent mod 16 with its source iff the source address is 16-byte aligned.  A conservative
       // count (later chunks, tiny or widened spans count as "no") decides whether the generic kernel is launched.
@@ -321,7 +324,7 @@ struct Walker {
     }
     seen_slots |= 1u << slot;
     // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
-    const uint32_t ct = cls != SC_VARINT ? static_cast<uint32_t>((len * out_mult + kCopyTileBytes - 1) / kCopyTileBytes) + 1u : 0u;
+    const uint32_t ct = (cls != SC_VARINT && !small) ? static_cast<uint32_t>((len * out_mult + kCopyTileBytes - 1) / kCopyTileBytes) + 1u : 0u;
     if (FILL) {
       DecSpan s;
       s.wire_off = off;
@@ -614,7 +617,8 @@ struct Walker {
           const uint64_t wa = reinterpret_cast<uintptr_t>(w), te = tend;
           uint64_t p = pos, lwb = win_base;
           uint4 lw = win;
-          uint32_t ns = n_spans, ng = n_generic, nc = n_ct;
+          uint32_t ns = n_spans, nsm = n_small;
+          const uint32_t nc = n_ct;  // (an element with a one-byte length is a small span: no copy tiles)
           const uint32_t nv = n_vt;
           const uint4 ids = make_uint4(cur, slot_of(8), msg, SC_STR);
           uint4* const spans = reinterpret_cast<uint4*>(T.spans);
@@ -653,16 +657,14 @@ struct Walker {
               sc[ns] = nc;
             }
             ns++;
-            ng += l != 0;
-            nc += (l != 0) + 1u;  // as add_span counts a span shorter than a copy tile
+            nsm += l != 0;  // as add_span counts a small span
             p += 2 + l;
           }
           pos = p;
           win = lw;
           win_base = lwb;
           n_spans = ns;
-          n_generic = ng;
-          n_ct = nc;
+          n_small = nsm;
         }
         return true;
       }
@@ -858,6 +860,7 @@ __device__ void walk_body(const DecTables& T, uint32_t mi) {
     T.cnt_ctiles[mi] = ok ? wk.n_ct : 0u;
     if (ok && wk.n_generic) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_GENERIC]), static_cast<unsigned long long>(wk.n_generic));
     if (ok && wk.n_bulk) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_BULK]), static_cast<unsigned long long>(wk.n_bulk));
+    if (ok && wk.n_small) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_SMALL]), static_cast<unsigned long long>(wk.n_small));
   } else {
     const int32_t st = T.msgs[mi].status;
     const uint64_t eo = T.msgs[mi].err_offset;
@@ -893,45 +896,51 @@ __global__ void __launch_bounds__(128) k_walk(DecTables T, uint32_t lanes) {
   if (mi < T.n_msgs) walk_body<FILL>(T, mi);
 }
 
-// exclusive scan of `a[0..n)` in place by one CTA of NW warps; returns the total in every thread
+// exclusive scan of `a[0..n)` in place by one CTA of NW warps, eight consecutive entries per thread and round (the arrays
+// are 64-byte aligned); returns the total in every thread
 template <int NW>
 __device__ uint64_t cta_scan_u32(uint32_t* a, uint32_t n, uint64_t* smem) {
   uint64_t carry = 0;
-  for (uint32_t base = 0; base < n; base += NW * 32) {
-    const uint32_t i = base + threadIdx.x;
-    const uint64_t v = i < n ? a[i] : 0u;
+  for (uint32_t base = 0; base < n; base += NW * 32 * 8) {
+    const uint32_t i = base + threadIdx.x * 8u;
+    uint32_t x[8];
+    if (i + 8u <= n) {
+      const uint4 lo = *reinterpret_cast<const uint4*>(a + i), hi = *reinterpret_cast<const uint4*>(a + i + 4);
+      x[0] = lo.x, x[1] = lo.y, x[2] = lo.z, x[3] = lo.w, x[4] = hi.x, x[5] = hi.y, x[6] = hi.z, x[7] = hi.w;
+    } else {
+#pragma unroll
+      for (uint32_t j = 0; j < 8; ++j) x[j] = i + j < n ? a[i + j] : 0u;
+    }
+    uint64_t v = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v += x[j];
     uint64_t total;
-    const uint64_t ex = block_exclusive_scan<uint64_t, NW>(v, smem, &total);
-    if (i < n) a[i] = static_cast<uint32_t>(carry + ex);
+    uint64_t run = carry + block_exclusive_scan<uint64_t, NW>(v, smem, &total);
+#pragma unroll
+    for (uint32_t j = 0; j < 8; ++j) {
+      if (i + j < n) a[i + j] = static_cast<uint32_t>(run);
+      run += x[j];
+    }
     carry += total;
     __syncthreads();
   }
   return carry;
 }
 
-template <int NW>
-__device__ void scan_counts_body(const DecTables& T, uint64_t* smem) {
-  const uint64_t t0 = cta_scan_u32<NW>(T.cnt_tensors, T.n_msgs, smem);
-  const uint64_t t1 = cta_scan_u32<NW>(T.cnt_filters, T.n_msgs, smem);
-  const uint64_t t2 = cta_scan_u32<NW>(T.cnt_spans, T.n_msgs, smem);
-  const uint64_t t3 = cta_scan_u32<NW>(T.cnt_strbytes, T.n_msgs, smem);
-  const uint64_t t4 = cta_scan_u32<NW>(T.cnt_vtiles, T.n_msgs, smem);
-  const uint64_t t5 = cta_scan_u32<NW>(T.cnt_ctiles, T.n_msgs, smem);
-  if (threadIdx.x == 0) {
-    T.totals[TOT_TENSORS] = t0;
-    T.totals[TOT_FILTERS] = t1;
-    T.totals[TOT_SPANS] = t2;
-    T.totals[TOT_STR] = t3;
-    T.totals[TOT_VTILES] = t4;
-    T.totals[TOT_CTILES] = t5;
-    T.totals[TOT_POOL] = 0;
-    T.totals[TOT_FAILED] = 0;
-    // TOT_GENERIC was accumulated by the walk (the host zeroes the totals before pass 1)
-  }
-}
+// the six per-message counters -> exclusive offsets and totals; one CTA per counter
 __global__ void __launch_bounds__(1024) k_scan_counts(DecTables T) {
   __shared__ uint64_t smem[33];
-  scan_counts_body<32>(T, smem);
+  uint32_t* const arr[6] = {T.cnt_tensors, T.cnt_filters, T.cnt_spans, T.cnt_strbytes, T.cnt_vtiles, T.cnt_ctiles};
+  const int tot[6] = {TOT_TENSORS, TOT_FILTERS, TOT_SPANS, TOT_STR, TOT_VTILES, TOT_CTILES};
+  const uint64_t t = cta_scan_u32<32>(arr[blockIdx.x], T.n_msgs, smem);
+  if (threadIdx.x == 0) {
+    T.totals[tot[blockIdx.x]] = t;
+    if (blockIdx.x == 0) {
+      T.totals[TOT_POOL] = 0;
+      T.totals[TOT_FAILED] = 0;
+      // TOT_GENERIC / TOT_BULK / TOT_SMALL were accumulated by the walk (the host zeroes the totals before pass 1)
+    }
+  }
 }
 
 constexpr uint32_t kSmallBatch = 256;
@@ -1313,6 +1322,7 @@ __global__ void __launch_bounds__(kPlanWarps * 32) k_plan_warp(DecTables T, Plan
         c_ct = wk.n_ct;
         if (wk.n_generic) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_GENERIC]), static_cast<unsigned long long>(wk.n_generic));
         if (wk.n_bulk) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_BULK]), static_cast<unsigned long long>(wk.n_bulk));
+        if (wk.n_small) atomicAdd(reinterpret_cast<unsigned long long*>(&T.totals[TOT_SMALL]), static_cast<unsigned long long>(wk.n_small));
         atomicMax(reinterpret_cast<unsigned long long*>(&T.totals[TOT_QT]), static_cast<unsigned long long>(c_t));
         atomicMax(reinterpret_cast<unsigned long long*>(&T.totals[TOT_QS]), static_cast<unsigned long long>(c_s));
         atomicMax(reinterpret_cast<unsigned long long*>(&T.totals[TOT_QF]), static_cast<unsigned long long>(c_f));
@@ -1487,7 +1497,9 @@ tfs_status_t launch_values(tfs_ctx* ctx, tfs_decoded* dec, uint8_t* pool, const 
   const bool need_generic = dec->totals[TOT_GENERIC] != 0 || (reinterpret_cast<uintptr_t>(pool) & 15u) != 0;
   // tensor_content of a 16-bit float tensor widened to f32 (TFS_F_CONTENT_HALF_TO_F32): the staged cast kernel
   const int cast_kind = (T.flags & TFS_F_CONTENT_HALF_TO_F32) ? 1 : 0;
-  if (n_ct) TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, gate, need_generic, host_segs, dec->totals[TOT_BULK] != 0, cast_kind));
+  const bool any_small = dec->totals[TOT_SMALL] != 0;
+  if (n_ct || any_small)
+    TFS_TRY(launch_copy(ctx, T.segs, static_cast<uint32_t>(n_spans), n_ct, gate, need_generic, host_segs, dec->totals[TOT_BULK] != 0, cast_kind, any_small));
   return TFS_OK;
 }
 
@@ -1703,7 +1715,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       k_walk<false><<<wblocks, 128, 0, ctx->stream>>>(T, walk_lanes);
     }
     ctx->launches++;
-    k_scan_counts<<<1, 1024, 0, ctx->stream>>>(T);
+    k_scan_counts<<<6, 1024, 0, ctx->stream>>>(T);
     ctx->launches++;
     DEC_CUDA(cudaGetLastError());
     DEC_TRY(need_down(kTotalsBytes));

@@ -586,13 +586,14 @@ struct Compiled {
   // (TFS_F_ALIGN_PAYLOAD, one bulk field per message, 16-byte aligned plain-byte sources): TMA ring only
   bool all_tma = true;
   bool any_bulk = false;   // some copy segment is >= 4 KiB of plain bytes (a candidate for the TMA ring)
+  bool any_small = false;  // some copy segment has <= kSmallSegBytes of output (no tiles: k_copy_small)
   int cast_kind = 0;       // staged cast kernel needed: 1 = widening segments only, 2 = narrowing ones too (launch_copy)
   bool has_input = false;  // some message is an Input / ClassificationRequest: features are framed by their own kernels
   void reset() {  // a new batch in the same storage
     strings.clear();
     n_copy_tiles = bound = 0;
     all_tma = true;
-    any_bulk = has_input = false;
+    any_bulk = any_small = has_input = false;
     cast_kind = 0;
   }
 };
@@ -903,7 +904,7 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
   struct TileSums {
     uint64_t vt = 0, rt = 0, ro = 0, ct = 0;  // varint tiles, ragged tiles, ragged output tiles, copy tiles
     uint64_t nseg = 0, nvf = 0, nrf = 0;      // copy segments, varint fields, ragged fields
-    bool any_bulk = false;
+    bool any_bulk = false, any_small = false;
     int cast_kind = 0;
   };
   // fields [f0, f1) starting at the sums `at`; FILL = false only counts.  Returns the sums at f1.
@@ -955,6 +956,10 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
           c->segs[at.nseg] = s;
         }
         ++at.nseg;
+        if (f.body_len <= kSmallSegBytes) {  // no tiles: k_copy_small takes it
+          at.any_small = true;
+          continue;
+        }
         // +1: byte segments are tiled on the 16-byte grid of the destination address, which can add a tile
         at.ct += (f.body_len + kCopyTileBytes - 1) / kCopyTileBytes + 1;
         at.any_bulk |= f.mode == CP_BYTES && f.body_len >= 4096;
@@ -979,6 +984,7 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
       n.vt += part[k].vt, n.rt += part[k].rt, n.ro += part[k].ro, n.ct += part[k].ct;
       n.nseg += part[k].nseg, n.nvf += part[k].nvf, n.nrf += part[k].nrf;
       n.any_bulk |= part[k].any_bulk;
+      n.any_small |= part[k].any_small;
       n.cast_kind = std::max(n.cast_kind, part[k].cast_kind);
     }
   }
@@ -1013,6 +1019,7 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
   c->rfield_first_out[end.nrf] = static_cast<uint32_t>(end.ro);
   c->n_copy_tiles = end.ct;
   c->any_bulk = end.any_bulk;
+  c->any_small = end.any_small;
   c->cast_kind = end.cast_kind;
   // can the generic copy kernel be skipped?  Only the largest bulk body of a message is placed on a 16-byte
   // boundary by TFS_F_ALIGN_PAYLOAD, so every message may carry at most one bulk field, a plain byte copy
@@ -1027,7 +1034,7 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
       const EncTensor& t = c->tensors[ti];
       for (uint32_t fi = t.first_field; fi < t.first_field + t.n_fields; ++fi) {
         const EncField& f = c->fields[fi];
-        if (f.is_varint || f.n_elems == 0) continue;
+        if (f.is_varint || f.n_elems == 0 || f.body_len <= kSmallSegBytes) continue;  // (small bodies need no alignment)
         ++bulk;
         // (a widening / narrowing field that the staged cast kernel takes needs no alignment at all)
         const uint32_t in_sz = (f.mode == CP_F32_F16 || f.mode == CP_F32_BF16) ? 4u : (f.mode == CP_F16_F32 || f.mode == CP_BF16_F32) ? 2u : 1u;
@@ -1260,7 +1267,7 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
           hs.push_back({reinterpret_cast<uintptr_t>(g.src), g.n * in, g.first_tile, next - g.first_tile, stb, stb});
         }
       }
-      TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, T.result + 1, !c.all_tma, hs.empty() ? nullptr : &hs, c.any_bulk, c.cast_kind));
+      TFS_TRY(launch_copy(ctx, T.segs, T.n_segs, u.n_copy_tiles, T.result + 1, !c.all_tma, hs.empty() ? nullptr : &hs, c.any_bulk, c.cast_kind, c.any_small));
     }
   }
   bool overflow = false;

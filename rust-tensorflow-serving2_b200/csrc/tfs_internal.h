@@ -23,6 +23,10 @@ constexpr int kVarintTile = kVarintThreads * kVarintRows;  // 2048 elements per 
 constexpr int kVarintMaxLen = 10;
 constexpr int kCopyThreads = 256;
 constexpr int kCopyTileBytes = 32768;                // output bytes per copy tile
+// A copy segment of at most this many OUTPUT bytes owns no tiles at all: k_copy_small takes it, one warp per segment
+// (a batch of 10^6 twelve-byte float_val bodies would otherwise launch two million CTAs).  The encoder's host tables,
+// the decoder's structure walk and the copy kernels apply the same rule.
+constexpr uint32_t kSmallSegBytes = 512;
 constexpr int kDecThreads = 256;
 constexpr int kDecTileBytes = 4096;                  // wire bytes per varint-decode tile (16 B per thread of the gather kernel)
 
@@ -369,8 +373,10 @@ struct HostSeg {
 // just the tiles that can end inside the chunk; without it the launch waits for the last chunk.
 // `cast_kind`: 0 = no widening / narrowing segment can be large enough for the staged cast kernel, 1 = only widening ones
 // (u8 -> f32, 16-bit -> f32), 2 = narrowing ones (f32 -> 16-bit) too (a larger input stage).
+// `any_small`: some segment has at most kSmallSegBytes of output (it owns no tiles; k_copy_small takes it).
 tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
-                         bool need_generic, const std::vector<HostSeg>* host_segs = nullptr, bool need_tma = true, int cast_kind = 0);
+                         bool need_generic, const std::vector<HostSeg>* host_segs = nullptr, bool need_tma = true, int cast_kind = 0,
+                         bool any_small = false);
 
 inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
