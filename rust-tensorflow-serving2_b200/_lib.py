@@ -11,7 +11,7 @@ from . import abi
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "libtfs_gpu.so")
+LIB_PATH = os.environ.get("TFS_LIB_PATH") or os.path.join(CSRC, "libtfs_gpu.so")  # (the override is for A/B runs of two builds)
 
 _lib = None
 

@@ -1070,9 +1070,14 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
                o_vfi = place(&cur, c.vfield_index), o_segs = place(&cur, c.segs), o_rft = place(&cur, c.rfield_first_tile),
                o_rfo = place(&cur, c.rfield_first_out), o_rfi = place(&cur, c.rfield_index);
   const size_t total = align_up(cur, 16) + 16, small = total - c.rec_bytes;
-  TFS_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, small));
+  // Small tables go up in ONE copy.  Measured (tfs_encode_host, 1.2 GB of payload arriving in chunks on the copy stream):
+  // one small host -> device copy overtakes the queued chunks, a second one behind it waits for all of them, and the
+  // framing kernel with it - 47.8 instead of 29.3 ms per call.  Only a large record block (10^5 messages and more) is
+  // uploaded from where it was compiled.
+  const bool oneup = total <= (256u << 10);
+  TFS_TRY(pinned_reserve(ctx, &ctx->h_up, &ctx->h_up_cap, oneup ? total : small));
   TFS_TRY(dev_reserve(ctx, &ctx->d_tables, total));
-  uint8_t* h = static_cast<uint8_t*>(ctx->h_up) - c.rec_bytes;  // (offsets below are those of the device block)
+  uint8_t* h = static_cast<uint8_t*>(ctx->h_up) - (oneup ? 0 : c.rec_bytes);  // (offsets below are those of the device block)
   auto put = [&](size_t off, const void* p, size_t n) {
     if (n) std::memcpy(h + off, p, n);
   };
@@ -1084,8 +1089,13 @@ tfs_status_t upload(tfs_ctx* ctx, const Compiled& c, Uploaded* u) {
   put(o_rft, c.rfield_first_tile.data(), c.rfield_first_tile.size() * 4);
   put(o_rfo, c.rfield_first_out.data(), c.rfield_first_out.size() * 4);
   put(o_rfi, c.rfield_index.data(), c.rfield_index.size() * 4);
-  if (c.rec_bytes) TFS_CUDA(ctx, cudaMemcpyAsync(ctx->d_tables.p, c.msgs, c.rec_bytes, cudaMemcpyHostToDevice, ctx->stream));
-  TFS_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(ctx->d_tables.p) + c.rec_bytes, ctx->h_up, small, cudaMemcpyHostToDevice, ctx->stream));
+  if (oneup) {
+    if (c.rec_bytes) std::memcpy(h, c.msgs, c.rec_bytes);
+    TFS_CUDA(ctx, cudaMemcpyAsync(ctx->d_tables.p, h, total, cudaMemcpyHostToDevice, ctx->stream));
+  } else {
+    TFS_CUDA(ctx, cudaMemcpyAsync(ctx->d_tables.p, c.msgs, c.rec_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    TFS_CUDA(ctx, cudaMemcpyAsync(static_cast<uint8_t*>(ctx->d_tables.p) + c.rec_bytes, ctx->h_up, small, cudaMemcpyHostToDevice, ctx->stream));
+  }
 
   const uint32_t n_msgs = static_cast<uint32_t>(c.n_msgs), n_tensors = static_cast<uint32_t>(c.n_tensors);
   const uint32_t n_vtiles = c.vfield_first_tile.back();
