@@ -231,6 +231,10 @@ tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx) {
   if (ctx->h_up) cudaFreeHost(ctx->h_up);
   if (ctx->h_down) cudaFreeHost(ctx->h_down);
   if (ctx->h_rec) cudaFreeHost(ctx->h_rec);
+  ctx->stage_crew.reset();  // joins the helper threads
+  if (ctx->h_ring) cudaFreeHost(ctx->h_ring);
+  for (cudaEvent_t e : ctx->ring_ev)
+    if (e) cudaEventDestroy(e);
   if (ctx->h_slab) cudaFreeHost(ctx->h_slab);
   for (auto& e : ctx->pool_extra) cudaFreeHost(e.first);
   if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);

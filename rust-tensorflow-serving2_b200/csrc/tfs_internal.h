@@ -275,6 +275,13 @@ struct tfs_ctx {
   size_t h_up_cap = 0;
   void* h_down = nullptr;
   size_t h_down_cap = 0;
+  // pageable host buffers: helper threads copy them through a pinned ring of four slots while the copy engine drains /
+  // fills the others (tfs_host.cu: StageCrew, staged_h2d / staged_d2h)
+  std::shared_ptr<void> stage_crew;
+  void* h_ring = nullptr;
+  cudaEvent_t ring_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  bool ring_busy[4] = {false, false, false, false};
+  uint32_t ring_next = 0;
   std::shared_ptr<void> enc_scratch;  // the encoder's host tables (tfs_encode.cu: Compiled), kept between calls: grow-only
   void* h_rec = nullptr;  // the encoder compiles its message / tensor / field records straight into this pinned block
   size_t h_rec_cap = 0;

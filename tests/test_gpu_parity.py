@@ -748,6 +748,41 @@ def test_pinned_buffers_take_the_chunked_copy_engine_path(codec, flags):
     roundtrip_check(codec, msgs, abi.MSG_PREDICT_REQUEST, "chunked pinned path", flags)
 
 
+@pytest.mark.parametrize("flags", [0, abi.F_ALIGN_PAYLOAD])
+def test_pageable_buffers_cross_the_pinned_ring(codec, flags):
+    """Pageable payloads / wire / pools of 1 MB and more are copied through a two-slot pinned ring by helper threads
+    (csrc/tfs_host.cu staged_h2d / staged_d2h): several ring turns, fields that end inside a slot, a pinned destination
+    (the copy kernel then follows the chunks) and a pageable one; bytes against the oracle, values back."""
+    import torch
+    rng = np.random.default_rng(9091)
+    msgs = [tfs.PredictRequest(tfs.ModelSpec("ring", signature_name="serving_default"), [
+        ("x", tfs.TensorProto(dtype=1, tensor_shape=tfs.TensorShapeProto([10_000_003 + i]), float_val=rng.standard_normal(10_000_003 + i).astype(np.float32))),
+        ("ids", tfs.TensorProto(dtype=9, int64_val=rng.integers(-5, 1 << 33, 700_001, dtype=np.int64))),
+        ("raw", tfs.TensorProto(dtype=4, tensor_content=rng.integers(0, 256, 1_048_577, dtype=np.uint8))),
+        ("tiny", tfs.TensorProto(dtype=1, float_val=rng.standard_normal(3).astype(np.float32)))]) for i in range(3)]
+    kind = abi.MSG_PREDICT_REQUEST
+    want = ob.encode_messages(msgs, kind)
+    enc, dec = codec.encoder(), codec.decoder()
+    built = tfs.build_batch(msgs, kind)
+    # pageable payloads -> pageable wire, and -> pinned wire
+    got = enc.encode_host(built, kind, flags)
+    assert_bytes_equal(got.all_bytes(), want, "pageable -> pageable")
+    pdst = torch.empty(enc.bound(built, flags) + 16, dtype=torch.uint8).pin_memory()
+    got_p = enc.encode_host(built, kind, flags, dst=pdst.numpy())
+    assert_bytes_equal(got_p.all_bytes(), want, "pageable -> pinned")
+    # pageable wire -> pageable pool, pinned pool
+    st_o, dec_o = ob.decode_bytes(want, kind)
+    wire = np.array(got.wire[: got.total], copy=True)
+    d = dec.decode_host(wire, got.offsets, got.lengths, kind)
+    pool = np.empty(d.pool_bytes + 64, np.uint8)
+    d.close()
+    for pool_buf in (pool, torch.empty(pool.size, dtype=torch.uint8).pin_memory().numpy()):
+        pool_buf[:] = 0xEE
+        d = dec.decode_host_into(wire, got.offsets, got.lengths, kind, pool_buf)
+        helpers.assert_same_decoded(dec_o, d.messages(), "request", "pageable wire decode")
+        d.close()
+
+
 def test_chunked_pinned_decode_with_bad_messages_and_prefix(codec):
     """The chunked copy-engine path of tfs_decode_host_into (pinned wire >= 8 MB, walk reading host memory while the wire
     is still arriving) with the gRPC prefix and with malformed messages between good ones."""
