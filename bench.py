@@ -306,6 +306,33 @@ def run_ours(args):
     pcie_bidir = pcie_ceiling()
     e2e_moved_GBps = world * e2e_steps * (h2d + d2h) / e2e_s / 1e9
 
+    # ---- the same calls with PAGEABLE buffers (what prost's Vecs and tonic's BytesMut are): the library's pinned ring and
+    #      staging threads are inside the timed region; 8 requests per variant (side figure)
+    e2e_pageable = None
+    if not args.no_extras:
+        Rp = min(8, Re)
+        p_rows = [np.array(h_src[i].numpy(), copy=True) for i in range(Rp)]
+        p_built = {v: tfs.build_batch(c2_requests(p_rows, v, Rp), kind) for v in VARIANTS}
+        p_wire = np.empty(enc.bound(p_built["float_val"], flags) + 4096, np.uint8)
+        p_pool = np.empty(Rp * (C2_ELEMS * 4 + 4096), np.uint8)
+
+        def pageable_step():
+            n = 0
+            for v in VARIANTS:
+                eb = enc.encode_host(p_built[v], kind, flags, dst=p_wire)
+                dec.decode_host_into(p_wire[: eb.total], eb.offsets_np, eb.lengths_np, kind, p_pool).close()
+                n += 2 * int(eb.lengths_np.sum())
+            return n
+
+        pageable_step()
+        barrier()
+        t_start = time.perf_counter()
+        nb = 0
+        for _ in range(3):
+            nb += pageable_step()
+        e2e_pageable = world * nb / max_over_ranks(time.perf_counter() - t_start) / 1e9
+        del p_rows, p_built, p_wire, p_pool
+
     # ---- the same work through the engine: two lanes (context + stream + worker thread each) on this GPU, the two variants in
     #      flight at once, so that one job's upload runs under the other's download (side figure; `e2e` above is one call at a time)
     e2e_engine = None
@@ -380,6 +407,7 @@ def run_ours(args):
         "dtype": "u8", "data": "synthetic", "config": config_of(args, world), "clocks": clocks,
         "e2e": {"value": round(world * e2e_bytes / e2e_s / 1e9, 3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "requests_per_variant_per_gpu": Re, "steps": e2e_steps, "engine_two_lanes_GBps": round(e2e_engine, 3) if e2e_engine else None,
+                "pageable_buffers_GBps": round(e2e_pageable, 3) if e2e_pageable else None,
                 "pcie_bidir_measured_GBps": round(pcie_bidir, 1), "pcie_moved_GBps": round(e2e_moved_GBps, 1),
                 "frac_of_pcie_bidir": round(e2e_moved_GBps / pcie_bidir, 3) if pcie_bidir else None,
                 "path": "tfs_encode_host + tfs_decode_host_into, pinned host buffers"},
