@@ -89,6 +89,20 @@ struct PredictResponse {
   std::optional<ModelSpec> model_spec;
 };
 
+// ---- the metadata call (reference src/lib.rs:300-312; get_model_metadata.proto:16-35) ----
+struct Any {  // prost_types::Any: the value stays opaque bytes (the reference never unpacks the SignatureDefMap)
+  std::string type_url;
+  std::vector<uint8_t> value;
+};
+struct GetModelMetadataRequest {
+  std::optional<ModelSpec> model_spec;
+  std::vector<std::string> metadata_field;
+};
+struct GetModelMetadataResponse {
+  std::optional<ModelSpec> model_spec;
+  std::vector<std::pair<std::string, Any>> metadata;  // HashMap<String, Any>: a repeated key replaces the earlier entry
+};
+
 // ---- Classify / Regress inputs: `Payload`, `impl From<Payload> for Feature`, `build_input` (reference src/lib.rs:413-431,
 //      497-571) ----
 struct Payload {  // enum Payload { Bytes(Vec<Vec<u8>>), Ints(Vec<i64>), Floats(Vec<f32>) }
@@ -394,6 +408,11 @@ class GpuEncoder {
     d.add_message(TFS_MSG_PREDICT_RESPONSE, item.model_spec, item.outputs, nullptr);
     run(d, dst, nullptr);
   }
+  void encode(const GetModelMetadataRequest& item, std::vector<uint8_t>& dst) const {
+    detail::Described d;
+    d.add_message(TFS_MSG_METADATA_REQUEST, item.model_spec, TensorMap{}, &item.metadata_field);
+    run(d, dst, nullptr);
+  }
   // Classify / Regress: what `build_input` returns, and the request around it
   void encode(const Input& item, std::vector<uint8_t>& dst) const {
     detail::Described d;
@@ -455,6 +474,33 @@ class GpuDecoder {
       for (uint32_t i = 0; i < m.n_tensors; ++i) {
         const tfs_tensor_out_t& t = v.tensors[m.first_tensor + i];
         detail::insert_last_wins(r.outputs, detail::text(v, t.key), detail::tensor_from(t, pool));
+      }
+    });
+    src.clear();
+    return r;
+  }
+  // GetModelMetadataResponse: every map entry comes back as a record with the key and string_val = [type_url, value]
+  std::optional<GetModelMetadataResponse> decode_metadata(std::vector<uint8_t>& src) const {
+    GetModelMetadataResponse r;
+    decode_one(src, TFS_MSG_METADATA_RESPONSE, [&](const tfs_decoded_view_t& v, const tfs_msg_out_t& m, const uint8_t* pool) {
+      r.model_spec = detail::spec_from(v, m);
+      for (uint32_t i = 0; i < m.n_tensors; ++i) {
+        const tfs_tensor_out_t& t = v.tensors[m.first_tensor + i];
+        TensorProto parts = detail::tensor_from(t, pool);
+        Any a;
+        if (parts.string_val.size() == 2) {
+          a.type_url.assign(parts.string_val[0].begin(), parts.string_val[0].end());
+          a.value = std::move(parts.string_val[1]);
+        }
+        std::string key = detail::text(v, t.key);
+        bool replaced = false;
+        for (auto& kv : r.metadata)
+          if (kv.first == key) {
+            kv.second = std::move(a);
+            replaced = true;
+            break;
+          }
+        if (!replaced) r.metadata.emplace_back(std::move(key), std::move(a));
       }
     });
     src.clear();

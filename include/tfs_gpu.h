@@ -143,7 +143,16 @@ enum {
    * it belongs to (ascending inside the message), and tfs_msg_desc_t.n_filters = number of Examples in the list
    * (first_filter unused; an Example without features is an empty map). */
   TFS_MSG_INPUT = 3,            /* input.proto:77-82 */
-  TFS_MSG_CLASSIFY_REQUEST = 4  /* classification.proto:33-40 = regression.proto:23-30: model_spec = 1, input = 2 */
+  TFS_MSG_CLASSIFY_REQUEST = 4, /* classification.proto:33-40 = regression.proto:23-30: model_spec = 1, input = 2 */
+  /* The metadata call of the reference (src/lib.rs:300-312), get_model_metadata.proto:16-35.
+   * REQUEST (encode and decode): model_spec = 1, repeated string metadata_field = 2 - the message's `filters`; no tensors.
+   * RESPONSE (decode only - the client never builds one): model_spec = 1, map<string, google.protobuf.Any> metadata = 2.
+   * Every map entry comes back as ONE tensor record: key = the map key, dtype 0, no shape, and a string_val of exactly
+   * two elements, [Any.type_url, Any.value].  prost keeps Any.value as opaque bytes (the SignatureDefMap inside is not
+   * parsed by the reference either); type_url is a `string` and must be UTF-8; repeated occurrences merge as prost
+   * merges them (the last type_url / value of an entry wins). */
+  TFS_MSG_METADATA_REQUEST = 5,
+  TFS_MSG_METADATA_RESPONSE = 6
 };
 
 enum { TFS_VERSION_NONE = 0, TFS_VERSION_NUMBER = 1, TFS_VERSION_LABEL = 2 }; /* model.proto:22-28 */

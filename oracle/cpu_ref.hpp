@@ -144,6 +144,26 @@ struct PredictResponse {
   std::optional<ModelSpec> model_spec;  // tag 2
 };
 
+// ---- the metadata call (src/lib.rs:300-312; get_model_metadata.proto:16-35, google/protobuf/any.proto) ----
+struct Any {               // prost_types::Any
+  std::string type_url;    // tag 1 (string: UTF-8 checked on decode)
+  std::vector<uint8_t> value;  // tag 2 (bytes: opaque - the reference never unpacks the SignatureDefMap inside)
+};
+struct GetModelMetadataRequest {
+  std::optional<ModelSpec> model_spec;      // tag 1
+  std::vector<std::string> metadata_field;  // tag 2
+};
+struct GetModelMetadataResponse {
+  std::optional<ModelSpec> model_spec;                 // tag 1
+  std::vector<std::pair<std::string, Any>> metadata;   // tag 2: map<string, Any>, wire order kept
+};
+size_t encoded_len(const GetModelMetadataRequest& m);
+void encode_raw(const GetModelMetadataRequest& m, BufMut& buf);
+size_t encoded_len(const GetModelMetadataResponse& m);
+void encode_raw(const GetModelMetadataResponse& m, BufMut& buf);
+bool decode(const uint8_t* p, size_t n, GetModelMetadataRequest* out, DecodeError* err);
+bool decode(const uint8_t* p, size_t n, GetModelMetadataResponse* out, DecodeError* err);
+
 // ---- Example / Features / Input (feature.proto:65-87, example.proto:88-90, input.proto:15-82, classification.proto:33-40;
 //      built by build_input + `impl From<Payload> for Feature`, src/lib.rs:413-431, 514-571) ----
 struct Feature {

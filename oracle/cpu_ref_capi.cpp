@@ -224,8 +224,10 @@ struct AnyMsg {
   PredictResponse resp;
   Input input;
   ClassificationRequest classify;
+  GetModelMetadataRequest meta_req;
   size_t encoded_len() const {
     switch (kind) {
+      case TFS_MSG_METADATA_REQUEST: return cpu_ref::encoded_len(meta_req);
       case TFS_MSG_TENSOR_PROTO: return cpu_ref::encoded_len(tensor);
       case TFS_MSG_PREDICT_REQUEST: return cpu_ref::encoded_len(req);
       case TFS_MSG_INPUT: return cpu_ref::encoded_len(input);
@@ -235,6 +237,7 @@ struct AnyMsg {
   }
   void prost_encode(std::vector<uint8_t>& dst) const {
     switch (kind) {
+      case TFS_MSG_METADATA_REQUEST: prost_encoder_encode(meta_req, dst); break;
       case TFS_MSG_TENSOR_PROTO: prost_encoder_encode(tensor, dst); break;
       case TFS_MSG_PREDICT_REQUEST: prost_encoder_encode(req, dst); break;
       case TFS_MSG_INPUT: prost_encoder_encode(input, dst); break;
@@ -316,6 +319,12 @@ bool build_msg(const tfs_batch_t& b, const tfs_msg_desc_t& m, AnyMsg* out) {
     if (m.has_model_spec) out->classify.model_spec = build_model_spec(m);
     out->classify.input = Input{};
     return build_input(b, m, &*out->classify.input);
+  }
+  if (m.kind == TFS_MSG_METADATA_REQUEST) {  // model_spec + metadata_field (the message's filters); decode-only kinds are refused
+    if (m.n_tensors) return false;
+    if (m.has_model_spec) out->meta_req.model_spec = build_model_spec(m);
+    for (uint32_t i = 0; i < m.n_filters; ++i) out->meta_req.metadata_field.push_back(str(b.filters[m.first_filter + i]));
+    return true;
   }
   if (m.kind != TFS_MSG_PREDICT_REQUEST && m.kind != TFS_MSG_PREDICT_RESPONSE) return false;
   TensorMap map;
@@ -487,6 +496,26 @@ void decode_one(Decoded& d, uint32_t index, const uint8_t* p, uint64_t n, int32_
           if (ok && !emit_tensor(d, index, kv.first, kv.second, flags)) { ok = false; err = {Err::Unsupported, 0}; }
         for (auto& s : r.output_filter) d.filters.push_back(add_string(d, s));
       }
+    } else if (kind == TFS_MSG_METADATA_REQUEST) {
+      GetModelMetadataRequest r;
+      ok = decode(p, n, &r, &err);
+      if (ok) {
+        emit_model_spec(d, mo, r.model_spec);
+        for (auto& s : r.metadata_field) d.filters.push_back(add_string(d, s));
+      }
+    } else if (kind == TFS_MSG_METADATA_RESPONSE) {
+      // every metadata entry as the library hands it back: a record with the map key and string_val = [type_url, value]
+      GetModelMetadataResponse r;
+      ok = decode(p, n, &r, &err);
+      if (ok) {
+        emit_model_spec(d, mo, r.model_spec);
+        for (auto& kv : r.metadata) {
+          TensorProto t;
+          t.string_val.emplace_back(kv.second.type_url.begin(), kv.second.type_url.end());
+          t.string_val.push_back(kv.second.value);
+          if (ok && !emit_tensor(d, index, kv.first, t, flags)) { ok = false; err = {Err::Unsupported, 0}; }
+        }
+      }
     } else {
       PredictResponse r;
       ok = decode(p, n, &r, &err);
@@ -597,7 +626,7 @@ int32_t oracle_decode(const uint8_t* wire, const uint64_t* msg_off, const uint64
   if (!out || (n_msgs && (!msg_off || !msg_len))) return TFS_ERR_INVALID_ARG;
   static const uint8_t kEmpty[1] = {0};
   if (!wire) wire = kEmpty;  // a batch of zero-length messages
-  if (msg_kind < 0 || msg_kind > 2) return TFS_ERR_INVALID_ARG;
+  if ((msg_kind < 0 || msg_kind > 2) && msg_kind != TFS_MSG_METADATA_REQUEST && msg_kind != TFS_MSG_METADATA_RESPONSE) return TFS_ERR_INVALID_ARG;
   Decoded* d = new Decoded();
   for (uint32_t i = 0; i < n_msgs; ++i) decode_one(*d, i, wire + msg_off[i], msg_len[i], msg_kind, flags);
   *out = reinterpret_cast<oracle_decoded_t*>(d);

@@ -9,7 +9,7 @@ from . import abi, messages, workloads, _lib, codec, sharding  # noqa: F401  (al
 from ._lib import TfsError  # noqa: F401
 from .codec import Coalescer, Engine, GpuCodec, GpuContext, GpuDecoder, GpuEncoder, Slab  # noqa: F401
 from .messages import (  # noqa: F401
-    ClassificationRequest, Feature, Input, ModelSpec, Payload, PredictRequest, PredictResponse, Ragged, TensorProto, TensorShapeProto, build_batch, ragged_block,
+    AnyProto, ClassificationRequest, Feature, GetModelMetadataRequest, GetModelMetadataResponse, Input, ModelSpec, Payload, PredictRequest, PredictResponse, Ragged, TensorProto, TensorShapeProto, build_batch, ragged_block,
     messages_from_view, replicate_batch, BuiltBatch, ResourceHandleProto, VariantTensorDataProto, resource_handle_body, variant_body,
     parse_resource_handle, parse_variant,
 )

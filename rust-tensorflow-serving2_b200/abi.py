@@ -71,6 +71,7 @@ TYPE_NUMPY = {T_U8: "u1", T_I8: "i1", T_U16: "<u2", T_I16: "<i2", T_I32: "<i4", 
 
 OP_NONE, OP_DIV, OP_MUL = 0, 1, 2
 MSG_TENSOR_PROTO, MSG_PREDICT_REQUEST, MSG_PREDICT_RESPONSE, MSG_INPUT, MSG_CLASSIFY_REQUEST = 0, 1, 2, 3, 4
+MSG_METADATA_REQUEST, MSG_METADATA_RESPONSE = 5, 6  # get_model_metadata.proto:16-35 (the response is decode only)
 KIND_BYTES_LIST, KIND_FLOAT_LIST, KIND_INT64_LIST = 1, 2, 3  # Feature.kind members (feature.proto:79-81)
 VERSION_NONE, VERSION_NUMBER, VERSION_LABEL = 0, 1, 2
 

@@ -720,6 +720,57 @@ struct Walker {
     }
     return loop_end(rend);
   }
+  // hash_map::merge of one `metadata` entry of a GetModelMetadataResponse (get_model_metadata.proto:29): key = 1 (string),
+  // value = 2 (google.protobuf.Any { string type_url = 1; bytes value = 2 }).  The entry becomes a tensor record whose
+  // string_val has two elements, [type_url, value]; repeated occurrences merge as prost merges them (the last one wins),
+  // so the two spans are emitted when the entry ends.
+  __device__ bool any_entry(uint32_t ctx) {
+    uint64_t rend;
+    if (!loop_begin(&rend)) return false;
+    begin_tensor();
+    uint64_t url_off = 0, url_len = 0, val_off = 0, val_len = 0;
+    while (pos < rend) {
+      uint32_t t2, w2;
+      if (!key(&t2, &w2)) return false;
+      if (t2 == 1) {
+        tfs_span_t sp;
+        if (!string_field(w2, &sp)) return false;
+        if (FILL) T.tensors[cur_w].key = sp;
+      } else if (t2 == 2) {  // message::merge of the Any
+        if (!check_wt(WT_LEN, w2)) return false;
+        if (ctx == 0) return fail(TFS_ERR_RECURSION);
+        uint64_t aend;
+        if (!loop_begin(&aend)) return false;
+        while (pos < aend) {
+          uint32_t t3, w3;
+          if (!key(&t3, &w3)) return false;
+          if (t3 == 1 || t3 == 2) {
+            if (!check_wt(WT_LEN, w3)) return false;
+            uint64_t len;
+            if (!varint(&len)) return false;
+            if (len > end - pos) return fail(TFS_ERR_BUFFER_UNDERFLOW);
+            const uint64_t off = pos;
+            pos += len;
+            if (t3 == 1) {
+              if (!utf8_ok([&](uint32_t i) { return byte_at(off + i); }, static_cast<uint32_t>(len))) return fail(TFS_ERR_UTF8);
+              url_off = off, url_len = len;
+            } else {
+              val_off = off, val_len = len;
+            }
+          } else if (!skip(w3, t3, ctx - 2)) {  // (the Any's own fields are merged two levels below the map field)
+            return false;
+          }
+        }
+        if (!loop_end(aend)) return false;
+      } else if (!skip(w2, t2, ctx - 1)) {
+        return false;
+      }
+    }
+    if (!loop_end(rend)) return false;
+    add_span(slot_of(8), SC_STR, url_off ? url_off : beg, url_len, 1, 1);  // (an absent field is an empty element; any valid offset)
+    add_span(slot_of(8), SC_STR, val_off ? val_off : beg, val_len, 1, 1);
+    return true;
+  }
   __device__ bool model_spec(uint32_t wt, uint32_t ctx, tfs_msg_out_t* mo) {
     if (!check_wt(WT_LEN, wt)) return false;
     uint64_t rend;
@@ -796,6 +847,18 @@ struct Walker {
         if (tag == 1) ok = model_spec(wt, 100, mo);
         else if (tag == 2) ok = map_entry(100);
         else if (tag == 3) {
+          tfs_span_t sp;
+          ok = string_field(wt, &sp);
+          if (ok) {
+            if (FILL && n_filters < cap_f) T.filters[n_filters] = sp;
+            if (FILL && n_filters >= cap_f) ovf = true;
+            n_filters++;
+          }
+        } else ok = skip(wt, tag, 100);
+      } else if (T.msg_kind == TFS_MSG_METADATA_REQUEST || T.msg_kind == TFS_MSG_METADATA_RESPONSE) {
+        if (tag == 1) ok = model_spec(wt, 100, mo);
+        else if (tag == 2 && T.msg_kind == TFS_MSG_METADATA_RESPONSE) ok = any_entry(100);
+        else if (tag == 2) {  // repeated string metadata_field
           tfs_span_t sp;
           ok = string_field(wt, &sp);
           if (ok) {
@@ -1511,7 +1574,8 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
                                 const uint64_t* msg_len, uint32_t n_msgs, int32_t msg_kind, uint32_t flags, void* pool_dev,
                                 uint64_t pool_capacity, tfs_decoded** out, const void* walk_wire_dev) {
   TFS_CUDA(ctx, cudaSetDevice(ctx->device));
-  if (msg_kind < TFS_MSG_TENSOR_PROTO || msg_kind > TFS_MSG_PREDICT_RESPONSE) return set_err(ctx, TFS_ERR_INVALID_ARG, "bad msg_kind");
+  if ((msg_kind < TFS_MSG_TENSOR_PROTO || msg_kind > TFS_MSG_PREDICT_RESPONSE) && msg_kind != TFS_MSG_METADATA_REQUEST && msg_kind != TFS_MSG_METADATA_RESPONSE)
+    return set_err(ctx, TFS_ERR_INVALID_ARG, "bad msg_kind");
   if (reinterpret_cast<uintptr_t>(pool_dev) & 15u) return set_err(ctx, TFS_ERR_INVALID_ARG, "the value pool must be 16-byte aligned (it holds typed arrays)");
   tfs_decoded* dec = new (std::nothrow) tfs_decoded();
   if (!dec) return TFS_ERR_NOMEM;

@@ -309,6 +309,11 @@ __device__ void emit_message(Sink& s, const EncTables& T, uint32_t mi, OnBody on
     emit_tensor_body(s, T, T.tensors[m.first_tensor], on_body);
     return;
   }
+  if (m.kind == TFS_MSG_METADATA_REQUEST) {  // get_model_metadata.proto:16-23: model_spec = 1, repeated string metadata_field = 2
+    if (m.has_model_spec) emit_model_spec(s, T, m, 1, T.spec_len[mi]);
+    for (uint32_t i = 0; i < m.n_filters; ++i) emit_string(s, 2, T.strings, T.filters[m.first_filter + i]);
+    return;
+  }
   const uint32_t map_field = m.kind == TFS_MSG_PREDICT_REQUEST ? 2u : 1u;
   const uint32_t spec_field = m.kind == TFS_MSG_PREDICT_REQUEST ? 1u : 2u;
   if (m.has_model_spec && spec_field == 1u) emit_model_spec(s, T, m, 1, T.spec_len[mi]);
@@ -725,7 +730,9 @@ void compile_range(const tfs_batch_t* b, uint32_t flags, Compiled* c, uint32_t m
     const tfs_msg_desc_t& m = b->msgs[mi];
     EncMsg& o = c->msgs[mi];
     std::memset(&o, 0, sizeof(o));
-    if (m.kind < TFS_MSG_TENSOR_PROTO || m.kind > TFS_MSG_CLASSIFY_REQUEST) RANGE_FAIL("bad message kind");
+    if (m.kind < TFS_MSG_TENSOR_PROTO || m.kind > TFS_MSG_METADATA_RESPONSE) RANGE_FAIL("bad message kind");
+    if (m.kind == TFS_MSG_METADATA_RESPONSE) RANGE_FAIL("GetModelMetadataResponse is decode only");
+    if (m.kind == TFS_MSG_METADATA_REQUEST && m.n_tensors) RANGE_FAIL("GetModelMetadataRequest carries no tensors");
     const bool input_kind = m.kind == TFS_MSG_INPUT || m.kind == TFS_MSG_CLASSIFY_REQUEST;  // n_filters counts Examples there
     if (static_cast<uint64_t>(m.first_tensor) + m.n_tensors > b->n_tensors) RANGE_FAIL("tensor range out of bounds");
     if (!input_kind && static_cast<uint64_t>(m.first_filter) + m.n_filters > b->n_filters) RANGE_FAIL("filter range out of bounds");

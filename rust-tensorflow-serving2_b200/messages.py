@@ -80,6 +80,27 @@ class ModelSpec:
 
 
 @dataclass
+class AnyProto:
+    """google.protobuf.Any as prost_types::Any holds it: the value stays opaque bytes."""
+    type_url: str = ""
+    value: bytes = b""
+
+
+@dataclass
+class GetModelMetadataRequest:
+    """get_model_metadata.proto:16-23 (built by the reference at src/lib.rs:305-308)."""
+    model_spec: Optional[ModelSpec] = None
+    metadata_field: List[str] = field(default_factory=list)
+
+
+@dataclass
+class GetModelMetadataResponse:
+    """get_model_metadata.proto:25-35; `metadata` in wire order (the reference keeps a HashMap: the last key wins)."""
+    model_spec: Optional[ModelSpec] = None
+    metadata: List[Tuple[str, AnyProto]] = field(default_factory=list)
+
+
+@dataclass
 class PredictRequest:
     model_spec: Optional[ModelSpec] = None
     inputs: List[Tuple[str, TensorProto]] = field(default_factory=list)
@@ -307,8 +328,10 @@ def build_batch(messages, kind) -> BuiltBatch:
             continue
         if kind == abi.MSG_TENSOR_PROTO:
             add_tensor("", m)
+        elif kind == abi.MSG_METADATA_RESPONSE:
+            raise ValueError("GetModelMetadataResponse is decode only")
         else:
-            entries = m.inputs if kind == abi.MSG_PREDICT_REQUEST else m.outputs
+            entries = [] if kind == abi.MSG_METADATA_REQUEST else m.inputs if kind == abi.MSG_PREDICT_REQUEST else m.outputs
             for name, t in entries:
                 add_tensor(name, t)
             if m.model_spec is not None:
@@ -322,8 +345,8 @@ def build_batch(messages, kind) -> BuiltBatch:
                 elif ms.version_label is not None:
                     md.version_choice = abi.VERSION_LABEL
                     md.version_label = _mk_str(ms.version_label, keep)
-            if kind == abi.MSG_PREDICT_REQUEST:
-                for s in m.output_filter:
+            if kind in (abi.MSG_PREDICT_REQUEST, abi.MSG_METADATA_REQUEST):
+                for s in (m.output_filter if kind == abi.MSG_PREDICT_REQUEST else m.metadata_field):
                     flt_l.append(_mk_str(s, keep))
         md.n_tensors = len(ten_l) - md.first_tensor
         md.n_filters = len(flt_l) - md.first_filter
@@ -555,6 +578,16 @@ def messages_from_view(view: abi.DecodedView, pool: np.ndarray, kind: int) -> Li
         elif kind == abi.MSG_PREDICT_REQUEST:
             flt = [_span_bytes(strings, view.filters[mo.first_filter + j]).decode("utf-8") for j in range(mo.n_filters)]
             msg = PredictRequest(ms, entries, flt)
+        elif kind == abi.MSG_METADATA_REQUEST:
+            flt = [_span_bytes(strings, view.filters[mo.first_filter + j]).decode("utf-8") for j in range(mo.n_filters)]
+            msg = GetModelMetadataRequest(ms, flt)
+        elif kind == abi.MSG_METADATA_RESPONSE:
+            # one record per map entry: key, string_val = [type_url, value]
+            meta = []
+            for key, t in entries:
+                url, value = (list(t.string_val) + [b"", b""])[:2]
+                meta.append((key, AnyProto(bytes(url).decode("utf-8"), bytes(value))))
+            msg = GetModelMetadataResponse(ms, meta)
         else:
             msg = PredictResponse(entries, ms)
         out.append(DecodedMessage(0, 0, msg))

@@ -166,6 +166,21 @@ int main() {
   auto d2 = dec.decode(dup);
   CHECK(d2 && d2->outputs.size() == 1 && d2->outputs[0].second.dtype == 3);
 
+  // the metadata call (src/lib.rs:300-312): the request the reference builds, byte for byte (upb and the oracle agree on
+  // these bytes, tests/test_metadata_messages.py), and a response with one signature_def entry
+  GetModelMetadataRequest mreq;
+  mreq.model_spec = ModelSpec{"resnet", 3, std::nullopt, ""};
+  mreq.metadata_field = {"signature_def"};
+  std::vector<uint8_t> mw;
+  enc.encode(mreq, mw);
+  CHECK(hex(mw) == "0a0c0a067265736e657412020803120d7369676e61747572655f646566");
+  std::vector<uint8_t> mresp = {0x0a, 0x03, 0x0a, 0x01, 0x6d, 0x12, 0x17, 0x0a, 0x0d, 's', 'i', 'g', 'n', 'a', 't', 'u', 'r', 'e', '_', 'd', 'e', 'f',
+                                0x12, 0x06, 0x0a, 0x01, 'u', 0x12, 0x01, 0x7f};
+  auto md = dec.decode_metadata(mresp);
+  CHECK(md && md->model_spec && md->model_spec->name == "m" && md->metadata.size() == 1);
+  CHECK(md && md->metadata.size() == 1 && md->metadata[0].first == "signature_def" && md->metadata[0].second.type_url == "u" &&
+        md->metadata[0].second.value == std::vector<uint8_t>{0x7f});
+
   std::printf(failures ? "FAILED: %d checks\n" : "cpp codec ok\n", failures);
   return failures ? 1 : 0;
 }

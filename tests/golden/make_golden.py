@@ -93,6 +93,45 @@ def build_predict_classes():
 PredictRequestPB, PredictResponsePB = build_predict_classes()
 
 
+def build_metadata_classes():
+    """GetModelMetadataRequest / GetModelMetadataResponse (protos/tensorflow_serving/apis/get_model_metadata.proto:16-35 of the
+    reference), rebuilt at run time: model_spec = 1; repeated string metadata_field = 2 / map<string, google.protobuf.Any>
+    metadata = 2."""
+    from google.protobuf import any_pb2  # noqa: F401  (registers google/protobuf/any.proto in the default pool)
+    pool = descriptor_pool.Default()
+    g = descriptor_pb2.FileDescriptorProto()
+    g.name = "golden/tfs_get_model_metadata.proto"
+    g.package = "tensorflow.serving"
+    g.syntax = "proto3"
+    g.dependency.extend(["google/protobuf/any.proto", "golden/tfs_model.proto"])
+    req = g.message_type.add()
+    req.name = "GetModelMetadataRequest"
+    fd = req.field.add()
+    fd.name, fd.number, fd.type, fd.label, fd.type_name = "model_spec", 1, 11, 1, ".tensorflow.serving.ModelSpec"
+    fd = req.field.add()
+    fd.name, fd.number, fd.type, fd.label = "metadata_field", 2, 9, 3
+    resp = g.message_type.add()
+    resp.name = "GetModelMetadataResponse"
+    e = resp.nested_type.add()
+    e.name = "MetadataEntry"
+    e.options.map_entry = True
+    k = e.field.add()
+    k.name, k.number, k.type, k.label = "key", 1, 9, 1
+    v = e.field.add()
+    v.name, v.number, v.type, v.label, v.type_name = "value", 2, 11, 1, ".google.protobuf.Any"
+    fd = resp.field.add()
+    fd.name, fd.number, fd.type, fd.label, fd.type_name = "model_spec", 1, 11, 1, ".tensorflow.serving.ModelSpec"
+    fd = resp.field.add()
+    fd.name, fd.number, fd.type, fd.label, fd.type_name = "metadata", 2, 11, 3, ".tensorflow.serving.GetModelMetadataResponse.MetadataEntry"
+    pool.Add(g)
+    get = message_factory.GetMessageClass
+    return (get(pool.FindMessageTypeByName("tensorflow.serving.GetModelMetadataRequest")),
+            get(pool.FindMessageTypeByName("tensorflow.serving.GetModelMetadataResponse")))
+
+
+MetadataRequestPB, MetadataResponsePB = build_metadata_classes()
+
+
 # ---- plain-dict message descriptions <-> upb messages ---------------------------------------------
 def build_example_classes():
     """Feature / Features / Example (feature.proto:65-87, example.proto:88-90), ExampleList / Input (input.proto:15-82) and
