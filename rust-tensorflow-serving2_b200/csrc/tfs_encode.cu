@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <system_error>
 #include <thread>
 
 #include "tfs_device.cuh"
@@ -811,6 +812,22 @@ void compile_range(const tfs_batch_t* b, uint32_t flags, Compiled* c, uint32_t m
 #undef RANGE_FAIL
 }
 
+// fn(k) for k in [0, n) on n - 1 short-lived threads and the calling one; a thread that cannot be started is run inline
+template <class F>
+void run_ranges(uint32_t n, F fn) {
+  std::vector<std::thread> crew;
+  crew.reserve(n);
+  for (uint32_t k = 1; k < n; ++k) {
+    try {
+      crew.emplace_back([&fn, k] { fn(k); });
+    } catch (const std::system_error&) {
+      fn(k);
+    }
+  }
+  fn(0);
+  for (std::thread& t : crew) t.join();
+}
+
 // a batch of tiny messages is host work: above this many messages the descriptors are compiled on
 // several threads
 constexpr uint32_t kParallelCompileMsgs = 8192;
@@ -851,9 +868,14 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
   for (uint32_t i = 0; i < b->n_filters; ++i) c->filters[i] = add_str(c->strings, b->filters[i]);
   uint32_t n_workers = 1;
   tr.mark("alloc");
-  if (b->n_msgs >= kParallelCompileMsgs)
-    n_workers = std::min<uint32_t>({kCompileThreadsMax, std::max(1u, std::thread::hardware_concurrency() / 2), b->n_msgs / (kParallelCompileMsgs / 2)});
-  if (const char* e = std::getenv("TFS_COMPILE_THREADS")) n_workers = std::max(1, std::atoi(e));
+  // (the work is per descriptor: 8 192 one-tensor requests and 64 ClassificationRequests of 192 features weigh the same)
+  const uint64_t n_desc = static_cast<uint64_t>(b->n_msgs) + b->n_tensors + b->n_fields;
+  // starting a thread costs ~0.1 ms, a descriptor ~30 ns: 64 ClassificationRequests of 192 features (25 k descriptors,
+  // 0.4 ms) were measured SLOWER on two threads (0.6 ms), so the work has to be a few milliseconds before it is split
+  if (n_desc >= 12ull * kParallelCompileMsgs && b->n_msgs >= 2)
+    n_workers = std::min<uint32_t>({kCompileThreadsMax, std::max(1u, std::thread::hardware_concurrency() / 2),
+                                    static_cast<uint32_t>(n_desc / (6ull * kParallelCompileMsgs)), b->n_msgs});
+  if (const char* e = std::getenv("TFS_COMPILE_THREADS")) n_workers = std::min<uint32_t>(std::max(1, std::atoi(e)), std::max(1u, b->n_msgs));
   if (n_workers <= 1) {
     c->strings.reserve(c->strings.size() + 64ull * b->n_msgs + 16ull * b->n_tensors);
     RangeOut r;
@@ -863,14 +885,11 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
     c->has_input = r.has_input;
   } else {
     std::vector<RangeOut> outs(n_workers);
-    std::vector<std::thread> crew;
     auto first_of = [&](uint32_t k) { return static_cast<uint32_t>(static_cast<uint64_t>(b->n_msgs) * k / n_workers); };
-    for (uint32_t k = 0; k < n_workers; ++k)
-      crew.emplace_back([&, k] {
-        outs[k].strings.reserve(64ull * (first_of(k + 1) - first_of(k)));
-        compile_range(b, flags, c, first_of(k), first_of(k + 1), outs[k].strings, field_bound, tensor_used, field_used, &outs[k]);
-      });
-    for (std::thread& t : crew) t.join();
+    run_ranges(n_workers, [&](uint32_t k) {
+      outs[k].strings.reserve(64ull * (first_of(k + 1) - first_of(k)));
+      compile_range(b, flags, c, first_of(k), first_of(k + 1), outs[k].strings, field_bound, tensor_used, field_used, &outs[k]);
+    });
     for (uint32_t k = 0; k < n_workers; ++k)  // the error of the earliest message, as the one-thread walk reports it
       if (outs[k].fail) return set_err(ctx, TFS_ERR_INVALID_ARG, outs[k].fail);
     // join the string blocks and move every name reference of a range by where its block landed
@@ -884,21 +903,18 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
     }
     if (total > 0xFFFFFFF0ull) return set_err(ctx, TFS_ERR_TOO_LARGE, "names of the batch exceed 4 GiB");
     c->strings.resize(total);
-    crew.clear();
-    for (uint32_t k = 0; k < n_workers; ++k)
-      crew.emplace_back([&, k] {
-        if (!outs[k].strings.empty()) std::memcpy(c->strings.data() + base[k], outs[k].strings.data(), outs[k].strings.size());
-        const uint32_t d = base[k];
-        for (uint32_t mi = first_of(k); mi < first_of(k + 1); ++mi) {
-          EncMsg& o = c->msgs[mi];
-          if (o.model_name.len) o.model_name.off += d;
-          if (o.signature_name.len) o.signature_name.off += d;
-          if (o.version_label.len) o.version_label.off += d;
-          for (uint32_t ti = o.first_tensor; ti < o.first_tensor + o.n_tensors; ++ti)
-            if (c->tensors[ti].name.len) c->tensors[ti].name.off += d;
-        }
-      });
-    for (std::thread& t : crew) t.join();
+    run_ranges(n_workers, [&](uint32_t k) {
+      if (!outs[k].strings.empty()) std::memcpy(c->strings.data() + base[k], outs[k].strings.data(), outs[k].strings.size());
+      const uint32_t d = base[k];
+      for (uint32_t mi = first_of(k); mi < first_of(k + 1); ++mi) {
+        EncMsg& o = c->msgs[mi];
+        if (o.model_name.len) o.model_name.off += d;
+        if (o.signature_name.len) o.signature_name.off += d;
+        if (o.version_label.len) o.version_label.off += d;
+        for (uint32_t ti = o.first_tensor; ti < o.first_tensor + o.n_tensors; ++ti)
+          if (c->tensors[ti].name.len) c->tensors[ti].name.off += d;
+      }
+    });
   }
   // descriptors no message refers to: the block is reused, give them a defined (empty) record
   for (uint32_t ti = 0; ti < b->n_tensors; ++ti)
@@ -976,15 +992,12 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
     }
     return at;
   };
-  const uint32_t tile_workers = b->n_fields >= 8 * kParallelCompileMsgs ? n_workers : 1;
+  const uint32_t tile_workers = b->n_fields >= 8 * kParallelCompileMsgs ? std::min<uint32_t>(n_workers, b->n_fields) : 1;
   auto field_first = [&](uint32_t k) { return static_cast<uint32_t>(static_cast<uint64_t>(b->n_fields) * k / tile_workers); };
   std::vector<TileSums> at(tile_workers + 1);
   if (tile_workers > 1) {
     std::vector<TileSums> part(tile_workers);
-    std::vector<std::thread> crew;
-    for (uint32_t k = 0; k < tile_workers; ++k)
-      crew.emplace_back([&, k] { part[k] = tile_range_pass(field_first(k), field_first(k + 1), TileSums{}, false); });
-    for (std::thread& t : crew) t.join();
+    run_ranges(tile_workers, [&](uint32_t k) { part[k] = tile_range_pass(field_first(k), field_first(k + 1), TileSums{}, false); });
     for (uint32_t k = 0; k < tile_workers; ++k) {
       TileSums& n = at[k + 1];
       n = at[k];
@@ -1005,10 +1018,7 @@ tfs_status_t compile_batch(tfs_ctx* ctx, const tfs_batch_t* b, uint32_t flags, C
   c->rfield_index.set_size(tile_workers > 1 ? cap.nrf : b->n_fields);
   TileSums end;
   if (tile_workers > 1) {
-    std::vector<std::thread> crew;
-    for (uint32_t k = 0; k < tile_workers; ++k)
-      crew.emplace_back([&, k] { tile_range_pass(field_first(k), field_first(k + 1), at[k], true); });
-    for (std::thread& t : crew) t.join();
+    run_ranges(tile_workers, [&](uint32_t k) { tile_range_pass(field_first(k), field_first(k + 1), at[k], true); });
     end = cap;
   } else {
     end = tile_range_pass(0, b->n_fields, TileSums{}, true);

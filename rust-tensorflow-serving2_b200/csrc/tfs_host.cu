@@ -25,6 +25,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <system_error>
 #include <thread>
 
 #include "tfs_internal.h"
@@ -131,7 +132,15 @@ void stream_copy(uint8_t* dst, const uint8_t* src, size_t n) {
 class StageCrew {
  public:
   explicit StageCrew(unsigned helpers) {
-    for (unsigned i = 0; i < helpers; ++i) threads_.emplace_back([this, i] { run(i + 1); });
+    threads_.reserve(helpers);
+    for (unsigned i = 0; i < helpers; ++i) {
+      try {
+        threads_.emplace_back([this, i] { run(i + 1); });
+      } catch (const std::system_error&) {  // no more threads to be had: work with the ones that started
+        break;
+      }
+    }
+    parts_ = static_cast<unsigned>(threads_.size()) + 1;
   }
   ~StageCrew() {
     {
@@ -143,7 +152,7 @@ class StageCrew {
   }
   // `bytes` from src to dst, split over the helpers and the calling thread; returns when every part is done
   void copy(uint8_t* dst, const uint8_t* src, size_t bytes) {
-    const unsigned parts = static_cast<unsigned>(threads_.size()) + 1;
+    const unsigned parts = parts_;
     if (bytes < (256u << 10) || parts == 1) {
       std::memcpy(dst, src, bytes);
       return;
@@ -174,7 +183,7 @@ class StageCrew {
         if (stop_) return;
         seen = generation_;
       }
-      part(id, static_cast<unsigned>(threads_.size()) + 1);
+      part(id, parts_);
       bool last;
       {
         std::lock_guard<std::mutex> lock(m_);
@@ -184,6 +193,7 @@ class StageCrew {
     }
   }
   std::vector<std::thread> threads_;
+  unsigned parts_ = 1;  // helpers + the calling thread (fixed once the constructor is done)
   std::mutex m_;
   std::condition_variable work_, done_;
   uint64_t generation_ = 0;

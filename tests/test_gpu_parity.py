@@ -700,14 +700,14 @@ def test_config_c1(codec):
 
 
 def test_many_small_messages_compile_on_several_threads(codec):
-    """Above 8 192 messages the host compiles the descriptors on several threads (csrc/tfs_encode.cu compile_batch): the
+    """Above ~10^5 descriptors (messages + tensors + fields) the host compiles them on several threads (csrc/tfs_encode.cu compile_batch): the
     names of every range land in their own block and are joined afterwards.  Distinct names, one to three tensors, some
     filters and version choices per message, against the oracle byte for byte; then a descriptor error in a late message
     must come back as the one-thread walk reports it."""
     from tfs_b200._lib import TfsError
     rng = np.random.default_rng(811)
     msgs = []
-    for i in range(20_000):
+    for i in range(30_000):
         nt = 1 + i % 3
         tensors = [("in_%d_%d" % (i, k) + "y" * (i % 7),
                     tfs.TensorProto(dtype=abi.DT_FLOAT if k != 1 else abi.DT_INT64, tensor_shape=tfs.TensorShapeProto([2 + k]),
@@ -717,10 +717,10 @@ def test_many_small_messages_compile_on_several_threads(codec):
         spec = None if i % 11 == 0 else tfs.ModelSpec("model_%d" % (i % 97), version=i if i % 5 == 0 else None,
                                                      version_label="stable" if i % 5 == 1 else None, signature_name="sig%d" % (i % 3))
         msgs.append(tfs.PredictRequest(spec, tensors, output_filter=["out%d" % i] if i % 13 == 0 else []))
-    roundtrip_check(codec, msgs, abi.MSG_PREDICT_REQUEST, "20 000 small requests")
+    roundtrip_check(codec, msgs, abi.MSG_PREDICT_REQUEST, "30 000 small requests")
     built = tfs.build_batch(msgs, abi.MSG_PREDICT_REQUEST)
     built.msgs[17_000].version_choice = 9
-    built.msgs[19_000].kind = 77
+    built.msgs[29_000].kind = 77
     with pytest.raises(TfsError) as e:
         codec.encoder().encode_host(built, abi.MSG_PREDICT_REQUEST)
     assert e.value.status == abi.TFS_ERR_INVALID_ARG and "version_choice" in str(e.value)
