@@ -166,8 +166,13 @@ enum {
                                     on a 16-byte boundary of dst (messages are then not back-to-back) */
   TFS_F_HALF_TO_F32 = 1u << 2,   /* decode: half_val of a DT_HALF(19)/DT_BFLOAT16(14) tensor is widened
                                     to f32 instead of prost's Vec<i32> */
-  TFS_F_CONTENT_HALF_TO_F32 = 1u << 3 /* decode: tensor_content of a DT_HALF/DT_BFLOAT16 tensor is
+  TFS_F_CONTENT_HALF_TO_F32 = 1u << 3, /* decode: tensor_content of a DT_HALF/DT_BFLOAT16 tensor is
                                     widened to f32 */
+  TFS_F_ASYNC = 1u << 4          /* tfs_encode (device destination) only: return as soon as the offsets and lengths of
+                                    the messages are known, while the payload kernels are still writing dst.  dst is
+                                    complete in stream order: for later work on the ctx's stream (a tfs_decode* of the
+                                    same bytes, a copy queued on that stream), or after tfs_sync.  Without the flag
+                                    tfs_encode returns with dst complete.  Ignored by the *_host entry points. */
 };
 
 typedef struct {

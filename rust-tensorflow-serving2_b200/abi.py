@@ -79,6 +79,7 @@ F_GRPC_PREFIX = 1 << 0
 F_ALIGN_PAYLOAD = 1 << 1
 F_HALF_TO_F32 = 1 << 2
 F_CONTENT_HALF_TO_F32 = 1 << 3
+F_ASYNC = 1 << 4  # tfs_encode: return once the offsets are known; dst completes in stream order
 
 # DataType values used by the path (types.proto:12-68)
 DT_FLOAT, DT_DOUBLE, DT_INT32, DT_UINT8, DT_INT16, DT_INT8, DT_STRING, DT_COMPLEX64, DT_INT64, DT_BOOL = range(1, 11)

@@ -1227,8 +1227,10 @@ tfs_status_t run_sizing(tfs_ctx* ctx, const Uploaded& u, uint32_t flags, uint32_
   return TFS_OK;
 }
 
+// `behind_layout`: the copy runs on the copy stream behind ctx->enc_layout_ev (recorded after the framing kernels) and only
+// that stream is waited for - the payload kernels queued after the event keep running (TFS_F_ASYNC)
 tfs_status_t fetch_results(tfs_ctx* ctx, const EncTables& T, uint64_t* msg_off_out, uint64_t* msg_len_out, uint64_t* total_out,
-                           bool* overflow) {
+                           bool* overflow, bool behind_layout = false) {
   // msg_len | msg_pay_off | msg_off | result were carved next to each other: one device -> host copy
   const size_t n = T.n_msgs;
   const uint8_t* base = reinterpret_cast<const uint8_t*>(T.msg_len);
@@ -1236,8 +1238,14 @@ tfs_status_t fetch_results(tfs_ctx* ctx, const EncTables& T, uint64_t* msg_off_o
   const size_t bytes = o_res + 32;
   TFS_TRY(pinned_reserve(ctx, &ctx->h_down, &ctx->h_down_cap, bytes));
   uint8_t* h = static_cast<uint8_t*>(ctx->h_down);
-  TFS_CUDA(ctx, cudaMemcpyAsync(h, base, bytes, cudaMemcpyDeviceToHost, ctx->stream));
-  TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (behind_layout) {
+    TFS_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->enc_layout_ev, 0));
+    TFS_CUDA(ctx, cudaMemcpyAsync(h, base, bytes, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    TFS_CUDA(ctx, cudaStreamSynchronize(ctx->copy_stream));
+  } else {
+    TFS_CUDA(ctx, cudaMemcpyAsync(h, base, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    TFS_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  }
   if (msg_off_out && n) std::memcpy(msg_off_out, h + o_off, 8 * n);
   if (msg_len_out && n) std::memcpy(msg_len_out, h, 8 * n);
   const uint64_t* res = reinterpret_cast<const uint64_t*>(h + o_res);
@@ -1265,6 +1273,12 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
   const uint32_t dst_skew = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(dst_dev) & 15u);
   TFS_TRY(run_sizing(ctx, u, size_only ? 0u : flags, dst_skew, size_only ? ~0ull : dst_capacity,
                      size_only ? nullptr : static_cast<uint8_t*>(dst_dev)));
+  const bool async = !size_only && (flags & TFS_F_ASYNC) != 0 && ctx->pipe.empty();
+  if (async) {  // offsets, lengths and the overflow / validity words are final here
+    if (!ctx->copy_stream) TFS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    if (!ctx->enc_layout_ev) TFS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->enc_layout_ev, cudaEventDisableTiming));
+    TFS_CUDA(ctx, cudaEventRecord(ctx->enc_layout_ev, ctx->stream));
+  }
   if (!size_only) {
     const EncTables& T = u.T;
     uint8_t* dst = static_cast<uint8_t*>(dst_dev);
@@ -1299,7 +1313,7 @@ tfs_status_t encode_device(tfs_ctx* ctx, const tfs_batch_t* batch, void* dst_dev
   }
   bool overflow = false;
   tr.mark("launch");
-  TFS_TRY(fetch_results(ctx, u.T, msg_off_out, msg_len_out, total_out, &overflow));
+  TFS_TRY(fetch_results(ctx, u.T, msg_off_out, msg_len_out, total_out, &overflow, async));
   tr.mark("fetch");
   if (overflow) return set_err(ctx, TFS_ERR_NOMEM, "dst_capacity is smaller than the encoded batch");
   return TFS_OK;

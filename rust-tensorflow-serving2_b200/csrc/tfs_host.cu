@@ -381,6 +381,7 @@ tfs_status_t tfs_encode_host(tfs_ctx_t* ctx, const tfs_batch_t* batch, void* dst
     fields[i].data = din + at[i];
   }
   tr.mark("sources");
+  flags &= ~static_cast<uint32_t>(TFS_F_ASYNC);  // a host destination is complete when the call returns
   tfs_batch_t dev_batch = *batch;
   dev_batch.fields = fields.data();
   // 2. encode; the wire bytes go straight into a pinned destination, else through a device slab + D2H

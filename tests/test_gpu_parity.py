@@ -699,6 +699,36 @@ def test_config_c1(codec):
     roundtrip_check(codec, [workloads.c1_request()] * 5000, abi.MSG_PREDICT_REQUEST, "C1 x5000")
 
 
+def test_async_encode_is_complete_in_stream_order(codec):
+    """TFS_F_ASYNC: tfs_encode returns when offsets and lengths are known, the payload kernels may still be running.  The
+    bytes must be what the synchronous call writes once the stream has been waited for, and a decode queued right behind
+    it (no host wait in between) must see them."""
+    import torch
+    rng = np.random.default_rng(2718)
+    dev = torch.device(f"cuda:{codec.ctx.device}")
+    msgs = [tfs.PredictRequest(tfs.ModelSpec("m", signature_name="s"), [
+        ("x", tfs.TensorProto(dtype=1, tensor_shape=tfs.TensorShapeProto([6_000_000 + i]), float_val=rng.standard_normal(6_000_000 + i).astype(np.float32))),
+        ("ids", tfs.TensorProto(dtype=9, int64_val=rng.integers(-5, 1 << 33, 900_001, dtype=np.int64))),
+        ("s", tfs.TensorProto(dtype=7, string_val=[b"abc", b"", b"z" * 5000]))]) for i in range(6)]
+    kind = abi.MSG_PREDICT_REQUEST
+    want = ob.encode_messages(msgs, kind)
+    dmsgs = workloads.to_device(msgs, kind, dev)
+    enc, dec = codec.encoder(), codec.decoder()
+    built = tfs.build_batch(dmsgs, kind)
+    for flags in (abi.F_ASYNC, abi.F_ASYNC | abi.F_ALIGN_PAYLOAD):
+        wire = torch.full((enc.bound(built, flags) + 64,), 0x5A, dtype=torch.uint8, device=dev)
+        pool = torch.empty(sum(len(w) for w in want) * 2 + (1 << 20), dtype=torch.uint8, device=dev)
+        for _ in range(3):
+            eb = enc.encode(built, kind, flags, dst=wire)
+            d = dec.decode_into(eb.wire, eb.offsets, eb.lengths, kind, pool)  # queued behind the encode on the same stream
+            codec.ctx.sync()
+            assert_bytes_equal(eb.all_bytes(), want, f"async encode (flags {flags})")
+            st_o, dec_o = ob.decode_bytes(want, kind)
+            helpers.assert_same_decoded(dec_o, d.messages(), "request", "decode behind an async encode")
+            d.close()
+            wire.fill_(0x5A)
+
+
 def test_many_small_messages_compile_on_several_threads(codec):
     """Above ~10^5 descriptors (messages + tensors + fields) the host compiles them on several threads (csrc/tfs_encode.cu compile_batch): the
     names of every range land in their own block and are joined afterwards.  Distinct names, one to three tensors, some
