@@ -393,6 +393,7 @@ def run_ours(args):
             "achieved": round(achieved, 1) if achieved else None, "peak": peak, "unit": "GB/s",
             "frac": round(achieved / peak, 4) if achieved else None, "peak_source": peak_src,
             "frac_of_nominal_8000_GBps": round(achieved / 8000.0, 4) if achieved else None,
+            "encode_call": "TFS_F_ASYNC: returns when offsets are known; stream waited for inside the timed region",
             "traffic": traffic, "launches_timed": n_copy, "avg_launch_ms": round(ms_copy / max(1, n_copy), 4),
             "algorithmic_bytes_per_launch": alg_per_launch, "step_frac_of_peak": round(2 * value / world / peak, 4),
             "step_ms_k_copy_tma": round(ms_copy / args.steps, 4), "step_ms_walk": round(ms_walk / args.steps, 4),
@@ -539,7 +540,9 @@ def per_config(codec, dev, peak, args):
         res["wire_MB"] = round(W / 1e6, 2)
         if encode:
             alg = in_bytes + W
-            ms, top, top_ms = timed(lambda: enc.encode(built, kind, eflags, dst=wire), alg)
+            # back-to-back calls, each returning when its offsets are known (F_ASYNC); the stream is waited for before the
+            # closing event, so every kernel of every call is inside the timed region
+            ms, top, top_ms = timed(lambda: enc.encode(built, kind, eflags | abi.F_ASYNC, dst=wire), alg)
             res.update({"enc_ms": round(ms, 4), "enc_GBps": round(alg / (ms * 1e-3) / 1e9, 1), "enc_frac": round(alg / (ms * 1e-3) / 1e9 / peak, 3),
                         "enc_kernel": top, "enc_kernel_ms": round(top_ms, 4),
                         "enc_kernel_frac": round(alg / (top_ms * 1e-3) / 1e9 / peak, 3) if top_ms else None})
