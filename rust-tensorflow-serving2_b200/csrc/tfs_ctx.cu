@@ -233,6 +233,7 @@ tfs_status_t tfs_ctx_destroy(tfs_ctx_t* ctx) {
   if (ctx->h_rec) cudaFreeHost(ctx->h_rec);
   ctx->stage_crew.reset();  // joins the helper threads
   if (ctx->enc_layout_ev) cudaEventDestroy(ctx->enc_layout_ev);
+  if (ctx->dec_tables_ev) cudaEventDestroy(ctx->dec_tables_ev);
   if (ctx->h_ring) cudaFreeHost(ctx->h_ring);
   for (cudaEvent_t e : ctx->ring_ev)
     if (e) cudaEventDestroy(e);

@@ -1663,6 +1663,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   uint64_t n_tensors = 0, n_filters = 0, n_spans = 0, n_str = 0, n_vt = 0;
   uint64_t p_flt = 0, p_str = 0, res2_bytes = 0;  // the result blob: tensors | filters | strings (one D2H)
   size_t blob_copied = 0;                           // bytes of the blob that already are in h_down
+  bool tables_behind_event = false;                 // the result tables come back on the copy stream, behind ctx->dec_tables_ev
   bool planned = false;                             // small path, no varint bodies: the tables are final after sync #1
   uint8_t* d2 = nullptr;
   auto load_totals = [&](const uint8_t* hd) {
@@ -1792,6 +1793,7 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       return bail(set_err(ctx, TFS_ERR_NOMEM, "batch too large (32-bit table offsets)"));
     // ---- pass 2 tables; tensors | filters | strings are contiguous: one D2H
     blob_layout(n_tensors, n_filters, n_str, &p_flt, &p_str, &res2_bytes);
+    DEC_TRY(need_down(h2 + res2_bytes + 64));  // now, while the stream is idle: growing the block later would wait for the value kernels
     cur = 0;
     const size_t p_blob = carve(&cur, res2_bytes), p_spn = carve(&cur, sizeof(DecSpan) * n_spans), p_sv = carve(&cur, 4 * (n_spans + 1)),
                  p_sc = carve(&cur, 4 * (n_spans + 1)), p_tc = carve(&cur, 4 * n_vt), p_ts = carve(&cur, sizeof(TileRef) * n_vt),
@@ -1868,7 +1870,15 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
       }
     }
     DEC_CUDA(cudaGetLastError());
-    // one-call decode: the value kernels follow at once, gated on the device by "the pool is large enough"
+    // one-call decode: the value kernels follow at once, gated on the device by "the pool is large enough".  The result
+    // tables are final HERE: they come back on the copy stream behind this event, so that the call returns while the value
+    // kernels are still running (the device-pool forms are asynchronous; the host forms wait for the stream themselves)
+    if (pool_dev && ctx->pipe.empty()) {
+      if (!ctx->copy_stream) DEC_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+      if (!ctx->dec_tables_ev) DEC_CUDA(cudaEventCreateWithFlags(&ctx->dec_tables_ev, cudaEventDisableTiming));
+      DEC_CUDA(cudaEventRecord(ctx->dec_tables_ev, ctx->stream));
+      tables_behind_event = true;
+    }
     if (pool_dev) {
       DEC_TRY(fetch_host_segs());
       DEC_TRY(launch_values(ctx, dec, static_cast<uint8_t*>(pool_dev), T.totals + TOT_OVERFLOW, hsegs.empty() ? nullptr : &hsegs));
@@ -1887,9 +1897,14 @@ tfs_status_t decode_scan_device(tfs_ctx* ctx, const void* wire_dev, uint64_t wir
   DEC_TRY(need_down(h2 + res2_bytes + 64));
   uint8_t* hd = static_cast<uint8_t*>(dec->down.p);
   if (!planned || regrown || blob_copied < res2_bytes) {
-    if (!planned || regrown) DEC_CUDA(cudaMemcpyAsync(hd + h1, d1 + o_tot, res1_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    if (res2_bytes) DEC_CUDA(cudaMemcpyAsync(hd + h2, T.tensors, res2_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-    DEC_CUDA(cudaStreamSynchronize(ctx->stream));  // sync #2: the caller needs the element counts (and, one-call, the values)
+    cudaStream_t rs = ctx->stream;
+    if (tables_behind_event && !regrown) {
+      rs = ctx->copy_stream;
+      DEC_CUDA(cudaStreamWaitEvent(rs, ctx->dec_tables_ev, 0));
+    }
+    if (!planned || regrown) DEC_CUDA(cudaMemcpyAsync(hd + h1, d1 + o_tot, res1_bytes, cudaMemcpyDeviceToHost, rs));
+    if (res2_bytes) DEC_CUDA(cudaMemcpyAsync(hd + h2, T.tensors, res2_bytes, cudaMemcpyDeviceToHost, rs));
+    DEC_CUDA(cudaStreamSynchronize(rs));  // sync #2: the caller needs the element counts
     std::memcpy(dec->totals, hd + h1, kTotalsBytes);
   }
   tr.mark("sync2");

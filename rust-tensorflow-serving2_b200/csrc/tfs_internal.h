@@ -282,6 +282,7 @@ struct tfs_ctx {
   cudaEvent_t ring_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   bool ring_busy[4] = {false, false, false, false};
   uint32_t ring_next = 0;
+  cudaEvent_t dec_tables_ev = nullptr;  // one-call decode: recorded when the result tables are final (before the value kernels)
   cudaEvent_t enc_layout_ev = nullptr;  // TFS_F_ASYNC: recorded when the framing is done; the results come back behind it
   std::shared_ptr<void> enc_scratch;  // the encoder's host tables (tfs_encode.cu: Compiled), kept between calls: grow-only
   void* h_rec = nullptr;  // the encoder compiles its message / tensor / field records straight into this pinned block
