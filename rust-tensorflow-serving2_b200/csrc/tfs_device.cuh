@@ -8,7 +8,7 @@
 namespace tfs {
 
 // ---- varint arithmetic (prost encoded_len_varint: max(1, ceil(bits / 7)); reference path src/lib.rs:265) ----
-// (the framing arithmetic is __host__ __device__: the host runs the same layout code to predict where varint bodies go)
+// (the framing arithmetic compiles for host and device alike; only device code calls it today)
 __host__ __device__ __forceinline__ uint32_t varint_len(uint64_t v) {
 #ifdef __CUDA_ARCH__
   return (70u - static_cast<uint32_t>(__clzll(static_cast<long long>(v | 1)))) / 7u;
