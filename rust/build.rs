@@ -2,7 +2,7 @@
 // UNCOMPILED on the build box of this repository (no rustc); see rust/README.md.
 use std::{env, path::PathBuf, process::Command};
 
-const CUDA_SOURCES: &[&str] = &["tfs_ctx.cu", "tfs_copy.cu", "tfs_encode.cu", "tfs_decode.cu", "tfs_host.cu", "tfs_noalloc.cu"];
+const CUDA_SOURCES: &[&str] = &["tfs_ctx.cu", "tfs_copy.cu", "tfs_encode.cu", "tfs_decode.cu", "tfs_host.cu", "tfs_noalloc.cu", "tfs_engine.cu"];
 
 fn main() -> Result<(), Box<dyn std::error::Error>> {
     // 1. unchanged: generate the prost structs and the tonic client stubs
@@ -42,6 +42,7 @@ fn main() -> Result<(), Box<dyn std::error::Error>> {
     println!("cargo:rustc-link-search=native=/usr/local/cuda/lib64");
     println!("cargo:rustc-link-lib=dylib=cudart");
     println!("cargo:rustc-link-lib=dylib=stdc++");
+    println!("cargo:rustc-link-lib=dylib=pthread"); // the engine lanes, the staging helper threads
     println!("cargo:rerun-if-changed=include/tfs_gpu.h");
     Ok(())
 }
