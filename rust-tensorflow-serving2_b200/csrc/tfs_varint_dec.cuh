@@ -231,6 +231,21 @@ __device__ __forceinline__ uint32_t pad_slot(uint32_t i) { return i + (i >> 4); 
 __device__ __forceinline__ uint32_t pad_word(uint32_t i) { return i + 4u * (i >> 4); }
 constexpr uint32_t kGatherOutBytes = (kRoundValues + kRoundValues / 16 + 1) * 8;
 
+// 32-bit shared-memory addresses held in registers, and loads / stores through them: inside the per-value loop of the fast
+// path the compiler otherwise rebuilds the base of every shared array from the thread index on each iteration (8 of the 49
+// instructions of the old loop body, profiles/README.md r02 gather capture)
+__device__ __forceinline__ uint32_t smem_addr_of(const void* p) {
+  uint32_t a;
+  asm volatile("{ .reg .u64 t; cvta.to.shared.u64 t, %1; cvt.u32.u64 %0, t; }" : "=r"(a) : "l"(p));
+  return a;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void sts_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+
 // One 16-byte chunk per thread, 256 threads per 4 KiB tile.  (Two chunks per thread, which pays for the count kernel, measured
 // 7-12 % SLOWER here - a thread's values come out of a serial loop over its terminators, and twice as many per thread doubled
 // that chain while the scan and the barriers it amortises are a small part of this kernel - and 8 KiB tiles with 512 threads
@@ -301,6 +316,41 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
           ++slot;
         }
       }
+    }
+  } else if (fast && total <= kRoundValues) {
+    // The common fast case (2-3 byte values: at most 2048 of them in a tile, one round).  As below, with what the profile of
+    // the loop asked for: shared addresses kept in registers, the length of a value from the position of the terminator
+    // before it (one subtraction) instead of from the continuation bits, values staged densely (no slot padding: a
+    // thread's values are consecutive and the threads of a warp start 5-8 slots apart), no per-value round test.
+    const uint32_t wa = smem_addr_of(sm_in) + threadIdx.x * 20u;
+    sts_u32(wa, pd.w);
+    sts_u32(wa + 4u, d.x);
+    sts_u32(wa + 8u, d.y);
+    sts_u32(wa + 12u, d.z);
+    sts_u32(wa + 16u, d.w);
+    // the value that ends at the first terminator of the chunk starts after the terminator before it: in the previous
+    // chunk (its trailing continuation bytes, at most 3 here), or at the first byte of the span if that lies in this chunk
+    int32_t jprev;
+    {
+      const uint32_t first_valid = static_cast<uint32_t>(__ffs(static_cast<int>(valid))) - 1u;  // (term != 0 => valid != 0)
+      const uint32_t lead = static_cast<uint32_t>(__clz(static_cast<int>(~(pcont << 16))));     // continuation bytes that end the previous chunk
+      jprev = static_cast<int32_t>(first_valid) - 1 - (first_valid == 0u ? static_cast<int32_t>(lead) : 0);
+    }
+    uint32_t oa = smem_addr_of(sm_out) + 4u * idx0;
+    uint32_t t = term;
+    while (t) {
+      const int32_t j = __ffs(static_cast<int>(t)) - 1;
+      t &= t - 1;
+      const uint32_t len = static_cast<uint32_t>(j - jprev);
+      jprev = j;
+      const uint32_t q = static_cast<uint32_t>(j) + 1u;  // offset of the first of the 4 bytes that end at the terminator, in the 20-byte strip
+      const uint32_t a = wa + (q & ~3u);
+      const uint32_t x = __funnelshift_r(lds_u32(a), lds_u32(a + 4u), q << 3);  // (the shift is taken mod 32)
+      uint32_t g = x & 0x7F7F7F7Fu;
+      g = (g & 0x007F007Fu) | ((g & 0x7F007F00u) >> 1);
+      g = (g & 0x00003FFFu) | ((g & 0x3FFF0000u) >> 2);
+      sts_u32(oa, convert_word<OUT>(g >> (28u - 7u * len)));
+      oa += 4u;
     }
   } else if (fast) {
     // The 20 bytes {last word before the chunk, the chunk} go to a thread-private strip of shared memory so that the
@@ -374,7 +424,9 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
   __syncthreads();
   // coalesced flush of this round's values
   const uint32_t n_round = total - round0 < kRoundValues ? total - round0 : kRoundValues;
-  if (fast) {  // (all1 implies fast) staged as 32-bit words
+  if (fast && !all1 && total <= kRoundValues) {  // staged densely as 32-bit words
+    for (uint32_t i = threadIdx.x; i < n_round; i += kGatherThreads) gdst[i] = static_cast<out_t>(out32[i]);
+  } else if (fast) {  // (all1 implies fast) staged as 32-bit words, padded
     for (uint32_t i = threadIdx.x; i < n_round; i += kGatherThreads) gdst[round0 + i] = static_cast<out_t>(out32[pad_word(i)]);
   } else {
     for (uint32_t i = threadIdx.x; i < n_round; i += kGatherThreads) gdst[round0 + i] = out[pad_slot(i)];
