@@ -263,9 +263,7 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
   // The 16 bytes before this thread's chunk: the previous lane has them.  Lane 0 of warps 1..7 gets the previous warp's
   // last lane through shared memory (its last word and continuation mask are all the fast path needs; the general path
   // reads the staged tile), only thread 0 has to go back to global memory for the bytes in front of the tile.
-  pd.x = __shfl_up_sync(0xFFFFFFFFu, d.x, 1);
-  pd.y = __shfl_up_sync(0xFFFFFFFFu, d.y, 1);
-  pd.z = __shfl_up_sync(0xFFFFFFFFu, d.z, 1);
+  pd.x = pd.y = pd.z = 0;  // (only thread 0's copy of the whole chunk is ever used: it stages the bytes in front of the tile)
   pd.w = __shfl_up_sync(0xFFFFFFFFu, d.w, 1);
   pcont = __shfl_up_sync(0xFFFFFFFFu, cont, 1);
   if (lane_id() == 31) {
