@@ -385,7 +385,9 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
     // end at it as three registers (four aligned word loads + funnel shifts), the 7-bit groups packed 4 / 4 / 2 at a
     // time, and the groups of the previous value shifted out.
     __syncthreads();
-    const uint32_t* sm_w = reinterpret_cast<const uint32_t*>(sm_in);
+    // (shared addresses in registers, as in the fast path: the compiler rebuilds them from the thread index otherwise)
+    const uint32_t ta = smem_addr_of(sm_in) + 16u + threadIdx.x * 16u - 11u;  // byte address of "11 bytes before this chunk"
+    const uint32_t out_a = smem_addr_of(sm_out);
     uint32_t t = term, idx = idx0;
     while (t) {
       const uint32_t j = static_cast<uint32_t>(__ffs(t)) - 1u;
@@ -394,9 +396,9 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
       if (slot >= kRoundValues) continue;  // belongs to another round
       const uint32_t run = static_cast<uint32_t>(__clz(static_cast<int>(~(c32 << (16u - j)))));  // continuation bytes right below it
       const uint32_t len = 1u + (run < 9u ? run : 9u);
-      const uint32_t a = 16u + threadIdx.x * 16u + j - 11u;  // first of the 12 bytes that end at the terminator
-      const uint32_t w0 = a >> 2, sh = (a & 3u) * 8u;
-      const uint32_t W0 = sm_w[w0], W1 = sm_w[w0 + 1], W2 = sm_w[w0 + 2], W3 = sm_w[w0 + 3];
+      const uint32_t a = ta + j;  // first of the 12 bytes that end at the terminator
+      const uint32_t wa4 = a & ~3u, sh = a << 3;  // (funnel shifts take the amount mod 32)
+      const uint32_t W0 = lds_u32(wa4), W1 = lds_u32(wa4 + 4u), W2 = lds_u32(wa4 + 8u), W3 = lds_u32(wa4 + 12u);
       const uint32_t x0 = __funnelshift_r(W0, W1, sh), x1 = __funnelshift_r(W1, W2, sh), x2 = __funnelshift_r(W2, W3, sh);
       auto pack4 = [](uint32_t x) {
         uint32_t g = x & 0x7F7F7F7Fu;
@@ -416,7 +418,11 @@ __device__ __forceinline__ void gather_tile(const TileRef& r, uint8_t* __restric
         const uint64_t c = (hi2 & 0x7Fu) | ((hi2 & 0x7F00u) >> 1);
         v = len == 9u ? ((A << 35) | (B << 7) | (c >> 7)) : ((A << 42) | (B << 14) | c);
       }
-      out[pad_slot(slot)] = convert_out<OUT>(v);
+      const out_t ov = convert_out<OUT>(v);
+      const uint32_t oa = out_a + pad_slot(slot) * static_cast<uint32_t>(sizeof(out_t));
+      if constexpr (sizeof(out_t) == 8) asm volatile("st.shared.u64 [%0], %1;" ::"r"(oa), "l"(static_cast<unsigned long long>(ov)) : "memory");
+      else if constexpr (sizeof(out_t) == 4) sts_u32(oa, static_cast<uint32_t>(ov));
+      else asm volatile("st.shared.u8 [%0], %1;" ::"r"(oa), "r"(static_cast<uint32_t>(ov)) : "memory");
     }
   }
   __syncthreads();
