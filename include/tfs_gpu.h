@@ -19,8 +19,8 @@
  *     pinned slabs (host<->device copies are inside those calls).  Pageable buffers of 1 MB and more are copied
  *     through a pinned ring by helper threads the context starts on first use (at most 7, TFS_STAGE_THREADS in the
  *     environment overrides the count; they sleep between calls and end with tfs_ctx_destroy); a batch of about
- *     10^5 descriptors (messages + tensors + fields) and more is compiled on up to 8 short-lived threads.
- *     TFS_TRACE=1 prints host phase times to stderr.
+ *     10^5 descriptors (messages + tensors + fields) and more is compiled on up to 8 short-lived threads
+ *     (TFS_COMPILE_THREADS overrides the count).  TFS_TRACE=1 prints host phase times to stderr.
  *   - output bytes are byte-identical to prost 0.6.0's encoding of the same message with map entries
  *     in the caller's order; decoded values are value-identical.
  *   - over-read contract: the kernels fetch whole ALIGNED 16-byte words, so up to 15 bytes before the first and
