@@ -867,6 +867,17 @@ def test_config_c5_mixed_responses(codec):
     roundtrip_check(codec, msgs, abi.MSG_PREDICT_RESPONSE, "C5")
 
 
+@pytest.mark.parametrize("flags", [abi.F_ALIGN_PAYLOAD, abi.F_GRPC_PREFIX, abi.F_GRPC_PREFIX | abi.F_ALIGN_PAYLOAD])
+@pytest.mark.parametrize("seed", [11, 12])
+def test_mixed_batches_under_every_flag(codec, flags, seed):
+    """Mixed-dtype responses and requests (element counts log-uniform from 1: most payloads are a few bytes and take the
+    warp-per-segment copy, some are large) under the flags the C5 test leaves out; host, device and pinned paths."""
+    msgs = workloads.c5_responses(160, seed=seed, max_log2=13)
+    roundtrip_check(codec, msgs, abi.MSG_PREDICT_RESPONSE, f"mixed responses (flags {flags})", flags)
+    reqs = [tfs.PredictRequest(m.model_spec if i % 3 else None, m.outputs, ["f%d" % i] * (i % 3)) for i, m in enumerate(msgs[:96])]
+    roundtrip_check(codec, reqs, abi.MSG_PREDICT_REQUEST, f"mixed requests (flags {flags})", flags)
+
+
 def test_varint_encode_around_length_prefix_boundaries(codec):
     """Element counts around the powers of 128 where a length prefix changes size, every varint source type, gRPC prefix on
     and off, two tensors and filters per request: bytes against the oracle."""
