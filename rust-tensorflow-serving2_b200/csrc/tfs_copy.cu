@@ -400,14 +400,34 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
 // ---------------------------------------------------------------------------------------------------
 constexpr uint32_t kCastPad = 64;  // slack around both stages (window alignment, group padding, flush over-read)
 
+// u8 -> f32 with a scale, ARITH: computed, not looked up.  `x * p` is the operation itself; `x / p` is the product with the
+// reciprocal corrected by the remainder (two fused multiply-adds), used only when the CTA has checked that it gives the bits
+// of the IEEE division for all 256 inputs (k_copy_cast).  The table costs shared-memory bank conflicts: pixel values are
+// random, so the 32 lanes of a look-up hit the same bank several at a time.
+struct CastScale {
+  float p, rcp;
+};
 template <int OP>
-__device__ __forceinline__ void cast_group(const uint8_t* in, uint8_t* out, const float* lut) {
+__device__ __forceinline__ float scale_u8(uint32_t b, const CastScale& s) {
+  const float x = static_cast<float>(b);
+  if constexpr (OP == CP_U8_F32_MUL) {
+    return __fmul_rn(x, s.p);
+  } else {
+    const float q0 = __fmul_rn(x, s.rcp);
+    return __fmaf_rn(__fmaf_rn(-q0, s.p, x), s.rcp, q0);
+  }
+}
+
+template <int OP, bool ARITH = false>
+__device__ __forceinline__ void cast_group(const uint8_t* in, uint8_t* out, const float* lut, const CastScale& sc) {
   // 4 elements: `in` / `out` are aligned to 4 input / output elements
   if constexpr (OP == CP_U8_F32 || OP == CP_U8_F32_DIV || OP == CP_U8_F32_MUL) {
     const uint32_t w = *reinterpret_cast<const uint32_t*>(in);
     float4 r;
     if constexpr (OP == CP_U8_F32) {
       r = make_float4(static_cast<float>(w & 0xFFu), static_cast<float>((w >> 8) & 0xFFu), static_cast<float>((w >> 16) & 0xFFu), static_cast<float>(w >> 24));
+    } else if constexpr (ARITH) {
+      r = make_float4(scale_u8<OP>(w & 0xFFu, sc), scale_u8<OP>((w >> 8) & 0xFFu, sc), scale_u8<OP>((w >> 16) & 0xFFu, sc), scale_u8<OP>(w >> 24, sc));
     } else {
       r = make_float4(lut[w & 0xFFu], lut[(w >> 8) & 0xFFu], lut[(w >> 16) & 0xFFu], lut[w >> 24]);
     }
@@ -433,8 +453,9 @@ __device__ __forceinline__ void cast_group(const uint8_t* in, uint8_t* out, cons
   }
 }
 
-template <int OP>
-__device__ __forceinline__ void cast_tile(const CopySeg& seg, uint64_t e0, uint32_t n, uint8_t* sm_in, uint8_t* sm_out, uint64_t* bar, const float* lut) {
+template <int OP, bool ARITH = false>
+__device__ __forceinline__ void cast_tile(const CopySeg& seg, uint64_t e0, uint32_t n, uint8_t* sm_in, uint8_t* sm_out, uint64_t* bar, const float* lut,
+                                          const CastScale& sc = CastScale{0.f, 0.f}) {
   constexpr uint32_t IS = (OP == CP_F32_F16 || OP == CP_F32_BF16) ? 4u : (OP == CP_F16_F32 || OP == CP_BF16_F32) ? 2u : 1u;
   constexpr uint32_t OS = (OP == CP_F32_F16 || OP == CP_F32_BF16) ? 2u : 4u;
   const uint64_t s_abs = reinterpret_cast<uintptr_t>(seg.src) + e0 * IS;
@@ -452,7 +473,7 @@ __device__ __forceinline__ void cast_tile(const CopySeg& seg, uint64_t e0, uint3
   mbar_wait(bar, 0);
   // output stage: element j of the tile at sm_out + (lead + j) * OS, so that group g's four outputs start at 4 * OS * g
   for (uint32_t g = threadIdx.x; g < n_groups; g += kCopyThreads)
-    cast_group<OP>(sm_in + (g0 + g) * 4u * IS, sm_out + g * 4u * OS, lut);
+    cast_group<OP, ARITH>(sm_in + (g0 + g) * 4u * IS, sm_out + g * 4u * OS, lut, sc);
   __syncthreads();
   // flush the bytes [lead * OS, (lead + n) * OS) of the stage to dst
   uint8_t* d = seg.dst + e0 * OS;
@@ -520,18 +541,24 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy_cast(const CopySeg* __res
     const uint64_t src_end = reinterpret_cast<uintptr_t>(seg.src) + e1 * in_size_of(seg.op);
     if (src_end <= src_lo || src_end > src_hi) return;
   }
-  if (seg.op == CP_U8_F32_DIV || seg.op == CP_U8_F32_MUL) {
+  const CastScale sc{seg.param, __frcp_rn(seg.param)};
+  bool div_arith = false;
+  if (seg.op == CP_U8_F32_DIV) {  // the table, and whether the two-FMA form reproduces it bit for bit (it does for 255.f)
     const float x = static_cast<float>(threadIdx.x);
-    lut[threadIdx.x] = seg.op == CP_U8_F32_DIV ? __fdiv_rn(x, seg.param) : __fmul_rn(x, seg.param);
-    __syncthreads();
+    const float exact = __fdiv_rn(x, seg.param);
+    lut[threadIdx.x] = exact;
+    div_arith = __syncthreads_and(__float_as_uint(exact) == __float_as_uint(scale_u8<CP_U8_F32_DIV>(threadIdx.x, sc))) != 0;
   }
   uint8_t* sm_in = cast_smem;
   uint8_t* sm_out = cast_smem + in_stage_bytes;
   const uint32_t n = static_cast<uint32_t>(e1 - e0);
   switch (seg.op) {
     case CP_U8_F32: cast_tile<CP_U8_F32>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
-    case CP_U8_F32_DIV: cast_tile<CP_U8_F32_DIV>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
-    case CP_U8_F32_MUL: cast_tile<CP_U8_F32_MUL>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
+    case CP_U8_F32_DIV:
+      if (div_arith) cast_tile<CP_U8_F32_DIV, true>(seg, e0, n, sm_in, sm_out, &bar, lut, sc);
+      else cast_tile<CP_U8_F32_DIV>(seg, e0, n, sm_in, sm_out, &bar, lut);
+      break;
+    case CP_U8_F32_MUL: cast_tile<CP_U8_F32_MUL, true>(seg, e0, n, sm_in, sm_out, &bar, lut, sc); break;
     case CP_F32_F16: cast_tile<CP_F32_F16>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
     case CP_F32_BF16: cast_tile<CP_F32_BF16>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
     case CP_F16_F32: cast_tile<CP_F16_F32>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
