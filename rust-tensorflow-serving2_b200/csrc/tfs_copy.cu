@@ -97,6 +97,19 @@ __device__ __forceinline__ uint32_t seg_of_tile_warp(const CopySeg* __restrict__
   return lo;
 }
 
+// `x / p` and `x * p` as the reference's host computes them (src/lib.rs:237-242 on x86-64): the IEEE operation, and when the
+// result is a NaN the bits SSE gives it - the NaN operand made quiet if `p` is one, the "real indefinite" 0xFFC00000 for
+// 0 / 0 and 0 * inf - not the GPU's canonical 0x7FFFFFFF.  (x comes from a u8: never a NaN, never negative.)
+__device__ __forceinline__ float nan_like_sse(float r, float p) {
+  if (r != r) {
+    const uint32_t pb = __float_as_uint(p);
+    return __uint_as_float((pb & 0x7FFFFFFFu) > 0x7F800000u ? (pb | 0x00400000u) : 0xFFC00000u);
+  }
+  return r;
+}
+__device__ __forceinline__ float u8_div(float x, float p) { return nan_like_sse(__fdiv_rn(x, p), p); }
+__device__ __forceinline__ float u8_mul(float x, float p) { return nan_like_sse(__fmul_rn(x, p), p); }
+
 // ---------------------------------------------------------------------------------------------------
 // generic path: one CTA per tile
 // ---------------------------------------------------------------------------------------------------
@@ -176,8 +189,8 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy(const CopySeg* __restrict
     case CP_BYTES: cta_copy_bytes(d, s, n); break;
     case CP_BOOL: cta_cast<uint8_t, uint8_t>(d, s, n, [](uint8_t x) { return static_cast<uint8_t>(x != 0); }); break;
     case CP_U8_F32: cta_cast<uint8_t, float>(d, s, n, [](uint8_t x) { return static_cast<float>(x); }); break;
-    case CP_U8_F32_DIV: cta_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return __fdiv_rn(static_cast<float>(x), p); }); break;
-    case CP_U8_F32_MUL: cta_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return __fmul_rn(static_cast<float>(x), p); }); break;
+    case CP_U8_F32_DIV: cta_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return u8_div(static_cast<float>(x), p); }); break;
+    case CP_U8_F32_MUL: cta_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return u8_mul(static_cast<float>(x), p); }); break;
     case CP_F32_F16: cta_cast<float, uint16_t>(d, s, n, [](float x) { return static_cast<uint16_t>(f32_to_f16_bits(x)); }); break;
     case CP_F32_BF16: cta_cast<float, uint16_t>(d, s, n, [](float x) { return static_cast<uint16_t>(f32_to_bf16_bits(x)); }); break;
     case CP_F16_F32: cta_cast<uint16_t, float>(d, s, n, [](uint16_t x) { return f16_bits_to_f32(x); }); break;
@@ -222,8 +235,8 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy_small(const CopySeg* __re
       break;
     case CP_BOOL: warp_cast<uint8_t, uint8_t>(d, s, n, [](uint8_t x) { return static_cast<uint8_t>(x != 0); }); break;
     case CP_U8_F32: warp_cast<uint8_t, float>(d, s, n, [](uint8_t x) { return static_cast<float>(x); }); break;
-    case CP_U8_F32_DIV: warp_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return __fdiv_rn(static_cast<float>(x), p); }); break;
-    case CP_U8_F32_MUL: warp_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return __fmul_rn(static_cast<float>(x), p); }); break;
+    case CP_U8_F32_DIV: warp_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return u8_div(static_cast<float>(x), p); }); break;
+    case CP_U8_F32_MUL: warp_cast<uint8_t, float>(d, s, n, [p](uint8_t x) { return u8_mul(static_cast<float>(x), p); }); break;
     case CP_F32_F16: warp_cast<float, uint16_t>(d, s, n, [](float x) { return static_cast<uint16_t>(f32_to_f16_bits(x)); }); break;
     case CP_F32_BF16: warp_cast<float, uint16_t>(d, s, n, [](float x) { return static_cast<uint16_t>(f32_to_bf16_bits(x)); }); break;
     case CP_F16_F32: warp_cast<uint16_t, float>(d, s, n, [](uint16_t x) { return f16_bits_to_f32(x); }); break;
@@ -542,12 +555,18 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy_cast(const CopySeg* __res
     if (src_end <= src_lo || src_end > src_hi) return;
   }
   const CastScale sc{seg.param, __frcp_rn(seg.param)};
-  bool div_arith = false;
+  bool arith = false;
   if (seg.op == CP_U8_F32_DIV) {  // the table, and whether the two-FMA form reproduces it bit for bit (it does for 255.f)
     const float x = static_cast<float>(threadIdx.x);
-    const float exact = __fdiv_rn(x, seg.param);
+    const float exact = u8_div(x, seg.param);
     lut[threadIdx.x] = exact;
-    div_arith = __syncthreads_and(__float_as_uint(exact) == __float_as_uint(scale_u8<CP_U8_F32_DIV>(threadIdx.x, sc))) != 0;
+    arith = __syncthreads_and(__float_as_uint(exact) == __float_as_uint(scale_u8<CP_U8_F32_DIV>(threadIdx.x, sc))) != 0;
+  } else if (seg.op == CP_U8_F32_MUL) {  // a finite factor cannot make a NaN: the multiplication itself; otherwise the table
+    arith = (__float_as_uint(seg.param) & 0x7F800000u) != 0x7F800000u;
+    if (!arith) {
+      lut[threadIdx.x] = u8_mul(static_cast<float>(threadIdx.x), seg.param);
+      __syncthreads();
+    }
   }
   uint8_t* sm_in = cast_smem;
   uint8_t* sm_out = cast_smem + in_stage_bytes;
@@ -555,10 +574,13 @@ __global__ void __launch_bounds__(kCopyThreads) k_copy_cast(const CopySeg* __res
   switch (seg.op) {
     case CP_U8_F32: cast_tile<CP_U8_F32>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
     case CP_U8_F32_DIV:
-      if (div_arith) cast_tile<CP_U8_F32_DIV, true>(seg, e0, n, sm_in, sm_out, &bar, lut, sc);
+      if (arith) cast_tile<CP_U8_F32_DIV, true>(seg, e0, n, sm_in, sm_out, &bar, lut, sc);
       else cast_tile<CP_U8_F32_DIV>(seg, e0, n, sm_in, sm_out, &bar, lut);
       break;
-    case CP_U8_F32_MUL: cast_tile<CP_U8_F32_MUL, true>(seg, e0, n, sm_in, sm_out, &bar, lut, sc); break;
+    case CP_U8_F32_MUL:
+      if (arith) cast_tile<CP_U8_F32_MUL, true>(seg, e0, n, sm_in, sm_out, &bar, lut, sc);
+      else cast_tile<CP_U8_F32_MUL>(seg, e0, n, sm_in, sm_out, &bar, lut);
+      break;
     case CP_F32_F16: cast_tile<CP_F32_F16>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
     case CP_F32_BF16: cast_tile<CP_F32_BF16>(seg, e0, n, sm_in, sm_out, &bar, lut); break;
     case CP_F16_F32: cast_tile<CP_F16_F32>(seg, e0, n, sm_in, sm_out, &bar, lut); break;

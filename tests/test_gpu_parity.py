@@ -269,6 +269,20 @@ def test_staged_casts_alignment_and_tile_edges(codec, flags):
     helpers.assert_same_decoded(dec_o, dec, "request", "staged casts decode (widened)")
 
 
+def test_u8_scale_by_any_divisor_is_the_ieee_operation(codec):
+    """u8 -> f32 with `/ p` is computed with a reciprocal and two fused multiply-adds only when the kernel has checked that
+    this gives the bits of the IEEE division for all 256 inputs, and looked up in a table of true quotients otherwise; `* p`
+    is the multiplication itself.  Divisors and factors of every kind (including ones where the shortcut is NOT exact, zero,
+    denormals, infinities and NaN) against the oracle's plain `x / p`, `x * p`."""
+    all_bytes = np.tile(np.arange(256, dtype=np.uint8), 9)[:2100]  # every input value, more than the staged kernel's minimum
+    params = [255.0, 3.0, 7.1, 127.5, 1.0, 0.1, 1e-30, 1e-40, 3.4e38, 0.0, -255.0, float("inf"), float("nan"), 2.0 ** -126, 65535.0, 0.00392156862745098]
+    msgs = [tfs.PredictRequest(None, [
+        ("d", tfs.TensorProto(dtype=1, float_val=tfs.Payload(all_bytes, abi.T_U8, abi.T_F32, abi.OP_DIV, p))),
+        ("m", tfs.TensorProto(dtype=1, float_val=tfs.Payload(all_bytes[3:], abi.T_U8, abi.T_F32, abi.OP_MUL, p)))]) for p in params]
+    kind = abi.MSG_PREDICT_REQUEST
+    assert_bytes_equal(gpu_encode_both(codec, msgs, kind), ob.encode_messages(msgs, kind), "u8 scale")
+
+
 def test_invalid_descriptors_are_rejected(codec):
     from tfs_b200._lib import TfsError
     enc = codec.encoder()
