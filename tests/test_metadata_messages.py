@@ -253,3 +253,16 @@ def test_gpu_metadata_response_mutations(codec):
     want = ob.decode_bytes(blobs, abi.MSG_METADATA_RESPONSE)[1]
     assert sum(m.status != 0 for m in want) > 100
     same_messages(want, gpu_decode(codec, blobs, abi.MSG_METADATA_RESPONSE), "mutated responses")
+
+
+@pytest.mark.gpu
+def test_gpu_metadata_large_batch_takes_the_two_walk_path(codec):
+    """More than 1 024 messages: the count / fill walks instead of the single-walk plan kernel."""
+    base = responses()
+    blobs = [base[i % len(base)] for i in range(3000)]
+    want = ob.decode_bytes(blobs, abi.MSG_METADATA_RESPONSE)[1]
+    same_messages(want, gpu_decode(codec, blobs, abi.MSG_METADATA_RESPONSE), "3 000 responses")
+    reqs = requests() * 40
+    wire = ob.encode_messages(reqs, abi.MSG_METADATA_REQUEST)
+    assert codec.encoder().encode_host(reqs, abi.MSG_METADATA_REQUEST).all_bytes() == wire
+    same_messages(ob.decode_bytes(wire, abi.MSG_METADATA_REQUEST)[1], gpu_decode(codec, wire, abi.MSG_METADATA_REQUEST), "1 760 requests")
