@@ -338,10 +338,17 @@ struct TileWalk {
   }
 };
 
+// counts that are still being computed on the device when the kernel is queued (launch_copy_tma_deferred)
+struct DeferredCounts {
+  const uint64_t* go = nullptr;  // nullptr: the by-value arguments hold
+  const uint64_t* n_segs = nullptr;
+  const uint64_t* n_tiles = nullptr;
+};
+
 template <bool COOP>
 __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ segs, uint32_t n_segs, uint64_t n_tiles,
                                                  const uint64_t* __restrict__ gate, uint64_t src_lo, uint64_t src_hi,
-                                                 uint64_t tile_begin) {
+                                                 uint64_t tile_begin, DeferredCounts deferred = DeferredCounts{}) {
   extern __shared__ __align__(128) uint8_t ring[];  // kTmaStages x kTmaChunk
   __shared__ __align__(8) uint64_t full_bar[kTmaStages];
   // Lane 0 drives the TMA engine.  COOP = false (few segments, the C2 shape): the other lanes leave at once.  COOP = true
@@ -350,6 +357,11 @@ __global__ void __launch_bounds__(32) k_copy_tma(const CopySeg* __restrict__ seg
   if (!COOP && threadIdx.x != 0) return;
   const bool leader = threadIdx.x == 0;
   if (gate && *gate != 0) return;
+  if (deferred.go) {  // queued before the counts existed: they are in device memory now (written by the kernel in front)
+    if (*deferred.go == 0) return;
+    n_segs = static_cast<uint32_t>(*deferred.n_segs);
+    n_tiles = *deferred.n_tiles;
+  }
   if (tile_begin + blockIdx.x >= n_tiles) return;
   if (leader) {
 #pragma unroll
@@ -678,6 +690,30 @@ tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs,
     ctx->pipe.clear();
     TFS_TRY(launch_small());
   }
+  TFS_CUDA(ctx, cudaGetLastError());
+  return TFS_OK;
+}
+
+tfs_status_t launch_copy_tma_deferred(tfs_ctx* ctx, const CopySeg* segs_dev, const uint64_t* go, const uint64_t* n_segs_dev,
+                                      const uint64_t* n_tiles_dev, bool many_segs) {
+  const uint32_t ring_bytes = kTmaStages * kTmaChunk;
+  if (!ctx->copy_attr_set) {
+    TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_tma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ring_bytes)));
+    TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_tma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(ring_bytes)));
+    TFS_CUDA(ctx, cudaFuncSetAttribute(k_copy_cast, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(3 * kCopyTileBytes + 2 * kCastPad)));
+    ctx->copy_attr_set = true;
+  }
+  DeferredCounts d;
+  d.go = go;
+  d.n_segs = n_segs_dev;
+  d.n_tiles = n_tiles_dev;
+  {
+    ProfScope prof(ctx, PK_COPY_TMA);
+    const uint32_t grid = static_cast<uint32_t>(ctx->sm_count);
+    if (many_segs) k_copy_tma<true><<<grid, 32, ring_bytes, ctx->stream>>>(segs_dev, 0u, 0ull, nullptr, 0ull, ~0ull, 0ull, d);
+    else k_copy_tma<false><<<grid, 32, ring_bytes, ctx->stream>>>(segs_dev, 0u, 0ull, nullptr, 0ull, ~0ull, 0ull, d);
+  }
+  ctx->launches++;
   TFS_CUDA(ctx, cudaGetLastError());
   return TFS_OK;
 }

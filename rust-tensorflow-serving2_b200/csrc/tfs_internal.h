@@ -256,6 +256,7 @@ struct tfs_ctx {
   // small-batch decode plans its tables optimistically from what earlier batches on this context needed
   uint64_t dec_hint_tensors = 0, dec_hint_filters = 0, dec_hint_spans = 0, dec_hint_str = 0, dec_hint_blob = 0;
   bool copy_attr_set = false;
+  bool dec_spec_tma = false;  // the last planned decode on this ctx was all bulk copies: launch the TMA ring ahead of the sync next time
   uint32_t* d_ctrl = nullptr;  // 256 bytes of control words, zeroed once (grid-wide meeting counters that clear themselves)
   // single-walk decode plan: per-message quota slots, from what the largest message of earlier batches needed
   uint32_t dec_q_t = 4, dec_q_s = 8, dec_q_f = 2, dec_q_str = 256;
@@ -386,6 +387,11 @@ struct HostSeg {
 tfs_status_t launch_copy(tfs_ctx* ctx, const CopySeg* segs_dev, uint32_t n_segs, uint64_t n_tiles, const uint64_t* gate,
                          bool need_generic, const std::vector<HostSeg>* host_segs = nullptr, bool need_tma = true, int cast_kind = 0,
                          bool any_small = false);
+// The TMA ring launched BEFORE the host knows the counts (the single-walk decode plan): the kernel reads the number of
+// segments and tiles from device memory and does nothing unless *go != 0 (set by the plan kernel when the tables are final,
+// the pool is large enough and every copy segment is bound).  `many_segs` only picks the warp-cooperative variant.
+tfs_status_t launch_copy_tma_deferred(tfs_ctx* ctx, const CopySeg* segs_dev, const uint64_t* go, const uint64_t* n_segs_dev,
+                                      const uint64_t* n_tiles_dev, bool many_segs);
 
 inline uint64_t align_up(uint64_t v, uint64_t a) { return (v + a - 1) / a * a; }
 
