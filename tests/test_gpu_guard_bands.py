@@ -166,3 +166,66 @@ def test_decode_into_a_too_small_pool_writes_nothing(codec):
         assert e.value.status == abi.TFS_ERR_NOMEM, name
         codec.ctx.sync()
         assert bool((buf == CANARY).all()), f"{name}: values were written although the pool was too small"
+
+
+def test_tma_ring_queued_ahead_of_the_counts(codec):
+    """After a decode of bulk payloads the next plan queues the TMA copy kernel BEHIND the plan kernel, before the host has
+    seen the counts (tfs_decode.cu: launch_copy_tma_deferred); the kernel reads them from device memory and must stay idle
+    unless the plan ended well.  Sequences on ONE context: bulk -> bulk (the ring runs ahead), -> a pool that is too small
+    (nothing may be written), -> varint bodies (the plan stops early), -> tiny messages (no bulk at all), -> malformed
+    messages between good ones, -> bulk again; values against the oracle every time, canaries around every pool."""
+    import torch
+    rng = np.random.default_rng(4711)
+    fresh = tfs.GpuCodec(tfs.GpuContext(0))
+    dec = fresh.decoder()
+
+    def bulk(n_msgs, n):
+        return [tfs.PredictResponse([("y", tfs.TensorProto(dtype=1, tensor_shape=tfs.TensorShapeProto([n + i]),
+                                                            float_val=rng.standard_normal(n + i).astype(np.float32)))], tfs.ModelSpec("m", version=i))
+                for i in range(n_msgs)]
+
+    varint = [tfs.PredictResponse([("i", tfs.TensorProto(dtype=9, int64_val=rng.integers(-9, 1 << 40, 70_000, dtype=np.int64))),
+                                   ("y", tfs.TensorProto(dtype=1, float_val=rng.standard_normal(50_000).astype(np.float32)))]) for _ in range(5)]
+    tiny = [tfs.PredictResponse([("t", tfs.TensorProto(dtype=1, float_val=rng.standard_normal(3).astype(np.float32)))]) for _ in range(40)]
+    kind = abi.MSG_PREDICT_RESPONSE
+
+    def run(msgs, shrink=0, corrupt=()):
+        blobs = ob.encode_messages(msgs, kind)
+        blobs = [b[: len(b) // 2] if i in corrupt else b for i, b in enumerate(blobs)]
+        offs, lens, cur = [], [], 0
+        for b in blobs:
+            offs.append(cur)
+            lens.append(len(b))
+            cur += len(b)
+        wire = torch.from_numpy(np.frombuffer(b"".join(blobs), dtype=np.uint8).copy()).cuda()
+        d0 = dec.scan(wire, offs, lens, kind)
+        need = d0.pool_bytes
+        d0.close()
+        buf = torch.full((GUARD + need + GUARD,), CANARY, dtype=torch.uint8, device="cuda:0")
+        if shrink:
+            with pytest.raises(tfs.TfsError) as e:
+                dec.decode_into(wire, offs, lens, kind, buf[GUARD: GUARD + need - shrink])
+            assert e.value.status == abi.TFS_ERR_NOMEM
+            fresh.ctx.sync()
+            assert bool((buf == CANARY).all()), "values were written although the pool was too small"
+            return
+        d = dec.decode_into(wire, offs, lens, kind, buf[GUARD: GUARD + need])
+        fresh.ctx.sync()
+        host = buf.cpu().numpy()
+        assert (host[:GUARD] == CANARY).all() and (host[GUARD + need:] == CANARY).all()
+        st, want = ob.decode_bytes(blobs, kind)
+        helpers.assert_same_decoded_fast(want, d.messages(), "response", "ring ahead")
+        d.close()
+
+    try:
+        run(bulk(6, 300_000))
+        run(bulk(6, 300_000))                 # the ring is queued ahead from here on
+        run(bulk(5, 250_000), shrink=4096)    # ... and must not write into a pool that is too small
+        run(bulk(4, 200_000))
+        run(varint)                           # the plan kernel stops before the layout: no go
+        run(bulk(70, 40_000))                 # more than 64 segments: the warp-cooperative variant
+        run(bulk(3, 100_000), corrupt=(1,))   # a truncated message between good ones
+        run(tiny)                             # nothing for the ring to do
+        run(bulk(2, 2_000_000))
+    finally:
+        fresh.ctx.close()
